@@ -1,0 +1,517 @@
+"""Device-vs-fp32-reference numerics for every sm_100a kernel (pattern of the reference's
+GPU-vs-numpy oracle tests: veles/tests/test_mean_disp_normalizer.py:79-98,
+veles/tests/test_ocl_blas.py:58-109, veles/tests/test_random.py:120-148)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def K():
+    from veles_b200.ops import kernels
+    return kernels
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def rel_err(a, b):
+    a = a.float()
+    b = b.float()
+    return ((a - b).abs().max() / (b.abs().max() + 1e-12)).item()
+
+
+GEMM_SHAPES = [
+    (128, 128, 64), (128, 128, 256), (100, 100, 784), (256, 10, 100), (17, 231, 1999), (1, 8, 8),
+    (300, 4096, 512), (1024, 1000, 4096), (7777, 24, 216), (513, 257, 129 * 8),
+]
+
+
+@pytest.mark.parametrize("M,N,K_", GEMM_SHAPES)
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+def test_gemm_layouts(M, N, K_, a_mn, b_mn):
+    k = K()
+    torch.manual_seed(M * 7 + N * 3 + K_)
+    pad = lambda v: (v + 7) // 8 * 8
+    A = torch.randn(M, K_, device=dev())
+    B = torch.randn(N, K_, device=dev())
+    a_src = A.t().contiguous() if a_mn else A
+    b_src = B.t().contiguous() if b_mn else B
+    a = k.pitched_empty(a_src.shape[0], a_src.shape[1], torch.bfloat16, dev())
+    b = k.pitched_empty(b_src.shape[0], b_src.shape[1], torch.bfloat16, dev())
+    a.copy_(a_src)
+    b.copy_(b_src)
+    ref = (a.float().t() if a_mn else a.float()) @ (b.float() if b_mn else b.float().t())
+    out = k.pitched_empty(M, N, torch.float32, dev(), align=4)
+    out.fill_(float("nan"))
+    k.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all()
+    assert rel_err(out, ref) < 2e-3, (M, N, K_, a_mn, b_mn)
+
+
+@pytest.mark.parametrize("block_n", [64, 128, 256])
+def test_gemm_block_n_and_bf16_out(block_n):
+    k = K()
+    torch.manual_seed(block_n)
+    M, N, K_ = 384, 520, 328
+    a = torch.randn(M, K_, device=dev()).bfloat16()
+    b = torch.randn(N, K_, device=dev()).bfloat16()
+    out = torch.empty(M, N, device=dev(), dtype=torch.bfloat16)
+    k.gemm(a, b, out, block_n=block_n)
+    ref = a.float() @ b.float().t()
+    assert rel_err(out, ref) < 1e-2
+
+
+@pytest.mark.parametrize("act", [0, 1, 2, 3, 4])
+def test_gemm_bias_activation_epilogue(act):
+    k = K()
+    torch.manual_seed(act)
+    M, N, K_ = 200, 136, 192
+    a = (torch.randn(M, K_, device=dev()) * 0.2).bfloat16()
+    b = (torch.randn(N, K_, device=dev()) * 0.2).bfloat16()
+    bias = torch.randn(N, device=dev())
+    out = torch.empty(M, N, device=dev(), dtype=torch.float32)
+    k.gemm(a, b, out, bias=bias, act=act)
+    s = a.float() @ b.float().t() + bias
+    ref = [s, 1.7159 * torch.tanh(0.6666 * s), torch.sigmoid(s), torch.nn.functional.softplus(s), torch.relu(s)][act]
+    assert rel_err(out, ref) < 2e-3
+
+
+@pytest.mark.parametrize("deriv", [1, 2, 3, 4])
+def test_gemm_fused_activation_backward(deriv):
+    k = K()
+    torch.manual_seed(10 + deriv)
+    M, N, K_ = 130, 264, 96
+    a = (torch.randn(M, K_, device=dev()) * 0.3).bfloat16()
+    b = (torch.randn(K_, N, device=dev()) * 0.3).bfloat16()  # MN-major B: dX = dY * W
+    z = torch.rand(M, N, device=dev()).bfloat16()
+    out = torch.empty(M, N, device=dev(), dtype=torch.bfloat16)
+    k.gemm(a, b, out, b_mn=True, z=z, deriv=deriv)
+    zf = z.float()
+    d = {1: 0.6666 * (1.7159 - zf * zf / 1.7159), 2: zf * (1 - zf), 3: 1 - torch.exp(-zf), 4: (zf > 0).float()}[deriv]
+    ref = (a.float() @ b.float()) * d
+    assert rel_err(out, ref) < 1e-2
+
+
+def test_gemm_split_k_accumulate():
+    k = K()
+    torch.manual_seed(5)
+    M, N, K_ = 96, 200, 20000  # dW-like: tiny output, huge reduction
+    a = (torch.randn(K_, M, device=dev()) * 0.1).bfloat16()
+    b = (torch.randn(K_, N, device=dev()) * 0.1).bfloat16()
+    out = torch.zeros(M, N, device=dev(), dtype=torch.float32)
+    k.gemm(a, b, out, a_mn=True, b_mn=True, accumulate=True, split_k=32)
+    ref = a.float().t() @ b.float()
+    assert rel_err(out, ref) < 2e-3
+    k.gemm(a, b, out, a_mn=True, b_mn=True, accumulate=True, split_k=7, alpha=-1.0)
+    torch.cuda.synchronize()
+    assert out.abs().max().item() < 2e-2 * ref.abs().max().item()
+
+
+def test_gemm_column_slice_output_grouped_conv_style():
+    k = K()
+    torch.manual_seed(6)
+    M, Kg, Ng = 500, 200, 64
+    cols = torch.randn(M, 2 * Kg, device=dev()).bfloat16()
+    w = torch.randn(2 * Ng, Kg, device=dev()).bfloat16()
+    y = torch.zeros(M, 2 * Ng, device=dev(), dtype=torch.bfloat16)
+    bias = torch.randn(2 * Ng, device=dev())
+    for g in range(2):
+        k.gemm(cols[:, g * Kg:(g + 1) * Kg], w[g * Ng:(g + 1) * Ng], y[:, g * Ng:(g + 1) * Ng],
+               bias=bias[g * Ng:(g + 1) * Ng], act=4)
+    ref = torch.cat([torch.relu(cols[:, g * Kg:(g + 1) * Kg].float() @ w[g * Ng:(g + 1) * Ng].float().t()
+                                + bias[g * Ng:(g + 1) * Ng]) for g in range(2)], dim=1)
+    assert rel_err(y, ref) < 1e-2
+
+
+@pytest.mark.parametrize("src_dtype", [torch.uint8, torch.float32])
+@pytest.mark.parametrize("dst_dtype", [torch.float32, torch.bfloat16])
+def test_gather_minibatch(src_dtype, dst_dtype):
+    k = K()
+    g = torch.Generator(device="cpu").manual_seed(3)
+    n, size, mb, count = 1000, 3 * 32 * 32 + 3, 128, 100
+    if src_dtype == torch.uint8:
+        src = torch.randint(0, 256, (n, size), generator=g, dtype=torch.uint8).to(dev())
+    else:
+        src = torch.randn(n, size, generator=g).to(dev())
+    labels = torch.randint(0, 10, (n,), generator=g, dtype=torch.int32).to(dev())
+    idx = torch.randperm(n, generator=g).int().to(dev())
+    mean = torch.randn(size, generator=g).to(dev())
+    rdisp = (torch.rand(size, generator=g) + 0.5).to(dev())
+    dst = torch.full((mb + mb, size), float("nan"), device=dev(), dtype=dst_dtype)  # guard band (doubling_reset pattern)
+    mbl = torch.full((mb,), 77, device=dev(), dtype=torch.int32)
+    mbi = torch.full((mb,), 77, device=dev(), dtype=torch.int32)
+    start = 250
+    k.gather_minibatch(src, idx, start, count, dst[:mb], mean, rdisp, labels, mbl, mbi)
+    sel = idx[start:start + count].long()
+    ref = (src[sel].float() - mean) * rdisp
+    tol = 1e-5 if dst_dtype == torch.float32 else 1e-2
+    assert rel_err(dst[:count], ref) < tol
+    assert (dst[count:mb] == 0).all()
+    assert torch.isnan(dst[mb:].float()).all(), "kernel wrote past the minibatch"
+    assert (mbl[:count] == labels[sel]).all() and (mbl[count:] == -1).all()
+    assert (mbi[:count] == idx[start:start + count]).all() and (mbi[count:] == -1).all()
+
+
+def test_mean_disp_normalizer():
+    k = K()
+    g = torch.Generator(device="cpu").manual_seed(4)
+    inp = torch.randint(0, 256, (37, 3, 21, 20), generator=g, dtype=torch.uint8).to(dev())
+    mean = torch.rand(3 * 21 * 20, generator=g).to(dev()) * 255
+    rdisp = (torch.rand(3 * 21 * 20, generator=g) + 0.1).to(dev())
+    out = torch.empty(37, 3 * 21 * 20, device=dev())
+    k.mean_disp_normalize(inp, mean, rdisp, out)
+    ref = (inp.reshape(37, -1).float() - mean) * rdisp
+    assert (out - ref).abs().max().item() < 1e-4
+
+
+def test_copy_2d_joiner():
+    k = K()
+    a = torch.randn(50, 30, device=dev())
+    b = torch.randn(50, 17, device=dev())
+    out = torch.zeros(50, 47, device=dev())
+    k.copy_2d(a, out[:, :30])
+    k.copy_2d(b, out[:, 30:])
+    assert torch.equal(out, torch.cat([a, b], dim=1))
+
+
+@pytest.mark.parametrize("act", list(range(1, 9)))
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_activations(act, dtype):
+    k = K()
+    torch.manual_seed(act)
+    x = (torch.randn(1000, 33, device=dev()) * 2).to(dtype)
+    y = torch.empty_like(x)
+    factor = 0.37
+    k.activation_forward(act, x, y, factor)
+    xd = x.double().cpu().requires_grad_(True)
+    idx = torch.arange(xd.numel()).reshape(xd.shape) & 1
+
+    def f(v):
+        if act == 1: return 1.7159 * torch.tanh(0.6666 * v)
+        if act == 2: return torch.sigmoid(v)
+        if act == 3: return torch.nn.functional.softplus(v)
+        if act == 4: return torch.relu(v)
+        if act == 5: return torch.log(v + torch.sqrt(v * v + 1))
+        if act == 6:
+            d, a, b = 3.0, 0.242528761112, 305.459953195
+            inner = 1.7159 * torch.tanh(0.6666 * v)
+            return torch.where(v > d, torch.log(v.clamp(min=1e-9) * b) * a,
+                               torch.where(v < -d, -torch.log((-v).clamp(min=1e-9) * b) * a, inner))
+        if act == 7: return torch.where(idx == 1, torch.sin(v), torch.cos(v))
+        if act == 8: return v * factor
+    ref = f(xd)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert rel_err(y.cpu(), ref.detach()) < tol
+    eo = torch.randn_like(x)
+    ei = torch.empty_like(x)
+    k.activation_backward(act, eo, x, y, ei, factor)
+    (ref * eo.double().cpu()).sum().backward()
+    tolb = 2e-4 if dtype == torch.float32 else 6e-2
+    assert rel_err(ei.cpu(), xd.grad) < tolb
+
+
+def test_dropout_reproducible_mask_and_scale():
+    k = K()
+    torch.manual_seed(1)
+    n_states = 4096
+    st = torch.randint(1, 2 ** 62, (n_states, 2), dtype=torch.int64, device=dev())
+    st2 = torch.empty_like(st)
+    x = torch.randn(1001, 333, device=dev())
+    y = torch.empty_like(x)
+    k.dropout(x, y, st, st2, 0.5)
+    kept = (y != 0)
+    frac = kept.float().mean().item()
+    assert 0.48 < frac < 0.52
+    assert torch.allclose(y[kept], x[kept] * 2.0)
+    # backward with the saved states regenerates the identical mask
+    e = torch.ones_like(x)
+    ei = torch.empty_like(x)
+    k.dropout(e, ei, st, None, 0.5)
+    assert torch.equal(ei != 0, kept)
+    assert not torch.equal(st, st2)
+
+
+@pytest.mark.parametrize("solver", [0, 1, 2])
+def test_gd_update(solver):
+    k = K()
+    torch.manual_seed(solver)
+    n = 100003
+    w = torch.randn(n, device=dev())
+    g = torch.randn(n, device=dev())
+    v = torch.randn(n, device=dev()) * 0.1 if solver != 1 else torch.zeros(n, device=dev())
+    if solver == 2:
+        v = v.abs()
+    acc = torch.rand(n, device=dev())
+    wb = torch.empty(n, device=dev(), dtype=torch.bfloat16)
+    w0, g0, v0, a0 = w.clone(), g.clone(), v.clone(), acc.clone()
+    lr, wd, l12, mom, gs, eps, rho = 0.03, 0.0005, 0.3, 0.9, 0.5, 1e-6, 0.95
+    k.gd_update(w, g, v, acc, wb, lr=lr, wd=wd, l1_vs_l2=l12, moment=mom, grad_scale=gs, solver=solver, eps=eps,
+                rho=rho, zero_grad=True)
+    gg = g0 * gs + wd * ((1 - l12) * w0 + 0.5 * l12 * torch.sign(w0))
+    if solver == 0:
+        vr = mom * v0 - lr * gg
+        wr = w0 + vr
+        assert torch.allclose(v, vr, atol=1e-6)
+    elif solver == 1:
+        ar = a0 + gg * gg
+        wr = w0 - lr * gg / torch.sqrt(ar + eps)
+        assert torch.allclose(acc, ar, atol=1e-5)
+    else:
+        ar = rho * a0 + (1 - rho) * gg * gg
+        d = -torch.sqrt(v0 + eps) / torch.sqrt(ar + eps) * gg
+        wr = w0 + d
+    assert torch.allclose(w, wr, atol=1e-4, rtol=1e-4)
+    assert (g == 0).all()
+    assert torch.allclose(wb.float(), w, atol=1e-2, rtol=1e-2)
+
+
+def _conv_geom(H, W, ky, kx, sy, sx, pt, pl, pb, pr, groups=1):
+    OH = (H + pt + pb - ky) // sy + 1
+    OW = (W + pl + pr - kx) // sx + 1
+    return dict(OH=OH, OW=OW, ky=ky, kx=kx, sy=sy, sx=sx, pt=pt, pl=pl, groups=groups)
+
+
+@pytest.mark.parametrize("C,groups,k_,s_,p_", [(3, 1, 5, 1, 2), (16, 1, 3, 1, 1), (32, 2, 5, 2, 2), (3, 1, 11, 4, 0)])
+def test_im2col_col2im_match_unfold(C, groups, k_, s_, p_):
+    k = K()
+    torch.manual_seed(C)
+    B, H, W = 3, 19, 23
+    x = torch.randn(B, H, W, C, device=dev()).bfloat16()
+    geom = _conv_geom(H, W, k_, k_, s_, s_, p_, p_, p_, p_, groups)
+    rows = B * geom["OH"] * geom["OW"]
+    kc = k_ * k_ * C
+    pitch = (kc + 7) // 8 * 8
+    full = torch.full((rows, pitch), float("nan"), device=dev(), dtype=torch.bfloat16)
+    cols = full[:, :kc]
+    k.im2col(x, cols, geom)
+    # oracle: unfold on NCHW, reorder to (g, tap, cg)
+    un = torch.nn.functional.unfold(x.float().permute(0, 3, 1, 2), k_, padding=p_, stride=s_)  # [B, C*k*k, L]
+    Cg = C // groups
+    un = un.reshape(B, groups, Cg, k_ * k_, -1).permute(0, 4, 1, 3, 2).reshape(rows, kc)
+    assert torch.equal(cols.float(), un)
+    assert (full[:, kc:] == 0).all(), "K tail must be zero-filled"
+    # col2im == fold (adjoint of unfold)
+    dcols = torch.randn(rows, kc, device=dev()).bfloat16()
+    dfull = torch.zeros_like(full)
+    dfull[:, :kc] = dcols
+    dx = torch.empty_like(x)
+    k.col2im(dfull[:, :kc], dx, geom)
+    dun = dcols.float().reshape(B, -1, groups, k_ * k_, Cg).permute(0, 2, 4, 3, 1).reshape(B, C * k_ * k_, -1)
+    ref = torch.nn.functional.fold(dun, (H, W), k_, padding=p_, stride=s_).permute(0, 2, 3, 1)
+    assert rel_err(dx, ref) < 1e-2
+
+
+@pytest.mark.parametrize("kind", ["max", "maxabs", "avg"])
+@pytest.mark.parametrize("kx,sx", [(2, 2), (3, 2)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_pooling(kind, kx, sx, dtype):
+    k = K()
+    torch.manual_seed(kx)
+    B, H, W, C = 2, 13, 14, 24
+    x = torch.randn(B, H, W, C, device=dev()).to(dtype)
+    OH = (H - kx + sx - 1) // sx + 1 if (H - kx) % sx else (H - kx) // sx + 1
+    OW = (W - kx + sx - 1) // sx + 1 if (W - kx) % sx else (W - kx) // sx + 1
+    y = torch.empty(B, OH, OW, C, device=dev(), dtype=dtype)
+    offs = torch.empty(B, OH, OW, C, device=dev(), dtype=torch.int32)
+    kid = k.POOL_KINDS[kind]
+    k.pool_forward(kid, x, y, offs, kx, kx, sx, sx)
+    xf = x.float()
+    ref = torch.empty(B, OH, OW, C, device=dev())
+    dy = torch.randn(B, OH, OW, C, device=dev()).to(dtype)
+    dref = torch.zeros(B, H, W, C, device=dev())
+    for oh in range(OH):
+        for ow in range(OW):
+            win = xf[:, oh * sx:min(oh * sx + kx, H), ow * sx:min(ow * sx + kx, W), :]
+            wh, ww = win.shape[1], win.shape[2]
+            flat = win.reshape(B, wh * ww, C)
+            if kind == "avg":
+                ref[:, oh, ow] = flat.mean(1)
+                dref[:, oh * sx:oh * sx + wh, ow * sx:ow * sx + ww, :] += (dy[:, oh, ow].float() / (wh * ww))[:, None, None, :]
+            else:
+                key = flat.abs() if kind == "maxabs" else flat
+                am = key.argmax(1)
+                ref[:, oh, ow] = flat.gather(1, am[:, None, :])[:, 0]
+                hh = oh * sx + am // ww
+                wwi = ow * sx + am % ww
+                for b in range(B):
+                    dref[b, hh[b], wwi[b], torch.arange(C)] += dy[b, oh, ow].float()
+    assert rel_err(y, ref) < (1e-6 if dtype == torch.float32 else 8e-3)
+    dx = torch.empty_like(x)
+    k.pool_backward(kid, dy, offs, dx, kx, kx, sx, sx)
+    assert rel_err(dx, dref) < (1e-5 if dtype == torch.float32 else 2e-2)
+
+
+def test_stochastic_pooling_picks_window_member():
+    k = K()
+    torch.manual_seed(0)
+    B, H, W, C = 2, 8, 8, 16
+    x = torch.rand(B, H, W, C, device=dev())
+    y = torch.empty(B, 4, 4, C, device=dev())
+    offs = torch.empty(B, 4, 4, C, device=dev(), dtype=torch.int32)
+    rnd = torch.randint(0, 65536, (B, 4, 4, C), device=dev(), dtype=torch.int32).to(torch.int16)
+    k.pool_forward(3, x, y, offs, 2, 2, 2, 2, rnd)
+    assert torch.equal(x.flatten()[offs.long().flatten()], y.flatten())
+    mx = torch.nn.functional.max_pool2d(x.permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1)
+    assert (y <= mx + 1e-6).all() and (y < mx - 1e-6).any()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_lrn_forward_backward(dtype):
+    k = K()
+    torch.manual_seed(2)
+    B, H, W, C = 2, 5, 6, 32
+    n, alpha, beta, kk = 5, 1e-2, 0.75, 2.0
+    x = torch.randn(B, H, W, C, device=dev()).to(dtype)
+    y = torch.empty_like(x)
+    k.lrn_forward(x, y, n, alpha, beta, kk)
+    xr = x.double().requires_grad_(True)
+    sq = torch.nn.functional.pad(xr * xr, (n // 2, n // 2))
+    s = kk + alpha * sum(sq[..., i:i + C] for i in range(n))
+    ref = xr * s ** (-beta)
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(y, ref.detach()) < tol
+    dy = torch.randn_like(x)
+    dx = torch.empty_like(x)
+    k.lrn_backward(x, dy, dx, n, alpha, beta, kk)
+    (ref * dy.double()).sum().backward()
+    assert rel_err(dx, xr.grad) < (1e-4 if dtype == torch.float32 else 2e-2)
+
+
+@pytest.mark.parametrize("N", [10, 1000])
+@pytest.mark.parametrize("in_dtype", [torch.float32, torch.bfloat16])
+def test_softmax_evaluator(N, in_dtype):
+    k = K()
+    torch.manual_seed(N)
+    B, valid = 100, 91
+    s = (torch.randn(B, N, device=dev()) * 3).to(in_dtype)
+    labels = torch.randint(0, N, (B,), device=dev(), dtype=torch.int32)
+    labels[valid:] = -1
+    y = torch.empty(B, N, device=dev())
+    err = torch.empty(B, N, device=dev())
+    max_idx = torch.empty(B, device=dev(), dtype=torch.int32)
+    n_err = torch.zeros(2, device=dev(), dtype=torch.int32)
+    conf = torch.zeros(N, N, device=dev(), dtype=torch.int32)
+    mes = torch.zeros(1, device=dev())
+    loss = torch.zeros(1, device=dev())
+    k.softmax_eval(s, y, err, labels, max_idx, err_scale=1.0 / valid, n_err=n_err, confusion=conf, max_err_sum=mes,
+                   loss_sum=loss)
+    p = torch.softmax(s.float(), 1)
+    assert rel_err(y, p) < 1e-5
+    am = p.argmax(1)
+    assert torch.equal(max_idx.long(), am)
+    oh = torch.zeros(B, N, device=dev())
+    oh[torch.arange(valid), labels[:valid].long()] = 1
+    eref = (p - oh) / valid
+    eref[valid:] = 0
+    assert (err - eref).abs().max().item() < 1e-6
+    assert n_err[0].item() == (am[:valid] != labels[:valid].long()).sum().item()
+    assert n_err[1].item() == valid
+    cref = torch.zeros(N, N, device=dev(), dtype=torch.int32)
+    for i in range(valid):
+        cref[am[i], labels[i].long()] += 1
+    assert torch.equal(conf, cref)
+    assert abs(mes.item() - eref.abs().sum(1).max().item()) < 1e-6
+    lref = -torch.log(p[torch.arange(valid), labels[:valid].long()]).sum().item()
+    assert abs(loss.item() - lref) < 1e-3 * max(1.0, abs(lref))
+
+
+def test_mse_evaluator():
+    k = K()
+    torch.manual_seed(9)
+    B, valid, N = 64, 50, 77
+    y = torch.randn(B, N, device=dev())
+    t = torch.randn(B, N, device=dev())
+    err = torch.empty(B, N, device=dev())
+    metrics = torch.tensor([0.0, 0.0, 1e30], device=dev())
+    per = torch.empty(B, device=dev())
+    k.mse_eval(y, t, err, valid, err_scale=0.5, metrics=metrics, mse_per_sample=per)
+    e = (y - t)
+    e[valid:] = 0
+    rm = torch.sqrt((e * e).mean(1))
+    assert torch.allclose(err, e * 0.5, atol=1e-6)
+    assert abs(metrics[0].item() - rm[:valid].sum().item()) < 1e-3
+    assert abs(metrics[1].item() - rm[:valid].max().item()) < 1e-6
+    assert abs(metrics[2].item() - rm[:valid].min().item()) < 1e-6
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_matrix_reduce(dtype):
+    k = K()
+    torch.manual_seed(3)
+    a = torch.randn(777, 203, device=dev()).to(dtype)
+    rs = torch.empty(777, device=dev())
+    k.row_sum(a, rs)
+    assert rel_err(rs, a.float().sum(1)) < 1e-5
+    cs = torch.ones(203, device=dev())
+    scratch = torch.empty(k.col_sum_scratch_elems(777, 203), device=dev())
+    k.col_sum(a, cs, scratch, alpha=2.0, accumulate=True)
+    assert rel_err(cs, 1 + 2 * a.float().sum(0)) < 1e-5
+    k.col_sum(a, cs, scratch)
+    assert rel_err(cs, a.float().sum(0)) < 1e-5
+
+
+def _xs1024_oracle(states, rounds):
+    """Pure-numpy xorshift1024* with the reference's output interleaving."""
+    S = states.shape[0]
+    st = states.copy()
+    out = np.zeros(rounds * 16 * S, dtype=np.uint64)
+    mult = np.uint64(1181783497276652981)
+    with np.errstate(over="ignore"):
+        for r in range(rounds):
+            for i in range(16):
+                s0 = st[:, i].copy()
+                s1 = st[:, (i + 1) & 15].copy()
+                s1 ^= s1 << np.uint64(31)
+                s1 ^= s1 >> np.uint64(11)
+                s0 ^= s0 >> np.uint64(30)
+                v = s0 ^ s1
+                st[:, (i + 1) & 15] = v
+                out[(r * 16 + i) * S:(r * 16 + i + 1) * S] = v * mult
+    return out, st
+
+
+def test_xorshift1024star_bit_exact():
+    k = K()
+    rng = np.random.RandomState(7)
+    S, rounds = 256, 3
+    states = rng.randint(0, 2 ** 63, size=(S, 16), dtype=np.int64).astype(np.uint64)
+    ref, st_ref = _xs1024_oracle(states, rounds)
+    d_states = torch.from_numpy(states.view(np.int64).copy()).to(dev())
+    out = torch.empty(rounds * 16 * S, dtype=torch.int64, device=dev())
+    k.xorshift1024star(d_states, rounds, out)
+    assert np.array_equal(out.cpu().numpy().view(np.uint64), ref)
+    assert np.array_equal(d_states.cpu().numpy().view(np.uint64), st_ref)
+
+
+def test_xorshift128plus_bit_exact():
+    k = K()
+    rng = np.random.RandomState(8)
+    n = 5000
+    st = rng.randint(1, 2 ** 63, size=(n, 2), dtype=np.int64).astype(np.uint64)
+    d = torch.from_numpy(st.view(np.int64).copy()).to(dev())
+    out = torch.empty(n, dtype=torch.int64, device=dev())
+    k.xorshift128plus(d, out)
+    with np.errstate(over="ignore"):
+        s1 = st[:, 0].copy()
+        s0 = st[:, 1].copy()
+        s1 ^= s1 << np.uint64(23)
+        ny = s1 ^ s0 ^ (s1 >> np.uint64(17)) ^ (s0 >> np.uint64(26))
+        ref = ny + s0
+    assert np.array_equal(out.cpu().numpy().view(np.uint64), ref)
+    back = d.cpu().numpy().view(np.uint64)
+    assert np.array_equal(back[:, 0], s0) and np.array_equal(back[:, 1], ny)
+
+
+def test_fill_random_moments():
+    k = K()
+    st = torch.randint(1, 2 ** 62, (2048, 2), dtype=torch.int64, device=dev())
+    out = torch.empty(1_000_001, device=dev())
+    k.fill_random(st, out, 0, 0.05)
+    assert out.abs().max().item() <= 0.05 and abs(out.mean().item()) < 1e-3
+    assert abs(out.std().item() - 0.05 / 3 ** 0.5) < 1e-3
+    k.fill_random(st, out, 1, 0.01)
+    assert abs(out.mean().item()) < 1e-4 and abs(out.std().item() - 0.01) < 2e-4

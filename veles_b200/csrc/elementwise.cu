@@ -1,0 +1,442 @@
+// veles_b200 — memory-bound kernels: minibatch gather (+cast +normalise),
+// mean/dispersion normaliser, joiner copy, stand-alone activations, dropout
+// with in-kernel xorshift128+, and the single-GPU fused gradient-descent update.
+//
+// Reference kernels these replace (all plain one-thread-per-element SIMT):
+//   cuda/fullbatch_loader.cu:9-61   fill_minibatch_data_labels / fill_minibatch_target
+//   cuda/mean_disp_normalizer.cu:11-19  (launched with block (1,1,1))
+//   cuda/join.jcu:10-35             (one thread per sample, serial copy loop)
+// Znicz activation / dropout / gradient-descent kernels are absent from the
+// reference checkout; their semantics are pinned by
+// veles_b200/znicz/*_oracle numpy code.
+#include "common.cuh"
+
+namespace vb {
+
+enum DType : int { DT_F32 = 0, DT_BF16 = 1, DT_U8 = 2, DT_I32 = 3 };
+
+template <typename T> __device__ __forceinline__ float to_f(T v);
+template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_f<uint8_t>(uint8_t v) { return static_cast<float>(v); }
+
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16(v); }
+
+// ---------------------------------------------------------------------------
+// K1/K2/K4: gather rows by shuffled index, cast, optional (x - mean) * rdisp,
+// -1 / zero padding for the tail of a short minibatch.  One CTA per output row
+// group; each thread streams 4 consecutive elements so uint8 sources are read
+// as 32-bit words and fp32/bf16 destinations are written as 128/64-bit stores.
+// ---------------------------------------------------------------------------
+template <typename SRC, typename DST>
+__global__ void gather_rows_kernel(const SRC* __restrict__ src, long long src_ld,
+                                   const int* __restrict__ indices, int start, int count,
+                                   int max_rows, int row_size, DST* __restrict__ dst,
+                                   long long dst_ld, const float* __restrict__ mean,
+                                   const float* __restrict__ rdisp) {
+  const int row = blockIdx.y;
+  if (row >= max_rows) return;
+  DST* drow = dst + static_cast<long long>(row) * dst_ld;
+  const bool valid = row < count;
+  const SRC* srow = valid ? src + static_cast<long long>(indices[start + row]) * src_ld : nullptr;
+  for (int c = (blockIdx.x * blockDim.x + threadIdx.x) * 4; c < row_size; c += gridDim.x * blockDim.x * 4) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int cc = c + j;
+      if (cc < row_size) {
+        float v = 0.0f;
+        if (valid) {
+          v = to_f<SRC>(srow[cc]);
+          if (mean != nullptr) v = (v - mean[cc]) * rdisp[cc];
+        }
+        drow[cc] = from_f<DST>(v);
+      }
+    }
+  }
+}
+
+__global__ void gather_labels_kernel(const int* __restrict__ labels, const int* __restrict__ indices,
+                                     int start, int count, int max_rows, int* __restrict__ mb_labels,
+                                     int* __restrict__ mb_indices) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= max_rows) return;
+  if (i < count) {
+    const int idx = indices[start + i];
+    if (mb_indices) mb_indices[i] = idx;
+    if (mb_labels && labels) mb_labels[i] = labels[idx];
+  } else {
+    if (mb_indices) mb_indices[i] = -1;
+    if (mb_labels) mb_labels[i] = -1;
+  }
+}
+
+template <typename SRC>
+static int launch_gather(int dst_dtype, const void* src, long long src_ld, const int* indices, int start,
+                         int count, int max_rows, int row_size, void* dst, long long dst_ld,
+                         const float* mean, const float* rdisp, cudaStream_t s) {
+  dim3 block(256);
+  int gx = ceil_div(row_size, 256 * 4);
+  if (gx > 64) gx = 64;
+  dim3 grid(gx, max_rows);
+  if (dst_dtype == DT_F32)
+    gather_rows_kernel<SRC, float><<<grid, block, 0, s>>>(static_cast<const SRC*>(src), src_ld, indices, start, count,
+                                                          max_rows, row_size, static_cast<float*>(dst), dst_ld, mean, rdisp);
+  else
+    gather_rows_kernel<SRC, __nv_bfloat16><<<grid, block, 0, s>>>(static_cast<const SRC*>(src), src_ld, indices, start,
+                                                                  count, max_rows, row_size,
+                                                                  static_cast<__nv_bfloat16*>(dst), dst_ld, mean, rdisp);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Generic strided 2-D copy with cast (InputJoiner column blocks, pitch changes)
+// ---------------------------------------------------------------------------
+template <typename SRC, typename DST>
+__global__ void copy2d_kernel(const SRC* __restrict__ src, long long src_ld, DST* __restrict__ dst,
+                              long long dst_ld, int rows, int cols) {
+  const long long total = static_cast<long long>(rows) * cols;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / cols);
+    const int c = static_cast<int>(i - static_cast<long long>(r) * cols);
+    dst[r * dst_ld + c] = from_f<DST>(to_f<SRC>(src[r * src_ld + c]));
+  }
+}
+
+// ---------------------------------------------------------------------------
+// A1: stand-alone activations.  forward: y = f(x); backward: err_in = err_out * f'(.)
+// tanh/sigmoid/relu/strict-relu differentiate through the OUTPUT y; log, tanhlog,
+// sincos and mul differentiate through the INPUT x (Znicz activation units keep both).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float act_forward_full(int act, float x, float factor, int idx) {
+  switch (act) {
+    case ACT_LOG:
+      return logf(x + sqrtf(x * x + 1.0f));
+    case ACT_TANHLOG: {
+      // tanh branch inside |x| <= d, log continuation outside (d = 3, scaled tanh)
+      const float d = 3.0f, a = 0.242528761112f, b = 305.459953195f;
+      if (x > d) return logf(x * b) * a;
+      if (x < -d) return -logf(-x * b) * a;
+      return 1.7159f * tanhf(0.6666f * x);
+    }
+    case ACT_SINCOS:
+      return (idx & 1) ? sinf(x) : cosf(x);
+    case ACT_MUL:
+      return x * factor;
+    default:
+      return act_forward(act, x);
+  }
+}
+__device__ __forceinline__ float act_backward_full(int act, float x, float y, float factor, int idx) {
+  switch (act) {
+    case ACT_LOG:
+      return rsqrtf(x * x + 1.0f);
+    case ACT_TANHLOG: {
+      const float d = 3.0f, a = 0.242528761112f;
+      if (x > d || x < -d) return a / fabsf(x);
+      return y * y * (-0.388484177f) + 1.14381894f;
+    }
+    case ACT_SINCOS:
+      return (idx & 1) ? cosf(x) : -sinf(x);
+    case ACT_MUL:
+      return factor;
+    default:
+      return act_deriv_from_output(act, y);
+  }
+}
+
+template <typename T>
+__global__ void act_forward_kernel(int act, const T* __restrict__ x, T* __restrict__ y, long long n, float factor) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    y[i] = from_f<T>(act_forward_full(act, to_f<T>(x[i]), factor, static_cast<int>(i & 1)));
+}
+template <typename T>
+__global__ void act_backward_kernel(int act, const T* __restrict__ err_out, const T* __restrict__ x,
+                                    const T* __restrict__ y, T* __restrict__ err_in, long long n, float factor) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float xv = x ? to_f<T>(x[i]) : 0.0f;
+    const float yv = y ? to_f<T>(y[i]) : 0.0f;
+    err_in[i] = from_f<T>(to_f<T>(err_out[i]) * act_backward_full(act, xv, yv, factor, static_cast<int>(i & 1)));
+  }
+}
+
+// ---------------------------------------------------------------------------
+// D1: dropout.  Each thread owns one xorshift128+ state (reference generator:
+// cuda/random.cu:107-128) and walks a contiguous chunk; the 0/scale mask is
+// regenerated in backward from the saved pre-forward states, so neither random
+// bytes nor the mask ever reach HBM.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t xs128p_next(uint64_t& s0, uint64_t& s1) {
+  uint64_t x = s0;
+  const uint64_t y = s1;
+  s0 = y;
+  x ^= x << 23;
+  s1 = x ^ y ^ (x >> 17) ^ (y >> 26);
+  return s1 + y;
+}
+
+template <typename T>
+__global__ void dropout_kernel(const T* __restrict__ in, T* __restrict__ out, long long n,
+                               const ulonglong2* __restrict__ states_in, ulonglong2* __restrict__ states_out,
+                               int n_states, uint32_t threshold, float scale) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_states) return;
+  ulonglong2 st = states_in[t];
+  uint64_t s0 = st.x, s1 = st.y;
+  // interleaved assignment keeps the warp's accesses coalesced:
+  // element i is handled by thread (i / 2) % n_states, two per 64-bit draw
+  for (long long base = 2LL * t; base < n; base += 2LL * n_states) {
+    const uint64_t r = xs128p_next(s0, s1);
+    const uint32_t r0 = static_cast<uint32_t>(r), r1 = static_cast<uint32_t>(r >> 32);
+    out[base] = from_f<T>(r0 >= threshold ? to_f<T>(in[base]) * scale : 0.0f);
+    if (base + 1 < n) out[base + 1] = from_f<T>(r1 >= threshold ? to_f<T>(in[base + 1]) * scale : 0.0f);
+  }
+  if (states_out) states_out[t] = make_ulonglong2(s0, s1);
+}
+
+// ---------------------------------------------------------------------------
+// U1: fused Znicz gradient-descent step (is the world_size==1 case of C1).
+//   g   = grad*grad_scale + wd * ((1-l1_vs_l2)*W + 0.5*l1_vs_l2*sign(W))
+//   sgd     : v = moment*v - lr*g ;           W += v
+//   adagrad : G += g^2 ; W -= lr*g/sqrt(G+eps)
+//   adadelta: G = rho*G+(1-rho)g^2 ; d = -sqrt(v+eps)/sqrt(G+eps)*g ; v = rho*v+(1-rho)d^2 ; W += d
+// Also emits the bf16 shadow copy the next forward GEMM TMA-loads, and may zero
+// the fp32 gradient so split-K atomics can accumulate into it next step.
+// ---------------------------------------------------------------------------
+struct GDParams {
+  float lr, wd, l1_vs_l2, moment, grad_scale, eps, rho;
+  int solver;     // 0 sgd(+momentum), 1 adagrad, 2 adadelta
+  int zero_grad;  // write 0 back to grad after consuming it
+};
+
+__device__ __forceinline__ float gd_step(const GDParams& p, float w, float g, float& v, float& G) {
+  const float sgn = (w > 0.0f) ? 1.0f : ((w < 0.0f) ? -1.0f : 0.0f);
+  g = g * p.grad_scale + p.wd * ((1.0f - p.l1_vs_l2) * w + 0.5f * p.l1_vs_l2 * sgn);
+  if (p.solver == 0) {
+    v = p.moment * v - p.lr * g;
+    return w + v;
+  } else if (p.solver == 1) {
+    G += g * g;
+    return w - p.lr * g * rsqrtf(G + p.eps);
+  } else {
+    G = p.rho * G + (1.0f - p.rho) * g * g;
+    const float d = -sqrtf(v + p.eps) * rsqrtf(G + p.eps) * g;
+    v = p.rho * v + (1.0f - p.rho) * d * d;
+    return w + d;
+  }
+}
+
+__global__ void gd_update_kernel(float* __restrict__ w, float* __restrict__ grad, float* __restrict__ vel,
+                                 float* __restrict__ acc, __nv_bfloat16* __restrict__ w_bf16, long long n,
+                                 const GDParams p) {
+  const long long n4 = n >> 2;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float4 wv = reinterpret_cast<float4*>(w)[i];
+    float4 gv = reinterpret_cast<float4*>(grad)[i];
+    float4 vv = vel ? reinterpret_cast<float4*>(vel)[i] : make_float4(0, 0, 0, 0);
+    float4 av = acc ? reinterpret_cast<float4*>(acc)[i] : make_float4(0, 0, 0, 0);
+    wv.x = gd_step(p, wv.x, gv.x, vv.x, av.x);
+    wv.y = gd_step(p, wv.y, gv.y, vv.y, av.y);
+    wv.z = gd_step(p, wv.z, gv.z, vv.z, av.z);
+    wv.w = gd_step(p, wv.w, gv.w, vv.w, av.w);
+    reinterpret_cast<float4*>(w)[i] = wv;
+    if (vel) reinterpret_cast<float4*>(vel)[i] = vv;
+    if (acc) reinterpret_cast<float4*>(acc)[i] = av;
+    if (p.zero_grad) reinterpret_cast<float4*>(grad)[i] = make_float4(0, 0, 0, 0);
+    if (w_bf16) {
+      uint2 o;
+      o.x = pack_bf16x2(wv.x, wv.y);
+      o.y = pack_bf16x2(wv.z, wv.w);
+      reinterpret_cast<uint2*>(w_bf16)[i] = o;
+    }
+  }
+  // scalar tail
+  const long long tail0 = n4 << 2;
+  const long long t = tail0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (t < n) {
+    float vv = vel ? vel[t] : 0.0f, av = acc ? acc[t] : 0.0f;
+    const float nw = gd_step(p, w[t], grad[t], vv, av);
+    w[t] = nw;
+    if (vel) vel[t] = vv;
+    if (acc) acc[t] = av;
+    if (p.zero_grad) grad[t] = 0.0f;
+    if (w_bf16) w_bf16[t] = __float2bfloat16(nw);
+  }
+}
+
+// fp32 -> bf16 (weight shadow initialisation) and bf16 -> fp32
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[i] = __float2bfloat16(in[i]);
+}
+__global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ in, float* __restrict__ out, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[i] = __bfloat162float(in[i]);
+}
+
+static inline int grid_for(long long n, int block, int per_thread = 1) {
+  long long g = ceil_div_ll(n, static_cast<long long>(block) * per_thread);
+  const long long cap = static_cast<long long>(device_sm_count()) * 16;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+
+}  // namespace vb
+
+using namespace vb;
+
+extern "C" int vb_gather_minibatch(const void* src, int src_dtype, long long src_ld, const int* indices,
+                                   int start, int count, int max_rows, int row_size, void* dst,
+                                   int dst_dtype, long long dst_ld, const float* mean, const float* rdisp,
+                                   const int* labels, int* mb_labels, int* mb_indices, cudaStream_t s) {
+  VB_REQUIRE(count >= 0 && count <= max_rows, "vb_gather_minibatch: count %d out of [0,%d]", count, max_rows);
+  VB_REQUIRE(dst_dtype == DT_F32 || dst_dtype == DT_BF16, "vb_gather_minibatch: dst dtype must be f32/bf16");
+  if (max_rows == 0) return 0;
+  int rc;
+  switch (src_dtype) {
+    case DT_U8: rc = launch_gather<uint8_t>(dst_dtype, src, src_ld, indices, start, count, max_rows, row_size, dst, dst_ld, mean, rdisp, s); break;
+    case DT_F32: rc = launch_gather<float>(dst_dtype, src, src_ld, indices, start, count, max_rows, row_size, dst, dst_ld, mean, rdisp, s); break;
+    case DT_BF16: rc = launch_gather<__nv_bfloat16>(dst_dtype, src, src_ld, indices, start, count, max_rows, row_size, dst, dst_ld, mean, rdisp, s); break;
+    default: VB_REQUIRE(false, "vb_gather_minibatch: unsupported source dtype %d", src_dtype);
+  }
+  if (rc) return rc;
+  if (mb_labels || mb_indices) {
+    gather_labels_kernel<<<ceil_div(max_rows, 256), 256, 0, s>>>(labels, indices, start, count, max_rows, mb_labels, mb_indices);
+    VB_CHECK_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+namespace vb {
+template <typename SRC, typename DST>
+__global__ void mean_disp_kernel(const SRC* __restrict__ in, const float* __restrict__ mean,
+                                 const float* __restrict__ rdisp, DST* __restrict__ out, int batch, int size) {
+  const long long total = static_cast<long long>(batch) * size;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int j = static_cast<int>(i % size);
+    out[i] = from_f<DST>((to_f<SRC>(in[i]) - mean[j]) * rdisp[j]);
+  }
+}
+}  // namespace vb
+
+// out[i,j] = ((float)in[i,j] - mean[j]) * rdisp[j]   (ref: cuda/mean_disp_normalizer.cu:11-19)
+extern "C" int vb_mean_disp_normalize(const void* in, int in_dtype, const float* mean, const float* rdisp,
+                                      void* out, int out_dtype, int batch, int size, cudaStream_t s) {
+  const long long total = static_cast<long long>(batch) * size;
+  if (total == 0) return 0;
+  const int g = grid_for(total, 256, 4);
+#define VB_MD(SRC, DST) mean_disp_kernel<SRC, DST><<<g, 256, 0, s>>>(static_cast<const SRC*>(in), mean, rdisp, static_cast<DST*>(out), batch, size)
+  if (in_dtype == DT_U8 && out_dtype == DT_F32) VB_MD(uint8_t, float);
+  else if (in_dtype == DT_U8 && out_dtype == DT_BF16) VB_MD(uint8_t, __nv_bfloat16);
+  else if (in_dtype == DT_F32 && out_dtype == DT_F32) VB_MD(float, float);
+  else if (in_dtype == DT_F32 && out_dtype == DT_BF16) VB_MD(float, __nv_bfloat16);
+  else if (in_dtype == DT_BF16 && out_dtype == DT_BF16) VB_MD(__nv_bfloat16, __nv_bfloat16);
+  else if (in_dtype == DT_BF16 && out_dtype == DT_F32) VB_MD(__nv_bfloat16, float);
+  else VB_REQUIRE(false, "vb_mean_disp_normalize: unsupported dtype pair %d -> %d", in_dtype, out_dtype);
+#undef VB_MD
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_copy_2d(const void* src, int src_dtype, long long src_ld, void* dst, int dst_dtype,
+                          long long dst_ld, int rows, int cols, cudaStream_t s) {
+  const long long total = static_cast<long long>(rows) * cols;
+  if (total == 0) return 0;
+  const int g = grid_for(total, 256, 4);
+#define VB_CP(SRC, DST) copy2d_kernel<SRC, DST><<<g, 256, 0, s>>>(static_cast<const SRC*>(src), src_ld, static_cast<DST*>(dst), dst_ld, rows, cols)
+  if (src_dtype == DT_F32 && dst_dtype == DT_F32) VB_CP(float, float);
+  else if (src_dtype == DT_F32 && dst_dtype == DT_BF16) VB_CP(float, __nv_bfloat16);
+  else if (src_dtype == DT_BF16 && dst_dtype == DT_BF16) VB_CP(__nv_bfloat16, __nv_bfloat16);
+  else if (src_dtype == DT_BF16 && dst_dtype == DT_F32) VB_CP(__nv_bfloat16, float);
+  else if (src_dtype == DT_U8 && dst_dtype == DT_F32) VB_CP(uint8_t, float);
+  else if (src_dtype == DT_U8 && dst_dtype == DT_BF16) VB_CP(uint8_t, __nv_bfloat16);
+  else VB_REQUIRE(false, "vb_copy_2d: unsupported dtype pair %d -> %d", src_dtype, dst_dtype);
+#undef VB_CP
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_activation_forward(int act, const void* x, void* y, long long n, int dtype, float factor,
+                                     cudaStream_t s) {
+  if (n == 0) return 0;
+  const int g = grid_for(n, 256, 4);
+  if (dtype == DT_F32) act_forward_kernel<float><<<g, 256, 0, s>>>(act, static_cast<const float*>(x), static_cast<float*>(y), n, factor);
+  else if (dtype == DT_BF16) act_forward_kernel<__nv_bfloat16><<<g, 256, 0, s>>>(act, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), n, factor);
+  else VB_REQUIRE(false, "vb_activation_forward: dtype must be f32/bf16");
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_activation_backward(int act, const void* err_out, const void* x, const void* y, void* err_in,
+                                      long long n, int dtype, float factor, cudaStream_t s) {
+  if (n == 0) return 0;
+  const int g = grid_for(n, 256, 4);
+  if (dtype == DT_F32)
+    act_backward_kernel<float><<<g, 256, 0, s>>>(act, static_cast<const float*>(err_out), static_cast<const float*>(x),
+                                                 static_cast<const float*>(y), static_cast<float*>(err_in), n, factor);
+  else if (dtype == DT_BF16)
+    act_backward_kernel<__nv_bfloat16><<<g, 256, 0, s>>>(act, static_cast<const __nv_bfloat16*>(err_out),
+                                                         static_cast<const __nv_bfloat16*>(x),
+                                                         static_cast<const __nv_bfloat16*>(y),
+                                                         static_cast<__nv_bfloat16*>(err_in), n, factor);
+  else VB_REQUIRE(false, "vb_activation_backward: dtype must be f32/bf16");
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Dropout forward AND backward (backward = same call on err_output with the saved states).
+extern "C" int vb_dropout(const void* in, void* out, long long n, int dtype, const void* states_in,
+                          void* states_out, int n_states, float ratio, cudaStream_t s) {
+  if (n == 0) return 0;
+  VB_REQUIRE(ratio >= 0.0f && ratio < 1.0f, "vb_dropout: ratio must be in [0,1)");
+  const double th = static_cast<double>(ratio) * 4294967296.0;
+  const uint32_t threshold = th >= 4294967295.0 ? 0xFFFFFFFFu : static_cast<uint32_t>(th);
+  const float scale = 1.0f / (1.0f - ratio);
+  const int g = ceil_div(n_states, 128);
+  if (dtype == DT_F32)
+    dropout_kernel<float><<<g, 128, 0, s>>>(static_cast<const float*>(in), static_cast<float*>(out), n,
+                                            static_cast<const ulonglong2*>(states_in), static_cast<ulonglong2*>(states_out),
+                                            n_states, threshold, scale);
+  else if (dtype == DT_BF16)
+    dropout_kernel<__nv_bfloat16><<<g, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(in), static_cast<__nv_bfloat16*>(out), n,
+                                                    static_cast<const ulonglong2*>(states_in),
+                                                    static_cast<ulonglong2*>(states_out), n_states, threshold, scale);
+  else VB_REQUIRE(false, "vb_dropout: dtype must be f32/bf16");
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_gd_update(float* w, float* grad, float* vel, float* acc, void* w_bf16, long long n, float lr,
+                            float wd, float l1_vs_l2, float moment, float grad_scale, int solver, float eps,
+                            float rho, int zero_grad, cudaStream_t s) {
+  if (n == 0) return 0;
+  VB_REQUIRE((reinterpret_cast<uintptr_t>(w) & 15) == 0 && (reinterpret_cast<uintptr_t>(grad) & 15) == 0,
+             "vb_gd_update: weights/grad must be 16-byte aligned");
+  GDParams p{lr, wd, l1_vs_l2, moment, grad_scale, eps, rho, solver, zero_grad};
+  const int g = grid_for(n, 256, 4);
+  gd_update_kernel<<<g, 256, 0, s>>>(w, grad, vel, acc, static_cast<__nv_bfloat16*>(w_bf16), n, p);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_cast(const void* in, int in_dtype, void* out, int out_dtype, long long n, cudaStream_t s) {
+  if (n == 0) return 0;
+  const int g = grid_for(n, 256, 4);
+  if (in_dtype == DT_F32 && out_dtype == DT_BF16)
+    cast_f32_bf16_kernel<<<g, 256, 0, s>>>(static_cast<const float*>(in), static_cast<__nv_bfloat16*>(out), n);
+  else if (in_dtype == DT_BF16 && out_dtype == DT_F32)
+    cast_bf16_f32_kernel<<<g, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(in), static_cast<float*>(out), n);
+  else VB_REQUIRE(false, "vb_cast: unsupported dtype pair %d -> %d", in_dtype, out_dtype);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,432 @@
+// veles_b200 — tcgen05/TMEM/TMA GEMM family for sm_100a.
+//
+//   D[M,N] = epilogue( sum_k A(m,k) * B(n,k) )
+//
+// A and B are bf16 in global memory in either "K-major" (row-major [M,K] /
+// [N,K]) or "MN-major" (row-major [K,M] / [K,N]) storage, which covers the
+// three products a Znicz layer needs without ever materialising a transpose:
+//   forward      Y  = X  * W^T   (A K-major,  B K-major )   ref: znicz all2all (absent)
+//   backward-dX  dX = dY * W     (A K-major,  B MN-major)   ref: znicz gd err_input
+//   backward-dW  dW = dY^T * X   (A MN-major, B MN-major)   ref: znicz gd weights gradient
+// replacing the reference's cuBLAS sgemm/dgemm call sites
+// (veles/accelerated_units.py:761-766, veles/backends.py:829-836) and the
+// OpenCL tiled GEMM with its STORE_OUTPUT epilogue include
+// (ocl/matrix_multiplication_precise.cl:43-45).
+//
+// Kernel anatomy (one persistent CTA per SM, 192 threads):
+//   warp 0   : TMA producer   (cp.async.bulk.tensor -> 128B-swizzled smem ring)
+//   warp 1   : TMEM allocator + single-thread tcgen05.mma issuer
+//   warps 2-5: epilogue       (tcgen05.ld -> bias/activation/derivative -> global)
+// The fp32 accumulator lives in TMEM, double-buffered (2 x BN columns) so the
+// epilogue of tile i overlaps the mainloop of tile i+1.
+#include "common.cuh"
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+namespace vb {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int GEMM_THREADS = 192;
+
+struct GemmParams {
+  int M, N, K;
+  void* D;          // bf16 or fp32, row-major, leading dimension ldd (elements)
+  long long ldd;
+  const float* bias;  // [N] or null
+  int act;            // vb::Act applied to (acc*alpha + bias)
+  int out_fp32;       // 1: D is float, 0: D is bf16
+  int accumulate;     // 1: atomically add into fp32 D (split-K / gradient accumulation)
+  const __nv_bfloat16* Z;  // optional [M,N] saved activation output: D *= f'(Z)
+  long long ldz;
+  int deriv;          // vb::Act code of the derivative taken through Z
+  float alpha;
+  int split_k;
+  int m_blocks, n_blocks, k_blocks;
+};
+
+template <int BN>
+struct SmemLayout {
+  static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
+  static constexpr int B_BYTES = BN * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int BAR_BYTES = 1024;
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024 /*align slack*/;
+};
+
+__device__ __forceinline__ float4 ld_z8(const __nv_bfloat16* p) {
+  return *reinterpret_cast<const float4*>(p);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
+                         const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+  using L = SmemLayout<BN>;
+  constexpr int STAGES = L::STAGES;
+  constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* bar_base = smem + STAGES * L::STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bar_base);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);  // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+    fence_proxy_async_smem();
+  }
+  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  const int tiles_mn = p.m_blocks * p.n_blocks;
+  const int num_tiles = tiles_mn * p.split_k;
+  const int kb_per_split = (p.k_blocks + p.split_k - 1) / p.split_k;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int ks = tile / tiles_mn;
+        const int mn = tile - ks * tiles_mn;
+        const int mb = mn % p.m_blocks;
+        const int nb = mn / p.m_blocks;
+        const int kb0 = ks * kb_per_split;
+        const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * L::STAGE_BYTES;
+          uint8_t* sb = sa + L::A_BYTES;
+          mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
+          if (!A_MN) {
+            tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BLOCK_K, mb * BLOCK_M);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BLOCK_M / 64; ++c)
+              tma_load_2d(sa + c * (BLOCK_K * 128), &tma_a, &full_bar[stage],
+                          mb * BLOCK_M + c * 64, kb * BLOCK_K);
+          }
+          if (!B_MN) {
+            tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BLOCK_K, nb * BN);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c)
+              tma_load_2d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage], nb * BN + c * 64,
+                          kb * BLOCK_K);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc(/*BF16*/ 1, A_MN, B_MN, BLOCK_M, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int ks = tile / tiles_mn;
+      const int kb0 = ks * kb_per_split;
+      const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
+      if (kb0 >= kb1) continue;  // empty split: the epilogue writes zeros without TMEM
+      mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
+          const uint32_t sb = sa + L::A_BYTES;
+          // K-major : rows of 128 B, 8-row swizzle atoms 1024 B apart (SBO); k-step = +32 B.
+          // MN-major: 64-element column chunks BLOCK_K*128 B apart (LBO), 8 k-rows per
+          //           1024 B atom (SBO); k-step (16 rows) = +2048 B.
+          const uint64_t a_desc0 =
+              A_MN ? make_smem_desc_sw128(sa, BLOCK_K * 128, 1024) : make_smem_desc_sw128(sa, 16, 1024);
+          const uint64_t b_desc0 =
+              B_MN ? make_smem_desc_sw128(sb, BLOCK_K * 128, 1024) : make_smem_desc_sw128(sb, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((A_MN ? k * 2048 : k * 32) >> 4);
+            const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * 2048 : k * 32) >> 4);
+            umma_f16(d_tmem, a_desc, b_desc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          if (kb == kb1 - 1) umma_commit(&tmem_full[acc]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===================== Epilogue (warps 2..5) =====================
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int ks = tile / tiles_mn;
+      const int mn = tile - ks * tiles_mn;
+      const int mb = mn % p.m_blocks;
+      const int nb = mn / p.m_blocks;
+      const int kb0 = ks * kb_per_split;
+      const bool has_k = kb0 < p.k_blocks;
+      const bool add_bias = (p.bias != nullptr) && (ks == 0);
+      if (has_k) {
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tc_fence_after();
+      }
+      const int row = mb * BLOCK_M + quarter * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        const int col0 = nb * BN + c0;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t v[32];
+        if (has_k) {
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                            static_cast<uint32_t>(acc * BN + c0),
+                        v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if (row_ok) {
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+          const bool full = (col0 + 32 <= p.N);
+          if (add_bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (full || col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
+          }
+          if (p.act != ACT_LINEAR) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = act_forward(p.act, f[j]);
+          }
+          if (p.Z != nullptr) {
+            const __nv_bfloat16* zrow = p.Z + static_cast<long long>(row) * p.ldz + col0;
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                float4 z = ld_z8(zrow + j);
+                const uint32_t* zu = reinterpret_cast<const uint32_t*>(&z);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  f[j + 2 * q] *= act_deriv_from_output(p.deriv, bf16_lo(zu[q]));
+                  f[j + 2 * q + 1] *= act_deriv_from_output(p.deriv, bf16_hi(zu[q]));
+                }
+              }
+            } else {
+              for (int j = 0; j < 32 && col0 + j < p.N; ++j)
+                f[j] *= act_deriv_from_output(p.deriv, __bfloat162float(zrow[j]));
+            }
+          }
+          if (p.out_fp32) {
+            float* drow = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + col0;
+            if (p.accumulate) {
+              for (int j = 0; j < 32; ++j)
+                if (full || col0 + j < p.N) atomicAdd(drow + j, f[j]);
+            } else if (full && ((p.ldd & 3) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(drow + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+            } else {
+              for (int j = 0; j < 32 && col0 + j < p.N; ++j) drow[j] = f[j];
+            }
+          } else {
+            __nv_bfloat16* drow =
+                reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<long long>(row) * p.ldd + col0;
+            if (full && ((p.ldd & 7) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 o;
+                o.x = pack_bf16x2(f[j], f[j + 1]);
+                o.y = pack_bf16x2(f[j + 2], f[j + 3]);
+                o.z = pack_bf16x2(f[j + 4], f[j + 5]);
+                o.w = pack_bf16x2(f[j + 6], f[j + 7]);
+                *reinterpret_cast<uint4*>(drow + j) = o;
+              }
+            } else {
+              for (int j = 0; j < 32 && col0 + j < p.N; ++j) drow[j] = __float2bfloat16(f[j]);
+            }
+          }
+        }
+      }
+      if (has_k) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<TMEM_COLS>(tmem_base);
+  }
+}
+
+// ----------------------------------------------------------------------------
+// Host side: tensor-map construction (driver entry point fetched at run time so
+// the library never links libcuda) and launch.
+// ----------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+  });
+  return fn;
+}
+
+// 2-D bf16 tensor map with 128B swizzle: dims {inner, outer}, row pitch in elements.
+int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long long outer,
+                      long long pitch_elems, int box_inner, int box_outer) {
+  EncodeTiledFn fn = get_encode_fn();
+  VB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  VB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base pointer must be 16-byte aligned");
+  VB_REQUIRE((pitch_elems * 2) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes (ld %% 8 == 0), got %lld", pitch_elems);
+  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(outer)};
+  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(pitch_elems) * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  VB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%lld outer=%lld pitch=%lld box=%dx%d)",
+             static_cast<int>(r), inner, outer, pitch_elems, box_inner, box_outer);
+  return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
+                       cudaStream_t stream) {
+  using L = SmemLayout<BN>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    VB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    attr_set = true;
+  }
+  kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, p);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int BN>
+static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
+                          const GemmParams& p, int grid, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_gemm<BN, false, false>(ta, tb, p, grid, s);
+  if (!a_mn && b_mn) return launch_gemm<BN, false, true>(ta, tb, p, grid, s);
+  if (a_mn && !b_mn) return launch_gemm<BN, true, false>(ta, tb, p, grid, s);
+  return launch_gemm<BN, true, true>(ta, tb, p, grid, s);
+}
+
+}  // namespace vb
+
+using namespace vb;
+
+extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
+                            int b_mn_major, void* D, long long ldd, int M, int N, int K,
+                            const float* bias, int act, int out_fp32, int accumulate, const void* Z,
+                            long long ldz, int deriv, float alpha, int split_k, int block_n,
+                            cudaStream_t stream) {
+  VB_REQUIRE(M > 0 && N > 0 && K > 0, "vb_gemm_bf16: empty problem %dx%dx%d", M, N, K);
+  VB_REQUIRE(!(accumulate && !out_fp32), "vb_gemm_bf16: accumulate requires fp32 output");
+  VB_REQUIRE(split_k >= 1, "vb_gemm_bf16: split_k must be >= 1");
+  VB_REQUIRE(split_k == 1 || (accumulate && act == 0 && Z == nullptr),
+             "vb_gemm_bf16: split-K needs accumulate=1 and a linear epilogue");
+  int BN = block_n;
+  const int sms = device_sm_count();
+  if (BN == 0) {
+    if (N <= 64) BN = 64;
+    else if (N <= 128) BN = 128;
+    else {
+      const long long t256 = static_cast<long long>(ceil_div(M, BLOCK_M)) * ceil_div(N, 256);
+      BN = (t256 >= 2LL * sms) ? 256 : 128;
+    }
+  }
+  VB_REQUIRE(BN == 64 || BN == 128 || BN == 256, "vb_gemm_bf16: block_n must be 0/64/128/256");
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.D = D; p.ldd = ldd; p.bias = bias; p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.alpha = alpha;
+  p.m_blocks = ceil_div(M, BLOCK_M);
+  p.n_blocks = ceil_div(N, BN);
+  p.k_blocks = ceil_div(K, BLOCK_K);
+  if (split_k > p.k_blocks) split_k = p.k_blocks;
+  // make every split non-empty
+  {
+    int per = ceil_div(p.k_blocks, split_k);
+    split_k = ceil_div(p.k_blocks, per);
+  }
+  p.split_k = split_k;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_bf16_2d(&ta, A, K, M, lda, BLOCK_K, BLOCK_M);
+  else rc = make_tmap_bf16_2d(&ta, A, M, K, lda, 64, BLOCK_K);
+  if (rc) return rc;
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BLOCK_K, BN);
+  else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BLOCK_K);
+  if (rc) return rc;
+  const long long tiles = static_cast<long long>(p.m_blocks) * p.n_blocks * p.split_k;
+  const int grid = static_cast<int>(tiles < sms ? tiles : sms);
+  switch (BN) {
+    case 64: return dispatch_major<64>(a_mn_major, b_mn_major, ta, tb, p, grid, stream);
+    case 128: return dispatch_major<128>(a_mn_major, b_mn_major, ta, tb, p, grid, stream);
+    default: return dispatch_major<256>(a_mn_major, b_mn_major, ta, tb, p, grid, stream);
+  }
+}

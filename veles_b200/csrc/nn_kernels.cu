@@ -1,0 +1,603 @@
+// veles_b200 — spatial / reduction kernels of the Znicz layer set, NHWC layout:
+// im2col / col2im ("unpack" for the conv GEMMs), max / maxabs / avg / stochastic
+// pooling forward+backward, cross-channel LRN forward+backward, fused softmax +
+// evaluator, MSE evaluator, row/column reductions.
+//
+// The Znicz sources are absent from the reference checkout; layer
+// semantics follow docs/source/manualrst_veles_workflow_parameters.rst:469-541
+// and are pinned by the numpy oracles in veles_b200/znicz/.  matrix_reduce
+// replaces cuda/matrix_reduce.cu:35-81 (shared-memory tree) with warp shuffles.
+#include "common.cuh"
+
+namespace vb {
+
+enum DType2 : int { D_F32 = 0, D_BF16 = 1 };
+
+template <typename T> __device__ __forceinline__ float ldf(const T* p);
+template <> __device__ __forceinline__ float ldf<float>(const float* p) { return *p; }
+template <> __device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+template <typename T> __device__ __forceinline__ void stf(T* p, float v);
+template <> __device__ __forceinline__ void stf<float>(float* p, float v) { *p = v; }
+template <> __device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16(v); }
+
+static inline int grid_cap(long long n, int block) {
+  long long g = (n + block - 1) / block;
+  const long long cap = static_cast<long long>(device_sm_count()) * 32;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+
+// ---------------------------------------------------------------------------
+// im2col: x[B,H,W,C] -> cols[B*OH*OW, ld] with column index
+//   g*(ky*kx*Cg) + (i*kx + j)*Cg + cg        (c = g*Cg + cg)
+// Vectorised over 8 channels (16 B) when Cg % 8 == 0, scalar otherwise.
+// Columns in [groups*ky*kx*Cg, ld) are zero-filled so the GEMM's K tail is clean.
+// ---------------------------------------------------------------------------
+struct ConvGeom {
+  int B, H, W, C, OH, OW, ky, kx, sy, sx, pt, pl, groups;
+  long long ld;  // row pitch of cols (elements)
+};
+
+__global__ void im2col_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols,
+                                   const ConvGeom g) {
+  const int Cg = g.C / g.groups;
+  const int kk = g.ky * g.kx;
+  const int vec_per_row = static_cast<int>(g.ld >> 3);
+  const int used = g.groups * kk * Cg;
+  const long long rows = static_cast<long long>(g.B) * g.OH * g.OW;
+  const long long total = rows * vec_per_row;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = t / vec_per_row;
+    const int col = static_cast<int>(t - row * vec_per_row) << 3;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (col < used) {
+      const int grp = col / (kk * Cg);
+      const int rem = col - grp * kk * Cg;
+      const int tap = rem / Cg;
+      const int cg = rem - tap * Cg;
+      const int i = tap / g.kx, j = tap - i * g.kx;
+      const int ow = static_cast<int>(row % g.OW);
+      const long long r2 = row / g.OW;
+      const int oh = static_cast<int>(r2 % g.OH);
+      const int b = static_cast<int>(r2 / g.OH);
+      const int ih = oh * g.sy - g.pt + i, iw = ow * g.sx - g.pl + j;
+      if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W)
+        v = *reinterpret_cast<const uint4*>(x + ((static_cast<long long>(b) * g.H + ih) * g.W + iw) * g.C + grp * Cg + cg);
+    }
+    *reinterpret_cast<uint4*>(cols + row * g.ld + col) = v;
+  }
+}
+
+__global__ void im2col_scalar_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols,
+                                     const ConvGeom g) {
+  const int Cg = g.C / g.groups;
+  const int kk = g.ky * g.kx;
+  const int used = g.groups * kk * Cg;
+  const long long rows = static_cast<long long>(g.B) * g.OH * g.OW;
+  const long long total = rows * g.ld;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = t / g.ld;
+    const int col = static_cast<int>(t - row * g.ld);
+    __nv_bfloat16 v = __float2bfloat16(0.0f);
+    if (col < used) {
+      const int grp = col / (kk * Cg);
+      const int rem = col - grp * kk * Cg;
+      const int tap = rem / Cg;
+      const int cg = rem - tap * Cg;
+      const int i = tap / g.kx, j = tap - i * g.kx;
+      const int ow = static_cast<int>(row % g.OW);
+      const long long r2 = row / g.OW;
+      const int oh = static_cast<int>(r2 % g.OH);
+      const int b = static_cast<int>(r2 / g.OH);
+      const int ih = oh * g.sy - g.pt + i, iw = ow * g.sx - g.pl + j;
+      if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W)
+        v = x[((static_cast<long long>(b) * g.H + ih) * g.W + iw) * g.C + grp * Cg + cg];
+    }
+    cols[t] = v;
+  }
+}
+
+// col2im in gather form (deterministic, no atomics, no pre-zeroing):
+// dx[b,ih,iw,c] = sum over taps (i,j) with (ih+pt-i) % sy == 0 ... of dcols[row(oh,ow), col(i,j,c)]
+// optional fused activation derivative through the saved forward output z of the
+// PREVIOUS layer (dx *= f'(z)), which is what Znicz GD units apply to err_output.
+__global__ void col2im_kernel(const __nv_bfloat16* __restrict__ dcols, __nv_bfloat16* __restrict__ dx,
+                              const ConvGeom g, const __nv_bfloat16* __restrict__ z, int deriv) {
+  const int Cg = g.C / g.groups;
+  const int kk = g.ky * g.kx;
+  const long long total = static_cast<long long>(g.B) * g.H * g.W * g.C;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % g.C);
+    long long r = t / g.C;
+    const int iw = static_cast<int>(r % g.W);
+    r /= g.W;
+    const int ih = static_cast<int>(r % g.H);
+    const int b = static_cast<int>(r / g.H);
+    const int grp = c / Cg, cg = c - grp * Cg;
+    float acc = 0.0f;
+    for (int i = 0; i < g.ky; ++i) {
+      const int nh = ih + g.pt - i;
+      if (nh < 0 || nh % g.sy) continue;
+      const int oh = nh / g.sy;
+      if (oh >= g.OH) continue;
+      for (int j = 0; j < g.kx; ++j) {
+        const int nw = iw + g.pl - j;
+        if (nw < 0 || nw % g.sx) continue;
+        const int ow = nw / g.sx;
+        if (ow >= g.OW) continue;
+        const long long row = (static_cast<long long>(b) * g.OH + oh) * g.OW + ow;
+        acc += __bfloat162float(dcols[row * g.ld + grp * kk * Cg + (i * g.kx + j) * Cg + cg]);
+      }
+    }
+    if (z != nullptr) acc *= act_deriv_from_output(deriv, __bfloat162float(z[t]));
+    dx[t] = __float2bfloat16(acc);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Pooling (NHWC).  kind: 0 max, 1 maxabs, 2 avg, 3 stochastic, 4 stochastic-abs.
+// Windows are clipped at the right/bottom border (Znicz semantics: the last
+// window may be partial).  `offs` records the flat input index of the chosen
+// element for max-like kinds so backward is an exact routing.
+// ---------------------------------------------------------------------------
+struct PoolGeom {
+  int B, H, W, C, OH, OW, ky, kx, sy, sx;
+};
+
+template <typename T>
+__global__ void pool_forward_kernel(int kind, const T* __restrict__ x, T* __restrict__ y, int* __restrict__ offs,
+                                    const PoolGeom g, const uint16_t* __restrict__ rnd) {
+  const long long total = static_cast<long long>(g.B) * g.OH * g.OW * g.C;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % g.C);
+    long long r = t / g.C;
+    const int ow = static_cast<int>(r % g.OW);
+    r /= g.OW;
+    const int oh = static_cast<int>(r % g.OH);
+    const int b = static_cast<int>(r / g.OH);
+    const int h0 = oh * g.sy, w0 = ow * g.sx;
+    const int h1 = min(h0 + g.ky, g.H), w1 = min(w0 + g.kx, g.W);
+    const long long base = static_cast<long long>(b) * g.H * g.W * g.C + c;
+    if (kind == 2) {
+      float s = 0.0f;
+      for (int h = h0; h < h1; ++h)
+        for (int w = w0; w < w1; ++w) s += ldf<T>(x + base + (static_cast<long long>(h) * g.W + w) * g.C);
+      stf<T>(y + t, s / static_cast<float>((h1 - h0) * (w1 - w0)));
+    } else if (kind <= 1) {
+      float best = 0.0f, bestkey = -INFINITY;
+      long long bo = base + (static_cast<long long>(h0) * g.W + w0) * g.C;
+      for (int h = h0; h < h1; ++h)
+        for (int w = w0; w < w1; ++w) {
+          const long long o = base + (static_cast<long long>(h) * g.W + w) * g.C;
+          const float v = ldf<T>(x + o);
+          const float key = kind == 1 ? fabsf(v) : v;
+          if (key > bestkey) {
+            bestkey = key;
+            best = v;
+            bo = o;
+          }
+        }
+      stf<T>(y + t, best);
+      if (offs) offs[t] = static_cast<int>(bo);
+    } else {
+      // stochastic: pick element with probability proportional to max(v,0) (or |v|)
+      float sum = 0.0f;
+      for (int h = h0; h < h1; ++h)
+        for (int w = w0; w < w1; ++w) {
+          const float v = ldf<T>(x + base + (static_cast<long long>(h) * g.W + w) * g.C);
+          sum += kind == 4 ? fabsf(v) : fmaxf(v, 0.0f);
+        }
+      const float pos = sum * (static_cast<float>(rnd[t]) * (1.0f / 65536.0f));
+      float run = 0.0f, best = 0.0f;
+      long long bo = base + (static_cast<long long>(h0) * g.W + w0) * g.C;
+      bool found = false;
+      for (int h = h0; h < h1 && !found; ++h)
+        for (int w = w0; w < w1; ++w) {
+          const long long o = base + (static_cast<long long>(h) * g.W + w) * g.C;
+          const float v = ldf<T>(x + o);
+          run += kind == 4 ? fabsf(v) : fmaxf(v, 0.0f);
+          if (sum > 0.0f && pos <= run) {
+            best = v;
+            bo = o;
+            found = true;
+            break;
+          }
+        }
+      stf<T>(y + t, best);
+      if (offs) offs[t] = static_cast<int>(bo);
+    }
+  }
+}
+
+// Backward, gather form: every input element scans the (few) windows covering it.
+template <typename T>
+__global__ void pool_backward_kernel(int kind, const T* __restrict__ dy, const int* __restrict__ offs,
+                                     T* __restrict__ dx, const PoolGeom g) {
+  const long long total = static_cast<long long>(g.B) * g.H * g.W * g.C;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % g.C);
+    long long r = t / g.C;
+    const int w = static_cast<int>(r % g.W);
+    r /= g.W;
+    const int h = static_cast<int>(r % g.H);
+    const int b = static_cast<int>(r / g.H);
+    const int oh_lo = max(0, (h - g.ky + g.sy) / g.sy), oh_hi = min(g.OH - 1, h / g.sy);
+    const int ow_lo = max(0, (w - g.kx + g.sx) / g.sx), ow_hi = min(g.OW - 1, w / g.sx);
+    float acc = 0.0f;
+    for (int oh = oh_lo; oh <= oh_hi; ++oh)
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        const long long o = ((static_cast<long long>(b) * g.OH + oh) * g.OW + ow) * g.C + c;
+        if (kind == 2) {
+          const int hh = min(oh * g.sy + g.ky, g.H) - oh * g.sy, ww = min(ow * g.sx + g.kx, g.W) - ow * g.sx;
+          acc += ldf<T>(dy + o) / static_cast<float>(hh * ww);
+        } else if (offs[o] == static_cast<int>(t)) {
+          acc += ldf<T>(dy + o);
+        }
+      }
+    stf<T>(dx + t, acc);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// LRN across channels (AlexNet): y = x * (k + alpha * sum_{window n} x^2)^(-beta)
+// One thread per element; the n-wide window is re-read through L1 (channels are
+// contiguous in NHWC).  Backward follows the closed form
+//   dx_i = dy_i * s_i^-beta - 2*alpha*beta * x_i * sum_{j: i in win(j)} dy_j * x_j * s_j^(-beta-1)
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void lrn_forward_kernel(const T* __restrict__ x, T* __restrict__ y, long long pixels, int C, int n,
+                                   float alpha, float beta, float k) {
+  const long long total = pixels * C;
+  const int half = n / 2;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % C);
+    const T* px = x + (t - c);
+    float s = 0.0f;
+    const int lo = max(0, c - half), hi = min(C - 1, c + half);
+    for (int j = lo; j <= hi; ++j) {
+      const float v = ldf<T>(px + j);
+      s += v * v;
+    }
+    s = k + alpha * s;
+    stf<T>(y + t, ldf<T>(px + c) * __powf(s, -beta));
+  }
+}
+
+template <typename T>
+__global__ void lrn_backward_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __restrict__ dx,
+                                    long long pixels, int C, int n, float alpha, float beta, float k) {
+  const long long total = pixels * C;
+  const int half = n / 2;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % C);
+    const T* px = x + (t - c);
+    const T* pdy = dy + (t - c);
+    const int lo = max(0, c - half), hi = min(C - 1, c + half);
+    float acc = 0.0f, si = 0.0f;
+    for (int j = lo; j <= hi; ++j) {
+      // s_j over its own window
+      const int lo2 = max(0, j - half), hi2 = min(C - 1, j + half);
+      float s = 0.0f;
+      for (int q = lo2; q <= hi2; ++q) {
+        const float v = ldf<T>(px + q);
+        s += v * v;
+      }
+      s = k + alpha * s;
+      if (j == c) si = s;
+      acc += ldf<T>(pdy + j) * ldf<T>(px + j) * __powf(s, -beta - 1.0f);
+    }
+    const float xi = ldf<T>(px + c);
+    stf<T>(dx + t, ldf<T>(pdy + c) * __powf(si, -beta) - 2.0f * alpha * beta * xi * acc);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// S1: softmax + argmax + EvaluatorSoftmax in one pass, one warp per sample.
+//   y = softmax(s)              max_idx[b] = argmax
+//   err_output = (y - onehot(label)) * err_scale for label >= 0, else 0
+//   n_err[0] += (argmax != label), n_err[1] += valid; confusion[argmax*N + label]++
+//   max_err_sum = max over samples of sum_j |err_output|; loss_sum += -log(y[label])
+// ---------------------------------------------------------------------------
+template <typename TIN, typename TOUT>
+__global__ void softmax_eval_kernel(const TIN* __restrict__ s, long long lds, TOUT* __restrict__ y, long long ldy,
+                                    TOUT* __restrict__ err, long long lde, const int* __restrict__ labels,
+                                    int* __restrict__ max_idx, int batch, int N, float err_scale,
+                                    int* __restrict__ n_err, int* __restrict__ confusion,
+                                    float* __restrict__ max_err_sum, float* __restrict__ loss_sum) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= batch) return;
+  const TIN* row = s + static_cast<long long>(warp) * lds;
+  float m = -INFINITY;
+  int mi = 0;
+  for (int j = lane; j < N; j += 32) {
+    const float v = ldf<TIN>(row + j);
+    if (v > m) {
+      m = v;
+      mi = j;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, mi, o);
+    if (om > m || (om == m && oi < mi)) {
+      m = om;
+      mi = oi;
+    }
+  }
+  float sum = 0.0f;
+  for (int j = lane; j < N; j += 32) sum += __expf(ldf<TIN>(row + j) - m);
+  sum = warp_sum(sum);
+  const float inv = 1.0f / sum;
+  const int label = labels ? labels[warp] : -1;
+  float esum = 0.0f;
+  for (int j = lane; j < N; j += 32) {
+    const float p = __expf(ldf<TIN>(row + j) - m) * inv;
+    if (y) stf<TOUT>(y + static_cast<long long>(warp) * ldy + j, p);
+    if (err) {
+      const float e = label >= 0 ? (p - (j == label ? 1.0f : 0.0f)) * err_scale : 0.0f;
+      stf<TOUT>(err + static_cast<long long>(warp) * lde + j, e);
+      esum += fabsf(e);
+    }
+  }
+  esum = warp_sum(esum);
+  if (lane == 0) {
+    if (max_idx) max_idx[warp] = mi;
+    if (label >= 0) {
+      if (n_err) {
+        if (mi != label) atomicAdd(n_err, 1);
+        atomicAdd(n_err + 1, 1);
+      }
+      if (confusion) atomicAdd(confusion + mi * N + label, 1);
+      if (max_err_sum) atomicMax(reinterpret_cast<int*>(max_err_sum), __float_as_int(esum));  // esum >= 0
+      if (loss_sum) {
+        const float pl = __expf(ldf<TIN>(row + label) - m) * inv;
+        atomicAdd(loss_sum, -__logf(fmaxf(pl, 1e-30f)));
+      }
+    }
+  }
+}
+
+// EvaluatorMSE: err = (y - target) * err_scale for valid rows (row < batch_valid);
+// metrics[0] += sum_b rmse_b, metrics[1] = max rmse_b, metrics[2] = min rmse_b.
+template <typename T>
+__global__ void mse_eval_kernel(const T* __restrict__ y, long long ldy, const T* __restrict__ target, long long ldt,
+                                T* __restrict__ err, long long lde, int batch, int batch_valid, int N,
+                                float err_scale, float* __restrict__ metrics, float* __restrict__ mse_per_sample) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= batch) return;
+  const bool valid = warp < batch_valid;
+  float ss = 0.0f;
+  for (int j = lane; j < N; j += 32) {
+    float e = 0.0f;
+    if (valid) e = ldf<T>(y + static_cast<long long>(warp) * ldy + j) - ldf<T>(target + static_cast<long long>(warp) * ldt + j);
+    ss += e * e;
+    if (err) stf<T>(err + static_cast<long long>(warp) * lde + j, e * err_scale);
+  }
+  ss = warp_sum(ss);
+  if (lane == 0) {
+    const float rmse = sqrtf(ss / static_cast<float>(N));
+    if (mse_per_sample) mse_per_sample[warp] = valid ? rmse : 0.0f;
+    if (valid && metrics) {
+      atomicAdd(metrics, rmse);
+      atomicMax(reinterpret_cast<int*>(metrics + 1), __float_as_int(rmse));
+      atomicMin(reinterpret_cast<int*>(metrics + 2), __float_as_int(rmse));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// R1: matrix_reduce.  Row sums: one warp per row.  Column sums (bias gradient
+// = sum over the batch of err_output): two-phase — a 2-D grid writes per-slab
+// partial sums into `scratch[slabs, cols]`, then one pass folds the slabs.
+// Deterministic (no atomics).
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void row_sum_kernel(const T* __restrict__ a, long long lda, int rows, int cols, float* __restrict__ out) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  float s = 0.0f;
+  for (int j = lane; j < cols; j += 32) s += ldf<T>(a + static_cast<long long>(warp) * lda + j);
+  s = warp_sum(s);
+  if (lane == 0) out[warp] = s;
+}
+
+constexpr int COLSUM_ROWS_PER_SLAB = 64;
+
+template <typename T>
+__global__ void col_sum_partial_kernel(const T* __restrict__ a, long long lda, int rows, int cols,
+                                       float* __restrict__ scratch) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  const int slab = blockIdx.y;
+  if (col >= cols) return;
+  const int r0 = slab * COLSUM_ROWS_PER_SLAB, r1 = min(rows, r0 + COLSUM_ROWS_PER_SLAB);
+  float s = 0.0f;
+  for (int r = r0; r < r1; ++r) s += ldf<T>(a + static_cast<long long>(r) * lda + col);
+  scratch[static_cast<long long>(slab) * cols + col] = s;
+}
+
+__global__ void col_sum_final_kernel(const float* __restrict__ scratch, int slabs, int cols, float* __restrict__ out,
+                                     float alpha, int accumulate) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= cols) return;
+  float s = 0.0f;
+  for (int k = 0; k < slabs; ++k) s += scratch[static_cast<long long>(k) * cols + col];
+  s *= alpha;
+  out[col] = accumulate ? out[col] + s : s;
+}
+
+}  // namespace vb
+
+using namespace vb;
+
+static int check_geom(const ConvGeom& g) {
+  VB_REQUIRE(g.groups >= 1 && g.C % g.groups == 0, "conv: channels %d not divisible by groups %d", g.C, g.groups);
+  VB_REQUIRE(g.ld >= static_cast<long long>(g.ky) * g.kx * g.C, "conv: cols pitch %lld < ky*kx*C", g.ld);
+  return 0;
+}
+
+extern "C" int vb_im2col(const void* x, void* cols, int B, int H, int W, int C, int OH, int OW, int ky, int kx,
+                         int sy, int sx, int pad_top, int pad_left, int groups, long long ld, cudaStream_t s) {
+  ConvGeom g{B, H, W, C, OH, OW, ky, kx, sy, sx, pad_top, pad_left, groups, ld};
+  if (int rc = check_geom(g)) return rc;
+  const long long rows = static_cast<long long>(B) * OH * OW;
+  if (rows == 0) return 0;
+  const int Cg = C / groups;
+  if (Cg % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(cols) & 15) == 0) {
+    const long long total = rows * (ld >> 3);
+    im2col_vec8_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), g);
+  } else {
+    const long long total = rows * ld;
+    im2col_scalar_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), g);
+  }
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_col2im(const void* dcols, void* dx, int B, int H, int W, int C, int OH, int OW, int ky, int kx,
+                         int sy, int sx, int pad_top, int pad_left, int groups, long long ld, const void* z,
+                         int deriv, cudaStream_t s) {
+  ConvGeom g{B, H, W, C, OH, OW, ky, kx, sy, sx, pad_top, pad_left, groups, ld};
+  if (int rc = check_geom(g)) return rc;
+  const long long total = static_cast<long long>(B) * H * W * C;
+  if (total == 0) return 0;
+  col2im_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dcols), static_cast<__nv_bfloat16*>(dx), g,
+                                                      static_cast<const __nv_bfloat16*>(z), deriv);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_pool_forward(int kind, const void* x, void* y, int* offs, int dtype, int B, int H, int W, int C,
+                               int OH, int OW, int ky, int kx, int sy, int sx, const void* rnd_u16, cudaStream_t s) {
+  VB_REQUIRE(kind >= 0 && kind <= 4, "vb_pool_forward: bad kind %d", kind);
+  VB_REQUIRE(kind < 3 || rnd_u16 != nullptr, "vb_pool_forward: stochastic pooling needs random input");
+  PoolGeom g{B, H, W, C, OH, OW, ky, kx, sy, sx};
+  const long long total = static_cast<long long>(B) * OH * OW * C;
+  if (total == 0) return 0;
+  VB_REQUIRE(static_cast<long long>(B) * H * W * C < 2147483647LL, "vb_pool_forward: input too large for int offsets");
+  if (dtype == D_F32)
+    pool_forward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const float*>(x), static_cast<float*>(y), offs, g, static_cast<const uint16_t*>(rnd_u16));
+  else
+    pool_forward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), offs, g, static_cast<const uint16_t*>(rnd_u16));
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_pool_backward(int kind, const void* dy, const int* offs, void* dx, int dtype, int B, int H, int W,
+                                int C, int OH, int OW, int ky, int kx, int sy, int sx, cudaStream_t s) {
+  VB_REQUIRE(kind == 2 || offs != nullptr, "vb_pool_backward: max-like pooling needs the offsets recorded in forward");
+  PoolGeom g{B, H, W, C, OH, OW, ky, kx, sy, sx};
+  const long long total = static_cast<long long>(B) * H * W * C;
+  if (total == 0) return 0;
+  if (dtype == D_F32)
+    pool_backward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const float*>(dy), offs, static_cast<float*>(dx), g);
+  else
+    pool_backward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(dy), offs, static_cast<__nv_bfloat16*>(dx), g);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_lrn_forward(const void* x, void* y, int dtype, long long pixels, int C, int n, float alpha,
+                              float beta, float k, cudaStream_t s) {
+  const long long total = pixels * C;
+  if (total == 0) return 0;
+  if (dtype == D_F32)
+    lrn_forward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const float*>(x), static_cast<float*>(y), pixels, C, n, alpha, beta, k);
+  else
+    lrn_forward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, n, alpha, beta, k);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_lrn_backward(const void* x, const void* dy, void* dx, int dtype, long long pixels, int C, int n,
+                               float alpha, float beta, float k, cudaStream_t s) {
+  const long long total = pixels * C;
+  if (total == 0) return 0;
+  if (dtype == D_F32)
+    lrn_backward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const float*>(x), static_cast<const float*>(dy), static_cast<float*>(dx), pixels, C, n, alpha, beta, k);
+  else
+    lrn_backward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), pixels, C, n, alpha, beta, k);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// in_dtype: dtype of the pre-softmax activations s; out_dtype: dtype of y / err_output.
+extern "C" int vb_softmax_eval(const void* sm_in, int in_dtype, long long lds, void* y, long long ldy, void* err,
+                               long long lde, int out_dtype, const int* labels, int* max_idx, int batch, int N,
+                               float err_scale, int* n_err, int* confusion, float* max_err_sum, float* loss_sum,
+                               cudaStream_t s) {
+  if (batch == 0) return 0;
+  const int threads = 128;
+  const int grid = ceil_div(batch * 32, threads);
+#define VB_SM(TIN, TOUT)                                                                                      \
+  softmax_eval_kernel<TIN, TOUT><<<grid, threads, 0, s>>>(static_cast<const TIN*>(sm_in), lds,                \
+                                                          static_cast<TOUT*>(y), ldy, static_cast<TOUT*>(err), \
+                                                          lde, labels, max_idx, batch, N, err_scale, n_err,   \
+                                                          confusion, max_err_sum, loss_sum)
+  if (in_dtype == D_F32 && out_dtype == D_F32) VB_SM(float, float);
+  else if (in_dtype == D_F32 && out_dtype == D_BF16) VB_SM(float, __nv_bfloat16);
+  else if (in_dtype == D_BF16 && out_dtype == D_BF16) VB_SM(__nv_bfloat16, __nv_bfloat16);
+  else if (in_dtype == D_BF16 && out_dtype == D_F32) VB_SM(__nv_bfloat16, float);
+  else VB_REQUIRE(false, "vb_softmax_eval: unsupported dtypes %d/%d", in_dtype, out_dtype);
+#undef VB_SM
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_mse_eval(const void* y, long long ldy, const void* target, long long ldt, void* err, long long lde,
+                           int dtype, int batch, int batch_valid, int N, float err_scale, float* metrics,
+                           float* mse_per_sample, cudaStream_t s) {
+  if (batch == 0) return 0;
+  const int threads = 128;
+  const int grid = ceil_div(batch * 32, threads);
+  if (dtype == D_F32)
+    mse_eval_kernel<float><<<grid, threads, 0, s>>>(static_cast<const float*>(y), ldy, static_cast<const float*>(target), ldt,
+                                                    static_cast<float*>(err), lde, batch, batch_valid, N, err_scale, metrics, mse_per_sample);
+  else
+    mse_eval_kernel<__nv_bfloat16><<<grid, threads, 0, s>>>(static_cast<const __nv_bfloat16*>(y), ldy,
+                                                            static_cast<const __nv_bfloat16*>(target), ldt,
+                                                            static_cast<__nv_bfloat16*>(err), lde, batch, batch_valid, N,
+                                                            err_scale, metrics, mse_per_sample);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int vb_row_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, cudaStream_t s) {
+  if (rows == 0) return 0;
+  const int grid = ceil_div(rows * 32, 128);
+  if (dtype == D_F32) row_sum_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, out);
+  else row_sum_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, out);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Number of floats of scratch vb_col_sum needs for a (rows x cols) input.
+extern "C" long long vb_col_sum_scratch_elems(int rows, int cols) {
+  return static_cast<long long>(ceil_div(rows > 0 ? rows : 1, COLSUM_ROWS_PER_SLAB)) * cols;
+}
+
+// out[j] (+)= alpha * sum_i a[i,j].  `scratch` must hold vb_col_sum_scratch_elems() floats.
+extern "C" int vb_col_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, float alpha,
+                          int accumulate, float* scratch, cudaStream_t s) {
+  if (cols == 0) return 0;
+  VB_REQUIRE(scratch != nullptr, "vb_col_sum: scratch buffer is required");
+  const int slabs = ceil_div(rows > 0 ? rows : 1, COLSUM_ROWS_PER_SLAB);
+  dim3 grid(ceil_div(cols, 128), slabs);
+  if (dtype == D_F32) col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch);
+  else col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch);
+  VB_CHECK_CUDA(cudaGetLastError());
+  col_sum_final_kernel<<<ceil_div(cols, 128), 128, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,297 @@
+"""Python entry points for the sm_100a kernel library.
+
+Every function takes ``torch`` CUDA tensors, launches on the current torch stream and
+returns immediately (no synchronisation).  There is no eager fallback: if the library
+cannot be loaded the call raises :class:`veles_b200.ops._lib.KernelError`.
+
+Counts launches in :data:`LAUNCHES` so ``bench.py`` can report ``gpu_launches``.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_float, c_int, c_longlong, c_void_p
+
+import torch
+
+from . import _lib
+
+# activation codes shared with csrc/common.cuh
+ACT_LINEAR, ACT_TANH, ACT_SIGMOID, ACT_RELU, ACT_STRICT_RELU, ACT_LOG, ACT_TANHLOG, ACT_SINCOS, ACT_MUL = range(9)
+ACT_CODES = {
+    "linear": ACT_LINEAR, "tanh": ACT_TANH, "sigmoid": ACT_SIGMOID, "relu": ACT_RELU,
+    "strict_relu": ACT_STRICT_RELU, "str": ACT_STRICT_RELU, "log": ACT_LOG, "tanhlog": ACT_TANHLOG,
+    "sincos": ACT_SINCOS, "mul": ACT_MUL,
+}
+POOL_KINDS = {"max": 0, "maxabs": 1, "avg": 2, "stochastic": 3, "stochastic_abs": 4}
+
+LAUNCHES = [0]
+
+
+def _dt(t):
+    if t.dtype == torch.float32:
+        return 0
+    if t.dtype == torch.bfloat16:
+        return 1
+    if t.dtype == torch.uint8:
+        return 2
+    if t.dtype == torch.int32:
+        return 3
+    raise TypeError("unsupported dtype %s" % t.dtype)
+
+
+def _p(t):
+    return c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ld(t):
+    """Leading dimension (elements) of a 2-D row-major, possibly pitched, tensor."""
+    assert t.dim() == 2 and (t.stride(1) == 1 or t.shape[1] == 1), "need unit inner stride, got %s" % (t.stride(),)
+    return max(t.stride(0), t.shape[1])
+
+
+def pitched_empty(rows, cols, dtype, device, align=8):
+    """[rows, cols] view whose row pitch is a multiple of ``align`` elements (TMA needs 16 B)."""
+    pitch = (cols + align - 1) // align * align
+    buf = torch.zeros(rows, pitch, dtype=dtype, device=device)
+    return buf[:, :cols]
+
+
+def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumulate=False, z=None, deriv=0,
+         alpha=1.0, split_k=1, block_n=0):
+    """out[M,N] = epilogue(sum_k A(m,k) B(n,k)); see csrc/gemm_tcgen05.cu.
+
+    ``a`` is [M,K] (K-major) or [K,M] (``a_mn``); ``b`` is [N,K] or [K,N] (``b_mn``); bf16.
+    ``out`` is bf16 or fp32 [M,N].  ``z``/``deriv`` multiply by f'(z) (activation backward).
+    """
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    assert K == Kb, "inner dimensions differ: %d vs %d" % (K, Kb)
+    assert out.shape[0] == M and out.shape[1] == N, "out shape %s != (%d,%d)" % (tuple(out.shape), M, N)
+    out_fp32 = 1 if out.dtype == torch.float32 else 0
+    L = _lib.lib()
+    rc = L.vb_gemm_bf16(_p(a), c_longlong(_ld(a)), c_int(int(a_mn)), _p(b), c_longlong(_ld(b)), c_int(int(b_mn)),
+                        _p(out), c_longlong(_ld(out)), c_int(M), c_int(N), c_int(K), _p(bias), c_int(act),
+                        c_int(out_fp32), c_int(int(accumulate)), _p(z), c_longlong(_ld(z) if z is not None else 0),
+                        c_int(deriv), c_float(alpha), c_int(split_k), c_int(block_n), _stream())
+    _lib.check(rc, "vb_gemm_bf16")
+    LAUNCHES[0] += 1
+    return out
+
+
+def gather_minibatch(src, indices, start, count, dst, mean=None, rdisp=None, labels=None, mb_labels=None,
+                     mb_indices=None):
+    """K1/K2/K4: dst[s] = normalise(cast(src[indices[start+s]])) for s<count else 0."""
+    src2 = src.reshape(src.shape[0], -1)
+    dst2 = dst.reshape(dst.shape[0], -1) if dst.dim() != 2 else dst
+    L = _lib.lib()
+    rc = L.vb_gather_minibatch(_p(src2), c_int(_dt(src2)), c_longlong(src2.stride(0)), _p(indices), c_int(start),
+                               c_int(count), c_int(dst2.shape[0]), c_int(src2.shape[1]), _p(dst2), c_int(_dt(dst2)),
+                               c_longlong(dst2.stride(0)), _p(mean), _p(rdisp), _p(labels), _p(mb_labels),
+                               _p(mb_indices), _stream())
+    _lib.check(rc, "vb_gather_minibatch")
+    LAUNCHES[0] += 2 if (mb_labels is not None or mb_indices is not None) else 1
+    return dst
+
+
+def mean_disp_normalize(inp, mean, rdisp, out):
+    inp2 = inp.reshape(inp.shape[0], -1)
+    rc = _lib.lib().vb_mean_disp_normalize(_p(inp2), c_int(_dt(inp2)), _p(mean), _p(rdisp), _p(out), c_int(_dt(out)),
+                                           c_int(inp2.shape[0]), c_int(inp2.shape[1]), _stream())
+    _lib.check(rc, "vb_mean_disp_normalize")
+    LAUNCHES[0] += 1
+    return out
+
+
+def copy_2d(src, dst):
+    """dst[:, :] = cast(src) for 2-D (possibly pitched / column-sliced) tensors."""
+    rc = _lib.lib().vb_copy_2d(_p(src), c_int(_dt(src)), c_longlong(src.stride(0)), _p(dst), c_int(_dt(dst)),
+                               c_longlong(dst.stride(0)), c_int(src.shape[0]), c_int(src.shape[1]), _stream())
+    _lib.check(rc, "vb_copy_2d")
+    LAUNCHES[0] += 1
+    return dst
+
+
+def activation_forward(act, x, y, factor=1.0):
+    rc = _lib.lib().vb_activation_forward(c_int(act), _p(x), _p(y), c_longlong(x.numel()), c_int(_dt(x)),
+                                          c_float(factor), _stream())
+    _lib.check(rc, "vb_activation_forward")
+    LAUNCHES[0] += 1
+    return y
+
+
+def activation_backward(act, err_out, x, y, err_in, factor=1.0):
+    rc = _lib.lib().vb_activation_backward(c_int(act), _p(err_out), _p(x), _p(y), _p(err_in),
+                                           c_longlong(err_out.numel()), c_int(_dt(err_out)), c_float(factor),
+                                           _stream())
+    _lib.check(rc, "vb_activation_backward")
+    LAUNCHES[0] += 1
+    return err_in
+
+
+def dropout(inp, out, states_in, states_out, ratio):
+    n_states = states_in.numel() // 2
+    rc = _lib.lib().vb_dropout(_p(inp), _p(out), c_longlong(inp.numel()), c_int(_dt(inp)), _p(states_in),
+                               _p(states_out), c_int(n_states), c_float(ratio), _stream())
+    _lib.check(rc, "vb_dropout")
+    LAUNCHES[0] += 1
+    return out
+
+
+def gd_update(w, grad, vel=None, acc=None, w_bf16=None, *, lr, wd=0.0, l1_vs_l2=0.0, moment=0.0, grad_scale=1.0,
+              solver=0, eps=1e-6, rho=0.9, zero_grad=False):
+    rc = _lib.lib().vb_gd_update(_p(w), _p(grad), _p(vel), _p(acc), _p(w_bf16), c_longlong(w.numel()), c_float(lr),
+                                 c_float(wd), c_float(l1_vs_l2), c_float(moment), c_float(grad_scale), c_int(solver),
+                                 c_float(eps), c_float(rho), c_int(int(zero_grad)), _stream())
+    _lib.check(rc, "vb_gd_update")
+    LAUNCHES[0] += 1
+
+
+def cast(inp, out):
+    rc = _lib.lib().vb_cast(_p(inp), c_int(_dt(inp)), _p(out), c_int(_dt(out)), c_longlong(inp.numel()), _stream())
+    _lib.check(rc, "vb_cast")
+    LAUNCHES[0] += 1
+    return out
+
+
+def im2col(x, cols, geom):
+    """x [B,H,W,C] bf16 -> cols [B*OH*OW, ld] bf16. geom: dict with OH,OW,ky,kx,sy,sx,pt,pl,groups."""
+    B, H, W, C = x.shape
+    rc = _lib.lib().vb_im2col(_p(x), _p(cols), c_int(B), c_int(H), c_int(W), c_int(C), c_int(geom["OH"]),
+                              c_int(geom["OW"]), c_int(geom["ky"]), c_int(geom["kx"]), c_int(geom["sy"]),
+                              c_int(geom["sx"]), c_int(geom["pt"]), c_int(geom["pl"]), c_int(geom.get("groups", 1)),
+                              c_longlong(cols.stride(0)), _stream())
+    _lib.check(rc, "vb_im2col")
+    LAUNCHES[0] += 1
+    return cols
+
+
+def col2im(dcols, dx, geom, z=None, deriv=0):
+    B, H, W, C = dx.shape
+    rc = _lib.lib().vb_col2im(_p(dcols), _p(dx), c_int(B), c_int(H), c_int(W), c_int(C), c_int(geom["OH"]),
+                              c_int(geom["OW"]), c_int(geom["ky"]), c_int(geom["kx"]), c_int(geom["sy"]),
+                              c_int(geom["sx"]), c_int(geom["pt"]), c_int(geom["pl"]), c_int(geom.get("groups", 1)),
+                              c_longlong(dcols.stride(0)), _p(z), c_int(deriv), _stream())
+    _lib.check(rc, "vb_col2im")
+    LAUNCHES[0] += 1
+    return dx
+
+
+def pool_forward(kind, x, y, offs, ky, kx, sy, sx, rnd=None):
+    B, H, W, C = x.shape
+    _, OH, OW, _ = y.shape
+    rc = _lib.lib().vb_pool_forward(c_int(kind), _p(x), _p(y), _p(offs), c_int(_dt(x)), c_int(B), c_int(H), c_int(W),
+                                    c_int(C), c_int(OH), c_int(OW), c_int(ky), c_int(kx), c_int(sy), c_int(sx),
+                                    _p(rnd), _stream())
+    _lib.check(rc, "vb_pool_forward")
+    LAUNCHES[0] += 1
+    return y
+
+
+def pool_backward(kind, dy, offs, dx, ky, kx, sy, sx):
+    B, H, W, C = dx.shape
+    _, OH, OW, _ = dy.shape
+    rc = _lib.lib().vb_pool_backward(c_int(kind), _p(dy), _p(offs), _p(dx), c_int(_dt(dy)), c_int(B), c_int(H),
+                                     c_int(W), c_int(C), c_int(OH), c_int(OW), c_int(ky), c_int(kx), c_int(sy),
+                                     c_int(sx), _stream())
+    _lib.check(rc, "vb_pool_backward")
+    LAUNCHES[0] += 1
+    return dx
+
+
+def lrn_forward(x, y, n, alpha, beta, k):
+    C = x.shape[-1]
+    rc = _lib.lib().vb_lrn_forward(_p(x), _p(y), c_int(_dt(x)), c_longlong(x.numel() // C), c_int(C), c_int(n),
+                                   c_float(alpha), c_float(beta), c_float(k), _stream())
+    _lib.check(rc, "vb_lrn_forward")
+    LAUNCHES[0] += 1
+    return y
+
+
+def lrn_backward(x, dy, dx, n, alpha, beta, k):
+    C = x.shape[-1]
+    rc = _lib.lib().vb_lrn_backward(_p(x), _p(dy), _p(dx), c_int(_dt(x)), c_longlong(x.numel() // C), c_int(C),
+                                    c_int(n), c_float(alpha), c_float(beta), c_float(k), _stream())
+    _lib.check(rc, "vb_lrn_backward")
+    LAUNCHES[0] += 1
+    return dx
+
+
+def softmax_eval(s, y, err, labels, max_idx, *, err_scale=1.0, n_err=None, confusion=None, max_err_sum=None,
+                 loss_sum=None):
+    batch, N = s.shape
+    out_dt = _dt(y if y is not None else err)
+    rc = _lib.lib().vb_softmax_eval(_p(s), c_int(_dt(s)), c_longlong(_ld(s)), _p(y),
+                                    c_longlong(_ld(y) if y is not None else 0), _p(err),
+                                    c_longlong(_ld(err) if err is not None else 0), c_int(out_dt), _p(labels),
+                                    _p(max_idx), c_int(batch), c_int(N), c_float(err_scale), _p(n_err), _p(confusion),
+                                    _p(max_err_sum), _p(loss_sum), _stream())
+    _lib.check(rc, "vb_softmax_eval")
+    LAUNCHES[0] += 1
+
+
+def mse_eval(y, target, err, batch_valid, *, err_scale=1.0, metrics=None, mse_per_sample=None):
+    batch, N = y.shape
+    rc = _lib.lib().vb_mse_eval(_p(y), c_longlong(_ld(y)), _p(target), c_longlong(_ld(target)), _p(err),
+                                c_longlong(_ld(err) if err is not None else 0), c_int(_dt(y)), c_int(batch),
+                                c_int(batch_valid), c_int(N), c_float(err_scale), _p(metrics), _p(mse_per_sample),
+                                _stream())
+    _lib.check(rc, "vb_mse_eval")
+    LAUNCHES[0] += 1
+
+
+def row_sum(a, out):
+    rc = _lib.lib().vb_row_sum(_p(a), c_int(_dt(a)), c_longlong(_ld(a)), c_int(a.shape[0]), c_int(a.shape[1]),
+                               _p(out), _stream())
+    _lib.check(rc, "vb_row_sum")
+    LAUNCHES[0] += 1
+    return out
+
+
+def col_sum_scratch_elems(rows, cols):
+    return int(_lib.lib().vb_col_sum_scratch_elems(c_int(rows), c_int(cols)))
+
+
+def col_sum(a, out, scratch, alpha=1.0, accumulate=False):
+    """out[j] (+)= alpha * sum_i a[i,j]; ``scratch`` fp32 with col_sum_scratch_elems() elements."""
+    assert scratch.numel() >= col_sum_scratch_elems(a.shape[0], a.shape[1])
+    rc = _lib.lib().vb_col_sum(_p(a), c_int(_dt(a)), c_longlong(_ld(a)), c_int(a.shape[0]), c_int(a.shape[1]),
+                               _p(out), c_float(alpha), c_int(int(accumulate)), _p(scratch), _stream())
+    _lib.check(rc, "vb_col_sum")
+    LAUNCHES[0] += 2
+    return out
+
+
+def xorshift1024star(states, rounds, out):
+    n_states = states.numel() // 16
+    rc = _lib.lib().vb_xorshift1024star(_p(states), c_int(n_states), c_int(rounds), _p(out), _stream())
+    _lib.check(rc, "vb_xorshift1024star")
+    LAUNCHES[0] += 1
+    return out
+
+
+def xorshift128plus(states, out):
+    n = states.numel() // 2
+    rc = _lib.lib().vb_xorshift128plus(_p(states), c_longlong(n), _p(out), _stream())
+    _lib.check(rc, "vb_xorshift128plus")
+    LAUNCHES[0] += 1
+    return out
+
+
+def fill_random(states, out, kind, amp):
+    """kind 0: uniform[-amp, amp); 1: normal(0, amp) clipped at 5 sigma."""
+    rc = _lib.lib().vb_fill_random(_p(states), c_int(states.numel() // 2), _p(out), c_longlong(out.numel()),
+                                   c_int(kind), c_float(amp), _stream())
+    _lib.check(rc, "vb_fill_random")
+    LAUNCHES[0] += 1
+    return out
