@@ -1,0 +1,83 @@
+"""End-to-end device runs of StandardWorkflow against the numpy oracle."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _build(device, layers, loader_cfg, loss="softmax", epochs=3, seed=7, loader="synthetic_fullbatch"):
+    from veles_b200 import prng
+    from veles_b200.config import root
+    from veles_b200.dummy import DummyLauncher
+    from veles_b200.znicz.standard_workflow import StandardWorkflow
+    import veles_b200.loader.synthetic  # noqa: F401
+    root.common.disable.snapshotting = True
+    prng.get().seed(seed)
+    launcher = DummyLauncher()
+    wf = StandardWorkflow(launcher, layers=layers, loader_name=loader, loader_config=loader_cfg,
+                          loss_function=loss, decision_config={"max_epochs": epochs})
+    wf.initialize(device=device)
+    return launcher, wf
+
+
+MLP = [{"type": "all2all_tanh", "->": {"output_sample_shape": 100},
+        "<-": {"learning_rate": 0.05, "gradient_moment": 0.9}},
+       {"type": "softmax", "<-": {"learning_rate": 0.05, "gradient_moment": 0.9}}]
+CFG = {"minibatch_size": 100, "n_train": 2000, "n_valid": 500, "sample_shape": (784,), "noise": 2.0}
+
+
+def test_mlp_trains_on_device_and_matches_numpy_oracle():
+    from veles_b200.backends import NumpyDevice, B200Device
+    l0, ref = _build(NumpyDevice(), MLP, CFG)
+    ref.run()
+    l1, wf = _build(B200Device(), MLP, CFG)
+    wf.run()
+    h_ref = ref.decision.epoch_metrics_history
+    h_dev = wf.decision.epoch_metrics_history
+    assert len(h_ref) == len(h_dev)
+    # identical data order and init => the curves must agree up to bf16 rounding
+    assert h_dev[-1]["n_err_pt"][1] <= 2.0
+    for a, b in zip(h_ref, h_dev):
+        assert abs(a["n_err_pt"][1] - b["n_err_pt"][1]) <= 3.0
+        assert abs(a["loss"][1] - b["loss"][1]) <= 0.05 + 0.1 * abs(a["loss"][1])
+    wf.forwards[0].weights.map_read()
+    ref.forwards[0].weights.map_read()
+    w_dev, w_ref = wf.forwards[0].weights.mem, ref.forwards[0].weights.mem
+    assert np.abs(w_dev - w_ref).max() < 0.05
+    l0.stop()
+    l1.stop()
+
+
+def test_first_iteration_gradients_match_oracle():
+    """One minibatch, no update: err_input / gradients of every layer vs the numpy backend."""
+    from veles_b200.backends import NumpyDevice, B200Device
+    layers = [{"type": "all2all_tanh", "->": {"output_sample_shape": 64}, "<-": {"learning_rate": 0.0}},
+              {"type": "all2all_str", "->": {"output_sample_shape": 48}, "<-": {"learning_rate": 0.0}},
+              {"type": "all2all_sigmoid", "->": {"output_sample_shape": 40}, "<-": {"learning_rate": 0.0}},
+              {"type": "softmax", "<-": {"learning_rate": 0.0}}]
+    cfg = dict(CFG, sample_shape=(100,), n_valid=0, minibatch_size=64)
+    res = []
+    for dev in (NumpyDevice(), B200Device()):
+        l, wf = _build(dev, layers, cfg, epochs=1)
+        for gd in wf.gds:
+            gd.apply_gradient = False
+        wf.loader.run()
+        for f in wf.forwards:
+            f.run()
+        wf.evaluator.run()
+        for gd in reversed(wf.gds):
+            gd.run()
+        out = {}
+        for i, gd in enumerate(wf.gds):
+            gd.gradient_weights.map_read()
+            out["gw%d" % i] = gd.gradient_weights.mem.copy()
+            gd.gradient_bias.map_read()
+            out["gb%d" % i] = gd.gradient_bias.mem.copy()
+        wf.forwards[-1].output.map_read()
+        out["y"] = wf.forwards[-1].output.mem.copy()
+        res.append(out)
+        l.stop()
+    for k in res[0]:
+        a, b = res[0][k], res[1][k]
+        denom = np.abs(a).max() + 1e-9
+        assert np.abs(a - b).max() / denom < 3e-2, k

@@ -386,7 +386,9 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
                             cudaStream_t stream) {
   VB_REQUIRE(M > 0 && N > 0 && K > 0, "vb_gemm_bf16: empty problem %dx%dx%d", M, N, K);
   VB_REQUIRE(!(accumulate && !out_fp32), "vb_gemm_bf16: accumulate requires fp32 output");
-  VB_REQUIRE(split_k >= 1, "vb_gemm_bf16: split_k must be >= 1");
+  VB_REQUIRE(split_k >= 0, "vb_gemm_bf16: split_k must be >= 0 (0 = choose automatically)");
+  const bool auto_split = (split_k == 0);
+  if (auto_split) split_k = 1;
   VB_REQUIRE(split_k == 1 || (accumulate && act == 0 && Z == nullptr),
              "vb_gemm_bf16: split-K needs accumulate=1 and a linear epilogue");
   int BN = block_n;
@@ -407,6 +409,16 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
   p.m_blocks = ceil_div(M, BLOCK_M);
   p.n_blocks = ceil_div(N, BN);
   p.k_blocks = ceil_div(K, BLOCK_K);
+  if (auto_split && accumulate && act == 0 && Z == nullptr) {
+    // fill the machine: tiles * split ~ number of SMs, but keep >= 4 k-blocks per split
+    const long long mn_tiles = static_cast<long long>(p.m_blocks) * p.n_blocks;
+    if (mn_tiles * 2 <= sms && p.k_blocks >= 8) {
+      long long s = sms / mn_tiles;
+      const long long cap = p.k_blocks / 4;
+      if (s > cap) s = cap;
+      if (s > 1) split_k = static_cast<int>(s);
+    }
+  }
   if (split_k > p.k_blocks) split_k = p.k_blocks;
   // make every split non-empty
   {

@@ -173,8 +173,10 @@ class Array(Pickleable):
         self.dev_dirty_ = False
 
     # -- device side ------------------------------------------------------------------------------------
-    def initialize(self, device):
-        """Allocate the device tensor (no-op on the numpy device) and upload the host copy."""
+    def initialize(self, device, storage=None):
+        """Allocate the device tensor (no-op on the numpy device) and upload the host copy.
+        ``storage``: an existing device tensor (e.g. a slice of a parameter arena or of a
+        symmetric-memory slab) to adopt instead of allocating."""
         if device is None or not getattr(device, "exists", False):
             self.device_ = device
             return
@@ -187,6 +189,14 @@ class Array(Pickleable):
         self._free_device()
         dt = self.dev_dtype or _torch_dtype(self._mem.dtype)
         shape = self._mem.shape
+        if storage is not None:
+            if storage.numel() != self._mem.size:
+                raise ValueError("storage has %d elements for an Array of %d" % (storage.numel(), self._mem.size))
+            self.devbuf_ = storage
+            self.devmem_ = storage.view(shape) if storage.is_contiguous() else storage
+            self.host_dirty_ = True
+            self.unmap()
+            return
         if self._pitched and len(shape) >= 2:
             cols = int(numpy.prod(shape[1:]))
             pitch = roundup(cols, 8)

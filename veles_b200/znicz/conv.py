@@ -1,0 +1,199 @@
+"""Convolutional layers (NHWC): ``conv``, ``conv_tanh``, ``conv_relu``, ``conv_str``, ``conv_sigmoid``.
+
+kwargs (``docs/source/manualrst_veles_workflow_parameters.rst:518-541``): ``n_kernels, kx, ky,
+padding (left, top, right, bottom), sliding (x, y), grouping, unpack_size, weights_filling,
+weights_stddev, bias_filling, bias_stddev, include_bias, weights_transposed``.
+Pinned layout: input ``[B, H, W, C]``, weights ``[n_kernels, ky*kx*C/grouping]`` with column
+order (tap row, tap col, channel), output ``[B, OH, OW, n_kernels]``; with ``grouping = G``
+kernels ``g*n/G .. (g+1)*n/G`` see input channels ``g*C/G .. (g+1)*C/G``.
+
+Device path: one vectorised im2col ("unpack", what Znicz did in ``unpack_size`` chunks) into a
+bf16 column matrix that stays resident for the backward pass (180 GB of HBM make the chunking
+unnecessary), then one tcgen05 GEMM per group with the bias+activation epilogue writing
+straight into the NHWC output (a column slice per group).
+"""
+from __future__ import annotations
+
+import numpy
+
+from ..memory import Array
+from .nn_units import Forward, act_forward_numpy
+
+
+def conv_output_size(size, k, pad_lo, pad_hi, stride):
+    return (size + pad_lo + pad_hi - k) // stride + 1
+
+
+def numpy_im2col(x, ky, kx, sy, sx, pl, pt, pr, pb, groups=1):
+    """x [B,H,W,C] -> cols [B*OH*OW, G*ky*kx*Cg] in (group, tap, channel) order."""
+    B, H, W, C = x.shape
+    xp = numpy.pad(x, ((0, 0), (pt, pb), (pl, pr), (0, 0)))
+    OH = (H + pt + pb - ky) // sy + 1
+    OW = (W + pl + pr - kx) // sx + 1
+    s = xp.strides
+    win = numpy.lib.stride_tricks.as_strided(
+        xp, shape=(B, OH, OW, ky, kx, C), strides=(s[0], s[1] * sy, s[2] * sx, s[1], s[2], s[3]), writeable=False)
+    Cg = C // groups
+    win = win.reshape(B * OH * OW, ky * kx, groups, Cg).transpose(0, 2, 1, 3)
+    return numpy.ascontiguousarray(win).reshape(B * OH * OW, groups * ky * kx * Cg), OH, OW
+
+
+def numpy_col2im(dcols, shape, ky, kx, sy, sx, pl, pt, pr, pb, groups=1):
+    """Adjoint of numpy_im2col."""
+    B, H, W, C = shape
+    OH = (H + pt + pb - ky) // sy + 1
+    OW = (W + pl + pr - kx) // sx + 1
+    Cg = C // groups
+    d = dcols.reshape(B, OH, OW, groups, ky, kx, Cg).transpose(0, 1, 2, 4, 5, 3, 6).reshape(B, OH, OW, ky, kx, C)
+    out = numpy.zeros((B, H + pt + pb, W + pl + pr, C), dtype=dcols.dtype)
+    for i in range(ky):
+        for j in range(kx):
+            out[:, i:i + sy * OH:sy, j:j + sx * OW:sx, :] += d[:, :, :, i, j, :]
+    return out[:, pt:pt + H, pl:pl + W, :]
+
+
+class Conv(Forward):
+    hide_from_registry = False
+    MAPPING = {"conv"}
+    ACTIVATION = 0
+
+    def __init__(self, workflow, **kwargs):
+        super(Conv, self).__init__(workflow, **kwargs)
+        try:
+            self.n_kernels = int(kwargs["n_kernels"])
+            self.kx = int(kwargs["kx"])
+            self.ky = int(kwargs["ky"])
+        except KeyError:
+            raise KeyError("n_kernels, kx and ky are required parameters of %s" % type(self).__name__)
+        self.padding = tuple(kwargs.get("padding", (0, 0, 0, 0)))  # left, top, right, bottom
+        self.sliding = tuple(kwargs.get("sliding", (1, 1)))        # x, y
+        self.grouping = int(kwargs.get("grouping", 1))
+        self.unpack_size = kwargs.get("unpack_size", 16)           # accepted for config compatibility
+        if len(self.padding) != 4 or len(self.sliding) != 2:
+            raise ValueError("padding must be (l, t, r, b) and sliding (x, y)")
+        self.exports += ["n_kernels", "kx", "ky", "padding", "sliding", "grouping"]
+
+    def init_unpickled(self):
+        super(Conv, self).init_unpickled()
+        self.cols_ = None
+
+    @property
+    def in_shape4(self):
+        s = self.input.shape
+        if len(s) == 4:
+            return s
+        if len(s) == 3:
+            return s + (1,)
+        raise ValueError("Conv input must be [B,H,W,C] or [B,H,W], got %s" % (s,))
+
+    @property
+    def geometry(self):
+        B, H, W, C = self.in_shape4
+        pl, pt, pr, pb = self.padding
+        sx, sy = self.sliding
+        return dict(OH=conv_output_size(H, self.ky, pt, pb, sy), OW=conv_output_size(W, self.kx, pl, pr, sx),
+                    ky=self.ky, kx=self.kx, sy=sy, sx=sx, pt=pt, pl=pl, groups=self.grouping)
+
+    def initialize(self, device=None, **kwargs):
+        if self.input is None or not self.input:
+            return True
+        self.device = device
+        B, H, W, C = self.in_shape4
+        if C % self.grouping or self.n_kernels % self.grouping:
+            raise ValueError("channels (%d) and n_kernels (%d) must be divisible by grouping (%d)"
+                             % (C, self.n_kernels, self.grouping))
+        g = self.geometry
+        if g["OH"] < 1 or g["OW"] < 1:
+            raise ValueError("Convolution kernel does not fit the padded input")
+        self.create_weights(self.n_kernels, self.ky * self.kx * C // self.grouping)
+        self.alloc_output((B, g["OH"], g["OW"], self.n_kernels))
+        self._backend_init_()
+        return None
+
+    def default_weights_stddev(self, fan_in, fan_out):
+        return float(min(numpy.sqrt(6.0 / (fan_in + fan_out * self.kx * self.ky // max(self.sliding[0] * self.sliding[1], 1))), 0.5))
+
+    # -- numpy oracle -----------------------------------------------------------------------------------------
+    def numpy_run(self):
+        self.input.map_read()
+        self.weights.map_read()
+        x = self.input.mem.reshape(self.in_shape4).astype(numpy.float32)
+        pl, pt, pr, pb = self.padding
+        sx, sy = self.sliding
+        G = self.grouping
+        cols, OH, OW = numpy_im2col(x, self.ky, self.kx, sy, sx, pl, pt, pr, pb, G)
+        w = self.weights.mem if not self.weights_transposed else self.weights.mem.T
+        nkg = self.n_kernels // G
+        kg = cols.shape[1] // G
+        out = numpy.empty((cols.shape[0], self.n_kernels), dtype=numpy.float32)
+        for gi in range(G):
+            out[:, gi * nkg:(gi + 1) * nkg] = cols[:, gi * kg:(gi + 1) * kg].dot(w[gi * nkg:(gi + 1) * nkg].T)
+        if self.include_bias:
+            self.bias.map_read()
+            out += self.bias.mem
+        self.output.map_invalidate()
+        self.output.mem[...] = act_forward_numpy(self.ACTIVATION, out).reshape(self.output.shape)
+
+    # -- device ---------------------------------------------------------------------------------------------------------
+    def b200_init(self):
+        import torch
+        dev = self.device_
+        self.place_parameters()
+        self.output.dev_dtype = dev.compute_dtype
+        self.output.initialize(dev)
+        B, H, W, C = self.in_shape4
+        g = self.geometry
+        kk = self.ky * self.kx * (C // self.grouping)
+        if self.grouping > 1 and (kk % 8 or (self.n_kernels // self.grouping) % 8):
+            raise ValueError("grouped convolution on the device needs ky*kx*C/G and n_kernels/G to be multiples of 8")
+        ld = (self.grouping * kk + 7) // 8 * 8
+        self.cols_ = torch.zeros(B * g["OH"] * g["OW"], ld, dtype=torch.bfloat16, device=dev.torch_device)
+        self._x_stage4_ = None
+        if self.input.devmem.dtype != torch.bfloat16:
+            self._x_stage4_ = torch.zeros(self.in_shape4, dtype=torch.bfloat16, device=dev.torch_device)
+
+    def device_input4(self):
+        from ..ops import kernels
+        x = self.input.devmem
+        B = self.in_shape4[0]
+        if self._x_stage4_ is not None:
+            kernels.copy_2d(x.reshape(B, -1), self._x_stage4_.view(B, -1))
+            return self._x_stage4_
+        return x.reshape(self.in_shape4) if tuple(x.shape) != tuple(self.in_shape4) else x
+
+    def b200_run(self):
+        from ..ops import kernels
+        self.input.unmap()
+        x = self.device_input4()
+        g = self.geometry
+        kernels.im2col(x, self.cols_, g)
+        G = self.grouping
+        nkg = self.n_kernels // G
+        kg = self.weights_bf16_.shape[1]
+        out2 = self.output.devmem.view(-1, self.n_kernels)
+        bias = self.bias.devmem if self.include_bias else None
+        for gi in range(G):
+            kernels.gemm(self.cols_[:, gi * kg:(gi + 1) * kg], self.weights_bf16_[gi * nkg:(gi + 1) * nkg],
+                         out2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else out2,
+                         bias=bias[gi * nkg:(gi + 1) * nkg] if bias is not None else None, act=self.ACTIVATION)
+        self.output.mark_device_written()
+
+
+class ConvTanh(Conv):
+    MAPPING = {"conv_tanh"}
+    ACTIVATION = 1
+
+
+class ConvRELU(Conv):
+    MAPPING = {"conv_relu"}
+    ACTIVATION = 3
+
+
+class ConvStrictRELU(Conv):
+    MAPPING = {"conv_str"}
+    ACTIVATION = 4
+
+
+class ConvSigmoid(Conv):
+    MAPPING = {"conv_sigmoid"}
+    ACTIVATION = 2

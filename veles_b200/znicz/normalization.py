@@ -1,0 +1,107 @@
+"""Local response normalisation across channels (``norm`` layer type; params ``alpha, beta, n, k``
+— ``docs/source/manualrst_veles_workflow_parameters.rst:63-64, 497, 538-541``).
+``y_c = x_c * (k + alpha * Σ_{c' in window(c, n)} x_{c'}²)^(-beta)`` (AlexNet LRN)."""
+from __future__ import annotations
+
+import numpy
+
+from .nn_units import ForwardBase, GDBase, act_deriv_numpy
+
+
+def _window_sums(sq, n):
+    """Σ over a centred window of n channels (last axis), zero padded."""
+    half = n // 2
+    C = sq.shape[-1]
+    pad = numpy.zeros(sq.shape[:-1] + (C + 2 * half,), dtype=sq.dtype)
+    pad[..., half:half + C] = sq
+    cs = numpy.concatenate([numpy.zeros(sq.shape[:-1] + (1,), dtype=sq.dtype), numpy.cumsum(pad, axis=-1)], axis=-1)
+    return cs[..., 2 * half + 1:2 * half + 1 + C] - cs[..., 0:C]
+
+
+class LRNormalizerForward(ForwardBase):
+    hide_from_registry = False
+    MAPPING = {"norm"}
+
+    def __init__(self, workflow, **kwargs):
+        super(LRNormalizerForward, self).__init__(workflow, **kwargs)
+        self.alpha = float(kwargs.get("alpha", 0.0001))
+        self.beta = float(kwargs.get("beta", 0.75))
+        self.k = float(kwargs.get("k", 2))
+        self.n = int(kwargs.get("n", 5))
+        self.exports = ["alpha", "beta", "k", "n"]
+
+    def initialize(self, device=None, **kwargs):
+        if self.input is None or not self.input:
+            return True
+        self.device = device
+        self.alloc_output(self.input.shape)
+        if self.on_device:
+            self.output.dev_dtype = self.input.devmem.dtype
+            self.output.initialize(self.device_)
+        self._backend_init_()
+        return None
+
+    def package_export(self):
+        return {"alpha": self.alpha, "beta": self.beta, "k": self.k, "n": self.n}
+
+    def numpy_run(self):
+        self.input.map_read()
+        x = self.input.mem.astype(numpy.float64)
+        s = self.k + self.alpha * _window_sums(x * x, self.n)
+        self.output.map_invalidate()
+        self.output.mem[...] = x * s ** (-self.beta)
+
+    def b200_run(self):
+        from ..ops import kernels
+        x = self.input.devmem
+        kernels.lrn_forward(x if x.is_contiguous() else x.contiguous(), self.output.devmem, self.n, self.alpha,
+                            self.beta, self.k)
+        self.output.mark_device_written()
+
+
+class LRNormalizerBackward(GDBase):
+    hide_from_registry = False
+    MAPPING = {"norm"}
+    CAN_FUSE_PREV_DERIVATIVE = True
+
+    def __init__(self, workflow, **kwargs):
+        super(LRNormalizerBackward, self).__init__(workflow, **kwargs)
+        self.demand("input")
+
+    def initialize(self, device=None, **kwargs):
+        if self.err_output is None or not self.err_output or self.input is None or not self.input:
+            return True
+        self.device = device
+        self.alloc_err_input()
+        if self.on_device:
+            self.err_input.dev_dtype = self.device_.compute_dtype
+            self.err_input.initialize(self.device_)
+        self._backend_init_()
+        return None
+
+    def numpy_run(self):
+        f = self.forward
+        self.input.map_read()
+        self.err_output.map_read()
+        x = self.input.mem.astype(numpy.float64)
+        dy = self.err_output.mem.reshape(x.shape).astype(numpy.float64)
+        s = f.k + f.alpha * _window_sums(x * x, f.n)
+        t = dy * x * s ** (-f.beta - 1.0)
+        dx = dy * s ** (-f.beta) - 2.0 * f.alpha * f.beta * x * _window_sums(t, f.n)
+        if self.prev_activation:
+            dx = dx * act_deriv_numpy(self.prev_activation, x)
+        self.err_input.map_invalidate()
+        self.err_input.mem[...] = dx
+
+    def b200_run(self):
+        from ..ops import kernels
+        f = self.forward
+        x = self.input.devmem
+        eo = self.err_output.devmem
+        ei = self.err_input.devmem
+        if eo.dtype != x.dtype or not eo.is_contiguous():
+            eo = eo.contiguous().to(x.dtype)
+        kernels.lrn_backward(x, eo.view(x.shape), ei, f.n, f.alpha, f.beta, f.k)
+        if self.prev_activation:
+            kernels.activation_backward(self.prev_activation, ei, None, x, ei)
+        self.err_input.mark_device_written()
