@@ -1,0 +1,209 @@
+#!/usr/bin/env python
+"""Headline benchmark: AlexNet (ImageNet shape 227x227x3, 1000 classes) training throughput in
+images/s on N B200s of one node (BASELINE.json: "CIFAR-10/AlexNet images/sec, 1/2/4/8 B200").
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Prints ONE JSON line on rank 0.  ``value`` is the whole-job images/s of the device-timed
+training step (forward + evaluator + backward + fused GD update [+ fused gradient all-reduce]);
+``e2e`` is the same measured through the public ``veles_b200.Trainer.step`` API including the
+per-step pinned-host -> device upload of the minibatch and the device -> host read of the loss.
+Weak scaling: the per-GPU minibatch is fixed, the global batch grows with N.
+
+``--impl reference`` would run the unmodified reference from baseline/_ref; it cannot be
+installed here (see DESIGN.md "Reference arm"), so it prints an "unavailable" line.
+``--model cifar_convnet|wide_mlp_ae|mnist_mlp`` benchmarks the other BASELINE configs.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=20)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", default="veles_b200", choices=["veles_b200", "reference", "nccl"])
+    p.add_argument("--model", default="alexnet")
+    p.add_argument("--batch", type=int, default=0, help="per-GPU minibatch (default: model's)")
+    p.add_argument("--no-graph", action="store_true")
+    p.add_argument("--skip-e2e", action="store_true")
+    return p.parse_args()
+
+
+def reference_unavailable():
+    why = ("devbib/veles cannot be installed/run on this image: Znicz NN engine submodule is absent from the "
+           "checkout, core uses Python<3.7-only syntax (async attribute), deps twisted/zope/cuda4py not in wheelhouse")
+    marker = os.path.join(ROOT, "baseline", "INSTALL_OUTCOME.txt")
+    if os.path.exists(marker):
+        with open(marker) as f:
+            first = f.readline().strip()
+        if first:
+            why = first
+    print(json.dumps({"impl": "reference", "unavailable": why}))
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_unavailable()
+        return 0
+    import torch
+    import torch.distributed as dist
+    from veles_b200.models.configs import MODEL_CONFIGS
+    from veles_b200.ops import kernels
+    from veles_b200.utils.clocks import ClockSampler
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus != world:
+        if world == 1 and args.gpus > 1:
+            # allow `python bench.py --gpus N` without torchrun: re-exec under torch.distributed.run
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+                   "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 2000)] + sys.argv
+            os.execv(sys.executable, cmd)
+        raise SystemExit("--gpus %d does not match WORLD_SIZE %d" % (args.gpus, world))
+    torch.cuda.set_device(local_rank)
+    dp = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        from veles_b200.parallel.dp import DataParallel
+        dp = DataParallel(mode="nccl" if args.impl == "nccl" else "fused")
+
+    from veles_b200.backends import B200Device
+    from veles_b200.trainer import Trainer
+    cfg = MODEL_CONFIGS[args.model]
+    B = args.batch or cfg["minibatch"]
+    device = B200Device(index=local_rank)
+    use_graph = not args.no_graph
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------------------------------------------------------- kernel-only (device resident data)
+    trainer = Trainer(args.model, minibatch_size=B, device=device, use_graph=use_graph, data_parallel=dp,
+                      n_train=8 * B)
+    for _ in range(max(args.warmup, 3)):
+        trainer.step_resident()
+    # count launches of one step eagerly (graph replays do not pass through the Python wrappers)
+    sync_all()
+    trainer.stepper.use_graph = False
+    l0 = kernels.LAUNCHES[0]
+    trainer.step_resident()
+    launches_per_step = kernels.LAUNCHES[0] - l0
+    trainer.stepper.use_graph = use_graph
+    for _ in range(3):
+        trainer.step_resident()
+    sync_all()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        trainer.step_resident()
+    e1.record()
+    sync_all()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop() if sampler is not None else None
+    loss_after = trainer.read_loss()
+    ms_per_step = ms_total / args.steps
+    value = world * B * 1000.0 / ms_per_step
+    trainer.close()
+    del trainer
+    torch.cuda.empty_cache()
+
+    # ---------------------------------------------------------------- end to end (public API, host-fed)
+    e2e = None
+    if not args.skip_e2e:
+        import numpy as np
+        dp2 = None
+        if world > 1:
+            from veles_b200.parallel.dp import DataParallel
+            dp2 = DataParallel(mode="nccl" if args.impl == "nccl" else "fused")
+        tr = Trainer(args.model, minibatch_size=B, device=device, use_graph=use_graph, streaming=True,
+                     data_parallel=dp2)
+        shape = cfg["sample_shape"]
+        image_like = len(shape) == 3
+        rng = np.random.RandomState(100 + rank)
+        pool = []
+        for i in range(4):
+            if image_like:
+                d = torch.from_numpy(rng.randint(0, 256, size=(B,) + shape).astype(np.uint8)).pin_memory()
+            else:
+                d = torch.from_numpy(rng.uniform(-1, 1, size=(B,) + shape).astype(np.float32)).pin_memory()
+            lab = torch.from_numpy(rng.randint(0, max(cfg["n_classes"], 2), size=B).astype(np.int32)).pin_memory()
+            pool.append((d, lab))
+        h2d = 0
+        # double buffering: minibatch i+1 is uploaded while minibatch i trains
+        tr.feed(*pool[0])
+        for i in range(max(args.warmup, 3) + 3):
+            tr.feed(*pool[(i + 1) % 4])
+            tr.step(prefetched=True)
+        sync_all()
+        t0 = time.perf_counter()
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last_loss = None
+        for i in range(args.steps):
+            h2d = tr.feed(*pool[(i + 1) % 4])
+            last_loss = tr.step(prefetched=True)
+        e1.record()
+        sync_all()
+        wall_ms = (time.perf_counter() - t0) * 1000.0
+        dev_ms = max_over_ranks(e0.elapsed_time(e1))
+        e2e_ms = max(dev_ms, max_over_ranks(wall_ms)) / args.steps
+        e2e = {"value": world * B * 1000.0 / e2e_ms, "unit": "images/s", "ms_per_step": e2e_ms,
+               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "last_loss": last_loss,
+               "api": "veles_b200.Trainer.feed/step (pinned host uint8 -> device, loss read back each step)"}
+        tr.close()
+
+    if rank == 0:
+        out = {
+            "metric": "AlexNet images/sec" if args.model == "alexnet" else "%s samples/sec" % args.model,
+            "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"model": args.model, "global_batch": world * B, "per_gpu_batch": B,
+                       "input_shape": list(cfg["sample_shape"]),
+                       "parallelism": "dp%d" % world if world > 1 else "single",
+                       "grad_exchange": ("none" if world == 1 else
+                                         ("nccl_allreduce+gd" if args.impl == "nccl" else "fused_multimem_allreduce_gd")),
+                       "cuda_graph": use_graph,
+                       "l2_policy": "inputs larger than L2: every step gathers a new minibatch from the resident "
+                                    "dataset and streams activations >> 126 MB",
+                       "precision": "bf16 operands/activations, fp32 accumulate, fp32 master weights"},
+            "impl": args.impl, "gpu_launches": int(launches_per_step * args.steps),
+            "launches_per_step": int(launches_per_step), "clocks": clocks, "e2e": e2e, "loss": loss_after,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -72,6 +72,9 @@ class FullBatchLoader(Loader):
             for i, ind in enumerate(idx):
                 self._raw_minibatch_labels[i] = self.original_labels[int(ind)]
 
+    def normalize_minibatch(self):
+        pass  # the whole dataset was normalised once in analyze_dataset()
+
     def analyze_dataset(self):
         """Normalise the whole dataset once (host), or keep affine coefficients for the fused kernel."""
         self._setup_labels()

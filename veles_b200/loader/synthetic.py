@@ -34,7 +34,7 @@ class SyntheticFullBatchLoader(FullBatchLoader):
             return
         rng = numpy.random.RandomState(self.seed)
         total = self.n_test + self.n_valid + self.n_train
-        protos = rng.uniform(-1.0, 1.0, size=(self.n_classes,) + self.sample_shape).astype(numpy.float32)
+        protos = self._prototypes(rng)
         labels = rng.randint(0, self.n_classes, size=total)
         data = numpy.empty((total,) + self.sample_shape, dtype=numpy.float32)
         chunk = max(1, (1 << 24) // max(1, int(numpy.prod(self.sample_shape))))
@@ -49,6 +49,20 @@ class SyntheticFullBatchLoader(FullBatchLoader):
         self.class_lengths[TEST] = self.n_test
         self.class_lengths[VALID] = self.n_valid
         self.class_lengths[TRAIN] = self.n_train
+
+
+    def _prototypes(self, rng):
+        """Class prototypes; image-shaped samples get spatially smooth (blocky low-frequency)
+        prototypes so that convolution + pooling can separate the classes."""
+        shape = self.sample_shape
+        if len(shape) == 3 and shape[0] >= 8 and shape[1] >= 8:
+            H, W, C = shape
+            cell = max(2, min(H, W) // 6)
+            gh, gw = -(-H // cell), -(-W // cell)
+            coarse = rng.uniform(-1.0, 1.0, size=(self.n_classes, gh, gw, C)).astype(numpy.float32)
+            full = numpy.repeat(numpy.repeat(coarse, cell, axis=1), cell, axis=2)
+            return numpy.ascontiguousarray(full[:, :H, :W, :])
+        return rng.uniform(-1.0, 1.0, size=(self.n_classes,) + shape).astype(numpy.float32)
 
 
 class MnistLikeLoader(SyntheticFullBatchLoader):

@@ -13,22 +13,28 @@ def mnist_mlp_layers(lr=0.03):
             {"type": "softmax", "name": "fc_softmax2", "->": {"output_sample_shape": 10}, "<-": _gd(lr, 0.0)}]
 
 
-def cifar_convnet_layers(lr=0.001, n_classes=10):
-    """Caffe "cifar10_quick"-style net as shipped in Znicz samples (conv 32-32-64, 5x5 pad 2)."""
+def cifar_convnet_layers(lr=0.001, n_classes=10, caffe_init=True):
+    """Caffe "cifar10_quick"-style net as shipped in Znicz samples (conv 32-32-64, 5x5 pad 2).
+    ``caffe_init=False`` uses the framework's fan-based default initialisation (trains faster)."""
     def conv(n, std):
-        return {"type": "conv_str", "->": {"n_kernels": n, "kx": 5, "ky": 5, "padding": (2, 2, 2, 2),
-                                           "sliding": (1, 1), "weights_filling": "gaussian", "weights_stddev": std,
-                                           "bias_filling": "constant", "bias_stddev": 0}, "<-": _gd(lr)}
+        fwd = {"n_kernels": n, "kx": 5, "ky": 5, "padding": (2, 2, 2, 2), "sliding": (1, 1)}
+        if caffe_init:
+            fwd.update({"weights_filling": "gaussian", "weights_stddev": std, "bias_filling": "constant",
+                        "bias_stddev": 0})
+        return {"type": "conv_str", "->": fwd, "<-": _gd(lr)}
+
+    def fc(tpe, n):
+        fwd = {"output_sample_shape": n}
+        if caffe_init:
+            fwd.update({"weights_filling": "gaussian", "weights_stddev": 0.05})
+        return {"type": tpe, "->": fwd, "<-": _gd(lr)}
     return [conv(32, 0.01),
             {"type": "max_pooling", "->": {"kx": 3, "ky": 3, "sliding": (2, 2)}},
             conv(32, 0.01),
             {"type": "avg_pooling", "->": {"kx": 3, "ky": 3, "sliding": (2, 2)}},
             conv(64, 0.01),
             {"type": "avg_pooling", "->": {"kx": 3, "ky": 3, "sliding": (2, 2)}},
-            {"type": "all2all_str", "->": {"output_sample_shape": 64, "weights_filling": "gaussian",
-                                           "weights_stddev": 0.05}, "<-": _gd(lr)},
-            {"type": "softmax", "->": {"output_sample_shape": n_classes, "weights_filling": "gaussian",
-                                       "weights_stddev": 0.05}, "<-": _gd(lr)}]
+            fc("all2all_str", 64), fc("softmax", n_classes)]
 
 
 def alexnet_layers(lr=0.01, n_classes=1000, dropout=0.5):

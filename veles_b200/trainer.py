@@ -1,0 +1,106 @@
+"""Trainer: the imperative public API around a StandardWorkflow.
+
+    trainer = veles_b200.Trainer("alexnet", minibatch_size=256)
+    loss = trainer.step(images_uint8, labels_int32)       # host tensors in, python float out
+
+``step`` uploads the minibatch from (pinned) host memory on a side stream, runs the whole
+training iteration (forward, evaluator, backward, fused GD update) as a replayed CUDA graph and
+reads the loss back — this is what ``bench.py`` times for its end-to-end number.
+``step_resident`` trains on the device-resident synthetic dataset (kernel-only number).
+"""
+from __future__ import annotations
+
+import os
+
+
+class Trainer(object):
+    def __init__(self, model="alexnet", minibatch_size=None, device=None, use_graph=True, streaming=False,
+                 data_parallel=None, n_train=None, layers_kwargs=None, loader_extra=None, seed=1234):
+        import torch
+        from . import prng
+        from .backends import Device
+        from .config import root
+        from .models.configs import MODEL_CONFIGS, build_workflow
+        from .parallel.step import FlatStep
+        root.common.disable.snapshotting = True
+        prng.get().seed(seed)
+        self.model = model
+        self.cfg = MODEL_CONFIGS[model]
+        self.dp = data_parallel
+        self.rank = data_parallel.rank if data_parallel is not None else 0
+        self.world = data_parallel.world_size if data_parallel is not None else 1
+        self.minibatch_size = minibatch_size or self.cfg["minibatch"]
+        self.device = device or Device()
+        extra = dict(loader_extra or {})
+        kwargs = {}
+        if streaming:
+            from .loader import stream  # noqa: F401
+            extra.setdefault("dtype", "uint8" if len(self.cfg["sample_shape"]) == 3 else "float32")
+            if extra["dtype"] == "uint8":
+                import numpy
+                n = int(numpy.prod(self.cfg["sample_shape"]))
+                extra.setdefault("mean", numpy.full(n, 127.5, dtype=numpy.float32))
+                extra.setdefault("rdisp", numpy.full(n, 1.0 / 127.5, dtype=numpy.float32))
+        else:
+            if len(self.cfg["sample_shape"]) == 3:
+                extra.setdefault("normalization_type", "mean_disp")
+        self.wf = build_workflow(model, minibatch_size=self.minibatch_size,
+                                 n_train=n_train or 8 * self.minibatch_size, n_valid=0, max_epochs=None,
+                                 loader_extra=extra, layers_kwargs=layers_kwargs, **kwargs) if not streaming else \
+            self._build_streaming(model, extra, layers_kwargs)
+        if data_parallel is not None:
+            data_parallel.attach(self.wf)
+        self.wf.initialize(device=self.device)
+        if data_parallel is not None:
+            data_parallel.finalize(self.wf)
+        self.streaming = streaming
+        self.stepper = FlatStep(self.wf, use_graph=use_graph and self.device.exists, comm=data_parallel)
+        self._loss_host = None
+        if self.device.exists:
+            self._loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self.last_h2d_bytes = 0
+
+    def _build_streaming(self, model, extra, layers_kwargs):
+        from .dummy import DummyLauncher
+        from .znicz.standard_workflow import StandardWorkflow
+        cfg = self.cfg
+        loader_cfg = {"minibatch_size": self.minibatch_size, "sample_shape": cfg["sample_shape"],
+                      "n_classes": cfg["n_classes"] or 10}
+        loader_cfg.update(extra)
+        return StandardWorkflow(DummyLauncher(), layers=cfg["layers"](**(layers_kwargs or {})),
+                                loader_name="stream", loader_config=loader_cfg,
+                                loss_function=cfg["loss_function"], decision_config={"max_epochs": None})
+
+    # -- steps --------------------------------------------------------------------------------------------------------
+    def step_resident(self):
+        """One training iteration on the device-resident dataset; nothing is synchronised."""
+        self.stepper.run(train=True, serve=True)
+
+    def feed(self, data, labels):
+        self.last_h2d_bytes = self.wf.loader.feed(data, labels)
+        return self.last_h2d_bytes
+
+    def step(self, data=None, labels=None, prefetched=False):
+        """Train on one host minibatch and return its mean loss (forces one D2H read)."""
+        import torch
+        if not prefetched:
+            self.feed(data, labels)
+        self.stepper.run(train=True, serve=True)
+        return self.read_loss()
+
+    def read_loss(self):
+        import torch
+        ev = self.wf.evaluator
+        if not self.device.exists:
+            src = ev.loss_sum if hasattr(ev, "loss_sum") else ev.metrics
+            val = float(src.mem[0])
+            src.mem[0] = 0
+            return val / max(1, self.wf.loader.minibatch_size)
+        src = ev.loss_sum.devmem if hasattr(ev, "loss_sum") else ev.metrics.devmem[:1]
+        self._loss_host.copy_(src, non_blocking=True)
+        src.zero_()
+        torch.cuda.current_stream().synchronize()
+        return float(self._loss_host[0]) / max(1, self.wf.loader.minibatch_size)
+
+    def close(self):
+        self.wf.launcher.stop()
