@@ -1,0 +1,91 @@
+/* veles_b200 — C ABI of the sm_100a kernel library (lib/libveles_b200.so).
+ *
+ * Every entry point enqueues work on `stream` and returns 0 on success or a negative code
+ * (message via vb_last_error()).  Pointers are device pointers unless stated otherwise.
+ * dtype codes: 0 = float32, 1 = bfloat16, 2 = uint8, 3 = int32.
+ * Activation codes: 0 linear, 1 tanh (1.7159*tanh(0.6666 s)), 2 sigmoid, 3 "relu" = log(1+e^s),
+ *                   4 strict relu, 5 log, 6 tanhlog, 7 sincos, 8 mul.
+ * Reference citations name the file of devbib/veles each entry point replaces.
+ */
+#ifndef VELES_B200_H_
+#define VELES_B200_H_
+
+#include <cuda_runtime.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime -------------------------------------------------------------------------------- */
+const char* vb_last_error(void);
+int vb_version(void);
+int vb_sm_count(void);
+int vb_device_cc(void);
+
+/* ---- tcgen05/TMEM/TMA GEMM: D[M,N] = epilogue(sum_k A(m,k) B(n,k))
+ * replaces cuBLAS sgemm/dgemm call sites (veles/accelerated_units.py:761-766, veles/backends.py:829-836)
+ * and the OpenCL tiled GEMM + STORE_OUTPUT epilogue (ocl/matrix_multiplication_precise.cl:43-185).
+ * a_mn_major/b_mn_major: 0 = operand stored [M|N, K] row-major, 1 = stored [K, M|N] row-major.
+ * Z/deriv: optional saved activation output, D *= f'(Z).  split_k: 0 = auto, >1 needs accumulate. */
+int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major,
+                 void* D, long long ldd, int M, int N, int K, const float* bias, int act, int out_fp32,
+                 int accumulate, const void* Z, long long ldz, int deriv, float alpha, int split_k, int block_n,
+                 cudaStream_t stream);
+
+/* ---- loader path: cuda/fullbatch_loader.cu:9-61, cuda/mean_disp_normalizer.cu:11-19, cuda/join.jcu:10-35 */
+int vb_gather_minibatch(const void* src, int src_dtype, long long src_ld, const int* indices, int start, int count,
+                        int max_rows, int row_size, void* dst, int dst_dtype, long long dst_ld, const float* mean,
+                        const float* rdisp, const int* labels, int* mb_labels, int* mb_indices, cudaStream_t stream);
+int vb_mean_disp_normalize(const void* in, int in_dtype, const float* mean, const float* rdisp, void* out,
+                           int out_dtype, int batch, int sample_size, cudaStream_t stream);
+int vb_copy_2d(const void* src, int src_dtype, long long src_ld, void* dst, int dst_dtype, long long dst_ld,
+               int rows, int cols, cudaStream_t stream);
+int vb_cast(const void* in, int in_dtype, void* out, int out_dtype, long long n, cudaStream_t stream);
+
+/* ---- Znicz element-wise units (sources absent from the reference checkout) -------- */
+int vb_activation_forward(int act, const void* x, void* y, long long n, int dtype, float factor, cudaStream_t stream);
+int vb_activation_backward(int act, const void* err_out, const void* x, const void* y, void* err_in, long long n,
+                           int dtype, float factor, cudaStream_t stream);
+int vb_dropout(const void* in, void* out, long long n, int dtype, const void* states_in, void* states_out,
+               int n_states, float ratio, cudaStream_t stream);
+int vb_gd_update(float* w, float* grad, float* vel, float* acc, void* w_bf16, long long n, float lr, float wd,
+                 float l1_vs_l2, float moment, float grad_scale, int solver, float eps, float rho, int zero_grad,
+                 cudaStream_t stream);
+
+/* ---- Znicz spatial units -------------------------------------------------------------------------------- */
+int vb_im2col(const void* x, void* cols, int B, int H, int W, int C, int OH, int OW, int ky, int kx, int sy, int sx,
+              int pad_top, int pad_left, int groups, long long ld, cudaStream_t stream);
+int vb_col2im(const void* dcols, void* dx, int B, int H, int W, int C, int OH, int OW, int ky, int kx, int sy,
+              int sx, int pad_top, int pad_left, int groups, long long ld, const void* z, int deriv,
+              cudaStream_t stream);
+int vb_pool_forward(int kind, const void* x, void* y, int* offs, int dtype, int B, int H, int W, int C, int OH,
+                    int OW, int ky, int kx, int sy, int sx, const void* rnd_u16, cudaStream_t stream);
+int vb_pool_backward(int kind, const void* dy, const int* offs, void* dx, int dtype, int B, int H, int W, int C,
+                     int OH, int OW, int ky, int kx, int sy, int sx, cudaStream_t stream);
+int vb_lrn_forward(const void* x, void* y, int dtype, long long pixels, int C, int n, float alpha, float beta,
+                   float k, cudaStream_t stream);
+int vb_lrn_backward(const void* x, const void* dy, void* dx, int dtype, long long pixels, int C, int n, float alpha,
+                    float beta, float k, cudaStream_t stream);
+int vb_softmax_eval(const void* sm_in, int in_dtype, long long lds, void* y, long long ldy, void* err, long long lde,
+                    int out_dtype, const int* labels, int* max_idx, int batch, int N, float err_scale, int* n_err,
+                    int* confusion, float* max_err_sum, float* loss_sum, cudaStream_t stream);
+int vb_mse_eval(const void* y, long long ldy, const void* target, long long ldt, void* err, long long lde, int dtype,
+                int batch, int batch_valid, int N, float err_scale, float* metrics, float* mse_per_sample,
+                cudaStream_t stream);
+
+/* ---- reductions: cuda/matrix_reduce.cu:35-81 ---------------------------------------------------------------- */
+int vb_row_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, cudaStream_t stream);
+long long vb_col_sum_scratch_elems(int rows, int cols);
+/* out[j] (+)= alpha * sum_i a[i,j]; `scratch` holds vb_col_sum_scratch_elems(rows, cols) floats. */
+int vb_col_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, float alpha, int accumulate,
+               float* scratch, cudaStream_t stream);
+
+/* ---- PRNG: cuda/random.cu:45-73 (xorshift1024*), :107-128 (xorshift128+) ------------------------------------- */
+int vb_xorshift1024star(void* states, int n_states, int rounds, void* out, cudaStream_t stream);
+int vb_xorshift128plus(void* states, long long n, void* out, cudaStream_t stream);
+int vb_fill_random(void* states, int n_states, float* out, long long n, int kind, float amp, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VELES_B200_H_ */
