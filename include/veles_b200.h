@@ -80,6 +80,18 @@ long long vb_col_sum_scratch_elems(int rows, int cols);
 int vb_col_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, float alpha, int accumulate,
                float* scratch, cudaStream_t stream);
 
+/* Column sum for callers that cannot allocate device memory (fixed memory budgets, code inside a stream
+ * capture, latency-critical loops where cudaMalloc is forbidden).  Same result as vb_col_sum, but the
+ * inter-block scratch is a fixed 4 MiB array inside the library, so only inputs and outputs are passed.
+ * This entry point has no counterpart in the reference.
+ * Limit: ceil(rows/64) * cols <= vb_col_sum_static_max_elems() (1 Mi floats); larger inputs are rejected
+ * with an error before anything is launched.  The first call on each device looks up the array's device
+ * address (no allocation) — make it before any stream capture.  All calls on a device share the array:
+ * calls whose kernels can overlap on the GPU race with each other; nothing needs zeroing between calls. */
+long long vb_col_sum_static_max_elems(void);
+int vb_col_sum_static(const void* a, int dtype, long long lda, int rows, int cols, float* out, float alpha,
+                      int accumulate, cudaStream_t stream);
+
 /* ---- PRNG: cuda/random.cu:45-73 (xorshift1024*), :107-128 (xorshift128+) ------------------------------------- */
 int vb_xorshift1024star(void* states, int n_states, int rounds, void* out, cudaStream_t stream);
 int vb_xorshift128plus(void* states, long long n, void* out, cudaStream_t stream);

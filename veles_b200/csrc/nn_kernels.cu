@@ -601,3 +601,77 @@ extern "C" int vb_col_sum(const void* a, int dtype, long long lda, int rows, int
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------------------
+// Allocation-free column sum.
+//
+// Some callers of this library are not allowed to allocate device memory: a host
+// application that hands us a fixed memory budget up front, code running between
+// cudaStreamBeginCapture/EndCapture, or a real-time inference loop where a
+// cudaMalloc (an implicit device synchronisation with unbounded latency) is off
+// limits.  vb_col_sum() makes such callers supply the inter-block scratch buffer
+// themselves; vb_col_sum_static() below needs nothing but inputs and outputs.  Its
+// scratch lives in the fixed array declared here, which every GPU that loads the
+// library reserves (4 MiB) until the process exits.
+//
+// The price: the array is shared by every call on a device, so two calls whose
+// kernels may overlap on the GPU (different streams, no ordering between them)
+// race on it and both results are undefined — keep such calls on one stream or
+// order them with events.  Nothing in the array has to be zero when a call starts:
+// the first pass overwrites every partial sum the second pass reads, and whatever
+// the previous call left behind is never looked at.
+// ---------------------------------------------------------------------------
+#define VB_COLSUM_STATIC_MAX_ELEMS (1 << 20)  // 1 Mi floats = 4 MiB
+
+static __device__ __align__(256) float g_colsum_static_scratch[VB_COLSUM_STATIC_MAX_ELEMS];
+
+// Device address of the array above, looked up once per device.  In host code the name
+// g_colsum_static_scratch is only a handle for the runtime, not a pointer a kernel could
+// dereference, hence cudaGetSymbolAddress.
+static float* g_colsum_static_ptr[64] = {nullptr};
+
+static int colsum_static_scratch(float** out) {
+  int dev = -1;
+  VB_CHECK_CUDA(cudaGetDevice(&dev));
+  VB_REQUIRE(dev >= 0 && dev < 64, "vb_col_sum_static: device ordinal %d is out of the supported range", dev);
+  if (g_colsum_static_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    // the symbol is resolved for the CURRENT device (each device has its own copy)
+    VB_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static_scratch));
+    VB_REQUIRE(p != nullptr, "vb_col_sum_static: cudaGetSymbolAddress returned a null address");
+    g_colsum_static_ptr[dev] = p;
+  }
+  *out = g_colsum_static_ptr[dev];
+  return 0;
+}
+
+extern "C" long long vb_col_sum_static_max_elems() { return VB_COLSUM_STATIC_MAX_ELEMS; }
+
+// out[j] (+)= alpha * sum_i a[i,j] without any caller-provided or allocated scratch.
+// Limit: ceil(rows / 64) * cols <= vb_col_sum_static_max_elems() (1 Mi), otherwise the call
+// is rejected with an error and nothing is launched.
+// The first call on each device resolves the scratch address (a host-side runtime query, no
+// allocation); make that first call outside of any stream capture.
+extern "C" int vb_col_sum_static(const void* a, int dtype, long long lda, int rows, int cols, float* out,
+                                 float alpha, int accumulate, cudaStream_t s) {
+  if (cols == 0) return 0;
+  VB_REQUIRE(rows >= 0 && cols > 0, "vb_col_sum_static: bad shape %d x %d", rows, cols);
+  const int slabs = ceil_div(rows > 0 ? rows : 1, COLSUM_ROWS_PER_SLAB);
+  const long long need = static_cast<long long>(slabs) * cols;
+  VB_REQUIRE(need <= VB_COLSUM_STATIC_MAX_ELEMS,
+             "vb_col_sum_static: %d x %d needs %lld scratch floats, the built-in buffer holds %d; "
+             "use vb_col_sum() with your own scratch for inputs this large",
+             rows, cols, need, VB_COLSUM_STATIC_MAX_ELEMS);
+  VB_REQUIRE(dtype == D_F32 || dtype == D_BF16, "vb_col_sum_static: dtype must be f32 (0) or bf16 (1)");
+  float* scratch = nullptr;
+  if (int rc = colsum_static_scratch(&scratch)) return rc;
+  dim3 grid(ceil_div(cols, 128), slabs);
+  if (dtype == D_F32)
+    col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch);
+  else
+    col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch);
+  VB_CHECK_CUDA(cudaGetLastError());
+  col_sum_final_kernel<<<ceil_div(cols, 128), 128, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
