@@ -62,6 +62,12 @@ int vb_pool_forward(int kind, const void* x, void* y, int* offs, int dtype, int 
                     int OW, int ky, int kx, int sy, int sx, const void* rnd_u16, cudaStream_t stream);
 int vb_pool_backward(int kind, const void* dy, const int* offs, void* dx, int dtype, int B, int H, int W, int C,
                      int OH, int OW, int ky, int kx, int sy, int sx, cudaStream_t stream);
+/* backward variants that also multiply by f'(z) of the activation which produced the layer input */
+int vb_pool_backward_fused(int kind, const void* dy, const int* offs, void* dx, int dtype, int B, int H, int W, int C,
+                           int OH, int OW, int ky, int kx, int sy, int sx, const void* z, int deriv,
+                           cudaStream_t stream);
+int vb_lrn_backward_fused(const void* x, const void* dy, void* dx, int dtype, long long pixels, int C, int n,
+                          float alpha, float beta, float k, int deriv, cudaStream_t stream);
 int vb_lrn_forward(const void* x, void* y, int dtype, long long pixels, int C, int n, float alpha, float beta,
                    float k, cudaStream_t stream);
 int vb_lrn_backward(const void* x, const void* dy, void* dx, int dtype, long long pixels, int C, int n, float alpha,

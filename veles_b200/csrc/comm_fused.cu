@@ -1,0 +1,288 @@
+// veles_b200 — C1: per-layer gradient all-reduce FUSED with the Znicz gradient-descent update
+// and the updated-weight broadcast, in ONE kernel over NVLink 5 / NVSwitch.
+//
+// It replaces the reference's whole master/slave exchange for data-parallel training:
+//   slave: Array.map_read (D2H) -> pickle -> ZeroMQ/shm "update"      veles/client.py:138-160, 333-342
+//   master: apply_data_from_slave under a lock, then pickle the new weights into the next "job"
+//                                                                      veles/server.py:141-169, 401-430
+//   slave: unpickle -> Array.map_write/unmap (H2D)                     veles/workflow.py:513-529
+// and the conventional NCCL all-reduce + separate optimizer kernel (kept only as the baseline).
+//
+// Every rank owns 1/world of each parameter segment.  For its slice the kernel
+//   1. sums the gradient over all ranks:  multimem.ld_reduce.add.v4.f32 on the NVLS multicast
+//      address (the switch reduces in-fabric), or P2P loads from every peer when there is no
+//      multicast mapping;
+//   2. applies weight decay (L1/L2 mix), momentum and the learning rate in registers, updating
+//      the local fp32 master weights and velocity;
+//   3. publishes the new fp32 weights and the bf16 shadow (what the next forward GEMM's TMA
+//      loads read) to ALL ranks with multimem.st (or P2P stores).
+// Synchronisation is device-side only: monotonically increasing epoch words in symmetric
+// memory (st.release.sys / ld.acquire.sys), so the kernel is CUDA-graph capturable and needs
+// no host round trip.  Gradients are double-buffered by step parity; the kernel zeroes the
+// other parity's local buffer, which every peer is known to have finished reading (they could
+// not have entered this epoch otherwise).
+#include "common.cuh"
+
+namespace vb {
+
+constexpr int MAX_WORLD = 8;
+constexpr int MAX_SEGS = 8;
+
+struct FusedSeg {
+  long long offset;         // element offset into the flat fp32 slabs
+  long long numel;
+  long long shadow_offset;  // element offset into the bf16 shadow slab, -1 = no shadow
+  int row_len, row_pitch;   // shadow rows: element i -> shadow[(i / row_len) * row_pitch + i % row_len]
+  float lr, wd, l12, moment;
+};
+
+struct FusedParams {
+  int world, rank, nseg, channel;
+  FusedSeg seg[MAX_SEGS];
+  float* grads_local;        // this step's parity
+  float* grads_mc;           // multicast alias of the same slab or null
+  float* grads_peer[MAX_WORLD];
+  float* grads_other_local;  // other parity: zeroed here
+  float* weights_local;
+  float* weights_mc;
+  float* weights_peer[MAX_WORLD];
+  float* vel_local;
+  __nv_bfloat16* shadow_local;
+  __nv_bfloat16* shadow_mc;
+  __nv_bfloat16* shadow_peer[MAX_WORLD];
+  uint32_t* flags_local;     // [channels][2][MAX_WORLD] epoch words written by peers
+  uint32_t* flags_peer[MAX_WORLD];
+  uint32_t* epochs;          // local [channels] last completed epoch
+  unsigned int* cta_counter; // local [channels]
+  int* status;               // local: set non-zero on a synchronisation timeout
+  float grad_scale;
+  long long timeout_cycles;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 mc_ld_reduce_f32x4(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_f32x4(float* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void mc_st_f32x2(float* p, float a, float b) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+
+__device__ __forceinline__ float gd_apply(float w, float g, float& v, const FusedSeg& s, float grad_scale) {
+  const float sgn = (w > 0.0f) ? 1.0f : ((w < 0.0f) ? -1.0f : 0.0f);
+  g = g * grad_scale + s.wd * ((1.0f - s.l12) * w + 0.5f * s.l12 * sgn);
+  v = s.moment * v - s.lr * g;
+  return w + v;
+}
+
+// Wait until flags_local[slot + r] >= epoch for every rank r != me; false on timeout.
+__device__ __forceinline__ bool wait_all(const FusedParams& p, int slot, uint32_t epoch) {
+  const long long t0 = clock64();
+  for (int r = 0; r < p.world; ++r) {
+    if (r == p.rank) continue;
+    const uint32_t* f = p.flags_local + slot + r;
+    while (static_cast<int32_t>(ld_acquire_sys(f) - epoch) < 0) {
+      if (clock64() - t0 > p.timeout_cycles) return false;
+      __nanosleep(64);
+    }
+  }
+  return true;
+}
+
+template <bool MULTIMEM>
+__global__ void __launch_bounds__(512) fused_allreduce_gd_kernel(const FusedParams p) {
+  __shared__ int s_ok;
+  __shared__ uint32_t s_epoch;
+  const int ready_slot = (p.channel * 2 + 0) * MAX_WORLD;
+  const int done_slot = (p.channel * 2 + 1) * MAX_WORLD;
+  if (threadIdx.x == 0) {
+    const uint32_t epoch = p.epochs[p.channel] + 1;  // identical in every CTA: bumped by the last CTA at exit
+    s_epoch = epoch;
+    if (blockIdx.x == 0) {
+      // my gradients for this segment are complete (stream order): tell every peer
+      __threadfence_system();
+      for (int r = 0; r < p.world; ++r)
+        if (r != p.rank) st_release_sys(p.flags_peer[r] + ready_slot + p.rank, epoch);
+    }
+    s_ok = wait_all(p, ready_slot, epoch) ? 1 : 0;
+  }
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
+  const bool ok = s_ok != 0;
+
+  if (ok) {
+    const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (int si = 0; si < p.nseg; ++si) {
+      const FusedSeg s = p.seg[si];
+      // zero the other parity's local gradients of this segment (everybody is done reading them)
+      if (p.grads_other_local != nullptr) {
+        float* z = p.grads_other_local + s.offset;
+        const long long n4 = s.numel >> 2;
+        for (long long i = tid; i < n4; i += nthreads) reinterpret_cast<float4*>(z)[i] = make_float4(0, 0, 0, 0);
+        for (long long i = (n4 << 2) + tid; i < s.numel; i += nthreads) z[i] = 0.0f;
+      }
+      // my slice of the segment
+      long long chunk = (s.numel + p.world - 1) / p.world;
+      chunk = (chunk + 3) & ~3LL;
+      const long long lo = min(s.numel, chunk * p.rank);
+      const long long hi = min(s.numel, lo + chunk);
+      const long long n4 = (hi - lo) >> 2;  // lo is a multiple of 4 and offset is 64-element aligned
+      const bool flat_shadow = s.shadow_offset >= 0 && s.row_len == s.row_pitch;
+      for (long long i4 = tid; i4 < n4; i4 += nthreads) {
+        const long long i = lo + (i4 << 2);
+        const long long gi = s.offset + i;
+        float4 g;
+        if (MULTIMEM) {
+          g = mc_ld_reduce_f32x4(p.grads_mc + gi);
+        } else {
+          g = *reinterpret_cast<const float4*>(p.grads_local + gi);
+          for (int r = 0; r < p.world; ++r) {
+            if (r == p.rank) continue;
+            const float4 o = *reinterpret_cast<const float4*>(p.grads_peer[r] + gi);
+            g.x += o.x; g.y += o.y; g.z += o.z; g.w += o.w;
+          }
+        }
+        float4 w = *reinterpret_cast<const float4*>(p.weights_local + gi);
+        float4 v = *reinterpret_cast<const float4*>(p.vel_local + gi);
+        w.x = gd_apply(w.x, g.x, v.x, s, p.grad_scale);
+        w.y = gd_apply(w.y, g.y, v.y, s, p.grad_scale);
+        w.z = gd_apply(w.z, g.z, v.z, s, p.grad_scale);
+        w.w = gd_apply(w.w, g.w, v.w, s, p.grad_scale);
+        *reinterpret_cast<float4*>(p.vel_local + gi) = v;
+        if (MULTIMEM) {
+          mc_st_f32x4(p.weights_mc + gi, w);
+        } else {
+          for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = w;
+        }
+        if (s.shadow_offset >= 0) {
+          const uint32_t b0 = pack_bf16x2(w.x, w.y), b1 = pack_bf16x2(w.z, w.w);
+          if (flat_shadow) {
+            const long long so = s.shadow_offset + i;
+            if (MULTIMEM) {
+              mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
+            } else {
+              for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
+            }
+          } else {
+            const float wv[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const long long e = i + q;
+              const long long so = s.shadow_offset + (e / s.row_len) * s.row_pitch + (e % s.row_len);
+              const __nv_bfloat16 b = __float2bfloat16(wv[q]);
+              for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = b;  // P2P scalar stores (tiny layers only)
+            }
+          }
+        }
+      }
+      // scalar tail of my slice (numel not a multiple of 4)
+      for (long long i = lo + (n4 << 2) + tid; i < hi; i += nthreads) {
+        const long long gi = s.offset + i;
+        float g = p.grads_local[gi];
+        for (int r = 0; r < p.world; ++r)
+          if (r != p.rank) g += p.grads_peer[r][gi];
+        float v = p.vel_local[gi];
+        const float w = gd_apply(p.weights_local[gi], g, v, s, p.grad_scale);
+        p.vel_local[gi] = v;
+        for (int r = 0; r < p.world; ++r) p.weights_peer[r][gi] = w;
+        if (s.shadow_offset >= 0) {
+          const long long so = s.shadow_offset + (i / s.row_len) * s.row_pitch + (i % s.row_len);
+          for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = __float2bfloat16(w);
+        }
+      }
+    }
+  }
+
+  // ---- completion: the last CTA tells the peers that all my stores are out and waits for theirs
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(p.cta_counter + p.channel, 1u);
+    if (prev == gridDim.x - 1) {
+      bool fine = ok;
+      __threadfence_system();
+      for (int r = 0; r < p.world; ++r)
+        if (r != p.rank) st_release_sys(p.flags_peer[r] + done_slot + p.rank, epoch);
+      if (fine) fine = wait_all(p, done_slot, epoch);
+      if (!fine) atomicExch(p.status, 1 + p.channel);
+      p.cta_counter[p.channel] = 0;
+      p.epochs[p.channel] = epoch;
+      __threadfence();
+    }
+  }
+}
+
+}  // namespace vb
+
+using namespace vb;
+
+// Host ABI: all arrays are passed flat so that ctypes callers need no struct mirror.
+//   segs: nseg x {offset, numel, shadow_offset, row_len, row_pitch} as long long[5]
+//   hyper: nseg x {lr, wd, l1_vs_l2, moment} as float[4]
+//   *_peer: world device pointers each
+extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg, const long long* segs,
+                                     const float* hyper, float* grads_local, float* grads_mc, float** grads_peer,
+                                     float* grads_other_local, float* weights_local, float* weights_mc,
+                                     float** weights_peer, float* vel_local, void* shadow_local, void* shadow_mc,
+                                     void** shadow_peer, unsigned int* flags_local, unsigned int** flags_peer,
+                                     unsigned int* epochs, unsigned int* cta_counter, int* status, float grad_scale,
+                                     int n_ctas, int use_multimem, double timeout_s, cudaStream_t stream) {
+  VB_REQUIRE(world >= 2 && world <= MAX_WORLD, "vb_fused_allreduce_gd: world size %d not in [2,%d]", world, MAX_WORLD);
+  VB_REQUIRE(nseg >= 1 && nseg <= MAX_SEGS, "vb_fused_allreduce_gd: %d segments (max %d per launch)", nseg, MAX_SEGS);
+  VB_REQUIRE(channel >= 0 && channel < 64, "vb_fused_allreduce_gd: channel %d out of range", channel);
+  VB_REQUIRE(!use_multimem || (grads_mc && weights_mc), "vb_fused_allreduce_gd: multimem path needs multicast pointers");
+  FusedParams p;
+  p.world = world; p.rank = rank; p.nseg = nseg; p.channel = channel;
+  for (int i = 0; i < nseg; ++i) {
+    p.seg[i].offset = segs[i * 5 + 0];
+    p.seg[i].numel = segs[i * 5 + 1];
+    p.seg[i].shadow_offset = segs[i * 5 + 2];
+    p.seg[i].row_len = static_cast<int>(segs[i * 5 + 3]);
+    p.seg[i].row_pitch = static_cast<int>(segs[i * 5 + 4]);
+    p.seg[i].lr = hyper[i * 4 + 0];
+    p.seg[i].wd = hyper[i * 4 + 1];
+    p.seg[i].l12 = hyper[i * 4 + 2];
+    p.seg[i].moment = hyper[i * 4 + 3];
+    VB_REQUIRE((p.seg[i].offset & 3) == 0, "vb_fused_allreduce_gd: segment offset must be a multiple of 4 elements");
+    VB_REQUIRE(p.seg[i].shadow_offset < 0 || p.seg[i].row_len > 0, "vb_fused_allreduce_gd: bad shadow geometry");
+    if (use_multimem && p.seg[i].shadow_offset >= 0 && p.seg[i].row_len == p.seg[i].row_pitch)
+      VB_REQUIRE(shadow_mc != nullptr, "vb_fused_allreduce_gd: shadow multicast pointer missing");
+  }
+  p.grads_local = grads_local; p.grads_mc = grads_mc; p.grads_other_local = grads_other_local;
+  p.weights_local = weights_local; p.weights_mc = weights_mc; p.vel_local = vel_local;
+  p.shadow_local = static_cast<__nv_bfloat16*>(shadow_local);
+  p.shadow_mc = static_cast<__nv_bfloat16*>(shadow_mc);
+  for (int r = 0; r < MAX_WORLD; ++r) {
+    p.grads_peer[r] = r < world ? grads_peer[r] : nullptr;
+    p.weights_peer[r] = r < world ? weights_peer[r] : nullptr;
+    p.shadow_peer[r] = r < world && shadow_peer ? static_cast<__nv_bfloat16*>(shadow_peer[r]) : nullptr;
+    p.flags_peer[r] = r < world ? flags_peer[r] : nullptr;
+  }
+  p.flags_local = flags_local; p.epochs = epochs; p.cta_counter = cta_counter; p.status = status;
+  p.grad_scale = grad_scale;
+  p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
+  if (n_ctas <= 0) n_ctas = 32;
+  if (use_multimem)
+    fused_allreduce_gd_kernel<true><<<n_ctas, 512, 0, stream>>>(p);
+  else
+    fused_allreduce_gd_kernel<false><<<n_ctas, 512, 0, stream>>>(p);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,399 @@
+// veles_b200 — bandwidth-tuned variants of the spatial kernels, selected by the entry points in
+// nn_kernels.cu whenever the shapes allow (bf16, channel counts that are multiples of 8, ...).
+// The generic kernels in nn_kernels.cu stay as the any-shape fallback and as the readable
+// statement of the semantics.
+//
+// First measurement that motivated them (AlexNet, B=256, ncu launch list, profiles/alexnet_r1_*):
+// col2im 17 %, im2col(C=3) 12.5 %, lrn_backward 12 %, pool_backward 8 %, col_sum_final 6 % of
+// the step — all far from the HBM roofline because of per-element div/mod address math,
+// 2-byte accesses and O(window^2) recomputation.
+#include "common.cuh"
+#include "fast_paths.cuh"
+
+namespace vb {
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 o;
+  o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+  o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+  return o;
+}
+__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+static inline int grid_cap2(long long n, int block) {
+  long long g = (n + block - 1) / block;
+  const long long cap = static_cast<long long>(device_sm_count()) * 32;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+
+// ---------------------------------------------------------------------------------------------
+// im2col for ANY channel count: one thread produces 8 consecutive columns (one 16-byte store);
+// the (group, tap, channel) decomposition is done once and then advanced incrementally.
+// ---------------------------------------------------------------------------------------------
+__global__ void im2col_any8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols,
+                                   const FastConvGeom g) {
+  const int Cg = g.C / g.groups;
+  const int kk = g.ky * g.kx;
+  const int vec_per_row = static_cast<int>(g.ld >> 3);
+  const int used = g.groups * kk * Cg;
+  const long long rows = static_cast<long long>(g.B) * g.OH * g.OW;
+  const long long total = rows * vec_per_row;
+  const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = t / vec_per_row;
+    int col = static_cast<int>(t - row * vec_per_row) << 3;
+    const int ow = static_cast<int>(row % g.OW);
+    const long long r2 = row / g.OW;
+    const int oh = static_cast<int>(r2 % g.OH);
+    const int b = static_cast<int>(r2 / g.OH);
+    int grp = col / (kk * Cg);
+    int rem = col - grp * kk * Cg;
+    int tap = rem / Cg;
+    int cg = rem - tap * Cg;
+    int i = tap / g.kx, j = tap - i * g.kx;
+    const int ih0 = oh * g.sy - g.pt, iw0 = ow * g.sx - g.pl;
+    const long long img = static_cast<long long>(b) * g.H * g.W * g.C;
+    unsigned short v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      unsigned short e = 0;
+      if (col + q < used) {
+        const int ih = ih0 + i, iw = iw0 + j;
+        if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W)
+          e = __ldg(xs + img + (static_cast<long long>(ih) * g.W + iw) * g.C + grp * Cg + cg);
+      }
+      v[q] = e;
+      if (++cg == Cg) {
+        cg = 0;
+        if (++j == g.kx) {
+          j = 0;
+          if (++i == g.ky) {
+            i = 0;
+            ++grp;
+          }
+        }
+      }
+    }
+    uint4 o;
+    o.x = v[0] | (static_cast<uint32_t>(v[1]) << 16);
+    o.y = v[2] | (static_cast<uint32_t>(v[3]) << 16);
+    o.z = v[4] | (static_cast<uint32_t>(v[5]) << 16);
+    o.w = v[6] | (static_cast<uint32_t>(v[7]) << 16);
+    *reinterpret_cast<uint4*>(cols + row * g.ld + col) = o;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// col2im, gather form, 8 channels per thread (Cg % 8 == 0): 16-byte loads of the column matrix.
+// ---------------------------------------------------------------------------------------------
+__global__ void col2im_vec8_kernel(const __nv_bfloat16* __restrict__ dcols, __nv_bfloat16* __restrict__ dx,
+                                   const FastConvGeom g, const __nv_bfloat16* __restrict__ z, int deriv) {
+  const int Cg = g.C / g.groups;
+  const int kk = g.ky * g.kx;
+  const int C8 = g.C >> 3;
+  const long long total = static_cast<long long>(g.B) * g.H * g.W * C8;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % C8) << 3;
+    long long r = t / C8;
+    const int iw = static_cast<int>(r % g.W);
+    r /= g.W;
+    const int ih = static_cast<int>(r % g.H);
+    const int b = static_cast<int>(r / g.H);
+    const int grp = c / Cg, cg = c - grp * Cg;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const __nv_bfloat16* base = dcols + grp * kk * Cg + cg;
+    for (int i = 0; i < g.ky; ++i) {
+      const int nh = ih + g.pt - i;
+      if (nh < 0) break;
+      if (nh % g.sy) continue;
+      const int oh = nh / g.sy;
+      if (oh >= g.OH) continue;
+      for (int j = 0; j < g.kx; ++j) {
+        const int nw = iw + g.pl - j;
+        if (nw < 0) break;
+        if (nw % g.sx) continue;
+        const int ow = nw / g.sx;
+        if (ow >= g.OW) continue;
+        const long long row = (static_cast<long long>(b) * g.OH + oh) * g.OW + ow;
+        float f[8];
+        unpack8(ldg16(base + row * g.ld + (i * g.kx + j) * Cg), f);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc[q] += f[q];
+      }
+    }
+    const long long o = ((static_cast<long long>(b) * g.H + ih) * g.W + iw) * g.C + c;
+    if (z != nullptr) {
+      float f[8];
+      unpack8(ldg16(z + o), f);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc[q] *= act_deriv_from_output(deriv, f[q]);
+    }
+    *reinterpret_cast<uint4*>(dx + o) = pack8(acc);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Pooling, 8 channels per thread (C % 8 == 0), bf16.
+// ---------------------------------------------------------------------------------------------
+__global__ void pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                         int* __restrict__ offs, const FastPoolGeom g) {
+  const int C8 = g.C >> 3;
+  const long long total = static_cast<long long>(g.B) * g.OH * g.OW * C8;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % C8) << 3;
+    long long r = t / C8;
+    const int ow = static_cast<int>(r % g.OW);
+    r /= g.OW;
+    const int oh = static_cast<int>(r % g.OH);
+    const int b = static_cast<int>(r / g.OH);
+    const int h0 = oh * g.sy, w0 = ow * g.sx;
+    const int h1 = min(h0 + g.ky, g.H), w1 = min(w0 + g.kx, g.W);
+    const long long img = static_cast<long long>(b) * g.H * g.W * g.C + c;
+    float best[8], key[8];
+    int bo[8];
+    float sum[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      best[q] = 0.0f; key[q] = -INFINITY; sum[q] = 0.0f;
+      bo[q] = static_cast<int>(img + (static_cast<long long>(h0) * g.W + w0) * g.C) + q;
+    }
+    for (int h = h0; h < h1; ++h)
+      for (int w = w0; w < w1; ++w) {
+        const long long o = img + (static_cast<long long>(h) * g.W + w) * g.C;
+        float f[8];
+        unpack8(ldg16(x + o), f);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (kind == 2) {
+            sum[q] += f[q];
+          } else {
+            const float kq = kind == 1 ? fabsf(f[q]) : f[q];
+            if (kq > key[q]) {
+              key[q] = kq;
+              best[q] = f[q];
+              bo[q] = static_cast<int>(o) + q;
+            }
+          }
+        }
+      }
+    const long long oo = ((static_cast<long long>(b) * g.OH + oh) * g.OW + ow) * g.C + c;
+    if (kind == 2) {
+      const float inv = 1.0f / static_cast<float>((h1 - h0) * (w1 - w0));
+#pragma unroll
+      for (int q = 0; q < 8; ++q) best[q] = sum[q] * inv;
+    }
+    *reinterpret_cast<uint4*>(y + oo) = pack8(best);
+    if (offs != nullptr && kind != 2) {
+      *reinterpret_cast<int4*>(offs + oo) = make_int4(bo[0], bo[1], bo[2], bo[3]);
+      *reinterpret_cast<int4*>(offs + oo + 4) = make_int4(bo[4], bo[5], bo[6], bo[7]);
+    }
+  }
+}
+
+__global__ void pool_backward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ dy, const int* __restrict__ offs,
+                                          __nv_bfloat16* __restrict__ dx, const FastPoolGeom g,
+                                          const __nv_bfloat16* __restrict__ z, int deriv) {
+  const int C8 = g.C >> 3;
+  const long long total = static_cast<long long>(g.B) * g.H * g.W * C8;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(t % C8) << 3;
+    long long r = t / C8;
+    const int w = static_cast<int>(r % g.W);
+    r /= g.W;
+    const int h = static_cast<int>(r % g.H);
+    const int b = static_cast<int>(r / g.H);
+    const int oh_lo = max(0, (h - g.ky + g.sy) / g.sy), oh_hi = min(g.OH - 1, h / g.sy);
+    const int ow_lo = max(0, (w - g.kx + g.sx) / g.sx), ow_hi = min(g.OW - 1, w / g.sx);
+    const long long me = ((static_cast<long long>(b) * g.H + h) * g.W + w) * g.C + c;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int oh = oh_lo; oh <= oh_hi; ++oh)
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        const long long o = ((static_cast<long long>(b) * g.OH + oh) * g.OW + ow) * g.C + c;
+        float f[8];
+        unpack8(ldg16(dy + o), f);
+        if (kind == 2) {
+          const int hh = min(oh * g.sy + g.ky, g.H) - oh * g.sy, ww = min(ow * g.sx + g.kx, g.W) - ow * g.sx;
+          const float inv = 1.0f / static_cast<float>(hh * ww);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) acc[q] += f[q] * inv;
+        } else {
+          const int4 o0 = __ldg(reinterpret_cast<const int4*>(offs + o));
+          const int4 o1 = __ldg(reinterpret_cast<const int4*>(offs + o + 4));
+          const int of[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+          const int mine = static_cast<int>(me);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            if (of[q] == mine + q) acc[q] += f[q];
+        }
+      }
+    if (z != nullptr) {
+      float f[8];
+      unpack8(ldg16(z + me), f);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc[q] *= act_deriv_from_output(deriv, f[q]);
+    }
+    *reinterpret_cast<uint4*>(dx + me) = pack8(acc);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// LRN: one warp per pixel, the pixel's channel vector staged in shared memory, so every element
+// costs one pow instead of one per window member (backward was O(n^2) pows per element).
+// smem per warp: 3*C floats (x, p = s^-beta, t = dy*x*p/s).
+// ---------------------------------------------------------------------------------------------
+__global__ void lrn_forward_row_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                       long long pixels, int C, int n, float alpha, float beta, float k) {
+  extern __shared__ float sm[];
+  const int warps = blockDim.x >> 5;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* xs = sm + warp * C;
+  const int half = n / 2;
+  for (long long px = blockIdx.x * static_cast<long long>(warps) + warp; px < pixels;
+       px += static_cast<long long>(gridDim.x) * warps) {
+    const __nv_bfloat16* xr = x + px * C;
+    for (int c = lane; c < C; c += 32) xs[c] = __bfloat162float(xr[c]);
+    __syncwarp();
+    for (int c = lane; c < C; c += 32) {
+      float s = 0.0f;
+      const int lo = max(0, c - half), hi = min(C - 1, c + half);
+      for (int j = lo; j <= hi; ++j) s += xs[j] * xs[j];
+      s = k + alpha * s;
+      y[px * C + c] = __float2bfloat16(xs[c] * __powf(s, -beta));
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void lrn_backward_row_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                        __nv_bfloat16* __restrict__ dx, long long pixels, int C, int n, float alpha,
+                                        float beta, float k, int deriv) {
+  extern __shared__ float sm[];
+  const int warps = blockDim.x >> 5;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* xs = sm + warp * 3 * C;
+  float* ps = xs + C;
+  float* ts = ps + C;
+  const int half = n / 2;
+  for (long long px = blockIdx.x * static_cast<long long>(warps) + warp; px < pixels;
+       px += static_cast<long long>(gridDim.x) * warps) {
+    const __nv_bfloat16* xr = x + px * C;
+    const __nv_bfloat16* dr = dy + px * C;
+    for (int c = lane; c < C; c += 32) xs[c] = __bfloat162float(xr[c]);
+    __syncwarp();
+    for (int c = lane; c < C; c += 32) {
+      float s = 0.0f;
+      const int lo = max(0, c - half), hi = min(C - 1, c + half);
+      for (int j = lo; j <= hi; ++j) s += xs[j] * xs[j];
+      s = k + alpha * s;
+      const float p = __powf(s, -beta);
+      const float d = __bfloat162float(dr[c]);
+      ps[c] = d * p;                 // dy * s^-beta
+      ts[c] = d * xs[c] * p / s;     // dy * x * s^(-beta-1)
+    }
+    __syncwarp();
+    for (int c = lane; c < C; c += 32) {
+      float acc = 0.0f;
+      const int lo = max(0, c - half), hi = min(C - 1, c + half);
+      for (int j = lo; j <= hi; ++j) acc += ts[j];
+      float v = ps[c] - 2.0f * alpha * beta * xs[c] * acc;
+      if (deriv) v *= act_deriv_from_output(deriv, xs[c]);
+      dx[px * C + c] = __float2bfloat16(v);
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Launchers (return 1 when the fast path was taken, 0 when the caller must use the generic one,
+// negative on error)
+// ---------------------------------------------------------------------------------------------
+int fast_im2col(const void* x, void* cols, const FastConvGeom& g, cudaStream_t s) {
+  if (g.ld % 8 || (reinterpret_cast<uintptr_t>(cols) & 15)) return 0;
+  const long long total = static_cast<long long>(g.B) * g.OH * g.OW * (g.ld >> 3);
+  if (total == 0) return 1;
+  im2col_any8_kernel<<<grid_cap2(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x),
+                                                           static_cast<__nv_bfloat16*>(cols), g);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 1;
+}
+
+int fast_col2im(const void* dcols, void* dx, const FastConvGeom& g, const void* z, int deriv, cudaStream_t s) {
+  const int Cg = g.C / g.groups;
+  if (Cg % 8 || g.ld % 8 || (reinterpret_cast<uintptr_t>(dcols) & 15) || (reinterpret_cast<uintptr_t>(dx) & 15) ||
+      (z && (reinterpret_cast<uintptr_t>(z) & 15)))
+    return 0;
+  const long long total = static_cast<long long>(g.B) * g.H * g.W * (g.C >> 3);
+  if (total == 0) return 1;
+  col2im_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(static_cast<const __nv_bfloat16*>(dcols),
+                                                           static_cast<__nv_bfloat16*>(dx), g,
+                                                           static_cast<const __nv_bfloat16*>(z), deriv);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 1;
+}
+
+int fast_pool_forward(int kind, const void* x, void* y, int* offs, const FastPoolGeom& g, cudaStream_t s) {
+  if (kind > 2 || g.C % 8 || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15) ||
+      (offs && (reinterpret_cast<uintptr_t>(offs) & 15)))
+    return 0;
+  const long long total = static_cast<long long>(g.B) * g.OH * g.OW * (g.C >> 3);
+  if (total == 0) return 1;
+  pool_forward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(x),
+                                                                 static_cast<__nv_bfloat16*>(y), offs, g);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 1;
+}
+
+int fast_pool_backward(int kind, const void* dy, const int* offs, void* dx, const FastPoolGeom& g, const void* z,
+                       int deriv, cudaStream_t s) {
+  if (g.C % 8 || (reinterpret_cast<uintptr_t>(dy) & 15) || (reinterpret_cast<uintptr_t>(dx) & 15) ||
+      (offs && (reinterpret_cast<uintptr_t>(offs) & 15)) || (z && (reinterpret_cast<uintptr_t>(z) & 15)))
+    return 0;
+  const long long total = static_cast<long long>(g.B) * g.H * g.W * (g.C >> 3);
+  if (total == 0) return 1;
+  pool_backward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(dy), offs,
+                                                                  static_cast<__nv_bfloat16*>(dx), g,
+                                                                  static_cast<const __nv_bfloat16*>(z), deriv);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 1;
+}
+
+int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, float alpha, float beta, float k,
+                     cudaStream_t s) {
+  if (C > 1024) return 0;
+  const int warps = 8;
+  const size_t smem = static_cast<size_t>(warps) * C * sizeof(float);
+  long long blocks = (pixels + warps - 1) / warps;
+  const long long cap = static_cast<long long>(device_sm_count()) * 8;
+  if (blocks > cap) blocks = cap;
+  lrn_forward_row_kernel<<<static_cast<int>(blocks), warps * 32, smem, s>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, n, alpha, beta, k);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 1;
+}
+
+int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels, int C, int n, float alpha, float beta,
+                      float k, int deriv, cudaStream_t s) {
+  if (C > 1024) return 0;
+  const int warps = 4;
+  const size_t smem = static_cast<size_t>(warps) * 3 * C * sizeof(float);
+  long long blocks = (pixels + warps - 1) / warps;
+  const long long cap = static_cast<long long>(device_sm_count()) * 12;
+  if (blocks > cap) blocks = cap;
+  lrn_backward_row_kernel<<<static_cast<int>(blocks), warps * 32, smem, s>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
+      pixels, C, n, alpha, beta, k, deriv);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 1;
+}
+
+}  // namespace vb

@@ -8,6 +8,7 @@
 // and are pinned by the numpy oracles in veles_b200/znicz/.  matrix_reduce
 // replaces cuda/matrix_reduce.cu:35-81 (shared-memory tree) with warp shuffles.
 #include "common.cuh"
+#include "fast_paths.cuh"
 
 namespace vb {
 
@@ -415,13 +416,22 @@ __global__ void row_sum_kernel(const T* __restrict__ a, long long lda, int rows,
 
 constexpr int COLSUM_ROWS_PER_SLAB = 64;
 
+// Rows per slab actually used: at least COLSUM_ROWS_PER_SLAB, grown so that the second pass folds
+// at most ~512 partial rows (a 774400-row conv err_output would otherwise leave 12100 of them).
+static inline int colsum_rows_per_slab(int rows) {
+  int rps = COLSUM_ROWS_PER_SLAB;
+  const int want = (rows + 511) / 512;
+  if (want > rps) rps = (want + COLSUM_ROWS_PER_SLAB - 1) / COLSUM_ROWS_PER_SLAB * COLSUM_ROWS_PER_SLAB;
+  return rps;
+}
+
 template <typename T>
 __global__ void col_sum_partial_kernel(const T* __restrict__ a, long long lda, int rows, int cols,
-                                       float* __restrict__ scratch) {
+                                       float* __restrict__ scratch, int rows_per_slab) {
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
   const int slab = blockIdx.y;
   if (col >= cols) return;
-  const int r0 = slab * COLSUM_ROWS_PER_SLAB, r1 = min(rows, r0 + COLSUM_ROWS_PER_SLAB);
+  const int r0 = slab * rows_per_slab, r1 = min(rows, r0 + rows_per_slab);
   float s = 0.0f;
   for (int r = r0; r < r1; ++r) s += ldf<T>(a + static_cast<long long>(r) * lda + col);
   scratch[static_cast<long long>(slab) * cols + col] = s;
@@ -458,6 +468,9 @@ extern "C" int vb_im2col(const void* x, void* cols, int B, int H, int W, int C, 
     const long long total = rows * (ld >> 3);
     im2col_vec8_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), g);
   } else {
+    FastConvGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx, pad_top, pad_left, groups, ld};
+    const int fr = fast_im2col(x, cols, fg, s);
+    if (fr != 0) return fr < 0 ? fr : 0;
     const long long total = rows * ld;
     im2col_scalar_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), g);
   }
@@ -472,6 +485,11 @@ extern "C" int vb_col2im(const void* dcols, void* dx, int B, int H, int W, int C
   if (int rc = check_geom(g)) return rc;
   const long long total = static_cast<long long>(B) * H * W * C;
   if (total == 0) return 0;
+  {
+    FastConvGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx, pad_top, pad_left, groups, ld};
+    const int fr = fast_col2im(dcols, dx, fg, z, deriv, s);
+    if (fr != 0) return fr < 0 ? fr : 0;
+  }
   col2im_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dcols), static_cast<__nv_bfloat16*>(dx), g,
                                                       static_cast<const __nv_bfloat16*>(z), deriv);
   VB_CHECK_CUDA(cudaGetLastError());
@@ -486,6 +504,11 @@ extern "C" int vb_pool_forward(int kind, const void* x, void* y, int* offs, int 
   const long long total = static_cast<long long>(B) * OH * OW * C;
   if (total == 0) return 0;
   VB_REQUIRE(static_cast<long long>(B) * H * W * C < 2147483647LL, "vb_pool_forward: input too large for int offsets");
+  if (dtype == D_BF16) {
+    FastPoolGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx};
+    const int fr = fast_pool_forward(kind, x, y, offs, fg, s);
+    if (fr != 0) return fr < 0 ? fr : 0;
+  }
   if (dtype == D_F32)
     pool_forward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const float*>(x), static_cast<float*>(y), offs, g, static_cast<const uint16_t*>(rnd_u16));
   else
@@ -494,17 +517,38 @@ extern "C" int vb_pool_forward(int kind, const void* x, void* y, int* offs, int 
   return 0;
 }
 
+extern "C" int vb_activation_backward(int act, const void* err_out, const void* x, const void* y, void* err_in,
+                                      long long n, int dtype, float factor, cudaStream_t s);
+
+// Pooling backward with the optional fused derivative of the activation that produced the pooling
+// input z (err_input *= f'(z)): one pass on the fast path, generic kernel + element-wise pass otherwise.
+extern "C" int vb_pool_backward_fused(int kind, const void* dy, const int* offs, void* dx, int dtype, int B, int H,
+                                      int W, int C, int OH, int OW, int ky, int kx, int sy, int sx, const void* z,
+                                      int deriv, cudaStream_t s);
+
 extern "C" int vb_pool_backward(int kind, const void* dy, const int* offs, void* dx, int dtype, int B, int H, int W,
                                 int C, int OH, int OW, int ky, int kx, int sy, int sx, cudaStream_t s) {
+  return vb_pool_backward_fused(kind, dy, offs, dx, dtype, B, H, W, C, OH, OW, ky, kx, sy, sx, nullptr, 0, s);
+}
+
+extern "C" int vb_pool_backward_fused(int kind, const void* dy, const int* offs, void* dx, int dtype, int B, int H,
+                                      int W, int C, int OH, int OW, int ky, int kx, int sy, int sx, const void* z,
+                                      int deriv, cudaStream_t s) {
   VB_REQUIRE(kind == 2 || offs != nullptr, "vb_pool_backward: max-like pooling needs the offsets recorded in forward");
   PoolGeom g{B, H, W, C, OH, OW, ky, kx, sy, sx};
   const long long total = static_cast<long long>(B) * H * W * C;
   if (total == 0) return 0;
+  if (dtype == D_BF16) {
+    FastPoolGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx};
+    const int fr = fast_pool_backward(kind, dy, offs, dx, fg, (z && deriv) ? z : nullptr, deriv, s);
+    if (fr != 0) return fr < 0 ? fr : 0;
+  }
   if (dtype == D_F32)
     pool_backward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const float*>(dy), offs, static_cast<float*>(dx), g);
   else
     pool_backward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(dy), offs, static_cast<__nv_bfloat16*>(dx), g);
   VB_CHECK_CUDA(cudaGetLastError());
+  if (z && deriv) return vb_activation_backward(deriv, dx, nullptr, z, dx, total, dtype, 1.0f, s);
   return 0;
 }
 
@@ -512,6 +556,10 @@ extern "C" int vb_lrn_forward(const void* x, void* y, int dtype, long long pixel
                               float beta, float k, cudaStream_t s) {
   const long long total = pixels * C;
   if (total == 0) return 0;
+  if (dtype == D_BF16) {
+    const int fr = fast_lrn_forward(x, y, pixels, C, n, alpha, beta, k, s);
+    if (fr != 0) return fr < 0 ? fr : 0;
+  }
   if (dtype == D_F32)
     lrn_forward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const float*>(x), static_cast<float*>(y), pixels, C, n, alpha, beta, k);
   else
@@ -520,15 +568,29 @@ extern "C" int vb_lrn_forward(const void* x, void* y, int dtype, long long pixel
   return 0;
 }
 
+// LRN backward with the optional fused derivative of the activation that produced x (dx *= f'(x)).
+extern "C" int vb_lrn_backward_fused(const void* x, const void* dy, void* dx, int dtype, long long pixels, int C, int n,
+                                     float alpha, float beta, float k, int deriv, cudaStream_t s);
+
 extern "C" int vb_lrn_backward(const void* x, const void* dy, void* dx, int dtype, long long pixels, int C, int n,
                                float alpha, float beta, float k, cudaStream_t s) {
+  return vb_lrn_backward_fused(x, dy, dx, dtype, pixels, C, n, alpha, beta, k, 0, s);
+}
+
+extern "C" int vb_lrn_backward_fused(const void* x, const void* dy, void* dx, int dtype, long long pixels, int C, int n,
+                                     float alpha, float beta, float k, int deriv, cudaStream_t s) {
   const long long total = pixels * C;
   if (total == 0) return 0;
+  if (dtype == D_BF16) {
+    const int fr = fast_lrn_backward(x, dy, dx, pixels, C, n, alpha, beta, k, deriv, s);
+    if (fr != 0) return fr < 0 ? fr : 0;
+  }
   if (dtype == D_F32)
     lrn_backward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const float*>(x), static_cast<const float*>(dy), static_cast<float*>(dx), pixels, C, n, alpha, beta, k);
   else
     lrn_backward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), pixels, C, n, alpha, beta, k);
   VB_CHECK_CUDA(cudaGetLastError());
+  if (deriv) return vb_activation_backward(deriv, dx, nullptr, x, dx, total, dtype, 1.0f, s);
   return 0;
 }
 
@@ -592,10 +654,11 @@ extern "C" int vb_col_sum(const void* a, int dtype, long long lda, int rows, int
                           int accumulate, float* scratch, cudaStream_t s) {
   if (cols == 0) return 0;
   VB_REQUIRE(scratch != nullptr, "vb_col_sum: scratch buffer is required");
-  const int slabs = ceil_div(rows > 0 ? rows : 1, COLSUM_ROWS_PER_SLAB);
+  const int rps = colsum_rows_per_slab(rows);
+  const int slabs = ceil_div(rows > 0 ? rows : 1, rps);
   dim3 grid(ceil_div(cols, 128), slabs);
-  if (dtype == D_F32) col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch);
-  else col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch);
+  if (dtype == D_F32) col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch, rps);
+  else col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch, rps);
   VB_CHECK_CUDA(cudaGetLastError());
   col_sum_final_kernel<<<ceil_div(cols, 128), 128, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate);
   VB_CHECK_CUDA(cudaGetLastError());
@@ -667,9 +730,9 @@ extern "C" int vb_col_sum_static(const void* a, int dtype, long long lda, int ro
   if (int rc = colsum_static_scratch(&scratch)) return rc;
   dim3 grid(ceil_div(cols, 128), slabs);
   if (dtype == D_F32)
-    col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch);
+    col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch, COLSUM_ROWS_PER_SLAB);
   else
-    col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch);
+    col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch, COLSUM_ROWS_PER_SLAB);
   VB_CHECK_CUDA(cudaGetLastError());
   col_sum_final_kernel<<<ceil_div(cols, 128), 128, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate);
   VB_CHECK_CUDA(cudaGetLastError());

@@ -198,13 +198,14 @@ def pool_forward(kind, x, y, offs, ky, kx, sy, sx, rnd=None):
     return y
 
 
-def pool_backward(kind, dy, offs, dx, ky, kx, sy, sx):
+def pool_backward(kind, dy, offs, dx, ky, kx, sy, sx, z=None, deriv=0):
+    """Pooling backward; ``z``/``deriv`` fold in f'(z) of the activation that produced the pooling input."""
     B, H, W, C = dx.shape
     _, OH, OW, _ = dy.shape
-    rc = _lib.lib().vb_pool_backward(c_int(kind), _p(dy), _p(offs), _p(dx), c_int(_dt(dy)), c_int(B), c_int(H),
-                                     c_int(W), c_int(C), c_int(OH), c_int(OW), c_int(ky), c_int(kx), c_int(sy),
-                                     c_int(sx), _stream())
-    _lib.check(rc, "vb_pool_backward")
+    rc = _lib.lib().vb_pool_backward_fused(c_int(kind), _p(dy), _p(offs), _p(dx), c_int(_dt(dy)), c_int(B), c_int(H),
+                                           c_int(W), c_int(C), c_int(OH), c_int(OW), c_int(ky), c_int(kx),
+                                           c_int(sy), c_int(sx), _p(z), c_int(deriv), _stream())
+    _lib.check(rc, "vb_pool_backward_fused")
     LAUNCHES[0] += 1
     return dx
 
@@ -218,11 +219,13 @@ def lrn_forward(x, y, n, alpha, beta, k):
     return y
 
 
-def lrn_backward(x, dy, dx, n, alpha, beta, k):
+def lrn_backward(x, dy, dx, n, alpha, beta, k, deriv=0):
+    """LRN backward; ``deriv`` folds in f'(x) of the activation that produced x."""
     C = x.shape[-1]
-    rc = _lib.lib().vb_lrn_backward(_p(x), _p(dy), _p(dx), c_int(_dt(x)), c_longlong(x.numel() // C), c_int(C),
-                                    c_int(n), c_float(alpha), c_float(beta), c_float(k), _stream())
-    _lib.check(rc, "vb_lrn_backward")
+    rc = _lib.lib().vb_lrn_backward_fused(_p(x), _p(dy), _p(dx), c_int(_dt(x)), c_longlong(x.numel() // C), c_int(C),
+                                          c_int(n), c_float(alpha), c_float(beta), c_float(k), c_int(deriv),
+                                          _stream())
+    _lib.check(rc, "vb_lrn_backward_fused")
     LAUNCHES[0] += 1
     return dx
 

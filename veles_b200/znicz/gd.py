@@ -138,10 +138,11 @@ class GradientDescent(GradientDescentBase):
             kernels.gemm(eo, w_bf16, ei2, b_mn=True, z=x if self.prev_activation else None,
                          deriv=self.prev_activation)
             self.err_input.mark_device_written()
-        gw = self.gradient_weights.devmem.view(w_bf16.shape[0], -1)
+        gw_t, gb_t = self.grad_tensors()
+        gw = gw_t.view(w_bf16.shape[0], -1)
         kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
         if self.bias is not None and self.bias:
-            kernels.col_sum(eo, self.gradient_bias.devmem, self.col_scratch_, accumulate=True)
+            kernels.col_sum(eo, gb_t, self.col_scratch_, accumulate=True)
             self.gradient_bias.mark_device_written()
         self.gradient_weights.mark_device_written()
         self.device_update()

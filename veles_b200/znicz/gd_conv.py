@@ -116,14 +116,15 @@ class GradientDescentConv(GradientDescentBase):
         w_bf16 = f.weights_bf16_
         kg = w_bf16.shape[1]
         cols = f.cols_
-        gw = self.gradient_weights.devmem.view(nk, kg)
+        gw_t, gb_t = self.grad_tensors()
+        gw = gw_t.view(nk, kg)
         for gi in range(G):
             e = eo2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else eo2
             kernels.gemm(e, cols[:, gi * kg:(gi + 1) * kg], gw[gi * nkg:(gi + 1) * nkg], a_mn=True, b_mn=True,
                          accumulate=True, split_k=0)
         self.gradient_weights.mark_device_written()
         if self.bias is not None and self.bias:
-            kernels.col_sum(eo2, self.gradient_bias.devmem, self.col_scratch_, accumulate=True)
+            kernels.col_sum(eo2, gb_t, self.col_scratch_, accumulate=True)
             self.gradient_bias.mark_device_written()
         if self.need_err_input:
             for gi in range(G):

@@ -68,11 +68,9 @@ class GDPooling(GDBase):
             eo = self._eo_stage_
         dy = eo.reshape(f.out_shape4)
         dx = self.err_input.devmem.reshape(f.in_shape4)
+        z = self.input.devmem.reshape(f.in_shape4) if self.prev_activation else None
         kernels.pool_backward(kernels.POOL_KINDS[f.KIND], dy, f.input_offset.devmem if f.KIND != "avg" else None,
-                              dx, f.ky, f.kx, f.sliding[1], f.sliding[0])
-        if self.prev_activation:
-            x = self.input.devmem.reshape(f.in_shape4)
-            kernels.activation_backward(self.prev_activation, dx, None, x, dx)
+                              dx, f.ky, f.kx, f.sliding[1], f.sliding[0], z=z, deriv=self.prev_activation)
         self.err_input.mark_device_written()
 
 

@@ -59,26 +59,29 @@ def act_deriv_numpy(act, y):
 
 class ParameterArena(object):
     """Bump allocator over big device slabs so that all trainable state of a workflow is a
-    handful of contiguous ranges: the fused all-reduce+GD kernel (veles_b200.parallel) walks
-    them with 128-bit loads, and in data-parallel mode the slabs come from symmetric memory
-    (identical offsets on every rank, multicast-mapped)."""
+    handful of contiguous ranges.  ``weights`` slabs are the master layout; ``mirror()`` hands
+    out views of other kinds (gradients, velocity, ...) at the SAME byte offsets, so one
+    (slab, offset, numel) triple addresses weight, gradient and optimizer state alike — which is
+    what the fused all-reduce+GD kernel (veles_b200.parallel) needs.  In data-parallel mode the
+    slabs of the exchanged kinds come from symmetric memory (identical offsets on every rank,
+    multicast-mapped): ``allocator(kind, nbytes)`` decides."""
 
     ALIGN = 256  # bytes
 
     def __init__(self, device, slab_bytes=None, allocator=None):
         self.device = device
-        self.slab_bytes = slab_bytes or int(get(root.common.engine.arena_slab_bytes, 256 << 20))
-        self.allocator = allocator  # callable(nbytes) -> uint8 tensor; default torch.zeros
+        self.slab_bytes = slab_bytes or int(get(root.common.engine.arena_slab_bytes, 512 << 20))
+        self.allocator = allocator  # callable(kind, nbytes) -> uint8 tensor or None (= default)
         self.slabs = {}             # kind -> list of [tensor(uint8), used_bytes]
         self.records = {}           # kind -> list of (name, slab_index, offset_bytes, nbytes)
 
-    def _new_slab(self, nbytes):
+    def _new_slab(self, kind, nbytes):
         import torch
-        if self.allocator is not None:
-            t = self.allocator(nbytes)
-            t.zero_()
-            return t
-        return torch.zeros(nbytes, dtype=torch.uint8, device=self.device.torch_device)
+        t = self.allocator(kind, nbytes) if self.allocator is not None else None
+        if t is None:
+            return torch.zeros(nbytes, dtype=torch.uint8, device=self.device.torch_device)
+        t.zero_()
+        return t
 
     def alloc(self, kind, name, numel, dtype):
         import torch
@@ -86,15 +89,34 @@ class ParameterArena(object):
         nbytes = (numel * esize + self.ALIGN - 1) // self.ALIGN * self.ALIGN
         slabs = self.slabs.setdefault(kind, [])
         if not slabs or slabs[-1][1] + nbytes > slabs[-1][0].numel():
-            slabs.append([self._new_slab(max(self.slab_bytes, nbytes)), 0])
+            slabs.append([self._new_slab(kind, max(self.slab_bytes, nbytes)), 0])
         slab = slabs[-1]
         off = slab[1]
         slab[1] += nbytes
         self.records.setdefault(kind, []).append((name, len(slabs) - 1, off, numel * esize))
         return slab[0][off:off + numel * esize].view(dtype)
 
+    def locate(self, tensor, kind="weights"):
+        """(slab index, byte offset) of a tensor that lives in a slab of ``kind``."""
+        ptr = tensor.data_ptr()
+        for i, (t, _) in enumerate(self.slabs.get(kind, [])):
+            base = t.data_ptr()
+            if base <= ptr < base + t.numel():
+                return i, ptr - base
+        raise ValueError("tensor does not live in a %r slab of this arena" % kind)
+
+    def mirror(self, kind, ref_tensor, ref_kind="weights"):
+        """View of ``kind`` storage at the same (slab, byte offset) as ``ref_tensor`` has in ``ref_kind``."""
+        idx, off = self.locate(ref_tensor, ref_kind)
+        ref_slabs = self.slabs[ref_kind]
+        slabs = self.slabs.setdefault(kind, [])
+        while len(slabs) <= idx:
+            j = len(slabs)
+            slabs.append([self._new_slab(kind, ref_slabs[j][0].numel()), ref_slabs[j][0].numel()])
+        nbytes = ref_tensor.numel() * ref_tensor.element_size()
+        return slabs[idx][0][off:off + nbytes].view(ref_tensor.dtype)
+
     def used_ranges(self, kind, dtype):
-        """[(tensor view of the used part of each slab)] for whole-slab kernels."""
         out = []
         for t, used in self.slabs.get(kind, []):
             if used:
@@ -112,7 +134,7 @@ class NNWorkflow(AcceleratedWorkflow):
 
     def get_arena(self, device):
         if self.arena_ is None or self.arena_.device is not device:
-            self.arena_ = ParameterArena(device, allocator=getattr(self, "arena_allocator_", None))
+            self.arena_ = ParameterArena(device, allocator=self.__dict__.get("arena_allocator_"))
         return self.arena_
 
 
@@ -413,27 +435,37 @@ class GradientDescentBase(GDBase):
             acc.reset(numpy.zeros(like.shape, dtype=numpy.float32))
 
     def place_state(self):
-        """Device: gradient / velocity buffers live in the arena next to the weights."""
+        """Device: gradient / velocity buffers mirror the weights' arena layout."""
         import torch
         arena = find_arena(self, self.device_)
-        if self.weights is not None and self.weights:
-            self._ensure_state(self.weights, self.gradient_weights_with_moment, self.accumulated_gradient_weights)
-            if not self.gradient_weights or self.gradient_weights.shape != self.weights.shape:
-                self.gradient_weights.reset(numpy.zeros(self.weights.shape, dtype=numpy.float32))
-            for kind, arr in (("grads", self.gradient_weights), ("velocity", self.gradient_weights_with_moment),
-                              ("accum", self.accumulated_gradient_weights)):
+        for w, grad, vel, acc in ((self.weights, self.gradient_weights, self.gradient_weights_with_moment,
+                                   self.accumulated_gradient_weights),
+                                  (self.bias, self.gradient_bias, self.gradient_bias_with_moment,
+                                   self.accumulated_gradient_bias)):
+            if w is None or not w:
+                continue
+            self._ensure_state(w, vel, acc)
+            if not grad or grad.shape != w.shape:
+                grad.reset(numpy.zeros(w.shape, dtype=numpy.float32))
+            try:
+                arena.locate(w.devmem)
+                mirrored = True
+            except (ValueError, AttributeError):
+                mirrored = False
+            for kind, arr in (("grads", grad), ("velocity", vel), ("accum", acc)):
                 if arr and arr.devmem is None:
-                    arr.initialize(self.device_, storage=arena.alloc(kind, "%s.w.%s" % (self.name, kind), arr.size,
-                                                                     torch.float32))
-        if self.bias is not None and self.bias:
-            self._ensure_state(self.bias, self.gradient_bias_with_moment, self.accumulated_gradient_bias)
-            if not self.gradient_bias or self.gradient_bias.shape != self.bias.shape:
-                self.gradient_bias.reset(numpy.zeros(self.bias.shape, dtype=numpy.float32))
-            for kind, arr in (("grads", self.gradient_bias), ("velocity", self.gradient_bias_with_moment),
-                              ("accum", self.accumulated_gradient_bias)):
-                if arr and arr.devmem is None:
-                    arr.initialize(self.device_, storage=arena.alloc(kind, "%s.b.%s" % (self.name, kind), arr.size,
-                                                                     torch.float32))
+                    if mirrored:
+                        arr.initialize(self.device_, storage=arena.mirror(kind, w.devmem.view(-1)))
+                    else:
+                        arr.initialize(self.device_, storage=arena.alloc(kind, "%s.%s" % (self.name, kind),
+                                                                         arr.size, torch.float32))
+
+    def grad_tensors(self):
+        """(dW, db) device tensors the backward GEMMs accumulate into this step."""
+        if self.dp_group_ is not None:
+            return self.dp_group_.grads_of(self)
+        return (self.gradient_weights.devmem,
+                self.gradient_bias.devmem if (self.bias is not None and self.bias) else None)
 
     def device_update(self, forward=None):
         """U1: fused single-GPU GD step on weights and bias (or hand over to the DP group)."""

@@ -101,7 +101,5 @@ class LRNormalizerBackward(GDBase):
         ei = self.err_input.devmem
         if eo.dtype != x.dtype or not eo.is_contiguous():
             eo = eo.contiguous().to(x.dtype)
-        kernels.lrn_backward(x, eo.view(x.shape), ei, f.n, f.alpha, f.beta, f.k)
-        if self.prev_activation:
-            kernels.activation_backward(self.prev_activation, ei, None, x, ei)
+        kernels.lrn_backward(x, eo.view(x.shape), ei, f.n, f.alpha, f.beta, f.k, deriv=self.prev_activation)
         self.err_input.mark_device_written()
