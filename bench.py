@@ -87,7 +87,7 @@ def main():
     cfg = MODEL_CONFIGS[args.model]
     B = args.batch or cfg["minibatch"]
     device = B200Device(index=local_rank)
-    use_graph = not args.no_graph
+    use_graph = not args.no_graph and args.impl != "nccl"
 
     def sync_all():
         torch.cuda.synchronize()

@@ -1,0 +1,84 @@
+"""Data-parallel correctness check, run under torchrun with N >= 2 ranks:
+N-rank training with the fused all-reduce+GD kernel (and with the NCCL baseline) must follow the
+same weight trajectory as 1-rank training on the same GLOBAL minibatches."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def run(model, B, steps, dp, rank, world, device, layers_kwargs=None, use_graph=True):
+    from veles_b200.trainer import Trainer
+    tr = Trainer(model, minibatch_size=B, device=device, use_graph=use_graph, data_parallel=dp, n_train=4 * B,
+                 layers_kwargs=layers_kwargs)
+    for _ in range(steps):
+        tr.step_resident()
+    torch.cuda.synchronize()
+    if dp is not None:
+        dp.check()
+    out = []
+    for f in tr.wf.forwards:
+        if getattr(f, "HAS_WEIGHTS", False):
+            f.weights.map_read()
+            f.bias.map_read()
+            out.append((f.weights.mem.copy(), f.bias.mem.copy(), f.weights_bf16_.float().cpu().numpy().copy()))
+    tr.close()
+    return out
+
+
+def main():
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    from veles_b200.backends import B200Device
+    from veles_b200.parallel.dp import DataParallel
+    device = B200Device(index=local_rank)
+    model = sys.argv[1] if len(sys.argv) > 1 else "cifar_convnet"
+    B, steps = 32, 6
+    kw = {"caffe_init": False, "lr": 0.01} if model == "cifar_convnet" else None
+    results = {}
+    for mode in ("fused", "nccl"):
+        for graph in ((True, False) if mode == "fused" else (False,)):
+            dp = DataParallel(mode=mode)
+            results[(mode, graph)] = run(model, B, steps, dp, rank, world, device, kw, use_graph=graph)
+            if rank == 0:
+                print("mode=%s graph=%s multimem=%s world=%d" % (mode, graph, dp.use_multimem, world), flush=True)
+            dist.barrier()
+    ok = True
+    if rank == 0:
+        # single-GPU reference on the same global minibatches (global batch = world * B)
+        ref = run(model, B * world, steps, None, 0, 1, device, kw, use_graph=False)
+        for key, res in results.items():
+            for li, ((w, b, sh), (rw, rb, rsh)) in enumerate(zip(res, ref)):
+                scale = np.abs(rw).max() + 1e-9
+                ew = np.abs(w - rw).max() / scale
+                eb = np.abs(b - rb).max() / (np.abs(rb).max() + 1e-6)
+                es = np.abs(sh - w).max() / scale
+                print("mode=%s graph=%s layer %d: |dW|/|W| = %.3e  |db| = %.3e  shadow-vs-master = %.3e"
+                      % (key[0], key[1], li, ew, eb, es), flush=True)
+                if not (ew < 2e-2 and es < 1e-2 and np.isfinite(w).all()):
+                    ok = False
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.broadcast(flag, 0)
+    # every rank must hold identical weights
+    for key, res in results.items():
+        for w, b, sh in res:
+            t = torch.from_numpy(w).cuda()
+            t0 = t.clone()
+            dist.broadcast(t0, 0)
+            if not torch.equal(t, t0):
+                print("rank %d: weights differ from rank 0 in mode %s" % (rank, key), flush=True)
+                flag.zero_()
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    dist.barrier()
+    dist.destroy_process_group()
+    print("DP_CHECK", "OK" if int(flag.item()) else "FAILED", flush=True)
+    sys.exit(0 if int(flag.item()) else 1)
+
+
+if __name__ == "__main__":
+    main()

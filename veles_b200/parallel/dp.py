@@ -1,0 +1,269 @@
+"""Synchronous data parallelism over the GPUs of one NVSwitch box.
+
+Every rank (one process per GPU) runs the identical workflow on its shard of each global
+minibatch.  What the reference did with a ZeroMQ parameter-server star — pickled weights down,
+pickled gradients up, merged by one Python master under a lock
+(``veles/server.py:141-169, 401-430``, ``veles/client.py:138-160``, ``veles/workflow.py:456-573``) —
+is ONE device kernel per layer here (``csrc/comm_fused.cu``): gradient all-reduce through NVLS
+multicast (or P2P loads), the Znicz GD update in registers, and the updated fp32 weights + bf16
+shadow multicast-stored back to every rank, launched on a side stream as soon as the layer's
+backward GEMMs are enqueued so it overlaps the rest of the backward pass.
+
+``mode="nccl"`` is the conventional baseline (NCCL all-reduce, then the local GD kernel).
+
+torch.distributed is used only for plumbing: rendezvous of symmetric-memory slabs
+(``torch.distributed._symmetric_memory``), epoch-boundary counter sums, barriers.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_double, c_float, c_int, c_longlong, c_void_p
+
+import numpy
+
+SYMMETRIC_KINDS = ("weights", "weights_bf16", "grads", "grads1", "dp_flags")
+MAX_WORLD = 8
+
+
+class DataParallel(object):
+    def __init__(self, mode="fused", n_ctas=32, timeout_s=20.0, use_multimem=None):
+        import torch
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            raise RuntimeError("DataParallel needs an initialised torch.distributed process group")
+        self.mode = mode
+        self.rank = dist.get_rank()
+        self.world_size = dist.get_world_size()
+        if self.world_size > MAX_WORLD:
+            raise ValueError("the fused kernel supports at most %d ranks" % MAX_WORLD)
+        self.n_ctas = n_ctas
+        self.timeout_s = timeout_s
+        self.use_multimem = use_multimem
+        self.parity = 0
+        self.grad_scale = 1.0      # 1/world when every rank normalised by its LOCAL batch size
+        self.units = []            # GD units in registration order -> channel index
+        self.unit_info = {}
+        self.handles = {}          # id(slab tensor) -> symm handle
+        self.symm_slabs = []       # [(kind, tensor)] in allocation order (identical on every rank)
+        self.comm_stream = None
+        self.arena = None
+        self.wf = None
+        self._dist = dist
+        self._pending_events = []
+
+    # -- setup -----------------------------------------------------------------------------------------------
+    def attach(self, wf):
+        """Before ``wf.initialize``: route the exchanged arena kinds into symmetric memory."""
+        self.wf = wf
+        if self.mode == "fused":
+            wf.arena_allocator_ = self._allocate
+        wf.dp_group_ = self
+
+    def _allocate(self, kind, nbytes):
+        if kind not in SYMMETRIC_KINDS:
+            return None
+        import torch
+        import torch.distributed._symmetric_memory as symm_mem
+        t = symm_mem.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+        self.symm_slabs.append((kind, t))
+        return t
+
+    def finalize(self, wf):
+        """After ``wf.initialize``: exchange handles, describe every GD unit's segments."""
+        import torch
+        import torch.distributed._symmetric_memory as symm_mem
+        dev = wf.device
+        self.comm_stream = torch.cuda.Stream(device=dev.torch_device)
+        self.arena = wf.get_arena(dev)
+        for gd in wf.gds:
+            if hasattr(gd, "gradient_weights") and gd.weights is not None and gd.weights:
+                gd.dp_group_ = self
+                self.units.append(gd)
+        if hasattr(wf, "decision") and wf.decision is not None:
+            wf.decision.dp_group = self
+        if self.mode != "fused":
+            return
+        if len(self.units) > 64:
+            raise ValueError("at most 64 trainable layers are supported by the flag layout")
+        arena = self.arena
+        # second gradient parity + flag words, mirrored/allocated identically on every rank
+        for gd in self.units:
+            for w in (gd.weights, gd.bias):
+                if w is not None and w:
+                    arena.mirror("grads1", w.devmem.view(-1))
+        self.flags = arena.alloc("dp_flags", "flags", 64 * 2 * MAX_WORLD, torch.int32)
+        self.epochs = torch.zeros(64, dtype=torch.int32, device=dev.torch_device)
+        self.cta_counter = torch.zeros(64, dtype=torch.int32, device=dev.torch_device)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev.torch_device)
+        torch.cuda.synchronize()
+        group = self._dist.group.WORLD
+        for kind, t in self.symm_slabs:
+            hdl = symm_mem.rendezvous(t, group=group)
+            self.handles[t.data_ptr()] = hdl
+        if self.use_multimem is None:
+            self.use_multimem = all(int(h.multicast_ptr) != 0 for h in self.handles.values())
+        for ch, gd in enumerate(self.units):
+            self.unit_info[id(gd)] = self._describe(ch, gd)
+        self._dist.barrier()
+        torch.cuda.synchronize()
+
+    def _slab_ptrs(self, kind, idx):
+        """(local base, multicast base or 0, [peer bases]) of slab ``idx`` of ``kind``."""
+        t = self.arena.slabs[kind][idx][0]
+        hdl = self.handles[t.data_ptr()]
+        delta = t.data_ptr() - int(hdl.buffer_ptrs[self.rank])
+        peers = [int(p) + delta for p in hdl.buffer_ptrs]
+        mc = int(hdl.multicast_ptr)
+        return t.data_ptr(), (mc + delta) if mc else 0, peers
+
+    def _describe(self, channel, gd):
+        import torch
+        arena = self.arena
+        fwd = gd.forward
+        segs, hyper_keys = [], []
+        slab_idx = None
+        for w, is_bias in ((gd.weights, False), (gd.bias, True)):
+            if w is None or not w:
+                continue
+            idx, off = arena.locate(w.devmem)
+            if slab_idx is None:
+                slab_idx = idx
+            elif idx != slab_idx:
+                raise ValueError("weights and bias of %s live in different arena slabs" % gd.name)
+            shadow_off, row_len, row_pitch = -1, 1, 1
+            if not is_bias and fwd is not None and fwd.weights_bf16_ is not None:
+                sh = fwd.weights_bf16_
+                sidx, soff = arena.locate(sh, "weights_bf16")
+                if sidx != 0 and len(arena.slabs["weights_bf16"]) > 1:
+                    pass
+                self._shadow_slab = sidx
+                shadow_off, row_len, row_pitch = soff // 2, sh.shape[1], sh.stride(0)
+            segs.append([off // 4, w.size, shadow_off, row_len, row_pitch])
+            hyper_keys.append("bias" if is_bias else "weights")
+        info = {"channel": channel, "slab": slab_idx, "segs": segs, "kinds": hyper_keys,
+                "shadow_slab": getattr(self, "_shadow_slab", 0)}
+        info["grads"] = [self._slab_ptrs("grads", slab_idx), self._slab_ptrs("grads1", slab_idx)]
+        info["weights"] = self._slab_ptrs("weights", slab_idx)
+        info["shadow"] = self._slab_ptrs("weights_bf16", info["shadow_slab"])
+        info["vel"] = arena.slabs["velocity"][slab_idx][0].data_ptr()
+        fl_idx, fl_off = arena.locate(self.flags, "dp_flags")
+        fl = self._slab_ptrs("dp_flags", fl_idx)
+        info["flags"] = (fl[0] + fl_off, [p + fl_off for p in fl[2]])
+        # per-parity views for the backward GEMMs
+        views = []
+        for kind in ("grads", "grads1"):
+            slab = arena.slabs[kind][slab_idx][0]
+            pair = []
+            for w in (gd.weights, gd.bias):
+                if w is None or not w:
+                    pair.append(None)
+                    continue
+                _, off = arena.locate(w.devmem)
+                pair.append(slab[off:off + w.size * 4].view(torch.float32))
+            views.append(tuple(pair))
+        info["views"] = views
+        return info
+
+    # -- per step ---------------------------------------------------------------------------------------------------
+    def grads_of(self, gd):
+        if self.mode != "fused":
+            return (gd.gradient_weights.devmem, gd.gradient_bias.devmem if (gd.bias is not None and gd.bias) else None)
+        return self.unit_info[id(gd)]["views"][self.parity]
+
+    def update_unit(self, gd):
+        import torch
+        if self.mode == "fused":
+            return self._update_fused(gd)
+        # --- NCCL baseline: all-reduce, then the single-GPU fused GD kernel
+        dist = self._dist
+        op = dist.ReduceOp.AVG if self.grad_scale != 1.0 else dist.ReduceOp.SUM
+        dist.all_reduce(gd.gradient_weights.devmem, op=op)
+        if gd.bias is not None and gd.bias:
+            dist.all_reduce(gd.gradient_bias.devmem, op=op)
+        group, gd.dp_group_ = gd.dp_group_, None
+        try:
+            gd.device_update()
+        finally:
+            gd.dp_group_ = group
+
+    def _update_fused(self, gd):
+        import torch
+        from ..ops import _lib
+        info = self.unit_info[id(gd)]
+        main = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self.comm_stream.wait_event(ev)
+        nseg = len(info["segs"])
+        segs = (c_longlong * (5 * nseg))(*[int(v) for s in info["segs"] for v in s])
+        hyper = []
+        for kind in info["kinds"]:
+            if kind == "weights":
+                hyper += [gd.learning_rate, gd.weights_decay, gd.l1_vs_l2, gd.gradient_moment]
+            else:
+                hyper += [gd.learning_rate_bias, gd.weights_decay_bias, gd.l1_vs_l2_bias, gd.gradient_moment_bias]
+        hyper = (c_float * (4 * nseg))(*hyper)
+        g_local, g_mc, g_peers = info["grads"][self.parity]
+        go_local = info["grads"][1 - self.parity][0]
+        w_local, w_mc, w_peers = info["weights"]
+        s_local, s_mc, s_peers = info["shadow"]
+        f_local, f_peers = info["flags"]
+        W = self.world_size
+
+        def arr(ptrs):
+            return (c_void_p * W)(*[c_void_p(p) for p in ptrs])
+
+        with torch.cuda.stream(self.comm_stream):
+            rc = _lib.lib().vb_fused_allreduce_gd(
+                c_int(W), c_int(self.rank), c_int(info["channel"]), c_int(nseg), segs, hyper,
+                c_void_p(g_local), c_void_p(g_mc), arr(g_peers), c_void_p(go_local),
+                c_void_p(w_local), c_void_p(w_mc), arr(w_peers), c_void_p(info["vel"]),
+                c_void_p(s_local), c_void_p(s_mc), arr(s_peers), c_void_p(f_local), arr(f_peers),
+                c_void_p(self.epochs.data_ptr()), c_void_p(self.cta_counter.data_ptr()),
+                c_void_p(self.status.data_ptr()), c_float(self.grad_scale), c_int(self.n_ctas),
+                c_int(1 if self.use_multimem else 0), c_double(self.timeout_s),
+                c_void_p(self.comm_stream.cuda_stream))
+            _lib.check(rc, "vb_fused_allreduce_gd")
+            from ..ops import kernels
+            kernels.LAUNCHES[0] += 1
+            done = torch.cuda.Event()
+            done.record(self.comm_stream)
+        self._pending_events.append(done)
+        gd.weights.mark_device_written()
+        if gd.bias is not None and gd.bias:
+            gd.bias.mark_device_written()
+
+    def finish_step(self):
+        """Join the comm stream into the compute stream and flip the gradient parity."""
+        import torch
+        main = torch.cuda.current_stream()
+        for ev in self._pending_events:
+            main.wait_event(ev)
+        self._pending_events = []
+        if self.mode == "fused":
+            self.parity ^= 1
+
+    def check(self):
+        """Raise if any fused kernel hit its synchronisation timeout (reads one int from the device)."""
+        if self.mode == "fused":
+            st = int(self.status.item())
+            if st:
+                raise RuntimeError("fused all-reduce+GD kernel timed out waiting for peers (channel %d)" % (st - 1))
+
+    # -- epoch-boundary reductions (Decision) -----------------------------------------------------------------------------
+    def sum_counters(self, vals, loss):
+        import torch
+        t = torch.tensor(list(map(float, vals)) + [float(loss)], dtype=torch.float64, device="cuda")
+        self._dist.all_reduce(t)
+        out = t.cpu().numpy()
+        return numpy.round(out[:-1]).astype(numpy.int64), float(out[-1])
+
+    def max_min(self, mx, mn):
+        import torch
+        t = torch.tensor([mx, -mn], dtype=torch.float64, device="cuda")
+        self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX)
+        out = t.cpu().numpy()
+        return float(out[0]), float(-out[1])
+
+    def barrier(self):
+        self._dist.barrier()

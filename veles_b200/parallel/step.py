@@ -29,7 +29,7 @@ class FlatStep(object):
         wf = self.wf
         hyper = tuple((gd.learning_rate, gd.learning_rate_bias, gd.weights_decay, gd.gradient_moment)
                       for gd in wf.gds if hasattr(gd, "learning_rate"))
-        return (bool(train), int(wf.loader.minibatch_size), hyper)
+        return (bool(train), int(wf.loader.minibatch_size), hyper, getattr(self.comm, "parity", 0))
 
     def _body(self, train):
         wf = self.wf

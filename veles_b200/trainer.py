@@ -44,10 +44,14 @@ class Trainer(object):
         else:
             if len(self.cfg["sample_shape"]) == 3:
                 extra.setdefault("normalization_type", "mean_disp")
-        self.wf = build_workflow(model, minibatch_size=self.minibatch_size,
-                                 n_train=n_train or 8 * self.minibatch_size, n_valid=0, max_epochs=None,
-                                 loader_extra=extra, layers_kwargs=layers_kwargs, **kwargs) if not streaming else \
+        # data parallel: the loader serves GLOBAL minibatches of world*B and materialises this rank's B rows
+        self.wf = build_workflow(model, minibatch_size=self.minibatch_size * self.world,
+                                 n_train=(n_train or 8 * self.minibatch_size) * self.world, n_valid=0,
+                                 max_epochs=None, loader_extra=extra, layers_kwargs=layers_kwargs,
+                                 shard_rank=self.rank, shard_world=self.world, **kwargs) if not streaming else \
             self._build_streaming(model, extra, layers_kwargs)
+        if data_parallel is not None and streaming:
+            data_parallel.grad_scale = 1.0 / self.world  # every rank divided by its local batch size
         if data_parallel is not None:
             data_parallel.attach(self.wf)
         self.wf.initialize(device=self.device)

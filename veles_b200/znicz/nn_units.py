@@ -67,6 +67,7 @@ class ParameterArena(object):
     multicast-mapped): ``allocator(kind, nbytes)`` decides."""
 
     ALIGN = 256  # bytes
+    SMALL_KINDS = {"dp_flags": 1 << 16}
 
     def __init__(self, device, slab_bytes=None, allocator=None):
         self.device = device
@@ -89,7 +90,7 @@ class ParameterArena(object):
         nbytes = (numel * esize + self.ALIGN - 1) // self.ALIGN * self.ALIGN
         slabs = self.slabs.setdefault(kind, [])
         if not slabs or slabs[-1][1] + nbytes > slabs[-1][0].numel():
-            slabs.append([self._new_slab(kind, max(self.slab_bytes, nbytes)), 0])
+            slabs.append([self._new_slab(kind, max(self.SMALL_KINDS.get(kind, self.slab_bytes), nbytes)), 0])
         slab = slabs[-1]
         off = slab[1]
         slab[1] += nbytes
