@@ -483,8 +483,8 @@ class Loader(AcceleratedUnit, metaclass=UserLoaderRegistry):
                 "last_minibatch": bool(self.last_minibatch), "epoch_ended": bool(self.epoch_ended),
                 "train_ended": bool(self.train_ended), "test_ended": bool(self.test_ended)}
         # epoch boundary = sync point: wait for every outstanding update before serving on
-        if self.class_ended and self.pending_minibatches_count > 1:
-            self.has_data_for_slave = False
+        if self.class_ended:
+            self.has_data_for_slave = False   # re-enabled when the last outstanding update has arrived
         return data
 
     def _stop_after_epoch(self, slave):

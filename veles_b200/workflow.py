@@ -284,6 +284,9 @@ class Workflow(Container):
         self._sync_event_.clear()
         self._finished_ = False
         self._is_running = True
+        self._stopped = False
+        for unit in self._units:
+            unit.stopped = False  # a finished workflow stopped its units; a new run (next slave job) revives them
         self._run_time_started_ = time.time()
         self.event("run", "begin")
         if not self.is_master:
@@ -359,7 +362,9 @@ class Workflow(Container):
                     "apply_data_from_slave", "drop_slave"))
 
     def _dist_units(self):
-        return [u for u in self.units_in_dependency_order if u is not self and self._distributable(u)]
+        # creation order: identical on master and slave (both execute the same constructor), whereas the
+        # BFS order depends on mode-specific links (e.g. where EndPoint hangs on a slave)
+        return [u for u in self._units if u is not self and self._distributable(u)]
 
     def generate_data_for_master(self):
         self.event("generate_data", "begin", side="slave")

@@ -75,6 +75,10 @@ class DecisionBase(Unit):
     def run(self):
         klass = int(self.minibatch_class)
         self.gd_skip <<= (klass != TRAIN) or self.testing
+        if self.is_slave:
+            # a slave job is ONE minibatch: close the loop, the master accumulates the statistics
+            self.complete <<= True
+            return
         self.on_minibatch(klass)
         if not self.last_minibatch:
             return
@@ -106,17 +110,33 @@ class DecisionBase(Unit):
         if stop:
             self.complete <<= True
 
-    # job-level master/slave (the master accumulates what slaves evaluated)
+    # -- job-level master/slave: the slave reports per-minibatch statistics, the master owns epochs ---------
     def generate_data_for_slave(self, slave):
-        return None
-
-    def generate_data_for_master(self):
-        return None
+        return {"epoch_number": int(self.epoch_number)}
 
     def apply_data_from_master(self, data):
-        pass
+        self.complete <<= False
+        self.improved <<= False
+
+    def generate_data_for_master(self):
+        data = {"minibatch_class": int(self.minibatch_class), "last_minibatch": bool(self.last_minibatch),
+                "epoch_ended": bool(self.epoch_ended), "stats": self.collect_minibatch_stats()}
+        return data
 
     def apply_data_from_slave(self, data, slave):
+        klass = data["minibatch_class"]
+        self.merge_minibatch_stats(klass, data["stats"])
+        # the MASTER's loader flags (already refreshed by Loader.apply_data_from_slave, which precedes this
+        # unit) say whether that was the last outstanding minibatch of the class / epoch
+        if self.last_minibatch:
+            self.on_class_ended(klass)
+            if self.epoch_ended:
+                self.on_epoch_ended()
+
+    def collect_minibatch_stats(self):
+        return None
+
+    def merge_minibatch_stats(self, klass, stats):
         pass
 
     def drop_slave(self, slave):
@@ -190,8 +210,22 @@ class DecisionGD(DecisionBase):
             ms.mem[0] = 0
             ms.unmap()
 
+    def collect_minibatch_stats(self):
+        saved = (list(self.epoch_n_err), list(self.epoch_n_evaluated), list(self.epoch_loss))
+        self.epoch_n_err, self.epoch_n_evaluated, self.epoch_loss = [0, 0, 0], [0, 0, 0], [0.0, 0.0, 0.0]
+        klass = int(self.minibatch_class)
+        self._drain(klass)
+        stats = (self.epoch_n_err[klass], self.epoch_n_evaluated[klass], self.epoch_loss[klass])
+        self.epoch_n_err, self.epoch_n_evaluated, self.epoch_loss = saved
+        return stats
+
+    def merge_minibatch_stats(self, klass, stats):
+        self.epoch_n_err[klass] += stats[0]
+        self.epoch_n_evaluated[klass] += stats[1]
+        self.epoch_loss[klass] += stats[2]
+
     def on_class_ended(self, klass):
-        if self._counters_on_device():
+        if self._counters_on_device() and not self.is_master:
             self._drain(klass)
         n = max(self.epoch_n_evaluated[klass], 1)
         self.epoch_n_err_pt[klass] = 100.0 * self.epoch_n_err[klass] / n
@@ -284,8 +318,25 @@ class DecisionMSE(DecisionBase):
         ne.mem[:2] = 0
         ne.unmap()
 
+    def collect_minibatch_stats(self):
+        saved = ([list(m) for m in self.epoch_metrics], list(self.epoch_n_evaluated))
+        self.epoch_metrics = [[0.0, 0.0, 1e30] for _ in range(3)]
+        self.epoch_n_evaluated = [0, 0, 0]
+        klass = int(self.minibatch_class)
+        self._drain(klass)
+        stats = (list(self.epoch_metrics[klass]), self.epoch_n_evaluated[klass])
+        self.epoch_metrics, self.epoch_n_evaluated = saved
+        return stats
+
+    def merge_minibatch_stats(self, klass, stats):
+        e = self.epoch_metrics[klass]
+        e[0] += stats[0][0]
+        e[1] = max(e[1], stats[0][1])
+        e[2] = min(e[2], stats[0][2])
+        self.epoch_n_evaluated[klass] += stats[1]
+
     def on_class_ended(self, klass):
-        if self._on_device():
+        if self._on_device() and not self.is_master:
             self._drain(klass)
         self.epoch_rmse[klass] = self.epoch_metrics[klass][0] / max(self.epoch_n_evaluated[klass], 1)
         if klass == self.decisive_class:

@@ -221,7 +221,7 @@ class Forward(ForwardBase):
     def init_unpickled(self):
         super(Forward, self).init_unpickled()
         self.weights_bf16_ = None   # bf16 shadow of the weights TMA-loaded by the GEMMs
-        self.forward_mode = False
+        self.job_weights_ = None
 
     # -- weights ---------------------------------------------------------------------------------------
     def fill_array(self, filling, arr, stddev):
@@ -294,15 +294,31 @@ class Forward(ForwardBase):
         data["activation_mode"] = {v: k for k, v in ACTIVATIONS.items()}[self.ACTIVATION]
         return data
 
-    # -- job-level distribution: weights travel only for genetics/ensemble style jobs ----------------------
+    # -- job-level master/slave protocol (the reference's asynchronous parameter-server mode) --------------
     def generate_data_for_slave(self, slave):
-        return None
+        """Master: ship the current weights with every job."""
+        self.weights.map_read()
+        data = {"weights": self.weights.mem.copy()}
+        if self.include_bias and self.bias:
+            self.bias.map_read()
+            data["bias"] = self.bias.mem.copy()
+        return data
 
     def generate_data_for_master(self):
         return None
 
     def apply_data_from_master(self, data):
-        pass
+        """Slave: adopt the job's weights (remembered so the GD unit can return a delta)."""
+        self.weights.map_invalidate()
+        numpy.copyto(self.weights.mem, data["weights"])
+        self.weights.unmap()
+        if "bias" in data and self.bias:
+            self.bias.map_invalidate()
+            numpy.copyto(self.bias.mem, data["bias"])
+            self.bias.unmap()
+        self.job_weights_ = (data["weights"], data.get("bias"))
+        if self.on_device and self.weights_bf16_ is not None:
+            self.refresh_shadow()
 
     def apply_data_from_slave(self, data, slave):
         pass
@@ -370,7 +386,7 @@ class GradientDescentBase(GDBase):
         self.gradient_moment = kwargs.get("gradient_moment", 0.0)
         self.gradient_moment_bias = kwargs.get("gradient_moment_bias", self.gradient_moment)
         self.accumulate_gradient = kwargs.get("accumulate_gradient", False)
-        self.apply_gradient = kwargs.get("apply_gradient", not workflow.is_slave if hasattr(workflow, "is_slave") else True)
+        self.apply_gradient = kwargs.get("apply_gradient", True)
         self.factor_ortho = kwargs.get("factor_ortho", 0.0)
         self.fast_learning_rate = kwargs.get("fast_learning_rate", None)
         self.adagrad_epsilon = kwargs.get("adagrad_epsilon", 1e-6)
@@ -501,7 +517,8 @@ class GradientDescentBase(GDBase):
             self.bias.mark_device_written()
             self.gradient_bias_with_moment.mark_device_written()
 
-    # job-level distribution hooks (hyper-parameters may be pushed by a genetics master)
+    # -- job-level master/slave protocol: the slave trains one minibatch locally and returns the weight DELTA,
+    #    the master adds deltas as they arrive (asynchronous SGD, like the reference's parameter server)
     def generate_data_for_slave(self, slave):
         return {"learning_rate": self.learning_rate, "learning_rate_bias": self.learning_rate_bias,
                 "weights_decay": self.weights_decay, "weights_decay_bias": self.weights_decay_bias,
@@ -512,10 +529,25 @@ class GradientDescentBase(GDBase):
             setattr(self, k, v)
 
     def generate_data_for_master(self):
-        return None
+        fwd = self.forward
+        if fwd is None or fwd.job_weights_ is None or self.weights is None or not self.weights:
+            return None
+        self.weights.map_read()
+        w0, b0 = fwd.job_weights_
+        data = {"dw": self.weights.mem - w0}
+        if self.bias is not None and self.bias and b0 is not None:
+            self.bias.map_read()
+            data["db"] = self.bias.mem - b0
+        return data
 
     def apply_data_from_slave(self, data, slave):
-        pass
+        if not data or self.weights is None or not self.weights:
+            return
+        self.weights.map_write()
+        self.weights.mem += data["dw"]
+        if "db" in data and self.bias is not None and self.bias:
+            self.bias.map_write()
+            self.bias.mem += data["db"]
 
     def drop_slave(self, slave):
         pass

@@ -366,6 +366,8 @@ class StandardWorkflow(StandardWorkflowBase):
         return self.repeater
 
     def link_end_point(self, *parents):
+        if self.is_slave and self.gds:
+            parents = (self.gds[0],)  # a slave job ends after the LAST backward unit of its single pass
         self.end_point.link_from(*parents)
         self.end_point.gate_block = ~self.decision.complete
         return self.end_point
