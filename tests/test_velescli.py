@@ -1,0 +1,103 @@
+"""CLI: run a sample workflow, result file, snapshot + resume, dry runs, seeding, genetics, ensembles
+(pattern of veles/tests/test_velescli.py:52-94)."""
+import glob
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SAMPLES = os.path.join(ROOT, "veles_b200", "znicz", "samples")
+ENV = dict(os.environ, PYTHONPATH=ROOT)
+
+
+def cli(*args, timeout=300):
+    cmd = [sys.executable, "-m", "veles_b200", "--no-logo", "-v", "warning", "-a", "numpy"] + list(args)
+    return subprocess.run(cmd, cwd=ROOT, env=ENV, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=timeout)
+
+
+def test_run_sample_with_result_file_snapshot_and_resume(tmp_path):
+    res = tmp_path / "res.json"
+    snaps = tmp_path / "snaps"
+    r = cli("--result-file", str(res), "-r", "1234", os.path.join(SAMPLES, "mnist.py"), "-",
+            "root.mnist.decision.max_epochs=2", 'root.common.dirs.snapshots="%s"' % snaps)
+    assert r.returncode == 0, r.stdout.decode()[-2000:]
+    data = json.loads(res.read_text())
+    assert 0.8 < data["EvaluationFitness"] <= 1.0
+    assert data["Total epochs"] >= 2 and "Snapshot" in data and len(data["Labels"]) == 10
+    current = glob.glob(str(snaps / "mnist_current*"))
+    assert current and os.path.islink(current[0])
+    # resume: the restored workflow continues from epoch 2 and stops at max_epochs=3
+    res2 = tmp_path / "res2.json"
+    r = cli("--result-file", str(res2), "-w", current[0], os.path.join(SAMPLES, "mnist.py"), "-",
+            "root.mnist.decision.max_epochs=3", 'root.common.dirs.snapshots="%s"' % snaps)
+    assert r.returncode == 0, r.stdout.decode()[-2000:]
+    d2 = json.loads(res2.read_text())
+    assert d2["Total epochs"] >= data["Total epochs"]
+
+
+def test_dry_run_and_graph_and_config_dump(tmp_path):
+    graph = tmp_path / "wf.dot"
+    r = cli("--dry-run", "init", "--workflow-graph", str(graph), os.path.join(SAMPLES, "mnist.py"), "-")
+    assert r.returncode == 0, r.stdout.decode()[-2000:]
+    text = graph.read_text()
+    assert "digraph" in text and "All2AllTanh" in text and "GDSoftmax" in text
+    r = cli("--dump-config", os.path.join(SAMPLES, "mnist.py"), "-")
+    assert r.returncode == 0 and b"loader_name" in r.stdout
+    r = cli("--version")
+    assert r.returncode == 0 and b"veles_b200" in r.stdout
+
+
+def test_same_seed_same_result(tmp_path):
+    outs = []
+    for i in range(2):
+        res = tmp_path / ("r%d.json" % i)
+        r = cli("--result-file", str(res), "-r", "00ff00ff", os.path.join(SAMPLES, "mnist.py"), "-",
+                "root.mnist.decision.max_epochs=1", "root.mnist.loader.n_train=500",
+                "root.common.disable.snapshotting=True")
+        assert r.returncode == 0, r.stdout.decode()[-2000:]
+        outs.append(json.loads(res.read_text())["Errors"])
+    assert outs[0] == outs[1]
+
+
+def test_callable_module_runs_in_process(tmp_path):
+    code = ("import veles_b200, json; l = veles_b200(%r, '-', 'root.mnist.decision.max_epochs=1', "
+            "'root.mnist.loader.n_train=300', 'root.common.disable.snapshotting=True', backend='numpy', "
+            "verbosity='error', no_logo=True); print('FIT', l.workflow.gather_results()['EvaluationFitness'])"
+            % os.path.join(SAMPLES, "mnist.py"))
+    r = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=ENV, stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, timeout=300)
+    assert r.returncode == 0 and b"FIT" in r.stdout, r.stdout.decode()[-2000:]
+
+
+def test_genetic_optimization_of_ranges(tmp_path):
+    res = tmp_path / "gen.json"
+    r = cli("--optimize", "3:2", "--result-file", str(res), os.path.join(SAMPLES, "mnist.py"), "-",
+            "root.mnist.decision.max_epochs=1", "root.mnist.loader.n_train=400", "root.mnist.loader.n_valid=200",
+            "root.common.disable.snapshotting=True", timeout=600)
+    assert r.returncode == 0, r.stdout.decode()[-3000:]
+    data = json.loads(res.read_text())
+    assert data["Generations"] == 2 and data["EvaluationFitness"] > 0.1
+    assert any("learning_rate" in k for k in data["BestGenes"])
+    best = os.path.join(SAMPLES, "mnist_best_config.py")
+    assert os.path.exists(best)
+    os.remove(best)
+
+
+def test_ensemble_train_then_test(tmp_path):
+    res = tmp_path / "ens.json"
+    snaps = tmp_path / "snaps"
+    r = cli("--ensemble-train", "2:0.8", "--result-file", str(res), os.path.join(SAMPLES, "mnist.py"), "-",
+            "root.mnist.decision.max_epochs=1", "root.mnist.loader.n_train=400", "root.mnist.loader.n_valid=200",
+            'root.common.dirs.snapshots="%s"' % snaps, timeout=600)
+    assert r.returncode == 0, r.stdout.decode()[-3000:]
+    data = json.loads(res.read_text())
+    assert len(data["models"]) == 2 and all("EvaluationFitness" in m and "Snapshot" in m for m in data["models"])
+    res2 = tmp_path / "ens_test.json"
+    r = cli("--ensemble-test", str(res), "--result-file", str(res2), os.path.join(SAMPLES, "mnist.py"), "-",
+            "root.mnist.loader.n_train=400", "root.mnist.loader.n_valid=200", timeout=600)
+    assert r.returncode == 0, r.stdout.decode()[-3000:]
+    d2 = json.loads(res2.read_text())
+    assert len(d2["models"]) == 2 and all("EvaluationFitness" in m for m in d2["models"])
