@@ -290,7 +290,15 @@ class Workflow(Container):
         self._run_time_started_ = time.time()
         self.event("run", "begin")
         if not self.is_master:
-            self.start_point.run_dependent()
+            # a nested workflow runs inside its parent's dispatch loop: give it a loop of its own,
+            # otherwise its first unit would only be queued behind this very call
+            from . import units as _units
+            saved = getattr(_units._tls, "queue", None)
+            _units._tls.queue = None
+            try:
+                self.start_point.run_dependent()
+            finally:
+                _units._tls.queue = saved
         if self._sync:
             self.wait_finished()
 
@@ -342,8 +350,8 @@ class Workflow(Container):
             if self.is_slave and self._do_job_callback_ is not None:
                 cb, self._do_job_callback_ = self._do_job_callback_, None
                 cb(self.generate_data_for_master())
-            elif host is not None and hasattr(host, "on_workflow_finished"):
-                host.on_workflow_finished()
+            elif host is not None and hasattr(host, "on_workflow_finished") and not isinstance(host, Workflow):
+                host.on_workflow_finished()   # launchers only: a parent workflow just sees run() return
         finally:
             self._sync_event_.set()
 
