@@ -1,0 +1,178 @@
+"""Forge server: stores versioned model packages and answers ``list``, ``details``, ``fetch``, ``upload``, ``delete``.
+
+Parity target: ``veles/forge/forge_server.py:462-915`` (Tornado, git-backed storage, e-mail confirmed tokens).
+Here: ``http.server`` + a directory per model with numbered versions; uploads need a token from ``register``."""
+from __future__ import annotations
+
+import json
+import os
+import shutil
+import threading
+import time
+import uuid
+from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
+from urllib.parse import urlparse, parse_qs
+
+from ..logger import Logger
+from .forge_common import unpack, validate_manifest
+
+
+class ForgeServer(Logger):
+    def __init__(self, root_dir, host="127.0.0.1", port=0):
+        super(ForgeServer, self).__init__()
+        self.root_dir = os.path.abspath(root_dir)
+        os.makedirs(self.root_dir, exist_ok=True)
+        self.host, self.port = host, port
+        self.tokens_file = os.path.join(self.root_dir, "tokens.json")
+        self.tokens = {}
+        if os.path.exists(self.tokens_file):
+            with open(self.tokens_file) as f:
+                self.tokens = json.load(f)
+        self.lock = threading.Lock()
+        self.httpd = None
+
+    # -- storage ----------------------------------------------------------------------------------------------
+    def model_dir(self, name):
+        if not name or "/" in name or name.startswith("."):
+            raise ValueError("invalid model name %r" % name)
+        return os.path.join(self.root_dir, "models", name)
+
+    def versions(self, name):
+        d = self.model_dir(name)
+        return sorted((v for v in os.listdir(d) if v.isdigit()), key=int) if os.path.isdir(d) else []
+
+    def list(self):
+        base = os.path.join(self.root_dir, "models")
+        out = []
+        for name in sorted(os.listdir(base)) if os.path.isdir(base) else []:
+            vs = self.versions(name)
+            if vs:
+                with open(os.path.join(base, name, vs[-1], "manifest.json")) as f:
+                    m = json.load(f)
+                out.append([name, m.get("short_description", ""), m.get("author", ""), "v%s" % vs[-1]])
+        return out
+
+    def details(self, name):
+        vs = self.versions(name)
+        if not vs:
+            raise KeyError(name)
+        with open(os.path.join(self.model_dir(name), vs[-1], "manifest.json")) as f:
+            m = json.load(f)
+        return {"name": name, "description": m.get("long_description", ""), "versions": ["v" + v for v in vs],
+                "manifest": m}
+
+    def register(self, email):
+        with self.lock:
+            token = str(uuid.uuid4())
+            self.tokens[token] = {"email": email, "time": time.time()}
+            with open(self.tokens_file, "w") as f:
+                json.dump(self.tokens, f)
+        return token
+
+    def upload(self, token, blob):
+        if token not in self.tokens:
+            raise PermissionError("unknown token")
+        tmp = os.path.join(self.root_dir, "incoming-%s" % uuid.uuid4().hex)
+        try:
+            manifest = validate_manifest(unpack(blob, tmp))
+            with self.lock:
+                vs = self.versions(manifest["name"])
+                version = str(int(vs[-1]) + 1 if vs else 1)
+                dest = os.path.join(self.model_dir(manifest["name"]), version)
+                os.makedirs(os.path.dirname(dest), exist_ok=True)
+                shutil.move(tmp, dest)
+                with open(os.path.join(dest, "package.tar.gz"), "wb") as f:
+                    f.write(blob)
+                with open(os.path.join(dest, "owner"), "w") as f:
+                    f.write(self.tokens[token]["email"])
+            return {"name": manifest["name"], "version": "v" + version}
+        finally:
+            shutil.rmtree(tmp, ignore_errors=True)
+
+    def fetch(self, name, version=None):
+        vs = self.versions(name)
+        if not vs:
+            raise KeyError(name)
+        v = (version or vs[-1]).lstrip("v")
+        with open(os.path.join(self.model_dir(name), v, "package.tar.gz"), "rb") as f:
+            return f.read()
+
+    def delete(self, token, name):
+        d = self.model_dir(name)
+        vs = self.versions(name)
+        if not vs:
+            raise KeyError(name)
+        with open(os.path.join(d, vs[-1], "owner")) as f:
+            owner = f.read()
+        if self.tokens.get(token, {}).get("email") != owner:
+            raise PermissionError("only the uploader may delete a model")
+        shutil.rmtree(d)
+
+    # -- http -----------------------------------------------------------------------------------------------------
+    def start(self):
+        srv = self
+
+        class Handler(BaseHTTPRequestHandler):
+            def log_message(self, fmt, *args):
+                srv.debug(fmt, *args)
+
+            def _send(self, code, body, ctype="application/json"):
+                if not isinstance(body, bytes):
+                    body = json.dumps(body).encode()
+                self.send_response(code)
+                self.send_header("Content-Type", ctype)
+                self.send_header("Content-Length", str(len(body)))
+                self.end_headers()
+                self.wfile.write(body)
+
+            def _guard(self, fn):
+                try:
+                    return fn()
+                except KeyError as e:
+                    self._send(404, {"error": "not found: %s" % e})
+                except PermissionError as e:
+                    self._send(403, {"error": str(e)})
+                except Exception as e:  # noqa: BLE001
+                    self._send(400, {"error": str(e)})
+
+            def do_GET(self):
+                url = urlparse(self.path)
+                q = {k: v[0] for k, v in parse_qs(url.query).items()}
+                if url.path.endswith("/service"):
+                    kind = q.get("query")
+                    if kind == "list":
+                        return self._guard(lambda: self._send(200, srv.list()))
+                    if kind == "details":
+                        return self._guard(lambda: self._send(200, srv.details(q.get("name"))))
+                    if kind == "register":
+                        return self._guard(lambda: self._send(200, {"token": srv.register(q.get("email", "?"))}))
+                    if kind == "delete":
+                        return self._guard(lambda: (srv.delete(q.get("token"), q.get("name")),
+                                                    self._send(200, {"ok": True})))
+                    return self._send(400, {"error": "unknown query"})
+                if url.path.endswith("/fetch"):
+                    return self._guard(lambda: self._send(200, srv.fetch(q.get("name"), q.get("version")),
+                                                          "application/x-gzip"))
+                self._send(404, {"error": "not found"})
+
+            def do_POST(self):
+                url = urlparse(self.path)
+                q = {k: v[0] for k, v in parse_qs(url.query).items()}
+                if url.path.endswith("/upload"):
+                    blob = self.rfile.read(int(self.headers.get("Content-Length", 0)))
+                    return self._guard(lambda: self._send(200, srv.upload(q.get("token"), blob)))
+                self._send(404, {"error": "not found"})
+
+        self.httpd = ThreadingHTTPServer((self.host, self.port), Handler)
+        self.port = self.httpd.server_address[1]
+        threading.Thread(target=self.httpd.serve_forever, name="forge-server", daemon=True).start()
+        return self
+
+    @property
+    def url(self):
+        return "http://%s:%d/forge" % (self.host, self.port)
+
+    def stop(self):
+        if self.httpd is not None:
+            self.httpd.shutdown()
+            self.httpd.server_close()

@@ -61,7 +61,8 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
     def __init__(self, interactive=False, **kwargs):
         super(Launcher, self).__init__()
         parser = Launcher.init_parser(parser=argparse.ArgumentParser(add_help=False))
-        self.args, _ = parser.parse_known_args(self.argv if hasattr(self, "argv") else sys.argv[1:])
+        # interactive (in-process / notebook / test) launchers take their options from kwargs only
+        self.args, _ = parser.parse_known_args(kwargs.get("argv", [] if interactive else sys.argv[1:]))
         for k, v in kwargs.items():
             if hasattr(self.args, k):
                 setattr(self.args, k, v)

@@ -345,6 +345,9 @@ class StandardWorkflow(StandardWorkflowBase):
                 gd.link_attrs(fwd, attr)
             gd.link_attrs(self.loader, ("batch_size", "minibatch_size"))
             gd.gate_skip = self.decision.gd_skip
+            if prev_gd is None and not self.is_slave:
+                # once training is complete the backward chain must not start (EndPoint is stopping the units)
+                gd.gate_block = self.decision.complete
             prev_gd = gd
         if self.fuse_derivatives:
             self._plan_derivative_fusion()
