@@ -1,0 +1,185 @@
+"""Extra Znicz layers: cutter, channel split/merge, deconv (gradient check + conv adjointness), depooling,
+zero_filter, resizable / rprop all2all, Kohonen, RBM, LR policies, mcdnnic topology parsing."""
+import numpy as np
+import pytest
+
+from veles_b200.backends import NumpyDevice
+from veles_b200.dummy import DummyWorkflow
+from veles_b200.memory import Array
+from veles_b200.znicz.standard_workflow import LayerRegistry, parse_mcdnnic_topology
+
+
+def _fwd(tpe, x, **kw):
+    wf = DummyWorkflow()
+    u = LayerRegistry.forwards()[tpe](wf, **kw)
+    u.input = Array(np.asarray(x, dtype=np.float32))
+    return wf, u
+
+
+def _gd(wf, tpe, fwd, eo, **kw):
+    g = LayerRegistry.gds()[tpe](wf, forward=fwd, apply_gradient=False, **kw)
+    g.input, g.output = fwd.input, fwd.output
+    if getattr(fwd, "HAS_WEIGHTS", False):
+        g.weights, g.bias = fwd.weights, fwd.bias
+    g.err_output = Array(np.asarray(eo, dtype=np.float32))
+    assert not g.initialize(device=NumpyDevice())
+    g.run()
+    return g
+
+
+def test_cutter_and_backward():
+    x = np.arange(2 * 6 * 7 * 3).reshape(2, 6, 7, 3)
+    wf, f = _fwd("cutter", x, padding=(1, 2, 3, 1))
+    assert not f.initialize(device=NumpyDevice())
+    f.run()
+    assert f.output.shape == (2, 3, 3, 3) and np.array_equal(f.output.mem, x[:, 2:5, 1:4, :])
+    g = _gd(wf, "cutter", f, np.ones(f.output.shape))
+    assert g.err_input.mem.sum() == f.output.size and g.err_input.mem[:, 0].sum() == 0
+
+
+def test_channel_splitter_merger_roundtrip():
+    x = np.random.rand(2, 4, 5, 3)
+    wf, s = _fwd("channel_splitter", x)
+    s.initialize(device=NumpyDevice())
+    s.run()
+    assert s.output.shape == (2, 3, 4, 5)
+    m = LayerRegistry.forwards()["channel_merger"](wf)
+    m.input = s.output
+    m.initialize(device=NumpyDevice())
+    m.run()
+    assert np.allclose(m.output.mem, x)
+    g = _gd(wf, "channel_splitter", s, np.random.rand(2, 3, 4, 5))
+    assert g.err_input.shape == (2, 4, 5, 3)
+
+
+def test_deconv_is_adjoint_of_conv_and_gradients_check():
+    rng = np.random.RandomState(0)
+    x = rng.rand(2, 9, 8, 3).astype(np.float32)
+    wf, conv = _fwd("conv", x, n_kernels=4, kx=3, ky=3, padding=(1, 1, 1, 1), sliding=(2, 2), include_bias=False)
+    conv.initialize(device=NumpyDevice())
+    conv.run()
+    y = rng.rand(*conv.output.shape).astype(np.float32)
+    dec = LayerRegistry.forwards()["deconv"](wf, n_kernels=4, kx=3, ky=3, padding=(1, 1, 1, 1), sliding=(2, 2),
+                                             output_shape_source=conv.input)
+    dec.input = Array(y)
+    dec.weights = conv.weights                      # tied weights
+    assert not dec.initialize(device=NumpyDevice())
+    dec.run()
+    # <conv(x), y> == <x, deconv(y)>
+    assert abs((conv.output.mem * y).sum() - (x * dec.output.mem).sum()) < 1e-2
+    R = rng.rand(*dec.output.shape).astype(np.float32)
+    g = _gd(wf, "deconv", dec, R)
+
+    def loss():
+        dec.run()
+        return float((dec.output.mem.astype(np.float64) * R).sum())
+    for arr, ana in ((dec.input.mem, g.err_input.mem), (dec.weights.mem, g.gradient_weights.mem)):
+        flat = arr.reshape(-1)
+        for i in rng.choice(flat.size, 6, replace=False):
+            saved = flat[i]
+            flat[i] = saved + 1e-2
+            up = loss()
+            flat[i] = saved - 1e-2
+            dn = loss()
+            flat[i] = saved
+            assert abs((up - dn) / 2e-2 - ana.reshape(-1)[i]) < 2e-2 * max(1.0, abs(ana.reshape(-1)[i]))
+
+
+def test_depooling_inverts_max_pooling_positions():
+    x = np.random.permutation(2 * 6 * 6 * 2).reshape(2, 6, 6, 2).astype(np.float32)
+    wf, pool = _fwd("max_pooling", x, kx=2, ky=2, sliding=(2, 2))
+    pool.initialize(device=NumpyDevice())
+    pool.run()
+    dep = LayerRegistry.forwards()["depooling"](wf)
+    dep.input = pool.output
+    dep.output_offset = pool.input_offset
+    dep.output_shape_source = pool.input
+    assert not dep.initialize(device=NumpyDevice())
+    dep.run()
+    nz = dep.output.mem != 0
+    assert nz.sum() == pool.output.size and np.array_equal(dep.output.mem[nz], x[nz])
+    g = _gd(wf, "depooling", dep, x)
+    assert np.array_equal(g.err_input.mem, pool.output.mem)
+
+
+def test_zero_filter_keeps_block_diagonal_weights():
+    wf, fc = _fwd("all2all", np.random.rand(3, 8), output_sample_shape=4)
+    fc.initialize(device=NumpyDevice())
+    z = LayerRegistry.forwards()["zero_filter"](wf, grouping=2, target=fc)
+    z.input = fc.output
+    assert not z.initialize(device=NumpyDevice())
+    z.run()
+    w = fc.weights.mem
+    assert (w[:2, 4:] == 0).all() and (w[2:, :4] == 0).all() and (w[:2, :4] != 0).any()
+
+
+def test_resizable_all2all_keeps_old_neurons():
+    wf, fc = _fwd("all2all_resizable", np.random.rand(3, 5), output_sample_shape=4)
+    fc.initialize(device=NumpyDevice())
+    old = fc.weights.mem.copy()
+    assert fc.resize(6) and not fc.resize(6)
+    fc.initialize(device=NumpyDevice())
+    fc.run()
+    assert fc.output.shape == (3, 6) and np.array_equal(fc.weights.mem[:4], old)
+
+
+def test_rprop_reduces_loss():
+    rng = np.random.RandomState(1)
+    x = rng.rand(20, 6).astype(np.float32)
+    target = x.dot(rng.rand(6, 3)).astype(np.float32)
+    wf, fc = _fwd("rprop_all2all", x, output_sample_shape=3)
+    fc.initialize(device=NumpyDevice())
+    g = LayerRegistry.gds()["rprop_all2all"](wf, forward=fc, need_err_input=False)
+    g.input, g.output, g.weights, g.bias = fc.input, fc.output, fc.weights, fc.bias
+    g.err_output = Array(np.zeros((20, 3), dtype=np.float32))
+    g.initialize(device=NumpyDevice())
+    losses = []
+    for _ in range(60):
+        fc.run()
+        err = fc.output.mem - target
+        losses.append(float((err ** 2).mean()))
+        g.err_output.mem[...] = err / 20
+        g.run()
+    assert losses[-1] < 0.05 * losses[0]
+
+
+def test_kohonen_and_rbm_learn():
+    from veles_b200.znicz.kohonen import KohonenTrainer, KohonenForward
+    from veles_b200.znicz.rbm import RBM
+    rng = np.random.RandomState(2)
+    centers = rng.rand(4, 5) * 4
+    x = (centers[rng.randint(0, 4, 200)] + 0.05 * rng.randn(200, 5)).astype(np.float32)
+    wf = DummyWorkflow()
+    tr = KohonenTrainer(wf, shape=(3, 3))
+    tr.input = Array(x)
+    tr.initialize(device=NumpyDevice())
+    for _ in range(80):
+        tr.run()
+    fw = KohonenForward(wf)
+    fw.input, fw.weights = tr.input, tr.weights
+    fw.initialize(device=NumpyDevice())
+    fw.run()
+    w = tr.weights.mem[fw.output.mem]
+    assert np.sqrt(((x - w) ** 2).sum(1)).mean() < 0.6
+    rbm = RBM(wf, n_hidden=16, learning_rate=0.2)
+    rbm.input = Array((rng.rand(100, 12) < 0.5).astype(np.float32) * np.array([1] * 6 + [0] * 6, dtype=np.float32))
+    rbm.initialize(device=NumpyDevice())
+    errs = []
+    for _ in range(150):
+        rbm.run()
+        errs.append(rbm.reconstruction_error)
+    assert errs[-1] < errs[0] * 0.7
+
+
+def test_lr_policies_and_mcdnnic():
+    from veles_b200.znicz.lr_adjust import ExpPolicy, StepExpPolicy, InvAdjustPolicy, ArbitraryStepPolicy, FixedAdjustPolicy
+    assert FixedAdjustPolicy(0.1)(50) == 0.1
+    assert abs(ExpPolicy(0.1, gamma=0.5)(2) - 0.025) < 1e-12
+    assert abs(StepExpPolicy(0.1, gamma=0.1, step=10)(25) - 0.001) < 1e-12
+    assert abs(InvAdjustPolicy(0.1, gamma=1.0, pow_ratio=1.0)(9) - 0.01) < 1e-12
+    p = ArbitraryStepPolicy(lrs_with_lengths=[(0.1, 3), (0.01, 2)])
+    assert [p(i) for i in range(7)] == [0.1, 0.1, 0.1, 0.01, 0.01, 0.01, 0.01]
+    layers = parse_mcdnnic_topology("12x256x256-32C4-MP2-64C4-MP3-32N-4N")
+    assert [l["type"] for l in layers] == ["conv_tanh", "max_pooling", "conv_tanh", "max_pooling", "all2all_tanh", "softmax"]
+    assert layers[0]["->"]["n_kernels"] == 32 and layers[3]["->"]["sliding"] == (3, 3)
+    assert layers[-1]["->"]["output_sample_shape"] == 4
