@@ -1,0 +1,101 @@
+"""Native (C++) inference runtime: CPU checks of loader/planner/optimizer through the test binary, and a GPU run of
+exported packages compared with the Python forward pass (reference: libVeles/tests/*.cc with mnist.zip/.tar.gz)."""
+import ctypes
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _build():
+    sys.path.insert(0, os.path.join(ROOT, "native"))
+    import importlib
+    build = importlib.import_module("build")
+    return build.build()
+
+
+def _trained(model, device, **kw):
+    from veles_b200 import prng
+    from veles_b200.config import root
+    from veles_b200.models import build_workflow
+    root.common.disable.snapshotting = True
+    prng.get().seed(9)
+    wf = build_workflow(model, max_epochs=1, **kw)
+    wf.initialize(device=device)
+    wf.run()
+    return wf
+
+
+def test_native_cpu_checks_and_package_loading(tmp_path):
+    from veles_b200.backends import NumpyDevice
+    lib, test_bin = _build()
+    wf = _trained("mnist_mlp", NumpyDevice(), minibatch_size=50, n_train=200, n_valid=50)
+    z, t = str(tmp_path / "mnist.zip"), str(tmp_path / "mnist.tar.gz")
+    wf.package_export(z, "zip")
+    wf.package_export(t, "tgz", precision=16)
+    r = subprocess.run([test_bin, z, t], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=120)
+    out = r.stdout.decode()
+    assert r.returncode == 0 and "0 failed" in out, out
+    assert "All2All" not in out or "2 units" in out
+    wf.launcher.stop()
+
+
+def _native(lib_path):
+    L = ctypes.CDLL(lib_path)
+    L.veles_native_load.restype = ctypes.c_void_p
+    L.veles_native_last_error.restype = ctypes.c_char_p
+    L.veles_native_output_size.restype = ctypes.c_longlong
+    L.veles_native_unit_name.restype = ctypes.c_char_p
+    for fn in (L.veles_native_initialize, L.veles_native_run, L.veles_native_output_size, L.veles_native_free,
+               L.veles_native_unit_count, L.veles_native_unit_name, L.veles_native_uses_graph, L.veles_native_plan):
+        fn.argtypes = None
+    return L
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("model,kw,shape", [
+    ("mnist_mlp", dict(minibatch_size=50, n_train=200, n_valid=50), (784,)),
+    ("cifar_convnet", dict(minibatch_size=32, n_train=64, n_valid=32, layers_kwargs={"caffe_init": False}), (32, 32, 3)),
+])
+def test_native_runtime_matches_python_forward(tmp_path, model, kw, shape):
+    from veles_b200.backends import B200Device
+    lib, _ = _build()
+    wf = _trained(model, B200Device(), **kw)
+    pkg = str(tmp_path / (model + ".zip"))
+    wf.package_export(pkg)
+    # reference: the framework's own forward pass on one minibatch
+    wf.loader.run()
+    for f in wf.forwards:
+        f.forward_mode = True
+        f.run()
+    if hasattr(wf.forwards[-1], "defer_softmax") and wf.forwards[-1].defer_softmax:
+        wf.forwards[-1].defer_softmax = False
+        wf.forwards[-1].run()
+    wf.loader.minibatch_data.map_read()
+    wf.forwards[-1].output.map_read()
+    x = np.ascontiguousarray(wf.loader.minibatch_data.mem.astype(np.float32))
+    ref = wf.forwards[-1].output.mem.reshape(x.shape[0], -1).astype(np.float32)
+    L = _native(lib)
+    h = ctypes.c_void_p(L.veles_native_load(pkg.encode()))
+    assert h.value, L.veles_native_last_error()
+    dims = (ctypes.c_longlong * len(shape))(*shape)
+    arena, naive = ctypes.c_longlong(), ctypes.c_longlong()
+    assert L.veles_native_plan(h, x.shape[0], dims, len(shape), ctypes.byref(arena), ctypes.byref(naive)) == 0
+    assert 0 < arena.value <= naive.value
+    assert L.veles_native_initialize(h, x.shape[0], dims, len(shape), 0, 1) == 0, L.veles_native_last_error()
+    n_out = L.veles_native_output_size(h)
+    assert n_out == ref.shape[1]
+    out = np.zeros((x.shape[0], n_out), dtype=np.float32)
+    for _ in range(3):   # the third run replays the captured CUDA graph
+        rc = L.veles_native_run(h, x.ctypes.data_as(ctypes.c_void_p), out.ctypes.data_as(ctypes.c_void_p), x.shape[0])
+        assert rc == 0, L.veles_native_last_error()
+    assert L.veles_native_uses_graph(h) == 1
+    assert np.abs(out.sum(axis=1) - 1.0).max() < 2e-2
+    assert np.abs(out - ref).max() < 3e-2, np.abs(out - ref).max()
+    assert (out.argmax(1) == ref.argmax(1)).mean() > 0.95
+    L.veles_native_free(h)
+    wf.launcher.stop()

@@ -47,6 +47,7 @@ def activation_backward_numpy(code, x, y, factor=1.0):
 class ActivationForward(ForwardBase):
     hide_from_registry = True
     CODE = 0
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0023"
 
     def __init__(self, workflow, **kwargs):
         super(ActivationForward, self).__init__(workflow, **kwargs)
@@ -66,6 +67,9 @@ class ActivationForward(ForwardBase):
             self.output.initialize(self.device_)
         self._backend_init_()
         return None
+
+    def package_export(self):
+        return {"activation": self.CODE, "factor": self.factor}
 
     def numpy_run(self):
         self.input.map_read()
@@ -145,6 +149,7 @@ class ActivationBackward(GDBase):
 
 def _make(name, code):
     fwd = type("Forward" + name, (ActivationForward,), {"MAPPING": {"activation_" + name.lower()}, "CODE": code,
+                                                        "__id__": ActivationForward.__id__,
                                                         "hide_from_registry": False, "__module__": __name__})
     bwd = type("Backward" + name, (ActivationBackward,), {"MAPPING": {"activation_" + name.lower()}, "CODE": code,
                                                           "hide_from_registry": False, "__module__": __name__})

@@ -56,6 +56,7 @@ class Conv(Forward):
     hide_from_registry = False
     MAPPING = {"conv"}
     ACTIVATION = 0
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0001"
 
     def __init__(self, workflow, **kwargs):
         super(Conv, self).__init__(workflow, **kwargs)
@@ -182,18 +183,22 @@ class Conv(Forward):
 class ConvTanh(Conv):
     MAPPING = {"conv_tanh"}
     ACTIVATION = 1
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0002"
 
 
 class ConvRELU(Conv):
     MAPPING = {"conv_relu"}
     ACTIVATION = 3
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0004"
 
 
 class ConvStrictRELU(Conv):
     MAPPING = {"conv_str"}
     ACTIVATION = 4
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0005"
 
 
 class ConvSigmoid(Conv):
     MAPPING = {"conv_sigmoid"}
     ACTIVATION = 2
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0003"

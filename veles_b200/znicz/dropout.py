@@ -19,6 +19,7 @@ class DropoutForward(ForwardBase):
     hide_from_registry = False
     MAPPING = {"dropout"}
     LOADER_ATTRS = ("minibatch_class",)
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0022"
     N_STATES = 16384
 
     def __init__(self, workflow, **kwargs):
@@ -36,6 +37,9 @@ class DropoutForward(ForwardBase):
         self.states_prev_ = None
         self.states_next_ = None
         self.active_ = True
+
+    def package_export(self):
+        return {"dropout_ratio": self.dropout_ratio}   # identity at inference time
 
     @property
     def training(self):

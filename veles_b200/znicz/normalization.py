@@ -21,6 +21,7 @@ def _window_sums(sq, n):
 class LRNormalizerForward(ForwardBase):
     hide_from_registry = False
     MAPPING = {"norm"}
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0021"
 
     def __init__(self, workflow, **kwargs):
         super(LRNormalizerForward, self).__init__(workflow, **kwargs)

@@ -132,18 +132,21 @@ class MaxPooling(Pooling):
     hide_from_registry = False
     MAPPING = {"max_pooling"}
     KIND = "max"
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0011"
 
 
 class MaxAbsPooling(Pooling):
     hide_from_registry = False
     MAPPING = {"maxabs_pooling"}
     KIND = "maxabs"
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0012"
 
 
 class AvgPooling(Pooling):
     hide_from_registry = False
     MAPPING = {"avg_pooling"}
     KIND = "avg"
+    __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0013"
 
 
 class StochasticPoolingBase(Pooling):
