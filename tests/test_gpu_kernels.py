@@ -127,6 +127,45 @@ def test_gemm_column_slice_output_grouped_conv_style():
     assert rel_err(y, ref) < 1e-2
 
 
+@pytest.mark.parametrize("direct", [False, True])
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_gemm_epilogue_paths_respect_tile_tails(direct, out_dtype):
+    """TMA store / reduce-add epilogue vs the per-thread fallback: same numbers, nothing written outside D."""
+    k = K()
+    torch.manual_seed(21)
+    M, N, K_ = 333, 200, 264
+    a = (torch.randn(M, K_, device=dev()) * 0.2).bfloat16()
+    b = (torch.randn(N, K_, device=dev()) * 0.2).bfloat16()
+    bias = torch.randn(N, device=dev())
+    big = torch.full((M + 64, N + 56), float("nan"), device=dev(), dtype=out_dtype)
+    out = big[:M, :N]
+    k.set_direct_epilogue(direct)
+    try:
+        k.gemm(a, b, out, bias=bias, act=1)
+        ref = 1.7159 * torch.tanh(0.6666 * (a.float() @ b.float().t() + bias))
+        assert rel_err(out, ref) < (2e-3 if out_dtype == torch.float32 else 1e-2)
+        assert torch.isnan(big[M:].float()).all() and torch.isnan(big[:, N:].float()).all()
+        if out_dtype == torch.float32:
+            out.zero_()
+            k.gemm(a, b, out, accumulate=True)
+            k.gemm(a, b, out, accumulate=True, split_k=3)
+            assert rel_err(out, 2 * (a.float() @ b.float().t())) < 2e-3
+            assert torch.isnan(big[M:]).all() and torch.isnan(big[:, N:]).all()
+    finally:
+        k.set_direct_epilogue(False)
+
+
+def test_gemm_unaligned_output_uses_fallback():
+    k = K()
+    torch.manual_seed(22)
+    M, N, K_ = 100, 30, 64
+    a = torch.randn(M, K_, device=dev()).bfloat16()
+    b = torch.randn(N, K_, device=dev()).bfloat16()
+    out = torch.empty(M, N + 1, device=dev(), dtype=torch.bfloat16)[:, 1:]   # 2-byte aligned base, odd pitch
+    k.gemm(a, b, out)
+    assert rel_err(out, a.float() @ b.float().t()) < 1e-2
+
+
 @pytest.mark.parametrize("src_dtype", [torch.uint8, torch.float32])
 @pytest.mark.parametrize("dst_dtype", [torch.float32, torch.bfloat16])
 def test_gather_minibatch(src_dtype, dst_dtype):

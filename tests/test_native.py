@@ -68,6 +68,8 @@ def test_native_runtime_matches_python_forward(tmp_path, model, kw, shape):
     pkg = str(tmp_path / (model + ".zip"))
     wf.package_export(pkg)
     # reference: the framework's own forward pass on one minibatch
+    for u in [wf.loader] + list(wf.forwards):
+        u.stopped = False
     wf.loader.run()
     for f in wf.forwards:
         f.forward_mode = True

@@ -21,6 +21,7 @@
 // epilogue of tile i overlaps the mainloop of tile i+1.
 #include "common.cuh"
 
+#include <cstring>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -45,6 +46,7 @@ struct GemmParams {
   int deriv;          // vb::Act code of the derivative taken through Z
   float alpha;
   int split_k;
+  int tma_store;      // 1: epilogue goes through smem + TMA store / reduce-add (tma_d valid)
   int m_blocks, n_blocks, k_blocks;
 };
 
@@ -55,8 +57,10 @@ struct SmemLayout {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int BAR_BYTES = 1024;
-  static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024 /*align slack*/;
+  static constexpr int EPI_BYTES = 4 /*warps*/ * 2 /*buffers*/ * 4096;  // 32 rows x 128 B slabs
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*align slack*/;
 };
+constexpr int EPI_BUF_BYTES = 4096;
 
 __device__ __forceinline__ float4 ld_z8(const __nv_bfloat16* p) {
   return *reinterpret_cast<const float4*>(p);
@@ -65,14 +69,16 @@ __device__ __forceinline__ float4 ld_z8(const __nv_bfloat16* p) {
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
-                         const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+                         const __grid_constant__ CUtensorMap tma_b,
+                         const __grid_constant__ CUtensorMap tma_d, const GemmParams p) {
   using L = SmemLayout<BN>;
   constexpr int STAGES = L::STAGES;
   constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* bar_base = smem + STAGES * L::STAGE_BYTES;
+  uint8_t* epi_smem = smem + STAGES * L::STAGE_BYTES;  // 1024-aligned: swizzle atoms line up
+  uint8_t* bar_base = epi_smem + L::EPI_BYTES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bar_base);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
@@ -85,6 +91,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
+    if (p.tma_store) tma_prefetch_desc(&tma_d);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -199,6 +206,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
     int acc = 0;
     uint32_t acc_phase = 0;
+    int ebuf = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int ks = tile / tiles_mn;
       const int mn = tile - ks * tiles_mn;
@@ -211,7 +219,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
       }
-      const int row = mb * BLOCK_M + quarter * 32 + lane;
+      const int row0 = mb * BLOCK_M + quarter * 32;
+      const int row = row0 + lane;
       const bool row_ok = row < p.M;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
@@ -227,38 +236,84 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = 0u;
         }
-        if (row_ok) {
-          float f[32];
+        float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
-          const bool full = (col0 + 32 <= p.N);
-          if (add_bias) {
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+        const bool full = (col0 + 32 <= p.N);
+        if (add_bias) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (full || col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
-          }
-          if (p.act != ACT_LINEAR) {
+          for (int j = 0; j < 32; ++j)
+            if (full || col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
+        }
+        if (p.act != ACT_LINEAR) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = act_forward(p.act, f[j]);
-          }
-          if (p.Z != nullptr) {
-            const __nv_bfloat16* zrow = p.Z + static_cast<long long>(row) * p.ldz + col0;
-            if (full) {
+          for (int j = 0; j < 32; ++j) f[j] = act_forward(p.act, f[j]);
+        }
+        if (p.Z != nullptr && row_ok) {
+          const __nv_bfloat16* zrow = p.Z + static_cast<long long>(row) * p.ldz + col0;
+          if (full && ((p.ldz & 7) == 0)) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                float4 z = ld_z8(zrow + j);
-                const uint32_t* zu = reinterpret_cast<const uint32_t*>(&z);
+            for (int j = 0; j < 32; j += 8) {
+              float4 z = ld_z8(zrow + j);
+              const uint32_t* zu = reinterpret_cast<const uint32_t*>(&z);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  f[j + 2 * q] *= act_deriv_from_output(p.deriv, bf16_lo(zu[q]));
-                  f[j + 2 * q + 1] *= act_deriv_from_output(p.deriv, bf16_hi(zu[q]));
-                }
+              for (int q = 0; q < 4; ++q) {
+                f[j + 2 * q] *= act_deriv_from_output(p.deriv, bf16_lo(zu[q]));
+                f[j + 2 * q + 1] *= act_deriv_from_output(p.deriv, bf16_hi(zu[q]));
               }
-            } else {
-              for (int j = 0; j < 32 && col0 + j < p.N; ++j)
-                f[j] *= act_deriv_from_output(p.deriv, __bfloat162float(zrow[j]));
+            }
+          } else {
+            for (int j = 0; j < 32 && col0 + j < p.N; ++j)
+              f[j] *= act_deriv_from_output(p.deriv, __bfloat162float(zrow[j]));
+          }
+        }
+        if (p.tma_store) {
+          // Stage the 32-row slab in 128B-swizzled smem (conflict-free 16-byte writes: the eight
+          // lanes of a quarter-warp phase hit eight different chunks), then one TMA store /
+          // L2 reduce-add per slab: full-line writes, M/N tails clipped by the tensor map.
+          uint8_t* buf = epi_smem + (quarter * 2 + ebuf) * EPI_BUF_BYTES;
+          uint8_t* srow = buf + lane * 128;
+          if (p.out_fp32) {
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              *reinterpret_cast<float4*>(srow + ((q ^ (lane & 7)) << 4)) =
+                  make_float4(f[4 * q], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (p.accumulate) tma_reduce_add_2d(&tma_d, buf, col0, row0);
+              else tma_store_2d(&tma_d, buf, col0, row0);
+              tma_store_commit();
+            }
+            ebuf ^= 1;
+          } else {
+            const int half = (c0 >> 5) & 1;
+            if (half == 0) {
+              if (lane == 0) tma_store_wait_read<1>();
+              __syncwarp();
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint4 o;
+              o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
+              o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+              o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+              o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+              *reinterpret_cast<uint4*>(srow + (((half * 4 + q) ^ (lane & 7)) << 4)) = o;
+            }
+            if (half == 1 || col0 + 32 >= p.N || c0 + 32 >= BN) {
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_2d(&tma_d, buf, col0 - half * 32, row0);
+                tma_store_commit();
+              }
+              ebuf ^= 1;
             }
           }
+        } else if (row_ok) {
           if (p.out_fp32) {
             float* drow = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + col0;
             if (p.accumulate) {
@@ -300,6 +355,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         }
       }
     }
+    if (p.tma_store && lane == 0) tma_store_wait_all<0>();  // smem must outlive the bulk reads
   }
 
   tc_fence_before();
@@ -333,17 +389,26 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2-D bf16 tensor map with 128B swizzle: dims {inner, outer}, row pitch in elements.
+static int make_tmap_2d(CUtensorMap* out, const void* base, long long inner, long long outer,
+                        long long pitch_elems, int box_inner, int box_outer, bool fp32);
+
 int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long long outer,
                       long long pitch_elems, int box_inner, int box_outer) {
+  return make_tmap_2d(out, base, inner, outer, pitch_elems, box_inner, box_outer, false);
+}
+
+static int make_tmap_2d(CUtensorMap* out, const void* base, long long inner, long long outer,
+                        long long pitch_elems, int box_inner, int box_outer, bool fp32) {
+  const int es = fp32 ? 4 : 2;
   EncodeTiledFn fn = get_encode_fn();
   VB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   VB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base pointer must be 16-byte aligned");
-  VB_REQUIRE((pitch_elems * 2) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes (ld %% 8 == 0), got %lld", pitch_elems);
+  VB_REQUIRE((pitch_elems * es) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes, got %lld elements of %d bytes", pitch_elems, es);
   cuuint64_t gdim[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(outer)};
-  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(pitch_elems) * 2};
+  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(pitch_elems) * es};
   cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box,
+  CUresult r = fn(out, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box,
                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   VB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%lld outer=%lld pitch=%lld box=%dx%d)",
@@ -352,8 +417,8 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long 
 }
 
 template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
-                       cudaStream_t stream) {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
+                       const GemmParams& p, int grid, cudaStream_t stream) {
   using L = SmemLayout<BN>;
   auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN>;
   static bool attr_set = false;
@@ -361,23 +426,30 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     VB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set = true;
   }
-  kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, p);
+  kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, td, p);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 template <int BN>
 static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
-                          const GemmParams& p, int grid, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_gemm<BN, false, false>(ta, tb, p, grid, s);
-  if (!a_mn && b_mn) return launch_gemm<BN, false, true>(ta, tb, p, grid, s);
-  if (a_mn && !b_mn) return launch_gemm<BN, true, false>(ta, tb, p, grid, s);
-  return launch_gemm<BN, true, true>(ta, tb, p, grid, s);
+                          const CUtensorMap& td, const GemmParams& p, int grid, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_gemm<BN, false, false>(ta, tb, td, p, grid, s);
+  if (!a_mn && b_mn) return launch_gemm<BN, false, true>(ta, tb, td, p, grid, s);
+  if (a_mn && !b_mn) return launch_gemm<BN, true, false>(ta, tb, td, p, grid, s);
+  return launch_gemm<BN, true, true>(ta, tb, td, p, grid, s);
 }
 
 }  // namespace vb
 
 using namespace vb;
+
+static int g_disable_tma_store = 0;
+// Test hook: 1 forces the per-thread store epilogue so both paths stay covered.
+extern "C" int vb_gemm_set_direct_epilogue(int on) {
+  g_disable_tma_store = on ? 1 : 0;
+  return 0;
+}
 
 extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
                             int b_mn_major, void* D, long long ldd, int M, int N, int K,
@@ -434,11 +506,21 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
   if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BLOCK_K, BN);
   else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BLOCK_K);
   if (rc) return rc;
+  // Output through TMA whenever D satisfies the tensor-map alignment rules; otherwise the
+  // epilogue falls back to per-thread global stores / atomics.
+  CUtensorMap td;
+  memset(&td, 0, sizeof(td));
+  const int es = out_fp32 ? 4 : 2;
+  p.tma_store = ((reinterpret_cast<uintptr_t>(D) & 15) == 0 && (ldd * es) % 16 == 0 && !g_disable_tma_store) ? 1 : 0;
+  if (p.tma_store) {
+    rc = make_tmap_2d(&td, D, N, M, ldd, out_fp32 ? 32 : 64, 32, out_fp32 != 0);
+    if (rc) return rc;
+  }
   const long long tiles = static_cast<long long>(p.m_blocks) * p.n_blocks * p.split_k;
   const int grid = static_cast<int>(tiles < sms ? tiles : sms);
   switch (BN) {
-    case 64: return dispatch_major<64>(a_mn_major, b_mn_major, ta, tb, p, grid, stream);
-    case 128: return dispatch_major<128>(a_mn_major, b_mn_major, ta, tb, p, grid, stream);
-    default: return dispatch_major<256>(a_mn_major, b_mn_major, ta, tb, p, grid, stream);
+    case 64: return dispatch_major<64>(a_mn_major, b_mn_major, ta, tb, td, p, grid, stream);
+    case 128: return dispatch_major<128>(a_mn_major, b_mn_major, ta, tb, td, p, grid, stream);
+    default: return dispatch_major<256>(a_mn_major, b_mn_major, ta, tb, td, p, grid, stream);
   }
 }

@@ -60,6 +60,11 @@ def pitched_empty(rows, cols, dtype, device, align=8):
     return buf[:, :cols]
 
 
+def set_direct_epilogue(on):
+    """Test hook: force the GEMM's per-thread store epilogue instead of the smem-staged TMA store / reduce-add."""
+    _lib.check(_lib.lib().vb_gemm_set_direct_epilogue(c_int(int(bool(on)))), "vb_gemm_set_direct_epilogue")
+
+
 def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumulate=False, z=None, deriv=0,
          alpha=1.0, split_k=1, block_n=0):
     """out[M,N] = epilogue(sum_k A(m,k) B(n,k)); see csrc/gemm_tcgen05.cu.
