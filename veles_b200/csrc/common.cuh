@@ -289,6 +289,21 @@ __device__ __forceinline__ float act_forward(int act, float s) {
       return s;
   }
 }
+// Compile-time activation with hardware approximations (tanh.approx / ex2 / lg2): the GEMM
+// epilogue's results are rounded to bf16 or feed bf16 operands, so 2^-11 relative error is free.
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+template <int ACT>
+__device__ __forceinline__ float act_forward_fast(float s) {
+  if (ACT == ACT_TANH) return 1.7159f * tanh_approx(0.6666f * s);
+  if (ACT == ACT_SIGMOID) return __fdividef(1.0f, 1.0f + __expf(-s));
+  if (ACT == ACT_RELU) return s > 15.0f ? s : __logf(1.0f + __expf(s));
+  if (ACT == ACT_STRICT_RELU) return fmaxf(s, 0.0f);
+  return s;
+}
 // Derivative expressed through the layer OUTPUT y (what Znicz GD units keep).
 __device__ __forceinline__ float act_deriv_from_output(int act, float y) {
   switch (act) {

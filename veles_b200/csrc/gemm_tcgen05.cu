@@ -66,6 +66,18 @@ __device__ __forceinline__ float4 ld_z8(const __nv_bfloat16* p) {
   return *reinterpret_cast<const float4*>(p);
 }
 
+// Epilogue math on a 32-column register slab with the activation fixed at compile time.
+template <int ACT>
+__device__ __forceinline__ void apply_act(float (&f)[32]) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) f[j] = act_forward_fast<ACT>(f[j]);
+}
+template <int ACT>
+__device__ __forceinline__ void apply_deriv(float (&f)[32], const float (&y)[32]) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) f[j] *= act_deriv_from_output(ACT, y[j]);
+}
+
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
@@ -245,12 +257,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           for (int j = 0; j < 32; ++j)
             if (full || col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
         }
-        if (p.act != ACT_LINEAR) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = act_forward(p.act, f[j]);
+        // The activation code is warp-uniform: branch once, keep f[] in registers.
+        switch (p.act) {
+          case ACT_TANH: apply_act<ACT_TANH>(f); break;
+          case ACT_SIGMOID: apply_act<ACT_SIGMOID>(f); break;
+          case ACT_RELU: apply_act<ACT_RELU>(f); break;
+          case ACT_STRICT_RELU: apply_act<ACT_STRICT_RELU>(f); break;
+          default: break;
         }
         if (p.Z != nullptr && row_ok) {
           const __nv_bfloat16* zrow = p.Z + static_cast<long long>(row) * p.ldz + col0;
+          float d[32];
           if (full && ((p.ldz & 7) == 0)) {
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
@@ -258,13 +275,20 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               const uint32_t* zu = reinterpret_cast<const uint32_t*>(&z);
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
-                f[j + 2 * q] *= act_deriv_from_output(p.deriv, bf16_lo(zu[q]));
-                f[j + 2 * q + 1] *= act_deriv_from_output(p.deriv, bf16_hi(zu[q]));
+                d[j + 2 * q] = bf16_lo(zu[q]);
+                d[j + 2 * q + 1] = bf16_hi(zu[q]);
               }
             }
           } else {
-            for (int j = 0; j < 32 && col0 + j < p.N; ++j)
-              f[j] *= act_deriv_from_output(p.deriv, __bfloat162float(zrow[j]));
+#pragma unroll
+            for (int j = 0; j < 32; ++j) d[j] = (col0 + j < p.N) ? __bfloat162float(zrow[j]) : 0.0f;
+          }
+          switch (p.deriv) {
+            case ACT_TANH: apply_deriv<ACT_TANH>(f, d); break;
+            case ACT_SIGMOID: apply_deriv<ACT_SIGMOID>(f, d); break;
+            case ACT_RELU: apply_deriv<ACT_RELU>(f, d); break;
+            case ACT_STRICT_RELU: apply_deriv<ACT_STRICT_RELU>(f, d); break;
+            default: break;
           }
         }
         if (p.tma_store) {
@@ -317,6 +341,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           if (p.out_fp32) {
             float* drow = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + col0;
             if (p.accumulate) {
+#pragma unroll
               for (int j = 0; j < 32; ++j)
                 if (full || col0 + j < p.N) atomicAdd(drow + j, f[j]);
             } else if (full && ((p.ldd & 3) == 0)) {
@@ -324,7 +349,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               for (int j = 0; j < 32; j += 4)
                 *reinterpret_cast<float4*>(drow + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
             } else {
-              for (int j = 0; j < 32 && col0 + j < p.N; ++j) drow[j] = f[j];
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j < p.N) drow[j] = f[j];
             }
           } else {
             __nv_bfloat16* drow =
@@ -340,7 +367,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                 *reinterpret_cast<uint4*>(drow + j) = o;
               }
             } else {
-              for (int j = 0; j < 32 && col0 + j < p.N; ++j) drow[j] = __float2bfloat16(f[j]);
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j < p.N) drow[j] = __float2bfloat16(f[j]);
             }
           }
         }
