@@ -166,6 +166,76 @@ def test_gemm_unaligned_output_uses_fallback():
     assert rel_err(out, a.float() @ b.float().t()) < 1e-2
 
 
+CONV_CASES = [
+    # B, H, W, C, n, ky, kx, sy, sx, pt, pl, pb, pr, groups
+    (4, 13, 13, 256, 384, 3, 3, 1, 1, 1, 1, 1, 1, 1),     # AlexNet conv3
+    (3, 13, 13, 384, 256, 3, 3, 1, 1, 1, 1, 1, 1, 2),     # AlexNet conv5 (grouped, 192 channels per group)
+    (2, 27, 27, 96, 256, 5, 5, 1, 1, 2, 2, 2, 2, 2),      # AlexNet conv2 (48 channels per group: padded K blocks)
+    (5, 9, 11, 16, 40, 3, 2, 1, 1, 0, 1, 2, 0, 1),        # asymmetric padding, odd sizes, tiny channels
+    (3, 17, 15, 64, 72, 3, 3, 2, 2, 1, 1, 1, 1, 1),       # strided (forward / weights only)
+    (2, 23, 23, 8, 24, 5, 5, 3, 2, 0, 0, 0, 0, 1),        # mixed strides
+]
+
+
+def _conv_ref(x, w, n, ky, kx, sy, sx, pt, pl, pb, pr, G):
+    """x [B,H,W,C] fp32, w [n, ky*kx*Cg] with (tap row, tap col, channel) columns -> y [B,OH,OW,n]."""
+    B, H, W, C = x.shape
+    Cg = C // G
+    wt = w.view(n, ky, kx, Cg).permute(0, 3, 1, 2).contiguous()
+    xp = torch.nn.functional.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb))
+    return torch.nn.functional.conv2d(xp, wt, stride=(sy, sx), groups=G).permute(0, 2, 3, 1).contiguous()
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_implicit_gemm_conv_forward_backward(case):
+    """TMA-im2col implicit GEMM (forward, err_input, weight gradient) vs torch conv2d autograd in fp32."""
+    k = K()
+    B, H, W, C, n, ky, kx, sy, sx, pt, pl, pb, pr, G = case
+    torch.manual_seed(sum(case))
+    Cg, ng = C // G, n // G
+    OH = (H + pt + pb - ky) // sy + 1
+    OW = (W + pl + pr - kx) // sx + 1
+    g = dict(OH=OH, OW=OW, ky=ky, kx=kx, sy=sy, sx=sx, pt=pt, pl=pl, H=H, W=W)
+    x = (torch.randn(B, H, W, C, device=dev()) * 0.5).bfloat16()
+    w = (torch.randn(n, ky * kx * Cg, device=dev()) * 0.1).bfloat16()
+    bias = torch.randn(n, device=dev())
+    xr = x.float().requires_grad_(True)
+    wr = w.float().requires_grad_(True)
+    yr = torch.tanh(0.6666 * (_conv_ref(xr, wr, n, ky, kx, sy, sx, pt, pl, pb, pr, G) + bias)) * 1.7159
+    dy = (torch.randn_like(yr) * 0.3).bfloat16()
+    yr.backward(dy.float())
+    # forward
+    y = torch.full((B * OH * OW + 3, n), float("nan"), device=dev(), dtype=torch.bfloat16)
+    for gi in range(G):
+        k.conv_forward(x[..., gi * Cg:(gi + 1) * Cg], w[gi * ng:(gi + 1) * ng], y[:B * OH * OW, gi * ng:(gi + 1) * ng], g,
+                       bias=bias[gi * ng:(gi + 1) * ng], act=1)
+    assert rel_err(y[:B * OH * OW], yr.detach().reshape(-1, n)) < 1e-2
+    assert torch.isnan(y[B * OH * OW:].float()).all()
+    # weight gradient of the pre-activation error e = dy * f'(y)
+    e = (dy.float() * (0.6666 * (1.7159 - yr.detach() ** 2 / 1.7159))).bfloat16()
+    yr2 = _conv_ref(xr, wr, n, ky, kx, sy, sx, pt, pl, pb, pr, G)
+    xr.grad = None
+    wr.grad = None
+    yr2.backward(e.float())
+    e2 = e.reshape(-1, n)
+    gw = torch.zeros(n, ky * kx * Cg, device=dev())
+    for gi in range(G):
+        k.conv_weight_grad(x[..., gi * Cg:(gi + 1) * Cg], e2[:, gi * ng:(gi + 1) * ng], gw[gi * ng:(gi + 1) * ng], g)
+    assert rel_err(gw, wr.grad) < 5e-3
+    for gi in range(G):   # accumulate: a second pass with alpha=-1 cancels
+        k.conv_weight_grad(x[..., gi * Cg:(gi + 1) * Cg], e2[:, gi * ng:(gi + 1) * ng], gw[gi * ng:(gi + 1) * ng], g,
+                           alpha=-1.0, split_k=3)
+    assert gw.abs().max().item() < 2e-2 * wr.grad.abs().max().item()
+    # err_input (unit stride), fused with the previous layer's tanh derivative through z = x
+    if sx == 1 and sy == 1:
+        dx = torch.full((B * H * W, C), float("nan"), device=dev(), dtype=torch.bfloat16)
+        for gi in range(G):
+            k.conv_err_input(e[..., gi * ng:(gi + 1) * ng], w[gi * ng:(gi + 1) * ng], dx[:, gi * Cg:(gi + 1) * Cg], g,
+                             z=x.reshape(-1, C)[:, gi * Cg:(gi + 1) * Cg], deriv=1)
+        ref = xr.grad * (0.6666 * (1.7159 - x.float() ** 2 / 1.7159))
+        assert rel_err(dx, ref.reshape(-1, C)) < 1e-2
+
+
 @pytest.mark.parametrize("src_dtype", [torch.uint8, torch.float32])
 @pytest.mark.parametrize("dst_dtype", [torch.float32, torch.bfloat16])
 def test_gather_minibatch(src_dtype, dst_dtype):
@@ -418,6 +488,29 @@ def test_lrn_forward_backward(dtype):
     k.lrn_backward(x, dy, dx, n, alpha, beta, kk)
     (ref * dy.double()).sum().backward()
     assert rel_err(dx, xr.grad) < (1e-4 if dtype == torch.float32 else 2e-2)
+
+
+@pytest.mark.parametrize("C,n", [(96, 5), (256, 5), (8, 3), (40, 9), (24, 7), (20, 5), (64, 11)])
+def test_lrn_vector_paths(C, n):
+    """bf16 LRN: the 8-channel register kernels (n <= 9, C % 8 == 0) and the row fallback, large alpha so the
+    window term matters; fused previous-layer strict-ReLU derivative in the backward."""
+    k = K()
+    torch.manual_seed(C + n)
+    B, H, W = 3, 7, 5
+    alpha, beta, kk = 0.3, 0.75, 1.5
+    x = torch.randn(B, H, W, C, device=dev()).bfloat16()
+    y = torch.empty_like(x)
+    k.lrn_forward(x, y, n, alpha, beta, kk)
+    xr = x.double().requires_grad_(True)
+    sq = torch.nn.functional.pad(xr * xr, (n // 2, n // 2))
+    s = kk + alpha * sum(sq[..., i:i + C] for i in range(n))
+    ref = xr * s ** (-beta)
+    assert rel_err(y, ref.detach()) < 1e-2
+    dy = torch.randn_like(x)
+    dx = torch.empty_like(x)
+    k.lrn_backward(x, dy, dx, n, alpha, beta, kk, deriv=4)
+    (ref * dy.double()).sum().backward()
+    assert rel_err(dx, xr.grad * (x > 0).double()) < 2e-2
 
 
 @pytest.mark.parametrize("N", [10, 1000])

@@ -314,6 +314,106 @@ __global__ void lrn_backward_row_kernel(const __nv_bfloat16* __restrict__ x, con
 }
 
 // ---------------------------------------------------------------------------------------------
+// LRN, vector form: one thread per (pixel, 8-channel group).  The thread loads its own 16-byte
+// vector plus the two neighbouring ones (L1 hits: the neighbours are other threads' own vectors),
+// so everything a +-HALF window needs (and, backward, the window of windows, +-2*HALF <= 8) sits
+// in registers; no shared memory, no inter-thread traffic, 16-byte loads/stores throughout.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void load24(const __nv_bfloat16* row, int g, int T, float (&v)[24]) {
+  float a[8];
+  if (g > 0) unpack8(ldg16(row + (g - 1) * 8), a);
+  else {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) a[q] = 0.0f;
+  }
+#pragma unroll
+  for (int q = 0; q < 8; ++q) v[q] = a[q];
+  unpack8(ldg16(row + g * 8), a);
+#pragma unroll
+  for (int q = 0; q < 8; ++q) v[8 + q] = a[q];
+  if (g + 1 < T) unpack8(ldg16(row + (g + 1) * 8), a);
+  else {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) a[q] = 0.0f;
+  }
+#pragma unroll
+  for (int q = 0; q < 8; ++q) v[16 + q] = a[q];
+}
+
+template <int HALF>
+__global__ void __launch_bounds__(256)
+lrn_forward_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels, int C,
+                        float alpha, float beta, float k) {
+  const int T = C >> 3;
+  const long long total = pixels * T;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long px = i / T;
+    const int g = static_cast<int>(i - px * T);
+    float xv[24];
+    load24(x + px * C, g, T, xv);
+    float sq[24];
+#pragma unroll
+    for (int j = 0; j < 24; ++j) sq[j] = xv[j] * xv[j];
+    float out[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      float s = 0.0f;
+#pragma unroll
+      for (int d = -HALF; d <= HALF; ++d) s += sq[8 + q + d];
+      out[q] = xv[8 + q] * __powf(k + alpha * s, -beta);
+    }
+    *reinterpret_cast<uint4*>(y + px * C + g * 8) = pack8(out);
+  }
+}
+
+template <int HALF>
+__global__ void __launch_bounds__(256)
+lrn_backward_vec8_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                         __nv_bfloat16* __restrict__ dx, long long pixels, int C, float alpha, float beta, float k,
+                         int deriv) {
+  const int T = C >> 3;
+  const long long total = pixels * T;
+  const float coef = 2.0f * alpha * beta;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long px = i / T;
+    const int g = static_cast<int>(i - px * T);
+    float xv[24], dv[24];
+    load24(x + px * C, g, T, xv);
+    load24(dy + px * C, g, T, dv);
+    float sq[24];
+#pragma unroll
+    for (int j = 0; j < 24; ++j) sq[j] = xv[j] * xv[j];
+    // t[jj] = dy*x*s^(-beta-1) for channels c0-HALF .. c0+7+HALF;  dp[q] = dy*s^-beta for the own 8
+    float t[8 + 2 * HALF], dp[8];
+#pragma unroll
+    for (int jj = 0; jj < 8 + 2 * HALF; ++jj) {
+      const int j = 8 - HALF + jj;
+      float s = 0.0f;
+#pragma unroll
+      for (int d = -HALF; d <= HALF; ++d) s += sq[j + d];
+      s = k + alpha * s;
+      const float pw = __powf(s, -beta);
+      const float dpw = dv[j] * pw;
+      t[jj] = __fdividef(dpw * xv[j], s);
+      if (jj >= HALF && jj < HALF + 8) dp[jj - HALF] = dpw;
+    }
+    float out[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      float acc = 0.0f;
+#pragma unroll
+      for (int d = 0; d <= 2 * HALF; ++d) acc += t[q + d];
+      float v = dp[q] - coef * xv[8 + q] * acc;
+      if (deriv) v *= act_deriv_from_output(deriv, xv[8 + q]);
+      out[q] = v;
+    }
+    *reinterpret_cast<uint4*>(dx + px * C + g * 8) = pack8(out);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Launchers (return 1 when the fast path was taken, 0 when the caller must use the generic one,
 // negative on error)
 // ---------------------------------------------------------------------------------------------
@@ -369,6 +469,23 @@ int fast_pool_backward(int kind, const void* dy, const int* offs, void* dx, cons
 
 int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, float alpha, float beta, float k,
                      cudaStream_t s) {
+  const int half = n / 2;
+  if (C % 8 == 0 && half >= 1 && half <= 4 && !(reinterpret_cast<uintptr_t>(x) & 15) &&
+      !(reinterpret_cast<uintptr_t>(y) & 15)) {
+    const long long total = pixels * (C >> 3);
+    if (total == 0) return 1;
+    const int grid = grid_cap2(total, 256);
+    const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
+    __nv_bfloat16* yp = static_cast<__nv_bfloat16*>(y);
+    switch (half) {
+      case 1: lrn_forward_vec8_kernel<1><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+      case 2: lrn_forward_vec8_kernel<2><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+      case 3: lrn_forward_vec8_kernel<3><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+      default: lrn_forward_vec8_kernel<4><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+    }
+    VB_CHECK_CUDA(cudaGetLastError());
+    return 1;
+  }
   if (C > 1024) return 0;
   const int warps = 8;
   const size_t smem = static_cast<size_t>(warps) * C * sizeof(float);
@@ -383,6 +500,24 @@ int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, flo
 
 int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels, int C, int n, float alpha, float beta,
                       float k, int deriv, cudaStream_t s) {
+  const int half = n / 2;
+  if (C % 8 == 0 && half >= 1 && half <= 4 && !(reinterpret_cast<uintptr_t>(x) & 15) &&
+      !(reinterpret_cast<uintptr_t>(dy) & 15) && !(reinterpret_cast<uintptr_t>(dx) & 15)) {
+    const long long total = pixels * (C >> 3);
+    if (total == 0) return 1;
+    const int grid = grid_cap2(total, 256);
+    const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
+    const __nv_bfloat16* dp = static_cast<const __nv_bfloat16*>(dy);
+    __nv_bfloat16* op = static_cast<__nv_bfloat16*>(dx);
+    switch (half) {
+      case 1: lrn_backward_vec8_kernel<1><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+      case 2: lrn_backward_vec8_kernel<2><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+      case 3: lrn_backward_vec8_kernel<3><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+      default: lrn_backward_vec8_kernel<4><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+    }
+    VB_CHECK_CUDA(cudaGetLastError());
+    return 1;
+  }
   if (C > 1024) return 0;
   const int warps = 4;
   const size_t smem = static_cast<size_t>(warps) * 3 * C * sizeof(float);

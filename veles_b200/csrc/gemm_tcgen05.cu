@@ -33,8 +33,25 @@ constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int GEMM_THREADS = 192;
 
+// Implicit-GEMM convolution: one operand is fetched by TMA in im2col mode straight from the NHWC
+// activation tensor (no column matrix is ever materialised).  mode:
+//   0 plain GEMM
+//   1 forward   A = im2col(X)  [pixels x (tap, c)]      B = W  K-major  [n, tap*cg + c]
+//   2 backward  A = im2col(dY) with flipped taps         B = W  MN-major [k = n, n = c] per tap   (stride 1)
+//   3 weights   A = dY MN-major [k = pixel, m = n]       B = im2col(X) MN-major [k = pixel, n = (tap, c)]
+struct ConvParams {
+  int mode;
+  int kx, ky;        // filter taps
+  int OW, OH;        // base positions per row / rows per image of the im2col traversal
+  int sx, sy;        // traversal strides
+  int low_w, low_h;  // bounding-box lower corner (= -pad; -(k-1-pad) for mode 2)
+  int cblocks;       // 64-channel blocks per tap along the im2col tensor's channel dimension
+  int cg;            // weight-matrix columns per tap
+};
+
 struct GemmParams {
   int M, N, K;
+  ConvParams cv;
   void* D;          // bf16 or fp32, row-major, leading dimension ldd (elements)
   long long ldd;
   const float* bias;  // [N] or null
@@ -137,26 +154,84 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         const int nb = mn / p.m_blocks;
         const int kb0 = ks * kb_per_split;
         const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
+        // im2col-mode A (modes 1, 2): first pixel of this M tile in traversal coordinates
+        int a_w = 0, a_h = 0, a_n = 0;
+        if (p.cv.mode == 1 || p.cv.mode == 2) {
+          const int m0 = mb * BLOCK_M;
+          const int per_img = p.cv.OH * p.cv.OW;
+          a_n = m0 / per_img;
+          const int rem = m0 - a_n * per_img;
+          const int oh = rem / p.cv.OW;
+          a_h = oh * p.cv.sy + p.cv.low_h;
+          a_w = (rem - oh * p.cv.OW) * p.cv.sx + p.cv.low_w;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * L::STAGE_BYTES;
           uint8_t* sb = sa + L::A_BYTES;
           mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
-          if (!A_MN) {
-            tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BLOCK_K, mb * BLOCK_M);
-          } else {
+          if (p.cv.mode == 0) {
+            if (!A_MN) {
+              tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BLOCK_K, mb * BLOCK_M);
+            } else {
+#pragma unroll
+              for (int c = 0; c < BLOCK_M / 64; ++c)
+                tma_load_2d(sa + c * (BLOCK_K * 128), &tma_a, &full_bar[stage],
+                            mb * BLOCK_M + c * 64, kb * BLOCK_K);
+            }
+            if (!B_MN) {
+              tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BLOCK_K, nb * BN);
+            } else {
+#pragma unroll
+              for (int c = 0; c < BN / 64; ++c)
+                tma_load_2d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage], nb * BN + c * 64,
+                            kb * BLOCK_K);
+            }
+          } else if (p.cv.mode == 3) {
+            // A: dY, MN-major tiled.  B: one im2col box (64 pixels x 64 channels) per 64-column chunk.
 #pragma unroll
             for (int c = 0; c < BLOCK_M / 64; ++c)
-              tma_load_2d(sa + c * (BLOCK_K * 128), &tma_a, &full_bar[stage],
-                          mb * BLOCK_M + c * 64, kb * BLOCK_K);
-          }
-          if (!B_MN) {
-            tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BLOCK_K, nb * BN);
-          } else {
-#pragma unroll
-            for (int c = 0; c < BN / 64; ++c)
-              tma_load_2d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage], nb * BN + c * 64,
+              tma_load_2d(sa + c * (BLOCK_K * 128), &tma_a, &full_bar[stage], mb * BLOCK_M + c * 64,
                           kb * BLOCK_K);
+            const int px0 = kb * BLOCK_K;
+            const int per_img = p.cv.OH * p.cv.OW;
+            const int img = px0 / per_img;
+            const int rem = px0 - img * per_img;
+            const int oh = rem / p.cv.OW;
+            const int bh = oh * p.cv.sy + p.cv.low_h;
+            const int bw = (rem - oh * p.cv.OW) * p.cv.sx + p.cv.low_w;
+            const int nblk = p.cv.kx * p.cv.ky * p.cv.cblocks;
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c) {
+              const int blk = nb * (BN / 64) + c;
+              if (blk < nblk) {
+                const int tap = blk / p.cv.cblocks;
+                const int cb = blk - tap * p.cv.cblocks;
+                const int r = tap / p.cv.kx;
+                tma_load_im2col_4d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage], cb * 64, bw, bh, img,
+                                   static_cast<uint16_t>(tap - r * p.cv.kx), static_cast<uint16_t>(r));
+              } else {  // past the last tap: channel coordinate out of range -> a box of zeros
+                tma_load_im2col_4d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage], p.cv.cblocks * 64, bw, bh,
+                                   img, 0, 0);
+              }
+            }
+          } else {
+            const int tap = kb / p.cv.cblocks;
+            const int cb = kb - tap * p.cv.cblocks;
+            const int r = tap / p.cv.kx;
+            const int sx_tap = tap - r * p.cv.kx;
+            tma_load_im2col_4d(sa, &tma_a, &full_bar[stage], cb * 64, a_w, a_h, a_n,
+                               static_cast<uint16_t>(sx_tap), static_cast<uint16_t>(r));
+            if (p.cv.mode == 1) {
+              tma_load_2d(sb, &tma_b, &full_bar[stage], tap * p.cv.cg + cb * 64, nb * BN);
+            } else {
+              // dX: the dY pixel reached through offset (s', r') pairs with filter tap (ky-1-r', kx-1-s')
+              const int wtap = (p.cv.ky - 1 - r) * p.cv.kx + (p.cv.kx - 1 - sx_tap);
+#pragma unroll
+              for (int c = 0; c < BN / 64; ++c)
+                tma_load_2d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage],
+                            wtap * p.cv.cg + nb * BN + c * 64, cb * 64);
+            }
           }
           if (++stage == STAGES) {
             stage = 0;
@@ -238,6 +313,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       for (int c0 = 0; c0 < BN; c0 += 32) {
         const int col0 = nb * BN + c0;
         if (col0 >= p.N) break;  // warp-uniform
+        int dcol0 = col0;          // first column of this slab in D
+        int nvalid = p.N - col0;   // columns of the slab that exist in D
+        if (p.cv.mode == 3) {      // virtual (tap, 64-channel block) columns -> weight-matrix columns
+          const int blk = col0 >> 6;
+          const int tap = blk / p.cv.cblocks;
+          const int cpos = (blk - tap * p.cv.cblocks) * 64 + (col0 & 63);
+          if (cpos >= p.cv.cg) continue;  // channel padding only
+          dcol0 = tap * p.cv.cg + cpos;
+          nvalid = p.cv.cg - cpos;
+        }
         uint32_t v[32];
         if (has_k) {
           tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
@@ -251,11 +336,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
-        const bool full = (col0 + 32 <= p.N);
+        const bool full = nvalid >= 32;
         if (add_bias) {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
-            if (full || col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
+            if (full || j < nvalid) f[j] += __ldg(p.bias + dcol0 + j);
         }
         // The activation code is warp-uniform: branch once, keep f[] in registers.
         switch (p.act) {
@@ -266,7 +351,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           default: break;
         }
         if (p.Z != nullptr && row_ok) {
-          const __nv_bfloat16* zrow = p.Z + static_cast<long long>(row) * p.ldz + col0;
+          const __nv_bfloat16* zrow = p.Z + static_cast<long long>(row) * p.ldz + dcol0;
           float d[32];
           if (full && ((p.ldz & 7) == 0)) {
 #pragma unroll
@@ -281,7 +366,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             }
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) d[j] = (col0 + j < p.N) ? __bfloat162float(zrow[j]) : 0.0f;
+            for (int j = 0; j < 32; ++j) d[j] = (j < nvalid) ? __bfloat162float(zrow[j]) : 0.0f;
           }
           switch (p.deriv) {
             case ACT_TANH: apply_deriv<ACT_TANH>(f, d); break;
@@ -307,8 +392,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
-              if (p.accumulate) tma_reduce_add_2d(&tma_d, buf, col0, row0);
-              else tma_store_2d(&tma_d, buf, col0, row0);
+              if (p.accumulate) tma_reduce_add_2d(&tma_d, buf, dcol0, row0);
+              else tma_store_2d(&tma_d, buf, dcol0, row0);
               tma_store_commit();
             }
             ebuf ^= 1;
@@ -339,11 +424,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           }
         } else if (row_ok) {
           if (p.out_fp32) {
-            float* drow = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + col0;
+            float* drow = reinterpret_cast<float*>(p.D) + static_cast<long long>(row) * p.ldd + dcol0;
             if (p.accumulate) {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                if (full || col0 + j < p.N) atomicAdd(drow + j, f[j]);
+                if (full || j < nvalid) atomicAdd(drow + j, f[j]);
             } else if (full && ((p.ldd & 3) == 0)) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4)
@@ -351,11 +436,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                if (col0 + j < p.N) drow[j] = f[j];
+                if (j < nvalid) drow[j] = f[j];
             }
           } else {
             __nv_bfloat16* drow =
-                reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<long long>(row) * p.ldd + col0;
+                reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<long long>(row) * p.ldd + dcol0;
             if (full && ((p.ldd & 7) == 0)) {
 #pragma unroll
               for (int j = 0; j < 32; j += 8) {
@@ -369,7 +454,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                if (col0 + j < p.N) drow[j] = __float2bfloat16(f[j]);
+                if (j < nvalid) drow[j] = __float2bfloat16(f[j]);
             }
           }
         }
@@ -445,6 +530,50 @@ static int make_tmap_2d(CUtensorMap* out, const void* base, long long inner, lon
   return 0;
 }
 
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeIm2colFn get_encode_im2col_fn() {
+  static EncodeIm2colFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeIm2colFn>(f);
+  });
+  return fn;
+}
+
+// NHWC bf16 tensor walked in im2col mode: `n_w x n_h` base positions per image starting at
+// (low_w, low_h) with traversal strides (sx, sy); a box is `pixels` consecutive base positions
+// (wrapping rows and images) x `channels` channels, 128B-swizzled; out-of-image taps read zeros.
+static int make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, int H, int B, long long pitch,
+                                 int low_w, int low_h, int n_w, int n_h, int sx, int sy, int channels, int pixels) {
+  EncodeIm2colFn fn = get_encode_im2col_fn();
+  VB_REQUIRE(fn != nullptr, "cuTensorMapEncodeIm2col entry point unavailable");
+  VB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "im2col TMA base pointer must be 16-byte aligned");
+  cuuint64_t gdim[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                        static_cast<cuuint64_t>(B)};
+  cuuint64_t gstride[3] = {static_cast<cuuint64_t>(pitch) * 2, static_cast<cuuint64_t>(pitch) * 2 * W,
+                           static_cast<cuuint64_t>(pitch) * 2 * W * H};
+  // upper corner chosen so that exactly n_w x n_h base positions exist
+  int lower[2] = {low_w, low_h};
+  int upper[2] = {low_w + (n_w - 1) * sx - (W - 1), low_h + (n_h - 1) * sy - (H - 1)};
+  cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(sx), static_cast<cuuint32_t>(sy), 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride, lower, upper,
+                  static_cast<cuuint32_t>(channels), static_cast<cuuint32_t>(pixels), estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  VB_REQUIRE(r == CUDA_SUCCESS,
+             "cuTensorMapEncodeIm2col failed with CUresult %d (C=%d W=%d H=%d B=%d pitch=%lld lower=%d,%d upper=%d,%d)",
+             static_cast<int>(r), C, W, H, B, pitch, lower[0], lower[1], upper[0], upper[1]);
+  return 0;
+}
+
 template <int BN, bool A_MN, bool B_MN>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
                        const GemmParams& p, int grid, cudaStream_t stream) {
@@ -480,6 +609,29 @@ extern "C" int vb_gemm_set_direct_epilogue(int on) {
   return 0;
 }
 
+// Builds the output tensor map (when D qualifies) and launches the right instantiation.
+static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtensorMap& tb, bool a_mn, bool b_mn,
+                             int BN, cudaStream_t stream, int d_cols = -1) {
+  const int sms = device_sm_count();
+  // Output through TMA whenever D satisfies the tensor-map alignment rules; otherwise the
+  // epilogue falls back to per-thread global stores / atomics.
+  CUtensorMap td;
+  memset(&td, 0, sizeof(td));
+  const int es = p.out_fp32 ? 4 : 2;
+  p.tma_store = ((reinterpret_cast<uintptr_t>(p.D) & 15) == 0 && (p.ldd * es) % 16 == 0 && !g_disable_tma_store) ? 1 : 0;
+  if (p.tma_store) {
+    int rc = make_tmap_2d(&td, p.D, d_cols > 0 ? d_cols : p.N, p.M, p.ldd, p.out_fp32 ? 32 : 64, 32, p.out_fp32 != 0);
+    if (rc) return rc;
+  }
+  const long long tiles = static_cast<long long>(p.m_blocks) * p.n_blocks * p.split_k;
+  const int grid = static_cast<int>(tiles < sms ? tiles : sms);
+  switch (BN) {
+    case 64: return dispatch_major<64>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+    case 128: return dispatch_major<128>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+    default: return dispatch_major<256>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+  }
+}
+
 extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
                             int b_mn_major, void* D, long long ldd, int M, int N, int K,
                             const float* bias, int act, int out_fp32, int accumulate, const void* Z,
@@ -504,6 +656,7 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
   }
   VB_REQUIRE(BN == 64 || BN == 128 || BN == 256, "vb_gemm_bf16: block_n must be 0/64/128/256");
   GemmParams p;
+  memset(&p, 0, sizeof(p));
   p.M = M; p.N = N; p.K = K;
   p.D = D; p.ldd = ldd; p.bias = bias; p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.alpha = alpha;
@@ -535,21 +688,103 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
   if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BLOCK_K, BN);
   else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BLOCK_K);
   if (rc) return rc;
-  // Output through TMA whenever D satisfies the tensor-map alignment rules; otherwise the
-  // epilogue falls back to per-thread global stores / atomics.
-  CUtensorMap td;
-  memset(&td, 0, sizeof(td));
-  const int es = out_fp32 ? 4 : 2;
-  p.tma_store = ((reinterpret_cast<uintptr_t>(D) & 15) == 0 && (ldd * es) % 16 == 0 && !g_disable_tma_store) ? 1 : 0;
-  if (p.tma_store) {
-    rc = make_tmap_2d(&td, D, N, M, ldd, out_fp32 ? 32 : 64, 32, out_fp32 != 0);
+  return finish_and_launch(p, ta, tb, a_mn_major != 0, b_mn_major != 0, BN, stream);
+}
+
+// ----------------------------------------------------------------------------
+// Implicit-GEMM convolution entry point (see ConvParams).  `T` is the NHWC tensor walked in
+// im2col mode (X for modes 1/3, dY for mode 2) with any group channel offset already applied:
+// tB x tH x tW pixels, `t_pitch` elements between pixels, `t_ch` channels visible.  `other` is
+// the weight matrix [rows, taps*cg] (modes 1, 2) or dY [pixels, M] (mode 3).
+// ----------------------------------------------------------------------------
+extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW, long long t_pitch, int t_ch,
+                                 int ky, int kx, int sy, int sx, int low_h, int low_w, int oH, int oW,
+                                 const void* other, long long ld_other, int other_rows, int cg, void* D,
+                                 long long ldd, int M, int N, const float* bias, int act, int out_fp32,
+                                 int accumulate, const void* Z, long long ldz, int deriv, float alpha,
+                                 int split_k, int block_n, cudaStream_t stream) {
+  VB_REQUIRE(mode >= 1 && mode <= 3, "vb_conv_gemm_bf16: mode must be 1 (forward), 2 (err_input) or 3 (weights)");
+  VB_REQUIRE(tB > 0 && tH > 0 && tW > 0 && oH > 0 && oW > 0 && M > 0 && N > 0, "vb_conv_gemm_bf16: empty problem");
+  VB_REQUIRE(t_ch % 8 == 0 && t_pitch % 8 == 0, "vb_conv_gemm_bf16: channels (%d) and pixel pitch (%lld) must be multiples of 8", t_ch, t_pitch);
+  VB_REQUIRE(kx >= 1 && ky >= 1 && kx <= 32 && ky <= 32, "vb_conv_gemm_bf16: filter %dx%d out of range", ky, kx);
+  VB_REQUIRE(!(accumulate && !out_fp32), "vb_conv_gemm_bf16: accumulate requires fp32 output");
+  VB_REQUIRE(mode != 2 || (sx == 1 && sy == 1), "vb_conv_gemm_bf16: err_input mode needs unit stride");
+  const long long pixels = static_cast<long long>(tB) * oH * oW;
+  VB_REQUIRE(pixels < (1LL << 31), "vb_conv_gemm_bf16: too many pixels");
+  const int taps = kx * ky;
+  const int cblocks = ceil_div(t_ch, 64);
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.cv.mode = mode; p.cv.kx = kx; p.cv.ky = ky; p.cv.OW = oW; p.cv.OH = oH; p.cv.sx = sx; p.cv.sy = sy;
+  p.cv.low_w = low_w; p.cv.low_h = low_h; p.cv.cblocks = cblocks; p.cv.cg = cg;
+  p.D = D; p.ldd = ldd; p.bias = bias; p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.alpha = alpha;
+  const int sms = device_sm_count();
+  int n_virtual = N;
+  if (mode == 3) {
+    VB_REQUIRE(out_fp32, "vb_conv_gemm_bf16: the weight gradient is fp32");
+    VB_REQUIRE(N == taps * cg && cg <= t_ch, "vb_conv_gemm_bf16: N must be taps*cg");
+    VB_REQUIRE(accumulate || cg % 32 == 0, "vb_conv_gemm_bf16: cg %% 32 != 0 needs accumulate=1");
+    VB_REQUIRE(bias == nullptr && act == 0 && Z == nullptr, "vb_conv_gemm_bf16: weights mode has a linear epilogue");
+    n_virtual = taps * cblocks * 64;
+  }
+  int BN = block_n;
+  if (BN == 0) {
+    if (n_virtual <= 64) BN = 64;
+    else if (n_virtual <= 128) BN = 128;
+    else {
+      const long long t256 = static_cast<long long>(ceil_div(M, BLOCK_M)) * ceil_div(n_virtual, 256);
+      BN = (t256 >= 2LL * sms) ? 256 : 128;
+    }
+  }
+  VB_REQUIRE(BN == 64 || BN == 128 || BN == 256, "vb_conv_gemm_bf16: block_n must be 0/64/128/256");
+  p.M = M; p.N = n_virtual;
+  p.m_blocks = ceil_div(M, BLOCK_M);
+  p.n_blocks = ceil_div(n_virtual, BN);
+  int rc;
+  CUtensorMap ta, tb;
+  bool a_mn = false, b_mn = false;
+  if (mode == 1 || mode == 2) {
+    VB_REQUIRE(static_cast<long long>(M) == pixels, "vb_conv_gemm_bf16: M must equal tB*oH*oW");
+    p.k_blocks = taps * cblocks;
+    p.K = p.k_blocks * BLOCK_K;
+    rc = make_tmap_im2col_bf16(&ta, T, t_ch, tW, tH, tB, t_pitch, low_w, low_h, oW, oH, sx, sy, 64, BLOCK_M);
+    if (rc) return rc;
+    if (mode == 1) {
+      rc = make_tmap_bf16_2d(&tb, other, static_cast<long long>(taps) * cg, other_rows, ld_other, BLOCK_K, BN);
+    } else {
+      b_mn = true;
+      rc = make_tmap_bf16_2d(&tb, other, static_cast<long long>(taps) * cg, other_rows, ld_other, 64, BLOCK_K);
+    }
+    if (rc) return rc;
+  } else {
+    a_mn = true; b_mn = true;
+    p.K = static_cast<int>(pixels);
+    p.k_blocks = ceil_div(p.K, BLOCK_K);
+    rc = make_tmap_bf16_2d(&ta, other, M, pixels, ld_other, 64, BLOCK_K);
+    if (rc) return rc;
+    rc = make_tmap_im2col_bf16(&tb, T, t_ch, tW, tH, tB, t_pitch, low_w, low_h, oW, oH, sx, sy, 64, BLOCK_K);
     if (rc) return rc;
   }
-  const long long tiles = static_cast<long long>(p.m_blocks) * p.n_blocks * p.split_k;
-  const int grid = static_cast<int>(tiles < sms ? tiles : sms);
-  switch (BN) {
-    case 64: return dispatch_major<64>(a_mn_major, b_mn_major, ta, tb, td, p, grid, stream);
-    case 128: return dispatch_major<128>(a_mn_major, b_mn_major, ta, tb, td, p, grid, stream);
-    default: return dispatch_major<256>(a_mn_major, b_mn_major, ta, tb, td, p, grid, stream);
+  const bool can_split = accumulate && act == 0 && Z == nullptr;
+  VB_REQUIRE(split_k >= 0 && (split_k <= 1 || can_split), "vb_conv_gemm_bf16: split-K needs accumulate=1 and a linear epilogue");
+  if (split_k == 0) {
+    split_k = 1;
+    const long long mn_tiles = static_cast<long long>(p.m_blocks) * p.n_blocks;
+    if (can_split && mn_tiles * 2 <= sms && p.k_blocks >= 8) {
+      long long sp = sms / mn_tiles;
+      const long long cap = p.k_blocks / 4;
+      if (sp > cap) sp = cap;
+      if (sp > 1) split_k = static_cast<int>(sp);
+    }
   }
+  if (split_k > p.k_blocks) split_k = p.k_blocks;
+  {
+    int per = ceil_div(p.k_blocks, split_k);
+    split_k = ceil_div(p.k_blocks, per);
+  }
+  p.split_k = split_k;
+  // D is described with its real extent so stores of padded / neighbouring-tap columns are clipped
+  p.N = n_virtual;
+  return finish_and_launch(p, ta, tb, a_mn, b_mn, BN, stream, mode == 3 ? N : -1);
 }

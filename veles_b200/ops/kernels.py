@@ -94,6 +94,57 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumu
     return out
 
 
+def _conv_gemm(mode, t4, ky, kx, sy, sx, low_h, low_w, n_h, n_w, other, other_rows, cg, out, M, N, bias=None,
+               act=ACT_LINEAR, accumulate=False, z=None, deriv=0, alpha=1.0, split_k=1, block_n=0):
+    assert t4.dtype == torch.bfloat16 and other.dtype == torch.bfloat16 and t4.dim() == 4
+    B, H, W, C = t4.shape
+    pitch = t4.stride(2)
+    assert t4.stride(3) == 1 and t4.stride(1) == W * pitch and t4.stride(0) == H * W * pitch, \
+        "im2col-mode tensor must be a (channel-sliced) contiguous NHWC view"
+    rc = _lib.lib().vb_conv_gemm_bf16(
+        c_int(mode), _p(t4), c_int(B), c_int(H), c_int(W), c_longlong(pitch), c_int(C), c_int(ky), c_int(kx),
+        c_int(sy), c_int(sx), c_int(low_h), c_int(low_w), c_int(n_h), c_int(n_w), _p(other), c_longlong(_ld(other)),
+        c_int(other_rows), c_int(cg), _p(out), c_longlong(_ld(out)), c_int(M), c_int(N), _p(bias), c_int(act),
+        c_int(1 if out.dtype == torch.float32 else 0), c_int(int(accumulate)), _p(z),
+        c_longlong(_ld(z) if z is not None else 0), c_int(deriv), c_float(alpha), c_int(split_k), c_int(block_n),
+        _stream())
+    _lib.check(rc, "vb_conv_gemm_bf16")
+    LAUNCHES[0] += 1
+    return out
+
+
+def conv_forward(x4, w, out2, g, bias=None, act=ACT_LINEAR, block_n=0):
+    """Implicit-GEMM convolution: out2[B*OH*OW, n] = act(im2col(x4) @ w^T + bias) with the im2col operand fetched
+    by TMA in im2col mode (no column matrix).  ``x4`` [B,H,W,Cg] (may be a channel slice), ``w`` [n, ky*kx*Cg];
+    ``g`` is the layer geometry dict (OH, OW, ky, kx, sy, sx, pt, pl)."""
+    B, H, W, Cg = x4.shape
+    n = w.shape[0]
+    assert w.shape[1] == g["ky"] * g["kx"] * Cg and tuple(out2.shape) == (B * g["OH"] * g["OW"], n)
+    return _conv_gemm(1, x4, g["ky"], g["kx"], g["sy"], g["sx"], -g["pt"], -g["pl"], g["OH"], g["OW"], w, n, Cg, out2,
+                      out2.shape[0], n, bias=bias, act=act, block_n=block_n)
+
+
+def conv_err_input(dy4, w, dx2, g, z=None, deriv=0, block_n=0):
+    """dx2[B*H*W, Cg] = (conv-transpose of dy4 [B,OH,OW,n] with w [n, ky*kx*Cg]) * f'(z); unit stride only.
+    ``g`` additionally carries H and W of the layer input."""
+    B, OH, OW, n = dy4.shape
+    Cg = dx2.shape[1]
+    assert g["sx"] == 1 and g["sy"] == 1 and w.shape[0] == n and w.shape[1] == g["ky"] * g["kx"] * Cg
+    assert dx2.shape[0] == B * g["H"] * g["W"]
+    return _conv_gemm(2, dy4, g["ky"], g["kx"], 1, 1, -(g["ky"] - 1 - g["pt"]), -(g["kx"] - 1 - g["pl"]), g["H"], g["W"],
+                      w, n, Cg, dx2, dx2.shape[0], Cg, z=z, deriv=deriv, block_n=block_n)
+
+
+def conv_weight_grad(x4, dy2, gw, g, accumulate=True, split_k=0, alpha=1.0, block_n=0):
+    """gw[n, ky*kx*Cg] (+)= dy2^T @ im2col(x4) with the im2col operand fetched by TMA (fp32 output)."""
+    B, H, W, Cg = x4.shape
+    n = dy2.shape[1]
+    assert dy2.shape[0] == B * g["OH"] * g["OW"] and tuple(gw.shape) == (n, g["ky"] * g["kx"] * Cg)
+    assert gw.dtype == torch.float32
+    return _conv_gemm(3, x4, g["ky"], g["kx"], g["sy"], g["sx"], -g["pt"], -g["pl"], g["OH"], g["OW"], dy2, n, Cg, gw,
+                      n, g["ky"] * g["kx"] * Cg, accumulate=accumulate, split_k=split_k, alpha=alpha, block_n=block_n)
+
+
 def gather_minibatch(src, indices, start, count, dst, mean=None, rdisp=None, labels=None, mb_labels=None,
                      mb_indices=None):
     """K1/K2/K4: dst[s] = normalise(cast(src[indices[start+s]])) for s<count else 0."""
