@@ -7,10 +7,12 @@ Pinned layout: input ``[B, H, W, C]``, weights ``[n_kernels, ky*kx*C/grouping]``
 order (tap row, tap col, channel), output ``[B, OH, OW, n_kernels]``; with ``grouping = G``
 kernels ``g*n/G .. (g+1)*n/G`` see input channels ``g*C/G .. (g+1)*C/G``.
 
-Device path: one vectorised im2col ("unpack", what Znicz did in ``unpack_size`` chunks) into a
-bf16 column matrix that stays resident for the backward pass (180 GB of HBM make the chunking
-unnecessary), then one tcgen05 GEMM per group with the bias+activation epilogue writing
-straight into the NHWC output (a column slice per group).
+Device path: an implicit GEMM.  The tcgen05 kernel's TMA producer walks the NHWC input in im2col
+mode (``cp.async.bulk.tensor.4d...im2col``: one box = 128 output pixels x 64 channels of one filter
+tap, out-of-image taps read as zeros), so the column matrix Znicz "unpacked" in ``unpack_size``
+chunks never exists; the bias+activation epilogue writes straight into the NHWC output (a column
+slice per group).  Layers whose per-group channel count is not a multiple of 8 (the 3-channel first
+layer) use one vectorised im2col into a resident bf16 column matrix and the same GEMM.
 """
 from __future__ import annotations
 
@@ -93,7 +95,7 @@ class Conv(Forward):
         pl, pt, pr, pb = self.padding
         sx, sy = self.sliding
         return dict(OH=conv_output_size(H, self.ky, pt, pb, sy), OW=conv_output_size(W, self.kx, pl, pr, sx),
-                    ky=self.ky, kx=self.kx, sy=sy, sx=sx, pt=pt, pl=pl, groups=self.grouping)
+                    ky=self.ky, kx=self.kx, sy=sy, sx=sx, pt=pt, pl=pl, groups=self.grouping, H=H, W=W)
 
     def initialize(self, device=None, **kwargs):
         if self.input is None or not self.input:
@@ -147,11 +149,26 @@ class Conv(Forward):
         kk = self.ky * self.kx * (C // self.grouping)
         if self.grouping > 1 and (kk % 8 or (self.n_kernels // self.grouping) % 8):
             raise ValueError("grouped convolution on the device needs ky*kx*C/G and n_kernels/G to be multiples of 8")
-        ld = (self.grouping * kk + 7) // 8 * 8
-        self.cols_ = torch.zeros(B * g["OH"] * g["OW"], ld, dtype=torch.bfloat16, device=dev.torch_device)
+        # Implicit GEMM (TMA im2col-mode loads, no column matrix) whenever the per-group channel count allows
+        # 16-byte channel vectors; otherwise (e.g. the 3-channel first layer) an explicit bf16 column matrix.
+        Cg, nkg = C // self.grouping, self.n_kernels // self.grouping
+        self.implicit_ = (Cg % 8 == 0 and nkg % 8 == 0 and not getattr(self, "force_explicit_im2col", False))
+        self.cols_ld_ = (self.grouping * kk + 7) // 8 * 8
+        self.cols_ = None
+        if not self.implicit_:
+            self.ensure_cols()
         self._x_stage4_ = None
         if self.input.devmem.dtype != torch.bfloat16:
             self._x_stage4_ = torch.zeros(self.in_shape4, dtype=torch.bfloat16, device=dev.torch_device)
+
+    def ensure_cols(self):
+        """The [B*OH*OW, G*ky*kx*Cg] bf16 column matrix (explicit path and strided err_input scratch)."""
+        import torch
+        if self.cols_ is None:
+            g = self.geometry
+            self.cols_ = torch.zeros(self.in_shape4[0] * g["OH"] * g["OW"], self.cols_ld_, dtype=torch.bfloat16,
+                                     device=self.device_.torch_device)
+        return self.cols_
 
     def device_input4(self):
         from ..ops import kernels
@@ -167,16 +184,25 @@ class Conv(Forward):
         self.input.unmap()
         x = self.device_input4()
         g = self.geometry
-        kernels.im2col(x, self.cols_, g)
         G = self.grouping
         nkg = self.n_kernels // G
         kg = self.weights_bf16_.shape[1]
         out2 = self.output.devmem.view(-1, self.n_kernels)
         bias = self.bias.devmem if self.include_bias else None
-        for gi in range(G):
-            kernels.gemm(self.cols_[:, gi * kg:(gi + 1) * kg], self.weights_bf16_[gi * nkg:(gi + 1) * nkg],
-                         out2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else out2,
-                         bias=bias[gi * nkg:(gi + 1) * nkg] if bias is not None else None, act=self.ACTIVATION)
+        if self.implicit_:
+            Cg = x.shape[3] // G
+            for gi in range(G):
+                kernels.conv_forward(x[..., gi * Cg:(gi + 1) * Cg] if G > 1 else x,
+                                     self.weights_bf16_[gi * nkg:(gi + 1) * nkg],
+                                     out2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else out2, g,
+                                     bias=bias[gi * nkg:(gi + 1) * nkg] if bias is not None else None,
+                                     act=self.ACTIVATION)
+        else:
+            kernels.im2col(x, self.cols_, g)
+            for gi in range(G):
+                kernels.gemm(self.cols_[:, gi * kg:(gi + 1) * kg], self.weights_bf16_[gi * nkg:(gi + 1) * nkg],
+                             out2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else out2,
+                             bias=bias[gi * nkg:(gi + 1) * nkg] if bias is not None else None, act=self.ACTIVATION)
         self.output.mark_device_written()
 
 

@@ -115,27 +115,47 @@ class GradientDescentConv(GradientDescentBase):
         nkg = nk // G
         w_bf16 = f.weights_bf16_
         kg = w_bf16.shape[1]
-        cols = f.cols_
         gw_t, gb_t = self.grad_tensors()
         gw = gw_t.view(nk, kg)
-        for gi in range(G):
-            e = eo2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else eo2
-            kernels.gemm(e, cols[:, gi * kg:(gi + 1) * kg], gw[gi * nkg:(gi + 1) * nkg], a_mn=True, b_mn=True,
-                         accumulate=True, split_k=0)
+        g = f.geometry
+        x4 = f.device_input4() if f._x_stage4_ is None else f._x_stage4_
+        Cg = x4.shape[3] // G
+        if f.implicit_:
+            for gi in range(G):
+                kernels.conv_weight_grad(x4[..., gi * Cg:(gi + 1) * Cg] if G > 1 else x4,
+                                         eo2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else eo2,
+                                         gw[gi * nkg:(gi + 1) * nkg], g, accumulate=True, split_k=0)
+        else:
+            cols = f.cols_
+            for gi in range(G):
+                e = eo2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else eo2
+                kernels.gemm(e, cols[:, gi * kg:(gi + 1) * kg], gw[gi * nkg:(gi + 1) * nkg], a_mn=True, b_mn=True,
+                             accumulate=True, split_k=0)
         self.gradient_weights.mark_device_written()
         if self.bias is not None and self.bias:
             kernels.col_sum(eo2, gb_t, self.col_scratch_, accumulate=True)
             self.gradient_bias.mark_device_written()
         if self.need_err_input:
-            for gi in range(G):
-                e = eo2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else eo2
-                kernels.gemm(e, w_bf16[gi * nkg:(gi + 1) * nkg], cols[:, gi * kg:(gi + 1) * kg], b_mn=True)
             ei = self.err_input.devmem
             ei4 = ei.reshape(f.in_shape4) if tuple(ei.shape) != tuple(f.in_shape4) else ei
-            z = None
-            if self.prev_activation:
-                z = f.device_input4() if f._x_stage4_ is None else f._x_stage4_
-            kernels.col2im(cols, ei4, f.geometry, z=z, deriv=self.prev_activation)
+            z = x4 if self.prev_activation else None
+            if f.implicit_ and g["sx"] == 1 and g["sy"] == 1:
+                # conv-transpose as one more implicit GEMM over dY; writes NHWC err_input directly
+                eo4 = eo2.view(x4.shape[0], g["OH"], g["OW"], nk)
+                ei2 = ei4.view(-1, x4.shape[3])
+                z2 = z.view(-1, x4.shape[3]) if z is not None else None
+                for gi in range(G):
+                    kernels.conv_err_input(eo4[..., gi * nkg:(gi + 1) * nkg] if G > 1 else eo4,
+                                           w_bf16[gi * nkg:(gi + 1) * nkg],
+                                           ei2[:, gi * Cg:(gi + 1) * Cg] if G > 1 else ei2, g,
+                                           z=(z2[:, gi * Cg:(gi + 1) * Cg] if G > 1 else z2) if z2 is not None else None,
+                                           deriv=self.prev_activation)
+            else:
+                cols = f.ensure_cols()
+                for gi in range(G):
+                    e = eo2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else eo2
+                    kernels.gemm(e, w_bf16[gi * nkg:(gi + 1) * nkg], cols[:, gi * kg:(gi + 1) * kg], b_mn=True)
+                kernels.col2im(cols, ei4, g, z=z, deriv=self.prev_activation)
             self.err_input.mark_device_written()
         self.device_update()
 
