@@ -52,7 +52,7 @@ def test_gemm_layouts(M, N, K_, a_mn, b_mn):
     assert rel_err(out, ref) < 2e-3, (M, N, K_, a_mn, b_mn)
 
 
-@pytest.mark.parametrize("block_n", [64, 128, 256])
+@pytest.mark.parametrize("block_n", [64, 128, 192, 256])
 def test_gemm_block_n_and_bf16_out(block_n):
     k = K()
     torch.manual_seed(block_n)
@@ -384,7 +384,8 @@ def _conv_geom(H, W, ky, kx, sy, sx, pt, pl, pb, pr, groups=1):
     return dict(OH=OH, OW=OW, ky=ky, kx=kx, sy=sy, sx=sx, pt=pt, pl=pl, groups=groups)
 
 
-@pytest.mark.parametrize("C,groups,k_,s_,p_", [(3, 1, 5, 1, 2), (16, 1, 3, 1, 1), (32, 2, 5, 2, 2), (3, 1, 11, 4, 0)])
+@pytest.mark.parametrize("C,groups,k_,s_,p_", [(3, 1, 5, 1, 2), (16, 1, 3, 1, 1), (32, 2, 5, 2, 2), (3, 1, 11, 4, 0),
+                                               (1, 1, 3, 2, 1), (4, 1, 4, 3, 0), (6, 2, 3, 1, 1)])
 def test_im2col_col2im_match_unfold(C, groups, k_, s_, p_):
     k = K()
     torch.manual_seed(C)

@@ -91,6 +91,58 @@ __global__ void im2col_any8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
 }
 
 // ---------------------------------------------------------------------------------------------
+// im2col through shared memory for few-channel layers (groups == 1, e.g. the RGB first layer).
+// One block per output row (b, oh): the ky input rows it touches are staged once (zero padded),
+// then every thread assembles 16-byte column vectors from smem.  Within a filter row the kx*C
+// elements of a tap row are contiguous in the staged row, so a vector is 8 two-byte smem reads
+// instead of 8 global loads with per-element bounds checks.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+im2col_rowtile_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, const FastConvGeom g,
+                      int rw) {
+  extern __shared__ unsigned short srows[];  // [ky][rw], rw = ((OW-1)*sx + kx) * C
+  const int b = blockIdx.x / g.OH;
+  const int oh = blockIdx.x - b * g.OH;
+  const unsigned short* xs = reinterpret_cast<const unsigned short*>(x);
+  const int wc = g.W * g.C;
+  for (int idx = threadIdx.x; idx < g.ky * rw; idx += blockDim.x) {
+    const int r = idx / rw;
+    const int e = idx - r * rw - g.pl * g.C;
+    const int h = oh * g.sy - g.pt + r;
+    unsigned short v = 0;
+    if (h >= 0 && h < g.H && e >= 0 && e < wc) v = __ldg(xs + (static_cast<long long>(b) * g.H + h) * wc + e);
+    srows[idx] = v;
+  }
+  __syncthreads();
+  const int kc = g.kx * g.C;
+  const int used = g.ky * kc;
+  const int vp = static_cast<int>(g.ld >> 3);
+  __nv_bfloat16* out_row = cols + static_cast<long long>(blockIdx.x) * g.OW * g.ld;
+  for (int v = threadIdx.x; v < g.OW * vp; v += blockDim.x) {
+    const int ow = v / vp;
+    const int j0 = (v - ow * vp) << 3;
+    int r = j0 / kc;
+    int t = j0 - r * kc;
+    const unsigned short* src = srows + ow * g.sx * g.C;
+    unsigned short e[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      e[q] = (j0 + q < used) ? src[r * rw + t] : static_cast<unsigned short>(0);
+      if (++t == kc) {
+        t = 0;
+        ++r;
+      }
+    }
+    uint4 o;
+    o.x = e[0] | (static_cast<uint32_t>(e[1]) << 16);
+    o.y = e[2] | (static_cast<uint32_t>(e[3]) << 16);
+    o.z = e[4] | (static_cast<uint32_t>(e[5]) << 16);
+    o.w = e[6] | (static_cast<uint32_t>(e[7]) << 16);
+    *reinterpret_cast<uint4*>(out_row + static_cast<long long>(ow) * g.ld + j0) = o;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // col2im, gather form, 8 channels per thread (Cg % 8 == 0): 16-byte loads of the column matrix.
 // ---------------------------------------------------------------------------------------------
 __global__ void col2im_vec8_kernel(const __nv_bfloat16* __restrict__ dcols, __nv_bfloat16* __restrict__ dx,
@@ -421,6 +473,21 @@ int fast_im2col(const void* x, void* cols, const FastConvGeom& g, cudaStream_t s
   if (g.ld % 8 || (reinterpret_cast<uintptr_t>(cols) & 15)) return 0;
   const long long total = static_cast<long long>(g.B) * g.OH * g.OW * (g.ld >> 3);
   if (total == 0) return 1;
+  if (g.groups == 1) {
+    const int rw = ((g.OW - 1) * g.sx + g.kx) * g.C;
+    const size_t smem = static_cast<size_t>(g.ky) * rw * sizeof(unsigned short);
+    if (smem <= 96 * 1024 && static_cast<long long>(g.B) * g.OH < 2147483647LL) {
+      static bool attr_set = false;
+      if (!attr_set) {
+        VB_CHECK_CUDA(cudaFuncSetAttribute(im2col_rowtile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        attr_set = true;
+      }
+      im2col_rowtile_kernel<<<g.B * g.OH, 256, smem, s>>>(static_cast<const __nv_bfloat16*>(x),
+                                                          static_cast<__nv_bfloat16*>(cols), g, rw);
+      VB_CHECK_CUDA(cudaGetLastError());
+      return 1;
+    }
+  }
   im2col_any8_kernel<<<grid_cap2(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x),
                                                            static_cast<__nv_bfloat16*>(cols), g);
   VB_CHECK_CUDA(cudaGetLastError());

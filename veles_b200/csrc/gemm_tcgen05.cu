@@ -72,7 +72,7 @@ struct SmemLayout {
   static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
   static constexpr int B_BYTES = BN * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 192 ? 4 : (BN == 128 ? 6 : 8));
   static constexpr int BAR_BYTES = 1024;
   static constexpr int EPI_BYTES = 4 /*warps*/ * 2 /*buffers*/ * 4096;  // 32 rows x 128 B slabs
   static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*align slack*/;
@@ -609,6 +609,48 @@ extern "C" int vb_gemm_set_direct_epilogue(int on) {
   return 0;
 }
 
+// Tile width and split-K selection.  The mainloop is bound by the per-SM operand ingest
+// (128 + BN rows of 128 B per k-block), so the cost of a candidate is
+//   waves * (k-blocks per split + per-tile overhead) * (128 + BN)
+// and the widest tile wins unless N-tail waste or a ragged last wave says otherwise.
+static void choose_config(int M, int N, int k_blocks, bool can_split, bool auto_split, bool b_k_major_only,
+                          int* bn_io, int* split_io) {
+  const int sms = device_sm_count();
+  const int m_blocks = ceil_div(M, BLOCK_M);
+  static const int cands[4] = {64, 128, 192, 256};
+  double best = 1e300;
+  int best_bn = 128, best_split = 1;
+  for (int ci = 0; ci < 4; ++ci) {
+    const int bn = cands[ci];
+    if (*bn_io != 0 && bn != *bn_io) continue;
+    if (*bn_io == 0 && bn > 64 && bn - 64 >= N) continue;  // a narrower candidate already covers N
+    const long long mn_tiles = static_cast<long long>(m_blocks) * ceil_div(N, bn);
+    int split = *split_io;
+    if (auto_split) {
+      split = 1;
+      if (can_split && mn_tiles * 2 <= sms && k_blocks >= 8) {
+        long long sp = sms / mn_tiles;
+        const long long cap = k_blocks / 4;
+        if (sp > cap) sp = cap;
+        if (sp > 1) split = static_cast<int>(sp);
+      }
+    }
+    if (split > k_blocks) split = k_blocks;
+    const int per = ceil_div(k_blocks, split);
+    split = ceil_div(k_blocks, per);  // every split non-empty
+    const long long waves = (mn_tiles * split + sms - 1) / sms;
+    const double cost = static_cast<double>(waves) * (per + 2.0) * (128 + bn);
+    if (cost < best) {
+      best = cost;
+      best_bn = bn;
+      best_split = split;
+    }
+  }
+  (void)b_k_major_only;
+  *bn_io = best_bn;
+  *split_io = best_split;
+}
+
 // Builds the output tensor map (when D qualifies) and launches the right instantiation.
 static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtensorMap& tb, bool a_mn, bool b_mn,
                              int BN, cudaStream_t stream, int d_cols = -1) {
@@ -628,6 +670,7 @@ static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtenso
   switch (BN) {
     case 64: return dispatch_major<64>(a_mn, b_mn, ta, tb, td, p, grid, stream);
     case 128: return dispatch_major<128>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+    case 192: return dispatch_major<192>(a_mn, b_mn, ta, tb, td, p, grid, stream);
     default: return dispatch_major<256>(a_mn, b_mn, ta, tb, td, p, grid, stream);
   }
 }
@@ -644,41 +687,18 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
   if (auto_split) split_k = 1;
   VB_REQUIRE(split_k == 1 || (accumulate && act == 0 && Z == nullptr),
              "vb_gemm_bf16: split-K needs accumulate=1 and a linear epilogue");
-  int BN = block_n;
-  const int sms = device_sm_count();
-  if (BN == 0) {
-    if (N <= 64) BN = 64;
-    else if (N <= 128) BN = 128;
-    else {
-      const long long t256 = static_cast<long long>(ceil_div(M, BLOCK_M)) * ceil_div(N, 256);
-      BN = (t256 >= 2LL * sms) ? 256 : 128;
-    }
-  }
-  VB_REQUIRE(BN == 64 || BN == 128 || BN == 256, "vb_gemm_bf16: block_n must be 0/64/128/256");
+  VB_REQUIRE(block_n == 0 || block_n == 64 || block_n == 128 || block_n == 192 || block_n == 256,
+             "vb_gemm_bf16: block_n must be 0/64/128/192/256");
   GemmParams p;
   memset(&p, 0, sizeof(p));
   p.M = M; p.N = N; p.K = K;
   p.D = D; p.ldd = ldd; p.bias = bias; p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.alpha = alpha;
+  p.k_blocks = ceil_div(K, BLOCK_K);
+  int BN = block_n;
+  choose_config(M, N, p.k_blocks, accumulate && act == 0 && Z == nullptr, auto_split, false, &BN, &split_k);
   p.m_blocks = ceil_div(M, BLOCK_M);
   p.n_blocks = ceil_div(N, BN);
-  p.k_blocks = ceil_div(K, BLOCK_K);
-  if (auto_split && accumulate && act == 0 && Z == nullptr) {
-    // fill the machine: tiles * split ~ number of SMs, but keep >= 4 k-blocks per split
-    const long long mn_tiles = static_cast<long long>(p.m_blocks) * p.n_blocks;
-    if (mn_tiles * 2 <= sms && p.k_blocks >= 8) {
-      long long s = sms / mn_tiles;
-      const long long cap = p.k_blocks / 4;
-      if (s > cap) s = cap;
-      if (s > 1) split_k = static_cast<int>(s);
-    }
-  }
-  if (split_k > p.k_blocks) split_k = p.k_blocks;
-  // make every split non-empty
-  {
-    int per = ceil_div(p.k_blocks, split_k);
-    split_k = ceil_div(p.k_blocks, per);
-  }
   p.split_k = split_k;
   CUtensorMap ta, tb;
   int rc;
@@ -728,16 +748,17 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
     VB_REQUIRE(bias == nullptr && act == 0 && Z == nullptr, "vb_conv_gemm_bf16: weights mode has a linear epilogue");
     n_virtual = taps * cblocks * 64;
   }
+  VB_REQUIRE(block_n == 0 || block_n == 64 || block_n == 128 || block_n == 192 || block_n == 256,
+             "vb_conv_gemm_bf16: block_n must be 0/64/128/192/256");
+  const bool can_split = accumulate && act == 0 && Z == nullptr;
+  VB_REQUIRE(split_k >= 0 && (split_k <= 1 || can_split), "vb_conv_gemm_bf16: split-K needs accumulate=1 and a linear epilogue");
+  const int kb_total = (mode == 3) ? ceil_div(static_cast<int>(pixels), BLOCK_K) : taps * cblocks;
   int BN = block_n;
-  if (BN == 0) {
-    if (n_virtual <= 64) BN = 64;
-    else if (n_virtual <= 128) BN = 128;
-    else {
-      const long long t256 = static_cast<long long>(ceil_div(M, BLOCK_M)) * ceil_div(n_virtual, 256);
-      BN = (t256 >= 2LL * sms) ? 256 : 128;
-    }
+  {
+    const bool auto_split = (split_k == 0);
+    if (auto_split) split_k = 1;
+    choose_config(M, n_virtual, kb_total, can_split, auto_split, false, &BN, &split_k);
   }
-  VB_REQUIRE(BN == 64 || BN == 128 || BN == 256, "vb_conv_gemm_bf16: block_n must be 0/64/128/256");
   p.M = M; p.N = n_virtual;
   p.m_blocks = ceil_div(M, BLOCK_M);
   p.n_blocks = ceil_div(n_virtual, BN);
@@ -765,23 +786,6 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
     if (rc) return rc;
     rc = make_tmap_im2col_bf16(&tb, T, t_ch, tW, tH, tB, t_pitch, low_w, low_h, oW, oH, sx, sy, 64, BLOCK_K);
     if (rc) return rc;
-  }
-  const bool can_split = accumulate && act == 0 && Z == nullptr;
-  VB_REQUIRE(split_k >= 0 && (split_k <= 1 || can_split), "vb_conv_gemm_bf16: split-K needs accumulate=1 and a linear epilogue");
-  if (split_k == 0) {
-    split_k = 1;
-    const long long mn_tiles = static_cast<long long>(p.m_blocks) * p.n_blocks;
-    if (can_split && mn_tiles * 2 <= sms && p.k_blocks >= 8) {
-      long long sp = sms / mn_tiles;
-      const long long cap = p.k_blocks / 4;
-      if (sp > cap) sp = cap;
-      if (sp > 1) split_k = static_cast<int>(sp);
-    }
-  }
-  if (split_k > p.k_blocks) split_k = p.k_blocks;
-  {
-    int per = ceil_div(p.k_blocks, split_k);
-    split_k = ceil_div(p.k_blocks, per);
   }
   p.split_k = split_k;
   // D is described with its real extent so stores of padded / neighbouring-tap columns are clipped

@@ -437,14 +437,84 @@ __global__ void col_sum_partial_kernel(const T* __restrict__ a, long long lda, i
   scratch[static_cast<long long>(slab) * cols + col] = s;
 }
 
+// bf16 fast path of the first phase: 16-byte loads.  A block is RL row-lanes x VCB 8-column vectors
+// (VCB = min(cols/8, 256), RL = 256 / VCB); each thread accumulates 8 columns over every RL-th row of
+// the slab, the row-lanes are folded through shared memory.  Same scratch layout as the scalar kernel.
+__global__ void __launch_bounds__(256)
+col_sum_partial_vec8_kernel(const __nv_bfloat16* __restrict__ a, long long lda, int rows, int cols,
+                            float* __restrict__ scratch, int rows_per_slab, int vcb, int rl) {
+  __shared__ float red[256 * 8];
+  const int vc_local = threadIdx.x % vcb;
+  const int lane_r = threadIdx.x / vcb;
+  const int vc = blockIdx.x * vcb + vc_local;
+  const int slab = blockIdx.y;
+  const int r0 = slab * rows_per_slab, r1 = min(rows, r0 + rows_per_slab);
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (lane_r < rl && vc * 8 < cols) {
+    const __nv_bfloat16* base = a + vc * 8;
+    for (int r = r0 + lane_r; r < r1; r += rl) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(r) * lda));
+      acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
+      acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 8; ++q) red[threadIdx.x * 8 + q] = acc[q];
+  __syncthreads();
+  // thread t < vcb*8 folds column t of this block over the row-lanes
+  for (int t = threadIdx.x; t < vcb * 8; t += blockDim.x) {
+    const int col = blockIdx.x * vcb * 8 + t;
+    if (col >= cols) continue;
+    float s2 = 0.0f;
+    for (int l = 0; l < rl; ++l) s2 += red[(l * vcb + (t >> 3)) * 8 + (t & 7)];
+    scratch[static_cast<long long>(slab) * cols + col] = s2;
+  }
+}
+
+// Second phase: 32 columns x 8 slab-lanes per block.
 __global__ void col_sum_final_kernel(const float* __restrict__ scratch, int slabs, int cols, float* __restrict__ out,
                                      float alpha, int accumulate) {
-  const int col = blockIdx.x * blockDim.x + threadIdx.x;
-  if (col >= cols) return;
+  __shared__ float red[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + tx;
   float s = 0.0f;
-  for (int k = 0; k < slabs; ++k) s += scratch[static_cast<long long>(k) * cols + col];
-  s *= alpha;
-  out[col] = accumulate ? out[col] + s : s;
+  if (col < cols)
+    for (int k = ty; k < slabs; k += 8) s += scratch[static_cast<long long>(k) * cols + col];
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && col < cols) {
+    float t = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][tx];
+    t *= alpha;
+    out[col] = accumulate ? out[col] + t : t;
+  }
+}
+
+// Launches both phases (shared by vb_col_sum and vb_col_sum_static).
+static int launch_col_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, float alpha,
+                          int accumulate, float* scratch, int rps, cudaStream_t s) {
+  const int slabs = rows > 0 ? ceil_div(rows, rps) : 0;
+  if (slabs > 0) {
+    if (dtype == D_BF16 && cols % 8 == 0 && lda % 8 == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0) {
+      const int vcols = cols / 8;
+      const int vcb = vcols < 256 ? vcols : 256;
+      const int rl = 256 / vcb;
+      dim3 grid(ceil_div(vcols, vcb), slabs);
+      col_sum_partial_vec8_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch,
+                                                       rps, vcb, rl);
+    } else {
+      dim3 grid(ceil_div(cols, 128), slabs);
+      if (dtype == D_F32)
+        col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch, rps);
+      else
+        col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch, rps);
+    }
+    VB_CHECK_CUDA(cudaGetLastError());
+  }
+  col_sum_final_kernel<<<ceil_div(cols, 32), 256, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }
 
 }  // namespace vb
@@ -654,15 +724,7 @@ extern "C" int vb_col_sum(const void* a, int dtype, long long lda, int rows, int
                           int accumulate, float* scratch, cudaStream_t s) {
   if (cols == 0) return 0;
   VB_REQUIRE(scratch != nullptr, "vb_col_sum: scratch buffer is required");
-  const int rps = colsum_rows_per_slab(rows);
-  const int slabs = ceil_div(rows > 0 ? rows : 1, rps);
-  dim3 grid(ceil_div(cols, 128), slabs);
-  if (dtype == D_F32) col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch, rps);
-  else col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch, rps);
-  VB_CHECK_CUDA(cudaGetLastError());
-  col_sum_final_kernel<<<ceil_div(cols, 128), 128, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate);
-  VB_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return launch_col_sum(a, dtype, lda, rows, cols, out, alpha, accumulate, scratch, colsum_rows_per_slab(rows), s);
 }
 
 // ---------------------------------------------------------------------------
@@ -728,13 +790,5 @@ extern "C" int vb_col_sum_static(const void* a, int dtype, long long lda, int ro
   VB_REQUIRE(dtype == D_F32 || dtype == D_BF16, "vb_col_sum_static: dtype must be f32 (0) or bf16 (1)");
   float* scratch = nullptr;
   if (int rc = colsum_static_scratch(&scratch)) return rc;
-  dim3 grid(ceil_div(cols, 128), slabs);
-  if (dtype == D_F32)
-    col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch, COLSUM_ROWS_PER_SLAB);
-  else
-    col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch, COLSUM_ROWS_PER_SLAB);
-  VB_CHECK_CUDA(cudaGetLastError());
-  col_sum_final_kernel<<<ceil_div(cols, 128), 128, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate);
-  VB_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return launch_col_sum(a, dtype, lda, rows, cols, out, alpha, accumulate, scratch, COLSUM_ROWS_PER_SLAB, s);
 }
