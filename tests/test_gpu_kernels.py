@@ -186,8 +186,37 @@ def _conv_ref(x, w, n, ky, kx, sy, sx, pt, pl, pb, pr, G):
     return torch.nn.functional.conv2d(xp, wt, stride=(sy, sx), groups=G).permute(0, 2, 3, 1).contiguous()
 
 
+@pytest.fixture(params=[1, 2], ids=["single_cta", "cta_pair"])
+def pair_mode(request):
+    """Runs a GEMM test with single-CTA tiles and again with cta_group::2 CTA-pair tiles forced."""
+    k = K()
+    k.set_pair_mode(request.param)
+    yield request.param
+    k.set_pair_mode(0)
+
+
+@pytest.mark.parametrize("M,N,K_", [(1024, 512, 320), (304, 264, 200), (776, 136, 1032), (4104, 96, 128)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("block_n", [0, 128, 256])
+def test_gemm_cta_pair_layouts(M, N, K_, a_mn, b_mn, block_n, pair_mode):
+    k = K()
+    torch.manual_seed(M + N + K_)
+    a = torch.randn((K_, M) if a_mn else (M, K_), device=dev()).bfloat16()
+    b = torch.randn((K_, N) if b_mn else (N, K_), device=dev()).bfloat16()
+    bias = torch.randn(N, device=dev())
+    ref = torch.relu((a.float().t() if a_mn else a.float()) @ (b.float() if b_mn else b.float().t()) + bias)
+    big = torch.full((M + 40, N + 24), float("nan"), device=dev(), dtype=torch.bfloat16)
+    k.gemm(a, b, big[:M, :N], a_mn=a_mn, b_mn=b_mn, bias=bias, act=4, block_n=block_n)
+    assert rel_err(big[:M, :N], ref) < 1e-2
+    assert torch.isnan(big[M:].float()).all() and torch.isnan(big[:, N:].float()).all()
+    out = torch.zeros(M, N, device=dev())
+    k.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn, accumulate=True, split_k=0, block_n=block_n)
+    k.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn, accumulate=True, split_k=2, block_n=block_n)
+    assert rel_err(out, 2 * ((a.float().t() if a_mn else a.float()) @ (b.float() if b_mn else b.float().t()))) < 3e-3
+
+
 @pytest.mark.parametrize("case", CONV_CASES)
-def test_implicit_gemm_conv_forward_backward(case):
+def test_implicit_gemm_conv_forward_backward(case, pair_mode):
     """TMA-im2col implicit GEMM (forward, err_input, weight gradient) vs torch conv2d autograd in fp32."""
     k = K()
     B, H, W, C, n, ky, kx, sy, sx, pt, pl, pb, pr, G = case

@@ -67,14 +67,16 @@ struct GemmParams {
   int m_blocks, n_blocks, k_blocks;
 };
 
-template <int BN>
+template <int BN, bool PAIR>
 struct SmemLayout {
   static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
-  static constexpr int B_BYTES = BN * BLOCK_K * 2;
+  static constexpr int B_ROWS = PAIR ? BN / 2 : BN;  // a CTA of a pair stages half of the B tile
+  static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 192 ? 4 : (BN == 128 ? 6 : 8));
   static constexpr int BAR_BYTES = 1024;
   static constexpr int EPI_BYTES = 4 /*warps*/ * 2 /*buffers*/ * 4096;  // 32 rows x 128 B slabs
+  static constexpr int BUDGET = 227 * 1024 - EPI_BYTES - BAR_BYTES - 1024;
+  static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
   static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*align slack*/;
 };
 constexpr int EPI_BUF_BYTES = 4096;
@@ -95,13 +97,22 @@ __device__ __forceinline__ void apply_deriv(float (&f)[32], const float (&y)[32]
   for (int j = 0; j < 32; ++j) f[j] *= act_deriv_from_output(ACT, y[j]);
 }
 
-template <int BN, bool A_MN, bool B_MN>
+// PAIR = true: the kernel runs as clusters of two CTAs (one TPC) driving tcgen05.mma.cta_group::2.
+// A pair owns a 256 x BN tile: CTA r stages A rows [r*128, r*128+128) and B rows
+// [r*BN/2, (r+1)*BN/2) of the tile, so every SM ingests 128 + BN/2 operand rows per k-block
+// instead of 128 + BN; the leader's MMA reads both halves (own smem + the peer's over the pair's
+// shared-memory path) and each CTA receives its 128 accumulator rows in its own TMEM.
+template <int BN, bool A_MN, bool B_MN, bool PAIR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                          const __grid_constant__ CUtensorMap tma_b,
                          const __grid_constant__ CUtensorMap tma_d, const GemmParams p) {
-  using L = SmemLayout<BN>;
+  using L = SmemLayout<BN, PAIR>;
   constexpr int STAGES = L::STAGES;
+  constexpr int TILE_M = PAIR ? 2 * BLOCK_M : BLOCK_M;
+  constexpr int BN_LOAD = L::B_ROWS;  // B rows / columns this CTA stages per k-block
+  const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
+  const bool leader = (cta_rank == 0);
   constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
 
   extern __shared__ uint8_t smem_raw[];
@@ -127,40 +138,48 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4);  // one arrive per epilogue warp
+      mbar_init(&tmem_empty[s], PAIR ? 8 : 4);  // one arrive per epilogue warp (of both CTAs)
     }
     fence_barrier_init();
     fence_proxy_async_smem();
   }
-  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_ptr);
+  if (warp == 1) {
+    if (PAIR) tmem_alloc_pair<TMEM_COLS>(tmem_ptr);
+    else tmem_alloc<TMEM_COLS>(tmem_ptr);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers exist before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
   const int tiles_mn = p.m_blocks * p.n_blocks;
   const int num_tiles = tiles_mn * p.split_k;
   const int kb_per_split = (p.k_blocks + p.split_k - 1) / p.split_k;
+  // persistent schedule: one work unit = one CTA (or one CTA pair)
+  const int unit = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int n_units = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = unit; tile < num_tiles; tile += n_units) {
         const int ks = tile / tiles_mn;
         const int mn = tile - ks * tiles_mn;
         const int mb = mn % p.m_blocks;
         const int nb = mn / p.m_blocks;
         const int kb0 = ks * kb_per_split;
         const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
-        // im2col-mode A (modes 1, 2): first pixel of this M tile in traversal coordinates
+        const int m_base = mb * TILE_M + static_cast<int>(cta_rank) * BLOCK_M;   // first A row staged here
+        const int n_base = nb * BN + static_cast<int>(cta_rank) * BN_LOAD;       // first B row/column staged here
+        // im2col-mode A (modes 1, 2): first pixel of this CTA's rows in traversal coordinates
         int a_w = 0, a_h = 0, a_n = 0;
         if (p.cv.mode == 1 || p.cv.mode == 2) {
-          const int m0 = mb * BLOCK_M;
           const int per_img = p.cv.OH * p.cv.OW;
-          a_n = m0 / per_img;
-          const int rem = m0 - a_n * per_img;
+          a_n = m_base / per_img;
+          const int rem = m_base - a_n * per_img;
           const int oh = rem / p.cv.OW;
           a_h = oh * p.cv.sy + p.cv.low_h;
           a_w = (rem - oh * p.cv.OW) * p.cv.sx + p.cv.low_w;
@@ -169,30 +188,37 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * L::STAGE_BYTES;
           uint8_t* sb = sa + L::A_BYTES;
-          mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
+          // completion lands on the leader's barrier, armed for the bytes of both CTAs
+          const uint32_t fb = PAIR ? mapa_u32(&full_bar[stage], 0) : smem_u32(&full_bar[stage]);
+          if (leader) mbar_expect_tx(&full_bar[stage], (PAIR ? 2 : 1) * L::STAGE_BYTES);
+          auto ld2 = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
+            if (PAIR) tma_load_2d_pair(dst, m, fb, c0, c1);
+            else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
+          };
+          auto ldi = [&](void* dst, const CUtensorMap* m, int c, int w, int h, int n, int wo, int ho) {
+            if (PAIR) tma_load_im2col_4d_pair(dst, m, fb, c, w, h, n, static_cast<uint16_t>(wo), static_cast<uint16_t>(ho));
+            else tma_load_im2col_4d(dst, m, &full_bar[stage], c, w, h, n, static_cast<uint16_t>(wo), static_cast<uint16_t>(ho));
+          };
           if (p.cv.mode == 0) {
             if (!A_MN) {
-              tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BLOCK_K, mb * BLOCK_M);
+              ld2(sa, &tma_a, kb * BLOCK_K, m_base);
             } else {
 #pragma unroll
               for (int c = 0; c < BLOCK_M / 64; ++c)
-                tma_load_2d(sa + c * (BLOCK_K * 128), &tma_a, &full_bar[stage],
-                            mb * BLOCK_M + c * 64, kb * BLOCK_K);
+                ld2(sa + c * (BLOCK_K * 128), &tma_a, m_base + c * 64, kb * BLOCK_K);
             }
             if (!B_MN) {
-              tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BLOCK_K, nb * BN);
+              ld2(sb, &tma_b, kb * BLOCK_K, n_base);
             } else {
 #pragma unroll
-              for (int c = 0; c < BN / 64; ++c)
-                tma_load_2d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage], nb * BN + c * 64,
-                            kb * BLOCK_K);
+              for (int c = 0; c < BN_LOAD / 64; ++c)
+                ld2(sb + c * (BLOCK_K * 128), &tma_b, n_base + c * 64, kb * BLOCK_K);
             }
           } else if (p.cv.mode == 3) {
             // A: dY, MN-major tiled.  B: one im2col box (64 pixels x 64 channels) per 64-column chunk.
 #pragma unroll
             for (int c = 0; c < BLOCK_M / 64; ++c)
-              tma_load_2d(sa + c * (BLOCK_K * 128), &tma_a, &full_bar[stage], mb * BLOCK_M + c * 64,
-                          kb * BLOCK_K);
+              ld2(sa + c * (BLOCK_K * 128), &tma_a, m_base + c * 64, kb * BLOCK_K);
             const int px0 = kb * BLOCK_K;
             const int per_img = p.cv.OH * p.cv.OW;
             const int img = px0 / per_img;
@@ -202,17 +228,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             const int bw = (rem - oh * p.cv.OW) * p.cv.sx + p.cv.low_w;
             const int nblk = p.cv.kx * p.cv.ky * p.cv.cblocks;
 #pragma unroll
-            for (int c = 0; c < BN / 64; ++c) {
-              const int blk = nb * (BN / 64) + c;
+            for (int c = 0; c < BN_LOAD / 64; ++c) {
+              const int blk = (n_base >> 6) + c;
               if (blk < nblk) {
                 const int tap = blk / p.cv.cblocks;
                 const int cb = blk - tap * p.cv.cblocks;
                 const int r = tap / p.cv.kx;
-                tma_load_im2col_4d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage], cb * 64, bw, bh, img,
-                                   static_cast<uint16_t>(tap - r * p.cv.kx), static_cast<uint16_t>(r));
+                ldi(sb + c * (BLOCK_K * 128), &tma_b, cb * 64, bw, bh, img, tap - r * p.cv.kx, r);
               } else {  // past the last tap: channel coordinate out of range -> a box of zeros
-                tma_load_im2col_4d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage], p.cv.cblocks * 64, bw, bh,
-                                   img, 0, 0);
+                ldi(sb + c * (BLOCK_K * 128), &tma_b, p.cv.cblocks * 64, bw, bh, img, 0, 0);
               }
             }
           } else {
@@ -220,17 +244,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             const int cb = kb - tap * p.cv.cblocks;
             const int r = tap / p.cv.kx;
             const int sx_tap = tap - r * p.cv.kx;
-            tma_load_im2col_4d(sa, &tma_a, &full_bar[stage], cb * 64, a_w, a_h, a_n,
-                               static_cast<uint16_t>(sx_tap), static_cast<uint16_t>(r));
+            ldi(sa, &tma_a, cb * 64, a_w, a_h, a_n, sx_tap, r);
             if (p.cv.mode == 1) {
-              tma_load_2d(sb, &tma_b, &full_bar[stage], tap * p.cv.cg + cb * 64, nb * BN);
+              ld2(sb, &tma_b, tap * p.cv.cg + cb * 64, n_base);
             } else {
               // dX: the dY pixel reached through offset (s', r') pairs with filter tap (ky-1-r', kx-1-s')
               const int wtap = (p.cv.ky - 1 - r) * p.cv.kx + (p.cv.kx - 1 - sx_tap);
 #pragma unroll
-              for (int c = 0; c < BN / 64; ++c)
-                tma_load_2d(sb + c * (BLOCK_K * 128), &tma_b, &full_bar[stage],
-                            wtap * p.cv.cg + nb * BN + c * 64, cb * 64);
+              for (int c = 0; c < BN_LOAD / 64; ++c)
+                ld2(sb + c * (BLOCK_K * 128), &tma_b, wtap * p.cv.cg + n_base + c * 64, cb * 64);
             }
           }
           if (++stage == STAGES) {
@@ -242,12 +264,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc(/*BF16*/ 1, A_MN, B_MN, BLOCK_M, BN);
+    constexpr uint32_t idesc = make_idesc(/*BF16*/ 1, A_MN, B_MN, TILE_M, BN);
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = unit; leader && tile < num_tiles; tile += n_units) {  // only the leader CTA issues MMAs
       const int ks = tile / tiles_mn;
       const int kb0 = ks * kb_per_split;
       const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
@@ -272,10 +294,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
             const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((A_MN ? k * 2048 : k * 32) >> 4);
             const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * 2048 : k * 32) >> 4);
-            umma_f16(d_tmem, a_desc, b_desc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (PAIR) umma_f16_pair(d_tmem, a_desc, b_desc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_f16(d_tmem, a_desc, b_desc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
-          if (kb == kb1 - 1) umma_commit(&tmem_full[acc]);
+          // frees the smem slot (in both CTAs of a pair) once these MMAs retire
+          if (PAIR) umma_commit_pair(&empty_bar[stage]);
+          else umma_commit(&empty_bar[stage]);
+          if (kb == kb1 - 1) {
+            if (PAIR) umma_commit_pair(&tmem_full[acc]);
+            else umma_commit(&tmem_full[acc]);
+          }
         }
         __syncwarp();
         if (++stage == STAGES) {
@@ -294,7 +322,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     int acc = 0;
     uint32_t acc_phase = 0;
     int ebuf = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = unit; tile < num_tiles; tile += n_units) {
       const int ks = tile / tiles_mn;
       const int mn = tile - ks * tiles_mn;
       const int mb = mn % p.m_blocks;
@@ -306,7 +334,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
       }
-      const int row0 = mb * BLOCK_M + quarter * 32;
+      const int row0 = mb * TILE_M + static_cast<int>(cta_rank) * BLOCK_M + quarter * 32;
       const int row = row0 + lane;
       const bool row_ok = row < p.M;
 #pragma unroll 1
@@ -462,7 +490,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       if (has_k) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (lane == 0) {
+          if (PAIR) mbar_arrive_cluster(mapa_u32(&tmem_empty[acc], 0));  // the leader's MMA warp waits on it
+          else mbar_arrive(&tmem_empty[acc]);
+        }
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -473,10 +504,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();  // nobody may still signal barriers or read operands of a CTA that exits
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<TMEM_COLS>(tmem_base);
+    if (PAIR) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+    else tmem_dealloc<TMEM_COLS>(tmem_base);
   }
 }
 
@@ -574,28 +607,45 @@ static int make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int 
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool PAIR>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
                        const GemmParams& p, int grid, cudaStream_t stream) {
-  using L = SmemLayout<BN>;
-  auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN>;
+  using L = SmemLayout<BN, PAIR>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN, PAIR>;
   static bool attr_set = false;
   if (!attr_set) {
     VB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set = true;
   }
-  kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, td, p);
+  if (PAIR) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = L::TOTAL;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p));
+  } else {
+    kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, td, p);
+  }
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
-template <int BN>
+template <int BN, bool PAIR>
 static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
                           const CUtensorMap& td, const GemmParams& p, int grid, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_gemm<BN, false, false>(ta, tb, td, p, grid, s);
-  if (!a_mn && b_mn) return launch_gemm<BN, false, true>(ta, tb, td, p, grid, s);
-  if (a_mn && !b_mn) return launch_gemm<BN, true, false>(ta, tb, td, p, grid, s);
-  return launch_gemm<BN, true, true>(ta, tb, td, p, grid, s);
+  if (!a_mn && !b_mn) return launch_gemm<BN, false, false, PAIR>(ta, tb, td, p, grid, s);
+  if (!a_mn && b_mn) return launch_gemm<BN, false, true, PAIR>(ta, tb, td, p, grid, s);
+  if (a_mn && !b_mn) return launch_gemm<BN, true, false, PAIR>(ta, tb, td, p, grid, s);
+  return launch_gemm<BN, true, true, PAIR>(ta, tb, td, p, grid, s);
 }
 
 }  // namespace vb
@@ -613,47 +663,57 @@ extern "C" int vb_gemm_set_direct_epilogue(int on) {
 // (128 + BN rows of 128 B per k-block), so the cost of a candidate is
 //   waves * (k-blocks per split + per-tile overhead) * (128 + BN)
 // and the widest tile wins unless N-tail waste or a ragged last wave says otherwise.
-static void choose_config(int M, int N, int k_blocks, bool can_split, bool auto_split, bool b_k_major_only,
-                          int* bn_io, int* split_io) {
+static int g_pair_mode = 0;  // 0 = choose by cost, 1 = never pair, 2 = pair whenever the shape allows (tests)
+
+static void choose_config(int M, int N, int k_blocks, bool can_split, bool auto_split, bool b_mn, int* bn_io,
+                          int* split_io, int* pair_out) {
   const int sms = device_sm_count();
-  const int m_blocks = ceil_div(M, BLOCK_M);
   static const int cands[4] = {64, 128, 192, 256};
   double best = 1e300;
-  int best_bn = 128, best_split = 1;
-  for (int ci = 0; ci < 4; ++ci) {
-    const int bn = cands[ci];
-    if (*bn_io != 0 && bn != *bn_io) continue;
-    if (*bn_io == 0 && bn > 64 && bn - 64 >= N) continue;  // a narrower candidate already covers N
-    const long long mn_tiles = static_cast<long long>(m_blocks) * ceil_div(N, bn);
-    int split = *split_io;
-    if (auto_split) {
-      split = 1;
-      if (can_split && mn_tiles * 2 <= sms && k_blocks >= 8) {
-        long long sp = sms / mn_tiles;
-        const long long cap = k_blocks / 4;
-        if (sp > cap) sp = cap;
-        if (sp > 1) split = static_cast<int>(sp);
+  int best_bn = 128, best_split = 1, best_pair = 0;
+  for (int pair = 0; pair < 2; ++pair) {
+    if (pair && (g_pair_mode == 1 || M <= BLOCK_M)) continue;
+    const int tile_m = pair ? 2 * BLOCK_M : BLOCK_M;
+    const int units = pair ? sms / 2 : sms;
+    const int m_blocks = ceil_div(M, tile_m);
+    for (int ci = 0; ci < 4; ++ci) {
+      const int bn = cands[ci];
+      if (*bn_io != 0 && bn != *bn_io) continue;
+      if (*bn_io == 0 && bn > 64 && bn - 64 >= N) continue;  // a narrower candidate already covers N
+      if (pair && (bn < 128 || (b_mn && (bn / 2) % 64 != 0))) continue;
+      const long long mn_tiles = static_cast<long long>(m_blocks) * ceil_div(N, bn);
+      int split = *split_io;
+      if (auto_split) {
+        split = 1;
+        if (can_split && mn_tiles * 2 <= units && k_blocks >= 8) {
+          long long sp = units / mn_tiles;
+          const long long cap = k_blocks / 4;
+          if (sp > cap) sp = cap;
+          if (sp > 1) split = static_cast<int>(sp);
+        }
+      }
+      if (split > k_blocks) split = k_blocks;
+      const int per = ceil_div(k_blocks, split);
+      split = ceil_div(k_blocks, per);  // every split non-empty
+      const long long waves = (mn_tiles * split + units - 1) / units;
+      double cost = static_cast<double>(waves) * (per + 2.0) * (128 + (pair ? bn / 2 : bn));
+      if (pair && g_pair_mode == 2) cost *= 1e-6;
+      if (cost < best) {
+        best = cost;
+        best_bn = bn;
+        best_split = split;
+        best_pair = pair;
       }
     }
-    if (split > k_blocks) split = k_blocks;
-    const int per = ceil_div(k_blocks, split);
-    split = ceil_div(k_blocks, per);  // every split non-empty
-    const long long waves = (mn_tiles * split + sms - 1) / sms;
-    const double cost = static_cast<double>(waves) * (per + 2.0) * (128 + bn);
-    if (cost < best) {
-      best = cost;
-      best_bn = bn;
-      best_split = split;
-    }
   }
-  (void)b_k_major_only;
   *bn_io = best_bn;
   *split_io = best_split;
+  *pair_out = best_pair;
 }
 
 // Builds the output tensor map (when D qualifies) and launches the right instantiation.
 static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtensorMap& tb, bool a_mn, bool b_mn,
-                             int BN, cudaStream_t stream, int d_cols = -1) {
+                             int BN, int pair, cudaStream_t stream, int d_cols = -1) {
   const int sms = device_sm_count();
   // Output through TMA whenever D satisfies the tensor-map alignment rules; otherwise the
   // epilogue falls back to per-thread global stores / atomics.
@@ -666,13 +726,30 @@ static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtenso
     if (rc) return rc;
   }
   const long long tiles = static_cast<long long>(p.m_blocks) * p.n_blocks * p.split_k;
+  if (pair) {
+    const int units = sms / 2;
+    const int grid = 2 * static_cast<int>(tiles < units ? tiles : units);
+    switch (BN) {
+      case 128: return dispatch_major<128, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+      case 192:
+        VB_REQUIRE(!b_mn, "paired 192-wide tiles need a K-major B operand");
+        return launch_gemm<192, false, false, true>(ta, tb, td, p, grid, stream) ;
+      default: return dispatch_major<256, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+    }
+  }
   const int grid = static_cast<int>(tiles < sms ? tiles : sms);
   switch (BN) {
-    case 64: return dispatch_major<64>(a_mn, b_mn, ta, tb, td, p, grid, stream);
-    case 128: return dispatch_major<128>(a_mn, b_mn, ta, tb, td, p, grid, stream);
-    case 192: return dispatch_major<192>(a_mn, b_mn, ta, tb, td, p, grid, stream);
-    default: return dispatch_major<256>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+    case 64: return dispatch_major<64, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+    case 128: return dispatch_major<128, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+    case 192: return dispatch_major<192, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+    default: return dispatch_major<256, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
   }
+}
+
+// Test hook: 0 = cost model decides, 1 = single-CTA tiles only, 2 = CTA pairs whenever the shape allows.
+extern "C" int vb_gemm_set_pair_mode(int mode) {
+  g_pair_mode = (mode == 1 || mode == 2) ? mode : 0;
+  return 0;
 }
 
 extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
@@ -695,20 +772,22 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
   p.D = D; p.ldd = ldd; p.bias = bias; p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.alpha = alpha;
   p.k_blocks = ceil_div(K, BLOCK_K);
-  int BN = block_n;
-  choose_config(M, N, p.k_blocks, accumulate && act == 0 && Z == nullptr, auto_split, false, &BN, &split_k);
-  p.m_blocks = ceil_div(M, BLOCK_M);
+  int BN = block_n, pair = 0;
+  choose_config(M, N, p.k_blocks, accumulate && act == 0 && Z == nullptr, auto_split, b_mn_major != 0, &BN, &split_k,
+                &pair);
+  p.m_blocks = ceil_div(M, pair ? 2 * BLOCK_M : BLOCK_M);
   p.n_blocks = ceil_div(N, BN);
   p.split_k = split_k;
+  const int bn_load = pair ? BN / 2 : BN;
   CUtensorMap ta, tb;
   int rc;
   if (!a_mn_major) rc = make_tmap_bf16_2d(&ta, A, K, M, lda, BLOCK_K, BLOCK_M);
   else rc = make_tmap_bf16_2d(&ta, A, M, K, lda, 64, BLOCK_K);
   if (rc) return rc;
-  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BLOCK_K, BN);
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BLOCK_K, bn_load);
   else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BLOCK_K);
   if (rc) return rc;
-  return finish_and_launch(p, ta, tb, a_mn_major != 0, b_mn_major != 0, BN, stream);
+  return finish_and_launch(p, ta, tb, a_mn_major != 0, b_mn_major != 0, BN, pair, stream);
 }
 
 // ----------------------------------------------------------------------------
@@ -753,14 +832,14 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
   const bool can_split = accumulate && act == 0 && Z == nullptr;
   VB_REQUIRE(split_k >= 0 && (split_k <= 1 || can_split), "vb_conv_gemm_bf16: split-K needs accumulate=1 and a linear epilogue");
   const int kb_total = (mode == 3) ? ceil_div(static_cast<int>(pixels), BLOCK_K) : taps * cblocks;
-  int BN = block_n;
+  int BN = block_n, pair = 0;
   {
     const bool auto_split = (split_k == 0);
     if (auto_split) split_k = 1;
-    choose_config(M, n_virtual, kb_total, can_split, auto_split, false, &BN, &split_k);
+    choose_config(M, n_virtual, kb_total, can_split, auto_split, mode != 1, &BN, &split_k, &pair);
   }
   p.M = M; p.N = n_virtual;
-  p.m_blocks = ceil_div(M, BLOCK_M);
+  p.m_blocks = ceil_div(M, pair ? 2 * BLOCK_M : BLOCK_M);
   p.n_blocks = ceil_div(n_virtual, BN);
   int rc;
   CUtensorMap ta, tb;
@@ -772,7 +851,7 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
     rc = make_tmap_im2col_bf16(&ta, T, t_ch, tW, tH, tB, t_pitch, low_w, low_h, oW, oH, sx, sy, 64, BLOCK_M);
     if (rc) return rc;
     if (mode == 1) {
-      rc = make_tmap_bf16_2d(&tb, other, static_cast<long long>(taps) * cg, other_rows, ld_other, BLOCK_K, BN);
+      rc = make_tmap_bf16_2d(&tb, other, static_cast<long long>(taps) * cg, other_rows, ld_other, BLOCK_K, pair ? BN / 2 : BN);
     } else {
       b_mn = true;
       rc = make_tmap_bf16_2d(&tb, other, static_cast<long long>(taps) * cg, other_rows, ld_other, 64, BLOCK_K);
@@ -790,5 +869,5 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
   p.split_k = split_k;
   // D is described with its real extent so stores of padded / neighbouring-tap columns are clipped
   p.N = n_virtual;
-  return finish_and_launch(p, ta, tb, a_mn, b_mn, BN, stream, mode == 3 ? N : -1);
+  return finish_and_launch(p, ta, tb, a_mn, b_mn, BN, pair, stream, mode == 3 ? N : -1);
 }

@@ -65,6 +65,12 @@ def set_direct_epilogue(on):
     _lib.check(_lib.lib().vb_gemm_set_direct_epilogue(c_int(int(bool(on)))), "vb_gemm_set_direct_epilogue")
 
 
+def set_pair_mode(mode):
+    """Test hook: 0 = the cost model picks, 1 = single-CTA tiles only, 2 = CTA-pair (cta_group::2) tiles whenever
+    the shape allows."""
+    _lib.check(_lib.lib().vb_gemm_set_pair_mode(c_int(int(mode))), "vb_gemm_set_pair_mode")
+
+
 def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumulate=False, z=None, deriv=0,
          alpha=1.0, split_k=1, block_n=0):
     """out[M,N] = epilogue(sum_k A(m,k) B(n,k)); see csrc/gemm_tcgen05.cu.
