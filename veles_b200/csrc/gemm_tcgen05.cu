@@ -85,6 +85,21 @@ __device__ __forceinline__ float4 ld_z8(const __nv_bfloat16* p) {
   return *reinterpret_cast<const float4*>(p);
 }
 
+// Tile rasterisation: N-blocks run fastest inside bands of up to 8 N-blocks, so the tiles in
+// flight at any moment share their A row-strips (A is the big operand of the layer GEMMs: it is
+// then fetched from HBM once and hit in L2 by the other N-blocks) while a band's B strips stay
+// L2-resident across the whole sweep over M.
+constexpr int RASTER_BAND = 8;
+__device__ __forceinline__ void decode_tile(int mn, int m_blocks, int n_blocks, int& mb, int& nb) {
+  const int band_tiles = RASTER_BAND * m_blocks;
+  const int band = mn / band_tiles;
+  const int within = mn - band * band_tiles;
+  const int n0 = band * RASTER_BAND;
+  const int w = min(RASTER_BAND, n_blocks - n0);
+  mb = within / w;
+  nb = n0 + (within - mb * w);
+}
+
 // Epilogue math on a 32-column register slab with the activation fixed at compile time.
 template <int ACT>
 __device__ __forceinline__ void apply_act(float (&f)[32]) {
@@ -168,8 +183,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       for (int tile = unit; tile < num_tiles; tile += n_units) {
         const int ks = tile / tiles_mn;
         const int mn = tile - ks * tiles_mn;
-        const int mb = mn % p.m_blocks;
-        const int nb = mn / p.m_blocks;
+        int mb, nb;
+        decode_tile(mn, p.m_blocks, p.n_blocks, mb, nb);
         const int kb0 = ks * kb_per_split;
         const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
         const int m_base = mb * TILE_M + static_cast<int>(cta_rank) * BLOCK_M;   // first A row staged here
@@ -325,8 +340,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     for (int tile = unit; tile < num_tiles; tile += n_units) {
       const int ks = tile / tiles_mn;
       const int mn = tile - ks * tiles_mn;
-      const int mb = mn % p.m_blocks;
-      const int nb = mn / p.m_blocks;
+      int mb, nb;
+      decode_tile(mn, p.m_blocks, p.n_blocks, mb, nb);
       const int kb0 = ks * kb_per_split;
       const bool has_k = kb0 < p.k_blocks;
       const bool add_bias = (p.bias != nullptr) && (ks == 0);
