@@ -38,6 +38,9 @@ def parse():
     p.add_argument("--batch", type=int, default=0, help="per-GPU minibatch (default: model's)")
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--skip-e2e", action="store_true")
+    p.add_argument("--weight-delivery", default="multicast", choices=["multicast", "peer_tma"],
+                   help="N>1: multimem.st broadcast of updated bf16 weights, or GEMMs TMA-loading weight tiles from owners")
+    p.add_argument("--replicate-master", action="store_true", help="N>1: also broadcast the fp32 master weights each step")
     return p.parse_args()
 
 
@@ -80,7 +83,8 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from veles_b200.parallel.dp import DataParallel
-        dp = DataParallel(mode="nccl" if args.impl == "nccl" else "fused")
+        dp = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
+                          shard_master=not args.replicate_master)
 
     from veles_b200.backends import B200Device
     from veles_b200.trainer import Trainer
@@ -141,7 +145,8 @@ def main():
         dp2 = None
         if world > 1:
             from veles_b200.parallel.dp import DataParallel
-            dp2 = DataParallel(mode="nccl" if args.impl == "nccl" else "fused")
+            dp2 = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
+                               shard_master=not args.replicate_master)
         tr = Trainer(args.model, minibatch_size=B, device=device, use_graph=use_graph, streaming=True,
                      data_parallel=dp2)
         shape = cfg["sample_shape"]
@@ -191,6 +196,9 @@ def main():
                        "parallelism": "dp%d" % world if world > 1 else "single",
                        "grad_exchange": ("none" if world == 1 else
                                          ("nccl_allreduce+gd" if args.impl == "nccl" else "fused_multimem_allreduce_gd")),
+                       "weight_delivery": (None if world == 1 or args.impl == "nccl" else args.weight_delivery),
+                       "master_weights": (None if world == 1 or args.impl == "nccl" else
+                                          ("replicated" if args.replicate_master else "sharded, gathered at epoch ends")),
                        "cuda_graph": use_graph,
                        "l2_policy": "inputs larger than L2: every step gathers a new minibatch from the resident "
                                     "dataset and streams activations >> 126 MB",

@@ -19,6 +19,12 @@ def run(model, B, steps, dp, rank, world, device, layers_kwargs=None, use_graph=
     torch.cuda.synchronize()
     if dp is not None:
         dp.check()
+        dp.sync_master()
+        if dp.mode == "fused" and dp.weight_delivery == "peer_tma":
+            for f in tr.wf.forwards:   # non-owned shadow rows are stale by design: rebuild them for the comparison
+                if getattr(f, "peer_weights_", None) is not None:
+                    f.refresh_shadow()
+            torch.cuda.synchronize()
     out = []
     for f in tr.wf.forwards:
         if getattr(f, "HAS_WEIGHTS", False):
@@ -41,12 +47,17 @@ def main():
     B, steps = 32, 6
     kw = {"caffe_init": False, "lr": 0.01} if model == "cifar_convnet" else None
     results = {}
-    for mode in ("fused", "nccl"):
-        for graph in ((True, False) if mode == "fused" else (False,)):
-            dp = DataParallel(mode=mode)
+    for mode in ("fused", "fused_peer_tma", "nccl"):
+        for graph in ((True, False) if mode == "fused" else (False,) if mode == "nccl" else (True,)):
+            if mode == "fused_peer_tma":
+                dp = DataParallel(mode="fused", weight_delivery="peer_tma")
+            else:
+                dp = DataParallel(mode=mode)
             results[(mode, graph)] = run(model, B, steps, dp, rank, world, device, kw, use_graph=graph)
             if rank == 0:
-                print("mode=%s graph=%s multimem=%s world=%d" % (mode, graph, dp.use_multimem, world), flush=True)
+                n_peer = sum(1 for i in dp.unit_info.values() if i.get("peer_shadow")) if mode != "nccl" else 0
+                print("mode=%s graph=%s multimem=%s world=%d peer-TMA layers=%d" % (mode, graph, dp.use_multimem, world, n_peer),
+                      flush=True)
             dist.barrier()
     ok = True
     if rank == 0:

@@ -215,6 +215,36 @@ def test_gemm_cta_pair_layouts(M, N, K_, a_mn, b_mn, block_n, pair_mode):
     assert rel_err(out, 2 * ((a.float().t() if a_mn else a.float()) @ (b.float() if b_mn else b.float().t()))) < 3e-3
 
 
+@pytest.mark.parametrize("b_mn", [False, True])
+@pytest.mark.parametrize("world", [2, 8])
+def test_gemm_row_sharded_weight_operand(b_mn, world, pair_mode):
+    """Peer-TMA weight delivery on one GPU: replica r holds valid data only in the rows rank r owns (NaN elsewhere);
+    the GEMM must pick every weight tile from its owner.  Forward (K-major B) and err_input (MN-major B) forms."""
+    k = K()
+    torch.manual_seed(world)
+    rows, inner = 1024, 320          # weight matrix [rows, inner]; shard = rows / world
+    shard = rows // world
+    w = (torch.randn(rows, inner, device=dev()) * 0.2).bfloat16()
+    reps = []
+    for r in range(world):
+        t = torch.full_like(w, float("nan"))
+        t[r * shard:(r + 1) * shard] = w[r * shard:(r + 1) * shard]
+        reps.append(t)
+    peers = ([t.data_ptr() for t in reps], shard, 1)
+    if not b_mn:      # Y = X W^T
+        x = (torch.randn(300, inner, device=dev()) * 0.2).bfloat16()
+        out = torch.empty(300, rows, device=dev(), dtype=torch.bfloat16)
+        k.gemm(x, reps[1], out, b_peers=peers)
+        ref = x.float() @ w.float().t()
+    else:             # dX = dY W
+        dy = (torch.randn(300, rows, device=dev()) * 0.2).bfloat16()
+        out = torch.empty(300, inner, device=dev(), dtype=torch.bfloat16)
+        k.gemm(dy, reps[1], out, b_mn=True, b_peers=peers)
+        ref = dy.float() @ w.float()
+    assert torch.isfinite(out.float()).all()
+    assert rel_err(out, ref) < 1e-2
+
+
 @pytest.mark.parametrize("case", CONV_CASES)
 def test_implicit_gemm_conv_forward_backward(case, pair_mode):
     """TMA-im2col implicit GEMM (forward, err_input, weight gradient) vs torch conv2d autograd in fp32."""

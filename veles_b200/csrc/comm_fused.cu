@@ -57,6 +57,8 @@ struct FusedParams {
   int* status;               // local: set non-zero on a synchronisation timeout
   float grad_scale;
   long long timeout_cycles;
+  int bcast_master;  // 0: the updated fp32 master slice stays on its owner (gathered on demand at epoch ends)
+  int bcast_shadow;  // 0: the bf16 shadow slice stays on its owner; GEMMs fetch it through peer tensor maps
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -166,7 +168,9 @@ __global__ void __launch_bounds__(512) fused_allreduce_gd_kernel(const FusedPara
         w.z = gd_apply(w.z, g.z, v.z, s, p.grad_scale);
         w.w = gd_apply(w.w, g.w, v.w, s, p.grad_scale);
         *reinterpret_cast<float4*>(p.vel_local + gi) = v;
-        if (MULTIMEM) {
+        if (!p.bcast_master) {
+          *reinterpret_cast<float4*>(p.weights_local + gi) = w;
+        } else if (MULTIMEM) {
           mc_st_f32x4(p.weights_mc + gi, w);
         } else {
           for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = w;
@@ -175,7 +179,9 @@ __global__ void __launch_bounds__(512) fused_allreduce_gd_kernel(const FusedPara
           const uint32_t b0 = pack_bf16x2(w.x, w.y), b1 = pack_bf16x2(w.z, w.w);
           if (flat_shadow) {
             const long long so = s.shadow_offset + i;
-            if (MULTIMEM) {
+            if (!p.bcast_shadow) {
+              *reinterpret_cast<uint2*>(p.shadow_local + so) = make_uint2(b0, b1);
+            } else if (MULTIMEM) {
               mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
             } else {
               for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
@@ -201,7 +207,9 @@ __global__ void __launch_bounds__(512) fused_allreduce_gd_kernel(const FusedPara
         float v = p.vel_local[gi];
         const float w = gd_apply(p.weights_local[gi], g, v, s, p.grad_scale);
         p.vel_local[gi] = v;
-        for (int r = 0; r < p.world; ++r) p.weights_peer[r][gi] = w;
+        if (!p.bcast_master) p.weights_local[gi] = w;
+        else
+          for (int r = 0; r < p.world; ++r) p.weights_peer[r][gi] = w;
         if (s.shadow_offset >= 0) {
           const long long so = s.shadow_offset + (i / s.row_len) * s.row_pitch + (i % s.row_len);
           for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = __float2bfloat16(w);
@@ -237,6 +245,8 @@ using namespace vb;
 //   segs: nseg x {offset, numel, shadow_offset, row_len, row_pitch} as long long[5]
 //   hyper: nseg x {lr, wd, l1_vs_l2, moment} as float[4]
 //   *_peer: world device pointers each
+//   use_multimem: bit 0 = NVLS multimem path; bit 1 = keep the fp32 master slice local (no broadcast);
+//                 bit 2 = keep the bf16 shadow slice local (flat-shadow segments only; peer-TMA weight delivery)
 extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg, const long long* segs,
                                      const float* hyper, float* grads_local, float* grads_mc, float** grads_peer,
                                      float* grads_other_local, float* weights_local, float* weights_mc,
@@ -244,6 +254,8 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
                                      void** shadow_peer, unsigned int* flags_local, unsigned int** flags_peer,
                                      unsigned int* epochs, unsigned int* cta_counter, int* status, float grad_scale,
                                      int n_ctas, int use_multimem, double timeout_s, cudaStream_t stream) {
+  const int local_master = (use_multimem >> 1) & 1, local_shadow = (use_multimem >> 2) & 1;
+  use_multimem &= 1;
   VB_REQUIRE(world >= 2 && world <= MAX_WORLD, "vb_fused_allreduce_gd: world size %d not in [2,%d]", world, MAX_WORLD);
   VB_REQUIRE(nseg >= 1 && nseg <= MAX_SEGS, "vb_fused_allreduce_gd: %d segments (max %d per launch)", nseg, MAX_SEGS);
   VB_REQUIRE(channel >= 0 && channel < 64, "vb_fused_allreduce_gd: channel %d out of range", channel);
@@ -277,6 +289,8 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   }
   p.flags_local = flags_local; p.epochs = epochs; p.cta_counter = cta_counter; p.status = status;
   p.grad_scale = grad_scale;
+  p.bcast_master = !local_master;
+  p.bcast_shadow = !local_shadow;
   p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
   if (n_ctas <= 0) n_ctas = 32;
   if (use_multimem)

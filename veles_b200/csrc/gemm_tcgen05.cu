@@ -49,8 +49,18 @@ struct ConvParams {
   int cg;            // weight-matrix columns per tap
 };
 
+// Row-sharded B operand ("peer-TMA weight delivery"): rank r of a data-parallel group owns rows
+// [r*b_shard_rows, (r+1)*b_shard_rows) of the [N, K] weight matrix (the slice its update kernel
+// writes); every other rank's copy of those rows is stale.  The producer therefore loads each B
+// tile through the tensor map of the OWNER's replica: a peer address over NVLink/NVSwitch, so
+// the all-gather of updated weights rides inside the GEMM's operand pipeline.
+struct PeerMaps {
+  CUtensorMap m[8];
+};
+
 struct GemmParams {
   int M, N, K;
+  int b_shard_rows;  // 0: B is read from tma_b only
   ConvParams cv;
   void* D;          // bf16 or fp32, row-major, leading dimension ldd (elements)
   long long ldd;
@@ -121,7 +131,8 @@ template <int BN, bool A_MN, bool B_MN, bool PAIR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                          const __grid_constant__ CUtensorMap tma_b,
-                         const __grid_constant__ CUtensorMap tma_d, const GemmParams p) {
+                         const __grid_constant__ CUtensorMap tma_d, const __grid_constant__ PeerMaps tma_bp,
+                         const GemmParams p) {
   using L = SmemLayout<BN, PAIR>;
   constexpr int STAGES = L::STAGES;
   constexpr int TILE_M = PAIR ? 2 * BLOCK_M : BLOCK_M;
@@ -222,12 +233,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               for (int c = 0; c < BLOCK_M / 64; ++c)
                 ld2(sa + c * (BLOCK_K * 128), &tma_a, m_base + c * 64, kb * BLOCK_K);
             }
+            // weight rows of this tile: N index for K-major B, K index for MN-major B (dX = dY * W)
+            const CUtensorMap* mb_ptr = &tma_b;
+            if (p.b_shard_rows > 0) mb_ptr = &tma_bp.m[(B_MN ? kb * BLOCK_K : n_base) / p.b_shard_rows];
             if (!B_MN) {
-              ld2(sb, &tma_b, kb * BLOCK_K, n_base);
+              ld2(sb, mb_ptr, kb * BLOCK_K, n_base);
             } else {
 #pragma unroll
               for (int c = 0; c < BN_LOAD / 64; ++c)
-                ld2(sb + c * (BLOCK_K * 128), &tma_b, n_base + c * 64, kb * BLOCK_K);
+                ld2(sb + c * (BLOCK_K * 128), mb_ptr, n_base + c * 64, kb * BLOCK_K);
             }
           } else if (p.cv.mode == 3) {
             // A: dY, MN-major tiled.  B: one im2col box (64 pixels x 64 channels) per 64-column chunk.
@@ -578,6 +592,11 @@ static int make_tmap_2d(CUtensorMap* out, const void* base, long long inner, lon
   return 0;
 }
 
+// Peer tensor maps of the launch being assembled on this host thread (all-zero when B is not
+// sharded): set by vb_gemm_bf16_sharded_b around its call, read by launch_gemm.
+static PeerMaps g_zero_peer_maps;
+static thread_local const PeerMaps* g_peer_maps = &g_zero_peer_maps;
+
 typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                    const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -625,6 +644,7 @@ static int make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int 
 template <int BN, bool A_MN, bool B_MN, bool PAIR>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
                        const GemmParams& p, int grid, cudaStream_t stream) {
+  const PeerMaps& tp = *g_peer_maps;
   using L = SmemLayout<BN, PAIR>;
   auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN, PAIR>;
   static bool attr_set = false;
@@ -646,9 +666,9 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p));
+    VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, tp, p));
   } else {
-    kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, td, p);
+    kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, td, tp, p);
   }
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -678,6 +698,7 @@ extern "C" int vb_gemm_set_direct_epilogue(int on) {
 // (128 + BN rows of 128 B per k-block), so the cost of a candidate is
 //   waves * (k-blocks per split + per-tile overhead) * (128 + BN)
 // and the widest tile wins unless N-tail waste or a ragged last wave says otherwise.
+static int g_pair_mode_override = 0;  // 1: this call may not pair (sharded-B retry)
 static int g_pair_mode = 0;  // 0 = choose by cost, 1 = never pair, 2 = pair whenever the shape allows (tests)
 
 static void choose_config(int M, int N, int k_blocks, bool can_split, bool auto_split, bool b_mn, int* bn_io,
@@ -687,7 +708,7 @@ static void choose_config(int M, int N, int k_blocks, bool can_split, bool auto_
   double best = 1e300;
   int best_bn = 128, best_split = 1, best_pair = 0;
   for (int pair = 0; pair < 2; ++pair) {
-    if (pair && (g_pair_mode == 1 || M <= BLOCK_M)) continue;
+    if (pair && (g_pair_mode == 1 || g_pair_mode_override || M <= BLOCK_M)) continue;
     const int tile_m = pair ? 2 * BLOCK_M : BLOCK_M;
     const int units = pair ? sms / 2 : sms;
     const int m_blocks = ceil_div(M, tile_m);
@@ -767,11 +788,11 @@ extern "C" int vb_gemm_set_pair_mode(int mode) {
   return 0;
 }
 
-extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
-                            int b_mn_major, void* D, long long ldd, int M, int N, int K,
-                            const float* bias, int act, int out_fp32, int accumulate, const void* Z,
-                            long long ldz, int deriv, float alpha, int split_k, int block_n,
-                            cudaStream_t stream) {
+static int gemm_impl(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
+                     int b_mn_major, void* D, long long ldd, int M, int N, int K,
+                     const float* bias, int act, int out_fp32, int accumulate, const void* Z,
+                     long long ldz, int deriv, float alpha, int split_k, int block_n,
+                     const void* const* b_peers, int world, int shard_rows, cudaStream_t stream) {
   VB_REQUIRE(M > 0 && N > 0 && K > 0, "vb_gemm_bf16: empty problem %dx%dx%d", M, N, K);
   VB_REQUIRE(!(accumulate && !out_fp32), "vb_gemm_bf16: accumulate requires fp32 output");
   VB_REQUIRE(split_k >= 0, "vb_gemm_bf16: split_k must be >= 0 (0 = choose automatically)");
@@ -788,8 +809,21 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
   p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.alpha = alpha;
   p.k_blocks = ceil_div(K, BLOCK_K);
   int BN = block_n, pair = 0;
-  choose_config(M, N, p.k_blocks, accumulate && act == 0 && Z == nullptr, auto_split, b_mn_major != 0, &BN, &split_k,
-                &pair);
+  {
+    // a row-sharded K-major B needs every staged B tile inside one owner's shard: narrow the tile until it does
+    const int forced[4] = {block_n, 128, 64, 64};
+    const int split_req = split_k;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+      BN = forced[attempt];
+      split_k = split_req;
+      if (attempt == 3) g_pair_mode_override = 1;
+      choose_config(M, N, p.k_blocks, accumulate && act == 0 && Z == nullptr, auto_split, b_mn_major != 0, &BN,
+                    &split_k, &pair);
+      g_pair_mode_override = 0;
+      if (b_peers == nullptr || b_mn_major || shard_rows % (pair ? BN / 2 : BN) == 0) break;
+      if (block_n != 0 && attempt == 0) break;  // the caller fixed the tile: report the mismatch below
+    }
+  }
   p.m_blocks = ceil_div(M, pair ? 2 * BLOCK_M : BLOCK_M);
   p.n_blocks = ceil_div(N, BN);
   p.split_k = split_k;
@@ -802,7 +836,52 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
   if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BLOCK_K, bn_load);
   else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BLOCK_K);
   if (rc) return rc;
-  return finish_and_launch(p, ta, tb, a_mn_major != 0, b_mn_major != 0, BN, pair, stream);
+  PeerMaps peers;
+  if (b_peers != nullptr) {
+    // every replica has the same shape and pitch; only the base address differs
+    VB_REQUIRE(world >= 1 && world <= 8 && shard_rows > 0, "sharded B: bad world %d / shard_rows %d", world, shard_rows);
+    const int w_rows = b_mn_major ? K : N;   // the weight-matrix row index the shard is cut along
+    VB_REQUIRE(static_cast<long long>(shard_rows) * world >= w_rows, "sharded B: %d ranks x %d rows do not cover %d rows",
+               world, shard_rows, w_rows);
+    VB_REQUIRE(shard_rows % (b_mn_major ? BLOCK_K : bn_load) == 0,
+               "sharded B: shard of %d rows is not a multiple of the %d-row tile", shard_rows,
+               b_mn_major ? BLOCK_K : bn_load);
+    memset(&peers, 0, sizeof(peers));
+    for (int r = 0; r < world; ++r) {
+      if (!b_mn_major) rc = make_tmap_bf16_2d(&peers.m[r], b_peers[r], K, N, ldb, BLOCK_K, bn_load);
+      else rc = make_tmap_bf16_2d(&peers.m[r], b_peers[r], N, K, ldb, 64, BLOCK_K);
+      if (rc) return rc;
+    }
+    p.b_shard_rows = shard_rows;
+    g_peer_maps = &peers;
+  }
+  rc = finish_and_launch(p, ta, tb, a_mn_major != 0, b_mn_major != 0, BN, pair, stream);
+  g_peer_maps = &g_zero_peer_maps;
+  return rc;
+}
+
+extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
+                            int b_mn_major, void* D, long long ldd, int M, int N, int K,
+                            const float* bias, int act, int out_fp32, int accumulate, const void* Z,
+                            long long ldz, int deriv, float alpha, int split_k, int block_n,
+                            cudaStream_t stream) {
+  return gemm_impl(A, lda, a_mn_major, B, ldb, b_mn_major, D, ldd, M, N, K, bias, act, out_fp32, accumulate, Z, ldz,
+                   deriv, alpha, split_k, block_n, nullptr, 0, 0, stream);
+}
+
+// Same product with the B (weight) operand row-sharded over `world` replicas: rows
+// [r*shard_rows, (r+1)*shard_rows) are read from b_peers[r] (device pointers to the same matrix in
+// each rank's symmetric memory; b_peers[own rank] is the local replica).  Fuses the all-gather of
+// freshly updated weight shards into the GEMM's TMA operand loads (see PeerMaps).
+extern "C" int vb_gemm_bf16_sharded_b(const void* A, long long lda, int a_mn_major, const void* const* b_peers,
+                                      int world, int shard_rows, int own_rank, long long ldb, int b_mn_major, void* D,
+                                      long long ldd, int M, int N, int K, const float* bias, int act, int out_fp32,
+                                      int accumulate, const void* Z, long long ldz, int deriv, float alpha,
+                                      int split_k, int block_n, cudaStream_t stream) {
+  VB_REQUIRE(b_peers != nullptr && world >= 1 && world <= 8 && own_rank >= 0 && own_rank < world,
+             "vb_gemm_bf16_sharded_b: bad peer list");
+  return gemm_impl(A, lda, a_mn_major, b_peers[own_rank], ldb, b_mn_major, D, ldd, M, N, K, bias, act, out_fp32,
+                   accumulate, Z, ldz, deriv, alpha, split_k, block_n, b_peers, world, shard_rows, stream);
 }
 
 // ----------------------------------------------------------------------------

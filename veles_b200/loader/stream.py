@@ -27,6 +27,11 @@ class StreamLoader(Loader):
         self.samples_per_epoch = int(kwargs.get("samples_per_epoch", 1 << 30))
         self.mean = kwargs.get("mean", None)
         self.rdisp = kwargs.get("rdisp", None)
+        # regression targets: None (classification), "input" (autoencoder: the normalised sample is the target)
+        # or a shape tuple (targets fed next to the data)
+        self.targets = kwargs.get("targets", None)
+        if self.targets is not None and self.targets != "input":
+            self.targets = tuple(self.targets)
         self.feed_class = TRAIN
 
     def init_unpickled(self):
@@ -51,6 +56,9 @@ class StreamLoader(Loader):
 
     def create_minibatch_data(self):
         self.minibatch_data.reset(numpy.zeros((self._max_minibatch_size,) + self.sample_shape, dtype=numpy.float32))
+        if self.targets is not None:
+            tshape = (int(numpy.prod(self.sample_shape)),) if self.targets == "input" else self.targets
+            self._minibatch_targets.reset(numpy.zeros((self._max_minibatch_size,) + tshape, dtype=numpy.float32))
 
     def fill_minibatch(self):
         pass
@@ -67,6 +75,14 @@ class StreamLoader(Loader):
         dev = self.device_
         self.minibatch_data.dev_dtype = dev.compute_dtype
         self.init_vectors(self.minibatch_data, self.minibatch_labels, self.minibatch_indices)
+        self.staging_targets_ = []
+        if self.targets is not None:
+            self._minibatch_targets.dev_dtype = dev.compute_dtype
+            self.init_vectors(self._minibatch_targets)
+            if self.targets != "input":
+                tsz = int(numpy.prod(self.targets))
+                self.staging_targets_ = [torch.zeros(self._max_minibatch_size, tsz, dtype=torch.float32,
+                                                     device=dev.torch_device) for _ in range(2)]
         tdt = torch.uint8 if self.data_dtype == "uint8" else torch.float32
         n = self._max_minibatch_size
         size = int(numpy.prod(self.sample_shape))
@@ -84,19 +100,21 @@ class StreamLoader(Loader):
             numpy.asarray(self.rdisp, dtype=numpy.float32).reshape(-1), device=dev.torch_device)
 
     # -- feeding -------------------------------------------------------------------------------------------------
-    def feed(self, data, labels=None):
+    def feed(self, data, labels=None, targets=None):
         """Enqueue one minibatch given as torch CPU tensors (ideally pinned) or numpy arrays.
         Returns the number of bytes that will cross PCIe."""
         import torch
         if isinstance(data, numpy.ndarray):
             data = torch.from_numpy(data)
+        if targets is not None and isinstance(targets, numpy.ndarray):
+            targets = torch.from_numpy(targets.astype(numpy.float32, copy=False))
         if labels is not None and isinstance(labels, numpy.ndarray):
             labels = torch.from_numpy(labels.astype(numpy.int32, copy=False))
         count = data.shape[0]
         if count > self._max_minibatch_size:
             raise ValueError("feed(): %d samples exceed max_minibatch_size %d" % (count, self._max_minibatch_size))
         if not self.on_device:
-            self.host_pending_.append((data, labels, count))
+            self.host_pending_.append((data, labels, count, targets))
             return 0
         slot = self.slot_
         self.slot_ ^= 1
@@ -108,6 +126,9 @@ class StreamLoader(Loader):
             if labels is not None:
                 self.staging_labels_[slot][:count].copy_(labels, non_blocking=True)
                 nbytes += labels.numel() * labels.element_size()
+            if targets is not None and self.staging_targets_:
+                self.staging_targets_[slot][:count].copy_(targets.reshape(count, -1), non_blocking=True)
+                nbytes += targets.numel() * targets.element_size()
             self.events_[slot].record(self.copy_stream_)
         self.pending_.append((slot, count))
         return nbytes
@@ -127,13 +148,21 @@ class StreamLoader(Loader):
         kernels.gather_minibatch(self.staging_[slot], self.identity_, 0, count, md.view(md.shape[0], -1),
                                  self.mean_dev_, self.rdisp_dev_, self.staging_labels_[slot],
                                  self.minibatch_labels.devmem, self.minibatch_indices.devmem)
+        if self.targets is not None:
+            mt = self._minibatch_targets.devmem
+            mt2 = mt.view(mt.shape[0], -1)
+            if self.targets == "input":
+                kernels.copy_2d(md.view(md.shape[0], -1), mt2)
+            else:
+                kernels.gather_minibatch(self.staging_targets_[slot], self.identity_, 0, count, mt2)
+            self._minibatch_targets.mark_device_written()
         self.consumed_[slot].record()
         self.samples_served += count
         for a in (self.minibatch_data, self.minibatch_labels, self.minibatch_indices):
             a.mark_device_written()
 
     def _run_host(self):
-        data, labels, count = self.host_pending_.pop(0)
+        data, labels, count, targets = self.host_pending_.pop(0)
         self._minibatch_size_ = count
         self.minibatch_class = self.feed_class
         arr = data.numpy() if hasattr(data, "numpy") else numpy.asarray(data)
@@ -146,6 +175,14 @@ class StreamLoader(Loader):
         self.minibatch_labels.mem[:] = -1
         if labels is not None:
             self.minibatch_labels.mem[:count] = labels.numpy() if hasattr(labels, "numpy") else labels
+        if self.targets is not None:
+            t = self.minibatch_data.mem.reshape(self.minibatch_data.shape[0], -1) if self.targets == "input" else None
+            if t is None:
+                t = numpy.zeros(self._minibatch_targets.shape, dtype=numpy.float32)
+                if targets is not None:
+                    tv = targets.numpy() if hasattr(targets, "numpy") else numpy.asarray(targets)
+                    t[:count] = tv.reshape((count,) + tuple(self._minibatch_targets.shape[1:]))
+            self._minibatch_targets.mem[...] = t.reshape(self._minibatch_targets.shape)
         self.samples_served += count
 
     def _wrap_run(self, fn):

@@ -72,11 +72,13 @@ def set_pair_mode(mode):
 
 
 def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumulate=False, z=None, deriv=0,
-         alpha=1.0, split_k=1, block_n=0):
+         alpha=1.0, split_k=1, block_n=0, b_peers=None):
     """out[M,N] = epilogue(sum_k A(m,k) B(n,k)); see csrc/gemm_tcgen05.cu.
 
     ``a`` is [M,K] (K-major) or [K,M] (``a_mn``); ``b`` is [N,K] or [K,N] (``b_mn``); bf16.
     ``out`` is bf16 or fp32 [M,N].  ``z``/``deriv`` multiply by f'(z) (activation backward).
+    ``b_peers = (pointers, shard_rows, own_rank)``: the weight matrix ``b`` is row-sharded over the replicas at
+    ``pointers`` (one per data-parallel rank, same shape/pitch); every tile is TMA-loaded from its owner.
     """
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     if a_mn:
@@ -91,11 +93,22 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumu
     assert out.shape[0] == M and out.shape[1] == N, "out shape %s != (%d,%d)" % (tuple(out.shape), M, N)
     out_fp32 = 1 if out.dtype == torch.float32 else 0
     L = _lib.lib()
-    rc = L.vb_gemm_bf16(_p(a), c_longlong(_ld(a)), c_int(int(a_mn)), _p(b), c_longlong(_ld(b)), c_int(int(b_mn)),
-                        _p(out), c_longlong(_ld(out)), c_int(M), c_int(N), c_int(K), _p(bias), c_int(act),
-                        c_int(out_fp32), c_int(int(accumulate)), _p(z), c_longlong(_ld(z) if z is not None else 0),
-                        c_int(deriv), c_float(alpha), c_int(split_k), c_int(block_n), _stream())
-    _lib.check(rc, "vb_gemm_bf16")
+    if b_peers is None:
+        rc = L.vb_gemm_bf16(_p(a), c_longlong(_ld(a)), c_int(int(a_mn)), _p(b), c_longlong(_ld(b)), c_int(int(b_mn)),
+                            _p(out), c_longlong(_ld(out)), c_int(M), c_int(N), c_int(K), _p(bias), c_int(act),
+                            c_int(out_fp32), c_int(int(accumulate)), _p(z), c_longlong(_ld(z) if z is not None else 0),
+                            c_int(deriv), c_float(alpha), c_int(split_k), c_int(block_n), _stream())
+        _lib.check(rc, "vb_gemm_bf16")
+    else:
+        ptrs, shard_rows, own = b_peers
+        arr = (c_void_p * len(ptrs))(*[c_void_p(int(q)) for q in ptrs])
+        rc = L.vb_gemm_bf16_sharded_b(_p(a), c_longlong(_ld(a)), c_int(int(a_mn)), arr, c_int(len(ptrs)),
+                                      c_int(int(shard_rows)), c_int(int(own)), c_longlong(_ld(b)), c_int(int(b_mn)),
+                                      _p(out), c_longlong(_ld(out)), c_int(M), c_int(N), c_int(K), _p(bias), c_int(act),
+                                      c_int(out_fp32), c_int(int(accumulate)), _p(z),
+                                      c_longlong(_ld(z) if z is not None else 0), c_int(deriv), c_float(alpha),
+                                      c_int(split_k), c_int(block_n), _stream())
+        _lib.check(rc, "vb_gemm_bf16_sharded_b")
     LAUNCHES[0] += 1
     return out
 

@@ -26,7 +26,8 @@ MAX_WORLD = 8
 
 
 class DataParallel(object):
-    def __init__(self, mode="fused", n_ctas=32, timeout_s=20.0, use_multimem=None):
+    def __init__(self, mode="fused", n_ctas=32, timeout_s=20.0, use_multimem=None, shard_master=True,
+                 weight_delivery="multicast"):
         import torch
         import torch.distributed as dist
         if not dist.is_initialized():
@@ -39,6 +40,16 @@ class DataParallel(object):
         self.n_ctas = n_ctas
         self.timeout_s = timeout_s
         self.use_multimem = use_multimem
+        # shard_master: each rank keeps only ITS slice of the fp32 master weights current (the slice it updates);
+        # the full master is reassembled by sync_master() at class/epoch boundaries, when the host may look.
+        self.shard_master = bool(shard_master)
+        # weight_delivery: how the updated bf16 operand weights reach the other ranks:
+        #   "multicast": multimem.st of every updated slice into all replicas (inside the update kernel);
+        #   "peer_tma":  nothing is sent; forward / err_input GEMMs TMA-load each weight tile from its owner.
+        if weight_delivery not in ("multicast", "peer_tma"):
+            raise ValueError("weight_delivery must be 'multicast' or 'peer_tma'")
+        self.weight_delivery = weight_delivery
+        self.master_stale = False
         self.parity = 0
         self.grad_scale = 1.0      # 1/world when every rank normalised by its LOCAL batch size
         self.units = []            # GD units in registration order -> channel index
@@ -122,6 +133,7 @@ class DataParallel(object):
         fwd = gd.forward
         segs, hyper_keys = [], []
         slab_idx = None
+        peer_shadow = None
         for w, is_bias in ((gd.weights, False), (gd.bias, True)):
             if w is None or not w:
                 continue
@@ -140,11 +152,23 @@ class DataParallel(object):
                 shadow_off, row_len, row_pitch = soff // 2, sh.shape[1], sh.stride(0)
             segs.append([off // 4, w.size, shadow_off, row_len, row_pitch])
             hyper_keys.append("bias" if is_bias else "weights")
+            if (not is_bias and shadow_off >= 0 and self.weight_delivery == "peer_tma" and row_len == row_pitch
+                    and getattr(fwd, "PEER_WEIGHTS_OK", False) and not getattr(fwd, "weights_transposed", False)):
+                n_rows = fwd.weights_bf16_.shape[0]
+                W = self.world_size
+                if n_rows % W == 0 and (n_rows // W) % 64 == 0 and (n_rows // W * row_len) % 4 == 0:
+                    peer_shadow = (sidx, soff, n_rows // W)
         info = {"channel": channel, "slab": slab_idx, "segs": segs, "kinds": hyper_keys,
                 "shadow_slab": getattr(self, "_shadow_slab", 0)}
         info["grads"] = [self._slab_ptrs("grads", slab_idx), self._slab_ptrs("grads1", slab_idx)]
         info["weights"] = self._slab_ptrs("weights", slab_idx)
         info["shadow"] = self._slab_ptrs("weights_bf16", info["shadow_slab"])
+        if peer_shadow is not None:
+            # the update kernel keeps this layer's bf16 shard local; its GEMMs read every tile from the owner
+            sidx, soff, shard_rows = peer_shadow
+            _, _, peers = self._slab_ptrs("weights_bf16", sidx)
+            fwd.peer_weights_ = ([p + soff for p in peers], shard_rows, self.rank)
+            info["peer_shadow"] = True
         info["vel"] = arena.slabs["velocity"][slab_idx][0].data_ptr()
         fl_idx, fl_off = arena.locate(self.flags, "dp_flags")
         fl = self._slab_ptrs("dp_flags", fl_idx)
@@ -221,7 +245,8 @@ class DataParallel(object):
                 c_void_p(s_local), c_void_p(s_mc), arr(s_peers), c_void_p(f_local), arr(f_peers),
                 c_void_p(self.epochs.data_ptr()), c_void_p(self.cta_counter.data_ptr()),
                 c_void_p(self.status.data_ptr()), c_float(self.grad_scale), c_int(self.n_ctas),
-                c_int(1 if self.use_multimem else 0), c_double(self.timeout_s),
+                c_int((1 if self.use_multimem else 0) | (2 if self.shard_master else 0) |
+                      (4 if info.get("peer_shadow") else 0)), c_double(self.timeout_s),
                 c_void_p(self.comm_stream.cuda_stream))
             _lib.check(rc, "vb_fused_allreduce_gd")
             from ..ops import kernels
@@ -229,6 +254,7 @@ class DataParallel(object):
             done = torch.cuda.Event()
             done.record(self.comm_stream)
         self._pending_events.append(done)
+        self.master_stale = self.shard_master
         gd.weights.mark_device_written()
         if gd.bias is not None and gd.bias:
             gd.bias.mark_device_written()
@@ -243,6 +269,49 @@ class DataParallel(object):
         if self.mode == "fused":
             self.parity ^= 1
 
+    def slice_bounds(self, numel, rank):
+        """[lo, hi) of the flat segment that ``rank`` reduces and updates (same arithmetic as the kernel)."""
+        chunk = (numel + self.world_size - 1) // self.world_size
+        chunk = (chunk + 3) & ~3
+        lo = min(numel, chunk * rank)
+        return lo, min(numel, lo + chunk)
+
+    def sync_master(self):
+        """Collective: reassemble the full fp32 master weights on every rank from the owners' slices
+        (P2P copies out of the peers' symmetric slabs).  No-op unless ``shard_master`` left them stale."""
+        import torch
+        if self.mode != "fused" or not self.master_stale:
+            return
+        self.finish_step_events()
+        torch.cuda.synchronize()
+        self._dist.barrier()
+        for gd in self.units:
+            info = self.unit_info[id(gd)]
+            slab = self.arena.slabs["weights"][info["slab"]][0]
+            hdl = self.handles[slab.data_ptr()]
+            delta = slab.data_ptr() - int(hdl.buffer_ptrs[self.rank])
+            local = slab.view(torch.float32)
+            for seg in info["segs"]:
+                off, numel = int(seg[0]), int(seg[1])
+                for r in range(self.world_size):
+                    if r == self.rank:
+                        continue
+                    lo, hi = self.slice_bounds(numel, r)
+                    if hi <= lo:
+                        continue
+                    peer = hdl.get_buffer(r, (hi - lo,), torch.float32, delta // 4 + off + lo)
+                    local[off + lo:off + hi].copy_(peer)
+        torch.cuda.synchronize()
+        self._dist.barrier()
+        self.master_stale = False
+
+    def finish_step_events(self):
+        import torch
+        main = torch.cuda.current_stream()
+        for ev in self._pending_events:
+            main.wait_event(ev)
+        self._pending_events = []
+
     def check(self):
         """Raise if any fused kernel hit its synchronisation timeout (reads one int from the device)."""
         if self.mode == "fused":
@@ -253,6 +322,7 @@ class DataParallel(object):
     # -- epoch-boundary reductions (Decision) -----------------------------------------------------------------------------
     def sum_counters(self, vals, loss):
         import torch
+        self.sync_master()   # class boundary: the host (Decision, Snapshotter, plotters) may read the weights now
         t = torch.tensor(list(map(float, vals)) + [float(loss)], dtype=torch.float64, device="cuda")
         self._dist.all_reduce(t)
         out = t.cpu().numpy()

@@ -70,6 +70,8 @@ class Trainer(object):
         cfg = self.cfg
         loader_cfg = {"minibatch_size": self.minibatch_size, "sample_shape": cfg["sample_shape"],
                       "n_classes": cfg["n_classes"] or 10}
+        if cfg["loss_function"] == "mse":
+            loader_cfg.setdefault("targets", "input")   # the MSE benchmark models are autoencoders
         loader_cfg.update(extra)
         return StandardWorkflow(DummyLauncher(), layers=cfg["layers"](**(layers_kwargs or {})),
                                 loader_name="stream", loader_config=loader_cfg,
@@ -80,8 +82,9 @@ class Trainer(object):
         """One training iteration on the device-resident dataset; nothing is synchronised."""
         self.stepper.run(train=True, serve=True)
 
-    def feed(self, data, labels):
-        self.last_h2d_bytes = self.wf.loader.feed(data, labels)
+    def feed(self, data, labels=None, targets=None):
+        self.last_h2d_bytes = self.wf.loader.feed(data, labels, targets) if targets is not None else \
+            self.wf.loader.feed(data, labels)
         return self.last_h2d_bytes
 
     def step(self, data=None, labels=None, prefetched=False):

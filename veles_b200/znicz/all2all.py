@@ -19,6 +19,7 @@ class All2All(Forward):
     hide_from_registry = False
     MAPPING = {"all2all"}
     ACTIVATION = 0
+    PEER_WEIGHTS_OK = True   # data parallel "peer_tma" delivery: GEMMs may read weight tiles from the owner rank
     __id__ = "58a5eadf-ae1e-498f-bf35-7d93939c4c86"
 
     def __init__(self, workflow, **kwargs):
@@ -113,7 +114,7 @@ class All2All(Forward):
         out = self.output.devmem
         out2 = out if out.dim() == 2 else out.reshape(out.shape[0], -1)
         kernels.gemm(x, self.weights_bf16_, out2, bias=self.bias.devmem if self.include_bias else None,
-                     act=self.ACTIVATION)
+                     act=self.ACTIVATION, b_peers=getattr(self, "peer_weights_", None))
         self.output.mark_device_written()
 
 
@@ -191,7 +192,8 @@ class All2AllSoftmax(All2All):
         from ..ops import kernels
         self.input.unmap()
         x = self.device_input_2d()
-        kernels.gemm(x, self.weights_bf16_, self.logits_, bias=self.bias.devmem if self.include_bias else None)
+        kernels.gemm(x, self.weights_bf16_, self.logits_, bias=self.bias.devmem if self.include_bias else None,
+                     b_peers=getattr(self, "peer_weights_", None))
         if not self.defer_softmax:
             out = self.output.devmem
             kernels.softmax_eval(self.logits_, out if out.dim() == 2 else out.reshape(out.shape[0], -1), None, None,

@@ -136,7 +136,7 @@ class GradientDescent(GradientDescentBase):
             ei = self.err_input.devmem
             ei2 = ei if ei.dim() == 2 else ei.reshape(ei.shape[0], -1)
             kernels.gemm(eo, w_bf16, ei2, b_mn=True, z=x if self.prev_activation else None,
-                         deriv=self.prev_activation)
+                         deriv=self.prev_activation, b_peers=getattr(self.forward, "peer_weights_", None))
             self.err_input.mark_device_written()
         gw_t, gb_t = self.grad_tensors()
         gw = gw_t.view(w_bf16.shape[0], -1)
