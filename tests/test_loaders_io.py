@@ -191,3 +191,18 @@ def test_zeromq_loader_accepts_external_work():
     assert l.minibatch_size == 1 and np.allclose(l.minibatch_data.mem[0], [1, 2, 3])
     l.stop()
     sock.close()
+
+
+def test_stream_loader_autoencoder_targets_train_on_cpu():
+    """StreamLoader with targets="input" (autoencoder): Trainer.step on host-fed minibatches lowers the MSE."""
+    import numpy as np
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.trainer import Trainer
+    tr = Trainer("wide_mlp_ae", minibatch_size=8, device=NumpyDevice(), streaming=True,
+                 layers_kwargs={"width": 32, "depth": 2, "in_features": 4096})
+    x = np.random.RandomState(0).rand(8, 4096).astype(np.float32)
+    first = tr.step(x, None)
+    for _ in range(15):
+        last = tr.step(x, None)
+    assert last < first
+    tr.close()

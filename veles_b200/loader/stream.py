@@ -32,7 +32,12 @@ class StreamLoader(Loader):
         self.targets = kwargs.get("targets", None)
         if self.targets is not None and self.targets != "input":
             self.targets = tuple(self.targets)
+        self._minibatch_targets = Array(shallow_pickle=True)
         self.feed_class = TRAIN
+
+    @property
+    def minibatch_targets(self):
+        return self._minibatch_targets
 
     def init_unpickled(self):
         super(StreamLoader, self).init_unpickled()
