@@ -40,6 +40,7 @@ def parse():
     p.add_argument("--skip-e2e", action="store_true")
     p.add_argument("--weight-delivery", default="multicast", choices=["multicast", "peer_tma"],
                    help="N>1: multimem.st broadcast of updated bf16 weights, or GEMMs TMA-loading weight tiles from owners")
+    p.add_argument("--comm-ctas", type=int, default=64, help="N>1: CTAs of the fused all-reduce+GD kernel")
     p.add_argument("--replicate-master", action="store_true", help="N>1: also broadcast the fp32 master weights each step")
     return p.parse_args()
 
@@ -84,7 +85,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from veles_b200.parallel.dp import DataParallel
         dp = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
-                          shard_master=not args.replicate_master)
+                          shard_master=not args.replicate_master, n_ctas=args.comm_ctas)
 
     from veles_b200.backends import B200Device
     from veles_b200.trainer import Trainer
@@ -146,7 +147,7 @@ def main():
         if world > 1:
             from veles_b200.parallel.dp import DataParallel
             dp2 = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
-                               shard_master=not args.replicate_master)
+                               shard_master=not args.replicate_master, n_ctas=args.comm_ctas)
         tr = Trainer(args.model, minibatch_size=B, device=device, use_graph=use_graph, streaming=True,
                      data_parallel=dp2)
         shape = cfg["sample_shape"]

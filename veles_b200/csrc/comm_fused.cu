@@ -108,7 +108,7 @@ __device__ __forceinline__ bool wait_all(const FusedParams& p, int slot, uint32_
 }
 
 template <bool MULTIMEM>
-__global__ void __launch_bounds__(512) fused_allreduce_gd_kernel(const FusedParams p) {
+__global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedParams p) {
   __shared__ int s_ok;
   __shared__ uint32_t s_epoch;
   const int ready_slot = (p.channel * 2 + 0) * MAX_WORLD;
@@ -147,53 +147,84 @@ __global__ void __launch_bounds__(512) fused_allreduce_gd_kernel(const FusedPara
       const long long hi = min(s.numel, lo + chunk);
       const long long n4 = (hi - lo) >> 2;  // lo is a multiple of 4 and offset is 64-element aligned
       const bool flat_shadow = s.shadow_offset >= 0 && s.row_len == s.row_pitch;
-      for (long long i4 = tid; i4 < n4; i4 += nthreads) {
-        const long long i = lo + (i4 << 2);
-        const long long gi = s.offset + i;
-        float4 g;
-        if (MULTIMEM) {
-          g = mc_ld_reduce_f32x4(p.grads_mc + gi);
-        } else {
-          g = *reinterpret_cast<const float4*>(p.grads_local + gi);
-          for (int r = 0; r < p.world; ++r) {
-            if (r == p.rank) continue;
-            const float4 o = *reinterpret_cast<const float4*>(p.grads_peer[r] + gi);
-            g.x += o.x; g.y += o.y; g.z += o.z; g.w += o.w;
+      // UNROLL independent 16-byte chains per thread: the NVLink round trip of multimem.ld_reduce is
+      // several microseconds, so bandwidth needs many loads in flight per SM, not many SMs.
+      constexpr int UNROLL = 4;
+      for (long long b4 = tid; b4 < n4; b4 += nthreads * UNROLL) {
+        float4 g[UNROLL], w[UNROLL], v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const long long i4 = b4 + u * nthreads;
+          if (i4 < n4) {
+            const long long gi = s.offset + lo + (i4 << 2);
+            if (MULTIMEM) {
+              g[u] = mc_ld_reduce_f32x4(p.grads_mc + gi);
+            } else {
+              g[u] = *reinterpret_cast<const float4*>(p.grads_local + gi);
+            }
           }
         }
-        float4 w = *reinterpret_cast<const float4*>(p.weights_local + gi);
-        float4 v = *reinterpret_cast<const float4*>(p.vel_local + gi);
-        w.x = gd_apply(w.x, g.x, v.x, s, p.grad_scale);
-        w.y = gd_apply(w.y, g.y, v.y, s, p.grad_scale);
-        w.z = gd_apply(w.z, g.z, v.z, s, p.grad_scale);
-        w.w = gd_apply(w.w, g.w, v.w, s, p.grad_scale);
-        *reinterpret_cast<float4*>(p.vel_local + gi) = v;
-        if (!p.bcast_master) {
-          *reinterpret_cast<float4*>(p.weights_local + gi) = w;
-        } else if (MULTIMEM) {
-          mc_st_f32x4(p.weights_mc + gi, w);
-        } else {
-          for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = w;
-        }
-        if (s.shadow_offset >= 0) {
-          const uint32_t b0 = pack_bf16x2(w.x, w.y), b1 = pack_bf16x2(w.z, w.w);
-          if (flat_shadow) {
-            const long long so = s.shadow_offset + i;
-            if (!p.bcast_shadow) {
-              *reinterpret_cast<uint2*>(p.shadow_local + so) = make_uint2(b0, b1);
-            } else if (MULTIMEM) {
-              mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
-            } else {
-              for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
-            }
-          } else {
-            const float wv[4] = {w.x, w.y, w.z, w.w};
+        if (!MULTIMEM) {
+          for (int r = 0; r < p.world; ++r) {
+            if (r == p.rank) continue;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const long long e = i + q;
-              const long long so = s.shadow_offset + (e / s.row_len) * s.row_pitch + (e % s.row_len);
-              const __nv_bfloat16 b = __float2bfloat16(wv[q]);
-              for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = b;  // P2P scalar stores (tiny layers only)
+            for (int u = 0; u < UNROLL; ++u) {
+              const long long i4 = b4 + u * nthreads;
+              if (i4 < n4) {
+                const float4 o = *reinterpret_cast<const float4*>(p.grads_peer[r] + s.offset + lo + (i4 << 2));
+                g[u].x += o.x; g[u].y += o.y; g[u].z += o.z; g[u].w += o.w;
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const long long i4 = b4 + u * nthreads;
+          if (i4 < n4) {
+            const long long gi = s.offset + lo + (i4 << 2);
+            w[u] = *reinterpret_cast<const float4*>(p.weights_local + gi);
+            v[u] = *reinterpret_cast<const float4*>(p.vel_local + gi);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const long long i4 = b4 + u * nthreads;
+          if (i4 >= n4) continue;
+          const long long i = lo + (i4 << 2);
+          const long long gi = s.offset + i;
+          float4 wv4 = w[u], vv = v[u];
+          wv4.x = gd_apply(wv4.x, g[u].x, vv.x, s, p.grad_scale);
+          wv4.y = gd_apply(wv4.y, g[u].y, vv.y, s, p.grad_scale);
+          wv4.z = gd_apply(wv4.z, g[u].z, vv.z, s, p.grad_scale);
+          wv4.w = gd_apply(wv4.w, g[u].w, vv.w, s, p.grad_scale);
+          *reinterpret_cast<float4*>(p.vel_local + gi) = vv;
+          if (!p.bcast_master) {
+            *reinterpret_cast<float4*>(p.weights_local + gi) = wv4;
+          } else if (MULTIMEM) {
+            mc_st_f32x4(p.weights_mc + gi, wv4);
+          } else {
+            for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = wv4;
+          }
+          if (s.shadow_offset >= 0) {
+            const uint32_t b0 = pack_bf16x2(wv4.x, wv4.y), b1 = pack_bf16x2(wv4.z, wv4.w);
+            if (flat_shadow) {
+              const long long so = s.shadow_offset + i;
+              if (!p.bcast_shadow) {
+                *reinterpret_cast<uint2*>(p.shadow_local + so) = make_uint2(b0, b1);
+              } else if (MULTIMEM) {
+                mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
+              } else {
+                for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
+              }
+            } else {
+              const float wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const long long e = i + q;
+                const long long so = s.shadow_offset + (e / s.row_len) * s.row_pitch + (e % s.row_len);
+                const __nv_bfloat16 bq = __float2bfloat16(wv[q]);
+                for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = bq;  // P2P scalar stores (tiny layers only)
+              }
             }
           }
         }
@@ -294,9 +325,9 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
   if (n_ctas <= 0) n_ctas = 32;
   if (use_multimem)
-    fused_allreduce_gd_kernel<true><<<n_ctas, 512, 0, stream>>>(p);
+    fused_allreduce_gd_kernel<true><<<n_ctas, 256, 0, stream>>>(p);
   else
-    fused_allreduce_gd_kernel<false><<<n_ctas, 512, 0, stream>>>(p);
+    fused_allreduce_gd_kernel<false><<<n_ctas, 256, 0, stream>>>(p);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
