@@ -13,6 +13,10 @@ CASES = [
     ("conv_tanh", (3, 15, 15, 16), {"n_kernels": 32, "kx": 3, "ky": 3, "padding": (1, 1, 1, 1), "sliding": (2, 2),
                                     "grouping": 2}),
     ("conv", (2, 27, 27, 3), {"n_kernels": 8, "kx": 11, "ky": 11, "padding": (0, 0, 0, 0), "sliding": (4, 4)}),
+    ("conv_str", (3, 37, 30, 3), {"n_kernels": 16, "kx": 7, "ky": 5, "padding": (0, 0, 0, 0), "sliding": (2, 4)}),
+    ("conv_str", (2, 13, 13, 64), {"n_kernels": 64, "kx": 3, "ky": 3, "padding": (1, 1, 1, 1), "sliding": (1, 1)}),
+    ("conv_tanh", (2, 14, 14, 32), {"n_kernels": 48, "kx": 5, "ky": 5, "padding": (2, 2, 2, 2), "sliding": (1, 1),
+                                    "grouping": 2}),
     ("max_pooling", (4, 15, 15, 32), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
     ("avg_pooling", (4, 16, 16, 32), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
     ("maxabs_pooling", (4, 8, 8, 16), {"kx": 2, "ky": 2, "sliding": (2, 2)}),

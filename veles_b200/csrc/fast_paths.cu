@@ -598,4 +598,104 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
   return 1;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Space-to-depth for strided few-channel convolutions (the 11x11 stride-4 RGB first layer):
+//   xs[b, h', w', (dy*sx + dx)*C + c] = x[b, h'*sy + dy, w'*sx + dx, c]   (zero outside the image)
+// turns the stride-s convolution into a unit-stride one with ceil(k/s)^2 taps over sy*sx*C
+// channels, which the TMA im2col-mode implicit GEMM can walk (channel vectors of >= 16 bytes).
+// One thread = 8 output channels (one 16-byte store).
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void space_to_depth_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ xs, int B, int H, int W,
+                                      int C, int sy, int sx, int H2, int W2) {
+  const int C2 = sy * sx * C;
+  const int V = C2 >> 3;
+  const long long total = static_cast<long long>(B) * H2 * W2 * V;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int v = static_cast<int>(t % V);
+    long long r = t / V;
+    const int w2 = static_cast<int>(r % W2);
+    r /= W2;
+    const int h2 = static_cast<int>(r % H2);
+    const int b = static_cast<int>(r / H2);
+    int q = v << 3;
+    int blk = q / C;
+    int c = q - blk * C;
+    int dy = blk / sx, dx = blk - dy * sx;
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int h = h2 * sy + dy, w = w2 * sx + dx;
+      float val = 0.0f;
+      if (h < H && w < W) val = static_cast<float>(x[((static_cast<long long>(b) * H + h) * W + w) * C + c]);
+      f[e] = val;
+      if (++c == C) {
+        c = 0;
+        if (++dx == sx) {
+          dx = 0;
+          ++dy;
+        }
+      }
+    }
+    *reinterpret_cast<uint4*>(xs + t * 8) = pack8(f);
+  }
+}
+
+// dst[r, j] (+)= src[r, map[j]] (0 where map[j] < 0); optional zeroing of the consumed source row
+// range afterwards is left to the caller.  Used to move weights / weight gradients between the
+// Znicz column order and the space-to-depth column order (tiny matrices).
+template <typename TS, typename TD>
+__global__ void gather_cols_kernel(const TS* __restrict__ src, long long ld_src, TD* __restrict__ dst,
+                                   long long ld_dst, const int* __restrict__ map, int rows, int cols, int accumulate) {
+  const long long total = static_cast<long long>(rows) * cols;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int j = static_cast<int>(t % cols);
+    const long long r = t / cols;
+    const int m = map[j];
+    float v = m >= 0 ? static_cast<float>(src[r * ld_src + m]) : 0.0f;
+    if (accumulate) v += static_cast<float>(dst[r * ld_dst + j]);
+    dst[r * ld_dst + j] = static_cast<TD>(v);
+  }
+}
+
 }  // namespace vb
+
+using namespace vb;
+
+// x: [B,H,W,C] (dtype 0 = f32, 1 = bf16) -> xs: bf16 [B, ceil(H/sy), ceil(W/sx), sy*sx*C]; sy*sx*C % 8 == 0.
+extern "C" int vb_space_to_depth(const void* x, int dtype, void* xs, int B, int H, int W, int C, int sy, int sx,
+                                 cudaStream_t s) {
+  VB_REQUIRE(sy >= 1 && sx >= 1 && C >= 1 && (sy * sx * C) % 8 == 0, "vb_space_to_depth: sy*sx*C must be a multiple of 8");
+  VB_REQUIRE((reinterpret_cast<uintptr_t>(xs) & 15) == 0, "vb_space_to_depth: output must be 16-byte aligned");
+  const int H2 = (H + sy - 1) / sy, W2 = (W + sx - 1) / sx;
+  const long long total = static_cast<long long>(B) * H2 * W2 * ((sy * sx * C) >> 3);
+  if (total == 0) return 0;
+  const int grid = grid_cap2(total, 256);
+  if (dtype == 0)
+    space_to_depth_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(x), static_cast<__nv_bfloat16*>(xs), B, H, W, C, sy, sx, H2, W2);
+  else if (dtype == 1)
+    space_to_depth_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(xs), B, H, W, C, sy, sx, H2, W2);
+  else
+    VB_REQUIRE(false, "vb_space_to_depth: dtype must be f32 (0) or bf16 (1)");
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// dst[r, j] (+)= src[r, map[j]]; dtypes 0 = f32, 1 = bf16 (any pair).
+extern "C" int vb_gather_cols(const void* src, int src_dtype, long long ld_src, void* dst, int dst_dtype,
+                              long long ld_dst, const int* map, int rows, int cols, int accumulate, cudaStream_t s) {
+  const long long total = static_cast<long long>(rows) * cols;
+  if (total == 0) return 0;
+  const int grid = grid_cap2(total, 256);
+#define VB_GC(TS, TD) gather_cols_kernel<TS, TD><<<grid, 256, 0, s>>>(static_cast<const TS*>(src), ld_src, static_cast<TD*>(dst), ld_dst, map, rows, cols, accumulate)
+  if (src_dtype == 0 && dst_dtype == 0) VB_GC(float, float);
+  else if (src_dtype == 0 && dst_dtype == 1) VB_GC(float, __nv_bfloat16);
+  else if (src_dtype == 1 && dst_dtype == 1) VB_GC(__nv_bfloat16, __nv_bfloat16);
+  else if (src_dtype == 1 && dst_dtype == 0) VB_GC(__nv_bfloat16, float);
+  else VB_REQUIRE(false, "vb_gather_cols: unsupported dtype pair %d -> %d", src_dtype, dst_dtype);
+#undef VB_GC
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -164,6 +164,29 @@ def conv_weight_grad(x4, dy2, gw, g, accumulate=True, split_k=0, alpha=1.0, bloc
                       n, g["ky"] * g["kx"] * Cg, accumulate=accumulate, split_k=split_k, alpha=alpha, block_n=block_n)
 
 
+def space_to_depth(x4, xs, sy, sx):
+    """xs[b,h',w',(dy*sx+dx)*C+c] = x4[b,h'*sy+dy,w'*sx+dx,c] (zeros past the image); xs is bf16."""
+    B, H, W, C = x4.shape
+    assert xs.dtype == torch.bfloat16 and tuple(xs.shape) == (B, (H + sy - 1) // sy, (W + sx - 1) // sx, sy * sx * C)
+    assert x4.is_contiguous() and xs.is_contiguous()
+    rc = _lib.lib().vb_space_to_depth(_p(x4), c_int(_dt(x4)), _p(xs), c_int(B), c_int(H), c_int(W), c_int(C),
+                                      c_int(sy), c_int(sx), _stream())
+    _lib.check(rc, "vb_space_to_depth")
+    LAUNCHES[0] += 1
+    return xs
+
+
+def gather_cols(src, dst, col_map, accumulate=False):
+    """dst[r, j] (+)= src[r, col_map[j]] (0 where col_map[j] < 0); col_map is an int32 device tensor."""
+    assert col_map.dtype == torch.int32 and col_map.numel() == dst.shape[1] and src.shape[0] == dst.shape[0]
+    rc = _lib.lib().vb_gather_cols(_p(src), c_int(_dt(src)), c_longlong(_ld(src)), _p(dst), c_int(_dt(dst)),
+                                   c_longlong(_ld(dst)), _p(col_map), c_int(dst.shape[0]), c_int(dst.shape[1]),
+                                   c_int(int(accumulate)), _stream())
+    _lib.check(rc, "vb_gather_cols")
+    LAUNCHES[0] += 1
+    return dst
+
+
 def gather_minibatch(src, indices, start, count, dst, mean=None, rdisp=None, labels=None, mb_labels=None,
                      mb_indices=None):
     """K1/K2/K4: dst[s] = normalise(cast(src[indices[start+s]])) for s<count else 0."""

@@ -155,11 +155,47 @@ class Conv(Forward):
         self.implicit_ = (Cg % 8 == 0 and nkg % 8 == 0 and not getattr(self, "force_explicit_im2col", False))
         self.cols_ld_ = (self.grouping * kk + 7) // 8 * 8
         self.cols_ = None
-        if not self.implicit_:
+        # Strided few-channel layers (11x11/4 on RGB): space-to-depth by the stride makes them unit-stride
+        # convolutions with ceil(k/s)^2 taps over sy*sx*C channels, which the implicit GEMM can walk.
+        sx, sy = self.sliding
+        self.s2d_ = None
+        if (not self.implicit_ and self.grouping == 1 and sx * sy > 1 and not any(self.padding)
+                and (sx * sy * C) % 8 == 0 and self.n_kernels % 8 == 0
+                and not getattr(self, "force_explicit_im2col", False)):
+            self._init_space_to_depth(B, H, W, C, g)
+        if not self.implicit_ and self.s2d_ is None:
             self.ensure_cols()
         self._x_stage4_ = None
         if self.input.devmem.dtype != torch.bfloat16:
             self._x_stage4_ = torch.zeros(self.in_shape4, dtype=torch.bfloat16, device=dev.torch_device)
+
+    def _init_space_to_depth(self, B, H, W, C, g):
+        import torch
+        dev = self.device_.torch_device
+        sx, sy = self.sliding
+        ky2, kx2 = (self.ky + sy - 1) // sy, (self.kx + sx - 1) // sx
+        H2, W2, C2 = (H + sy - 1) // sy, (W + sx - 1) // sx, sy * sx * C
+        # column maps between the Znicz weight layout [(r, s, c)] and the space-to-depth one [(by, bx, dy, dx, c)]
+        to_s2d = numpy.full(ky2 * kx2 * C2, -1, dtype=numpy.int32)
+        from_s2d = numpy.zeros(self.ky * self.kx * C, dtype=numpy.int32)
+        for by in range(ky2):
+            for bx in range(kx2):
+                for dy in range(sy):
+                    for dx in range(sx):
+                        r, s_ = by * sy + dy, bx * sx + dx
+                        if r >= self.ky or s_ >= self.kx:
+                            continue
+                        for c in range(C):
+                            j2 = ((by * kx2 + bx) * sy * sx + dy * sx + dx) * C + c
+                            j = (r * self.kx + s_) * C + c
+                            to_s2d[j2] = j
+                            from_s2d[j] = j2
+        self.s2d_ = dict(
+            geom=dict(OH=g["OH"], OW=g["OW"], ky=ky2, kx=kx2, sy=1, sx=1, pt=0, pl=0, groups=1, H=H2, W=W2),
+            x=torch.zeros(B, H2, W2, C2, dtype=torch.bfloat16, device=dev),
+            w=torch.zeros(self.n_kernels, ky2 * kx2 * C2, dtype=torch.bfloat16, device=dev),
+            gw=torch.zeros(self.n_kernels, ky2 * kx2 * C2, dtype=torch.float32, device=dev),
+            to_s2d=torch.from_numpy(to_s2d).to(dev), from_s2d=torch.from_numpy(from_s2d).to(dev))
 
     def ensure_cols(self):
         """The [B*OH*OW, G*ky*kx*Cg] bf16 column matrix (explicit path and strided err_input scratch)."""
@@ -189,7 +225,12 @@ class Conv(Forward):
         kg = self.weights_bf16_.shape[1]
         out2 = self.output.devmem.view(-1, self.n_kernels)
         bias = self.bias.devmem if self.include_bias else None
-        if self.implicit_:
+        if self.s2d_ is not None:
+            sd = self.s2d_
+            kernels.space_to_depth(x, sd["x"], g["sy"], g["sx"])
+            kernels.gather_cols(self.weights_bf16_, sd["w"], sd["to_s2d"])   # refreshed bf16 weights, s2d order
+            kernels.conv_forward(sd["x"], sd["w"], out2, sd["geom"], bias=bias, act=self.ACTIVATION)
+        elif self.implicit_:
             Cg = x.shape[3] // G
             for gi in range(G):
                 kernels.conv_forward(x[..., gi * Cg:(gi + 1) * Cg] if G > 1 else x,

@@ -120,7 +120,14 @@ class GradientDescentConv(GradientDescentBase):
         g = f.geometry
         x4 = f.device_input4() if f._x_stage4_ is None else f._x_stage4_
         Cg = x4.shape[3] // G
-        if f.implicit_:
+        if f.s2d_ is not None:
+            # the forward pass left the space-to-depth input in place; gradient in s2d column order, then folded
+            # into the Znicz-ordered gradient (and the scratch cleared for the next step)
+            sd = f.s2d_
+            kernels.conv_weight_grad(sd["x"], eo2, sd["gw"], sd["geom"], accumulate=True, split_k=0)
+            kernels.gather_cols(sd["gw"], gw, sd["from_s2d"], accumulate=True)
+            sd["gw"].zero_()
+        elif f.implicit_:
             for gi in range(G):
                 kernels.conv_weight_grad(x4[..., gi * Cg:(gi + 1) * Cg] if G > 1 else x4,
                                          eo2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else eo2,
@@ -151,7 +158,7 @@ class GradientDescentConv(GradientDescentBase):
                                            z=(z2[:, gi * Cg:(gi + 1) * Cg] if G > 1 else z2) if z2 is not None else None,
                                            deriv=self.prev_activation)
             else:
-                cols = f.ensure_cols()
+                cols = f.ensure_cols()   # (also the err_input scratch of strided / space-to-depth layers)
                 for gi in range(G):
                     e = eo2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else eo2
                     kernels.gemm(e, w_bf16[gi * nkg:(gi + 1) * nkg], cols[:, gi * kg:(gi + 1) * kg], b_mn=True)
