@@ -31,7 +31,8 @@ namespace vb {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;  // producer warp, MMA warp, 8 epilogue warps
+constexpr int EPI_WARPS = 8;
 
 // Implicit-GEMM convolution: one operand is fetched by TMA in im2col mode straight from the NHWC
 // activation tensor (no column matrix is ever materialised).  mode:
@@ -84,7 +85,7 @@ struct SmemLayout {
   static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_BYTES = 1024;
-  static constexpr int EPI_BYTES = 4 /*warps*/ * 2 /*buffers*/ * 4096;  // 32 rows x 128 B slabs
+  static constexpr int EPI_BYTES = EPI_WARPS * 4096;  // one 32-row x 128 B slab per epilogue warp
   static constexpr int BUDGET = 227 * 1024 - EPI_BYTES - BAR_BYTES - 1024;
   static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
   static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*align slack*/;
@@ -164,7 +165,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], PAIR ? 8 : 4);  // one arrive per epilogue warp (of both CTAs)
+      mbar_init(&tmem_empty[s], PAIR ? 2 * EPI_WARPS : EPI_WARPS);  // one arrive per epilogue warp (of both CTAs)
     }
     fence_barrier_init();
     fence_proxy_async_smem();
@@ -347,10 +348,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
   } else {
     // ===================== Epilogue (warps 2..5) =====================
-    const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
+    // Two warps per TMEM lane quarter (a warp may only touch lanes 32*(warp%4)..+31): they take
+    // alternate column slabs, so every SM sub-partition has two epilogue warps to interleave and
+    // the dependent tcgen05.ld -> math -> st.shared chain of one hides behind the other.
+    const int quarter = warp & 3;
+    const int ehalf = (warp - 2) >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
-    int ebuf = 0;
     for (int tile = unit; tile < num_tiles; tile += n_units) {
       const int ks = tile / tiles_mn;
       const int mn = tile - ks * tiles_mn;
@@ -370,6 +374,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       for (int c0 = 0; c0 < BN; c0 += 32) {
         const int col0 = nb * BN + c0;
         if (col0 >= p.N) break;  // warp-uniform
+        // slab ownership: 32-column fp32 slabs / 64-column bf16 slab pairs alternate between the two warps
+        if ((((p.out_fp32 && p.tma_store) ? (c0 >> 5) : (c0 >> 6)) & 1) != ehalf) continue;
         int dcol0 = col0;          // first column of this slab in D
         int nvalid = p.N - col0;   // columns of the slab that exist in D
         if (p.cv.mode == 3) {      // virtual (tap, 64-channel block) columns -> weight-matrix columns
@@ -392,12 +398,25 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         }
         float f[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.alpha != 1.0f) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] *= p.alpha;
+        }
         const bool full = nvalid >= 32;
         if (add_bias) {
+          const float* bp = p.bias + dcol0;
+          if (full && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (full || j < nvalid) f[j] += __ldg(p.bias + dcol0 + j);
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp + j));
+              f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (full || j < nvalid) f[j] += __ldg(bp + j);
+          }
         }
         // The activation code is warp-uniform: branch once, keep f[] in registers.
         switch (p.act) {
@@ -437,10 +456,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           // Stage the 32-row slab in 128B-swizzled smem (conflict-free 16-byte writes: the eight
           // lanes of a quarter-warp phase hit eight different chunks), then one TMA store /
           // L2 reduce-add per slab: full-line writes, M/N tails clipped by the tensor map.
-          uint8_t* buf = epi_smem + (quarter * 2 + ebuf) * EPI_BUF_BYTES;
+          uint8_t* buf = epi_smem + (warp - 2) * EPI_BUF_BYTES;
           uint8_t* srow = buf + lane * 128;
           if (p.out_fp32) {
-            if (lane == 0) tma_store_wait_read<1>();
+            if (lane == 0) tma_store_wait_read<0>();  // the previous slab has left this warp's buffer
             __syncwarp();
 #pragma unroll
             for (int q = 0; q < 8; ++q)
@@ -453,11 +472,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               else tma_store_2d(&tma_d, buf, dcol0, row0);
               tma_store_commit();
             }
-            ebuf ^= 1;
           } else {
             const int half = (c0 >> 5) & 1;
             if (half == 0) {
-              if (lane == 0) tma_store_wait_read<1>();
+              if (lane == 0) tma_store_wait_read<0>();
               __syncwarp();
             }
 #pragma unroll
@@ -476,7 +494,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                 tma_store_2d(&tma_d, buf, col0 - half * 32, row0);
                 tma_store_commit();
               }
-              ebuf ^= 1;
             }
           }
         } else if (row_ok) {
