@@ -32,6 +32,37 @@ int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, lo
                  int accumulate, const void* Z, long long ldz, int deriv, float alpha, int split_k, int block_n,
                  cudaStream_t stream);
 
+/* The same product with the weight operand B row-sharded over `world` replicas (one device pointer per rank to the
+ * same [N,K] / [K,N] matrix in symmetric memory): rows [r*shard_rows, (r+1)*shard_rows) are TMA-loaded from
+ * b_peers[r].  Fuses the all-gather of updated weight shards into the GEMM (no counterpart in the reference, whose
+ * master pushed pickled weights over ZeroMQ: veles/server.py:401-430). */
+int vb_gemm_bf16_sharded_b(const void* A, long long lda, int a_mn_major, const void* const* b_peers, int world,
+                           int shard_rows, int own_rank, long long ldb, int b_mn_major, void* D, long long ldd, int M,
+                           int N, int K, const float* bias, int act, int out_fp32, int accumulate, const void* Z,
+                           long long ldz, int deriv, float alpha, int split_k, int block_n, cudaStream_t stream);
+
+/* Implicit-GEMM convolution (Znicz conv / gd_conv, absent from the checkout: SURVEY 2.4): one operand is fetched by
+ * TMA in im2col mode from the NHWC bf16 tensor T (tB x tH x tW pixels, t_pitch elements between pixels, t_ch
+ * channels visible, group offset applied by the caller).  mode 1 forward: D[pixels, N] = act(im2col(T) W^T + bias),
+ * other = W [other_rows, ky*kx*cg]; mode 2 err_input (unit stride): T = dY, D[tB*oH*oW, cg] = convT * f'(Z);
+ * mode 3 weight gradient: other = dY [pixels, M], D[M, ky*kx*cg] fp32 (+)=.  (low_h, low_w) = -padding
+ * (mode 2: -(k-1-padding)); oH x oW = traversal positions per image. */
+int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW, long long t_pitch, int t_ch, int ky, int kx,
+                      int sy, int sx, int low_h, int low_w, int oH, int oW, const void* other, long long ld_other,
+                      int other_rows, int cg, void* D, long long ldd, int M, int N, const float* bias, int act,
+                      int out_fp32, int accumulate, const void* Z, long long ldz, int deriv, float alpha, int split_k,
+                      int block_n, cudaStream_t stream);
+/* x [B,H,W,C] (dtype 0 f32 / 1 bf16) -> bf16 [B, ceil(H/sy), ceil(W/sx), sy*sx*C]: strided few-channel convolutions
+ * become unit-stride ones the implicit GEMM can walk. */
+int vb_space_to_depth(const void* x, int dtype, void* xs, int B, int H, int W, int C, int sy, int sx,
+                      cudaStream_t stream);
+/* dst[r, j] (+)= src[r, map[j]] (0 where map[j] < 0); dtypes 0 f32 / 1 bf16. */
+int vb_gather_cols(const void* src, int src_dtype, long long ld_src, void* dst, int dst_dtype, long long ld_dst,
+                   const int* map, int rows, int cols, int accumulate, cudaStream_t stream);
+/* Test hooks: force the per-thread store epilogue; 0 cost model / 1 single-CTA tiles / 2 CTA-pair tiles. */
+int vb_gemm_set_direct_epilogue(int on);
+int vb_gemm_set_pair_mode(int mode);
+
 /* ---- loader path: cuda/fullbatch_loader.cu:9-61, cuda/mean_disp_normalizer.cu:11-19, cuda/join.jcu:10-35 */
 int vb_gather_minibatch(const void* src, int src_dtype, long long src_ld, const int* indices, int start, int count,
                         int max_rows, int row_size, void* dst, int dst_dtype, long long dst_ld, const float* mean,

@@ -148,7 +148,14 @@ class ConvUnit : public WeightedUnit {
     return Shape{(s[0] + pad_[1] + pad_[3] - ky_) / slide_[1] + 1, (s[1] + pad_[0] + pad_[2] - kx_) / slide_[0] + 1,
                  n_kernels_};
   }
+  // Layers whose per-group channel count allows 16-byte channel vectors run as an implicit GEMM (TMA im2col-mode
+  // operand loads inside vb_conv_gemm_bf16): no column matrix, hence no scratch.
+  bool Implicit(const Shape& in) const {
+    const Shape s = In3(in);
+    return (s[2] / groups_) % 8 == 0 && (n_kernels_ / groups_) % 8 == 0;
+  }
   size_t ScratchBytes(int batch, const Shape& in) const override {
+    if (Implicit(in)) return 0;
     const Shape o = OutputShape(in);
     return static_cast<size_t>(batch) * o[0] * o[1] * ColsPitch(in) * 2;
   }
@@ -159,6 +166,23 @@ class ConvUnit : public WeightedUnit {
   void Execute(const void* in, void* out, void* scratch, int batch, const Shape& ishape, cudaStream_t st) override {
     const Shape s = In3(ishape), o = OutputShape(ishape);
     const long long ld = ColsPitch(ishape);
+    if (Implicit(ishape)) {
+      const int cg = static_cast<int>(s[2] / groups_), nkg_i = static_cast<int>(n_kernels_ / groups_);
+      const int M_i = static_cast<int>(batch * o[0] * o[1]);
+      const int act_i = act_ ? act_ : ACT;
+      for (int g = 0; g < groups_; ++g) {
+        const char* x = static_cast<const char*>(in) + static_cast<size_t>(g) * cg * 2;
+        const char* w = static_cast<const char*>(w_dev_) + static_cast<size_t>(g) * nkg_i * pitch_ * 2;
+        char* d = static_cast<char*>(out) + static_cast<size_t>(g) * nkg_i * 2;
+        const float* b = b_dev_ ? static_cast<const float*>(b_dev_) + g * nkg_i : nullptr;
+        vb_check(vb_conv_gemm_bf16(1, x, batch, static_cast<int>(s[0]), static_cast<int>(s[1]), s[2], cg, ky_, kx_,
+                                   slide_[1], slide_[0], -pad_[1], -pad_[0], static_cast<int>(o[0]),
+                                   static_cast<int>(o[1]), w, pitch_, nkg_i, cg, d, n_kernels_, M_i, nkg_i, b, act_i, 0,
+                                   0, nullptr, 0, 0, 1.0f, 1, 0, st),
+                 "vb_conv_gemm_bf16");
+      }
+      return;
+    }
     vb_check(vb_im2col(in, scratch, batch, static_cast<int>(s[0]), static_cast<int>(s[1]), static_cast<int>(s[2]),
                        static_cast<int>(o[0]), static_cast<int>(o[1]), ky_, kx_, slide_[1], slide_[0], pad_[1], pad_[0],
                        groups_, ld, st), "vb_im2col");
