@@ -97,6 +97,16 @@ int vb_pool_backward(int kind, const void* dy, const int* offs, void* dx, int dt
 int vb_pool_backward_fused(int kind, const void* dy, const int* offs, void* dx, int dtype, int B, int H, int W, int C,
                            int OH, int OW, int ky, int kx, int sy, int sx, const void* z, int deriv,
                            cudaStream_t stream);
+/* Compact argmax records (bf16, C % 8 == 0): one byte per output = window-local index (row*kx + col) instead of the
+ * 4-byte global offset; return 1 if the shape is unsupported (use the int32 entry points), 0 on success.
+ * vb_pool_expand_offsets rebuilds the Znicz-visible int32 input_offset on demand. */
+int vb_pool_forward_local(int kind, const void* x, void* y, int* offs, unsigned char* offs8, int B, int H, int W,
+                          int C, int OH, int OW, int ky, int kx, int sy, int sx, cudaStream_t stream);
+int vb_pool_backward_local(int kind, const void* dy, const unsigned char* offs8, void* dx, int B, int H, int W, int C,
+                           int OH, int OW, int ky, int kx, int sy, int sx, const void* z, int deriv,
+                           cudaStream_t stream);
+int vb_pool_expand_offsets(const unsigned char* offs8, int* offs, int B, int H, int W, int C, int OH, int OW, int ky,
+                           int kx, int sy, int sx, cudaStream_t stream);
 int vb_lrn_backward_fused(const void* x, const void* dy, void* dx, int dtype, long long pixels, int C, int n,
                           float alpha, float beta, float k, int deriv, cudaStream_t stream);
 int vb_lrn_forward(const void* x, void* y, int dtype, long long pixels, int C, int n, float alpha, float beta,

@@ -66,6 +66,9 @@ def _run(tpe, x, kw, device, R, weights=None, prev_activation=0):
     res["output"] = fwd.output.mem.copy()
     gd.err_input.map_read()
     res["err_input"] = gd.err_input.mem.copy()
+    if getattr(fwd, "input_offset", None) is not None and fwd.input_offset:
+        fwd.input_offset.map_read()     # lazily expanded from the 1-byte records on the device path
+        res["offs"] = fwd.input_offset.mem.copy()
     if getattr(fwd, "HAS_WEIGHTS", False):
         gd.gradient_weights.map_read()
         gd.gradient_bias.map_read()
@@ -100,6 +103,8 @@ def test_layer_device_vs_numpy(tpe, shape, kw, prev_act):
         w = (torch.from_numpy(w[0]).bfloat16().float().numpy(), w[1])
     ref = _run(tpe, x, kw, NumpyDevice(), R, weights=w, prev_activation=prev_act)
     dev = _run(tpe, x, kw, B200Device(), R, weights=w, prev_activation=prev_act)
+    if "offs" in ref:
+        assert np.array_equal(ref["offs"], dev["offs"])
     for key in ("output", "err_input", "gw", "gb"):
         if key not in ref:
             continue

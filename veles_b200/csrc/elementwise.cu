@@ -190,7 +190,29 @@ __global__ void dropout_kernel(const T* __restrict__ in, T* __restrict__ out, lo
   uint64_t s0 = st.x, s1 = st.y;
   // interleaved assignment keeps the warp's accesses coalesced:
   // element i is handled by thread (i / 2) % n_states, two per 64-bit draw
-  for (long long base = 2LL * t; base < n; base += 2LL * n_states) {
+  // The generator chain is serial per state but the loads are not: draw UNR numbers, then issue all the
+  // loads of those iterations together so their latencies overlap (same stream -> same mask as the oracle).
+  constexpr int UNR = 4;
+  const long long step = 2LL * n_states;
+  long long base = 2LL * t;
+  for (; base + (UNR - 1) * step + 1 < n; base += UNR * step) {
+    uint64_t r[UNR];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) r[u] = xs128p_next(s0, s1);
+    float a[UNR], b[UNR];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      a[u] = to_f<T>(in[base + u * step]);
+      b[u] = to_f<T>(in[base + u * step + 1]);
+    }
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const uint32_t r0 = static_cast<uint32_t>(r[u]), r1 = static_cast<uint32_t>(r[u] >> 32);
+      out[base + u * step] = from_f<T>(r0 >= threshold ? a[u] * scale : 0.0f);
+      out[base + u * step + 1] = from_f<T>(r1 >= threshold ? b[u] * scale : 0.0f);
+    }
+  }
+  for (; base < n; base += step) {
     const uint64_t r = xs128p_next(s0, s1);
     const uint32_t r0 = static_cast<uint32_t>(r), r1 = static_cast<uint32_t>(r >> 32);
     out[base] = from_f<T>(r0 >= threshold ? to_f<T>(in[base]) * scale : 0.0f);

@@ -196,13 +196,14 @@ __global__ void col2im_vec8_kernel(const __nv_bfloat16* __restrict__ dcols, __nv
 // Pooling, 8 channels per thread (C % 8 == 0), bf16.
 // ---------------------------------------------------------------------------------------------
 __global__ void pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
-                                         int* __restrict__ offs, const FastPoolGeom g) {
-  const int C8 = g.C >> 3;
-  const long long total = static_cast<long long>(g.B) * g.OH * g.OW * C8;
+                                         int* __restrict__ offs, uint8_t* __restrict__ offs8, const FastPoolGeom g) {
+  const unsigned C8 = g.C >> 3;
+  const long long total = static_cast<long long>(g.B) * g.OH * g.OW * C8;   // < 2^31 (checked by the launcher)
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
        t += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c = static_cast<int>(t % C8) << 3;
-    long long r = t / C8;
+    const unsigned tt = static_cast<unsigned>(t);   // 32-bit index arithmetic: 64-bit divisions cost ~100 instructions each
+    const int c = static_cast<int>(tt % C8) << 3;
+    unsigned r = tt / C8;
     const int ow = static_cast<int>(r % g.OW);
     r /= g.OW;
     const int oh = static_cast<int>(r % g.OH);
@@ -212,14 +213,16 @@ __global__ void pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restri
     const long long img = static_cast<long long>(b) * g.H * g.W * g.C + c;
     float best[8], key[8];
     int bo[8];
+    unsigned bl[8];   // window-local argmax (row * kx + col): what the backward pass really needs, 1 byte
     float sum[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      best[q] = 0.0f; key[q] = -INFINITY; sum[q] = 0.0f;
+      best[q] = 0.0f; key[q] = -INFINITY; sum[q] = 0.0f; bl[q] = 0;
       bo[q] = static_cast<int>(img + (static_cast<long long>(h0) * g.W + w0) * g.C) + q;
     }
     for (int h = h0; h < h1; ++h)
       for (int w = w0; w < w1; ++w) {
+        const unsigned local = static_cast<unsigned>((h - h0) * g.kx + (w - w0));
         const long long o = img + (static_cast<long long>(h) * g.W + w) * g.C;
         float f[8];
         unpack8(ldg16(x + o), f);
@@ -233,6 +236,7 @@ __global__ void pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restri
               key[q] = kq;
               best[q] = f[q];
               bo[q] = static_cast<int>(o) + q;
+              bl[q] = local;
             }
           }
         }
@@ -248,18 +252,42 @@ __global__ void pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restri
       *reinterpret_cast<int4*>(offs + oo) = make_int4(bo[0], bo[1], bo[2], bo[3]);
       *reinterpret_cast<int4*>(offs + oo + 4) = make_int4(bo[4], bo[5], bo[6], bo[7]);
     }
+    if (offs8 != nullptr && kind != 2) {
+      *reinterpret_cast<uint2*>(offs8 + oo) =
+          make_uint2(bl[0] | (bl[1] << 8) | (bl[2] << 16) | (bl[3] << 24), bl[4] | (bl[5] << 8) | (bl[6] << 16) | (bl[7] << 24));
+    }
+  }
+}
+
+// int32 global offsets (the Znicz-visible ``input_offset``) from the 1-byte window-local argmax.
+__global__ void pool_expand_offsets_kernel(const uint8_t* __restrict__ offs8, int* __restrict__ offs,
+                                           const FastPoolGeom g) {
+  const long long total = static_cast<long long>(g.B) * g.OH * g.OW * g.C;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const unsigned tt = static_cast<unsigned>(t);
+    const int c = static_cast<int>(tt % g.C);
+    unsigned r = tt / g.C;
+    const int ow = static_cast<int>(r % g.OW);
+    r /= g.OW;
+    const int oh = static_cast<int>(r % g.OH);
+    const int b = static_cast<int>(r / g.OH);
+    const int l = offs8[t];
+    const int ih = oh * g.sy + l / g.kx, iw = ow * g.sx + l % g.kx;
+    offs[t] = ((b * g.H + ih) * g.W + iw) * g.C + c;
   }
 }
 
 __global__ void pool_backward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ dy, const int* __restrict__ offs,
-                                          __nv_bfloat16* __restrict__ dx, const FastPoolGeom g,
-                                          const __nv_bfloat16* __restrict__ z, int deriv) {
-  const int C8 = g.C >> 3;
-  const long long total = static_cast<long long>(g.B) * g.H * g.W * C8;
+                                          const uint8_t* __restrict__ offs8, __nv_bfloat16* __restrict__ dx,
+                                          const FastPoolGeom g, const __nv_bfloat16* __restrict__ z, int deriv) {
+  const unsigned C8 = g.C >> 3;
+  const long long total = static_cast<long long>(g.B) * g.H * g.W * C8;   // < 2^31 (checked by the launcher)
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
        t += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c = static_cast<int>(t % C8) << 3;
-    long long r = t / C8;
+    const unsigned tt = static_cast<unsigned>(t);
+    const int c = static_cast<int>(tt % C8) << 3;
+    unsigned r = tt / C8;
     const int w = static_cast<int>(r % g.W);
     r /= g.W;
     const int h = static_cast<int>(r % g.H);
@@ -278,6 +306,15 @@ __global__ void pool_backward_vec8_kernel(int kind, const __nv_bfloat16* __restr
           const float inv = 1.0f / static_cast<float>(hh * ww);
 #pragma unroll
           for (int q = 0; q < 8; ++q) acc[q] += f[q] * inv;
+        } else if (offs8 != nullptr) {
+          // 8 one-byte window-local argmax indices: this input pixel is position (h - oh*sy, w - ow*sx)
+          const uint2 l8 = __ldg(reinterpret_cast<const uint2*>(offs8 + o));
+          const unsigned mine = static_cast<unsigned>((h - oh * g.sy) * g.kx + (w - ow * g.sx));
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (((l8.x >> (8 * q)) & 0xffu) == mine) acc[q] += f[q];
+            if (((l8.y >> (8 * q)) & 0xffu) == mine) acc[4 + q] += f[4 + q];
+          }
         } else {
           const int4 o0 = __ldg(reinterpret_cast<const int4*>(offs + o));
           const int4 o1 = __ldg(reinterpret_cast<const int4*>(offs + o + 4));
@@ -508,28 +545,42 @@ int fast_col2im(const void* dcols, void* dx, const FastConvGeom& g, const void* 
   return 1;
 }
 
-int fast_pool_forward(int kind, const void* x, void* y, int* offs, const FastPoolGeom& g, cudaStream_t s) {
+int fast_pool_forward(int kind, const void* x, void* y, int* offs, uint8_t* offs8, const FastPoolGeom& g,
+                      cudaStream_t s) {
+  if (static_cast<long long>(g.B) * g.H * g.W * g.C >= 2147483647LL || g.kx * g.ky > 255) return 0;
+  if (offs8 && (reinterpret_cast<uintptr_t>(offs8) & 7)) return 0;
   if (kind > 2 || g.C % 8 || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15) ||
       (offs && (reinterpret_cast<uintptr_t>(offs) & 15)))
     return 0;
   const long long total = static_cast<long long>(g.B) * g.OH * g.OW * (g.C >> 3);
   if (total == 0) return 1;
   pool_forward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(x),
-                                                                 static_cast<__nv_bfloat16*>(y), offs, g);
+                                                                 static_cast<__nv_bfloat16*>(y), offs, offs8, g);
   VB_CHECK_CUDA(cudaGetLastError());
   return 1;
 }
 
-int fast_pool_backward(int kind, const void* dy, const int* offs, void* dx, const FastPoolGeom& g, const void* z,
-                       int deriv, cudaStream_t s) {
+int fast_pool_backward(int kind, const void* dy, const int* offs, const uint8_t* offs8, void* dx,
+                       const FastPoolGeom& g, const void* z, int deriv, cudaStream_t s) {
+  if (static_cast<long long>(g.B) * g.H * g.W * g.C >= 2147483647LL) return 0;
+  if (offs8 && (reinterpret_cast<uintptr_t>(offs8) & 7)) return 0;
   if (g.C % 8 || (reinterpret_cast<uintptr_t>(dy) & 15) || (reinterpret_cast<uintptr_t>(dx) & 15) ||
       (offs && (reinterpret_cast<uintptr_t>(offs) & 15)) || (z && (reinterpret_cast<uintptr_t>(z) & 15)))
     return 0;
   const long long total = static_cast<long long>(g.B) * g.H * g.W * (g.C >> 3);
   if (total == 0) return 1;
-  pool_backward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(dy), offs,
+  pool_backward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(dy), offs, offs8,
                                                                   static_cast<__nv_bfloat16*>(dx), g,
                                                                   static_cast<const __nv_bfloat16*>(z), deriv);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 1;
+}
+
+int fast_pool_expand_offsets(const uint8_t* offs8, int* offs, const FastPoolGeom& g, cudaStream_t s) {
+  const long long total = static_cast<long long>(g.B) * g.OH * g.OW * g.C;
+  if (total == 0) return 1;
+  if (static_cast<long long>(g.B) * g.H * g.W * g.C >= 2147483647LL) return 0;
+  pool_expand_offsets_kernel<<<grid_cap2(total, 256), 256, 0, s>>>(offs8, offs, g);
   VB_CHECK_CUDA(cudaGetLastError());
   return 1;
 }

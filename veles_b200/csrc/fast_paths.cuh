@@ -1,5 +1,6 @@
 // Internal prototypes of the bandwidth-tuned kernel variants (fast_paths.cu).
 #pragma once
+#include <cstdint>
 #include <cuda_runtime.h>
 
 namespace vb {
@@ -15,9 +16,12 @@ struct FastPoolGeom {
 // each returns 1 = launched, 0 = shape not supported (use the generic kernel), <0 = error
 int fast_im2col(const void* x, void* cols, const FastConvGeom& g, cudaStream_t s);
 int fast_col2im(const void* dcols, void* dx, const FastConvGeom& g, const void* z, int deriv, cudaStream_t s);
-int fast_pool_forward(int kind, const void* x, void* y, int* offs, const FastPoolGeom& g, cudaStream_t s);
-int fast_pool_backward(int kind, const void* dy, const int* offs, void* dx, const FastPoolGeom& g, const void* z,
-                       int deriv, cudaStream_t s);
+// offs8 (optional): one byte per output element, the window-local argmax (row * kx + col)
+int fast_pool_forward(int kind, const void* x, void* y, int* offs, uint8_t* offs8, const FastPoolGeom& g,
+                      cudaStream_t s);
+int fast_pool_backward(int kind, const void* dy, const int* offs, const uint8_t* offs8, void* dx,
+                       const FastPoolGeom& g, const void* z, int deriv, cudaStream_t s);
+int fast_pool_expand_offsets(const uint8_t* offs8, int* offs, const FastPoolGeom& g, cudaStream_t s);
 int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, float alpha, float beta, float k,
                      cudaStream_t s);
 int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels, int C, int n, float alpha, float beta,

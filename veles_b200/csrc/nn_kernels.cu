@@ -576,7 +576,7 @@ extern "C" int vb_pool_forward(int kind, const void* x, void* y, int* offs, int 
   VB_REQUIRE(static_cast<long long>(B) * H * W * C < 2147483647LL, "vb_pool_forward: input too large for int offsets");
   if (dtype == D_BF16) {
     FastPoolGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx};
-    const int fr = fast_pool_forward(kind, x, y, offs, fg, s);
+    const int fr = fast_pool_forward(kind, x, y, offs, nullptr, fg, s);
     if (fr != 0) return fr < 0 ? fr : 0;
   }
   if (dtype == D_F32)
@@ -610,7 +610,7 @@ extern "C" int vb_pool_backward_fused(int kind, const void* dy, const int* offs,
   if (total == 0) return 0;
   if (dtype == D_BF16) {
     FastPoolGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx};
-    const int fr = fast_pool_backward(kind, dy, offs, dx, fg, (z && deriv) ? z : nullptr, deriv, s);
+    const int fr = fast_pool_backward(kind, dy, offs, nullptr, dx, fg, (z && deriv) ? z : nullptr, deriv, s);
     if (fr != 0) return fr < 0 ? fr : 0;
   }
   if (dtype == D_F32)
@@ -620,6 +620,36 @@ extern "C" int vb_pool_backward_fused(int kind, const void* dy, const int* offs,
   VB_CHECK_CUDA(cudaGetLastError());
   if (z && deriv) return vb_activation_backward(deriv, dx, nullptr, z, dx, total, dtype, 1.0f, s);
   return 0;
+}
+
+// ---- pooling with compact argmax records (bf16, C % 8 == 0, ky*kx <= 255) ---------------------------------
+// The backward pass only needs to know WHICH element of its window won, so the hot path keeps one byte per
+// output (window-local index) instead of the 4-byte global offset; the Znicz-visible int32 ``input_offset``
+// is expanded from it on demand.  Each returns 1 when the shape is not supported by this path (the caller
+// then uses vb_pool_forward / vb_pool_backward_fused), 0 on success, negative on error.
+extern "C" int vb_pool_forward_local(int kind, const void* x, void* y, int* offs, unsigned char* offs8, int B, int H,
+                                     int W, int C, int OH, int OW, int ky, int kx, int sy, int sx, cudaStream_t s) {
+  VB_REQUIRE(kind >= 0 && kind <= 1 && offs8 != nullptr, "vb_pool_forward_local: max / maxabs pooling with an offs8 buffer");
+  FastPoolGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx};
+  const int fr = fast_pool_forward(kind, x, y, offs, offs8, fg, s);
+  return fr < 0 ? fr : (fr == 1 ? 0 : 1);
+}
+
+extern "C" int vb_pool_backward_local(int kind, const void* dy, const unsigned char* offs8, void* dx, int B, int H,
+                                      int W, int C, int OH, int OW, int ky, int kx, int sy, int sx, const void* z,
+                                      int deriv, cudaStream_t s) {
+  VB_REQUIRE(kind >= 0 && kind <= 1 && offs8 != nullptr, "vb_pool_backward_local: max / maxabs pooling with an offs8 buffer");
+  FastPoolGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx};
+  const int fr = fast_pool_backward(kind, dy, nullptr, offs8, dx, fg, (z && deriv) ? z : nullptr, deriv, s);
+  return fr < 0 ? fr : (fr == 1 ? 0 : 1);
+}
+
+extern "C" int vb_pool_expand_offsets(const unsigned char* offs8, int* offs, int B, int H, int W, int C, int OH,
+                                      int OW, int ky, int kx, int sy, int sx, cudaStream_t s) {
+  FastPoolGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx};
+  const int fr = fast_pool_expand_offsets(offs8, offs, fg, s);
+  VB_REQUIRE(fr != 0, "vb_pool_expand_offsets: tensor too large for int32 offsets");
+  return fr < 0 ? fr : 0;
 }
 
 extern "C" int vb_lrn_forward(const void* x, void* y, int dtype, long long pixels, int C, int n, float alpha,

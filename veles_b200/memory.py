@@ -108,6 +108,15 @@ class Array(Pickleable):
 
     @property
     def devmem(self):
+        # ``lazy_device_`` (optional callable): brings lazily produced device contents up to date before anybody
+        # touches the tensor (e.g. pooling's int32 offsets expanded from its 1-byte argmax records)
+        hook = getattr(self, "lazy_device_", None)
+        if hook is not None:
+            self.lazy_device_ = None
+            try:
+                hook()
+            finally:
+                self.lazy_device_ = hook
         return self.devmem_
 
     @property
@@ -216,6 +225,9 @@ class Array(Pickleable):
         return self.devmem_
 
     def map_read(self):
+        hook = getattr(self, "lazy_device_", None)
+        if hook is not None:
+            hook()
         if self.devmem_ is None or not self.dev_dirty_:
             return
         with self.lock_:

@@ -308,6 +308,44 @@ def pool_backward(kind, dy, offs, dx, ky, kx, sy, sx, z=None, deriv=0):
     return dx
 
 
+def pool_forward_local(kind, x, y, offs, offs8, ky, kx, sy, sx):
+    """Max/maxabs pooling recording the 1-byte window-local argmax (``offs8``); ``offs`` (int32) optional.
+    Returns False when the shape is not supported by this path."""
+    B, H, W, C = x.shape
+    _, OH, OW, _ = y.shape
+    rc = _lib.lib().vb_pool_forward_local(c_int(kind), _p(x), _p(y), _p(offs), _p(offs8), c_int(B), c_int(H), c_int(W),
+                                          c_int(C), c_int(OH), c_int(OW), c_int(ky), c_int(kx), c_int(sy), c_int(sx),
+                                          _stream())
+    if rc == 1:
+        return False
+    _lib.check(rc, "vb_pool_forward_local")
+    LAUNCHES[0] += 1
+    return True
+
+
+def pool_backward_local(kind, dy, offs8, dx, ky, kx, sy, sx, z=None, deriv=0):
+    B, H, W, C = dx.shape
+    _, OH, OW, _ = dy.shape
+    rc = _lib.lib().vb_pool_backward_local(c_int(kind), _p(dy), _p(offs8), _p(dx), c_int(B), c_int(H), c_int(W),
+                                           c_int(C), c_int(OH), c_int(OW), c_int(ky), c_int(kx), c_int(sy), c_int(sx),
+                                           _p(z), c_int(deriv), _stream())
+    if rc == 1:
+        return False
+    _lib.check(rc, "vb_pool_backward_local")
+    LAUNCHES[0] += 1
+    return True
+
+
+def pool_expand_offsets(offs8, offs, in_shape4, ky, kx, sy, sx):
+    B, H, W, C = in_shape4
+    _, OH, OW, _ = offs8.shape
+    rc = _lib.lib().vb_pool_expand_offsets(_p(offs8), _p(offs), c_int(B), c_int(H), c_int(W), c_int(C), c_int(OH),
+                                           c_int(OW), c_int(ky), c_int(kx), c_int(sy), c_int(sx), _stream())
+    _lib.check(rc, "vb_pool_expand_offsets")
+    LAUNCHES[0] += 1
+    return offs
+
+
 def lrn_forward(x, y, n, alpha, beta, k):
     C = x.shape[-1]
     rc = _lib.lib().vb_lrn_forward(_p(x), _p(y), c_int(_dt(x)), c_longlong(x.numel() // C), c_int(C), c_int(n),

@@ -69,6 +69,13 @@ class GDPooling(GDBase):
         dy = eo.reshape(f.out_shape4)
         dx = self.err_input.devmem.reshape(f.in_shape4)
         z = self.input.devmem.reshape(f.in_shape4) if self.prev_activation else None
+        if getattr(f, "offs8_", None) is not None and kernels.pool_backward_local(
+                kernels.POOL_KINDS[f.KIND], dy, f.offs8_, dx, f.ky, f.kx, f.sliding[1], f.sliding[0], z=z,
+                deriv=self.prev_activation):
+            self.err_input.mark_device_written()
+            return
+        if f.KIND != "avg" and hasattr(f, "ensure_input_offset"):
+            f.ensure_input_offset()
         kernels.pool_backward(kernels.POOL_KINDS[f.KIND], dy, f.input_offset.devmem if f.KIND != "avg" else None,
                               dx, f.ky, f.kx, f.sliding[1], f.sliding[0], z=z, deriv=self.prev_activation)
         self.err_input.mark_device_written()

@@ -110,6 +110,26 @@ class Pooling(ForwardBase):
         self.output.initialize(dev)
         if self.KIND != "avg":
             self.input_offset.initialize(dev)
+        # Hot path of max / maxabs pooling: one byte per output (window-local argmax) is all the backward pass
+        # needs; the Znicz-visible int32 ``input_offset`` is written only for units that asked for it
+        # (``need_input_offset``) and otherwise expanded lazily when the host maps it.
+        self.offs8_ = None
+        self.offsets_stale_ = False
+        import torch
+        if (self.KIND in ("max", "maxabs") and self.output.devmem.dtype == torch.bfloat16
+                and self.in_shape4[3] % 8 == 0 and self.kx * self.ky <= 255):
+            self.offs8_ = torch.zeros(self.out_shape4, dtype=torch.uint8, device=dev.torch_device)
+            self.input_offset.lazy_device_ = self.ensure_input_offset
+
+    def ensure_input_offset(self):
+        """Bring the int32 ``input_offset`` up to date on the device (no-op unless the compact path skipped it)."""
+        if getattr(self, "offs8_", None) is None or not self.offsets_stale_:
+            return
+        from ..ops import kernels
+        self.offsets_stale_ = False
+        kernels.pool_expand_offsets(self.offs8_, self.input_offset.devmem_, self.in_shape4, self.ky, self.kx,
+                                    self.sliding[1], self.sliding[0])
+        self.input_offset.mark_device_written()
 
     def b200_run(self):
         import torch
@@ -120,6 +140,17 @@ class Pooling(ForwardBase):
         rnd = None
         if self.KIND.startswith("stochastic"):
             rnd = torch.from_numpy(self._random_u16().view(numpy.int16)).to(x.device)
+        if self.offs8_ is not None:
+            want_int = bool(getattr(self, "need_input_offset", False))
+            if kernels.pool_forward_local(kernels.POOL_KINDS[self.KIND], x, y,
+                                          self.input_offset.devmem_ if want_int else None, self.offs8_,
+                                          self.ky, self.kx, self.sliding[1], self.sliding[0]):
+                self.output.mark_device_written()
+                self.offsets_stale_ = not want_int
+                if want_int:
+                    self.input_offset.mark_device_written()
+                return
+            self.offs8_ = None   # shape not supported by the compact path: use the int32 one from now on
         kernels.pool_forward(kernels.POOL_KINDS[self.KIND], x, y,
                              self.input_offset.devmem if self.KIND != "avg" else None,
                              self.ky, self.kx, self.sliding[1], self.sliding[0], rnd)
