@@ -557,7 +557,7 @@ def test_lrn_vector_paths(C, n):
     k = K()
     torch.manual_seed(C + n)
     B, H, W = 3, 7, 5
-    alpha, beta, kk = 0.3, 0.75, 1.5
+    alpha, beta, kk = 0.3, (0.75 if C != 40 else 0.6), 1.5   # 0.75 takes the rsqrt path, anything else exp2/log2
     x = torch.randn(B, H, W, C, device=dev()).bfloat16()
     y = torch.empty_like(x)
     k.lrn_forward(x, y, n, alpha, beta, kk)

@@ -429,15 +429,36 @@ __device__ __forceinline__ void load24(const __nv_bfloat16* row, int g, int T, f
   for (int q = 0; q < 8; ++q) v[16 + q] = a[q];
 }
 
+// s^-beta.  The AlexNet value beta = 0.75 needs no log/exp: r = rsqrt(s), s^-0.75 = r * sqrt(r), 1/s = r * r.
+__device__ __forceinline__ float lrn_pow_neg(float s, float beta, bool beta34) {
+  if (beta34) {
+    const float r = rsqrtf(s);
+    return r * sqrtf(r);
+  }
+  return __powf(s, -beta);
+}
+__device__ __forceinline__ float lrn_pow_neg_inv(float s, float beta, bool beta34, float& inv_s) {
+  if (beta34) {
+    const float r = rsqrtf(s);
+    inv_s = r * r;
+    return r * sqrtf(r);
+  }
+  inv_s = __fdividef(1.0f, s);
+  return __powf(s, -beta);
+}
+
 template <int HALF>
 __global__ void __launch_bounds__(256)
 lrn_forward_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels, int C,
                         float alpha, float beta, float k) {
   const int T = C >> 3;
   const long long total = pixels * T;
+  const bool beta34 = (beta == 0.75f);
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long px = i / T;
+    // 32-bit arithmetic when it fits (a 64-bit division is ~100 instructions)
+    const long long px = (total <= 0xffffffffLL) ? static_cast<long long>(static_cast<unsigned>(i) / static_cast<unsigned>(T))
+                                                  : i / T;
     const int g = static_cast<int>(i - px * T);
     float xv[24];
     load24(x + px * C, g, T, xv);
@@ -450,7 +471,7 @@ lrn_forward_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __re
       float s = 0.0f;
 #pragma unroll
       for (int d = -HALF; d <= HALF; ++d) s += sq[8 + q + d];
-      out[q] = xv[8 + q] * __powf(k + alpha * s, -beta);
+      out[q] = xv[8 + q] * lrn_pow_neg(k + alpha * s, beta, beta34);
     }
     *reinterpret_cast<uint4*>(y + px * C + g * 8) = pack8(out);
   }
@@ -464,9 +485,12 @@ lrn_backward_vec8_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
   const int T = C >> 3;
   const long long total = pixels * T;
   const float coef = 2.0f * alpha * beta;
+  const bool beta34 = (beta == 0.75f);
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long px = i / T;
+    // 32-bit arithmetic when it fits (a 64-bit division is ~100 instructions)
+    const long long px = (total <= 0xffffffffLL) ? static_cast<long long>(static_cast<unsigned>(i) / static_cast<unsigned>(T))
+                                                  : i / T;
     const int g = static_cast<int>(i - px * T);
     float xv[24], dv[24];
     load24(x + px * C, g, T, xv);
@@ -483,9 +507,10 @@ lrn_backward_vec8_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
 #pragma unroll
       for (int d = -HALF; d <= HALF; ++d) s += sq[j + d];
       s = k + alpha * s;
-      const float pw = __powf(s, -beta);
+      float inv_s;
+      const float pw = lrn_pow_neg_inv(s, beta, beta34, inv_s);
       const float dpw = dv[j] * pw;
-      t[jj] = __fdividef(dpw * xv[j], s);
+      t[jj] = dpw * xv[j] * inv_s;
       if (jj >= HALF && jj < HALF + 8) dp[jj - HALF] = dpw;
     }
     float out[8];
