@@ -877,6 +877,19 @@ static int gemm_impl(const void* A, long long lda, int a_mn_major, const void* B
   return rc;
 }
 
+// What the scheduler would pick for a plain GEMM: tile width, split-K factor, CTA pairing.  Callers use it to
+// decide whether a gradient buffer needs accumulate (split-K) semantics or can be plainly stored.
+extern "C" int vb_gemm_plan(int M, int N, int K, int b_mn_major, int can_split, int block_n, int* bn_out,
+                            int* split_out, int* pair_out) {
+  VB_REQUIRE(M > 0 && N > 0 && K > 0, "vb_gemm_plan: empty problem");
+  int bn = block_n, split = 1, pair = 0;
+  choose_config(M, N, ceil_div(K, BLOCK_K), can_split != 0, true, b_mn_major != 0, &bn, &split, &pair);
+  if (bn_out) *bn_out = bn;
+  if (split_out) *split_out = split;
+  if (pair_out) *pair_out = pair;
+  return 0;
+}
+
 extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
                             int b_mn_major, void* D, long long ldd, int M, int N, int K,
                             const float* bias, int act, int out_fp32, int accumulate, const void* Z,

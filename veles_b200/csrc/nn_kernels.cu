@@ -379,11 +379,34 @@ __global__ void mse_eval_kernel(const T* __restrict__ y, long long ldy, const T*
   if (warp >= batch) return;
   const bool valid = warp < batch_valid;
   float ss = 0.0f;
-  for (int j = lane; j < N; j += 32) {
+  const T* yr = y + static_cast<long long>(warp) * ldy;
+  const T* tr = target + static_cast<long long>(warp) * ldt;
+  T* er = err ? err + static_cast<long long>(warp) * lde : nullptr;
+  int j0 = 0;
+  if (sizeof(T) == 2 && ((ldy | ldt | lde) & 7) == 0 &&
+      ((reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(target) | reinterpret_cast<uintptr_t>(err)) & 15) == 0) {
+    // bf16 rows with 16-byte alignment: 8 elements per lane per step
+    const int nv = N & ~7;
+    for (int j = lane * 8; j < nv; j += 256) {
+      const uint4 a = valid ? __ldg(reinterpret_cast<const uint4*>(yr + j)) : make_uint4(0, 0, 0, 0);
+      const uint4 b = valid ? __ldg(reinterpret_cast<const uint4*>(tr + j)) : make_uint4(0, 0, 0, 0);
+      const uint32_t au[4] = {a.x, a.y, a.z, a.w}, bu[4] = {b.x, b.y, b.z, b.w};
+      uint32_t ou[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float e0 = bf16_lo(au[q]) - bf16_lo(bu[q]), e1 = bf16_hi(au[q]) - bf16_hi(bu[q]);
+        ss += e0 * e0 + e1 * e1;
+        ou[q] = pack_bf16x2(e0 * err_scale, e1 * err_scale);
+      }
+      if (er) *reinterpret_cast<uint4*>(er + j) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+    }
+    j0 = nv;
+  }
+  for (int j = j0 + lane; j < N; j += 32) {
     float e = 0.0f;
-    if (valid) e = ldf<T>(y + static_cast<long long>(warp) * ldy + j) - ldf<T>(target + static_cast<long long>(warp) * ldt + j);
+    if (valid) e = ldf<T>(yr + j) - ldf<T>(tr + j);
     ss += e * e;
-    if (err) stf<T>(err + static_cast<long long>(warp) * lde + j, e * err_scale);
+    if (er) stf<T>(er + j, e * err_scale);
   }
   ss = warp_sum(ss);
   if (lane == 0) {
@@ -438,7 +461,7 @@ __global__ void col_sum_partial_kernel(const T* __restrict__ a, long long lda, i
 }
 
 // bf16 fast path of the first phase: 16-byte loads.  A block is RL row-lanes x VCB 8-column vectors
-// (VCB = min(cols/8, 256), RL = 256 / VCB); each thread accumulates 8 columns over every RL-th row of
+// (VCB = min(cols/8, 32), RL = 256 / VCB); each thread accumulates 8 columns over every RL-th row of
 // the slab, the row-lanes are folded through shared memory.  Same scratch layout as the scalar kernel.
 __global__ void __launch_bounds__(256)
 col_sum_partial_vec8_kernel(const __nv_bfloat16* __restrict__ a, long long lda, int rows, int cols,
@@ -498,7 +521,8 @@ static int launch_col_sum(const void* a, int dtype, long long lda, int rows, int
   if (slabs > 0) {
     if (dtype == D_BF16 && cols % 8 == 0 && lda % 8 == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0) {
       const int vcols = cols / 8;
-      const int vcb = vcols < 256 ? vcols : 256;
+      // 32 vector-columns (512 B of a row) per block: small-batch FC layers then still launch >= one block per SM
+      const int vcb = vcols < 32 ? vcols : 32;
       const int rl = 256 / vcb;
       dim3 grid(ceil_div(vcols, vcb), slabs);
       col_sum_partial_vec8_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch,

@@ -25,6 +25,8 @@ ACT_CODES = {
 POOL_KINDS = {"max": 0, "maxabs": 1, "avg": 2, "stochastic": 3, "stochastic_abs": 4}
 
 LAUNCHES = [0]
+TRACE = None      # set to a list to record (name, start event, end event, tensor bytes, flops, shapes) per call
+_FLOPS = [0.0]
 
 
 def _dt(t):
@@ -71,6 +73,15 @@ def set_pair_mode(mode):
     _lib.check(_lib.lib().vb_gemm_set_pair_mode(c_int(int(mode))), "vb_gemm_set_pair_mode")
 
 
+def gemm_plan(M, N, K, b_mn=False, can_split=True, block_n=0):
+    """(tile width, split-K factor, uses CTA pairs) the GEMM scheduler picks for this problem."""
+    bn, split, pair = c_int(0), c_int(0), c_int(0)
+    _lib.check(_lib.lib().vb_gemm_plan(c_int(M), c_int(N), c_int(K), c_int(int(b_mn)), c_int(int(can_split)),
+                                       c_int(block_n), ctypes.byref(bn), ctypes.byref(split), ctypes.byref(pair)),
+               "vb_gemm_plan")
+    return bn.value, split.value, bool(pair.value)
+
+
 def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumulate=False, z=None, deriv=0,
          alpha=1.0, split_k=1, block_n=0, b_peers=None):
     """out[M,N] = epilogue(sum_k A(m,k) B(n,k)); see csrc/gemm_tcgen05.cu.
@@ -92,6 +103,7 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumu
     assert K == Kb, "inner dimensions differ: %d vs %d" % (K, Kb)
     assert out.shape[0] == M and out.shape[1] == N, "out shape %s != (%d,%d)" % (tuple(out.shape), M, N)
     out_fp32 = 1 if out.dtype == torch.float32 else 0
+    _FLOPS[0] = 2.0 * M * N * K
     L = _lib.lib()
     if b_peers is None:
         rc = L.vb_gemm_bf16(_p(a), c_longlong(_ld(a)), c_int(int(a_mn)), _p(b), c_longlong(_ld(b)), c_int(int(b_mn)),
@@ -118,6 +130,8 @@ def _conv_gemm(mode, t4, ky, kx, sy, sx, low_h, low_w, n_h, n_w, other, other_ro
     assert t4.dtype == torch.bfloat16 and other.dtype == torch.bfloat16 and t4.dim() == 4
     B, H, W, C = t4.shape
     pitch = t4.stride(2)
+    _FLOPS[0] = 2.0 * (B * n_h * n_w if mode != 3 else M) * (N if mode != 3 else B * n_h * n_w) * ky * kx * \
+        (C if mode != 3 else cg)
     assert t4.stride(3) == 1 and t4.stride(1) == W * pitch and t4.stride(0) == H * W * pitch, \
         "im2col-mode tensor must be a (channel-sliced) contiguous NHWC view"
     rc = _lib.lib().vb_conv_gemm_bf16(
@@ -434,3 +448,31 @@ def fill_random(states, out, kind, amp):
     _lib.check(rc, "vb_fill_random")
     LAUNCHES[0] += 1
     return out
+
+
+# -- optional per-call tracing (utils/roofline.py): CUDA events around every wrapper call ---------------------------
+def _traced(fn):
+    import functools
+
+    @functools.wraps(fn)
+    def wrap(*a, **kw):
+        if TRACE is None:
+            return fn(*a, **kw)
+        tensors = [t for t in list(a) + list(kw.values()) if isinstance(t, torch.Tensor)]
+        nbytes = sum(t.numel() * t.element_size() for t in tensors)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        _FLOPS[0] = 0.0
+        e0.record()
+        r = fn(*a, **kw)
+        e1.record()
+        TRACE.append([fn.__name__, e0, e1, nbytes, _FLOPS[0], [tuple(t.shape) for t in tensors[:3]]])
+        return r
+    return wrap
+
+
+for _name in ("gemm", "conv_forward", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
+              "gather_minibatch", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
+              "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
+              "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",
+              "row_sum", "col_sum", "xorshift1024star", "xorshift128plus", "fill_random"):
+    globals()[_name] = _traced(globals()[_name])

@@ -99,6 +99,11 @@ class GradientDescent(GradientDescentBase):
         self.col_scratch_ = torch.empty(kernels.col_sum_scratch_elems(self.err_output.shape[0], n_out),
                                         dtype=torch.float32, device=dev.torch_device)
         self._eo_stage_ = None
+        # dW = dY^T X either accumulates into a zeroed buffer (split-K over the batch) or, when the scheduler would
+        # not split, is plainly stored: the latter skips the read-modify-write at L2 and the re-zeroing pass.
+        n_in = self.input.size // self.input.shape[0]
+        self.dw_store_ = (self.dp_group_ is None and self.apply_gradient and
+                          kernels.gemm_plan(n_out, n_in, self.err_output.shape[0], b_mn=True)[1] == 1)
 
     def device_err_output(self):
         """bf16 2-D err_output with own activation derivative applied (unless fused upstream)."""
@@ -140,7 +145,10 @@ class GradientDescent(GradientDescentBase):
             self.err_input.mark_device_written()
         gw_t, gb_t = self.grad_tensors()
         gw = gw_t.view(w_bf16.shape[0], -1)
-        kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
+        if self.dw_store_:
+            kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=False, split_k=1)
+        else:
+            kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
         if self.bias is not None and self.bias:
             kernels.col_sum(eo, gb_t, self.col_scratch_, accumulate=True)
             self.gradient_bias.mark_device_written()

@@ -503,7 +503,8 @@ class GradientDescentBase(GDBase):
                               self.gradient_weights_with_moment.devmem,
                               self.accumulated_gradient_weights.devmem if self.accumulated_gradient_weights else None,
                               w_shadow, lr=self.learning_rate, wd=self.weights_decay, l1_vs_l2=self.l1_vs_l2,
-                              moment=self.gradient_moment, solver=solver, eps=eps, rho=rho, zero_grad=True)
+                              moment=self.gradient_moment, solver=solver, eps=eps, rho=rho,
+                              zero_grad=not getattr(self, "dw_store_", False))
             if shadow is not None and w_shadow is None:
                 kernels.copy_2d(self.weights.devmem.view(shadow.shape[0], -1), shadow)
             self.weights.mark_device_written()
