@@ -560,11 +560,14 @@ class Unit(Distributable, Verified, metaclass=UnitRegistry):
                     raise RunAfterStopError(self, "%s's run() was called after stop()" % self)
                 self.warning("run() was called after stop()")
                 return None
+            nvtx = _nvtx_push(self)
             t0 = time.perf_counter()
             try:
                 return fn(*args, **kwargs)
             finally:
                 dt = time.perf_counter() - t0
+                if nvtx is not None:
+                    nvtx.range_pop()
                 Unit.timers[self._id] += dt
                 self._run_calls += 1
                 if self._timings:
@@ -578,6 +581,30 @@ class Unit(Distributable, Verified, metaclass=UnitRegistry):
             return fn(*args, **kwargs)
         stop.__wrapped__ = fn
         return stop
+
+
+_NVTX = [None]   # None = not probed; False = disabled; else torch.cuda.nvtx
+
+
+def _nvtx_push(unit):
+    """NVTX range per unit run (``root.common.trace.nvtx = True`` or ``VELES_NVTX=1``): profiler timelines
+    (nsys / ncu --nvtx) then show the dataflow graph's units over the kernels they launch."""
+    mod = _NVTX[0]
+    if mod is None:
+        import os
+        mod = False
+        if get(root.common.trace.nvtx, False) or os.environ.get("VELES_NVTX") == "1":
+            try:
+                import torch
+                if torch.cuda.is_available():
+                    mod = torch.cuda.nvtx
+            except ImportError:
+                pass
+        _NVTX[0] = mod
+    if mod is False:
+        return None
+    mod.range_push("%s:%s" % (type(unit).__name__, unit.name))
+    return mod
 
 
 class TrivialUnit(Unit, TriviallyDistributable):
