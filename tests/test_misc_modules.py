@@ -135,3 +135,12 @@ def test_blas_facade_column_major_sgemm():
     BLAS().sgemm(OP_T, OP_N, m, n, k, 1.0, A2, Bt, 0.0, Ct)
     ref = (A2.float() @ Bt.float().t()).t()
     assert ((Ct - ref).abs().max() / ref.abs().max()).item() < 2e-3
+
+
+@pytest.mark.gpu
+def test_sanitizer_smoke_program_runs():
+    """The program compute-sanitizer is pointed at (scripts/sanitizer_smoke.py) must at least run clean on its own."""
+    import runpy
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    mod = runpy.run_path(os.path.join(root, "scripts", "sanitizer_smoke.py"), run_name="smoke")
+    mod["main"]()
