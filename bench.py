@@ -41,6 +41,8 @@ def parse():
     p.add_argument("--weight-delivery", default="multicast", choices=["multicast", "peer_tma"],
                    help="N>1: multimem.st broadcast of updated bf16 weights, or GEMMs TMA-loading weight tiles from owners")
     p.add_argument("--comm-ctas", type=int, default=64, help="N>1: CTAs of the fused all-reduce+GD kernel")
+    p.add_argument("--gemm-schedule", default="static", choices=["static", "clc"],
+                   help="GEMM tile scheduling: static persistent round-robin, or cluster-launch-control work stealing")
     p.add_argument("--replicate-master", action="store_true", help="N>1: also broadcast the fp32 master weights each step")
     return p.parse_args()
 
@@ -89,6 +91,9 @@ def main():
 
     from veles_b200.backends import B200Device
     from veles_b200.trainer import Trainer
+    if args.gemm_schedule == "clc":
+        from veles_b200.ops import kernels as _k
+        _k.set_dynamic_schedule(True)
     cfg = MODEL_CONFIGS[args.model]
     B = args.batch or cfg["minibatch"]
     device = B200Device(index=local_rank)
@@ -200,6 +205,7 @@ def main():
                        "weight_delivery": (None if world == 1 or args.impl == "nccl" else args.weight_delivery),
                        "master_weights": (None if world == 1 or args.impl == "nccl" else
                                           ("replicated" if args.replicate_master else "sharded, gathered at epoch ends")),
+                       "gemm_schedule": args.gemm_schedule,
                        "cuda_graph": use_graph,
                        "l2_policy": "inputs larger than L2: every step gathers a new minibatch from the resident "
                                     "dataset and streams activations >> 126 MB",

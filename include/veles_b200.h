@@ -62,6 +62,7 @@ int vb_gather_cols(const void* src, int src_dtype, long long ld_src, void* dst, 
 /* Test hooks: force the per-thread store epilogue; 0 cost model / 1 single-CTA tiles / 2 CTA-pair tiles. */
 int vb_gemm_plan(int M, int N, int K, int b_mn_major, int can_split, int block_n, int* bn_out, int* split_out,
                  int* pair_out);
+int vb_gemm_set_dynamic_schedule(int on);
 int vb_gemm_set_direct_epilogue(int on);
 int vb_gemm_set_pair_mode(int mode);
 

@@ -195,10 +195,37 @@ def pair_mode(request):
     k.set_pair_mode(0)
 
 
+@pytest.fixture(params=[False, True], ids=["static_sched", "clc_sched"])
+def dyn_sched(request):
+    """Static persistent round-robin vs cluster-launch-control work stealing."""
+    k = K()
+    k.set_dynamic_schedule(request.param)
+    yield request.param
+    k.set_dynamic_schedule(False)
+
+
+def test_gemm_dynamic_schedule_many_tiles(pair_mode):
+    """Far more tiles than SMs, so almost every tile is obtained through clusterlaunchcontrol.try_cancel."""
+    k = K()
+    k.set_dynamic_schedule(True)
+    try:
+        torch.manual_seed(3)
+        M, N, K_ = 128 * 70, 128 * 9, 192
+        a = (torch.randn(M, K_, device=dev()) * 0.2).bfloat16()
+        b = (torch.randn(N, K_, device=dev()) * 0.2).bfloat16()
+        out = torch.full((M, N), float("nan"), device=dev(), dtype=torch.bfloat16)
+        for _ in range(3):
+            k.gemm(a, b, out, block_n=128)
+        torch.cuda.synchronize()
+        assert rel_err(out, a.float() @ b.float().t()) < 1e-2
+    finally:
+        k.set_dynamic_schedule(False)
+
+
 @pytest.mark.parametrize("M,N,K_", [(1024, 512, 320), (304, 264, 200), (776, 136, 1032), (4104, 96, 128)])
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
 @pytest.mark.parametrize("block_n", [0, 128, 256])
-def test_gemm_cta_pair_layouts(M, N, K_, a_mn, b_mn, block_n, pair_mode):
+def test_gemm_cta_pair_layouts(M, N, K_, a_mn, b_mn, block_n, pair_mode, dyn_sched):
     k = K()
     torch.manual_seed(M + N + K_)
     a = torch.randn((K_, M) if a_mn else (M, K_), device=dev()).bfloat16()
@@ -246,7 +273,7 @@ def test_gemm_row_sharded_weight_operand(b_mn, world, pair_mode):
 
 
 @pytest.mark.parametrize("case", CONV_CASES)
-def test_implicit_gemm_conv_forward_backward(case, pair_mode):
+def test_implicit_gemm_conv_forward_backward(case, pair_mode, dyn_sched):
     """TMA-im2col implicit GEMM (forward, err_input, weight gradient) vs torch conv2d autograd in fp32."""
     k = K()
     B, H, W, C, n, ky, kx, sy, sx, pt, pl, pb, pr, G = case

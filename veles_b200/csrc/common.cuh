@@ -189,6 +189,42 @@ __device__ __forceinline__ void tma_load_im2col_4d_pair(void* smem_dst, const CU
       : "memory");
 }
 
+// ---- cluster launch control (hardware work stealing for persistent kernels) -----------------------
+// A running CTA (cluster) asks the scheduler to CANCEL the launch of a not-yet-started CTA (cluster) of the
+// same grid and takes over its blockIdx; the 16-byte response lands in shared memory through the async proxy
+// and completes 16 bytes on an mbarrier.  `all_ctas`: deliver to every CTA of the cluster (same offsets).
+__device__ __forceinline__ void clc_try_cancel(void* resp16, uint64_t* bar, bool all_ctas) {
+  if (all_ctas)
+    asm volatile(
+        "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128 "
+        "[%0], [%1];" ::"r"(smem_u32(resp16)), "r"(smem_u32(bar))
+        : "memory");
+  else
+    asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];" ::"r"(
+                     smem_u32(resp16)),
+                 "r"(smem_u32(bar))
+                 : "memory");
+}
+// Decodes a response: returns true and the x index of the first CTA of the cancelled cluster, or false when
+// nothing was left to cancel.
+__device__ __forceinline__ bool clc_query(const void* resp16, uint32_t& ctaid_x) {
+  uint32_t x = 0, y, z, ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p1;\n"
+      ".reg .b128 r;\n"
+      "ld.shared.b128 r, [%4];\n"
+      "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, r;\n"
+      "selp.u32 %3, 1, 0, p1;\n"
+      "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%0, %1, %2, _}, r;\n"
+      "}\n"
+      : "+r"(x), "=r"(y), "=r"(z), "=r"(ok)
+      : "r"(smem_u32(resp16))
+      : "memory");
+  ctaid_x = x;
+  return ok != 0;
+}
+
 // ---- tcgen05 ------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

@@ -21,6 +21,7 @@
 // epilogue of tile i overlaps the mainloop of tile i+1.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -74,6 +75,7 @@ struct GemmParams {
   int deriv;          // vb::Act code of the derivative taken through Z
   float alpha;
   int split_k;
+  int dyn_sched;      // 1: tiles are handed out by cluster launch control (grid = one CTA / pair per tile)
   int tma_store;      // 1: epilogue goes through smem + TMA store / reduce-add (tma_d valid)
   int m_blocks, n_blocks, k_blocks;
 };
@@ -151,6 +153,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   uint64_t* tmem_full = empty_bar + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  // dynamic tile scheduler state: two 16-byte response slots + full/empty barriers
+  uint64_t* clc_resp = reinterpret_cast<uint64_t*>(bar_base + 512);   // [2][2]
+  uint64_t* clc_full = clc_resp + 4;
+  uint64_t* clc_empty = clc_full + 2;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -166,6 +172,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
       mbar_init(&tmem_empty[s], PAIR ? 2 * EPI_WARPS : EPI_WARPS);  // one arrive per epilogue warp (of both CTAs)
+      mbar_init(&clc_full[s], 1);
+      // readers of a response: producer thread + MMA warp + epilogue warps (the peer CTA has no MMA loop)
+      mbar_init(&clc_empty[s], PAIR ? 2 * (EPI_WARPS + 1) + 1 : EPI_WARPS + 2);
     }
     fence_barrier_init();
     fence_proxy_async_smem();
@@ -183,16 +192,42 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   const int tiles_mn = p.m_blocks * p.n_blocks;
   const int num_tiles = tiles_mn * p.split_k;
   const int kb_per_split = (p.k_blocks + p.split_k - 1) / p.split_k;
-  // persistent schedule: one work unit = one CTA (or one CTA pair)
+  // persistent schedule: one work unit = one CTA (or one CTA pair).  Static: tiles unit, unit + n_units, ...
+  // Dynamic (p.dyn_sched): the grid has one unit per tile; a running unit starts with its own tile and then
+  // keeps cancelling pending units and taking their tiles (cluster launch control), so SMs held by another
+  // kernel (the data-parallel update kernel on its side stream) merely shrink the pool instead of delaying
+  // the tiles statically assigned to them.
   const int unit = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
   const int n_units = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  // request #it is issued while tile #it is being worked on; its answer names tile #it+1
+  auto sched_request = [&](int it) {   // producer thread of every CTA
+    const int slot = it & 1;
+    if (leader && it >= 2) mbar_wait(&clc_empty[slot], static_cast<uint32_t>(((it >> 1) & 1) ^ 1));
+    mbar_expect_tx(&clc_full[slot], 16);
+    if (leader) clc_try_cancel(clc_resp + 2 * slot, &clc_full[slot], PAIR);
+  };
+  auto sched_next = [&](int tile, int it, bool arrive, bool whole_warp) -> int {
+    if (!p.dyn_sched) return tile + n_units;
+    const int slot = it & 1;
+    mbar_wait(&clc_full[slot], static_cast<uint32_t>((it >> 1) & 1));
+    uint32_t x;
+    const bool ok = clc_query(clc_resp + 2 * slot, x);
+    if (whole_warp) __syncwarp();   // every lane has read the slot before lane 0 releases it
+    if (arrive) {
+      if (PAIR) mbar_arrive_cluster(mapa_u32(&clc_empty[slot], 0));
+      else mbar_arrive(&clc_empty[slot]);
+    }
+    return ok ? static_cast<int>(PAIR ? (x >> 1) : x) : num_tiles;
+  };
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = unit; tile < num_tiles; tile += n_units) {
+      int it = 0;
+      for (int tile = unit; tile < num_tiles; tile = sched_next(tile, it, true, false), ++it) {
+        if (p.dyn_sched) sched_request(it);
         const int ks = tile / tiles_mn;
         const int mn = tile - ks * tiles_mn;
         int mb, nb;
@@ -299,7 +334,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = unit; leader && tile < num_tiles; tile += n_units) {  // only the leader CTA issues MMAs
+    int it = 0;
+    for (int tile = unit; leader && tile < num_tiles; tile = sched_next(tile, it, lane == 0, true), ++it) {  // leader CTA only
       const int ks = tile / tiles_mn;
       const int kb0 = ks * kb_per_split;
       const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
@@ -355,7 +391,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     const int ehalf = (warp - 2) >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = unit; tile < num_tiles; tile += n_units) {
+    int it = 0;
+    for (int tile = unit; tile < num_tiles; tile = sched_next(tile, it, lane == 0, true), ++it) {
       const int ks = tile / tiles_mn;
       const int mn = tile - ks * tiles_mn;
       int mb, nb;
@@ -715,6 +752,10 @@ extern "C" int vb_gemm_set_direct_epilogue(int on) {
 // (128 + BN rows of 128 B per k-block), so the cost of a candidate is
 //   waves * (k-blocks per split + per-tile overhead) * (128 + BN)
 // and the widest tile wins unless N-tail waste or a ragged last wave says otherwise.
+static int g_dyn_sched = [] {
+  const char* e = getenv("VB_GEMM_DYNAMIC");
+  return e ? atoi(e) : 0;
+}();   // 1: tiles handed out by cluster launch control (see the kernel); VB_GEMM_DYNAMIC overrides the default
 static int g_pair_mode_override = 0;  // 1: this call may not pair (sharded-B retry)
 static int g_pair_mode = 0;  // 0 = choose by cost, 1 = never pair, 2 = pair whenever the shape allows (tests)
 
@@ -779,9 +820,11 @@ static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtenso
     if (rc) return rc;
   }
   const long long tiles = static_cast<long long>(p.m_blocks) * p.n_blocks * p.split_k;
+  // dynamic (cluster-launch-control) scheduling: one unit per tile in the grid, running units steal the rest
+  p.dyn_sched = (g_dyn_sched && tiles < (1LL << 30)) ? 1 : 0;
   if (pair) {
     const int units = sms / 2;
-    const int grid = 2 * static_cast<int>(tiles < units ? tiles : units);
+    const int grid = 2 * static_cast<int>((p.dyn_sched || tiles < units) ? tiles : units);
     switch (BN) {
       case 128: return dispatch_major<128, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
       case 192:
@@ -790,13 +833,19 @@ static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtenso
       default: return dispatch_major<256, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
     }
   }
-  const int grid = static_cast<int>(tiles < sms ? tiles : sms);
+  const int grid = static_cast<int>((p.dyn_sched || tiles < sms) ? tiles : sms);
   switch (BN) {
     case 64: return dispatch_major<64, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
     case 128: return dispatch_major<128, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
     case 192: return dispatch_major<192, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
     default: return dispatch_major<256, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
   }
+}
+
+// 1: dynamic (cluster launch control) tile scheduling, 0: static round-robin over a persistent grid.
+extern "C" int vb_gemm_set_dynamic_schedule(int on) {
+  g_dyn_sched = on ? 1 : 0;
+  return 0;
 }
 
 // Test hook: 0 = cost model decides, 1 = single-CTA tiles only, 2 = CTA pairs whenever the shape allows.

@@ -67,6 +67,11 @@ def set_direct_epilogue(on):
     _lib.check(_lib.lib().vb_gemm_set_direct_epilogue(c_int(int(bool(on)))), "vb_gemm_set_direct_epilogue")
 
 
+def set_dynamic_schedule(on):
+    """GEMM tile scheduling: True = cluster-launch-control work stealing, False = static persistent round-robin."""
+    _lib.check(_lib.lib().vb_gemm_set_dynamic_schedule(c_int(int(bool(on)))), "vb_gemm_set_dynamic_schedule")
+
+
 def set_pair_mode(mode):
     """Test hook: 0 = the cost model picks, 1 = single-CTA tiles only, 2 = CTA-pair (cta_group::2) tiles whenever
     the shape allows."""
