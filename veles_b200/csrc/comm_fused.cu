@@ -107,26 +107,26 @@ __device__ __forceinline__ bool wait_all(const FusedParams& p, int slot, uint32_
   return true;
 }
 
+// Footprint: 128 threads, <= 128 registers, NO shared memory - chosen so that one of these CTAs fits on an SM next
+// to a resident tcgen05 GEMM CTA (320 threads x 152 registers, 226 KB of the 228 KB of shared memory): the update
+// kernel then overlaps the backward GEMMs on the same SMs instead of taking SMs away from their persistent grids.
 template <bool MULTIMEM>
-__global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedParams p) {
-  __shared__ int s_ok;
-  __shared__ uint32_t s_epoch;
+__global__ void __launch_bounds__(128) fused_allreduce_gd_kernel(const FusedParams p) {
   const int ready_slot = (p.channel * 2 + 0) * MAX_WORLD;
   const int done_slot = (p.channel * 2 + 1) * MAX_WORLD;
+  // identical in every CTA: epochs[] is bumped by the LAST CTA to finish, i.e. after every CTA has read it here
+  const uint32_t epoch = p.epochs[p.channel] + 1;
+  int my_ok = 1;
   if (threadIdx.x == 0) {
-    const uint32_t epoch = p.epochs[p.channel] + 1;  // identical in every CTA: bumped by the last CTA at exit
-    s_epoch = epoch;
     if (blockIdx.x == 0) {
       // my gradients for this segment are complete (stream order): tell every peer
       __threadfence_system();
       for (int r = 0; r < p.world; ++r)
         if (r != p.rank) st_release_sys(p.flags_peer[r] + ready_slot + p.rank, epoch);
     }
-    s_ok = wait_all(p, ready_slot, epoch) ? 1 : 0;
+    my_ok = wait_all(p, ready_slot, epoch) ? 1 : 0;
   }
-  __syncthreads();
-  const uint32_t epoch = s_epoch;
-  const bool ok = s_ok != 0;
+  const bool ok = __syncthreads_and(my_ok) != 0;   // barrier + predicate broadcast without shared memory
 
   if (ok) {
     const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
@@ -325,9 +325,9 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
   if (n_ctas <= 0) n_ctas = 32;
   if (use_multimem)
-    fused_allreduce_gd_kernel<true><<<n_ctas, 256, 0, stream>>>(p);
+    fused_allreduce_gd_kernel<true><<<n_ctas, 128, 0, stream>>>(p);
   else
-    fused_allreduce_gd_kernel<false><<<n_ctas, 256, 0, stream>>>(p);
+    fused_allreduce_gd_kernel<false><<<n_ctas, 128, 0, stream>>>(p);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -26,7 +26,7 @@ MAX_WORLD = 8
 
 
 class DataParallel(object):
-    def __init__(self, mode="fused", n_ctas=64, timeout_s=20.0, use_multimem=None, shard_master=True,
+    def __init__(self, mode="fused", n_ctas=96, timeout_s=20.0, use_multimem=None, shard_master=True,
                  weight_delivery="multicast"):
         import torch
         import torch.distributed as dist
@@ -160,6 +160,10 @@ class DataParallel(object):
                     peer_shadow = (sidx, soff, n_rows // W)
         info = {"channel": channel, "slab": slab_idx, "segs": segs, "kinds": hyper_keys,
                 "shadow_slab": getattr(self, "_shadow_slab", 0)}
+        # CTAs of the update kernel scale with the layer: every CTA takes an SM's worth of registers away from the
+        # overlapped GEMMs for as long as it runs, and small layers are latency-, not bandwidth-bound
+        numel = sum(int(sg[1]) for sg in segs)
+        info["n_ctas"] = int(max(8, min(self.n_ctas, (numel + 131071) // 131072)))
         info["grads"] = [self._slab_ptrs("grads", slab_idx), self._slab_ptrs("grads1", slab_idx)]
         info["weights"] = self._slab_ptrs("weights", slab_idx)
         info["shadow"] = self._slab_ptrs("weights_bf16", info["shadow_slab"])
@@ -244,7 +248,7 @@ class DataParallel(object):
                 c_void_p(w_local), c_void_p(w_mc), arr(w_peers), c_void_p(info["vel"]),
                 c_void_p(s_local), c_void_p(s_mc), arr(s_peers), c_void_p(f_local), arr(f_peers),
                 c_void_p(self.epochs.data_ptr()), c_void_p(self.cta_counter.data_ptr()),
-                c_void_p(self.status.data_ptr()), c_float(self.grad_scale), c_int(self.n_ctas),
+                c_void_p(self.status.data_ptr()), c_float(self.grad_scale), c_int(info["n_ctas"]),
                 c_int((1 if self.use_multimem else 0) | (2 if self.shard_master else 0) |
                       (4 if info.get("peer_shadow") else 0)), c_double(self.timeout_s),
                 c_void_p(self.comm_stream.cuda_stream))
