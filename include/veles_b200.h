@@ -32,6 +32,12 @@ int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, lo
                  int accumulate, const void* Z, long long ldz, int deriv, float alpha, int split_k, int block_n,
                  cudaStream_t stream);
 
+/* fp32 operands multiplied as TF32 (tcgen05.mma.kind::tf32), fp32 accumulate: the "float" precision mode
+ * (precision_type of veles/config.py:236-241).  A, B and Z are float; leading dimensions multiples of 4. */
+int vb_gemm_tf32(const float* A, long long lda, int a_mn_major, const float* B, long long ldb, int b_mn_major, void* D,
+                 long long ldd, int M, int N, int K, const float* bias, int act, int out_fp32, int accumulate,
+                 const float* Z, long long ldz, int deriv, float alpha, int split_k, int block_n, cudaStream_t stream);
+
 /* The same product with the weight operand B row-sharded over `world` replicas (one device pointer per rank to the
  * same [N,K] / [K,N] matrix in symmetric memory): rows [r*shard_rows, (r+1)*shard_rows) are TMA-loaded from
  * b_peers[r].  Fuses the all-gather of updated weight shards into the GEMM (no counterpart in the reference, whose

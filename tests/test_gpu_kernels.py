@@ -195,6 +195,37 @@ def pair_mode(request):
     k.set_pair_mode(0)
 
 
+@pytest.mark.parametrize("M,N,K_", [(256, 512, 384), (300, 136, 100), (1028, 64, 36), (640, 1000, 4096)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+def test_gemm_tf32_layouts(M, N, K_, a_mn, b_mn, pair_mode):
+    """fp32 operands through tcgen05 kind::tf32 vs an fp64 reference: ~1e-3 (10-bit mantissa products), far tighter than bf16."""
+    k = K()
+    torch.manual_seed(M + N)
+    a = torch.randn((K_, M) if a_mn else (M, K_), device=dev()) * 0.2
+    b = torch.randn((K_, N) if b_mn else (N, K_), device=dev()) * 0.2
+    bias = torch.randn(N, device=dev())
+    A = a.double().t() if a_mn else a.double()
+    B = b.double() if b_mn else b.double().t()
+    ref = torch.sigmoid(A @ B + bias.double())
+    big = torch.full((M + 8, N + 8), float("nan"), device=dev())
+    k.gemm_tf32(a, b, big[:M, :N], a_mn=a_mn, b_mn=b_mn, bias=bias, act=2)
+    assert rel_err(big[:M, :N], ref) < 3e-3
+    assert torch.isnan(big[M:]).all() and torch.isnan(big[:, N:]).all()
+    out = torch.zeros(M, N, device=dev())
+    k.gemm_tf32(a, b, out, a_mn=a_mn, b_mn=b_mn, accumulate=True, split_k=0)
+    z = torch.rand(M, N, device=dev())
+    out2 = torch.empty(M, N, device=dev())
+    k.gemm_tf32(a, b, out2, a_mn=a_mn, b_mn=b_mn, z=z, deriv=2)
+    lin = A @ B
+    assert rel_err(out, lin) < 3e-3
+    assert rel_err(out2, lin * (z * (1 - z)).double()) < 3e-3
+    # and it IS tighter than the bf16 path on the same data
+    if not a_mn and not b_mn and K_ % 8 == 0:
+        o16 = torch.empty(M, N, device=dev())
+        k.gemm(a.bfloat16(), b.bfloat16(), o16)
+        assert rel_err(out, lin) < rel_err(o16, lin)
+
+
 @pytest.fixture(params=[False, True], ids=["static_sched", "clc_sched"])
 def dyn_sched(request):
     """Static persistent round-robin vs cluster-launch-control work stealing."""

@@ -81,3 +81,29 @@ def test_first_iteration_gradients_match_oracle():
         a, b = res[0][k], res[1][k]
         denom = np.abs(a).max() + 1e-9
         assert np.abs(a - b).max() / denom < 0.12, k  # four bf16 layers deep
+
+
+def test_float_precision_mode_runs_tf32_gemms_and_tracks_the_oracle_closely():
+    """root.common.engine.precision_type = "float": fp32 activations + tcgen05 kind::tf32 GEMMs.  The weight
+    trajectory must follow the numpy (fp32) oracle markedly closer than the default bf16 mode does."""
+    from veles_b200.backends import NumpyDevice, B200Device
+    from veles_b200.config import root
+    l0, ref = _build(NumpyDevice(), MLP, CFG, epochs=2)
+    ref.run()
+    ref.forwards[0].weights.map_read()
+    w_ref = ref.forwards[0].weights.mem.copy()
+    errs = {}
+    for mode in ("float", "bf16"):
+        root.common.engine.precision_type = mode
+        try:
+            l1, wf = _build(B200Device(), MLP, CFG, epochs=2)
+            assert bool(getattr(wf.forwards[0], "tf32_", False)) == (mode == "float")
+            wf.run()
+            wf.forwards[0].weights.map_read()
+            errs[mode] = float(np.abs(wf.forwards[0].weights.mem - w_ref).max())
+            assert wf.decision.epoch_metrics_history[-1]["n_err_pt"][1] <= 2.0
+            l1.stop()
+        finally:
+            root.common.engine.precision_type = "bf16"
+    assert errs["float"] < 0.02 and errs["float"] < errs["bf16"], errs
+    l0.stop()

@@ -73,6 +73,7 @@ struct GemmParams {
   const __nv_bfloat16* Z;  // optional [M,N] saved activation output: D *= f'(Z)
   long long ldz;
   int deriv;          // vb::Act code of the derivative taken through Z
+  int z_fp32;         // 1: Z is float (TF32 mode), 0: bf16
   float alpha;
   int split_k;
   int dyn_sched;      // 1: tiles are handed out by cluster launch control (grid = one CTA / pair per tile)
@@ -130,7 +131,10 @@ __device__ __forceinline__ void apply_deriv(float (&f)[32], const float (&y)[32]
 // [r*BN/2, (r+1)*BN/2) of the tile, so every SM ingests 128 + BN/2 operand rows per k-block
 // instead of 128 + BN; the leader's MMA reads both halves (own smem + the peer's over the pair's
 // shared-memory path) and each CTA receives its 128 accumulator rows in its own TMEM.
-template <int BN, bool A_MN, bool B_MN, bool PAIR>
+// TF32 = true: fp32 operands in global memory, `kind::tf32` MMAs (10-bit mantissa products, fp32 accumulate) -
+// the "float" precision mode.  A 128-byte swizzle row then holds 32 elements, so a k-block is 32 elements deep and
+// an MN-major chunk 32 elements wide; stage sizes, the four MMAs per k-block and everything downstream are unchanged.
+template <int BN, bool A_MN, bool B_MN, bool PAIR, bool TF32>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                          const __grid_constant__ CUtensorMap tma_b,
@@ -139,6 +143,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   using L = SmemLayout<BN, PAIR>;
   constexpr int STAGES = L::STAGES;
   constexpr int TILE_M = PAIR ? 2 * BLOCK_M : BLOCK_M;
+  constexpr int KE = TF32 ? 32 : 64;        // elements per k-block (one 128-byte row)
+  constexpr int MNC = TF32 ? 32 : 64;       // elements per MN-major chunk (128 bytes along M / N)
+  constexpr int CHUNK_BYTES = KE * 128;     // an MN-major chunk: KE k-rows of 128 bytes
+  constexpr int UK = TF32 ? 8 : 16;         // k extent of one MMA
   constexpr int BN_LOAD = L::B_ROWS;  // B rows / columns this CTA stages per k-block
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
   const bool leader = (cta_rank == 0);
@@ -263,21 +271,21 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           };
           if (p.cv.mode == 0) {
             if (!A_MN) {
-              ld2(sa, &tma_a, kb * BLOCK_K, m_base);
+              ld2(sa, &tma_a, kb * KE, m_base);
             } else {
 #pragma unroll
-              for (int c = 0; c < BLOCK_M / 64; ++c)
-                ld2(sa + c * (BLOCK_K * 128), &tma_a, m_base + c * 64, kb * BLOCK_K);
+              for (int c = 0; c < BLOCK_M / MNC; ++c)
+                ld2(sa + c * CHUNK_BYTES, &tma_a, m_base + c * MNC, kb * KE);
             }
             // weight rows of this tile: N index for K-major B, K index for MN-major B (dX = dY * W)
             const CUtensorMap* mb_ptr = &tma_b;
-            if (p.b_shard_rows > 0) mb_ptr = &tma_bp.m[(B_MN ? kb * BLOCK_K : n_base) / p.b_shard_rows];
+            if (p.b_shard_rows > 0) mb_ptr = &tma_bp.m[(B_MN ? kb * KE : n_base) / p.b_shard_rows];
             if (!B_MN) {
-              ld2(sb, mb_ptr, kb * BLOCK_K, n_base);
+              ld2(sb, mb_ptr, kb * KE, n_base);
             } else {
 #pragma unroll
-              for (int c = 0; c < BN_LOAD / 64; ++c)
-                ld2(sb + c * (BLOCK_K * 128), mb_ptr, n_base + c * 64, kb * BLOCK_K);
+              for (int c = 0; c < BN_LOAD / MNC; ++c)
+                ld2(sb + c * CHUNK_BYTES, mb_ptr, n_base + c * MNC, kb * KE);
             }
           } else if (p.cv.mode == 3) {
             // A: dY, MN-major tiled.  B: one im2col box (64 pixels x 64 channels) per 64-column chunk.
@@ -329,7 +337,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc(/*BF16*/ 1, A_MN, B_MN, TILE_M, BN);
+    constexpr uint32_t idesc = make_idesc(/*BF16 = 1, TF32 = 2*/ TF32 ? 2 : 1, A_MN, B_MN, TILE_M, BN);
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
@@ -352,16 +360,25 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           // K-major : rows of 128 B, 8-row swizzle atoms 1024 B apart (SBO); k-step = +32 B.
           // MN-major: 64-element column chunks BLOCK_K*128 B apart (LBO), 8 k-rows per
           //           1024 B atom (SBO); k-step (16 rows) = +2048 B.
+          // MN-major tf32 operands use the 32-byte-atom flavour of the 128-byte swizzle: 4 k-rows per pattern
+          constexpr uint32_t MN_LAYOUT = TF32 ? 1u : 2u;
+          constexpr uint32_t MN_SBO = TF32 ? 512u : 1024u;
           const uint64_t a_desc0 =
-              A_MN ? make_smem_desc_sw128(sa, BLOCK_K * 128, 1024) : make_smem_desc_sw128(sa, 16, 1024);
+              A_MN ? make_smem_desc(sa, CHUNK_BYTES, MN_SBO, MN_LAYOUT) : make_smem_desc_sw128(sa, 16, 1024);
           const uint64_t b_desc0 =
-              B_MN ? make_smem_desc_sw128(sb, BLOCK_K * 128, 1024) : make_smem_desc_sw128(sb, 16, 1024);
+              B_MN ? make_smem_desc(sb, CHUNK_BYTES, MN_SBO, MN_LAYOUT) : make_smem_desc_sw128(sb, 16, 1024);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((A_MN ? k * 2048 : k * 32) >> 4);
-            const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * 2048 : k * 32) >> 4);
-            if (PAIR) umma_f16_pair(d_tmem, a_desc, b_desc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            else umma_f16(d_tmem, a_desc, b_desc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < KE / UK; ++k) {   // 4 MMAs per k-block: +32 B along a K-major row, +UK rows MN-major
+            const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((A_MN ? k * UK * 128 : k * 32) >> 4);
+            const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * UK * 128 : k * 32) >> 4);
+            const uint32_t accf = (kb > kb0 || k > 0) ? 1u : 0u;
+            if (TF32) {
+              if (PAIR) umma_tf32_pair(d_tmem, a_desc, b_desc, idesc, accf);
+              else umma_tf32(d_tmem, a_desc, b_desc, idesc, accf);
+            } else {
+              if (PAIR) umma_f16_pair(d_tmem, a_desc, b_desc, idesc, accf);
+              else umma_f16(d_tmem, a_desc, b_desc, idesc, accf);
+            }
           }
           // frees the smem slot (in both CTAs of a pair) once these MMAs retire
           if (PAIR) umma_commit_pair(&empty_bar[stage]);
@@ -466,7 +483,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         if (p.Z != nullptr && row_ok) {
           const __nv_bfloat16* zrow = p.Z + static_cast<long long>(row) * p.ldz + dcol0;
           float d[32];
-          if (full && ((p.ldz & 7) == 0)) {
+          if (p.z_fp32) {
+            const float* zf = reinterpret_cast<const float*>(p.Z) + static_cast<long long>(row) * p.ldz + dcol0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) d[j] = (j < nvalid) ? zf[j] : 0.0f;
+          } else if (full && ((p.ldz & 7) == 0)) {
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
               float4 z = ld_z8(zrow + j);
@@ -620,7 +641,7 @@ static EncodeTiledFn get_encode_fn() {
 
 // 2-D bf16 tensor map with 128B swizzle: dims {inner, outer}, row pitch in elements.
 static int make_tmap_2d(CUtensorMap* out, const void* base, long long inner, long long outer,
-                        long long pitch_elems, int box_inner, int box_outer, bool fp32);
+                        long long pitch_elems, int box_inner, int box_outer, bool fp32, bool atom32 = false);
 
 int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long long outer,
                       long long pitch_elems, int box_inner, int box_outer) {
@@ -628,7 +649,7 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long 
 }
 
 static int make_tmap_2d(CUtensorMap* out, const void* base, long long inner, long long outer,
-                        long long pitch_elems, int box_inner, int box_outer, bool fp32) {
+                        long long pitch_elems, int box_inner, int box_outer, bool fp32, bool atom32) {
   const int es = fp32 ? 4 : 2;
   EncodeTiledFn fn = get_encode_fn();
   VB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
@@ -639,7 +660,8 @@ static int make_tmap_2d(CUtensorMap* out, const void* base, long long inner, lon
   cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(out, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box,
-                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   VB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%lld outer=%lld pitch=%lld box=%dx%d)",
              static_cast<int>(r), inner, outer, pitch_elems, box_inner, box_outer);
@@ -695,12 +717,12 @@ static int make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int 
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool PAIR>
+template <int BN, bool A_MN, bool B_MN, bool PAIR, bool TF32 = false>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
                        const GemmParams& p, int grid, cudaStream_t stream) {
   const PeerMaps& tp = *g_peer_maps;
   using L = SmemLayout<BN, PAIR>;
-  auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN, PAIR>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN, PAIR, TF32>;
   static bool attr_set = false;
   if (!attr_set) {
     VB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -728,13 +750,13 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   return 0;
 }
 
-template <int BN, bool PAIR>
+template <int BN, bool PAIR, bool TF32 = false>
 static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
                           const CUtensorMap& td, const GemmParams& p, int grid, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_gemm<BN, false, false, PAIR>(ta, tb, td, p, grid, s);
-  if (!a_mn && b_mn) return launch_gemm<BN, false, true, PAIR>(ta, tb, td, p, grid, s);
-  if (a_mn && !b_mn) return launch_gemm<BN, true, false, PAIR>(ta, tb, td, p, grid, s);
-  return launch_gemm<BN, true, true, PAIR>(ta, tb, td, p, grid, s);
+  if (!a_mn && !b_mn) return launch_gemm<BN, false, false, PAIR, TF32>(ta, tb, td, p, grid, s);
+  if (!a_mn && b_mn) return launch_gemm<BN, false, true, PAIR, TF32>(ta, tb, td, p, grid, s);
+  if (a_mn && !b_mn) return launch_gemm<BN, true, false, PAIR, TF32>(ta, tb, td, p, grid, s);
+  return launch_gemm<BN, true, true, PAIR, TF32>(ta, tb, td, p, grid, s);
 }
 
 }  // namespace vb
@@ -807,7 +829,7 @@ static void choose_config(int M, int N, int k_blocks, bool can_split, bool auto_
 
 // Builds the output tensor map (when D qualifies) and launches the right instantiation.
 static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtensorMap& tb, bool a_mn, bool b_mn,
-                             int BN, int pair, cudaStream_t stream, int d_cols = -1) {
+                             int BN, int pair, cudaStream_t stream, int d_cols = -1, bool tf32 = false) {
   const int sms = device_sm_count();
   // Output through TMA whenever D satisfies the tensor-map alignment rules; otherwise the
   // epilogue falls back to per-thread global stores / atomics.
@@ -825,15 +847,31 @@ static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtenso
   if (pair) {
     const int units = sms / 2;
     const int grid = 2 * static_cast<int>((p.dyn_sched || tiles < units) ? tiles : units);
+    if (tf32) {
+      switch (BN) {
+        case 128: return dispatch_major<128, true, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+        case 256: return dispatch_major<256, true, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+        default: VB_REQUIRE(false, "tf32 CTA-pair tiles are 128 or 256 wide");
+      }
+    }
     switch (BN) {
       case 128: return dispatch_major<128, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
       case 192:
         VB_REQUIRE(!b_mn, "paired 192-wide tiles need a K-major B operand");
-        return launch_gemm<192, false, false, true>(ta, tb, td, p, grid, stream) ;
+        if (a_mn) return launch_gemm<192, true, false, true>(ta, tb, td, p, grid, stream);
+        return launch_gemm<192, false, false, true>(ta, tb, td, p, grid, stream);
       default: return dispatch_major<256, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
     }
   }
   const int grid = static_cast<int>((p.dyn_sched || tiles < sms) ? tiles : sms);
+  if (tf32) {
+    switch (BN) {
+      case 64: return dispatch_major<64, false, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+      case 128: return dispatch_major<128, false, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+      case 256: return dispatch_major<256, false, true>(a_mn, b_mn, ta, tb, td, p, grid, stream);
+      default: VB_REQUIRE(false, "tf32 tiles are 64, 128 or 256 wide");
+    }
+  }
   switch (BN) {
     case 64: return dispatch_major<64, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
     case 128: return dispatch_major<128, false>(a_mn, b_mn, ta, tb, td, p, grid, stream);
@@ -1043,4 +1081,49 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
   // D is described with its real extent so stores of padded / neighbouring-tap columns are clipped
   p.N = n_virtual;
   return finish_and_launch(p, ta, tb, a_mn, b_mn, BN, pair, stream, mode == 3 ? N : -1);
+}
+
+// D[M,N] = epilogue(sum_k A(m,k) B(n,k)) with fp32 operands multiplied as TF32 (`tcgen05.mma.kind::tf32`, fp32
+// accumulate): the "float" precision mode for layers that must track an fp32 reference more closely than bf16 does.
+// Same conventions as vb_gemm_bf16; A, B (and Z) are float, leading dimensions multiples of 4 elements.
+extern "C" int vb_gemm_tf32(const float* A, long long lda, int a_mn_major, const float* B, long long ldb,
+                            int b_mn_major, void* D, long long ldd, int M, int N, int K, const float* bias, int act,
+                            int out_fp32, int accumulate, const float* Z, long long ldz, int deriv, float alpha,
+                            int split_k, int block_n, cudaStream_t stream) {
+  VB_REQUIRE(M > 0 && N > 0 && K > 0, "vb_gemm_tf32: empty problem %dx%dx%d", M, N, K);
+  VB_REQUIRE(!(accumulate && !out_fp32), "vb_gemm_tf32: accumulate requires fp32 output");
+  VB_REQUIRE(split_k >= 0, "vb_gemm_tf32: split_k must be >= 0 (0 = choose automatically)");
+  VB_REQUIRE(block_n == 0 || block_n == 64 || block_n == 128 || block_n == 256, "vb_gemm_tf32: block_n must be 0/64/128/256");
+  const bool auto_split = (split_k == 0);
+  if (auto_split) split_k = 1;
+  const bool can_split = accumulate && act == 0 && Z == nullptr;
+  VB_REQUIRE(split_k == 1 || can_split, "vb_gemm_tf32: split-K needs accumulate=1 and a linear epilogue");
+  constexpr int KE = 32;   // fp32 elements per 128-byte k-block row
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M; p.N = N; p.K = K;
+  p.D = D; p.ldd = ldd; p.bias = bias; p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.z_fp32 = 1; p.alpha = alpha;
+  p.k_blocks = ceil_div(K, KE);
+  int BN = block_n, pair = 0;
+  const int split_req = split_k;
+  for (int attempt = 0; attempt < 2; ++attempt) {   // 192-wide tiles are not instantiated for tf32: fall back to 128
+    BN = attempt == 0 ? block_n : 128;
+    split_k = split_req;
+    choose_config(M, N, p.k_blocks, can_split, auto_split, b_mn_major != 0, &BN, &split_k, &pair);
+    if (BN != 192) break;
+  }
+  p.m_blocks = ceil_div(M, pair ? 2 * BLOCK_M : BLOCK_M);
+  p.n_blocks = ceil_div(N, BN);
+  p.split_k = split_k;
+  const int bn_load = pair ? BN / 2 : BN;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_2d(&ta, A, K, M, lda, KE, BLOCK_M, true);
+  else rc = make_tmap_2d(&ta, A, M, K, lda, 32, KE, true, true);
+  if (rc) return rc;
+  if (!b_mn_major) rc = make_tmap_2d(&tb, B, K, N, ldb, KE, bn_load, true);
+  else rc = make_tmap_2d(&tb, B, N, K, ldb, 32, KE, true, true);
+  if (rc) return rc;
+  return finish_and_launch(p, ta, tb, a_mn_major != 0, b_mn_major != 0, BN, pair, stream, -1, true);
 }

@@ -130,6 +130,31 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumu
     return out
 
 
+def gemm_tf32(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumulate=False, z=None, deriv=0,
+              alpha=1.0, split_k=1, block_n=0):
+    """``gemm`` with fp32 operands multiplied as TF32 (fp32 accumulate): the "float" precision mode."""
+    assert a.dtype == torch.float32 and b.dtype == torch.float32
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    assert K == Kb and tuple(out.shape) == (M, N)
+    assert z is None or z.dtype == torch.float32
+    _FLOPS[0] = 2.0 * M * N * K
+    rc = _lib.lib().vb_gemm_tf32(_p(a), c_longlong(_ld(a)), c_int(int(a_mn)), _p(b), c_longlong(_ld(b)),
+                                 c_int(int(b_mn)), _p(out), c_longlong(_ld(out)), c_int(M), c_int(N), c_int(K),
+                                 _p(bias), c_int(act), c_int(1 if out.dtype == torch.float32 else 0),
+                                 c_int(int(accumulate)), _p(z), c_longlong(_ld(z) if z is not None else 0),
+                                 c_int(deriv), c_float(alpha), c_int(split_k), c_int(block_n), _stream())
+    _lib.check(rc, "vb_gemm_tf32")
+    LAUNCHES[0] += 1
+    return out
+
+
 def _conv_gemm(mode, t4, ky, kx, sy, sx, low_h, low_w, n_h, n_w, other, other_rows, cg, out, M, N, bias=None,
                act=ACT_LINEAR, accumulate=False, z=None, deriv=0, alpha=1.0, split_k=1, block_n=0):
     assert t4.dtype == torch.bfloat16 and other.dtype == torch.bfloat16 and t4.dim() == 4
@@ -475,7 +500,7 @@ def _traced(fn):
     return wrap
 
 
-for _name in ("gemm", "conv_forward", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
+for _name in ("gemm", "gemm_tf32", "conv_forward", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
               "gather_minibatch", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
               "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",

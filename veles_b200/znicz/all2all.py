@@ -93,15 +93,21 @@ class All2All(Forward):
         self._x_stage_ = None
         n_in = self.weights_bf16_.shape[1]
         xin = self.input.devmem
-        need_stage = (xin.dtype != torch.bfloat16) or (n_in % 8 != 0)
+        # "float" precision (root.common.engine.precision_type): fp32 activations and master weights go straight into
+        # the tf32 tensor-core GEMM, no bf16 staging and no weight shadow on this layer's path
+        self.tf32_ = (dev.compute_dtype == torch.float32 and xin.dtype == torch.float32 and n_in % 4 == 0
+                      and not self.weights_transposed)
+        need_stage = not self.tf32_ and ((xin.dtype != torch.bfloat16) or (n_in % 8 != 0))
         if need_stage:
             self._x_stage_ = kernels.pitched_empty(self.input.shape[0], n_in, torch.bfloat16, dev.torch_device)
 
     def device_input_2d(self):
-        """bf16 [batch, n_in] view of the input with a TMA-legal pitch."""
+        """[batch, n_in] view of the input with a TMA-legal pitch (bf16, or fp32 in tf32 mode)."""
         from ..ops import kernels
         x = self.input.devmem
         x2 = x if x.dim() == 2 else x.reshape(x.shape[0], -1)
+        if getattr(self, "tf32_", False) and x2.stride(0) % 4 != 0:
+            x2 = x2.contiguous()
         if self._x_stage_ is not None:
             kernels.copy_2d(x2, self._x_stage_)
             return self._x_stage_
@@ -113,8 +119,13 @@ class All2All(Forward):
         x = self.device_input_2d()
         out = self.output.devmem
         out2 = out if out.dim() == 2 else out.reshape(out.shape[0], -1)
-        kernels.gemm(x, self.weights_bf16_, out2, bias=self.bias.devmem if self.include_bias else None,
-                     act=self.ACTIVATION, b_peers=getattr(self, "peer_weights_", None))
+        if self.tf32_:
+            self.weights.unmap()
+            kernels.gemm_tf32(x, self.weights.devmem.view(self.weights_bf16_.shape), out2,
+                              bias=self.bias.devmem if self.include_bias else None, act=self.ACTIVATION)
+        else:
+            kernels.gemm(x, self.weights_bf16_, out2, bias=self.bias.devmem if self.include_bias else None,
+                         act=self.ACTIVATION, b_peers=getattr(self, "peer_weights_", None))
         self.output.mark_device_written()
 
 
@@ -192,8 +203,13 @@ class All2AllSoftmax(All2All):
         from ..ops import kernels
         self.input.unmap()
         x = self.device_input_2d()
-        kernels.gemm(x, self.weights_bf16_, self.logits_, bias=self.bias.devmem if self.include_bias else None,
-                     b_peers=getattr(self, "peer_weights_", None))
+        if self.tf32_:
+            self.weights.unmap()
+            kernels.gemm_tf32(x, self.weights.devmem.view(self.weights_bf16_.shape), self.logits_,
+                              bias=self.bias.devmem if self.include_bias else None)
+        else:
+            kernels.gemm(x, self.weights_bf16_, self.logits_, bias=self.bias.devmem if self.include_bias else None,
+                         b_peers=getattr(self, "peer_weights_", None))
         if not self.defer_softmax:
             out = self.output.devmem
             kernels.softmax_eval(self.logits_, out if out.dim() == 2 else out.reshape(out.shape[0], -1), None, None,

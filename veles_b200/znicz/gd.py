@@ -102,7 +102,7 @@ class GradientDescent(GradientDescentBase):
         # dW = dY^T X either accumulates into a zeroed buffer (split-K over the batch) or, when the scheduler would
         # not split, is plainly stored: the latter skips the read-modify-write at L2 and the re-zeroing pass.
         n_in = self.input.size // self.input.shape[0]
-        self.dw_store_ = (self.dp_group_ is None and self.apply_gradient and
+        self.dw_store_ = (self.dp_group_ is None and self.apply_gradient and not self.tf32_mode() and
                           kernels.gemm_plan(n_out, n_in, self.err_output.shape[0], b_mn=True)[1] == 1)
 
     def device_err_output(self):
@@ -111,6 +111,16 @@ class GradientDescent(GradientDescentBase):
         from ..ops import kernels
         eo = self.err_output.devmem
         eo2 = eo if eo.dim() == 2 else eo.reshape(eo.shape[0], -1)
+        if self.tf32_mode():     # fp32 err_output straight into the tf32 GEMMs
+            if eo2.dtype != torch.float32 or eo2.stride(0) % 4 != 0:
+                eo2 = eo2.float().contiguous()
+            if self.ACTIVATION and not self.derivative_applied:
+                y = self.output.devmem
+                y2 = (y if y.dim() == 2 else y.reshape(y.shape[0], -1))
+                tmp = eo2.contiguous()
+                kernels.activation_backward(self.ACTIVATION, tmp, None, y2.contiguous(), tmp)
+                eo2 = tmp
+            return eo2
         bad_layout = eo2.dtype != torch.bfloat16 or eo2.stride(0) % 8 != 0
         if bad_layout:
             if self._eo_stage_ is None:
@@ -128,9 +138,35 @@ class GradientDescent(GradientDescentBase):
                 kernels.copy_2d(tmp, eo2)
         return eo2
 
+    def tf32_mode(self):
+        return bool(self.forward is not None and getattr(self.forward, "tf32_", False))
+
+    def b200_run_tf32(self):
+        """The three GEMMs of the layer on fp32 tensors through tcgen05 kind::tf32."""
+        from ..ops import kernels
+        fwd = self.forward
+        eo = self.device_err_output()
+        x = fwd.device_input_2d()
+        w = fwd.weights.devmem.view(fwd.weights_bf16_.shape)
+        if self.need_err_input:
+            ei = self.err_input.devmem
+            ei2 = ei if ei.dim() == 2 else ei.reshape(ei.shape[0], -1)
+            kernels.gemm_tf32(eo, w, ei2, b_mn=True, z=x if self.prev_activation else None, deriv=self.prev_activation)
+            self.err_input.mark_device_written()
+        gw_t, gb_t = self.grad_tensors()
+        gw = gw_t.view(w.shape[0], -1)
+        kernels.gemm_tf32(eo, x, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
+        if self.bias is not None and self.bias:
+            kernels.col_sum(eo, gb_t, self.col_scratch_, accumulate=True)
+            self.gradient_bias.mark_device_written()
+        self.gradient_weights.mark_device_written()
+        self.device_update()
+
     def b200_run(self):
         from ..ops import kernels
         self.err_output.unmap()
+        if self.tf32_mode():
+            return self.b200_run_tf32()
         eo = self.device_err_output()
         fwd = self.forward
         # the forward unit staged (cast/pitched) its input this iteration: reuse it
