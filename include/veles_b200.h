@@ -58,6 +58,13 @@ int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW, long long
                       int other_rows, int cg, void* D, long long ldd, int M, int N, const float* bias, int act,
                       int out_fp32, int accumulate, const void* Z, long long ldz, int deriv, float alpha, int split_k,
                       int block_n, cudaStream_t stream);
+/* Halo-tile variant for unit-stride layers (OW + kx - 1 <= 64): every 64-channel block of the walked tensor is loaded
+ * once per output tile (4-D TMA box with halo) and all ky*kx taps are issued from that shared-memory tile.
+ * mode 1 forward / 2 err_input as above; D is [tB, oH, oW, N] with pixel pitch d_pitch.  Returns 1 when unsupported. */
+int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW, long long t_pitch, int t_ch, int ky, int kx,
+                      int low_h, int low_w, int oH, int oW, const void* W, long long ldw, int w_rows, int cg, void* D,
+                      long long d_pitch, int N, const float* bias, int act, const void* Z, long long ldz, int deriv,
+                      cudaStream_t stream);
 /* x [B,H,W,C] (dtype 0 f32 / 1 bf16) -> bf16 [B, ceil(H/sy), ceil(W/sx), sy*sx*C]: strided few-channel convolutions
  * become unit-stride ones the implicit GEMM can walk. */
 int vb_space_to_depth(const void* x, int dtype, void* xs, int B, int H, int W, int C, int sy, int sx,

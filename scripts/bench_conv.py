@@ -10,6 +10,7 @@ from veles_b200.ops import kernels as k
 from bench_gemm import timeit, dev
 
 LAYERS = {   # name: (B, H, W, Cg, n_g, ky, kx, pad)
+    "conv1s2d": (256, 57, 57, 48, 96, 3, 3, 0),
     "conv2": (256, 27, 27, 48, 128, 5, 5, 2),
     "conv3": (256, 13, 13, 256, 384, 3, 3, 1),
     "conv4": (256, 13, 13, 192, 192, 3, 3, 1),
@@ -21,16 +22,17 @@ if __name__ == "__main__":
     which = sys.argv[1:] or list(LAYERS)
     for name in which:
         B, H, W, C, n, ky, kx, p = LAYERS[name]
-        g = dict(OH=H, OW=W, ky=ky, kx=kx, sy=1, sx=1, pt=p, pl=p, H=H, W=W)
+        OHW = H + 2 * p - ky + 1
+        g = dict(OH=OHW, OW=OHW, ky=ky, kx=kx, sy=1, sx=1, pt=p, pl=p, H=H, W=W)
         x = torch.randn(B, H, W, C, device=dev).bfloat16()
         w = (torch.randn(n, ky * kx * C, device=dev) * 0.05).bfloat16()
-        y = torch.empty(B * H * W, n, device=dev, dtype=torch.bfloat16)
-        dy = torch.randn(B, H, W, n, device=dev).bfloat16()
+        y = torch.empty(B * OHW * OHW, n, device=dev, dtype=torch.bfloat16)
+        dy = torch.randn(B, OHW, OHW, n, device=dev).bfloat16()
         dx = torch.empty(B * H * W, C, device=dev, dtype=torch.bfloat16)
         gw = torch.zeros(n, ky * kx * C, device=dev)
-        fl = 2.0 * B * H * W * n * ky * kx * C
-        for bn in (0, 64, 128, 192, 256):
-            for pair in (1, 2):
+        fl = 2.0 * B * OHW * OHW * n * ky * kx * C
+        for bn in (0,):
+            for pair in (0,):
                 k.set_pair_mode(pair)
                 row = dict(layer=name, block_n=bn, pair=pair == 2)
                 for op, fn in (("fwd", lambda: k.conv_forward(x, w, y, g, act=4, block_n=bn)),
@@ -44,6 +46,16 @@ if __name__ == "__main__":
                         row[op + "_us"] = None
                 print(json.dumps(row), flush=True)
                 res.append(row)
+        k.set_pair_mode(0)
+        row = dict(layer=name, kernel="halo")
+        for op, fn in (("fwd", lambda: k.conv_forward_halo(x, w, y, g, act=4)),
+                       ("dx", lambda: k.conv_err_input_halo(dy, w, dx, g))):
+            if fn():
+                t = timeit(fn, iters=5, warm=2)
+                row[op + "_us"] = round(t * 1e3, 1)
+                row[op + "_tflops"] = round(fl / t / 1e9, 1)
+        print(json.dumps(row), flush=True)
+        res.append(row)
     k.set_pair_mode(0)
     os.makedirs("../gpurun_out", exist_ok=True)
     json.dump(res, open("../gpurun_out/bench_conv.json", "w"), indent=1)

@@ -273,6 +273,50 @@ def test_gemm_cta_pair_layouts(M, N, K_, a_mn, b_mn, block_n, pair_mode, dyn_sch
     assert rel_err(out, 2 * ((a.float().t() if a_mn else a.float()) @ (b.float() if b_mn else b.float().t()))) < 3e-3
 
 
+HALO_CASES = [
+    # B, H, W, C, n, ky, kx, pt, pl, pb, pr, groups
+    (3, 27, 27, 96, 256, 5, 5, 2, 2, 2, 2, 2),     # AlexNet conv2: P = 32, 48 channels / 128 kernels per group
+    (4, 13, 13, 256, 384, 3, 3, 1, 1, 1, 1, 1),    # conv3: P = 16, two image rows per epilogue warp, 3 N tiles
+    (2, 13, 13, 384, 256, 3, 3, 1, 1, 1, 1, 2),    # conv5 (grouped)
+    (2, 55, 55, 48, 96, 3, 3, 0, 0, 2, 2, 1),      # conv1 after space-to-depth: P = 64
+    (3, 9, 11, 16, 40, 3, 2, 0, 1, 2, 0, 1),       # asymmetric padding, odd sizes, N tail
+    (2, 30, 7, 8, 24, 7, 3, 3, 1, 3, 1, 1),        # tall filter: many halo rows
+]
+
+
+@pytest.mark.parametrize("case", HALO_CASES)
+def test_halo_tile_conv_forward_and_err_input(case):
+    """Halo-tile kernel (all taps from one smem tile, shifted UMMA descriptors, 4-D TMA boxes) vs torch conv2d."""
+    k = K()
+    B, H, W, C, n, ky, kx, pt, pl, pb, pr, G = case
+    torch.manual_seed(sum(case))
+    Cg, ng = C // G, n // G
+    OH, OW = H + pt + pb - ky + 1, W + pl + pr - kx + 1
+    g = dict(OH=OH, OW=OW, ky=ky, kx=kx, sy=1, sx=1, pt=pt, pl=pl, H=H, W=W)
+    x = (torch.randn(B, H, W, C, device=dev()) * 0.5).bfloat16()
+    w = (torch.randn(n, ky * kx * Cg, device=dev()) * 0.1).bfloat16()
+    bias = torch.randn(n, device=dev())
+    xr = x.float().requires_grad_(True)
+    yr = torch.relu(_conv_ref(xr, w.float(), n, ky, kx, 1, 1, pt, pl, pb, pr, G) + bias)
+    y = torch.full((B * OH * OW + 5, n), float("nan"), device=dev(), dtype=torch.bfloat16)
+    for gi in range(G):
+        assert k.conv_forward_halo(x[..., gi * Cg:(gi + 1) * Cg], w[gi * ng:(gi + 1) * ng],
+                                   y[:B * OH * OW, gi * ng:(gi + 1) * ng], g, bias=bias[gi * ng:(gi + 1) * ng], act=4)
+    assert rel_err(y[:B * OH * OW], yr.detach().reshape(-1, n)) < 1e-2
+    assert torch.isnan(y[B * OH * OW:].float()).all()
+    e = (torch.randn(B, OH, OW, n, device=dev()) * 0.3).bfloat16()
+    yl = _conv_ref(xr, w.float(), n, ky, kx, 1, 1, pt, pl, pb, pr, G)
+    yl.backward(e.float())
+    dx = torch.full((B * H * W + 3, C), float("nan"), device=dev(), dtype=torch.bfloat16)
+    for gi in range(G):
+        assert k.conv_err_input_halo(e[..., gi * ng:(gi + 1) * ng], w[gi * ng:(gi + 1) * ng],
+                                     dx[:B * H * W, gi * Cg:(gi + 1) * Cg], g,
+                                     z=x.reshape(-1, C)[:, gi * Cg:(gi + 1) * Cg], deriv=1)
+    ref = xr.grad * (0.6666 * (1.7159 - x.float() ** 2 / 1.7159))
+    assert rel_err(dx[:B * H * W], ref.reshape(-1, C)) < 1e-2
+    assert torch.isnan(dx[B * H * W:].float()).all()
+
+
 @pytest.mark.parametrize("b_mn", [False, True])
 @pytest.mark.parametrize("world", [2, 8])
 def test_gemm_row_sharded_weight_operand(b_mn, world, pair_mode):

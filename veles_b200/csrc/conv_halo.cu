@@ -1,0 +1,418 @@
+// veles_b200 — "halo tile" implicit-GEMM convolution for unit-stride layers with many taps.
+//
+// The im2col-mode kernel (gemm_tcgen05.cu) re-fetches the activation operand once per filter tap:
+// for a 5x5 layer every input element enters an SM 25 times, and with few output channels per
+// tile (AlexNet conv2: 48 / 128 per group) that operand ingest, not the tensor core, bounds the
+// kernel.  Here a CTA loads, per 64-channel block, ONE spatial tile of the input with its halo
+//     (R + ky - 1) image rows  x  P pixels  x  64 channels        (P = 16/32/64 >= OW + kx - 1)
+// through a 4-D tiled TMA box (negative / out-of-range coordinates zero-fill = the padding), and
+// issues the MMAs of all ky*kx taps from that same shared-memory tile: tap (r, s) is simply the
+// 128-row window that starts (r*P + s) rows further down, described by a shifted UMMA descriptor.
+// The M rows of the MMA are R image rows of P lanes each (lane w' < OW is a real output pixel,
+// the rest is discarded), so a 32-lane epilogue warp covers whole image-row segments and writes
+// them with rectangular 4-D TMA store boxes that the tensor map clips to the image.
+// Only the (small) weight tiles stream per tap.  Modes: forward, and err_input (the same walk
+// over dY with flipped taps).  Replaces Znicz conv / gd_conv err_input (absent).
+#include "common.cuh"
+
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+namespace vb {
+
+constexpr int HALO_THREADS = 320;   // producer warp, MMA warp, 8 epilogue warps
+constexpr int HALO_A_SLOT = 32768;  // <= 256 rows x 128 B
+constexpr int HALO_EPI_BYTES = 8 * 4096;
+
+struct HaloParams {
+  int B, OH, OW;         // output grid (err_input mode: the layer INPUT grid)
+  int P, R;              // lanes per image row, image rows per 128-row tile (R = 128 / P)
+  int kx, ky;            // taps
+  int low_w, low_h;      // first input coordinate of output 0 = -(padding)   (err_input: -(k-1-padding))
+  int flip;              // 1: weight tap of window offset (r, s) is (ky-1-r, kx-1-s)    (err_input)
+  int cblocks, cg;       // 64-channel blocks of the walked tensor; weight-matrix columns per tap
+  int N, n_blocks;       // output channels, N tiles
+  int tiles_per_img;     // ceil(OH / R)
+  int a_rows;            // (R + ky - 1) * P rows of 128 B per activation tile
+  const float* bias;
+  int act;
+  const __nv_bfloat16* Z;  // optional [pixels, N] (pixel pitch ldz): D *= f'(Z)
+  long long ldz;
+  int deriv;
+};
+
+template <int ACT>
+__device__ __forceinline__ void halo_apply_act(float (&f)[32]) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) f[j] = act_forward_fast<ACT>(f[j]);
+}
+template <int ACT>
+__device__ __forceinline__ void halo_apply_deriv(float (&f)[32], const float (&y)[32]) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) f[j] *= act_deriv_from_output(ACT, y[j]);
+}
+
+template <int BN>
+struct HaloSmem {
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int BUDGET = 227 * 1024 - 2 * HALO_A_SLOT - HALO_EPI_BYTES - 2048;
+  static constexpr int B_STAGES = (BUDGET / B_BYTES) > 12 ? 12 : (BUDGET / B_BYTES);
+  static constexpr int TOTAL = 2 * HALO_A_SLOT + B_STAGES * B_BYTES + HALO_EPI_BYTES + 2048;
+};
+
+// B_MN = false: weights K-major [N, taps*cg] (forward).  B_MN = true: weights [K = kernels, taps*cg] read as
+// MN-major [k, n = input channel] tiles (err_input).
+template <int BN, bool B_MN>
+__global__ void __launch_bounds__(HALO_THREADS, 1)
+conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w,
+                 const __grid_constant__ CUtensorMap tma_d, const HaloParams p) {
+  using S = HaloSmem<BN>;
+  constexpr int B_STAGES = S::B_STAGES;
+  constexpr int TMEM_COLS = (2 * BN <= 64) ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512));
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_smem = smem;                                   // 2 activation slots
+  uint8_t* b_smem = smem + 2 * HALO_A_SLOT;                 // weight ring
+  uint8_t* epi_smem = b_smem + B_STAGES * S::B_BYTES;       // 8 x 4 KB staging slabs (1024-aligned)
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(epi_smem + HALO_EPI_BYTES);
+  uint64_t* a_empty = a_full + 2;
+  uint64_t* b_full = a_empty + 2;
+  uint64_t* b_empty = b_full + B_STAGES;
+  uint64_t* tmem_full = b_empty + B_STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tma_x);
+    tma_prefetch_desc(&tma_w);
+    tma_prefetch_desc(&tma_d);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], 1);
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 8);
+    }
+    for (int s = 0; s < B_STAGES; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    fence_barrier_init();
+    fence_proxy_async_smem();
+  }
+  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  const int taps = p.kx * p.ky;
+  const int num_tiles = p.B * p.tiles_per_img * p.n_blocks;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      int a_slot = 0, b_stage = 0;
+      uint32_t a_phase = 0, b_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int nb = tile % p.n_blocks;
+        const int sp = tile / p.n_blocks;
+        const int img = sp / p.tiles_per_img;
+        const int oh0 = (sp - img * p.tiles_per_img) * p.R;
+        for (int cb = 0; cb < p.cblocks; ++cb) {
+          mbar_wait(&a_empty[a_slot], a_phase ^ 1);
+          mbar_expect_tx(&a_full[a_slot], static_cast<uint32_t>(p.a_rows) * 128u);
+          tma_load_4d(a_smem + a_slot * HALO_A_SLOT, &tma_x, &a_full[a_slot], cb * 64, p.low_w, oh0 + p.low_h, img);
+          if (++a_slot == 2) {
+            a_slot = 0;
+            a_phase ^= 1;
+          }
+          for (int tap = 0; tap < taps; ++tap) {
+            int wtap = tap;
+            if (p.flip) {
+              const int r = tap / p.kx, s = tap - r * p.kx;
+              wtap = (p.ky - 1 - r) * p.kx + (p.kx - 1 - s);
+            }
+            mbar_wait(&b_empty[b_stage], b_phase ^ 1);
+            uint8_t* sb = b_smem + b_stage * S::B_BYTES;
+            mbar_expect_tx(&b_full[b_stage], S::B_BYTES);
+            if (!B_MN) {
+              tma_load_2d(sb, &tma_w, &b_full[b_stage], wtap * p.cg + cb * 64, nb * BN);
+            } else {
+#pragma unroll
+              for (int c = 0; c < BN / 64; ++c)
+                tma_load_2d(sb + c * 8192, &tma_w, &b_full[b_stage], wtap * p.cg + nb * BN + c * 64, cb * 64);
+            }
+            if (++b_stage == B_STAGES) {
+              b_stage = 0;
+              b_phase ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc(/*BF16*/ 1, false, B_MN, 128, BN);
+    int a_slot = 0, b_stage = 0, acc = 0;
+    uint32_t a_phase = 0, b_phase = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+      for (int cb = 0; cb < p.cblocks; ++cb) {
+        mbar_wait(&a_full[a_slot], a_phase);
+        const uint32_t sa0 = smem_u32(a_smem + a_slot * HALO_A_SLOT);
+        for (int tap = 0; tap < taps; ++tap) {
+          mbar_wait(&b_full[b_stage], b_phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const int r = tap / p.kx, s = tap - r * p.kx;
+            // the tap's 128-row window of the halo tile: (r*P + s) rows further down
+            const uint32_t sa = sa0 + static_cast<uint32_t>(r * p.P + s) * 128u;
+            const uint32_t sb = smem_u32(b_smem + b_stage * S::B_BYTES);
+            const uint64_t b_desc0 = B_MN ? make_smem_desc_sw128(sb, 8192, 1024) : make_smem_desc_sw128(sb, 16, 1024);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              // plain SWIZZLE_128B descriptor (base-offset field 0): the swizzle is a function of the absolute
+              // shared-memory address, so a window shifted by whole rows reads exactly what TMA wrote (measured:
+              // setting the base-offset field to the row phase gives wrong products)
+              const uint64_t a_desc = make_smem_desc_sw128(sa + k * 32, 16, 1024);
+              const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * 2048 : k * 32) >> 4);
+              umma_f16(d_tmem, a_desc, b_desc, idesc, (cb > 0 || tap > 0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(&b_empty[b_stage]);
+            if (tap == taps - 1) {
+              umma_commit(&a_empty[a_slot]);
+              if (cb == p.cblocks - 1) umma_commit(&tmem_full[acc]);
+            }
+          }
+          __syncwarp();
+          if (++b_stage == B_STAGES) {
+            b_stage = 0;
+            b_phase ^= 1;
+          }
+        }
+        if (++a_slot == 2) {
+          a_slot = 0;
+          a_phase ^= 1;
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===================== Epilogue (warps 2..9) =====================
+    const int quarter = warp & 3;        // TMEM lanes [32*quarter, 32*quarter + 32)
+    const int ehalf = (warp - 2) >> 2;   // which 64-column slabs this warp takes
+    uint8_t* buf = epi_smem + (warp - 2) * 4096;
+    uint8_t* srow = buf + lane * 128;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int nb = tile % p.n_blocks;
+      const int sp = tile / p.n_blocks;
+      const int img = sp / p.tiles_per_img;
+      const int oh0 = (sp - img * p.tiles_per_img) * p.R;
+      // this lane's output pixel
+      const int m = quarter * 32 + lane;
+      const int r_loc = m / p.P;
+      const int w = m - r_loc * p.P;
+      const int oh = oh0 + r_loc;
+      const bool px_ok = (oh < p.OH) && (w < p.OW);
+      const long long pixel = (static_cast<long long>(img) * p.OH + oh) * p.OW + w;
+      // the warp's store box: lanes 0..31 = rows (w fastest, then image rows) starting here
+      const int box_w0 = (quarter * 32) % p.P;
+      const int box_h0 = oh0 + (quarter * 32) / p.P;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c0 = ehalf * 64; c0 < BN; c0 += 128) {
+        const int col0 = nb * BN + c0;
+        if (col0 >= p.N) break;
+        if (lane == 0) tma_store_wait_read<0>();
+        __syncwarp();
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+          const int colh = col0 + half * 32;
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                            static_cast<uint32_t>(acc * BN + c0 + half * 32),
+                        v);
+          tmem_ld_wait();
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          const int nvalid = p.N - colh;   // may be <= 0 for the second half of the last slab
+          if (p.bias != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < nvalid) f[j] += __ldg(p.bias + colh + j);
+          }
+          switch (p.act) {
+            case ACT_TANH: halo_apply_act<ACT_TANH>(f); break;
+            case ACT_SIGMOID: halo_apply_act<ACT_SIGMOID>(f); break;
+            case ACT_RELU: halo_apply_act<ACT_RELU>(f); break;
+            case ACT_STRICT_RELU: halo_apply_act<ACT_STRICT_RELU>(f); break;
+            default: break;
+          }
+          if (p.Z != nullptr && px_ok) {
+            const __nv_bfloat16* zrow = p.Z + pixel * p.ldz + colh;
+            float d[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) d[j] = (j < nvalid) ? __bfloat162float(zrow[j]) : 0.0f;
+            switch (p.deriv) {
+              case ACT_TANH: halo_apply_deriv<ACT_TANH>(f, d); break;
+              case ACT_SIGMOID: halo_apply_deriv<ACT_SIGMOID>(f, d); break;
+              case ACT_RELU: halo_apply_deriv<ACT_RELU>(f, d); break;
+              case ACT_STRICT_RELU: halo_apply_deriv<ACT_STRICT_RELU>(f, d); break;
+              default: break;
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 o;
+            o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
+            o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+            o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+            o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+            *reinterpret_cast<uint4*>(srow + (((half * 4 + q) ^ (lane & 7)) << 4)) = o;
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          // {64 channels, min(P,32) pixels, 32/min(P,32) image rows, 1 image}: clipped to N, OW, OH by the map
+          tma_store_4d(&tma_d, buf, col0, box_w0, box_h0, img);
+          tma_store_commit();
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (lane == 0) tma_store_wait_all<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<TMEM_COLS>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn halo_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+  });
+  return fn;
+}
+
+// bf16 NHWC tensor {C, W, H, B} (pixel pitch in elements), 128B-swizzled boxes {bc, bw, bh, 1}
+static int halo_tmap_4d(CUtensorMap* out, const void* base, int C, int W, int H, int B, long long pitch, int bc, int bw,
+                        int bh) {
+  EncodeTiledFn fn = halo_encode_fn();
+  VB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t gdim[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                        static_cast<cuuint64_t>(B)};
+  cuuint64_t gstride[3] = {static_cast<cuuint64_t>(pitch) * 2, static_cast<cuuint64_t>(pitch) * 2 * W,
+                           static_cast<cuuint64_t>(pitch) * 2 * W * H};
+  cuuint32_t box[4] = {static_cast<cuuint32_t>(bc), static_cast<cuuint32_t>(bw), static_cast<cuuint32_t>(bh), 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  VB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(4D) failed with CUresult %d (C=%d W=%d H=%d B=%d box %dx%dx%d)",
+             static_cast<int>(r), C, W, H, B, bc, bw, bh);
+  return 0;
+}
+
+int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long long outer, long long pitch_elems,
+                      int box_inner, int box_outer);   // gemm_tcgen05.cu
+
+template <int BN, bool B_MN>
+static int launch_halo(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& td, const HaloParams& p,
+                       cudaStream_t s) {
+  using S = HaloSmem<BN>;
+  auto kern = conv_halo_kernel<BN, B_MN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    VB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+    attr_set = true;
+  }
+  const long long tiles = static_cast<long long>(p.B) * p.tiles_per_img * p.n_blocks;
+  const int sms = device_sm_count();
+  const int grid = static_cast<int>(tiles < sms ? tiles : sms);
+  kern<<<grid, HALO_THREADS, S::TOTAL, s>>>(tx, tw, td, p);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace vb
+
+using namespace vb;
+
+// mode 1 forward:   D[B,oH,oW,N]  = act(conv(T, W) + bias),  W = [N, ky*kx*cg] (row pitch ldw), T = [tB,tH,tW,t_ch]
+// mode 2 err_input: D[B,oH,oW,cg] = convT(T = dY, W) * f'(Z), W = [w_rows = t_ch kernels, ky*kx*cg]
+// (low_h, low_w) = -padding (mode 2: -(k-1-padding)); unit stride only.  T and D may be channel slices of wider
+// NHWC tensors (pitches in elements).  Returns 1 when the geometry is not supported by this kernel (use
+// vb_conv_gemm_bf16), 0 on success, negative on error.
+extern "C" int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW, long long t_pitch, int t_ch, int ky,
+                                 int kx, int low_h, int low_w, int oH, int oW, const void* W, long long ldw,
+                                 int w_rows, int cg, void* D, long long d_pitch, int N, const float* bias, int act,
+                                 const void* Z, long long ldz, int deriv, cudaStream_t stream) {
+  VB_REQUIRE(mode == 1 || mode == 2, "vb_conv_halo_bf16: mode must be 1 (forward) or 2 (err_input)");
+  if (oW + kx - 1 > 64 || t_ch % 8 || t_pitch % 8 || d_pitch % 8 || ldw % 8 || kx * ky < 2) return 1;
+  if ((reinterpret_cast<uintptr_t>(T) | reinterpret_cast<uintptr_t>(D) | reinterpret_cast<uintptr_t>(W)) & 15) return 1;
+  int P = 16;
+  while (P < oW + kx - 1) P <<= 1;
+  const int R = 128 / P;
+  const int a_rows = (R + ky - 1) * P;
+  if (a_rows > 256 || R + ky - 1 > 256) return 1;
+  HaloParams p;
+  memset(&p, 0, sizeof(p));
+  p.B = tB; p.OH = oH; p.OW = oW; p.P = P; p.R = R; p.kx = kx; p.ky = ky; p.low_w = low_w; p.low_h = low_h;
+  p.flip = (mode == 2) ? 1 : 0;
+  p.cblocks = ceil_div(t_ch, 64); p.cg = cg; p.N = N;
+  p.tiles_per_img = ceil_div(oH, R);
+  p.a_rows = a_rows;
+  p.bias = bias; p.act = act; p.Z = static_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv;
+  const int BN = (N <= 64) ? 64 : 128;
+  p.n_blocks = ceil_div(N, BN);
+  CUtensorMap tx, tw, td;
+  int rc = halo_tmap_4d(&tx, T, t_ch, tW, tH, tB, t_pitch, 64, P, R + ky - 1);
+  if (rc) return rc;
+  const int pw = P < 32 ? P : 32;
+  rc = halo_tmap_4d(&td, D, N, oW, oH, tB, d_pitch, 64, pw, 32 / pw);
+  if (rc) return rc;
+  const long long kk = static_cast<long long>(kx) * ky * cg;
+  if (mode == 1) rc = make_tmap_bf16_2d(&tw, W, kk, w_rows, ldw, 64, BN);
+  else rc = make_tmap_bf16_2d(&tw, W, kk, w_rows, ldw, 64, 64);
+  if (rc) return rc;
+  if (mode == 1) return BN == 64 ? launch_halo<64, false>(tx, tw, td, p, stream) : launch_halo<128, false>(tx, tw, td, p, stream);
+  return BN == 64 ? launch_halo<64, true>(tx, tw, td, p, stream) : launch_halo<128, true>(tx, tw, td, p, stream);
+}

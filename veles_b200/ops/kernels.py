@@ -198,6 +198,42 @@ def conv_err_input(dy4, w, dx2, g, z=None, deriv=0, block_n=0):
                       w, n, Cg, dx2, dx2.shape[0], Cg, z=z, deriv=deriv, block_n=block_n)
 
 
+def _conv_halo(mode, t4, ky, kx, low_h, low_w, n_h, n_w, w, cg, out2, bias=None, act=ACT_LINEAR, z=None, deriv=0):
+    """Halo-tile implicit GEMM (csrc/conv_halo.cu); returns False when the geometry is not supported."""
+    B, H, W, C = t4.shape
+    pitch = t4.stride(2)
+    if not (t4.stride(3) == 1 and t4.stride(1) == W * pitch and t4.stride(0) == H * W * pitch):
+        return False
+    N = out2.shape[1]
+    _FLOPS[0] = 2.0 * B * n_h * n_w * N * ky * kx * C
+    rc = _lib.lib().vb_conv_halo_bf16(
+        c_int(mode), _p(t4), c_int(B), c_int(H), c_int(W), c_longlong(pitch), c_int(C), c_int(ky), c_int(kx),
+        c_int(low_h), c_int(low_w), c_int(n_h), c_int(n_w), _p(w), c_longlong(_ld(w)), c_int(w.shape[0]), c_int(cg),
+        _p(out2), c_longlong(_ld(out2)), c_int(N), _p(bias), c_int(act), _p(z),
+        c_longlong(_ld(z) if z is not None else 0), c_int(deriv), _stream())
+    if rc == 1:
+        return False
+    _lib.check(rc, "vb_conv_halo_bf16")
+    LAUNCHES[0] += 1
+    return True
+
+
+def conv_forward_halo(x4, w, out2, g, bias=None, act=ACT_LINEAR):
+    """``conv_forward`` through the halo-tile kernel (unit stride, OW + kx - 1 <= 64); False if unsupported."""
+    if g["sx"] != 1 or g["sy"] != 1 or out2.dtype != torch.bfloat16:
+        return False
+    return _conv_halo(1, x4, g["ky"], g["kx"], -g["pt"], -g["pl"], g["OH"], g["OW"], w, x4.shape[3], out2, bias=bias,
+                      act=act)
+
+
+def conv_err_input_halo(dy4, w, dx2, g, z=None, deriv=0):
+    """``conv_err_input`` through the halo-tile kernel; False if unsupported."""
+    if g["sx"] != 1 or g["sy"] != 1 or dx2.dtype != torch.bfloat16:
+        return False
+    return _conv_halo(2, dy4, g["ky"], g["kx"], -(g["ky"] - 1 - g["pt"]), -(g["kx"] - 1 - g["pl"]), g["H"], g["W"], w,
+                      dx2.shape[1], dx2, z=z, deriv=deriv)
+
+
 def conv_weight_grad(x4, dy2, gw, g, accumulate=True, split_k=0, alpha=1.0, block_n=0):
     """gw[n, ky*kx*Cg] (+)= dy2^T @ im2col(x4) with the im2col operand fetched by TMA (fp32 output)."""
     B, H, W, Cg = x4.shape
@@ -500,7 +536,7 @@ def _traced(fn):
     return wrap
 
 
-for _name in ("gemm", "gemm_tf32", "conv_forward", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
+for _name in ("gemm", "gemm_tf32", "conv_forward", "conv_forward_halo", "conv_err_input_halo", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
               "gather_minibatch", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
               "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",
