@@ -272,3 +272,24 @@ def test_results_and_package_export(tmp_path):
     assert any(n.endswith("100x784.npy") for n in names)
     wf.package_export(str(tmp_path / "mnist.tgz"), "tgz", precision=16)
     wf.launcher.stop()
+
+
+def test_reference_import_paths_alias_to_this_package():
+    """``import veles.x`` resolves to ``veles_b200.x`` (same module objects) so workflows and snapshots written
+    against the reference's module names load."""
+    import pickle
+    from veles_b200.compat import install_veles_alias
+    if not install_veles_alias():
+        import pytest
+        pytest.skip("a real 'veles' package is installed")
+    import veles
+    import veles_b200
+    assert veles.__name__ == "veles_b200"
+    from veles.znicz.all2all import All2AllTanh
+    from veles_b200.znicz import all2all
+    assert All2AllTanh is all2all.All2AllTanh
+    import veles.loader.fullbatch as fb
+    assert fb.__name__ == "veles_b200.loader.fullbatch"
+    cls = pickle.loads(b"cveles.mutable\nBool\n.")   # a pickle GLOBAL opcode naming the reference path
+    from veles_b200.mutable import Bool
+    assert cls is Bool

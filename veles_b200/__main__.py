@@ -266,6 +266,8 @@ class Main(Logger, CommandLineBase):
             self.warning("main() was not called by the workflow module's run()")
 
     def run(self):
+        from .compat import install_veles_alias
+        install_veles_alias()   # user workflows / snapshots may name the reference's module paths (veles.*)
         args = self._parse()
         if args.version:
             print("veles_b200", __version__)
