@@ -73,6 +73,10 @@ int vb_space_to_depth(const void* x, int dtype, void* xs, int B, int H, int W, i
 int vb_gather_cols(const void* src, int src_dtype, long long ld_src, void* dst, int dst_dtype, long long ld_dst,
                    const int* map, int rows, int cols, int accumulate, cudaStream_t stream);
 /* Test hooks: force the per-thread store epilogue; 0 cost model / 1 single-CTA tiles / 2 CTA-pair tiles. */
+/* Second phase of a split-K layer GEMM: out = act(acc + bias) [* f'(z)]; acc (fp32, what the K-splits reduce-added
+ * into) is re-zeroed when zero_acc. */
+int vb_bias_act_2d(float* acc, long long ld_acc, const float* bias, int act, const void* z, long long ldz, int deriv,
+                   void* out, int out_dtype, long long ld_out, int M, int N, int zero_acc, cudaStream_t stream);
 int vb_gemm_plan(int M, int N, int K, int b_mn_major, int can_split, int block_n, int* bn_out, int* split_out,
                  int* pair_out);
 int vb_gemm_set_dynamic_schedule(int on);

@@ -809,3 +809,22 @@ def test_fill_random_moments():
     assert abs(out.std().item() - 0.05 / 3 ** 0.5) < 1e-3
     k.fill_random(st, out, 1, 0.01)
     assert abs(out.mean().item()) < 1e-4 and abs(out.std().item() - 0.01) < 2e-4
+
+
+def test_two_phase_split_k_bias_activation_pass():
+    """Split-K GEMM into an fp32 scratch followed by vb_bias_act_2d equals the fused epilogue; the scratch is re-zeroed."""
+    k = K()
+    torch.manual_seed(9)
+    M, N, K_ = 256, 520, 4096
+    a = (torch.randn(M, K_, device=dev()) * 0.05).bfloat16()
+    b = (torch.randn(N, K_, device=dev()) * 0.05).bfloat16()
+    bias = torch.randn(N, device=dev())
+    z = torch.rand(M, N, device=dev()).bfloat16()
+    acc = torch.zeros(M, N, device=dev())
+    out = torch.empty(M, N, device=dev(), dtype=torch.bfloat16)
+    assert k.gemm_plan(M, N, K_)[1] >= 2
+    k.gemm(a, b, acc, accumulate=True, split_k=0)
+    k.bias_act(acc, out, bias=bias, act=1, z=z, deriv=2)
+    ref = 1.7159 * torch.tanh(0.6666 * (a.float() @ b.float().t() + bias)) * (z.float() * (1 - z.float()))
+    assert rel_err(out, ref) < 1e-2
+    assert (acc == 0).all()

@@ -451,6 +451,59 @@ extern "C" int vb_gd_update(float* w, float* grad, float* vel, float* acc, void*
   return 0;
 }
 
+// ---------------------------------------------------------------------------
+// Second phase of a split-K layer GEMM: out = f(acc + bias) [* f'(z)], acc is the fp32 matrix the K-splits
+// reduce-added into; it is zeroed again on the way out so the next step can accumulate into it.
+// ---------------------------------------------------------------------------
+template <typename DST>
+__global__ void bias_act_kernel(float* __restrict__ acc, long long ld_acc, const float* __restrict__ bias, int act,
+                                const __nv_bfloat16* __restrict__ z, long long ldz, int deriv, DST* __restrict__ out,
+                                long long ld_out, int M, int N, int zero_acc) {
+  const int n4 = N >> 2;   // N % 4 == 0 (checked by the launcher)
+  const long long total = static_cast<long long>(M) * n4;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(t / n4);
+    const int c = static_cast<int>(t - static_cast<long long>(r) * n4) << 2;
+    float4* ap = reinterpret_cast<float4*>(acc + r * ld_acc + c);
+    float4 v = *ap;
+    if (zero_acc) *ap = make_float4(0.f, 0.f, 0.f, 0.f);
+    float f[4] = {v.x, v.y, v.z, v.w};
+    if (bias != nullptr) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(bias + c));
+      f[0] += b.x; f[1] += b.y; f[2] += b.z; f[3] += b.w;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) f[q] = act_forward(act, f[q]);
+    if (z != nullptr) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) f[q] *= act_deriv_from_output(deriv, __bfloat162float(z[r * ldz + c + q]));
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) out[r * ld_out + c + q] = from_f<DST>(f[q]);
+  }
+}
+
+extern "C" int vb_bias_act_2d(float* acc, long long ld_acc, const float* bias, int act, const void* z, long long ldz,
+                              int deriv, void* out, int out_dtype, long long ld_out, int M, int N, int zero_acc,
+                              cudaStream_t s) {
+  if (M == 0 || N == 0) return 0;
+  VB_REQUIRE(N % 4 == 0 && ld_acc % 4 == 0 && (reinterpret_cast<uintptr_t>(acc) & 15) == 0 &&
+                 (bias == nullptr || (reinterpret_cast<uintptr_t>(bias) & 15) == 0),
+             "vb_bias_act_2d: N and the accumulator pitch must be multiples of 4, pointers 16-byte aligned");
+  const int g = grid_for(static_cast<long long>(M) * (N >> 2), 256, 2);
+  if (out_dtype == DT_F32)
+    bias_act_kernel<float><<<g, 256, 0, s>>>(acc, ld_acc, bias, act, static_cast<const __nv_bfloat16*>(z), ldz, deriv,
+                                             static_cast<float*>(out), ld_out, M, N, zero_acc);
+  else if (out_dtype == DT_BF16)
+    bias_act_kernel<__nv_bfloat16><<<g, 256, 0, s>>>(acc, ld_acc, bias, act, static_cast<const __nv_bfloat16*>(z), ldz,
+                                                     deriv, static_cast<__nv_bfloat16*>(out), ld_out, M, N, zero_acc);
+  else
+    VB_REQUIRE(false, "vb_bias_act_2d: output dtype must be f32/bf16");
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int vb_cast(const void* in, int in_dtype, void* out, int out_dtype, long long n, cudaStream_t s) {
   if (n == 0) return 0;
   const int g = grid_for(n, 256, 4);

@@ -78,6 +78,18 @@ def set_pair_mode(mode):
     _lib.check(_lib.lib().vb_gemm_set_pair_mode(c_int(int(mode))), "vb_gemm_set_pair_mode")
 
 
+def bias_act(acc, out, bias=None, act=ACT_LINEAR, z=None, deriv=0, zero_acc=True):
+    """out = act(acc + bias) [* f'(z)]; ``acc`` is the fp32 result of a split-K GEMM and is zeroed again on the way."""
+    assert acc.dtype == torch.float32 and acc.shape == out.shape
+    rc = _lib.lib().vb_bias_act_2d(_p(acc), c_longlong(_ld(acc)), _p(bias), c_int(act), _p(z),
+                                   c_longlong(_ld(z) if z is not None else 0), c_int(deriv), _p(out), c_int(_dt(out)),
+                                   c_longlong(_ld(out)), c_int(acc.shape[0]), c_int(acc.shape[1]),
+                                   c_int(int(zero_acc)), _stream())
+    _lib.check(rc, "vb_bias_act_2d")
+    LAUNCHES[0] += 1
+    return out
+
+
 def gemm_plan(M, N, K, b_mn=False, can_split=True, block_n=0):
     """(tile width, split-K factor, uses CTA pairs) the GEMM scheduler picks for this problem."""
     bn, split, pair = c_int(0), c_int(0), c_int(0)
@@ -536,7 +548,7 @@ def _traced(fn):
     return wrap
 
 
-for _name in ("gemm", "gemm_tf32", "conv_forward", "conv_forward_halo", "conv_err_input_halo", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
+for _name in ("gemm", "bias_act", "gemm_tf32", "conv_forward", "conv_forward_halo", "conv_err_input_halo", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
               "gather_minibatch", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
               "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",

@@ -102,6 +102,12 @@ class GradientDescent(GradientDescentBase):
         # dW = dY^T X either accumulates into a zeroed buffer (split-K over the batch) or, when the scheduler would
         # not split, is plainly stored: the latter skips the read-modify-write at L2 and the re-zeroing pass.
         n_in = self.input.size // self.input.shape[0]
+        # err_input = dY W with few M tiles: same two-phase split-K as the forward pass
+        self.ei_acc_ = None
+        if (getattr(self.forward, "TWO_PHASE_SPLIT_K", False) and self.need_err_input and not self.tf32_mode()
+                and n_in % 4 == 0
+                and kernels.gemm_plan(self.err_output.shape[0], n_in, n_out, b_mn=True)[1] >= 2):
+            self.ei_acc_ = torch.zeros(self.err_output.shape[0], n_in, dtype=torch.float32, device=dev.torch_device)
         self.dw_store_ = (self.dp_group_ is None and self.apply_gradient and not self.tf32_mode() and
                           kernels.gemm_plan(n_out, n_in, self.err_output.shape[0], b_mn=True)[1] == 1)
 
@@ -176,8 +182,13 @@ class GradientDescent(GradientDescentBase):
         if self.need_err_input:
             ei = self.err_input.devmem
             ei2 = ei if ei.dim() == 2 else ei.reshape(ei.shape[0], -1)
-            kernels.gemm(eo, w_bf16, ei2, b_mn=True, z=x if self.prev_activation else None,
-                         deriv=self.prev_activation, b_peers=getattr(self.forward, "peer_weights_", None))
+            peers = getattr(self.forward, "peer_weights_", None)
+            if self.ei_acc_ is not None and peers is None:
+                kernels.gemm(eo, w_bf16, self.ei_acc_, b_mn=True, accumulate=True, split_k=0)
+                kernels.bias_act(self.ei_acc_, ei2, z=x if self.prev_activation else None, deriv=self.prev_activation)
+            else:
+                kernels.gemm(eo, w_bf16, ei2, b_mn=True, z=x if self.prev_activation else None,
+                             deriv=self.prev_activation, b_peers=peers)
             self.err_input.mark_device_written()
         gw_t, gb_t = self.grad_tensors()
         gw = gw_t.view(w_bf16.shape[0], -1)
