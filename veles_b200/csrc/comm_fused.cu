@@ -107,11 +107,11 @@ __device__ __forceinline__ bool wait_all(const FusedParams& p, int slot, uint32_
   return true;
 }
 
-// Footprint: 128 threads, <= 128 registers, NO shared memory - chosen so that one of these CTAs fits on an SM next
-// to a resident tcgen05 GEMM CTA (320 threads x 152 registers, 226 KB of the 228 KB of shared memory): the update
-// kernel then overlaps the backward GEMMs on the same SMs instead of taking SMs away from their persistent grids.
+// Footprint: 256 threads x <= 128 registers x 4 independent 16-byte chains, no shared memory.  (A 128-thread
+// variant sized to co-reside with a tcgen05 GEMM CTA was measured slower: 5.1 vs 4.2 ms/step on 4 GPUs - too few
+// loads in flight per CTA for the NVLink round trip.)
 template <bool MULTIMEM>
-__global__ void __launch_bounds__(128) fused_allreduce_gd_kernel(const FusedParams p) {
+__global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedParams p) {
   const int ready_slot = (p.channel * 2 + 0) * MAX_WORLD;
   const int done_slot = (p.channel * 2 + 1) * MAX_WORLD;
   // identical in every CTA: epochs[] is bumped by the LAST CTA to finish, i.e. after every CTA has read it here
@@ -325,9 +325,9 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
   if (n_ctas <= 0) n_ctas = 32;
   if (use_multimem)
-    fused_allreduce_gd_kernel<true><<<n_ctas, 128, 0, stream>>>(p);
+    fused_allreduce_gd_kernel<true><<<n_ctas, 256, 0, stream>>>(p);
   else
-    fused_allreduce_gd_kernel<false><<<n_ctas, 128, 0, stream>>>(p);
+    fused_allreduce_gd_kernel<false><<<n_ctas, 256, 0, stream>>>(p);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -433,7 +433,7 @@ __device__ __forceinline__ void load24(const __nv_bfloat16* row, int g, int T, f
 __device__ __forceinline__ float lrn_pow_neg(float s, float beta, bool beta34) {
   if (beta34) {
     const float r = rsqrtf(s);
-    return r * sqrtf(r);
+    return r * r * rsqrtf(r);   // r^1.5 with two MUFU.RSQ (sqrtf would take the slow IEEE path)
   }
   return __powf(s, -beta);
 }
@@ -441,7 +441,7 @@ __device__ __forceinline__ float lrn_pow_neg_inv(float s, float beta, bool beta3
   if (beta34) {
     const float r = rsqrtf(s);
     inv_s = r * r;
-    return r * sqrtf(r);
+    return inv_s * rsqrtf(r);
   }
   inv_s = __fdividef(1.0f, s);
   return __powf(s, -beta);

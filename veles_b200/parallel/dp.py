@@ -26,7 +26,7 @@ MAX_WORLD = 8
 
 
 class DataParallel(object):
-    def __init__(self, mode="fused", n_ctas=96, timeout_s=20.0, use_multimem=None, shard_master=True,
+    def __init__(self, mode="fused", n_ctas=64, timeout_s=20.0, use_multimem=None, shard_master=True,
                  weight_delivery="multicast"):
         import torch
         import torch.distributed as dist
