@@ -195,7 +195,8 @@ __global__ void col2im_vec8_kernel(const __nv_bfloat16* __restrict__ dcols, __nv
 // ---------------------------------------------------------------------------------------------
 // Pooling, 8 channels per thread (C % 8 == 0), bf16.
 // ---------------------------------------------------------------------------------------------
-__global__ void pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+__global__ void __launch_bounds__(128, 8)   // <= 64 registers: latency-bound gather, occupancy matters
+pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                          int* __restrict__ offs, uint8_t* __restrict__ offs8, const FastPoolGeom g) {
   const unsigned C8 = g.C >> 3;
   const long long total = static_cast<long long>(g.B) * g.OH * g.OW * C8;   // < 2^31 (checked by the launcher)
