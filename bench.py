@@ -43,6 +43,8 @@ def parse():
     p.add_argument("--comm-ctas", type=int, default=64, help="N>1: CTAs of the fused all-reduce+GD kernel")
     p.add_argument("--gemm-schedule", default="static", choices=["static", "clc"],
                    help="GEMM tile scheduling: static persistent round-robin, or cluster-launch-control work stealing")
+    p.add_argument("--split-handshake", action="store_true",
+                   help="N>1: await the peers' ready flags in a separate 1-CTA launch ahead of the worker CTAs")
     p.add_argument("--replicate-master", action="store_true", help="N>1: also broadcast the fp32 master weights each step")
     return p.parse_args()
 
@@ -87,7 +89,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from veles_b200.parallel.dp import DataParallel
         dp = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
-                          shard_master=not args.replicate_master, n_ctas=args.comm_ctas)
+                          shard_master=not args.replicate_master, n_ctas=args.comm_ctas,
+                          split_handshake=args.split_handshake)
 
     from veles_b200.backends import B200Device
     from veles_b200.trainer import Trainer
@@ -152,7 +155,8 @@ def main():
         if world > 1:
             from veles_b200.parallel.dp import DataParallel
             dp2 = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
-                               shard_master=not args.replicate_master, n_ctas=args.comm_ctas)
+                               shard_master=not args.replicate_master, n_ctas=args.comm_ctas,
+                               split_handshake=args.split_handshake)
         tr = Trainer(args.model, minibatch_size=B, device=device, use_graph=use_graph, streaming=True,
                      data_parallel=dp2)
         shape = cfg["sample_shape"]

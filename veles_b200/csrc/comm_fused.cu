@@ -57,6 +57,7 @@ struct FusedParams {
   int* status;               // local: set non-zero on a synchronisation timeout
   float grad_scale;
   long long timeout_cycles;
+  int phase;         // 0: handshake + work in one launch; 1: ready handshake only (1 CTA); 2: work only
   int bcast_master;  // 0: the updated fp32 master slice stays on its owner (gathered on demand at epoch ends)
   int bcast_shadow;  // 0: the bf16 shadow slice stays on its owner; GEMMs fetch it through peer tensor maps
 };
@@ -117,7 +118,9 @@ __global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedPara
   // identical in every CTA: epochs[] is bumped by the LAST CTA to finish, i.e. after every CTA has read it here
   const uint32_t epoch = p.epochs[p.channel] + 1;
   int my_ok = 1;
-  if (threadIdx.x == 0) {
+  if (p.phase == 2) {
+    my_ok = (*reinterpret_cast<volatile int*>(p.status) == 0) ? 1 : 0;   // the handshake launch may have timed out
+  } else if (threadIdx.x == 0) {
     if (blockIdx.x == 0) {
       // my gradients for this segment are complete (stream order): tell every peer
       __threadfence_system();
@@ -127,6 +130,10 @@ __global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedPara
     my_ok = wait_all(p, ready_slot, epoch) ? 1 : 0;
   }
   const bool ok = __syncthreads_and(my_ok) != 0;   // barrier + predicate broadcast without shared memory
+  if (p.phase == 1) {   // handshake-only launch: one small CTA waits for the peers so that the worker CTAs never
+    if (!ok && threadIdx.x == 0) atomicExch(p.status, 1 + p.channel);   // hold SMs while ranks are skewed
+    return;
+  }
 
   if (ok) {
     const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
@@ -278,6 +285,7 @@ using namespace vb;
 //   *_peer: world device pointers each
 //   use_multimem: bit 0 = NVLS multimem path; bit 1 = keep the fp32 master slice local (no broadcast);
 //                 bit 2 = keep the bf16 shadow slice local (flat-shadow segments only; peer-TMA weight delivery)
+//                 bit 3 = wait for the peers' gradients in a separate 1-CTA launch ahead of the worker CTAs
 extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg, const long long* segs,
                                      const float* hyper, float* grads_local, float* grads_mc, float** grads_peer,
                                      float* grads_other_local, float* weights_local, float* weights_mc,
@@ -286,6 +294,7 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
                                      unsigned int* epochs, unsigned int* cta_counter, int* status, float grad_scale,
                                      int n_ctas, int use_multimem, double timeout_s, cudaStream_t stream) {
   const int local_master = (use_multimem >> 1) & 1, local_shadow = (use_multimem >> 2) & 1;
+  const int split_handshake = (use_multimem >> 3) & 1;
   use_multimem &= 1;
   VB_REQUIRE(world >= 2 && world <= MAX_WORLD, "vb_fused_allreduce_gd: world size %d not in [2,%d]", world, MAX_WORLD);
   VB_REQUIRE(nseg >= 1 && nseg <= MAX_SEGS, "vb_fused_allreduce_gd: %d segments (max %d per launch)", nseg, MAX_SEGS);
@@ -324,6 +333,14 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   p.bcast_shadow = !local_shadow;
   p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
   if (n_ctas <= 0) n_ctas = 32;
+  if (split_handshake) {
+    p.phase = 1;
+    fused_allreduce_gd_kernel<false><<<1, 32, 0, stream>>>(p);
+    VB_CHECK_CUDA(cudaGetLastError());
+    p.phase = 2;
+  } else {
+    p.phase = 0;
+  }
   if (use_multimem)
     fused_allreduce_gd_kernel<true><<<n_ctas, 256, 0, stream>>>(p);
   else

@@ -27,7 +27,7 @@ MAX_WORLD = 8
 
 class DataParallel(object):
     def __init__(self, mode="fused", n_ctas=64, timeout_s=20.0, use_multimem=None, shard_master=True,
-                 weight_delivery="multicast"):
+                 weight_delivery="multicast", split_handshake=False):
         import torch
         import torch.distributed as dist
         if not dist.is_initialized():
@@ -49,6 +49,9 @@ class DataParallel(object):
         if weight_delivery not in ("multicast", "peer_tma"):
             raise ValueError("weight_delivery must be 'multicast' or 'peer_tma'")
         self.weight_delivery = weight_delivery
+        # split_handshake: a 1-CTA launch waits for the peers' "gradients ready" flags, THEN the worker CTAs start,
+        # so rank skew never parks 64 CTAs on SMs the backward GEMMs could use
+        self.split_handshake = bool(split_handshake)
         self.master_stale = False
         self.parity = 0
         self.grad_scale = 1.0      # 1/world when every rank normalised by its LOCAL batch size
@@ -250,11 +253,12 @@ class DataParallel(object):
                 c_void_p(self.epochs.data_ptr()), c_void_p(self.cta_counter.data_ptr()),
                 c_void_p(self.status.data_ptr()), c_float(self.grad_scale), c_int(info["n_ctas"]),
                 c_int((1 if self.use_multimem else 0) | (2 if self.shard_master else 0) |
-                      (4 if info.get("peer_shadow") else 0)), c_double(self.timeout_s),
+                      (4 if info.get("peer_shadow") else 0) | (8 if self.split_handshake else 0)),
+                c_double(self.timeout_s),
                 c_void_p(self.comm_stream.cuda_stream))
             _lib.check(rc, "vb_fused_allreduce_gd")
             from ..ops import kernels
-            kernels.LAUNCHES[0] += 1
+            kernels.LAUNCHES[0] += 2 if self.split_handshake else 1
             done = torch.cuda.Event()
             done.record(self.comm_stream)
         self._pending_events.append(done)
