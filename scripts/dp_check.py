@@ -87,7 +87,9 @@ def main():
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.barrier()
     dist.destroy_process_group()
-    print("DP_CHECK", "OK" if int(flag.item()) else "FAILED", flush=True)
+    if rank == 0:   # one writer: concurrent prints of several ranks interleave
+        sys.stdout.write("DP_CHECK %s\n" % ("OK" if int(flag.item()) else "FAILED"))
+        sys.stdout.flush()
     sys.exit(0 if int(flag.item()) else 1)
 
 

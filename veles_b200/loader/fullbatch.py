@@ -209,10 +209,35 @@ class FullBatchLoader(Loader):
             self._shuffled_version_ = self._shuffle_count_
         return self._shuffled_dev_
 
+    def _fill_shard_host(self, start_offset, count):
+        """numpy backend, data parallel: materialise this rank's contiguous slice of the global minibatch."""
+        per = self.local_minibatch_size
+        lo = min(count, self.shard_rank * per)
+        hi = min(count, lo + per)
+        n = hi - lo
+        self.local_count = n
+        idx = self.shuffled_indices.mem[start_offset + lo:start_offset + hi]
+        for a in (self.minibatch_indices, self.minibatch_data, self.minibatch_labels):
+            if a:
+                a.map_invalidate()
+        self.minibatch_indices.mem[:n] = idx
+        self.minibatch_indices.mem[n:] = -1
+        self.minibatch_data.mem[:n] = self.original_data.mem[idx]
+        self.minibatch_data.mem[n:] = 0
+        if self._has_labels:
+            self.minibatch_labels.mem[:n] = self._mapped_original_labels_.mem[idx]
+            self.minibatch_labels.mem[n:] = -1
+        targets = getattr(self, "original_targets", None)
+        if targets is not None and targets:
+            self._minibatch_targets.map_invalidate()
+            self._minibatch_targets.mem[:n] = targets.mem[idx]
+            self._minibatch_targets.mem[n:] = 0
+        return True
+
     def fill_indices(self, start_offset, count):
         if not self.on_device_data or self.force_numpy_data:
             if self.shard_world > 1:
-                raise LoaderError("Rank-sharded serving requires device-resident data")
+                return self._fill_shard_host(start_offset, count)
             return super(FullBatchLoader, self).fill_indices(start_offset, count)
         from ..ops import kernels
         # this rank's contiguous slice of the global minibatch
@@ -276,7 +301,7 @@ class FullBatchLoaderMSEMixin(LoaderMSEMixin):
 
     def fill_indices(self, start_offset, count):
         done = super(FullBatchLoaderMSEMixin, self).fill_indices(start_offset, count)
-        if done:
+        if done and self.on_device_data and not self.force_numpy_data:   # (the host shard path fills targets itself)
             from ..ops import kernels
             if self.shard_world > 1:
                 per = self.local_minibatch_size

@@ -10,6 +10,9 @@ shadow multicast-stored back to every rank, launched on a side stream as soon as
 backward GEMMs are enqueued so it overlaps the rest of the backward pass.
 
 ``mode="nccl"`` is the conventional baseline (NCCL all-reduce, then the local GD kernel).
+``mode="host"`` runs the same protocol for the numpy backend (gradients all-reduced as host arrays over whatever
+backend the process group has, normally gloo): the CPU oracle of the fused kernel's math and the way the host-side
+logic (loader sharding, counter reductions, scheduling) is tested without GPUs.
 
 torch.distributed is used only for plumbing: rendezvous of symmetric-memory slabs
 (``torch.distributed._symmetric_memory``), epoch-boundary counter sums, barriers.
@@ -69,6 +72,8 @@ class DataParallel(object):
     def attach(self, wf):
         """Before ``wf.initialize``: route the exchanged arena kinds into symmetric memory."""
         self.wf = wf
+        if self.mode not in ("fused", "nccl", "host"):
+            raise ValueError("DataParallel mode must be 'fused', 'nccl' or 'host'")
         if self.mode == "fused":
             wf.arena_allocator_ = self._allocate
         wf.dp_group_ = self
@@ -87,6 +92,14 @@ class DataParallel(object):
         import torch
         import torch.distributed._symmetric_memory as symm_mem
         dev = wf.device
+        if self.mode == "host":
+            for gd in wf.gds:
+                if hasattr(gd, "gradient_weights") and gd.weights is not None and gd.weights:
+                    gd.dp_group_ = self
+                    self.units.append(gd)
+            if hasattr(wf, "decision") and wf.decision is not None:
+                wf.decision.dp_group = self
+            return
         self.comm_stream = torch.cuda.Stream(device=dev.torch_device)
         self.arena = wf.get_arena(dev)
         for gd in wf.gds:
@@ -267,8 +280,22 @@ class DataParallel(object):
         if gd.bias is not None and gd.bias:
             gd.bias.mark_device_written()
 
+    def allreduce_host(self, grad):
+        """Host mode: sum a numpy gradient over the ranks (scaled like the device kernel scales it)."""
+        import torch
+        if grad is None:
+            return None
+        t = torch.from_numpy(numpy.ascontiguousarray(grad, dtype=numpy.float32).copy())
+        self._dist.all_reduce(t)
+        out = t.numpy()
+        if self.grad_scale != 1.0:
+            out = out * numpy.float32(self.grad_scale)
+        return out.reshape(grad.shape)
+
     def finish_step(self):
         """Join the comm stream into the compute stream and flip the gradient parity."""
+        if self.mode == "host":
+            return
         import torch
         main = torch.cuda.current_stream()
         for ev in self._pending_events:
@@ -331,17 +358,20 @@ class DataParallel(object):
     def sum_counters(self, vals, loss):
         import torch
         self.sync_master()   # class boundary: the host (Decision, Snapshotter, plotters) may read the weights now
-        t = torch.tensor(list(map(float, vals)) + [float(loss)], dtype=torch.float64, device="cuda")
+        t = torch.tensor(list(map(float, vals)) + [float(loss)], dtype=torch.float64, device=self._reduce_device())
         self._dist.all_reduce(t)
         out = t.cpu().numpy()
         return numpy.round(out[:-1]).astype(numpy.int64), float(out[-1])
 
     def max_min(self, mx, mn):
         import torch
-        t = torch.tensor([mx, -mn], dtype=torch.float64, device="cuda")
+        t = torch.tensor([mx, -mn], dtype=torch.float64, device=self._reduce_device())
         self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX)
         out = t.cpu().numpy()
         return float(out[0]), float(-out[1])
+
+    def _reduce_device(self):
+        return "cpu" if self.mode == "host" else "cuda"
 
     def barrier(self):
         self._dist.barrier()

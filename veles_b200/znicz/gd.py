@@ -70,6 +70,7 @@ class GradientDescent(GradientDescentBase):
         gw = eo.T.dot(x)
         if transposed:
             gw = gw.T
+        gw, = self.dp_reduce_host(gw)
         self.gradient_weights.reset(gw.astype(numpy.float32))
         if self.apply_gradient:
             self.numpy_update(w, gw, self.gradient_weights_with_moment.mem,
@@ -78,6 +79,7 @@ class GradientDescent(GradientDescentBase):
         if self.bias is not None and self.bias:
             self.bias.map_write()
             gb = eo.sum(axis=0)
+            gb, = self.dp_reduce_host(gb)
             self.gradient_bias.reset(gb.astype(numpy.float32))
             if self.apply_gradient:
                 self.numpy_update(self.bias.mem, gb, self.gradient_bias_with_moment.mem,

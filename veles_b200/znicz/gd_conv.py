@@ -72,6 +72,7 @@ class GradientDescentConv(GradientDescentBase):
                 ei = ei * act_deriv_numpy(self.prev_activation, x)
             self.err_input.map_invalidate()
             self.err_input.mem[...] = ei.reshape(self.err_input.shape)
+        gw, = self.dp_reduce_host(gw)
         self.gradient_weights.reset(gw.astype(numpy.float32))
         if self.apply_gradient:
             self.numpy_update(w, gw, self.gradient_weights_with_moment.mem,
@@ -80,6 +81,7 @@ class GradientDescentConv(GradientDescentBase):
         if self.bias is not None and self.bias:
             self.bias.map_write()
             gb = eo.sum(axis=0)
+            gb, = self.dp_reduce_host(gb)
             self.gradient_bias.reset(gb.astype(numpy.float32))
             if self.apply_gradient:
                 self.numpy_update(self.bias.mem, gb, self.gradient_bias_with_moment.mem,

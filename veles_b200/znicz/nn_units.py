@@ -477,6 +477,13 @@ class GradientDescentBase(GDBase):
                         arr.initialize(self.device_, storage=arena.alloc(kind, "%s.%s" % (self.name, kind),
                                                                          arr.size, torch.float32))
 
+    def dp_reduce_host(self, *grads):
+        """numpy backend under a host-mode DataParallel group: all-reduce the freshly computed gradients."""
+        dp = self.dp_group_
+        if dp is None or getattr(dp, "mode", None) != "host":
+            return grads
+        return tuple(dp.allreduce_host(g) for g in grads)
+
     def grad_tensors(self):
         """(dW, db) device tensors the backward GEMMs accumulate into this step."""
         if self.dp_group_ is not None:
