@@ -9,7 +9,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "veles_b200", "lib", "libveles_b200.so")
-KEYS = ["UTCHMMA", "UTCQMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UTMAPF", "UBLKCP", "SYNCS",
+KEYS = ["UTCHMMA", "UTCQMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UTMAPF", "UBLKCP", "UGETNEXTWORKID", "SYNCS",
         "HMMA", "MULTIMEM", "LDG", "STG", "RED", "ATOM", "LDS", "STS", "MUFU", "BAR", "UCGABAR", "MEMBAR"]
 
 
