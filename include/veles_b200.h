@@ -58,6 +58,13 @@ int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW, long long
                       int other_rows, int cg, void* D, long long ldd, int M, int N, const float* bias, int act,
                       int out_fp32, int accumulate, const void* Z, long long ldz, int deriv, float alpha, int split_k,
                       int block_n, cudaStream_t stream);
+/* All groups of a grouped convolution in ONE launch (modes 1, 2): T / other / D are the whole tensors, t_ch and N the
+ * total widths; per-group channel and kernel counts must be multiples of 64. */
+int vb_conv_gemm_grouped_bf16(int mode, int groups, const void* T, int tB, int tH, int tW, long long t_pitch, int t_ch,
+                              int ky, int kx, int sy, int sx, int low_h, int low_w, int oH, int oW, const void* other,
+                              long long ld_other, int other_rows, int cg, void* D, long long ldd, int M, int N,
+                              const float* bias, int act, int out_fp32, const void* Z, long long ldz, int deriv,
+                              int block_n, cudaStream_t stream);
 /* Halo-tile variant for unit-stride layers (OW + kx - 1 <= 64): every 64-channel block of the walked tensor is loaded
  * once per output tile (4-D TMA box with halo) and all ky*kx taps are issued from that shared-memory tile.
  * mode 1 forward / 2 err_input as above; D is [tB, oH, oW, N] with pixel pitch d_pitch.  Returns 1 when unsupported. */

@@ -828,3 +828,30 @@ def test_two_phase_split_k_bias_activation_pass():
     ref = 1.7159 * torch.tanh(0.6666 * (a.float() @ b.float().t() + bias)) * (z.float() * (1 - z.float()))
     assert rel_err(out, ref) < 1e-2
     assert (acc == 0).all()
+
+
+@pytest.mark.parametrize("C,n,G", [(384, 384, 2), (384, 256, 2), (256, 512, 4)])
+def test_grouped_conv_single_launch(C, n, G, pair_mode):
+    """All groups of a grouped convolution in one implicit-GEMM launch (tile -> group) vs torch conv2d."""
+    k = K()
+    torch.manual_seed(C + n + G)
+    B, H, W, ky, kx, p = 3, 13, 13, 3, 3, 1
+    Cg = C // G
+    assert k.grouped_conv_ok(C, n, G)
+    g = dict(OH=H, OW=W, ky=ky, kx=kx, sy=1, sx=1, pt=p, pl=p, H=H, W=W)
+    x = (torch.randn(B, H, W, C, device=dev()) * 0.5).bfloat16()
+    w = (torch.randn(n, ky * kx * Cg, device=dev()) * 0.1).bfloat16()
+    bias = torch.randn(n, device=dev())
+    xr = x.float().requires_grad_(True)
+    yr = torch.relu(_conv_ref(xr, w.float(), n, ky, kx, 1, 1, p, p, p, p, G) + bias)
+    y = torch.full((B * H * W + 2, n), float("nan"), device=dev(), dtype=torch.bfloat16)
+    k.conv_forward_grouped(x, w, y[:B * H * W], g, G, bias=bias, act=4)
+    assert rel_err(y[:B * H * W], yr.detach().reshape(-1, n)) < 1e-2
+    assert torch.isnan(y[B * H * W:].float()).all()
+    e = (torch.randn(B, H, W, n, device=dev()) * 0.3).bfloat16()
+    _conv_ref(xr, w.float(), n, ky, kx, 1, 1, p, p, p, p, G).backward(e.float())
+    dx = torch.full((B * H * W + 2, C), float("nan"), device=dev(), dtype=torch.bfloat16)
+    k.conv_err_input_grouped(e, w, dx[:B * H * W], g, G, z=x.reshape(-1, C), deriv=1)
+    ref = xr.grad * (0.6666 * (1.7159 - x.float() ** 2 / 1.7159))
+    assert rel_err(dx[:B * H * W], ref.reshape(-1, C)) < 1e-2
+    assert torch.isnan(dx[B * H * W:].float()).all()

@@ -49,6 +49,8 @@ struct ConvParams {
   int low_w, low_h;  // bounding-box lower corner (= -pad; -(k-1-pad) for mode 2)
   int cblocks;       // 64-channel blocks per tap along the im2col tensor's channel dimension
   int cg;            // weight-matrix columns per tap
+  int nbpg;          // grouped convolution in one launch: N tiles per group (0 = not grouped); tile nb belongs to
+                     // group nb / nbpg, whose im2col channels start at group * cblocks * 64
 };
 
 // Row-sharded B operand ("peer-TMA weight delivery"): rank r of a data-parallel group owns rows
@@ -317,15 +319,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             const int cb = kb - tap * p.cv.cblocks;
             const int r = tap / p.cv.kx;
             const int sx_tap = tap - r * p.cv.kx;
-            ldi(sa, &tma_a, cb * 64, a_w, a_h, a_n, sx_tap, r);
+            // grouped layers in one launch: this N tile's group selects the channel range of the walked tensor
+            const int grp = p.cv.nbpg > 0 ? nb / p.cv.nbpg : 0;
+            const int ch0 = (grp * p.cv.cblocks + cb) * 64;
+            ldi(sa, &tma_a, ch0, a_w, a_h, a_n, sx_tap, r);
             if (p.cv.mode == 1) {
               ld2(sb, &tma_b, tap * p.cv.cg + cb * 64, n_base);
             } else {
               // dX: the dY pixel reached through offset (s', r') pairs with filter tap (ky-1-r', kx-1-s')
               const int wtap = (p.cv.ky - 1 - r) * p.cv.kx + (p.cv.kx - 1 - sx_tap);
+              const int n_local = n_base - grp * p.cv.nbpg * BN;   // column inside the group's [kernels, taps*cg] slab
 #pragma unroll
               for (int c = 0; c < BN_LOAD / 64; ++c)
-                ld2(sb + c * (BLOCK_K * 128), &tma_b, wtap * p.cv.cg + n_base + c * 64, cb * 64);
+                ld2(sb + c * (BLOCK_K * 128), &tma_b, wtap * p.cv.cg + n_local + c * 64, ch0);
             }
           }
           if (++stage == STAGES) {
@@ -1007,12 +1013,12 @@ extern "C" int vb_gemm_bf16_sharded_b(const void* A, long long lda, int a_mn_maj
 // tB x tH x tW pixels, `t_pitch` elements between pixels, `t_ch` channels visible.  `other` is
 // the weight matrix [rows, taps*cg] (modes 1, 2) or dY [pixels, M] (mode 3).
 // ----------------------------------------------------------------------------
-extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW, long long t_pitch, int t_ch,
-                                 int ky, int kx, int sy, int sx, int low_h, int low_w, int oH, int oW,
-                                 const void* other, long long ld_other, int other_rows, int cg, void* D,
-                                 long long ldd, int M, int N, const float* bias, int act, int out_fp32,
-                                 int accumulate, const void* Z, long long ldz, int deriv, float alpha,
-                                 int split_k, int block_n, cudaStream_t stream) {
+static int conv_gemm_impl(int mode, const void* T, int tB, int tH, int tW, long long t_pitch, int t_ch,
+                          int ky, int kx, int sy, int sx, int low_h, int low_w, int oH, int oW,
+                          const void* other, long long ld_other, int other_rows, int cg, void* D,
+                          long long ldd, int M, int N, const float* bias, int act, int out_fp32,
+                          int accumulate, const void* Z, long long ldz, int deriv, float alpha,
+                          int split_k, int block_n, int groups, cudaStream_t stream) {
   VB_REQUIRE(mode >= 1 && mode <= 3, "vb_conv_gemm_bf16: mode must be 1 (forward), 2 (err_input) or 3 (weights)");
   VB_REQUIRE(tB > 0 && tH > 0 && tW > 0 && oH > 0 && oW > 0 && M > 0 && N > 0, "vb_conv_gemm_bf16: empty problem");
   VB_REQUIRE(t_ch % 8 == 0 && t_pitch % 8 == 0, "vb_conv_gemm_bf16: channels (%d) and pixel pitch (%lld) must be multiples of 8", t_ch, t_pitch);
@@ -1022,7 +1028,14 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
   const long long pixels = static_cast<long long>(tB) * oH * oW;
   VB_REQUIRE(pixels < (1LL << 31), "vb_conv_gemm_bf16: too many pixels");
   const int taps = kx * ky;
-  const int cblocks = ceil_div(t_ch, 64);
+  VB_REQUIRE(groups >= 1, "vb_conv_gemm_bf16: groups must be >= 1");
+  if (groups > 1) {
+    // all groups in one launch: T / other / D are the WHOLE tensors, N the total output width
+    VB_REQUIRE(mode != 3, "vb_conv_gemm_bf16: grouped launches cover forward and err_input");
+    VB_REQUIRE(t_ch % groups == 0 && (t_ch / groups) % 64 == 0 && N % groups == 0 && (N / groups) % 64 == 0,
+               "vb_conv_gemm_bf16: grouped launch needs per-group channel counts that are multiples of 64");
+  }
+  const int cblocks = ceil_div(t_ch / groups, 64);
   GemmParams p;
   memset(&p, 0, sizeof(p));
   p.cv.mode = mode; p.cv.kx = kx; p.cv.ky = ky; p.cv.OW = oW; p.cv.OH = oH; p.cv.sx = sx; p.cv.sy = sy;
@@ -1048,7 +1061,22 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
     const bool auto_split = (split_k == 0);
     if (auto_split) split_k = 1;
     choose_config(M, n_virtual, kb_total, can_split, auto_split, mode != 1, &BN, &split_k, &pair);
+    if (groups > 1 && (N / groups) % BN != 0) {
+      // a tile may not straddle two groups: widest tile that divides the per-group width
+      const int npg = N / groups;
+      static const int widths[4] = {256, 192, 128, 64};
+      for (int i = 0; i < 4; ++i) {
+        if (npg % widths[i] != 0) continue;
+        BN = widths[i];
+        int sk = auto_split ? 1 : split_k;
+        choose_config(M, n_virtual, kb_total, can_split, auto_split, mode != 1, &BN, &sk, &pair);
+        split_k = sk;
+        break;
+      }
+      if (pair && (mode != 1) && (BN / 2) % 64 != 0) pair = 0;
+    }
   }
+  if (groups > 1) p.cv.nbpg = (N / groups) / BN;
   p.M = M; p.N = n_virtual;
   p.m_blocks = ceil_div(M, pair ? 2 * BLOCK_M : BLOCK_M);
   p.n_blocks = ceil_div(n_virtual, BN);
@@ -1081,6 +1109,31 @@ extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW
   // D is described with its real extent so stores of padded / neighbouring-tap columns are clipped
   p.N = n_virtual;
   return finish_and_launch(p, ta, tb, a_mn, b_mn, BN, pair, stream, mode == 3 ? N : -1);
+}
+
+extern "C" int vb_conv_gemm_bf16(int mode, const void* T, int tB, int tH, int tW, long long t_pitch, int t_ch,
+                                 int ky, int kx, int sy, int sx, int low_h, int low_w, int oH, int oW,
+                                 const void* other, long long ld_other, int other_rows, int cg, void* D,
+                                 long long ldd, int M, int N, const float* bias, int act, int out_fp32,
+                                 int accumulate, const void* Z, long long ldz, int deriv, float alpha,
+                                 int split_k, int block_n, cudaStream_t stream) {
+  return conv_gemm_impl(mode, T, tB, tH, tW, t_pitch, t_ch, ky, kx, sy, sx, low_h, low_w, oH, oW, other, ld_other,
+                        other_rows, cg, D, ldd, M, N, bias, act, out_fp32, accumulate, Z, ldz, deriv, alpha, split_k,
+                        block_n, 1, stream);
+}
+
+// All `groups` of a grouped convolution in ONE launch (modes 1 and 2): T, other (the whole [n_kernels, taps*cg] weight
+// matrix) and D are the full tensors, t_ch / N the total channel counts; tile -> group by its N index.  Needs
+// per-group channel and kernel counts that are multiples of 64 (AlexNet conv4 / conv5).
+extern "C" int vb_conv_gemm_grouped_bf16(int mode, int groups, const void* T, int tB, int tH, int tW, long long t_pitch,
+                                         int t_ch, int ky, int kx, int sy, int sx, int low_h, int low_w, int oH,
+                                         int oW, const void* other, long long ld_other, int other_rows, int cg,
+                                         void* D, long long ldd, int M, int N, const float* bias, int act,
+                                         int out_fp32, const void* Z, long long ldz, int deriv, int block_n,
+                                         cudaStream_t stream) {
+  return conv_gemm_impl(mode, T, tB, tH, tW, t_pitch, t_ch, ky, kx, sy, sx, low_h, low_w, oH, oW, other, ld_other,
+                        other_rows, cg, D, ldd, M, N, bias, act, out_fp32, 0, Z, ldz, deriv, 1.0f, 1, block_n, groups,
+                        stream);
 }
 
 // D[M,N] = epilogue(sum_k A(m,k) B(n,k)) with fp32 operands multiplied as TF32 (`tcgen05.mma.kind::tf32`, fp32

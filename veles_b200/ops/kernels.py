@@ -210,6 +210,44 @@ def conv_err_input(dy4, w, dx2, g, z=None, deriv=0, block_n=0):
                       w, n, Cg, dx2, dx2.shape[0], Cg, z=z, deriv=deriv, block_n=block_n)
 
 
+def _conv_gemm_grouped(mode, groups, t4, ky, kx, sy, sx, low_h, low_w, n_h, n_w, w, cg, out2, bias=None,
+                       act=ACT_LINEAR, z=None, deriv=0, block_n=0):
+    B, H, W, C = t4.shape
+    pitch = t4.stride(2)
+    assert t4.is_contiguous() and out2.dtype == torch.bfloat16
+    M, N = out2.shape
+    _FLOPS[0] = 2.0 * M * N * ky * kx * (C // groups)
+    rc = _lib.lib().vb_conv_gemm_grouped_bf16(
+        c_int(mode), c_int(groups), _p(t4), c_int(B), c_int(H), c_int(W), c_longlong(pitch), c_int(C), c_int(ky),
+        c_int(kx), c_int(sy), c_int(sx), c_int(low_h), c_int(low_w), c_int(n_h), c_int(n_w), _p(w),
+        c_longlong(_ld(w)), c_int(w.shape[0]), c_int(cg), _p(out2), c_longlong(_ld(out2)), c_int(M), c_int(N),
+        _p(bias), c_int(act), c_int(0), _p(z), c_longlong(_ld(z) if z is not None else 0), c_int(deriv),
+        c_int(block_n), _stream())
+    _lib.check(rc, "vb_conv_gemm_grouped_bf16")
+    LAUNCHES[0] += 1
+    return out2
+
+
+def grouped_conv_ok(C, n_kernels, groups):
+    """Can all groups of the layer run in one implicit-GEMM launch? (per-group widths multiples of 64)"""
+    return groups > 1 and C % groups == 0 and n_kernels % groups == 0 and (C // groups) % 64 == 0 \
+        and (n_kernels // groups) % 64 == 0
+
+
+def conv_forward_grouped(x4, w, out2, g, groups, bias=None, act=ACT_LINEAR, block_n=0):
+    """All groups of ``conv_forward`` in one launch: full NHWC input, full [n, ky*kx*Cg] weights, full output."""
+    return _conv_gemm_grouped(1, groups, x4, g["ky"], g["kx"], g["sy"], g["sx"], -g["pt"], -g["pl"], g["OH"], g["OW"],
+                              w, x4.shape[3] // groups, out2, bias=bias, act=act, block_n=block_n)
+
+
+def conv_err_input_grouped(dy4, w, dx2, g, groups, z=None, deriv=0, block_n=0):
+    """All groups of ``conv_err_input`` in one launch."""
+    assert g["sx"] == 1 and g["sy"] == 1
+    return _conv_gemm_grouped(2, groups, dy4, g["ky"], g["kx"], 1, 1, -(g["ky"] - 1 - g["pt"]),
+                              -(g["kx"] - 1 - g["pl"]), g["H"], g["W"], w, dx2.shape[1] // groups, dx2, z=z,
+                              deriv=deriv, block_n=block_n)
+
+
 def _conv_halo(mode, t4, ky, kx, low_h, low_w, n_h, n_w, w, cg, out2, bias=None, act=ACT_LINEAR, z=None, deriv=0):
     """Halo-tile implicit GEMM (csrc/conv_halo.cu); returns False when the geometry is not supported."""
     B, H, W, C = t4.shape
@@ -548,7 +586,7 @@ def _traced(fn):
     return wrap
 
 
-for _name in ("gemm", "bias_act", "gemm_tf32", "conv_forward", "conv_forward_halo", "conv_err_input_halo", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
+for _name in ("gemm", "bias_act", "gemm_tf32", "conv_forward", "conv_forward_grouped", "conv_err_input_grouped", "conv_forward_halo", "conv_err_input_halo", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
               "gather_minibatch", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
               "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",

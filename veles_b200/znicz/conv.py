@@ -230,6 +230,9 @@ class Conv(Forward):
             kernels.space_to_depth(x, sd["x"], g["sy"], g["sx"])
             kernels.gather_cols(self.weights_bf16_, sd["w"], sd["to_s2d"])   # refreshed bf16 weights, s2d order
             kernels.conv_forward(sd["x"], sd["w"], out2, sd["geom"], bias=bias, act=self.ACTIVATION)
+        elif self.implicit_ and kernels.grouped_conv_ok(x.shape[3], self.n_kernels, G):
+            # every group in ONE launch (tile -> group): fewer, fuller waves than one launch per group
+            kernels.conv_forward_grouped(x, self.weights_bf16_, out2, g, G, bias=bias, act=self.ACTIVATION)
         elif self.implicit_:
             Cg = x.shape[3] // G
             for gi in range(G):

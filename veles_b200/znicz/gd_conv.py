@@ -153,6 +153,11 @@ class GradientDescentConv(GradientDescentBase):
                 eo4 = eo2.view(x4.shape[0], g["OH"], g["OW"], nk)
                 ei2 = ei4.view(-1, x4.shape[3])
                 z2 = z.view(-1, x4.shape[3]) if z is not None else None
+                if kernels.grouped_conv_ok(x4.shape[3], nk, G):
+                    kernels.conv_err_input_grouped(eo4, w_bf16, ei2, g, G, z=z2, deriv=self.prev_activation)
+                    self.err_input.mark_device_written()
+                    self.device_update()
+                    return
                 for gi in range(G):
                     kernels.conv_err_input(eo4[..., gi * nkg:(gi + 1) * nkg] if G > 1 else eo4,
                                            w_bf16[gi * nkg:(gi + 1) * nkg],
