@@ -101,3 +101,29 @@ def test_ensemble_train_then_test(tmp_path):
     assert r.returncode == 0, r.stdout.decode()[-3000:]
     d2 = json.loads(res2.read_text())
     assert len(d2["models"]) == 2 and all("EvaluationFitness" in m for m in d2["models"])
+
+
+import pytest as _pytest
+
+
+@_pytest.mark.parametrize("sample", ["mnist", "cifar", "mnist_ae"])
+def test_every_sample_loads_its_config_and_initialises(sample):
+    """`python -m veles_b200 --dry-run init samples/<x>.py -` for every bundled sample (configs with Range genes too)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    wf = os.path.join(root, "veles_b200", "znicz", "samples", sample + ".py")
+    r = subprocess.run([sys.executable, "-m", "veles_b200", "-a", "numpy", "--dry-run", "init", wf, "-"],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=300, cwd=root,
+                       env=dict(os.environ, VELES_ALLOW_ROOT="1"))
+    assert r.returncode == 0, r.stdout.decode(errors="replace")[-2000:]
+
+
+def test_range_arithmetic_keeps_a_tunable_interval():
+    from veles_b200.genetics import Range
+    r = 2 * Range(0.01, 0.0005, 0.05)
+    assert isinstance(r, Range) and abs(r.default - 0.02) < 1e-12 and abs(r.max_value - 0.1) < 1e-12
+    assert abs(float(Range(1.0, 0.0, 2.0) / 4) - 0.25) < 1e-12
+    n = -Range(1.0, 0.5, 2.0)
+    assert n.min_value == -2.0 and n.max_value == -0.5

@@ -56,6 +56,35 @@ class Range(Tuneable):
     def details(self):
         return "[%s, %s] (default: %s)" % (self.min_value, self.max_value, self.default)
 
+    # A config may derive further hyper-parameters from a Range before the genes are fixed
+    # (``learning_rate_bias = 2 * lr``): arithmetic with a number gives a Range over the transformed interval.
+    def _scaled(self, fn):
+        vals = sorted((fn(self.min_value), fn(self.max_value)))
+        d = fn(self.default)
+        return Range(min(max(d, vals[0]), vals[1]), vals[0], vals[1])
+
+    def __mul__(self, k):
+        return self._scaled(lambda v: v * k)
+
+    __rmul__ = __mul__
+
+    def __truediv__(self, k):
+        return self._scaled(lambda v: v / k)
+
+    def __add__(self, k):
+        return self._scaled(lambda v: v + k)
+
+    __radd__ = __add__
+
+    def __sub__(self, k):
+        return self._scaled(lambda v: v - k)
+
+    def __neg__(self):
+        return self._scaled(lambda v: -v)
+
+    def __float__(self):
+        return float(self.default)
+
 
 def process_config(config, class_to_process, callback):
     """Apply ``callback(path, (container, key), name, value) -> new value`` to every element of
