@@ -17,6 +17,9 @@ CASES = [
     ("conv_str", (2, 13, 13, 64), {"n_kernels": 64, "kx": 3, "ky": 3, "padding": (1, 1, 1, 1), "sliding": (1, 1)}),
     ("conv_tanh", (2, 14, 14, 32), {"n_kernels": 48, "kx": 5, "ky": 5, "padding": (2, 2, 2, 2), "sliding": (1, 1),
                                     "grouping": 2}),
+    ("conv_sigmoid", (3, 12, 10, 5), {"n_kernels": 20, "kx": 3, "ky": 4, "padding": (1, 2, 0, 1), "sliding": (1, 2)}),
+    ("all2all_tanh", (7, 33), {"output_sample_shape": 19}),
+    ("max_pooling", (3, 9, 9, 5), {"kx": 2, "ky": 2, "sliding": (2, 2)}),
     ("max_pooling", (4, 15, 15, 32), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
     ("avg_pooling", (4, 16, 16, 32), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
     ("maxabs_pooling", (4, 8, 8, 16), {"kx": 2, "ky": 2, "sliding": (2, 2)}),
