@@ -113,6 +113,12 @@ class GradientDescentConv(GradientDescentBase):
         if self.ACTIVATION and not self.derivative_applied:
             y = self.output.devmem
             kernels.activation_backward(self.ACTIVATION, eo2, None, y.reshape(-1, nk), eo2)
+        if eo2.dtype != torch.bfloat16 or eo2.stride(0) % 8 != 0:
+            # TMA operand rules (bf16, row pitch a multiple of 16 bytes): stage odd kernel counts into a pitched copy
+            if getattr(self, "_eo_stage_", None) is None:
+                self._eo_stage_ = kernels.pitched_empty(eo2.shape[0], nk, torch.bfloat16, eo2.device)
+            kernels.copy_2d(eo2, self._eo_stage_)
+            eo2 = self._eo_stage_
         G = f.grouping
         nkg = nk // G
         w_bf16 = f.weights_bf16_
