@@ -23,6 +23,9 @@ CASES = [
     ("max_pooling", (4, 15, 15, 32), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
     ("avg_pooling", (4, 16, 16, 32), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
     ("maxabs_pooling", (4, 8, 8, 16), {"kx": 2, "ky": 2, "sliding": (2, 2)}),
+    ("cutter", (3, 10, 12, 8), {"padding": (2, 1, 3, 2)}),
+    ("cutter", (2, 9, 7, 5), {"padding": (1, 0, 0, 2)}),
+    ("all2all_resizable", (16, 40), {"output_sample_shape": 24}),
     ("norm", (4, 6, 6, 96), {"alpha": 0.0001, "beta": 0.75, "n": 5, "k": 1}),
     ("activation_tanh", (8, 40), {}),
     ("activation_str", (8, 40), {}),
