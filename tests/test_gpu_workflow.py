@@ -107,3 +107,57 @@ def test_float_precision_mode_runs_tf32_gemms_and_tracks_the_oracle_closely():
             root.common.engine.precision_type = "bf16"
     assert errs["float"] < 0.02 and errs["float"] < errs["bf16"], errs
     l0.stop()
+
+
+def test_partial_minibatches_match_numpy_oracle():
+    """Dataset sizes that do not divide by the minibatch size: padded rows must not leak into errors / gradients."""
+    from veles_b200.backends import NumpyDevice, B200Device
+    cfg = dict(CFG, n_train=230, n_valid=70, minibatch_size=100)
+    l0, ref = _build(NumpyDevice(), MLP, cfg, epochs=2)
+    ref.run()
+    l1, wf = _build(B200Device(), MLP, cfg, epochs=2)
+    wf.run()
+    for a, b in zip(ref.decision.epoch_metrics_history, wf.decision.epoch_metrics_history):
+        assert a["n_err"] is None or abs(a["n_err_pt"][1] - b["n_err_pt"][1]) <= 5.0
+        assert abs(a["loss"][1] - b["loss"][1]) <= 0.05 + 0.1 * abs(a["loss"][1])
+        assert abs(a["loss"][2] - b["loss"][2]) <= 0.05 + 0.1 * abs(a["loss"][2])
+    wf.forwards[0].weights.map_read()
+    ref.forwards[0].weights.map_read()
+    assert np.abs(wf.forwards[0].weights.mem - ref.forwards[0].weights.mem).max() < 0.05
+    l0.stop()
+    l1.stop()
+
+
+def test_snapshot_from_device_resumes_on_device(tmp_path):
+    """Pickle a workflow trained on the GPU (device tensors must not leak into the pickle), restore it, keep training on
+    the GPU: the resumed run must continue from the restored weights, loader position and epoch counter."""
+    import pickle
+    from veles_b200.backends import B200Device
+    from veles_b200.snapshotter import SnapshotterToFile
+    l1, wf = _build(B200Device(), MLP, CFG, epochs=1)
+    wf.run()
+    snap = SnapshotterToFile(wf, directory=str(tmp_path), prefix="dev", compression="gz", time_interval=0)
+    snap.suffix = "e1"
+    snap.export()
+    raw = open(snap.destination, "rb").read()
+    assert b"torch" not in __import__("gzip").decompress(raw)      # host arrays only
+    wf.forwards[0].weights.map_read()
+    w_before = wf.forwards[0].weights.mem.copy()
+    err_before = wf.decision.epoch_metrics_history[-1]["n_err_pt"][1]
+    l1.stop()
+    back = SnapshotterToFile.import_(snap.destination)
+    assert back.restored_from_snapshot
+    assert np.array_equal(back.forwards[0].weights.mem, w_before)
+    from veles_b200.dummy import DummyLauncher
+    launcher = DummyLauncher()
+    back.workflow = launcher
+    back.decision.max_epochs = 3
+    back.decision.complete <<= False
+    back.initialize(device=B200Device())
+    back.run()
+    hist = back.decision.epoch_metrics_history
+    assert hist[-1]["epoch"] == 3 and len(hist) == 3
+    assert hist[-1]["n_err_pt"][1] <= err_before + 1.0
+    back.forwards[0].weights.map_read()
+    assert np.abs(back.forwards[0].weights.mem - w_before).max() > 0
+    launcher.stop()
