@@ -926,7 +926,8 @@ static int gemm_impl(const void* A, long long lda, int a_mn_major, const void* B
     for (int attempt = 0; attempt < 4; ++attempt) {
       BN = forced[attempt];
       split_k = split_req;
-      if (attempt == 3) g_pair_mode_override = 1;
+      // peer replicas are read by plain single-CTA TMA loads only: every CTA fetches its own tile
+      if (attempt == 3 || b_peers != nullptr) g_pair_mode_override = 1;
       choose_config(M, N, p.k_blocks, accumulate && act == 0 && Z == nullptr, auto_split, b_mn_major != 0, &BN,
                     &split_k, &pair);
       g_pair_mode_override = 0;
@@ -950,6 +951,7 @@ static int gemm_impl(const void* A, long long lda, int a_mn_major, const void* B
   if (b_peers != nullptr) {
     // every replica has the same shape and pitch; only the base address differs
     VB_REQUIRE(world >= 1 && world <= 8 && shard_rows > 0, "sharded B: bad world %d / shard_rows %d", world, shard_rows);
+    VB_REQUIRE(!pair, "sharded B: peer replicas are read by single-CTA tiles only");
     const int w_rows = b_mn_major ? K : N;   // the weight-matrix row index the shard is cut along
     VB_REQUIRE(static_cast<long long>(shard_rows) * world >= w_rows, "sharded B: %d ranks x %d rows do not cover %d rows",
                world, shard_rows, w_rows);
