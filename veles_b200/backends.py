@@ -233,6 +233,8 @@ class B200Device(Device):
                 % (self.index, props.name, props.major, props.minor))
         from .ops import _lib
         _lib.lib()  # fail loudly now if the kernel library is missing
+        from .ops import kernels
+        kernels.bind_device(self.index)
         precision = get(root.common.engine.precision_type, "bf16")
         self.compute_dtype = torch.bfloat16 if precision in ("bf16", "bfloat16") else torch.float32
         self.info("Using %s", self.device_info)

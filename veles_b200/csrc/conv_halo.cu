@@ -329,6 +329,12 @@ static EncodeTiledFn halo_encode_fn() {
         q == cudaDriverEntryPointSuccess)
       fn = reinterpret_cast<EncodeTiledFn>(f);
   });
+  // the driver call needs this thread to have a current context: bind the primary one once per thread
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(nullptr);
+    ctx_bound = true;
+  }
   return fn;
 }
 

@@ -642,6 +642,12 @@ static EncodeTiledFn get_encode_fn() {
         q == cudaDriverEntryPointSuccess)
       fn = reinterpret_cast<EncodeTiledFn>(f);
   });
+  // the driver call needs this thread to have a current context: bind the primary one once per thread
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(nullptr);
+    ctx_bound = true;
+  }
   return fn;
 }
 
@@ -694,6 +700,12 @@ static EncodeIm2colFn get_encode_im2col_fn() {
         q == cudaDriverEntryPointSuccess)
       fn = reinterpret_cast<EncodeIm2colFn>(f);
   });
+  // the driver call needs this thread to have a current context: bind the primary one once per thread
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(nullptr);
+    ctx_bound = true;
+  }
   return fn;
 }
 

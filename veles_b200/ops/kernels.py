@@ -9,6 +9,7 @@ Counts launches in :data:`LAUNCHES` so ``bench.py`` can report ``gpu_launches``.
 from __future__ import annotations
 
 import ctypes
+import threading
 from ctypes import c_float, c_int, c_longlong, c_void_p
 
 import torch
@@ -45,7 +46,25 @@ def _p(t):
     return c_void_p(0 if t is None else t.data_ptr())
 
 
+_TLS = threading.local()
+_DEVICE_INDEX = [None]
+
+
+def bind_device(index):
+    """The device this process computes on (set by B200Device); worker threads bind to it on their first launch."""
+    if _DEVICE_INDEX[0] != int(index):
+        _DEVICE_INDEX[0] = int(index)
+        _DEVICE_INDEX.append(None)       # new generation: every thread re-binds
+
+
 def _stream():
+    # The C entry points use the calling thread's current CUDA device / context (driver-API tensor-map encoding
+    # fails with CUDA_ERROR_INVALID_CONTEXT in a thread that never touched the runtime).  A workflow's thread
+    # pool starts threads that may reach a launch before any torch op: bind them once.
+    if getattr(_TLS, "gen", -1) != len(_DEVICE_INDEX):
+        idx = _DEVICE_INDEX[0]
+        torch.cuda.set_device(torch.cuda.current_device() if idx is None else idx)
+        _TLS.gen = len(_DEVICE_INDEX)
     return c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
