@@ -171,6 +171,34 @@ int vb_xorshift1024star(void* states, int n_states, int rounds, void* out, cudaS
 int vb_xorshift128plus(void* states, long long n, void* out, cudaStream_t stream);
 int vb_fill_random(void* states, int n_states, float* out, long long n, int kind, float amp, cudaStream_t stream);
 
+/* ---- batched signal kernels (csrc/signal.cu): device side of libVeles/simd ------------------------------------- */
+/* Rows are fp32, `batch` of them, pitches in elements.  out has x_length + h_length - 1 elements per row;
+ * h_pitch 0 shares one filter between all rows; reverse = 1 gives cross-correlation (correlate.h:58-135). */
+int vb_sig_convolve(const float* x, long long x_pitch, int x_length, const float* h, long long h_pitch, int h_length,
+                    int reverse, float* out, long long out_pitch, int batch, cudaStream_t stream);
+/* One wavelet analysis step (wavelet.h:96-137).  lowpass / highpass are HOST arrays of `order` (<= 76) taps.
+ * stationary = 0: hi / lo get length / 2 outputs; 1: `length` outputs with the taps 2^(level-1) apart.
+ * ext: 0 periodic, 1 mirror, 2 constant, 3 zero. */
+int vb_sig_wavelet(const float* x, long long x_pitch, int length, const float* lowpass, const float* highpass,
+                   int order, int level, int stationary, int ext, float* hi, float* lo, long long out_pitch,
+                   int batch, cudaStream_t stream);
+/* out[2 r] = min, out[2 r + 1] = max of row r (normalize.h:84-89). */
+int vb_sig_minmax_f32(const float* x, long long pitch, int length, int batch, float* out, cudaStream_t stream);
+/* uint8 planes -> (v - min) / ((max - min) / 2) - 1 (normalize.h:48-82).  minmax: int32 [batch][2], computed here
+ * unless have_minmax; dst may be null (range pass only). */
+int vb_sig_normalize_u8(const unsigned char* src, long long plane_pitch, int stride, int width, int height, int batch,
+                        int* minmax, int have_minmax, float* dst, long long dst_plane_pitch, int dst_stride,
+                        cudaStream_t stream);
+/* Strict interior extrema in index order (detect_peaks.h).  type 1 max, 2 min, 3 both.  counts: scratch of
+ * batch * ceil(length / 1024) ints; positions / values: [batch][capacity]; totals[batch] = peaks found. */
+int vb_sig_detect_peaks(const float* x, long long pitch, int length, int batch, int type, int* counts, int* positions,
+                        float* values, int capacity, int* totals, cudaStream_t stream);
+/* out = a * b (or a * conj(b)) * scale on interleaved complex rows; pitches in complex elements, b_pitch 0 broadcasts. */
+int vb_sig_complex_mul(const float* a, long long a_pitch, const float* b, long long b_pitch, float* out,
+                       long long out_pitch, int n_complex, int batch, int conj_b, float scale, cudaStream_t stream);
+/* kind 0 int16->float, 1 float->int16 (truncate), 2 int32->float, 3 float->int32, 4 half->float (arithmetic.h). */
+int vb_sig_convert(const void* src, void* dst, long long n, int kind, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -32,7 +32,29 @@ def build(force=False):
     if force or not os.path.exists(test) or os.path.getmtime(test) < max(newest, os.path.getmtime(test_src)):
         subprocess.check_call([nvcc, "-x", "cu"] + common + ["-o", test, test_src, "-L", out_dir, "-lveles_native"] +
                               link + ["-Xlinker", "-rpath", "-Xlinker", "$ORIGIN"])
+    build_simd(force)
     return lib, test
+
+
+def build_simd(force=False):
+    """native/lib/libveles_simd.so: the host signal / array primitives (no CUDA dependency, plain g++)."""
+    out_dir = os.path.join(HERE, "lib")
+    os.makedirs(out_dir, exist_ok=True)
+    src_dir = os.path.join(HERE, "simd")
+    srcs = [os.path.join(src_dir, f) for f in sorted(os.listdir(src_dir)) if f.endswith(".cc")]
+    hdrs = [os.path.join(HERE, "include", "veles", f) for f in ("simd.h", "wavelet_tables.h")]
+    lib = os.path.join(out_dir, "libveles_simd.so")
+    newest = max(os.path.getmtime(p) for p in srcs + hdrs)
+    if force or not os.path.exists(lib) or os.path.getmtime(lib) < newest:
+        subprocess.check_call(["g++", "-std=c++17", "-O3", "-fno-math-errno", "-fPIC", "-shared",
+                               "-I", os.path.join(HERE, "include"), "-o", lib] + srcs)
+    test = os.path.join(out_dir, "test_simd")
+    test_src = os.path.join(HERE, "tests", "test_simd.cc")
+    if os.path.exists(test_src) and (force or not os.path.exists(test) or
+                                     os.path.getmtime(test) < max(newest, os.path.getmtime(test_src))):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-I", os.path.join(HERE, "include"), "-o", test, test_src,
+                               "-L", out_dir, "-lveles_simd", "-Wl,-rpath,$ORIGIN"])
+    return lib
 
 
 if __name__ == "__main__":

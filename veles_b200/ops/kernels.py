@@ -611,3 +611,86 @@ for _name in ("gemm", "bias_act", "gemm_tf32", "conv_forward", "conv_forward_gro
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",
               "row_sum", "col_sum", "xorshift1024star", "xorshift128plus", "fill_random"):
     globals()[_name] = _traced(globals()[_name])
+
+
+# -- batched signal kernels (csrc/signal.cu; API in veles_b200/simd) --------------------------------------------------
+def _rows(t):
+    assert t.dim() == 2 and t.stride(1) == 1, "need [batch, length] rows with unit inner stride"
+    return t.shape[0], t.shape[1], t.stride(0)
+
+
+def sig_convolve(x, h, out, reverse=False):
+    """out[b] = x[b] (*) h[b or 0] (full convolution; ``reverse`` = cross-correlation).  fp32 rows."""
+    B, X, xp = _rows(x)
+    hb, M, hp = _rows(h)
+    assert hb in (1, B) and out.shape == (B, X + M - 1)
+    rc = _lib.lib().vb_sig_convolve(_p(x), c_longlong(xp), c_int(X), _p(h), c_longlong(hp if hb == B else 0), c_int(M),
+                                    c_int(int(reverse)), _p(out), c_longlong(out.stride(0)), c_int(B), _stream())
+    _lib.check(rc, "vb_sig_convolve")
+    LAUNCHES[0] += 1
+    return out
+
+
+def sig_wavelet(x, lowpass, highpass, hi, lo, ext, level=1, stationary=False):
+    """One analysis step over every row of ``x``; ``lowpass`` / ``highpass`` are host float32 arrays."""
+    import numpy
+    B, n, xp = _rows(x)
+    lp = numpy.ascontiguousarray(lowpass, dtype=numpy.float32)
+    hp = numpy.ascontiguousarray(highpass, dtype=numpy.float32)
+    assert hi.stride(0) == lo.stride(0)
+    rc = _lib.lib().vb_sig_wavelet(_p(x), c_longlong(xp), c_int(n), lp.ctypes.data_as(c_void_p),
+                                   hp.ctypes.data_as(c_void_p), c_int(lp.size), c_int(level), c_int(int(stationary)),
+                                   c_int(int(ext)), _p(hi), _p(lo), c_longlong(hi.stride(0)), c_int(B), _stream())
+    _lib.check(rc, "vb_sig_wavelet")
+    LAUNCHES[0] += 1
+    return hi, lo
+
+
+def sig_minmax(x, out):
+    B, n, xp = _rows(x)
+    rc = _lib.lib().vb_sig_minmax_f32(_p(x), c_longlong(xp), c_int(n), c_int(B), _p(out), _stream())
+    _lib.check(rc, "vb_sig_minmax_f32")
+    LAUNCHES[0] += 1
+    return out
+
+
+def sig_normalize_u8(src, minmax, dst, have_minmax=False):
+    """src uint8 [batch, H, W] (row stride free), minmax int32 [batch, 2], dst float32 [batch, H, W] or None."""
+    assert src.dim() == 3 and src.stride(2) == 1
+    B, H, W = src.shape
+    rc = _lib.lib().vb_sig_normalize_u8(
+        _p(src), c_longlong(src.stride(0)), c_int(src.stride(1)), c_int(W), c_int(H), c_int(B), _p(minmax),
+        c_int(int(have_minmax)), _p(dst), c_longlong(0 if dst is None else dst.stride(0)),
+        c_int(W if dst is None else dst.stride(1)), _stream())
+    _lib.check(rc, "vb_sig_normalize_u8")
+    LAUNCHES[0] += 1 + (0 if have_minmax else 1) - (1 if dst is None else 0)
+    return dst
+
+
+def sig_detect_peaks(x, extremum_type, counts, positions, values, totals):
+    B, n, xp = _rows(x)
+    rc = _lib.lib().vb_sig_detect_peaks(_p(x), c_longlong(xp), c_int(n), c_int(B), c_int(int(extremum_type)),
+                                        _p(counts), _p(positions), _p(values), c_int(positions.shape[1]), _p(totals),
+                                        _stream())
+    _lib.check(rc, "vb_sig_detect_peaks")
+    LAUNCHES[0] += 2
+    return totals
+
+
+def sig_complex_mul(a, b, out, conj_b=False, scale=1.0):
+    """Interleaved complex rows (float32 views of complex64): out = a * b (b broadcast when it has one row)."""
+    B, n2, ap = _rows(a)
+    bb, _, bp = _rows(b)
+    rc = _lib.lib().vb_sig_complex_mul(_p(a), c_longlong(ap // 2), _p(b), c_longlong(bp // 2 if bb == B else 0), _p(out),
+                                       c_longlong(out.stride(0) // 2), c_int(n2 // 2), c_int(B), c_int(int(conj_b)),
+                                       c_float(scale), _stream())
+    _lib.check(rc, "vb_sig_complex_mul")
+    LAUNCHES[0] += 1
+    return out
+
+
+def sig_convert(src, dst, kind):
+    rc = _lib.lib().vb_sig_convert(_p(src), _p(dst), c_longlong(src.numel()), c_int(kind), _stream())
+    _lib.check(rc, "vb_sig_convert")
+    LAUNCHES[0] += 1
+    return dst
