@@ -199,6 +199,23 @@ int vb_sig_complex_mul(const float* a, long long a_pitch, const float* b, long l
 /* kind 0 int16->float, 1 float->int16 (truncate), 2 int32->float, 3 float->int32, 4 half->float (arithmetic.h). */
 int vb_sig_convert(const void* src, void* dst, long long n, int kind, cudaStream_t stream);
 
+/* ---- recurrent cells (csrc/recurrent.cu): RNN / LSTM units of docs/source/manualrst_veles_algorithms.rst:108-135 - */
+/* z: [B, 4H] fp32 pre-activations (gate blocks i f g o, bias included).  Writes the gate activations (saved for the
+ * backward pass), c, and h both into h_next (bf16 h-slot of the next step's [x | h] operand; may be null) and into
+ * `out` rows (fp32 = 0 / bf16 = 1; may be null).  c_prev null = zero state. */
+int vb_lstm_cell_forward(const float* z, long long ldz, const float* c_prev, float* c, float* gates, long long ldg,
+                         void* h_next, long long ld_next, void* out, int out_dtype, long long ld_out, int B, int H,
+                         cudaStream_t stream);
+/* dh = dh_ext + dh_rec (either may be null); dc is the running dL/dc (ignored on input when first != 0);
+ * dz: bf16 [B, 4H] gradient w.r.t. the pre-activations. */
+int vb_lstm_cell_backward(const void* dh_ext, int ext_dtype, long long ld_ext, const float* dh_rec, long long ld_rec,
+                          float* dc, int first, const float* gates, long long ldg, const float* c_prev, const float* c,
+                          void* dz, long long ld_dz, int B, int H, cudaStream_t stream);
+int vb_rnn_cell_forward(const float* z, long long ldz, float* h_save, void* h_next, long long ld_next, void* out,
+                        int out_dtype, long long ld_out, int B, int H, cudaStream_t stream);
+int vb_rnn_cell_backward(const void* dh_ext, int ext_dtype, long long ld_ext, const float* dh_rec, long long ld_rec,
+                         const float* h_save, void* dz, long long ld_dz, int B, int H, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

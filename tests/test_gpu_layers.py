@@ -30,6 +30,12 @@ CASES = [
     ("activation_tanh", (8, 40), {}),
     ("activation_str", (8, 40), {}),
     ("activation_log", (8, 40), {}),
+    ("rnn", (16, 6, 24), {"hidden_size": 32}),
+    ("rnn", (5, 7, 10), {"hidden_size": 12, "return_sequences": False}),
+    ("lstm", (16, 6, 24), {"hidden_size": 32}),
+    ("lstm", (8, 5, 13), {"hidden_size": 20}),
+    ("lstm", (32, 4, 64), {"hidden_size": 64, "return_sequences": False}),
+    ("lstm", (4, 36), {"hidden_size": 8, "sequence_length": 6}),
 ]
 
 
@@ -91,8 +97,8 @@ def _run(tpe, x, kw, device, R, weights=None, prev_activation=0):
 def test_layer_device_vs_numpy(tpe, shape, kw, prev_act):
     from veles_b200.backends import NumpyDevice, B200Device
     from veles_b200 import prng
-    if prev_act and tpe.startswith("activation"):
-        pytest.skip("activation units do not fuse a previous derivative")
+    if prev_act and (tpe.startswith("activation") or tpe in ("rnn", "lstm")):
+        pytest.skip("this unit does not fuse a previous derivative")
     rng = np.random.RandomState(abs(hash(tpe)) % 1000)
     x = rng.uniform(-1, 1, size=shape)
     if "pooling" in tpe:

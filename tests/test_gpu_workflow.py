@@ -144,6 +144,8 @@ def test_snapshot_from_device_resumes_on_device(tmp_path):
     wf.forwards[0].weights.map_read()
     w_before = wf.forwards[0].weights.mem.copy()
     err_before = wf.decision.epoch_metrics_history[-1]["n_err_pt"][1]
+    n_before = len(wf.decision.epoch_metrics_history)
+    epoch_before = wf.decision.epoch_metrics_history[-1]["epoch"]
     l1.stop()
     back = SnapshotterToFile.import_(snap.destination)
     assert back.restored_from_snapshot
@@ -156,8 +158,32 @@ def test_snapshot_from_device_resumes_on_device(tmp_path):
     back.initialize(device=B200Device())
     back.run()
     hist = back.decision.epoch_metrics_history
-    assert hist[-1]["epoch"] == 3 and len(hist) == 3
+    assert hist[-1]["epoch"] == 3 and len(hist) == n_before + (3 - epoch_before)   # history restored, then extended
+    assert [h["epoch"] for h in hist] == sorted(set(h["epoch"] for h in hist))
     assert hist[-1]["n_err_pt"][1] <= err_before + 1.0
     back.forwards[0].weights.map_read()
     assert np.abs(back.forwards[0].weights.mem - w_before).max() > 0
     launcher.stop()
+
+
+def test_lstm_workflow_on_device_follows_numpy_oracle():
+    """LSTM -> softmax trained through StandardWorkflow: device curve vs the numpy oracle (same data, same init)."""
+    from veles_b200.backends import NumpyDevice, B200Device
+    layers = [{"type": "lstm", "->": {"hidden_size": 32, "return_sequences": False},
+               "<-": {"learning_rate": 0.05, "gradient_moment": 0.9}},
+              {"type": "softmax", "<-": {"learning_rate": 0.05, "gradient_moment": 0.9}}]
+    cfg = {"minibatch_size": 64, "n_train": 640, "n_valid": 128, "sample_shape": (6, 16), "noise": 0.5}
+    l0, ref = _build(NumpyDevice(), layers, cfg, epochs=4)
+    ref.run()
+    l1, wf = _build(B200Device(), layers, cfg, epochs=4)
+    wf.run()
+    h_ref, h_dev = ref.decision.epoch_metrics_history, wf.decision.epoch_metrics_history
+    assert len(h_ref) == len(h_dev)
+    assert h_dev[-1]["loss"][2] < h_dev[1]["loss"][2]
+    for a, b in zip(h_ref, h_dev):
+        assert abs(a["loss"][1] - b["loss"][1]) <= 0.05 + 0.1 * abs(a["loss"][1]), (a, b)
+    wf.forwards[0].weights.map_read()
+    ref.forwards[0].weights.map_read()
+    assert np.abs(wf.forwards[0].weights.mem - ref.forwards[0].weights.mem).max() < 0.05
+    l0.stop()
+    l1.stop()

@@ -183,3 +183,77 @@ def test_lr_policies_and_mcdnnic():
     assert [l["type"] for l in layers] == ["conv_tanh", "max_pooling", "conv_tanh", "max_pooling", "all2all_tanh", "softmax"]
     assert layers[0]["->"]["n_kernels"] == 32 and layers[3]["->"]["sliding"] == (3, 3)
     assert layers[-1]["->"]["output_sample_shape"] == 4
+
+
+def test_recurrent_layers_train_in_standard_workflow():
+    """rnn / lstm layer types are reachable from a StandardWorkflow config and learn a sequence task (numpy oracle)."""
+    from veles_b200 import prng
+    from veles_b200.config import root
+    from veles_b200.dummy import DummyLauncher
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.znicz.standard_workflow import StandardWorkflow
+    import veles_b200.loader.synthetic  # noqa: F401
+    root.common.disable.snapshotting = True
+    cfg = {"minibatch_size": 50, "n_train": 500, "n_valid": 100, "sample_shape": (6, 8), "noise": 0.5}
+    for tpe in ("lstm", "rnn"):
+        prng.get().seed(3)
+        layers = [{"type": tpe, "->": {"hidden_size": 16, "return_sequences": False},
+                   "<-": {"learning_rate": 0.05, "gradient_moment": 0.9}},
+                  {"type": "softmax", "<-": {"learning_rate": 0.05, "gradient_moment": 0.9}}]
+        launcher = DummyLauncher()
+        wf = StandardWorkflow(launcher, layers=layers, loader_name="synthetic_fullbatch", loader_config=cfg,
+                              loss_function="softmax", decision_config={"max_epochs": 12})
+        wf.initialize(device=NumpyDevice())
+        assert wf.forwards[0].weights.shape == ((4 if tpe == "lstm" else 1) * 16, 8 + 16)
+        wf.run()
+        hist = wf.decision.epoch_metrics_history
+        assert hist[-1]["n_err_pt"][1] < 0.75 * hist[0]["n_err_pt"][1], (tpe, hist)
+        assert hist[-1]["loss"][2] < hist[1]["loss"][2]
+        launcher.stop()
+
+
+def test_stacked_recurrent_layers_and_sequence_outputs():
+    import numpy as np
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.dummy import DummyWorkflow
+    from veles_b200.memory import Array
+    from veles_b200.znicz.recurrent import LSTM, RNN, GDLSTM, GDRNN
+    rng = np.random.RandomState(0)
+    wf = DummyWorkflow()
+    x = rng.uniform(-1, 1, (4, 5, 3)).astype(np.float32)
+    l1 = LSTM(wf, hidden_size=6)
+    l1.input = Array(x)
+    assert not l1.initialize(device=NumpyDevice())
+    assert np.allclose(l1.bias.mem[6:12] - 1.0, l1.bias.mem[6:12] - 1.0) and l1.bias.mem[6:12].mean() > 0.5
+    l1.run()
+    assert l1.output.shape == (4, 5, 6)
+    l2 = RNN(wf, hidden_size=2, return_sequences=False)
+    l2.input = l1.output
+    assert not l2.initialize(device=NumpyDevice())
+    l2.run()
+    assert l2.output.shape == (4, 2) and np.all(np.abs(l2.output.mem) <= 1)
+    g2 = GDRNN(wf, forward=l2, learning_rate=0.1, weights_decay=0.0)
+    g2.input, g2.output, g2.weights, g2.bias = l2.input, l2.output, l2.weights, l2.bias
+    g2.err_output = Array(np.ones((4, 2), np.float32))
+    assert not g2.initialize(device=NumpyDevice())
+    w_before = l2.weights.mem.copy()
+    g2.run()
+    assert g2.err_input.shape == (4, 5, 6) and np.abs(l2.weights.mem - w_before).max() > 0
+    g1 = GDLSTM(wf, forward=l1, learning_rate=0.1, weights_decay=0.0, need_err_input=False)
+    g1.input, g1.output, g1.weights, g1.bias = l1.input, l1.output, l1.weights, l1.bias
+    g1.err_output = g2.err_input
+    assert not g1.initialize(device=NumpyDevice())
+    g1.run()
+    assert g1.gradient_weights.shape == (24, 9)
+    # a causal layer: output at step t must not depend on inputs after t
+    x2 = x.copy()
+    x2[:, 3:, :] += 1.0
+    l1b = LSTM(wf, hidden_size=6)
+    l1b.input = Array(x2)
+    l1b.initialize(device=NumpyDevice())
+    l1b.weights.mem[...] = l1.weights.mem
+    l1b.bias.mem[...] = l1.bias.mem
+    l1.run()
+    l1b.run()
+    assert np.allclose(l1.output.mem[:, :3], l1b.output.mem[:, :3]) and \
+        not np.allclose(l1.output.mem[:, 3:], l1b.output.mem[:, 3:])

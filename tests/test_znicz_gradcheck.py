@@ -64,10 +64,15 @@ CASES = [
     ("activation_tanhlog", (4, 10), {}),
     ("activation_sincos", (4, 10), {}),
     ("activation_mul", (4, 10), {"factor": 0.3}),
+    ("rnn", (3, 5, 4), {"hidden_size": 6}),
+    ("rnn", (3, 5, 4), {"hidden_size": 6, "return_sequences": False}),
+    ("lstm", (3, 5, 4), {"hidden_size": 6}),
+    ("lstm", (2, 4, 3), {"hidden_size": 5, "return_sequences": False}),
+    ("lstm", (3, 20), {"hidden_size": 4, "sequence_length": 5}),
 ]
 
 
-@pytest.mark.parametrize("tpe,shape,kw", CASES, ids=[c[0] for c in CASES])
+@pytest.mark.parametrize("tpe,shape,kw", CASES, ids=[c[0] + str(i) for i, c in enumerate(CASES)])
 def test_backward_matches_numeric_derivative(tpe, shape, kw):
     rng = np.random.RandomState(hash(tpe) % 1000)
     x = rng.uniform(-1.5, 1.5, size=shape)

@@ -14,19 +14,24 @@ namespace vb {
 // ---------------------------------------------------------------------------------------------------------------
 // Direct convolution:  out[n] = sum_m h'[m] * x[n - m],  n in [0, X + M - 1),  h' = h or h reversed (correlation).
 // A block owns CONV_TILE consecutive outputs of one row; taps are consumed in chunks of CONV_HC held in shared
-// memory next to the matching window of x (zero-filled outside the signal).  Thread t computes outputs
-// t, t + 256, ...: consecutive threads read consecutive shared words (no bank conflicts), the tap is a broadcast.
+// memory next to the matching window of x (zero-filled outside the signal).  Thread t computes CONV_ITEMS
+// CONSECUTIVE outputs: 8 taps x 8 outputs need only 15 window samples, which live in registers, so a step is
+// 15 + 2 shared loads for 64 FMAs.  The window is stored with one pad word per 32 (index j + j / 32): the
+// stride-8 accesses of neighbouring threads then fall into distinct banks.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int CONV_THREADS = 256;
-constexpr int CONV_ITEMS = 4;
+constexpr int CONV_ITEMS = 8;
 constexpr int CONV_TILE = CONV_THREADS * CONV_ITEMS;
-constexpr int CONV_HC = 512;
+constexpr int CONV_HC = 256;
+constexpr int CONV_XS = CONV_TILE + CONV_HC;
+
+__device__ __forceinline__ int conv_pad(int j) { return j + (j >> 5); }
 
 __global__ void __launch_bounds__(CONV_THREADS)
 sig_conv_kernel(const float* __restrict__ x, long long x_pitch, int X, const float* __restrict__ h, long long h_pitch,
                 int M, int reverse, float* __restrict__ out, long long out_pitch) {
-  __shared__ float h_s[CONV_HC];
-  __shared__ float x_s[CONV_TILE + CONV_HC];
+  __shared__ __align__(16) float h_s[CONV_HC];
+  __shared__ float x_s[CONV_XS + CONV_XS / 32 + 1];
   const int row = blockIdx.y;
   const int n0 = blockIdx.x * CONV_TILE;
   const int out_len = X + M - 1;
@@ -46,26 +51,36 @@ sig_conv_kernel(const float* __restrict__ x, long long x_pitch, int X, const flo
       const int m = m0 + i;
       h_s[i] = (i < hc) ? hr[reverse ? (M - 1 - m) : m] : 0.f;
     }
-    // x_s[j] = x[n0 - m0 - (CONV_HC - 1) + j]
+    // window sample j = x[n0 - m0 - (CONV_HC - 1) + j]
     const int xbase = n0 - m0 - (CONV_HC - 1);
-    for (int j = threadIdx.x; j < CONV_TILE + CONV_HC; j += CONV_THREADS) {
+    for (int j = threadIdx.x; j < CONV_XS; j += CONV_THREADS) {
       const int p = xbase + j;
-      x_s[j] = (p >= 0 && p < X) ? xr[p] : 0.f;
+      x_s[conv_pad(j)] = (p >= 0 && p < X) ? xr[p] : 0.f;
     }
     __syncthreads();
-    for (int i = 0; i < hc; ++i) {
-      const float tap = h_s[i];
-      const int off = threadIdx.x + (CONV_HC - 1) - i;
+    const int hc8 = (hc + 7) & ~7;     // the tail of h_s is zero
+    for (int i0 = 0; i0 < hc8; i0 += 8) {
+      // output k, tap i0 + i reads window sample  t*8 + k - i0 - i + HC - 1  =  base + (k - i + 7)
+      const int base = threadIdx.x * CONV_ITEMS - i0 + (CONV_HC - 1) - 7;
+      float v[15];
 #pragma unroll
-      for (int k = 0; k < CONV_ITEMS; ++k) acc[k] = fmaf(tap, x_s[off + k * CONV_THREADS], acc[k]);
+      for (int j = 0; j < 15; ++j) v[j] = x_s[conv_pad(base + j)];
+      const float4 ha = *reinterpret_cast<const float4*>(h_s + i0);
+      const float4 hb = *reinterpret_cast<const float4*>(h_s + i0 + 4);
+      const float taps[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+#pragma unroll
+        for (int k = 0; k < CONV_ITEMS; ++k) acc[k] = fmaf(taps[i], v[k - i + 7], acc[k]);
+      }
     }
     __syncthreads();
   }
   float* outr = out + row * out_pitch;
+  const int nb = n0 + threadIdx.x * CONV_ITEMS;
 #pragma unroll
   for (int k = 0; k < CONV_ITEMS; ++k) {
-    const int n = n0 + threadIdx.x + k * CONV_THREADS;
-    if (n < out_len) outr[n] = acc[k];
+    if (nb + k < out_len) outr[nb + k] = acc[k];
   }
 }
 
@@ -93,29 +108,50 @@ __device__ __forceinline__ float dwt_ext(const float* __restrict__ xr, int lengt
 }
 
 constexpr int DWT_THREADS = 256;
+constexpr int DWT_ITEMS = 4;                       // outputs per thread (d0 + t + k * 256)
+constexpr int DWT_TILE = DWT_THREADS * DWT_ITEMS;  // outputs per block
+constexpr int DWT_WIN = 2 * DWT_TILE + DWT_MAX_ORDER + 2;
 
 __global__ void __launch_bounds__(DWT_THREADS)
 sig_dwt_kernel(const float* __restrict__ x, long long x_pitch, int length, const __grid_constant__ DwtTaps taps,
                int order, int ext, float* __restrict__ hi, float* __restrict__ lo, long long out_pitch) {
-  // window of the block: inputs [2 d0, 2 d0 + 2 * 256 + order)
-  __shared__ float win[2 * DWT_THREADS + DWT_MAX_ORDER + 2];
+  // window of the block: inputs [2 d0, 2 d0 + 2 * TILE + order), stored with one pad word per 32 so that the
+  // stride-2 reads of neighbouring threads hit distinct banks.  Each thread keeps 8+ independent global loads in
+  // flight while filling it (the kernel is bound by bytes in flight, not by arithmetic, for short filters).
+  __shared__ float win[DWT_WIN + DWT_WIN / 32 + 1];
   const int row = blockIdx.y;
-  const int d0 = blockIdx.x * DWT_THREADS;
+  const int d0 = blockIdx.x * DWT_TILE;
   const float* xr = x + row * x_pitch;
-  const int need = 2 * DWT_THREADS + order;
-  for (int j = threadIdx.x; j < need; j += DWT_THREADS) win[j] = dwt_ext(xr, length, 2 * d0 + j, ext);
-  __syncthreads();
-  const int d = d0 + threadIdx.x;
-  if (d >= length / 2) return;
-  float rh = 0.f, rl = 0.f;
-  const float* w = win + 2 * threadIdx.x;
-  for (int j = 0; j < order; ++j) {
-    const float v = w[j];
-    rh = fmaf(taps.hi[j], v, rh);
-    rl = fmaf(taps.lo[j], v, rl);
+  const int need = 2 * DWT_TILE + order;
+  const int first = 2 * d0;
+  if (first + need <= length) {      // interior block: no extension logic
+#pragma unroll 4
+    for (int j = threadIdx.x; j < need; j += DWT_THREADS) win[j + (j >> 5)] = __ldg(xr + first + j);
+  } else {
+    for (int j = threadIdx.x; j < need; j += DWT_THREADS) win[j + (j >> 5)] = dwt_ext(xr, length, first + j, ext);
   }
-  hi[row * out_pitch + d] = rh;
-  lo[row * out_pitch + d] = rl;
+  __syncthreads();
+  float rh[DWT_ITEMS], rl[DWT_ITEMS];
+#pragma unroll
+  for (int k = 0; k < DWT_ITEMS; ++k) rh[k] = rl[k] = 0.f;
+  for (int j = 0; j < order; ++j) {
+    const float th = taps.hi[j], tl = taps.lo[j];
+#pragma unroll
+    for (int k = 0; k < DWT_ITEMS; ++k) {
+      const int idx = 2 * (threadIdx.x + k * DWT_THREADS) + j;
+      const float v = win[idx + (idx >> 5)];
+      rh[k] = fmaf(th, v, rh[k]);
+      rl[k] = fmaf(tl, v, rl[k]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < DWT_ITEMS; ++k) {
+    const int d = d0 + threadIdx.x + k * DWT_THREADS;
+    if (d < length / 2) {
+      hi[row * out_pitch + d] = rh[k];
+      lo[row * out_pitch + d] = rl[k];
+    }
+  }
 }
 
 __global__ void __launch_bounds__(DWT_THREADS)
@@ -174,7 +210,27 @@ __global__ void __launch_bounds__(512) sig_minmax_f32_kernel(const float* __rest
                                                              float* __restrict__ out) {
   const float* xr = x + blockIdx.x * pitch;
   float lo = __ldg(xr), hi = lo;
-  for (int i = threadIdx.x; i < length; i += blockDim.x) {
+  int done = 0;
+  if ((reinterpret_cast<uintptr_t>(xr) & 15) == 0) {
+    // 16-byte loads, four of them in flight per thread
+    const float4* x4 = reinterpret_cast<const float4*>(xr);
+    const int n4 = length >> 2;
+    int i = threadIdx.x;
+    for (; i + 3 * 512 < n4; i += 4 * 512) {
+      const float4 a = __ldg(x4 + i), b = __ldg(x4 + i + 512), c = __ldg(x4 + i + 1024), d = __ldg(x4 + i + 1536);
+      lo = fminf(fminf(fminf(lo, fminf(a.x, a.y)), fminf(fminf(a.z, a.w), fminf(b.x, b.y))),
+                 fminf(fminf(fminf(b.z, b.w), fminf(c.x, c.y)), fminf(fminf(c.z, c.w), fminf(fminf(d.x, d.y), fminf(d.z, d.w)))));
+      hi = fmaxf(fmaxf(fmaxf(hi, fmaxf(a.x, a.y)), fmaxf(fmaxf(a.z, a.w), fmaxf(b.x, b.y))),
+                 fmaxf(fmaxf(fmaxf(b.z, b.w), fmaxf(c.x, c.y)), fmaxf(fmaxf(c.z, c.w), fmaxf(fmaxf(d.x, d.y), fmaxf(d.z, d.w)))));
+    }
+    for (; i < n4; i += 512) {
+      const float4 a = __ldg(x4 + i);
+      lo = fminf(fminf(lo, fminf(a.x, a.y)), fminf(a.z, a.w));
+      hi = fmaxf(fmaxf(hi, fmaxf(a.x, a.y)), fmaxf(a.z, a.w));
+    }
+    done = n4 << 2;
+  }
+  for (int i = done + threadIdx.x; i < length; i += blockDim.x) {
     const float v = __ldg(xr + i);
     lo = fminf(lo, v);
     hi = fmaxf(hi, v);
@@ -191,12 +247,22 @@ __global__ void __launch_bounds__(512) sig_minmax_u8_kernel(const uint8_t* __res
                                                             int stride, int width, int height, int* __restrict__ out) {
   const uint8_t* p = src + blockIdx.x * plane_pitch;
   int lo = 255, hi = 0;
-  const int total = width * height;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    const int y = i / width, xx = i - y * width;
-    const int v = p[static_cast<long long>(y) * stride + xx];
-    lo = min(lo, v);
-    hi = max(hi, v);
+  if (((reinterpret_cast<uintptr_t>(p) | static_cast<uintptr_t>(stride) | static_cast<uintptr_t>(width)) & 3) == 0) {
+    const int w4 = width >> 2, total4 = w4 * height;
+    for (int i = threadIdx.x; i < total4; i += blockDim.x) {
+      const int y = i / w4, xx = i - y * w4;
+      const uchar4 v = __ldg(reinterpret_cast<const uchar4*>(p + static_cast<long long>(y) * stride) + xx);
+      lo = min(min(lo, min(v.x, v.y)), min(v.z, v.w));
+      hi = max(max(hi, max(v.x, v.y)), max(v.z, v.w));
+    }
+  } else {
+    const int total = width * height;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+      const int y = i / width, xx = i - y * width;
+      const int v = p[static_cast<long long>(y) * stride + xx];
+      lo = min(lo, v);
+      hi = max(hi, v);
+    }
   }
   block_minmax(lo, hi);
   if (threadIdx.x == 0) {
@@ -211,15 +277,32 @@ sig_normalize_u8_kernel(const uint8_t* __restrict__ src, long long plane_pitch, 
                         int dst_stride) {
   const int plane = blockIdx.y;
   const int lo = minmax[2 * plane], hi = minmax[2 * plane + 1];
+  // flat plane (max == min): all zeros
   const float inv = hi > lo ? 2.f / static_cast<float>(hi - lo) : 0.f;
-  const int total = width * height;
+  const float off = hi > lo ? -static_cast<float>(lo) * inv - 1.f : 0.f;
   const uint8_t* p = src + plane * plane_pitch;
   float* d = dst + plane * dst_plane_pitch;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    const int y = i / width, xx = i - y * width;
-    const float v = static_cast<float>(p[static_cast<long long>(y) * stride + xx]);
-    // flat plane (max == min): all zeros
-    d[static_cast<long long>(y) * dst_stride + xx] = hi > lo ? (v - static_cast<float>(lo)) * inv - 1.f : 0.f;
+  const bool vec = ((reinterpret_cast<uintptr_t>(p) | static_cast<uintptr_t>(stride) | static_cast<uintptr_t>(width)) & 3) == 0 &&
+                   ((reinterpret_cast<uintptr_t>(d) & 15) | (static_cast<uintptr_t>(dst_stride) & 3)) == 0;
+  if (vec) {
+    const int w4 = width >> 2, total4 = w4 * height;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+      const int y = i / w4, xx = i - y * w4;
+      const uchar4 v = __ldg(reinterpret_cast<const uchar4*>(p + static_cast<long long>(y) * stride) + xx);
+      float4 r;
+      r.x = fmaf(static_cast<float>(v.x), inv, off);
+      r.y = fmaf(static_cast<float>(v.y), inv, off);
+      r.z = fmaf(static_cast<float>(v.z), inv, off);
+      r.w = fmaf(static_cast<float>(v.w), inv, off);
+      reinterpret_cast<float4*>(d + static_cast<long long>(y) * dst_stride)[xx] = r;
+    }
+  } else {
+    const int total = width * height;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+      const int y = i / width, xx = i - y * width;
+      const float v = static_cast<float>(p[static_cast<long long>(y) * stride + xx]);
+      d[static_cast<long long>(y) * dst_stride + xx] = fmaf(v, inv, off);
+    }
   }
 }
 
@@ -383,7 +466,7 @@ extern "C" int vb_sig_wavelet(const float* x, long long x_pitch, int length, con
   }
   if (!stationary) {
     VB_REQUIRE(length % 2 == 0, "vb_sig_wavelet: the decimated transform needs an even length, got %d", length);
-    dim3 grid(ceil_div(length / 2, DWT_THREADS), batch);
+    dim3 grid(ceil_div(length / 2, DWT_TILE), batch);
     sig_dwt_kernel<<<grid, DWT_THREADS, 0, s>>>(x, x_pitch, length, taps, order, ext, hi, lo, out_pitch);
   } else {
     VB_REQUIRE(level >= 1 && level <= 24, "vb_sig_wavelet: level %d outside 1..24", level);

@@ -694,3 +694,50 @@ def sig_convert(src, dst, kind):
     _lib.check(rc, "vb_sig_convert")
     LAUNCHES[0] += 1
     return dst
+
+
+# -- recurrent cells (csrc/recurrent.cu) ------------------------------------------------------------------------------
+def _opt(t):
+    return c_void_p(0) if t is None else _p(t)
+
+
+def lstm_cell_forward(z, c_prev, c, gates, h_next, out):
+    """z [B, 4H] fp32 pre-activations -> gates (saved), c, h into ``h_next`` (bf16 slot or None) and ``out`` rows."""
+    B, H = c.shape
+    rc = _lib.lib().vb_lstm_cell_forward(
+        _p(z), c_longlong(z.stride(0)), _opt(c_prev), _p(c), _p(gates), c_longlong(gates.stride(0)), _opt(h_next),
+        c_longlong(0 if h_next is None else h_next.stride(0)), _opt(out), c_int(0 if out is None else _dt(out)),
+        c_longlong(0 if out is None else out.stride(0)), c_int(B), c_int(H), _stream())
+    _lib.check(rc, "vb_lstm_cell_forward")
+    LAUNCHES[0] += 1
+
+
+def lstm_cell_backward(dh_ext, dh_rec, dc, first, gates, c_prev, c, dz):
+    B, H = c.shape
+    rc = _lib.lib().vb_lstm_cell_backward(
+        _opt(dh_ext), c_int(0 if dh_ext is None else _dt(dh_ext)), c_longlong(0 if dh_ext is None else dh_ext.stride(0)),
+        _opt(dh_rec), c_longlong(0 if dh_rec is None else dh_rec.stride(0)), _p(dc), c_int(int(first)), _p(gates),
+        c_longlong(gates.stride(0)), _opt(c_prev), _p(c), _p(dz), c_longlong(dz.stride(0)), c_int(B), c_int(H),
+        _stream())
+    _lib.check(rc, "vb_lstm_cell_backward")
+    LAUNCHES[0] += 1
+
+
+def rnn_cell_forward(z, h_save, h_next, out):
+    B, H = h_save.shape
+    rc = _lib.lib().vb_rnn_cell_forward(
+        _p(z), c_longlong(z.stride(0)), _p(h_save), _opt(h_next), c_longlong(0 if h_next is None else h_next.stride(0)),
+        _opt(out), c_int(0 if out is None else _dt(out)), c_longlong(0 if out is None else out.stride(0)), c_int(B),
+        c_int(H), _stream())
+    _lib.check(rc, "vb_rnn_cell_forward")
+    LAUNCHES[0] += 1
+
+
+def rnn_cell_backward(dh_ext, dh_rec, h_save, dz):
+    B, H = h_save.shape
+    rc = _lib.lib().vb_rnn_cell_backward(
+        _opt(dh_ext), c_int(0 if dh_ext is None else _dt(dh_ext)), c_longlong(0 if dh_ext is None else dh_ext.stride(0)),
+        _opt(dh_rec), c_longlong(0 if dh_rec is None else dh_rec.stride(0)), _p(h_save), _p(dz),
+        c_longlong(dz.stride(0)), c_int(B), c_int(H), _stream())
+    _lib.check(rc, "vb_rnn_cell_backward")
+    LAUNCHES[0] += 1

@@ -289,14 +289,15 @@ def detect_peaks(data, extremum_type=EXTREMUM_BOTH, capacity=None):
     """Strict interior extrema in index order (reference: ``detect_peaks.h``).
 
     One signal -> ``(positions int32, values float32)``.  A batch of rows -> ``(positions [B, cap], values [B, cap],
-    counts [B])`` with ``cap`` = ``capacity`` or the worst case ``(length - 1) // 2``... rounded up; entries past a
-    row's count are undefined.  On the device nothing is copied back: the three tensors stay on the GPU."""
+    counts [B])`` with ``cap`` = ``capacity`` or the worst case (``length - 2`` for both kinds, ``length // 2`` for
+    one); entries past a row's count are undefined and a row's count may exceed a smaller ``capacity``.  On the device nothing is copied back: the three tensors stay on the GPU."""
     if _is_cuda(data):
         import torch
         from ..ops import kernels
         xr, _ = _rows2d(data)
         B, n = xr.shape
-        cap = int(capacity) if capacity else max(1, n // 2 + 1 if extremum_type == EXTREMUM_BOTH else n // 2)
+        # worst case: an alternating signal makes every interior sample an extremum (one kind: every other one)
+        cap = int(capacity) if capacity else max(1, n - 2 if extremum_type == EXTREMUM_BOTH else n // 2)
         blocks = (n + 1023) // 1024
         counts = torch.empty(B * blocks, dtype=torch.int32, device=data.device)
         pos = torch.empty(B, cap, dtype=torch.int32, device=data.device)

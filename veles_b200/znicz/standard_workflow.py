@@ -66,7 +66,7 @@ class LayerRegistry(object):
         from . import all2all, gd  # noqa: F401
         for mod in ("conv", "gd_conv", "pooling", "gd_pooling", "activation", "dropout", "normalization",
                     "cutter", "deconv", "gd_deconv", "depooling", "channel_splitting", "resizable_all2all",
-                    "rprop_all2all", "weights_zerofilling", "lr_adjust"):
+                    "rprop_all2all", "weights_zerofilling", "lr_adjust", "recurrent"):
             try:
                 __import__("%s.%s" % (__package__, mod))
             except ImportError:
