@@ -75,6 +75,46 @@ def test_snapshot_codecs_roundtrip_whole_workflow(tmp_path, compression):
     wf.launcher.stop()
 
 
+@pytest.mark.parametrize("compression", ["", "gz", "xz"])
+def test_snapshot_to_database_roundtrip(tmp_path, compression):
+    """SnapshotterToDB over the DB-API module that ships with Python (sqlite:<path>); pyodbc is optional."""
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.config import root
+    from veles_b200.models import build_workflow
+    from veles_b200.snapshotter import Snapshotter, SnapshotterToDB
+    root.common.disable.snapshotting = True
+    wf = build_workflow("mnist_mlp", max_epochs=1, minibatch_size=50, n_train=100, n_valid=50)
+    wf.initialize(device=NumpyDevice())
+    wf.run()
+    dsn = "sqlite:" + str(tmp_path / "snapshots.db")
+    snap = Snapshotter(wf, odbc=dsn, table="runs", prefix="t", compression=compression, time_interval=0)
+    assert isinstance(snap, SnapshotterToDB)
+    snap.initialize()
+    wf.launcher.id, wf.launcher.log_id = "job-1", "log-1"
+    snap.suffix = "first"
+    snap.export()
+    first_w = wf.forwards[0].weights.mem.copy()
+    wf.forwards[0].weights.mem[...] += 1.0
+    snap.suffix = "second"
+    snap.export()
+    newest = SnapshotterToDB.import_(dsn, "runs", "job-1", "log-1")
+    assert newest.restored_from_snapshot
+    assert np.array_equal(newest.forwards[0].weights.mem, first_w + 1.0)
+    named = Snapshotter.import_odbc(dsn, "runs", "job-1", "log-1", name=snap.destination.replace("second", "first"))
+    assert np.array_equal(named.forwards[0].weights.mem, first_w)
+    with pytest.raises(KeyError):
+        SnapshotterToDB.import_(dsn, "runs", "nobody", "log-1")
+    assert snap.get_metric_values()["Snapshot"]["table"] == "runs"
+    # the CLI's odbc:// locator resolves to the same call
+    from veles_b200.__main__ import Main
+    m = Main.__new__(Main)
+    m.error = lambda *a: None
+    back = m._load_workflow("odbc://%s&runs&job-1&log-1&" % dsn + snap.destination)
+    assert back is not None and np.array_equal(back.forwards[0].weights.mem, first_w + 1.0)
+    assert m._load_workflow("odbc://%s&runs" % dsn) is None
+    wf.launcher.stop()
+
+
 def _png(path, rgb, size=8):
     from PIL import Image
     Image.fromarray(np.full((size, size, 3), rgb, dtype=np.uint8)).save(path)

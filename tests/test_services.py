@@ -183,3 +183,131 @@ def test_frontend_generator_lists_every_flag():
                  "--force-numpy", "--sync-run", "--train-ratio", "--job-timeout", "--slave-death-probability",
                  "--result-file", "--dry-run", "--backend", "--device", "--random-seed"):
         assert flag in text, flag
+
+
+def _report_info(tmp_path):
+    plot = tmp_path / "curve.svg"
+    plot.write_text("<svg xmlns='http://www.w3.org/2000/svg'></svg>")
+    return {"name": "MnistMLP", "description": "two layers (test)", "id": "abc", "mode": "standalone", "device": "numpy",
+            "run_time": 1.5, "epochs": 3, "seeds": [1, 2], "results": {"EvaluationFitness": 0.97, "Total epochs": 3},
+            "unit_times": [("loader", 0.1), ("fc_tanh1", 0.25)], "config": {"loader": {"minibatch_size": 50}},
+            "plots": [str(plot)], "graph": "digraph Workflow { a -> b }"}
+
+
+def test_pdf_backend_writes_a_wellformed_document(tmp_path):
+    import re
+    from veles_b200.publishing.backend import BackendRegistry, write_text_pdf
+    info = _report_info(tmp_path)
+    info["unit_times"] = [("unit%d" % i, i * 0.01) for i in range(150)]       # forces a second page
+    backend = BackendRegistry.backends["pdf"](directory=str(tmp_path))
+    path = backend.render(info)
+    data = open(path, "rb").read()
+    assert data.startswith(b"%PDF-1.4") and data.rstrip().endswith(b"%%EOF")
+    xref = int(re.search(rb"startxref\n(\d+)", data).group(1))
+    assert data[xref:xref + 4] == b"xref"
+    n = int(re.search(rb"xref\n0 (\d+)", data).group(1))
+    offsets = [int(m) for m in re.findall(rb"(\d{10}) 00000 n", data)]
+    assert len(offsets) == n - 1
+    for i, off in enumerate(offsets, 1):
+        assert data[off:off + len(b"%d 0 obj" % i)] == b"%d 0 obj" % i        # every xref entry points at its object
+    assert len(re.findall(rb"/Type /Page ", data)) == getattr(backend, "pages", 2) >= 2
+    assert b"EvaluationFitness" in data and b"unit149" in data
+    assert write_text_pdf(str(tmp_path / "one.pdf"), "a (b) \\ c") == 1
+
+
+def test_confluence_backend_against_a_local_xmlrpc_server(tmp_path):
+    """The XML-RPC client and the backend against an in-process server speaking the confluence2 API."""
+    import threading
+    import xmlrpc.client
+    from xmlrpc.server import SimpleXMLRPCServer
+    from veles_b200.publishing.backend import BackendRegistry
+    from veles_b200.publishing.confluence import Confluence, ConfluenceError
+
+    pages, attachments, calls = {}, {}, []
+
+    class API(object):
+        def login(self, user, password):
+            if password != "secret":
+                raise xmlrpc.client.Fault(1, "bad credentials")
+            return "tok-1"
+
+        def getPageSummary(self, token, space, title):
+            calls.append(("summary", title))
+            if (space, title) not in pages:
+                raise xmlrpc.client.Fault(2, "no such page")
+            p = pages[(space, title)]
+            return {"id": p["id"], "title": title, "space": space}
+
+        def getPage(self, token, space, title):
+            if (space, title) not in pages:
+                raise xmlrpc.client.Fault(2, "no such page")
+            return dict(pages[(space, title)])
+
+        def storePage(self, token, data):
+            key = (data["space"], data["title"])
+            data = dict(data)
+            data.setdefault("id", str(100 + len(pages)))
+            data["url"] = "http://wiki/%s/%s" % key
+            pages[key] = data
+            return data
+
+        def addAttachment(self, token, page_id, meta, blob):
+            attachments.setdefault(page_id, {})[meta["fileName"]] = (meta["contentType"], blob.data)
+            return meta
+
+        def removeAttachment(self, token, page_id, name):
+            if name not in attachments.get(page_id, {}):
+                raise xmlrpc.client.Fault(3, "no attachment")
+            del attachments[page_id][name]
+            return True
+
+        def getAttachments(self, token, page_id):
+            return [{"fileName": n} for n in attachments.get(page_id, {})]
+
+        def getSpaces(self, token):
+            return [{"key": "ML"}]
+
+    from xmlrpc.server import SimpleXMLRPCRequestHandler
+
+    class Handler(SimpleXMLRPCRequestHandler):
+        rpc_paths = ("/rpc/xmlrpc",)
+
+    srv = SimpleXMLRPCServer(("127.0.0.1", 0), requestHandler=Handler, logRequests=False, allow_none=True)
+    api = API()
+    for name in dir(api):
+        if not name.startswith("_"):
+            srv.register_function(getattr(api, name), "confluence2." + name)
+    port = srv.server_address[1]
+    th = threading.Thread(target=srv.serve_forever, daemon=True)
+    th.start()
+    try:
+        url = "http://127.0.0.1:%d" % port
+        with pytest.raises(ConfluenceError):
+            Confluence(url, "bot", "wrong")
+        conf = Confluence(url, "bot", "secret")
+        assert conf.token == "tok-1" and conf.get_spaces() == [{"key": "ML"}]
+        assert conf.get_page_summary("Reports", "ML") is None
+        conf.store_page_content("Reports", "ML", "<p>index</p>", convert_wiki=False)
+        kw = dict(server=url, username="bot", password="secret", space="ML", parent="Reports")
+        info = _report_info(tmp_path)
+        first = BackendRegistry.backends["confluence"](**kw)
+        assert first.render(info) == "http://wiki/ML/MnistMLP" and first.page == "MnistMLP"
+        second = BackendRegistry.backends["confluence"](**kw)
+        second.render(info)
+        assert second.page == "MnistMLP (1)"                       # an existing title is not overwritten
+        stored = pages[("ML", "MnistMLP")]
+        assert stored["parentId"] == pages[("ML", "Reports")]["id"]
+        assert "EvaluationFitness" in stored["content"] and 'ri:filename="curve.svg"' in stored["content"]
+        att = attachments[stored["id"]]
+        assert set(att) == {"curve.svg", "workflow.dot"} and att["curve.svg"][0] == "image/svg+xml"
+        assert att["workflow.dot"][1].startswith(b"digraph")
+        conf.attach_file("MnistMLP", "ML", {"curve.svg": b"<svg/>"})             # replaces
+        assert attachments[stored["id"]]["curve.svg"][1] == b"<svg/>"
+        assert conf.remove_all_attachments("MnistMLP", "ML") == 2 and not attachments[stored["id"]]
+        with pytest.raises(ConfluenceError):
+            conf.store_page_content("X", "ML", "<p/>", convert_wiki=False, parent="missing")
+        with pytest.raises(ValueError):
+            BackendRegistry.backends["confluence"](server=url)
+    finally:
+        srv.shutdown()
+        srv.server_close()

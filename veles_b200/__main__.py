@@ -184,8 +184,20 @@ class Main(Logger, CommandLineBase):
             urllib.request.urlretrieve(fname_snapshot, tmp)
             fname_snapshot = tmp
         elif fname_snapshot.startswith("odbc://"):
-            self.error("odbc:// snapshots need pyodbc, which is not available")
-            return None
+            # odbc://<data source | sqlite:path>&<table>&<id>&<log id>[&<name>]   (reference __main__.py:543-571)
+            parsed = fname_snapshot[len("odbc://"):].split("&")
+            if len(parsed) not in (4, 5):
+                self.error("Invalid ODBC source; template: odbc://<data source>&<table>&<id>&<log id>[&<name>] "
+                           "(<table> and <log id> may be empty)")
+                return None
+            odbc, table, id_, log_id = parsed[:4]
+            from .snapshotter import SnapshotterToDB
+            try:
+                return SnapshotterToDB.import_(odbc, table or "veles", id_, log_id or id_,
+                                               parsed[4] if len(parsed) == 5 else None)
+            except Exception as e:
+                self.error("Failed to load the snapshot from the database: %s", e)
+                return None
         try:
             return SnapshotterToFile.import_(fname_snapshot)
         except FileNotFoundError:

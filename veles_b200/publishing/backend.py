@@ -1,6 +1,6 @@
 """Publishing backends selected by name (reference: ``veles/publishing/*_backend.py``: markdown, pdf via weasyprint,
-confluence).  Here: ``markdown``, ``html`` (self-contained, plots inlined as SVG), ``json``; ``pdf`` and
-``confluence`` are recognised and raise a clear error (weasyprint / network are unavailable)."""
+confluence).  Here: ``markdown``, ``html`` (self-contained, plots inlined as SVG), ``json``, ``pdf`` (weasyprint
+when installed, else a built-in text PDF writer) and ``confluence`` (XML-RPC client in ``confluence.py``)."""
 from __future__ import annotations
 
 import json
@@ -85,15 +85,141 @@ class JSONBackend(Backend):
         return path
 
 
-class PDFBackend(Backend):
+def write_text_pdf(path, text, title="report", font_size=9, page=(595, 842), margin=40):
+    """A self-contained PDF 1.4 writer for monospaced text reports (Courier, Latin-1): pages, xref, trailer.
+    The reference renders HTML through weasyprint (``publishing/pdf_backend.py:48-90``), which is not available
+    here; a report that is text plus tables does not need a layout engine."""
+    leading = font_size * 1.25
+    cols = int((page[0] - 2 * margin) / (font_size * 0.6))
+    rows = int((page[1] - 2 * margin) / leading)
+    lines = []
+    for raw in text.replace("\t", "    ").split("\n"):
+        if not raw:
+            lines.append("")
+        while raw:
+            lines.append(raw[:cols])
+            raw = raw[cols:]
+    pages = [lines[k:k + rows] for k in range(0, max(len(lines), 1), rows)]
+
+    def esc(t):
+        t = t.encode("latin-1", "replace").decode("latin-1")
+        return t.replace("\\", "\\\\").replace("(", "\\(").replace(")", "\\)")
+
+    objs = []                                   # 1-based object bodies (bytes)
+
+    def add(body):
+        objs.append(body if isinstance(body, bytes) else body.encode("latin-1"))
+        return len(objs)
+
+    catalog = add("")                           # filled below
+    pages_obj = add("")
+    font = add("<< /Type /Font /Subtype /Type1 /BaseFont /Courier /Encoding /WinAnsiEncoding >>")
+    kids = []
+    for chunk in pages:
+        ops = ["BT", "/F1 %d Tf" % font_size, "%g TL" % leading, "%d %g Td" % (margin, page[1] - margin - font_size)]
+        for ln in chunk:
+            ops.append("(%s) Tj T*" % esc(ln))
+        ops.append("ET")
+        stream = "\n".join(ops).encode("latin-1")
+        content = add(b"<< /Length %d >>\nstream\n" % len(stream) + stream + b"\nendstream")
+        kids.append(add("<< /Type /Page /Parent %d 0 R /MediaBox [0 0 %d %d] /Contents %d 0 R "
+                        "/Resources << /Font << /F1 %d 0 R >> >> >>" % (pages_obj, page[0], page[1], content, font)))
+    objs[catalog - 1] = ("<< /Type /Catalog /Pages %d 0 R >>" % pages_obj).encode("latin-1")
+    objs[pages_obj - 1] = ("<< /Type /Pages /Count %d /Kids [%s] >>"
+                           % (len(kids), " ".join("%d 0 R" % k for k in kids))).encode("latin-1")
+    info = add("<< /Title (%s) /Producer (veles_b200) >>" % esc(title))
+    out = bytearray(b"%PDF-1.4\n%\xe2\xe3\xcf\xd3\n")
+    offsets = []
+    for n, body in enumerate(objs, 1):
+        offsets.append(len(out))
+        out += b"%d 0 obj\n" % n + body + b"\nendobj\n"
+    xref = len(out)
+    out += b"xref\n0 %d\n0000000000 65535 f \n" % (len(objs) + 1)
+    for off in offsets:
+        out += b"%010d 00000 n \n" % off
+    out += b"trailer\n<< /Size %d /Root %d 0 R /Info %d 0 R >>\nstartxref\n%d\n%%%%EOF\n" % (
+        len(objs) + 1, catalog, info, xref)
+    with open(path, "wb") as f:
+        f.write(bytes(out))
+    return len(pages)
+
+
+class PDFBackend(MarkdownBackend):
+    """Report as PDF: through weasyprint when it is installed (the reference's route), else as a paginated text PDF
+    written by ``write_text_pdf``."""
     MAPPING = "pdf"
 
     def render(self, info):
-        raise RuntimeError("The PDF backend needs weasyprint, which is not installed; use \"html\" or \"markdown\"")
+        path = self.target(info["name"], "pdf")
+        try:
+            import weasyprint
+        except ImportError:
+            weasyprint = None
+        if weasyprint is not None:
+            import html
+            doc = "<html><body><pre>%s</pre></body></html>" % html.escape(self.text(info))
+            weasyprint.HTML(string=doc).write_pdf(path)
+        else:
+            self.pages = write_text_pdf(path, self.text(dict(info, graph="")), title=info["name"])
+        return path
 
 
-class ConfluenceBackend(Backend):
+class ConfluenceBackend(MarkdownBackend):
+    """Publishes the report as a Confluence page and attaches the plots (reference:
+    ``publishing/confluence_backend.py:42-80``).  kwargs: ``server``, ``username``, ``password``, ``space``,
+    optional ``page`` (default: the workflow name, made unique with " (n)") and ``parent``."""
     MAPPING = "confluence"
 
+    def __init__(self, **kwargs):
+        super(ConfluenceBackend, self).__init__(**kwargs)
+        missing = [k for k in ("server", "username", "password", "space") if k not in kwargs]
+        if missing:
+            raise ValueError("ConfluenceBackend: missing %s" % ", ".join(missing))
+        self.access = {k: kwargs[k] for k in ("server", "username", "password")}
+        self.space = kwargs["space"]
+        self.page = kwargs.get("page")
+        self.parent = kwargs.get("parent")
+        self.url = None
+
+    def storage_xml(self, info):
+        import html
+        parts = ["<h1>%s</h1>" % html.escape(str(info["name"])), "<p>%s</p>" % html.escape(info.get("description") or ""),
+                 "<ul>"]
+        for k in ("id", "mode", "device", "epochs", "seeds"):
+            parts.append("<li><strong>%s</strong>: %s</li>" % (k, html.escape(str(info.get(k)))))
+        parts.append("<li><strong>run time</strong>: %.1f s</li></ul><h2>Results</h2><table><tbody>"
+                     % info.get("run_time", 0))
+        for k, v in sorted(info.get("results", {}).items()):
+            if k not in ("Confusion", "Labels", "models"):
+                parts.append("<tr><th>%s</th><td>%s</td></tr>" % (html.escape(str(k)), html.escape(str(v))))
+        parts.append("</tbody></table><h2>Unit run times</h2><table><tbody>")
+        for n, t in info.get("unit_times", []):
+            parts.append("<tr><td>%s</td><td>%.4f</td></tr>" % (html.escape(str(n)), t))
+        parts.append("</tbody></table><h2>Configuration</h2>")
+        parts.append('<ac:structured-macro ac:name="code"><ac:plain-text-body><![CDATA[%s]]></ac:plain-text-body>'
+                     '</ac:structured-macro>' % json.dumps(info.get("config", {}), indent=1, default=str)
+                     .replace("]]>", "]] >"))
+        for p in info.get("plots", []):
+            parts.append('<p><ac:image><ri:attachment ri:filename="%s" /></ac:image></p>'
+                         % html.escape(os.path.basename(p)))
+        return "".join(parts)
+
     def render(self, info):
-        raise RuntimeError("The Confluence backend needs network access; use \"html\" or \"markdown\"")
+        from .confluence import Confluence
+        conf = Confluence(**self.access)
+        page = self.page
+        if page is None:
+            page, index = str(info["name"]), 1
+            while conf.get_page_summary(page, self.space) is not None:
+                page = "%s (%d)" % (info["name"], index)
+                index += 1
+        published = conf.store_page_content(page, self.space, self.storage_xml(info), convert_wiki=False,
+                                            parent=self.parent)
+        files = {os.path.basename(p): p for p in info.get("plots", []) if p and os.path.exists(p)}
+        if info.get("graph"):
+            files["workflow.dot"] = info["graph"].encode("utf-8")
+        if files:
+            conf.attach_file(page, self.space, files)
+        self.page = page
+        self.url = published.get("url")
+        return self.url or page

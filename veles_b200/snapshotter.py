@@ -183,39 +183,113 @@ class SnapshotterToFile(SnapshotterBase):
 
 
 class SnapshotterToDB(SnapshotterBase):
-    """ODBC blob storage (reference :427-518).  Requires pyodbc, which is optional."""
+    """Snapshots as blobs in a database table (reference ``snapshotter.py:428-518``, ODBC only there).
+
+    ``odbc`` is an ODBC connection string (needs ``pyodbc``) or ``sqlite:<path>`` for the DB-API module that ships
+    with Python, which creates the table on first use.  Columns: timestamp, id, log_id, workflow, name, codec, data.
+    ``SnapshotterToDB.import_(odbc, table, id_, log_id, name=None)`` restores the named (or the newest) snapshot.
+    """
     MAPPING = "odbc"
     hide_from_registry = False
+    CODECS = {None: (lambda b, l: b, lambda b: b, "pickle"), "": (lambda b, l: b, lambda b: b, "pickle"),
+              "gz": (lambda b, l: gzip.compress(b, l), gzip.decompress, "gz"),
+              "bz2": (lambda b, l: __import__("bz2").compress(b, l), lambda b: __import__("bz2").decompress(b), "bz2"),
+              "xz": (lambda b, l: __import__("lzma").compress(b, preset=l), lambda b: __import__("lzma").decompress(b),
+                     "xz")}
 
     def __init__(self, workflow, **kwargs):
         super(SnapshotterToDB, self).__init__(workflow, **kwargs)
         self.odbc = kwargs.get("odbc")
         self.table = kwargs.get("table", "veles")
+        if self.compression not in self.CODECS:
+            raise ValueError("SnapshotterToDB: unsupported compression %r" % (self.compression,))
+
+    @staticmethod
+    def connect(dsn, table=None):
+        if dsn is None:
+            raise ValueError("SnapshotterToDB needs odbc=<connection string>")
+        if str(dsn).startswith("sqlite:"):
+            import sqlite3
+            conn = sqlite3.connect(str(dsn)[len("sqlite:"):])
+            if table is not None:
+                conn.execute("create table if not exists %s(timestamp text, id text, log_id text, workflow text, "
+                             "name text, codec text, data blob)" % table)
+            return conn
+        try:
+            import pyodbc
+        except ImportError:
+            raise RuntimeError("SnapshotterToDB: %r needs pyodbc, which is not installed (sqlite:<path> works "
+                               "without it)" % dsn)
+        return pyodbc.connect(dsn)
 
     def initialize(self, **kwargs):
         super(SnapshotterToDB, self).initialize(**kwargs)
-        try:
-            import pyodbc  # noqa: F401
-        except ImportError:
-            raise RuntimeError("SnapshotterToDB needs pyodbc, which is not installed; use the \"file\" snapshotter")
+        self.connect(self.odbc, self.table).close()      # fail now, not at the first snapshot
 
     def export(self):
-        import pyodbc
-        payload = gzip.compress(pickle.dumps(self.workflow, protocol=best_protocol), self.compression_level)
-        conn = pyodbc.connect(self.odbc)
+        enc, _, codec = self.CODECS[self.compression]
+        payload = enc(pickle.dumps(self.workflow, protocol=best_protocol), self.compression_level)
+        name = ".".join((self.prefix, self.suffix or "", str(best_protocol)))
+        conn = self.connect(self.odbc, self.table)
         try:
             cur = conn.cursor()
-            now = time.strftime("%Y-%m-%d %H:%M:%S")
+            now = time.strftime("%Y-%m-%d %H:%M:%S") + (".%06d" % int((time.time() % 1) * 1e6))
             cur.execute("insert into %s(timestamp, id, log_id, workflow, name, codec, data) "
-                        "values (?, ?, ?, ?, ?, ?, ?);" % self.table, now, getattr(self.launcher, "id", ""),
-                        getattr(self.launcher, "log_id", ""), self.workflow.name,
-                        "%s_%s" % (self.prefix, self.suffix), "gz", payload)
+                        "values (?, ?, ?, ?, ?, ?, ?);" % self.table,
+                        (now, str(getattr(self.launcher, "id", "")), str(getattr(self.launcher, "log_id", "")),
+                         str(self.workflow.name), name, codec, payload))
             conn.commit()
-            self.destination = "odbc://%s&%s" % (self.odbc, self.table)
+            self.destination = name
+            self.info("Wrote %d bytes as %s into table %s", len(payload), name, self.table)
         finally:
             conn.close()
 
+    @staticmethod
+    def import_(odbc, table, id_, log_id, name=None):
+        conn = SnapshotterToDB.connect(odbc)
+        try:
+            cur = conn.cursor()
+            query = "select codec, data from %s where id=? and log_id=?" % table
+            args = [str(id_), str(log_id)]
+            if name is not None:
+                query += " and name=?"
+                args.append(name)
+            query += " order by timestamp desc"
+            cur.execute(query, args)
+            row = cur.fetchone()
+        finally:
+            conn.close()
+        if row is None:
+            raise KeyError("no snapshot id=%s log_id=%s name=%s in %s" % (id_, log_id, name, table))
+        decoders = {c[2]: c[1] for c in SnapshotterToDB.CODECS.values()}
+        wf = pickle.loads(decoders[row[0]](bytes(row[1])))
+        try:
+            wf._restored_from_snapshot_ = True
+        except AttributeError:
+            pass
+        return wf
+
+    def get_metric_values(self):
+        return {"Snapshot": {"odbc": self.odbc, "table": self.table, "name": self.destination}}
+
 
 class Snapshotter(SnapshotterToFile):
-    """Default snapshotter (kwarg ``odbc=...`` is rejected with a pointer to SnapshotterToDB)."""
+    """Default snapshotter: files, or the database variant when constructed with ``odbc=...`` (reference :522-535)."""
     MAPPING = "default"
+
+    def __new__(cls, workflow=None, **kwargs):
+        if cls is Snapshotter and kwargs.get("odbc"):
+            return SnapshotterToDB(workflow, **kwargs)
+        return super(Snapshotter, cls).__new__(cls)
+
+    def __init__(self, workflow, **kwargs):
+        kwargs.get("odbc"), kwargs.get("table")      # accepted: they select the database variant in __new__
+        super(Snapshotter, self).__init__(workflow, **kwargs)
+
+    @staticmethod
+    def import_file(file_name):
+        return SnapshotterToFile.import_(file_name)
+
+    @staticmethod
+    def import_odbc(odbc, table, id_, log_id, name=None):
+        return SnapshotterToDB.import_(odbc, table, id_, log_id, name)
