@@ -27,6 +27,14 @@ CASES = [
     ("cutter", (2, 9, 7, 5), {"padding": (1, 0, 0, 2)}),
     ("all2all_resizable", (16, 40), {"output_sample_shape": 24}),
     ("norm", (4, 6, 6, 96), {"alpha": 0.0001, "beta": 0.75, "n": 5, "k": 1}),
+    ("norm", (3, 5, 7, 256), {"alpha": 0.0001, "beta": 0.75, "n": 5, "k": 2}),
+    ("norm", (5, 3, 3, 40), {"alpha": 0.01, "beta": 0.5, "n": 3, "k": 1}),
+    ("norm", (2, 9, 4, 8), {"alpha": 0.01, "beta": 0.75, "n": 7, "k": 1}),
+    ("norm", (2, 4, 4, 384), {"alpha": 0.001, "beta": 0.75, "n": 5, "k": 2}),
+    ("max_pooling", (3, 16, 14, 24), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
+    ("max_pooling", (2, 13, 13, 256), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
+    ("maxabs_pooling", (3, 11, 15, 16), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
+    ("max_pooling", (2, 5, 3, 8), {"kx": 3, "ky": 3, "sliding": (2, 2)}),
     ("activation_tanh", (8, 40), {}),
     ("activation_str", (8, 40), {}),
     ("activation_log", (8, 40), {}),

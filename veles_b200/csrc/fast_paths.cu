@@ -337,6 +337,139 @@ __global__ void pool_backward_vec8_kernel(int kind, const __nv_bfloat16* __restr
 }
 
 // ---------------------------------------------------------------------------------------------
+// 3x3 / stride 2 max (kind 0) and max-abs (kind 1) pooling, the AlexNet geometry, with compile-time window
+// constants: all nine (forward) or four (backward) 16-byte loads of a thread are issued before any arithmetic and
+// the index arithmetic has no run-time divisors besides the tensor extents.
+// Backward is organised by 2x2 input blocks: block (bh, bw) = pixels (2bh+i, 2bw+j) is covered exactly by the
+// windows (bh-1..bh) x (bw-1..bw), so four dy / argmax loads serve four input pixels (the per-pixel gather form
+// loads up to four windows for every single pixel: 9 loads per block instead of 4).
+// ---------------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(128)
+pool_fwd_3x3s2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ offs8,
+                      const FastPoolGeom g) {
+  const unsigned C8 = g.C >> 3;
+  const unsigned total = static_cast<unsigned>(g.B) * g.OH * g.OW * C8;
+  for (unsigned tt = blockIdx.x * blockDim.x + threadIdx.x; tt < total; tt += gridDim.x * blockDim.x) {
+    const int c = static_cast<int>(tt % C8) << 3;
+    unsigned r = tt / C8;
+    const int ow = static_cast<int>(r % g.OW);
+    r /= g.OW;
+    const int oh = static_cast<int>(r % g.OH);
+    const int b = static_cast<int>(r / g.OH);
+    const int h0 = 2 * oh, w0 = 2 * ow;
+    const __nv_bfloat16* base = x + ((static_cast<long long>(b) * g.H + h0) * g.W + w0) * g.C + c;
+    uint4 v[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const bool ok = (h0 + i < g.H) && (w0 + j < g.W);
+        v[i * 3 + j] = ok ? ldg16(base + (static_cast<long long>(i) * g.W + j) * g.C) : make_uint4(0, 0, 0, 0);
+      }
+    float best[8], key[8];
+    unsigned bl[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      best[q] = 0.0f;
+      key[q] = -INFINITY;
+      bl[q] = 0;
+    }
+#pragma unroll
+    for (int l = 0; l < 9; ++l) {
+      const bool ok = (h0 + l / 3 < g.H) && (w0 + l % 3 < g.W);
+      float f[8];
+      unpack8(v[l], f);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float kq = KIND == 1 ? fabsf(f[q]) : f[q];
+        if (ok && kq > key[q]) {
+          key[q] = kq;
+          best[q] = f[q];
+          bl[q] = l;
+        }
+      }
+    }
+    const long long oo = ((static_cast<long long>(b) * g.OH + oh) * g.OW + ow) * g.C + c;
+    *reinterpret_cast<uint4*>(y + oo) = pack8(best);
+    *reinterpret_cast<uint2*>(offs8 + oo) =
+        make_uint2(bl[0] | (bl[1] << 8) | (bl[2] << 16) | (bl[3] << 24), bl[4] | (bl[5] << 8) | (bl[6] << 16) | (bl[7] << 24));
+  }
+}
+
+__global__ void __launch_bounds__(128)
+pool_bwd_3x3s2_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ offs8,
+                      __nv_bfloat16* __restrict__ dx, const FastPoolGeom g, const __nv_bfloat16* __restrict__ z,
+                      int deriv) {
+  const unsigned C8 = g.C >> 3;
+  const int BH = (g.H + 1) >> 1, BW = (g.W + 1) >> 1;
+  const unsigned total = static_cast<unsigned>(g.B) * BH * BW * C8;
+  for (unsigned tt = blockIdx.x * blockDim.x + threadIdx.x; tt < total; tt += gridDim.x * blockDim.x) {
+    const int c = static_cast<int>(tt % C8) << 3;
+    unsigned r = tt / C8;
+    const int bw = static_cast<int>(r % BW);
+    r /= BW;
+    const int bh = static_cast<int>(r % BH);
+    const int b = static_cast<int>(r / BH);
+    // windows (bh - 1 + a, bw - 1 + e), a, e in {0, 1}
+    uint4 dv[4];
+    uint2 lv[4];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int oh = bh - 1 + a, ow = bw - 1 + e;
+        const bool ok = oh >= 0 && oh < g.OH && ow >= 0 && ow < g.OW;
+        const long long o = ((static_cast<long long>(b) * g.OH + oh) * g.OW + ow) * g.C + c;
+        dv[a * 2 + e] = ok ? ldg16(dy + o) : make_uint4(0, 0, 0, 0);
+        // 0xff never equals a window-local index (0..8): an absent window contributes nothing
+        lv[a * 2 + e] = ok ? __ldg(reinterpret_cast<const uint2*>(offs8 + o)) : make_uint2(0xffffffffu, 0xffffffffu);
+      }
+    float acc[4][8];
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc[p][q] = 0.0f;
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        float f[8];
+        unpack8(dv[a * 2 + e], f);
+        const uint2 l8 = lv[a * 2 + e];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const unsigned l = ((q < 4 ? l8.x : l8.y) >> (8 * (q & 3))) & 0xffu;
+          // pixel (i, j) of the block sits at window-local row (a ? i : 2 [only i == 0]), column (e ? j : 2 [only j == 0])
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              if ((a == 0 && i == 1) || (e == 0 && j == 1)) continue;
+              const unsigned want = static_cast<unsigned>((a ? i : 2) * 3 + (e ? j : 2));
+              if (l == want) acc[i * 2 + j][q] += f[q];
+            }
+        }
+      }
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int h = 2 * bh + i, w = 2 * bw + j;
+        if (h >= g.H || w >= g.W) continue;
+        const long long me = ((static_cast<long long>(b) * g.H + h) * g.W + w) * g.C + c;
+        if (z != nullptr) {
+          float f[8];
+          unpack8(ldg16(z + me), f);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) acc[i * 2 + j][q] *= act_deriv_from_output(deriv, f[q]);
+        }
+        *reinterpret_cast<uint4*>(dx + me) = pack8(acc[i * 2 + j]);
+      }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // LRN: one warp per pixel, the pixel's channel vector staged in shared memory, so every element
 // costs one pow instead of one per window member (backward was O(n^2) pows per element).
 // smem per warp: 3*C floats (x, p = s^-beta, t = dy*x*p/s).
@@ -529,6 +662,121 @@ lrn_backward_vec8_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
 }
 
 // ---------------------------------------------------------------------------------------------
+// LRN for C <= 256: the lanes of a warp hold consecutive 8-channel groups of whole pixels (32 / T pixels per warp,
+// T = C / 8), so the +-HALF neighbour channels of a group are two registers of the adjacent lane: a thread loads its
+// own 16 bytes only (the register-window kernels above load 48) and evaluates one power per own channel (backward:
+// 8 instead of 8 + 2 HALF); 2 HALF shuffles replace the neighbour loads (backward: twice, for the squares and for
+// the t terms).  Pixel borders are lanes with g == 0 / g == T - 1: their outer neighbours are zeroed.
+// ---------------------------------------------------------------------------------------------
+template <int HALF>
+__device__ __forceinline__ void lrn_exchange(const float (&own)[8], float (&ext)[8 + 2 * HALF], bool first, bool last) {
+#pragma unroll
+  for (int q = 0; q < 8; ++q) ext[HALF + q] = own[q];
+#pragma unroll
+  for (int d = 0; d < HALF; ++d) {
+    const float l = __shfl_up_sync(0xffffffffu, own[8 - HALF + d], 1);
+    const float r = __shfl_down_sync(0xffffffffu, own[d], 1);
+    ext[d] = first ? 0.0f : l;
+    ext[HALF + 8 + d] = last ? 0.0f : r;
+  }
+}
+
+template <int HALF>
+__global__ void __launch_bounds__(256)
+lrn_forward_shfl_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels, int C,
+                        float alpha, float beta, float k) {
+  const int T = C >> 3;
+  const int ppw = 32 / T;                       // pixels per warp
+  const int lane = threadIdx.x & 31;
+  const int pl = lane / T, g = lane - pl * T;
+  const bool active_lane = pl < ppw;
+  const bool beta34 = (beta == 0.75f);
+  const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const long long groups = (pixels + ppw - 1) / ppw;
+  for (long long w = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5; w < groups; w += warps_total) {
+    const long long px = w * ppw + pl;
+    const bool active = active_lane && px < pixels;
+    float xv[8];
+    if (active) unpack8(ldg16(x + px * C + g * 8), xv);
+    else {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) xv[q] = 0.0f;
+    }
+    float sq[8], ext[8 + 2 * HALF];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) sq[q] = xv[q] * xv[q];
+    lrn_exchange<HALF>(sq, ext, g == 0, g == T - 1);
+    float out[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      float s = 0.0f;
+#pragma unroll
+      for (int d = 0; d <= 2 * HALF; ++d) s += ext[q + d];
+      out[q] = xv[q] * lrn_pow_neg(k + alpha * s, beta, beta34);
+    }
+    if (active) *reinterpret_cast<uint4*>(y + px * C + g * 8) = pack8(out);
+  }
+}
+
+template <int HALF>
+__global__ void __launch_bounds__(256)
+lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                         __nv_bfloat16* __restrict__ dx, long long pixels, int C, float alpha, float beta, float k,
+                         int deriv) {
+  const int T = C >> 3;
+  const int ppw = 32 / T;
+  const int lane = threadIdx.x & 31;
+  const int pl = lane / T, g = lane - pl * T;
+  const bool active_lane = pl < ppw;
+  const bool beta34 = (beta == 0.75f);
+  const float coef = 2.0f * alpha * beta;
+  const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const long long groups = (pixels + ppw - 1) / ppw;
+  for (long long w = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5; w < groups; w += warps_total) {
+    const long long px = w * ppw + pl;
+    const bool active = active_lane && px < pixels;
+    float xv[8], dv[8];
+    if (active) {
+      const uint4 xr = ldg16(x + px * C + g * 8);
+      const uint4 dr = ldg16(dy + px * C + g * 8);
+      unpack8(xr, xv);
+      unpack8(dr, dv);
+    } else {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) xv[q] = dv[q] = 0.0f;
+    }
+    float sq[8], ext[8 + 2 * HALF];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) sq[q] = xv[q] * xv[q];
+    lrn_exchange<HALF>(sq, ext, g == 0, g == T - 1);
+    float t[8], dp[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      float s = 0.0f;
+#pragma unroll
+      for (int d = 0; d <= 2 * HALF; ++d) s += ext[q + d];
+      s = k + alpha * s;
+      float inv_s;
+      const float pw = lrn_pow_neg_inv(s, beta, beta34, inv_s);
+      dp[q] = dv[q] * pw;
+      t[q] = dp[q] * xv[q] * inv_s;
+    }
+    lrn_exchange<HALF>(t, ext, g == 0, g == T - 1);
+    float out[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      float acc = 0.0f;
+#pragma unroll
+      for (int d = 0; d <= 2 * HALF; ++d) acc += ext[q + d];
+      float v = dp[q] - coef * xv[q] * acc;
+      if (deriv) v *= act_deriv_from_output(deriv, xv[q]);
+      out[q] = v;
+    }
+    if (active) *reinterpret_cast<uint4*>(dx + px * C + g * 8) = pack8(out);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Launchers (return 1 when the fast path was taken, 0 when the caller must use the generic one,
 // negative on error)
 // ---------------------------------------------------------------------------------------------
@@ -580,6 +828,16 @@ int fast_pool_forward(int kind, const void* x, void* y, int* offs, uint8_t* offs
     return 0;
   const long long total = static_cast<long long>(g.B) * g.OH * g.OW * (g.C >> 3);
   if (total == 0) return 1;
+  if (offs == nullptr && offs8 != nullptr && kind != 2 && g.kx == 3 && g.ky == 3 && g.sx == 2 && g.sy == 2) {
+    if (kind == 1)
+      pool_fwd_3x3s2_kernel<1><<<grid_cap2(total, 128), 128, 0, s>>>(static_cast<const __nv_bfloat16*>(x),
+                                                                    static_cast<__nv_bfloat16*>(y), offs8, g);
+    else
+      pool_fwd_3x3s2_kernel<0><<<grid_cap2(total, 128), 128, 0, s>>>(static_cast<const __nv_bfloat16*>(x),
+                                                                    static_cast<__nv_bfloat16*>(y), offs8, g);
+    VB_CHECK_CUDA(cudaGetLastError());
+    return 1;
+  }
   pool_forward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(x),
                                                                  static_cast<__nv_bfloat16*>(y), offs, offs8, g);
   VB_CHECK_CUDA(cudaGetLastError());
@@ -595,6 +853,14 @@ int fast_pool_backward(int kind, const void* dy, const int* offs, const uint8_t*
     return 0;
   const long long total = static_cast<long long>(g.B) * g.H * g.W * (g.C >> 3);
   if (total == 0) return 1;
+  if (offs8 != nullptr && kind != 2 && g.kx == 3 && g.ky == 3 && g.sx == 2 && g.sy == 2) {
+    const long long blocks4 = static_cast<long long>(g.B) * ((g.H + 1) / 2) * ((g.W + 1) / 2) * (g.C >> 3);
+    pool_bwd_3x3s2_kernel<<<grid_cap2(blocks4, 128), 128, 0, s>>>(static_cast<const __nv_bfloat16*>(dy), offs8,
+                                                                 static_cast<__nv_bfloat16*>(dx), g,
+                                                                 static_cast<const __nv_bfloat16*>(z), deriv);
+    VB_CHECK_CUDA(cudaGetLastError());
+    return 1;
+  }
   pool_backward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(dy), offs, offs8,
                                                                   static_cast<__nv_bfloat16*>(dx), g,
                                                                   static_cast<const __nv_bfloat16*>(z), deriv);
@@ -621,6 +887,18 @@ int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, flo
     const int grid = grid_cap2(total, 256);
     const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
     __nv_bfloat16* yp = static_cast<__nv_bfloat16*>(y);
+    if (C <= 256) {      // whole pixels per warp: neighbours by shuffle
+      const int ppw = 32 / (C >> 3);
+      const int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
+      switch (half) {
+        case 1: lrn_forward_shfl_kernel<1><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+        case 2: lrn_forward_shfl_kernel<2><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+        case 3: lrn_forward_shfl_kernel<3><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+        default: lrn_forward_shfl_kernel<4><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+      }
+      VB_CHECK_CUDA(cudaGetLastError());
+      return 1;
+    }
     switch (half) {
       case 1: lrn_forward_vec8_kernel<1><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
       case 2: lrn_forward_vec8_kernel<2><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
@@ -653,6 +931,18 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
     const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
     const __nv_bfloat16* dp = static_cast<const __nv_bfloat16*>(dy);
     __nv_bfloat16* op = static_cast<__nv_bfloat16*>(dx);
+    if (C <= 256) {
+      const int ppw = 32 / (C >> 3);
+      const int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
+      switch (half) {
+        case 1: lrn_backward_shfl_kernel<1><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+        case 2: lrn_backward_shfl_kernel<2><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+        case 3: lrn_backward_shfl_kernel<3><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+        default: lrn_backward_shfl_kernel<4><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+      }
+      VB_CHECK_CUDA(cudaGetLastError());
+      return 1;
+    }
     switch (half) {
       case 1: lrn_backward_vec8_kernel<1><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
       case 2: lrn_backward_vec8_kernel<2><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
