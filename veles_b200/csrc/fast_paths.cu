@@ -344,12 +344,22 @@ __global__ void pool_backward_vec8_kernel(int kind, const __nv_bfloat16* __restr
 // windows (bh-1..bh) x (bw-1..bw), so four dy / argmax loads serve four input pixels (the per-pixel gather form
 // loads up to four windows for every single pixel: 9 loads per block instead of 4).
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ __nv_bfloat162 as_bf162(unsigned u) {
+  __nv_bfloat162 r;
+  *reinterpret_cast<unsigned*>(&r) = u;
+  return r;
+}
+__device__ __forceinline__ unsigned as_u32(__nv_bfloat162 v) { return *reinterpret_cast<unsigned*>(&v); }
+
+// Forward: two channels per instruction (bf16x2 compare / max), the running argmax kept as two 16-bit lanes that are
+// merged by one LOP3 per candidate; the result pairs are stored without any float conversion.
 template <int KIND>
 __global__ void __launch_bounds__(128)
 pool_fwd_3x3s2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ offs8,
                       const FastPoolGeom g) {
   const unsigned C8 = g.C >> 3;
   const unsigned total = static_cast<unsigned>(g.B) * g.OH * g.OW * C8;
+  const unsigned NEG_INF2 = 0xff80ff80u;     // (-inf, -inf): never wins, stands for taps outside the image
   for (unsigned tt = blockIdx.x * blockDim.x + threadIdx.x; tt < total; tt += gridDim.x * blockDim.x) {
     const int c = static_cast<int>(tt % C8) << 3;
     unsigned r = tt / C8;
@@ -365,35 +375,38 @@ pool_fwd_3x3s2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __rest
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
         const bool ok = (h0 + i < g.H) && (w0 + j < g.W);
-        v[i * 3 + j] = ok ? ldg16(base + (static_cast<long long>(i) * g.W + j) * g.C) : make_uint4(0, 0, 0, 0);
+        v[i * 3 + j] = ok ? ldg16(base + (static_cast<long long>(i) * g.W + j) * g.C)
+                          : make_uint4(NEG_INF2, NEG_INF2, NEG_INF2, NEG_INF2);
       }
-    float best[8], key[8];
-    unsigned bl[8];
+    // tap 0 always lies inside the image: it seeds the running maximum (first maximum wins ties, like the oracle)
+    unsigned best[4] = {v[0].x, v[0].y, v[0].z, v[0].w};
+    unsigned idx[4] = {0u, 0u, 0u, 0u};
+    __nv_bfloat162 key[4];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      best[q] = 0.0f;
-      key[q] = -INFINITY;
-      bl[q] = 0;
-    }
+    for (int p2 = 0; p2 < 4; ++p2) key[p2] = KIND == 1 ? __habs2(as_bf162(best[p2])) : as_bf162(best[p2]);
 #pragma unroll
-    for (int l = 0; l < 9; ++l) {
-      const bool ok = (h0 + l / 3 < g.H) && (w0 + l % 3 < g.W);
-      float f[8];
-      unpack8(v[l], f);
+    for (int l = 1; l < 9; ++l) {
+      const unsigned cand[4] = {v[l].x, v[l].y, v[l].z, v[l].w};
 #pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const float kq = KIND == 1 ? fabsf(f[q]) : f[q];
-        if (ok && kq > key[q]) {
-          key[q] = kq;
-          best[q] = f[q];
-          bl[q] = l;
+      for (int p2 = 0; p2 < 4; ++p2) {
+        const __nv_bfloat162 cv = as_bf162(cand[p2]);
+        const __nv_bfloat162 ck = KIND == 1 ? __habs2(cv) : cv;
+        // a tap outside the image is -inf (|-inf| = +inf would win the max-abs race: mask it out explicitly)
+        unsigned m = __hgt2_mask(ck, key[p2]);
+        if (KIND == 1) {
+          const bool ok = (h0 + l / 3 < g.H) && (w0 + l % 3 < g.W);
+          m = ok ? m : 0u;
         }
+        key[p2] = as_bf162((as_u32(ck) & m) | (as_u32(key[p2]) & ~m));
+        best[p2] = (cand[p2] & m) | (best[p2] & ~m);
+        idx[p2] = ((static_cast<unsigned>(l) * 0x00010001u) & m) | (idx[p2] & ~m);
       }
     }
     const long long oo = ((static_cast<long long>(b) * g.OH + oh) * g.OW + ow) * g.C + c;
-    *reinterpret_cast<uint4*>(y + oo) = pack8(best);
+    *reinterpret_cast<uint4*>(y + oo) = make_uint4(best[0], best[1], best[2], best[3]);
+    // idx[p2] = (index of channel 2 p2) | (index of channel 2 p2 + 1) << 16  ->  one byte per channel
     *reinterpret_cast<uint2*>(offs8 + oo) =
-        make_uint2(bl[0] | (bl[1] << 8) | (bl[2] << 16) | (bl[3] << 24), bl[4] | (bl[5] << 8) | (bl[6] << 16) | (bl[7] << 24));
+        make_uint2(__byte_perm(idx[0], idx[1], 0x6420), __byte_perm(idx[2], idx[3], 0x6420));
   }
 }
 
@@ -447,7 +460,7 @@ pool_bwd_3x3s2_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __res
             for (int j = 0; j < 2; ++j) {
               if ((a == 0 && i == 1) || (e == 0 && j == 1)) continue;
               const unsigned want = static_cast<unsigned>((a ? i : 2) * 3 + (e ? j : 2));
-              if (l == want) acc[i * 2 + j][q] += f[q];
+              acc[i * 2 + j][q] += (l == want) ? f[q] : 0.0f;
             }
         }
       }
@@ -563,19 +576,26 @@ __device__ __forceinline__ void load24(const __nv_bfloat16* row, int g, int T, f
   for (int q = 0; q < 8; ++q) v[16 + q] = a[q];
 }
 
+// One MUFU.RSQ: s = k + alpha * sum >= k > 0 is a normal number, so the denormal fix-up code that rsqrtf() carries
+// (a compare and two predicated multiplies per call) is dead weight in these instruction-bound kernels.
+__device__ __forceinline__ float rsqrt_fast(float v) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
 // s^-beta.  The AlexNet value beta = 0.75 needs no log/exp: r = rsqrt(s), s^-0.75 = r * sqrt(r), 1/s = r * r.
 __device__ __forceinline__ float lrn_pow_neg(float s, float beta, bool beta34) {
   if (beta34) {
-    const float r = rsqrtf(s);
-    return r * r * rsqrtf(r);   // r^1.5 with two MUFU.RSQ (sqrtf would take the slow IEEE path)
+    const float r = rsqrt_fast(s);
+    return r * r * rsqrt_fast(r);   // r^1.5 with two MUFU.RSQ (sqrtf would take the slow IEEE path)
   }
   return __powf(s, -beta);
 }
 __device__ __forceinline__ float lrn_pow_neg_inv(float s, float beta, bool beta34, float& inv_s) {
   if (beta34) {
-    const float r = rsqrtf(s);
+    const float r = rsqrt_fast(s);
     inv_s = r * r;
-    return inv_s * rsqrtf(r);
+    return inv_s * rsqrt_fast(r);
   }
   inv_s = __fdividef(1.0f, s);
   return __powf(s, -beta);
@@ -681,7 +701,21 @@ __device__ __forceinline__ void lrn_exchange(const float (&own)[8], float (&ext)
   }
 }
 
+// out[q] = sum of ext[q .. q + 2 HALF]: the window slides by one element per output (2 adds instead of 2 HALF)
 template <int HALF>
+__device__ __forceinline__ void lrn_window_sums(const float (&ext)[8 + 2 * HALF], float (&out)[8]) {
+  float s = 0.0f;
+#pragma unroll
+  for (int d = 0; d <= 2 * HALF; ++d) s += ext[d];
+  out[0] = s;
+#pragma unroll
+  for (int q = 1; q < 8; ++q) {
+    s = s - ext[q - 1] + ext[q + 2 * HALF];
+    out[q] = s;
+  }
+}
+
+template <int HALF, bool B34>
 __global__ void __launch_bounds__(256)
 lrn_forward_shfl_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels, int C,
                         float alpha, float beta, float k) {
@@ -690,7 +724,7 @@ lrn_forward_shfl_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __re
   const int lane = threadIdx.x & 31;
   const int pl = lane / T, g = lane - pl * T;
   const bool active_lane = pl < ppw;
-  const bool beta34 = (beta == 0.75f);
+  constexpr bool beta34 = B34;   // beta == 0.75 (checked by the launcher): two MUFU.RSQ, no log/exp
   const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   const long long groups = (pixels + ppw - 1) / ppw;
   for (long long w = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5; w < groups; w += warps_total) {
@@ -706,19 +740,15 @@ lrn_forward_shfl_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __re
 #pragma unroll
     for (int q = 0; q < 8; ++q) sq[q] = xv[q] * xv[q];
     lrn_exchange<HALF>(sq, ext, g == 0, g == T - 1);
-    float out[8];
+    float out[8], ws[8];
+    lrn_window_sums<HALF>(ext, ws);
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      float s = 0.0f;
-#pragma unroll
-      for (int d = 0; d <= 2 * HALF; ++d) s += ext[q + d];
-      out[q] = xv[q] * lrn_pow_neg(k + alpha * s, beta, beta34);
-    }
+    for (int q = 0; q < 8; ++q) out[q] = xv[q] * lrn_pow_neg(k + alpha * ws[q], beta, beta34);
     if (active) *reinterpret_cast<uint4*>(y + px * C + g * 8) = pack8(out);
   }
 }
 
-template <int HALF>
+template <int HALF, bool B34>
 __global__ void __launch_bounds__(256)
 lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                          __nv_bfloat16* __restrict__ dx, long long pixels, int C, float alpha, float beta, float k,
@@ -728,7 +758,7 @@ lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
   const int lane = threadIdx.x & 31;
   const int pl = lane / T, g = lane - pl * T;
   const bool active_lane = pl < ppw;
-  const bool beta34 = (beta == 0.75f);
+  constexpr bool beta34 = B34;   // beta == 0.75 (checked by the launcher): two MUFU.RSQ, no log/exp
   const float coef = 2.0f * alpha * beta;
   const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   const long long groups = (pixels + ppw - 1) / ppw;
@@ -749,13 +779,11 @@ lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
 #pragma unroll
     for (int q = 0; q < 8; ++q) sq[q] = xv[q] * xv[q];
     lrn_exchange<HALF>(sq, ext, g == 0, g == T - 1);
-    float t[8], dp[8];
+    float t[8], dp[8], ws[8];
+    lrn_window_sums<HALF>(ext, ws);
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      float s = 0.0f;
-#pragma unroll
-      for (int d = 0; d <= 2 * HALF; ++d) s += ext[q + d];
-      s = k + alpha * s;
+      const float s = k + alpha * ws[q];
       float inv_s;
       const float pw = lrn_pow_neg_inv(s, beta, beta34, inv_s);
       dp[q] = dv[q] * pw;
@@ -763,14 +791,15 @@ lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
     }
     lrn_exchange<HALF>(t, ext, g == 0, g == T - 1);
     float out[8];
+    lrn_window_sums<HALF>(ext, ws);
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      float acc = 0.0f;
+    for (int q = 0; q < 8; ++q) out[q] = dp[q] - coef * xv[q] * ws[q];
+    if (deriv == ACT_STRICT_RELU) {          // warp-uniform: the common fused derivative costs one select per value
 #pragma unroll
-      for (int d = 0; d <= 2 * HALF; ++d) acc += ext[q + d];
-      float v = dp[q] - coef * xv[q] * acc;
-      if (deriv) v *= act_deriv_from_output(deriv, xv[q]);
-      out[q] = v;
+      for (int q = 0; q < 8; ++q) out[q] = xv[q] > 0.0f ? out[q] : 0.0f;
+    } else if (deriv) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) out[q] *= act_deriv_from_output(deriv, xv[q]);
     }
     if (active) *reinterpret_cast<uint4*>(dx + px * C + g * 8) = pack8(out);
   }
@@ -890,12 +919,16 @@ int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, flo
     if (C <= 256) {      // whole pixels per warp: neighbours by shuffle
       const int ppw = 32 / (C >> 3);
       const int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
+#define VB_LRN_F(H_)                                                                                              \
+  if (beta == 0.75f) lrn_forward_shfl_kernel<H_, true><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k);        \
+  else lrn_forward_shfl_kernel<H_, false><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k)
       switch (half) {
-        case 1: lrn_forward_shfl_kernel<1><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
-        case 2: lrn_forward_shfl_kernel<2><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
-        case 3: lrn_forward_shfl_kernel<3><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
-        default: lrn_forward_shfl_kernel<4><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+        case 1: VB_LRN_F(1); break;
+        case 2: VB_LRN_F(2); break;
+        case 3: VB_LRN_F(3); break;
+        default: VB_LRN_F(4); break;
       }
+#undef VB_LRN_F
       VB_CHECK_CUDA(cudaGetLastError());
       return 1;
     }
@@ -934,12 +967,16 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
     if (C <= 256) {
       const int ppw = 32 / (C >> 3);
       const int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
+#define VB_LRN_B(H_)                                                                                                     \
+  if (beta == 0.75f) lrn_backward_shfl_kernel<H_, true><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv);   \
+  else lrn_backward_shfl_kernel<H_, false><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv)
       switch (half) {
-        case 1: lrn_backward_shfl_kernel<1><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
-        case 2: lrn_backward_shfl_kernel<2><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
-        case 3: lrn_backward_shfl_kernel<3><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
-        default: lrn_backward_shfl_kernel<4><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+        case 1: VB_LRN_B(1); break;
+        case 2: VB_LRN_B(2); break;
+        case 3: VB_LRN_B(3); break;
+        default: VB_LRN_B(4); break;
       }
+#undef VB_LRN_B
       VB_CHECK_CUDA(cudaGetLastError());
       return 1;
     }
