@@ -426,6 +426,62 @@ def test_gather_minibatch(src_dtype, dst_dtype):
     assert (mbi[:count] == idx[start:start + count]).all() and (mbi[count:] == -1).all()
 
 
+@pytest.mark.parametrize("M,N,KK", [(256, 512, 128), (1000, 4096, 256), (100, 784, 64), (130, 70, 100), (64, 33, 40)])
+@pytest.mark.parametrize("moment,wd,l12", [(0.0, 0.0, 0.0), (0.9, 0.0005, 0.0), (0.5, 0.01, 0.3)])
+def test_gemm_with_fused_gd_epilogue(M, N, KK, moment, wd, l12):
+    """dW = A^T B never leaves the GEMM: its epilogue applies the momentum step to w / velocity and refreshes the bf16
+    shadow.  Reference: the same GEMM in fp32 + the update rule of vb_gd_update."""
+    k = K()
+    g = torch.Generator(device="cpu").manual_seed(M + N + KK)
+    a = k.pitched_empty(KK, M, torch.bfloat16, dev())          # err_output: [batch, n_out], read MN-major
+    b = k.pitched_empty(KK, N, torch.bfloat16, dev())          # input:      [batch, n_in]
+    a.copy_(torch.randn(KK, M, generator=g).to(dev()) * 0.1)
+    b.copy_(torch.randn(KK, N, generator=g).to(dev()))
+    w = (torch.randn(M, N, generator=g) * 0.1).to(dev())
+    w[0, :min(N, 5)] = 0.0                                   # sign(0) = 0 in the L1 term
+    vel = (torch.randn(M, N, generator=g) * 0.01).to(dev())
+    shadow = k.pitched_empty(M, N, torch.bfloat16, dev())
+    lr = 0.05
+    grad = a.float().t() @ b.float()
+    gref = grad + wd * ((1 - l12) * w + 0.5 * l12 * torch.sign(w))
+    vref = moment * vel - lr * gref
+    wref = w + vref
+    before = k.LAUNCHES[0]
+    k.gemm_fused_gd(a, b, w, vel, shadow, lr=lr, wd=wd, l1_vs_l2=l12, moment=moment)
+    assert k.LAUNCHES[0] == before + 1
+    scale = vref.abs().max().item() + 1e-9
+    assert (vel - vref).abs().max().item() < 2e-3 * scale + 1e-6
+    assert (w - wref).abs().max().item() < 2e-3 * scale + 1e-6
+    assert torch.equal(shadow, w.bfloat16())
+    pair_w, pair_v = w.clone(), vel.clone()
+    # second step from the updated state, CTA-pair tiles forced when the shape allows them
+    k.set_pair_mode(2)
+    try:
+        k.gemm_fused_gd(a, b, w, vel, shadow, lr=lr, wd=wd, l1_vs_l2=l12, moment=moment)
+    finally:
+        k.set_pair_mode(0)
+    g2 = grad + wd * ((1 - l12) * pair_w + 0.5 * l12 * torch.sign(pair_w))
+    v2 = moment * pair_v - lr * g2
+    assert (vel - v2).abs().max().item() < 2e-3 * (v2.abs().max().item() + 1e-9) + 1e-6
+    assert (w - (pair_w + v2)).abs().max().item() < 2e-3 * (v2.abs().max().item() + 1e-9) + 1e-6
+
+
+def test_gather_u8_to_bf16_is_exact_for_odd_row_sizes():
+    """The flat 8-element gather path: odd row sizes (unaligned rows), partial minibatch, no normalisation."""
+    k = K()
+    g = torch.Generator(device="cpu").manual_seed(5)
+    for size, mb, count in ((227 * 3 * 5 + 1, 16, 16), (4099, 7, 5), (17, 33, 32), (16, 8, 8)):
+        n = 50
+        src = torch.randint(0, 256, (n, size), generator=g, dtype=torch.uint8).to(dev())
+        idx = torch.randperm(n, generator=g).int().to(dev())
+        dst = torch.full((mb + 3, size), float("nan"), device=dev(), dtype=torch.bfloat16)
+        k.gather_minibatch(src, idx, 3, count, dst[:mb], None, None, None, None, None)
+        sel = idx[3:3 + count].long()
+        assert torch.equal(dst[:count].float(), src[sel].float()), size
+        assert (dst[count:mb] == 0).all()
+        assert torch.isnan(dst[mb:].float()).all(), "kernel wrote past the minibatch"
+
+
 def test_mean_disp_normalizer():
     k = K()
     g = torch.Generator(device="cpu").manual_seed(4)

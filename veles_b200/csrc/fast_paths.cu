@@ -1046,6 +1046,41 @@ __global__ void space_to_depth_kernel(const T* __restrict__ x, __nv_bfloat16* __
   }
 }
 
+// Row-segment form of the same transform for bf16 inputs with (sx * C) % 4 == 0: the sx * C elements that one output
+// pixel takes from input row 4 h' + dy are CONTIGUOUS in the input, so a thread copies one such segment (scalar 2-byte
+// loads - an NHWC row of 3-channel pixels is only 2-byte aligned - packed into 8-byte stores) with no per-element
+// index arithmetic.  The AlexNet first layer (sx * C = 12) moves 24 bytes per thread.
+__global__ void __launch_bounds__(256)
+space_to_depth_rows_kernel(const unsigned short* __restrict__ x, unsigned short* __restrict__ xs, int B, int H, int W,
+                           int C, int sy, int sx, int H2, int W2) {
+  const int n = sx * C;                 // segment length (elements), multiple of 4
+  const int C2 = sy * n;
+  const long long total = static_cast<long long>(B) * H2 * W2 * sy;
+  for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const unsigned tt = static_cast<unsigned>(t);       // < 2^32 (checked by the launcher)
+    const int dy = static_cast<int>(tt % sy);
+    unsigned r = tt / sy;
+    const int w2 = static_cast<int>(r % W2);
+    r /= W2;
+    const int h2 = static_cast<int>(r % H2);
+    const int b = static_cast<int>(r / H2);
+    const int h = h2 * sy + dy;
+    const int w0 = w2 * sx;
+    int avail = 0;                       // elements of the segment that lie inside the image
+    if (h < H) avail = min(n, (W - w0) * C);
+    const unsigned short* src = x + ((static_cast<long long>(b) * H + h) * W + w0) * C;
+    unsigned short* dst = xs + (static_cast<long long>(tt / sy) * C2 + dy * n);
+    for (int k = 0; k < n; k += 4) {
+      unsigned short e[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) e[j] = (k + j < avail) ? __ldg(src + k + j) : static_cast<unsigned short>(0);
+      *reinterpret_cast<uint2*>(dst + k) = make_uint2(e[0] | (static_cast<unsigned>(e[1]) << 16),
+                                                      e[2] | (static_cast<unsigned>(e[3]) << 16));
+    }
+  }
+}
+
 // dst[r, j] (+)= src[r, map[j]] (0 where map[j] < 0); optional zeroing of the consumed source row
 // range afterwards is left to the caller.  Used to move weights / weight gradients between the
 // Znicz column order and the space-to-depth column order (tiny matrices).
@@ -1076,6 +1111,14 @@ extern "C" int vb_space_to_depth(const void* x, int dtype, void* xs, int B, int 
   const int H2 = (H + sy - 1) / sy, W2 = (W + sx - 1) / sx;
   const long long total = static_cast<long long>(B) * H2 * W2 * ((sy * sx * C) >> 3);
   if (total == 0) return 0;
+  const long long segs = static_cast<long long>(B) * H2 * W2 * sy;
+  if (dtype == 1 && (sx * C) % 4 == 0 && segs < 0xffffffffLL) {
+    space_to_depth_rows_kernel<<<grid_cap2(segs, 256), 256, 0, s>>>(static_cast<const unsigned short*>(x),
+                                                                   static_cast<unsigned short*>(xs), B, H, W, C, sy, sx,
+                                                                   H2, W2);
+    VB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   const int grid = grid_cap2(total, 256);
   if (dtype == 0)
     space_to_depth_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(x), static_cast<__nv_bfloat16*>(xs), B, H, W, C, sy, sx, H2, W2);

@@ -81,7 +81,22 @@ struct GemmParams {
   int dyn_sched;      // 1: tiles are handed out by cluster launch control (grid = one CTA / pair per tile)
   int tma_store;      // 1: epilogue goes through smem + TMA store / reduce-add (tma_d valid)
   int m_blocks, n_blocks, k_blocks;
+  // Fused gradient-descent epilogue (gd_w != null): the accumulator tile IS the weight gradient; instead of storing
+  // it, the epilogue reads the fp32 master weights and momentum at the tile's position, applies the Znicz update and
+  // writes weights, momentum and the bf16 shadow - the gradient never reaches HBM.
+  float* gd_w;
+  float* gd_vel;
+  __nv_bfloat16* gd_shadow;   // may be null
+  long long gd_ld, gd_ld_shadow;
+  float gd_lr, gd_wd, gd_l12, gd_moment;
 };
+
+__device__ __forceinline__ float gd_step_momentum(const GemmParams& p, float w, float g, float& v) {
+  const float sgn = (w > 0.0f) ? 1.0f : ((w < 0.0f) ? -1.0f : 0.0f);
+  g = g + p.gd_wd * ((1.0f - p.gd_l12) * w + 0.5f * p.gd_l12 * sgn);
+  v = p.gd_moment * v - p.gd_lr * g;
+  return w + v;
+}
 
 template <int BN, bool PAIR>
 struct SmemLayout {
@@ -464,6 +479,81 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           for (int j = 0; j < 32; ++j) f[j] *= p.alpha;
         }
         const bool full = nvalid >= 32;
+        if (p.gd_w != nullptr) {
+          // The accumulator slab has one weight ROW per lane; touching w / momentum that way would make every
+          // load and store instruction hit 32 different cache lines.  So the slab is transposed through this warp's
+          // (swizzled) staging buffer, and the update runs with 8 lanes x 16 bytes along each row: four full
+          // 128-byte row segments per instruction, for w, momentum and the bf16 shadow alike.
+          uint8_t* buf = epi_smem + (warp - 2) * EPI_BUF_BYTES;
+          uint8_t* srow = buf + lane * 128;
+          __syncwarp();
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            *reinterpret_cast<float4*>(srow + ((q ^ (lane & 7)) << 4)) =
+                make_float4(f[4 * q], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
+          __syncwarp();
+          const int q = lane & 7;                 // 16-byte chunk (4 columns) of a row
+          const int cbase = dcol0 + 4 * q;
+          const int cvalid = nvalid - 4 * q;      // columns of this chunk that exist
+          const bool vec_ok = ((p.gd_ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.gd_w) & 15) == 0) &&
+                              ((reinterpret_cast<uintptr_t>(p.gd_vel) & 15) == 0);
+          const bool svec_ok = p.gd_shadow != nullptr && ((p.gd_ld_shadow & 3) == 0) &&
+                               ((reinterpret_cast<uintptr_t>(p.gd_shadow) & 7) == 0);
+          float4 g4[8], w4[8], v4[8];
+          bool ok[8];
+#pragma unroll
+          for (int i2 = 0; i2 < 8; ++i2) {         // all loads of the slab first
+            const int r = i2 * 4 + (lane >> 3);
+            const int grow = row0 + r;
+            ok[i2] = grow < p.M && cvalid > 0;
+            g4[i2] = *reinterpret_cast<const float4*>(buf + r * 128 + ((q ^ (r & 7)) << 4));
+            if (ok[i2]) {
+              const float* wr = p.gd_w + static_cast<long long>(grow) * p.gd_ld + cbase;
+              const float* vr = p.gd_vel + static_cast<long long>(grow) * p.gd_ld + cbase;
+              if (vec_ok && cvalid >= 4) {
+                w4[i2] = *reinterpret_cast<const float4*>(wr);
+                v4[i2] = *reinterpret_cast<const float4*>(vr);
+              } else {
+                w4[i2].x = wr[0]; v4[i2].x = vr[0];
+                w4[i2].y = cvalid > 1 ? wr[1] : 0.0f; v4[i2].y = cvalid > 1 ? vr[1] : 0.0f;
+                w4[i2].z = cvalid > 2 ? wr[2] : 0.0f; v4[i2].z = cvalid > 2 ? vr[2] : 0.0f;
+                w4[i2].w = cvalid > 3 ? wr[3] : 0.0f; v4[i2].w = cvalid > 3 ? vr[3] : 0.0f;
+              }
+            }
+          }
+#pragma unroll
+          for (int i2 = 0; i2 < 8; ++i2) {
+            if (!ok[i2]) continue;
+            const int grow = row0 + i2 * 4 + (lane >> 3);
+            w4[i2].x = gd_step_momentum(p, w4[i2].x, g4[i2].x, v4[i2].x);
+            w4[i2].y = gd_step_momentum(p, w4[i2].y, g4[i2].y, v4[i2].y);
+            w4[i2].z = gd_step_momentum(p, w4[i2].z, g4[i2].z, v4[i2].z);
+            w4[i2].w = gd_step_momentum(p, w4[i2].w, g4[i2].w, v4[i2].w);
+            float* wr = p.gd_w + static_cast<long long>(grow) * p.gd_ld + cbase;
+            float* vr = p.gd_vel + static_cast<long long>(grow) * p.gd_ld + cbase;
+            __nv_bfloat16* sr = p.gd_shadow ? p.gd_shadow + static_cast<long long>(grow) * p.gd_ld_shadow + cbase : nullptr;
+            if (vec_ok && cvalid >= 4) {
+              *reinterpret_cast<float4*>(wr) = w4[i2];
+              *reinterpret_cast<float4*>(vr) = v4[i2];
+            } else {
+              wr[0] = w4[i2].x; vr[0] = v4[i2].x;
+              if (cvalid > 1) { wr[1] = w4[i2].y; vr[1] = v4[i2].y; }
+              if (cvalid > 2) { wr[2] = w4[i2].z; vr[2] = v4[i2].z; }
+              if (cvalid > 3) { wr[3] = w4[i2].w; vr[3] = v4[i2].w; }
+            }
+            if (sr != nullptr) {
+              if (svec_ok && cvalid >= 4) {
+                *reinterpret_cast<uint2*>(sr) = make_uint2(pack_bf16x2(w4[i2].x, w4[i2].y), pack_bf16x2(w4[i2].z, w4[i2].w));
+              } else {
+                sr[0] = __float2bfloat16(w4[i2].x);
+                if (cvalid > 1) sr[1] = __float2bfloat16(w4[i2].y);
+                if (cvalid > 2) sr[2] = __float2bfloat16(w4[i2].z);
+                if (cvalid > 3) sr[3] = __float2bfloat16(w4[i2].w);
+              }
+            }
+          }
+          continue;
+        }
         if (add_bias) {
           const float* bp = p.bias + dcol0;
           if (full && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
@@ -845,6 +935,15 @@ static void choose_config(int M, int N, int k_blocks, bool can_split, bool auto_
   *pair_out = best_pair;
 }
 
+struct GdRequest {
+  float* w;
+  float* vel;
+  void* shadow;
+  long long ld, ld_shadow;
+  float lr, wd, l12, moment;
+};
+static thread_local const GdRequest* g_gd_request = nullptr;
+
 // Builds the output tensor map (when D qualifies) and launches the right instantiation.
 static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtensorMap& tb, bool a_mn, bool b_mn,
                              int BN, int pair, cudaStream_t stream, int d_cols = -1, bool tf32 = false) {
@@ -855,6 +954,13 @@ static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtenso
   memset(&td, 0, sizeof(td));
   const int es = p.out_fp32 ? 4 : 2;
   p.tma_store = ((reinterpret_cast<uintptr_t>(p.D) & 15) == 0 && (p.ldd * es) % 16 == 0 && !g_disable_tma_store) ? 1 : 0;
+  if (g_gd_request != nullptr) {
+    const GdRequest& r = *g_gd_request;
+    p.gd_w = r.w; p.gd_vel = r.vel; p.gd_shadow = static_cast<__nv_bfloat16*>(r.shadow);
+    p.gd_ld = r.ld; p.gd_ld_shadow = r.ld_shadow;
+    p.gd_lr = r.lr; p.gd_wd = r.wd; p.gd_l12 = r.l12; p.gd_moment = r.moment;
+    p.tma_store = 0;       // nothing is stored through D
+  }
   if (p.tma_store) {
     int rc = make_tmap_2d(&td, p.D, d_cols > 0 ? d_cols : p.N, p.M, p.ldd, p.out_fp32 ? 32 : 64, 32, p.out_fp32 != 0);
     if (rc) return rc;
@@ -1004,6 +1110,25 @@ extern "C" int vb_gemm_bf16(const void* A, long long lda, int a_mn_major, const 
                             cudaStream_t stream) {
   return gemm_impl(A, lda, a_mn_major, B, ldb, b_mn_major, D, ldd, M, N, K, bias, act, out_fp32, accumulate, Z, ldz,
                    deriv, alpha, split_k, block_n, nullptr, 0, 0, stream);
+}
+
+// Weight-gradient GEMM with the gradient-descent step in its epilogue (single GPU, momentum solver, no split-K):
+//   g = alpha * sum_k A(m,k) B(n,k) + wd * ((1 - l1_vs_l2) * w + 0.5 * l1_vs_l2 * sign(w));  v = moment * v - lr * g;  w += v
+// applied to the fp32 master weights `w` / momentum `vel` ([M, N], pitch ldw) and mirrored into the bf16 `shadow`
+// ([M, N], pitch ld_shadow, may be null).  The gradient itself is never written.
+extern "C" int vb_gemm_bf16_fused_gd(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
+                                     int b_mn_major, int M, int N, int K, float* w, long long ldw, float* vel,
+                                     void* shadow, long long ld_shadow, float lr, float wd, float l1_vs_l2,
+                                     float moment, float alpha, int block_n, cudaStream_t stream) {
+  VB_REQUIRE(w != nullptr && vel != nullptr, "vb_gemm_bf16_fused_gd: weights and momentum are required");
+  VB_REQUIRE(ldw >= N && (shadow == nullptr || ld_shadow >= N), "vb_gemm_bf16_fused_gd: pitch smaller than N");
+  GdRequest req{w, vel, shadow, ldw, ld_shadow, lr, wd, l1_vs_l2, moment};
+  g_gd_request = &req;
+  // D is only a formal argument here (fp32, pitch ldw): the epilogue takes the GD branch before any store
+  const int rc = gemm_impl(A, lda, a_mn_major, B, ldb, b_mn_major, w, ldw, M, N, K, nullptr, 0, 1, 0, nullptr, 0, 0,
+                           alpha, 1, block_n, nullptr, 0, 0, stream);
+  g_gd_request = nullptr;
+  return rc;
 }
 
 // Same product with the B (weight) operand row-sharded over `world` replicas: rows

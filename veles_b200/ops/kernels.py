@@ -161,6 +161,32 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumu
     return out
 
 
+def gemm_fused_gd(a, b, w, vel, shadow, *, a_mn=True, b_mn=True, lr, wd=0.0, l1_vs_l2=0.0, moment=0.0, alpha=1.0,
+                  block_n=0):
+    """Weight-gradient GEMM whose epilogue applies the momentum GD step to ``w`` / ``vel`` (fp32 [M, N]) and refreshes
+    the bf16 ``shadow``; the gradient is never stored.  ``a`` / ``b`` as in :func:`gemm`."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert w.dtype == torch.float32 and vel.dtype == torch.float32 and w.dim() == 2 and vel.shape == w.shape
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    assert K == Kb and tuple(w.shape) == (M, N) and _ld(vel) == _ld(w)
+    assert shadow is None or (shadow.dtype == torch.bfloat16 and tuple(shadow.shape) == (M, N))
+    _FLOPS[0] = 2.0 * M * N * K
+    rc = _lib.lib().vb_gemm_bf16_fused_gd(
+        _p(a), c_longlong(_ld(a)), c_int(int(a_mn)), _p(b), c_longlong(_ld(b)), c_int(int(b_mn)), c_int(M), c_int(N),
+        c_int(K), _p(w), c_longlong(_ld(w)), _p(vel), _p(shadow), c_longlong(_ld(shadow) if shadow is not None else 0),
+        c_float(lr), c_float(wd), c_float(l1_vs_l2), c_float(moment), c_float(alpha), c_int(block_n), _stream())
+    _lib.check(rc, "vb_gemm_bf16_fused_gd")
+    LAUNCHES[0] += 1
+    return w
+
+
 def gemm_tf32(a, b, out, *, a_mn=False, b_mn=False, bias=None, act=ACT_LINEAR, accumulate=False, z=None, deriv=0,
               alpha=1.0, split_k=1, block_n=0):
     """``gemm`` with fp32 operands multiplied as TF32 (fp32 accumulate): the "float" precision mode."""
@@ -605,7 +631,7 @@ def _traced(fn):
     return wrap
 
 
-for _name in ("gemm", "bias_act", "gemm_tf32", "conv_forward", "conv_forward_grouped", "conv_err_input_grouped", "conv_forward_halo", "conv_err_input_halo", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
+for _name in ("gemm", "gemm_fused_gd", "bias_act", "gemm_tf32", "conv_forward", "conv_forward_grouped", "conv_err_input_grouped", "conv_forward_halo", "conv_err_input_halo", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
               "gather_minibatch", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
               "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",

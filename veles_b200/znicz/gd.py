@@ -112,6 +112,14 @@ class GradientDescent(GradientDescentBase):
             self.ei_acc_ = torch.zeros(self.err_output.shape[0], n_in, dtype=torch.float32, device=dev.torch_device)
         self.dw_store_ = (self.dp_group_ is None and self.apply_gradient and not self.tf32_mode() and
                           kernels.gemm_plan(n_out, n_in, self.err_output.shape[0], b_mn=True)[1] == 1)
+        # Optionally (root.common.engine.fuse_gd_update) the GD step runs in that GEMM's epilogue: the update reads w
+        # and momentum at the tile's position and the gradient never reaches HBM (single GPU, momentum solver).
+        # Measured on AlexNet's fc6/fc7 it only breaks even (+236 us in the GEMMs, -193 us of update kernels): the
+        # separate update already finds the freshly written gradient in the 126 MB L2 -> off by default.
+        from ..config import root, get
+        self.fused_gd_ = bool(self.dw_store_ and self.solver_code == 0 and not self.accumulate_gradient and
+                              self.forward is not None and getattr(self.forward, "weights_bf16_", None) is not None and
+                              get(root.common.engine.fuse_gd_update, False))
 
     def device_err_output(self):
         """bf16 2-D err_output with own activation derivative applied (unless fused upstream)."""
@@ -194,15 +202,25 @@ class GradientDescent(GradientDescentBase):
             self.err_input.mark_device_written()
         gw_t, gb_t = self.grad_tensors()
         gw = gw_t.view(w_bf16.shape[0], -1)
-        if self.dw_store_:
+        # (a data-parallel group attaches after initialize: its gradients must be exchanged, never fused away)
+        fused = getattr(self, "fused_gd_", False) and self.apply_gradient and self.dp_group_ is None
+        if fused:
+            w2d = self.weights.devmem.view(w_bf16.shape[0], -1)
+            kernels.gemm_fused_gd(eo, x, w2d, self.gradient_weights_with_moment.devmem.view(w2d.shape), w_bf16,
+                                  lr=self.learning_rate, wd=self.weights_decay, l1_vs_l2=self.l1_vs_l2,
+                                  moment=self.gradient_moment)
+            self.weights.mark_device_written()
+            self.gradient_weights_with_moment.mark_device_written()
+        elif self.dw_store_:
             kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=False, split_k=1)
         else:
             kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
         if self.bias is not None and self.bias:
             kernels.col_sum(eo, gb_t, self.col_scratch_, accumulate=True)
             self.gradient_bias.mark_device_written()
-        self.gradient_weights.mark_device_written()
-        self.device_update()
+        if not fused:
+            self.gradient_weights.mark_device_written()
+        self.device_update(skip_weights=fused)
 
     def _input_2d(self):
         import torch

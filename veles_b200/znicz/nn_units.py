@@ -491,8 +491,9 @@ class GradientDescentBase(GDBase):
         return (self.gradient_weights.devmem,
                 self.gradient_bias.devmem if (self.bias is not None and self.bias) else None)
 
-    def device_update(self, forward=None):
-        """U1: fused single-GPU GD step on weights and bias (or hand over to the DP group)."""
+    def device_update(self, forward=None, skip_weights=False):
+        """U1: fused single-GPU GD step on weights and bias (or hand over to the DP group).  ``skip_weights``: the
+        weight-gradient GEMM already applied the step in its epilogue (``kernels.gemm_fused_gd``)."""
         from ..ops import kernels
         if not self.apply_gradient:
             return
@@ -504,7 +505,7 @@ class GradientDescentBase(GDBase):
         eps = self.adagrad_epsilon if solver == 1 else self.adadelta_epsilon
         fwd = self.forward
         shadow = fwd.weights_bf16_ if fwd is not None else None
-        if self.weights is not None and self.weights:
+        if self.weights is not None and self.weights and not skip_weights:
             w_shadow = shadow if (shadow is not None and shadow.is_contiguous()) else None
             kernels.gd_update(self.weights.devmem, self.gradient_weights.devmem,
                               self.gradient_weights_with_moment.devmem,
