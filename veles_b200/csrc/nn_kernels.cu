@@ -475,7 +475,20 @@ col_sum_partial_vec8_kernel(const __nv_bfloat16* __restrict__ a, long long lda, 
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (lane_r < rl && vc * 8 < cols) {
     const __nv_bfloat16* base = a + vc * 8;
-    for (int r = r0 + lane_r; r < r1; r += rl) {
+    int r = r0 + lane_r;
+    // four independent 16-byte loads in flight per thread (a slab of a large err_output is ~70 rows per thread:
+    // one load at a time leaves the kernel latency-bound at a third of the copy bandwidth)
+    for (; r + 3 * rl < r1; r += 4 * rl) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(r + u * rl) * lda));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        acc[0] += bf16_lo(v[u].x); acc[1] += bf16_hi(v[u].x); acc[2] += bf16_lo(v[u].y); acc[3] += bf16_hi(v[u].y);
+        acc[4] += bf16_lo(v[u].z); acc[5] += bf16_hi(v[u].z); acc[6] += bf16_lo(v[u].w); acc[7] += bf16_hi(v[u].w);
+      }
+    }
+    for (; r < r1; r += rl) {
       const uint4 v = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(r) * lda));
       acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
       acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
