@@ -10,7 +10,8 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("model,port", [("mnist_mlp", 29661), ("cifar_convnet", 29662), ("wide_mlp_ae", 29663)])
+@pytest.mark.parametrize("model,port", [("mnist_mlp", 29661), ("cifar_convnet", 29662), ("wide_mlp_ae", 29663),
+                                        ("lstm_classifier", 29664)])
 def test_two_gloo_ranks_match_single_process(model, port):
     env = dict(os.environ, OMP_NUM_THREADS="2")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",

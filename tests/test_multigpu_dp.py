@@ -9,7 +9,7 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("model", ["cifar_convnet", "mnist_mlp", "wide_mlp_ae"])
+@pytest.mark.parametrize("model", ["cifar_convnet", "mnist_mlp", "wide_mlp_ae", "lstm_classifier"])
 def test_dp_matches_single_gpu(model):
     import torch
     n = min(torch.cuda.device_count(), 4)

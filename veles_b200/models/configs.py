@@ -69,7 +69,19 @@ def wide_mlp_ae_layers(width=4096, depth=4, in_features=4096, lr=0.001):
     return layers
 
 
+def lstm_classifier_layers(hidden=128, n_classes=10, lr=0.02, stacked=False):
+    """Sequence classifier: LSTM over [T, D] samples (optionally two stacked layers), last state -> softmax."""
+    layers = []
+    if stacked:
+        layers.append({"type": "lstm", "->": {"hidden_size": hidden}, "<-": _gd(lr, 0.0)})
+    layers.append({"type": "lstm", "->": {"hidden_size": hidden, "return_sequences": False}, "<-": _gd(lr, 0.0)})
+    layers.append({"type": "softmax", "->": {"output_sample_shape": n_classes}, "<-": _gd(lr, 0.0)})
+    return layers
+
+
 MODEL_CONFIGS = {
+    "lstm_classifier": dict(layers=lstm_classifier_layers, loader_name="synthetic_fullbatch", loss_function="softmax",
+                            sample_shape=(16, 64), n_classes=10, minibatch=128),
     "mnist_mlp": dict(layers=mnist_mlp_layers, loader_name="mnist_loader", loss_function="softmax",
                       sample_shape=(784,), n_classes=10, minibatch=100),
     "cifar_convnet": dict(layers=cifar_convnet_layers, loader_name="cifar_loader", loss_function="softmax",
