@@ -154,6 +154,13 @@ long long vb_col_sum_scratch_elems(int rows, int cols);
 int vb_col_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, float alpha, int accumulate,
                float* scratch, cudaStream_t stream);
 
+/* vb_col_sum whose result is used on the spot as the gradient of the vector w (a layer's bias): momentum GD step
+ * v = moment * v - lr * (g + wd * ((1 - l1_vs_l2) * w + 0.5 * l1_vs_l2 * sign w)), w += v, applied by the reduction's
+ * second phase; `grad` (needed only with accumulate) is left zeroed. */
+int vb_col_sum_gd(const void* a, int dtype, long long lda, int rows, int cols, float* grad, float alpha, int accumulate,
+                  float* scratch, float* w, float* vel, float lr, float wd, float l1_vs_l2, float moment,
+                  cudaStream_t stream);
+
 /* Column sum for callers that cannot allocate device memory (fixed memory budgets, code inside a stream
  * capture, latency-critical loops where cudaMalloc is forbidden).  Same result as vb_col_sum, but the
  * inter-block scratch is a fixed 4 MiB array inside the library, so only inputs and outputs are passed.

@@ -507,29 +507,51 @@ col_sum_partial_vec8_kernel(const __nv_bfloat16* __restrict__ a, long long lda, 
   }
 }
 
-// Second phase: 32 columns x 8 slab-lanes per block.
-__global__ void col_sum_final_kernel(const float* __restrict__ scratch, int slabs, int cols, float* __restrict__ out,
-                                     float alpha, int accumulate) {
-  __shared__ float red[8][33];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int col = blockIdx.x * 32 + tx;
+// Optional gradient-descent step applied by the second phase to the vector the column sums are the gradient of (a
+// layer's bias): saves the separate, latency-bound update launch per layer.
+struct ColSumGD {
+  float* w;       // null: plain column sum
+  float* vel;
+  float lr, wd, l12, moment;
+};
+
+// Second phase: 8 columns x 32 slab-lanes per block (the partial rows are folded 32 at a time: with up to ~512
+// slabs the former 8-lane version was a chain of 64 dependent loads per thread).
+__global__ void __launch_bounds__(256)
+col_sum_final_kernel(const float* __restrict__ scratch, int slabs, int cols, float* __restrict__ out, float alpha,
+                     int accumulate, const ColSumGD gd) {
+  __shared__ float red[32][9];
+  const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
+  const int col = blockIdx.x * 8 + tx;
   float s = 0.0f;
   if (col < cols)
-    for (int k = ty; k < slabs; k += 8) s += scratch[static_cast<long long>(k) * cols + col];
+    for (int k = ty; k < slabs; k += 32) s += scratch[static_cast<long long>(k) * cols + col];
   red[ty][tx] = s;
   __syncthreads();
   if (ty == 0 && col < cols) {
     float t = 0.0f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t += red[k][tx];
+    for (int k = 0; k < 32; ++k) t += red[k][tx];
     t *= alpha;
-    out[col] = accumulate ? out[col] + t : t;
+    if (gd.w != nullptr) {
+      // the bias-gradient buffer stays zero (what the separate update leaves behind with zero_grad)
+      const float g = (accumulate ? out[col] + t : t);
+      const float w = gd.w[col];
+      const float sgn = (w > 0.0f) ? 1.0f : ((w < 0.0f) ? -1.0f : 0.0f);
+      const float gg = g + gd.wd * ((1.0f - gd.l12) * w + 0.5f * gd.l12 * sgn);
+      const float v = gd.moment * gd.vel[col] - gd.lr * gg;
+      gd.vel[col] = v;
+      gd.w[col] = w + v;
+      if (accumulate) out[col] = 0.0f;
+    } else {
+      out[col] = accumulate ? out[col] + t : t;
+    }
   }
 }
 
 // Launches both phases (shared by vb_col_sum and vb_col_sum_static).
 static int launch_col_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, float alpha,
-                          int accumulate, float* scratch, int rps, cudaStream_t s) {
+                          int accumulate, float* scratch, int rps, cudaStream_t s, ColSumGD gd = ColSumGD{}) {
   const int slabs = rows > 0 ? ceil_div(rows, rps) : 0;
   if (slabs > 0) {
     if (dtype == D_BF16 && cols % 8 == 0 && lda % 8 == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0) {
@@ -549,7 +571,7 @@ static int launch_col_sum(const void* a, int dtype, long long lda, int rows, int
     }
     VB_CHECK_CUDA(cudaGetLastError());
   }
-  col_sum_final_kernel<<<ceil_div(cols, 32), 256, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate);
+  col_sum_final_kernel<<<ceil_div(cols, 8), 256, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate, gd);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -792,6 +814,19 @@ extern "C" int vb_col_sum(const void* a, int dtype, long long lda, int rows, int
   if (cols == 0) return 0;
   VB_REQUIRE(scratch != nullptr, "vb_col_sum: scratch buffer is required");
   return launch_col_sum(a, dtype, lda, rows, cols, out, alpha, accumulate, scratch, colsum_rows_per_slab(rows), s);
+}
+
+// Column sum whose result is consumed on the spot as the gradient of `w` (a bias vector): momentum GD step
+//   g = alpha * sum_i a[i,j] (+ grad[j] when accumulate) + wd * ((1 - l1_vs_l2) * w + 0.5 * l1_vs_l2 * sign(w));
+//   v = moment * v - lr * g;  w += v.   `grad` (may be null when !accumulate) is left zeroed.
+extern "C" int vb_col_sum_gd(const void* a, int dtype, long long lda, int rows, int cols, float* grad, float alpha,
+                             int accumulate, float* scratch, float* w, float* vel, float lr, float wd, float l1_vs_l2,
+                             float moment, cudaStream_t s) {
+  if (cols == 0) return 0;
+  VB_REQUIRE(scratch != nullptr && w != nullptr && vel != nullptr, "vb_col_sum_gd: scratch, w and vel are required");
+  VB_REQUIRE(!accumulate || grad != nullptr, "vb_col_sum_gd: accumulate needs the gradient buffer");
+  ColSumGD gd{w, vel, lr, wd, l1_vs_l2, moment};
+  return launch_col_sum(a, dtype, lda, rows, cols, grad, alpha, accumulate, scratch, colsum_rows_per_slab(rows), s, gd);
 }
 
 // ---------------------------------------------------------------------------

@@ -586,6 +586,19 @@ def col_sum(a, out, scratch, alpha=1.0, accumulate=False):
     return out
 
 
+def col_sum_gd(a, grad, scratch, w, vel, *, lr, wd=0.0, l1_vs_l2=0.0, moment=0.0, alpha=1.0, accumulate=True):
+    """``col_sum`` that applies the momentum GD step to ``w`` / ``vel`` (a bias) in its second phase; ``grad`` is the
+    accumulation buffer (read when ``accumulate``) and is left zeroed."""
+    assert scratch.numel() >= col_sum_scratch_elems(a.shape[0], a.shape[1])
+    assert w.dtype == torch.float32 and vel.dtype == torch.float32 and w.numel() == a.shape[1] == vel.numel()
+    rc = _lib.lib().vb_col_sum_gd(_p(a), c_int(_dt(a)), c_longlong(_ld(a)), c_int(a.shape[0]), c_int(a.shape[1]),
+                                  _p(grad), c_float(alpha), c_int(int(accumulate)), _p(scratch), _p(w), _p(vel),
+                                  c_float(lr), c_float(wd), c_float(l1_vs_l2), c_float(moment), _stream())
+    _lib.check(rc, "vb_col_sum_gd")
+    LAUNCHES[0] += 2
+    return w
+
+
 def xorshift1024star(states, rounds, out):
     n_states = states.numel() // 16
     rc = _lib.lib().vb_xorshift1024star(_p(states), c_int(n_states), c_int(rounds), _p(out), _stream())
@@ -635,7 +648,7 @@ for _name in ("gemm", "gemm_fused_gd", "bias_act", "gemm_tf32", "conv_forward", 
               "gather_minibatch", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
               "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",
-              "row_sum", "col_sum", "xorshift1024star", "xorshift128plus", "fill_random"):
+              "row_sum", "col_sum", "col_sum_gd", "xorshift1024star", "xorshift128plus", "fill_random"):
     globals()[_name] = _traced(globals()[_name])
 
 

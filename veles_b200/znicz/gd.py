@@ -173,8 +173,7 @@ class GradientDescent(GradientDescentBase):
         gw = gw_t.view(w.shape[0], -1)
         kernels.gemm_tf32(eo, x, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
         if self.bias is not None and self.bias:
-            kernels.col_sum(eo, gb_t, self.col_scratch_, accumulate=True)
-            self.gradient_bias.mark_device_written()
+            self.device_bias_sum(eo, gb_t)
         self.gradient_weights.mark_device_written()
         self.device_update()
 
@@ -216,8 +215,7 @@ class GradientDescent(GradientDescentBase):
         else:
             kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
         if self.bias is not None and self.bias:
-            kernels.col_sum(eo, gb_t, self.col_scratch_, accumulate=True)
-            self.gradient_bias.mark_device_written()
+            self.device_bias_sum(eo, gb_t)
         if not fused:
             self.gradient_weights.mark_device_written()
         self.device_update(skip_weights=fused)

@@ -148,8 +148,7 @@ class GradientDescentConv(GradientDescentBase):
                              accumulate=True, split_k=0)
         self.gradient_weights.mark_device_written()
         if self.bias is not None and self.bias:
-            kernels.col_sum(eo2, gb_t, self.col_scratch_, accumulate=True)
-            self.gradient_bias.mark_device_written()
+            self.device_bias_sum(eo2, gb_t)
         if self.need_err_input:
             ei = self.err_input.devmem
             ei4 = ei.reshape(f.in_shape4) if tuple(ei.shape) != tuple(f.in_shape4) else ei

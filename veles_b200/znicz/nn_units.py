@@ -491,6 +491,25 @@ class GradientDescentBase(GDBase):
         return (self.gradient_weights.devmem,
                 self.gradient_bias.devmem if (self.bias is not None and self.bias) else None)
 
+    def device_bias_sum(self, eo2, gb_t):
+        """Bias gradient = column sums of the 2-D err_output.  On the plain single-GPU momentum path the reduction's
+        second phase applies the bias GD step itself (``vb_col_sum_gd``): one latency-bound launch less per layer."""
+        from ..ops import kernels
+        fuse = (self.apply_gradient and self.dp_group_ is None and self.solver_code == 0
+                and not self.accumulate_gradient and self.gradient_bias_with_moment
+                and self.gradient_bias_with_moment.devmem is not None
+                and get(root.common.engine.fuse_bias_update, True))
+        if fuse:
+            kernels.col_sum_gd(eo2, gb_t, self.col_scratch_, self.bias.devmem, self.gradient_bias_with_moment.devmem,
+                               lr=self.learning_rate_bias, wd=self.weights_decay_bias, l1_vs_l2=self.l1_vs_l2_bias,
+                               moment=self.gradient_moment_bias)
+            self.bias.mark_device_written()
+            self.gradient_bias_with_moment.mark_device_written()
+        else:
+            kernels.col_sum(eo2, gb_t, self.col_scratch_, accumulate=True)
+            self.gradient_bias.mark_device_written()
+        self.bias_updated_ = fuse
+
     def device_update(self, forward=None, skip_weights=False):
         """U1: fused single-GPU GD step on weights and bias (or hand over to the DP group).  ``skip_weights``: the
         weight-gradient GEMM already applied the step in its epilogue (``kernels.gemm_fused_gd``)."""
@@ -517,7 +536,8 @@ class GradientDescentBase(GDBase):
                 kernels.copy_2d(self.weights.devmem.view(shadow.shape[0], -1), shadow)
             self.weights.mark_device_written()
             self.gradient_weights_with_moment.mark_device_written()
-        if self.bias is not None and self.bias:
+        bias_done, self.bias_updated_ = getattr(self, "bias_updated_", False), False
+        if self.bias is not None and self.bias and not bias_done:
             kernels.gd_update(self.bias.devmem, self.gradient_bias.devmem, self.gradient_bias_with_moment.devmem,
                               self.accumulated_gradient_bias.devmem if self.accumulated_gradient_bias else None,
                               None, lr=self.learning_rate_bias, wd=self.weights_decay_bias,

@@ -357,8 +357,7 @@ class GDRecurrentBase(GradientDescentBase):
         gw = gw_t.view(w.shape[0], -1)
         kernels.gemm(self.dz_, fwd.xh_, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)   # dW = dZ^T . xh
         if self.bias is not None and self.bias:
-            kernels.col_sum(self.dz_, gb_t, self.col_scratch_, accumulate=True)
-            self.gradient_bias.mark_device_written()
+            self.device_bias_sum(self.dz_, gb_t)
         self.gradient_weights.mark_device_written()
         self.device_update()
 
