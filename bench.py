@@ -40,7 +40,8 @@ def parse():
     p.add_argument("--skip-e2e", action="store_true")
     p.add_argument("--weight-delivery", default="multicast", choices=["multicast", "peer_tma"],
                    help="N>1: multimem.st broadcast of updated bf16 weights, or GEMMs TMA-loading weight tiles from owners")
-    p.add_argument("--comm-ctas", type=int, default=64, help="N>1: CTAs of the fused all-reduce+GD kernel")
+    p.add_argument("--comm-ctas", type=int, default=0,
+                   help="N>1: CTAs of the fused all-reduce+GD kernel (0 = by world size: 96 for 2 ranks, else 64)")
     p.add_argument("--gemm-schedule", default="static", choices=["static", "clc"],
                    help="GEMM tile scheduling: static persistent round-robin, or cluster-launch-control work stealing")
     p.add_argument("--split-handshake", action="store_true",
