@@ -1,4 +1,6 @@
 """Control-flow plumbing units (reference: veles/plumbing.py:17-112)."""
+import os
+
 from .distributable import TriviallyDistributable
 from .units import Unit, TrivialUnit
 
@@ -16,6 +18,14 @@ class Repeater(TrivialUnit):
     def link_from(self, *args):
         super(Repeater, self).link_from(*args)
         return self
+
+    def run(self):
+        # one beat per loop iteration for the rank supervisor (no-op unless VELES_HEARTBEAT_FILE is set)
+        if os.environ.get("VELES_HEARTBEAT_FILE"):
+            from .parallel.supervisor import heartbeat, maybe_die
+            heartbeat()
+            maybe_die()
+        return super(Repeater, self).run()
 
 
 class UttermostPoint(TrivialUnit):

@@ -93,6 +93,9 @@ class Trainer(object):
         if not prefetched:
             self.feed(data, labels)
         self.stepper.run(train=True, serve=True)
+        if os.environ.get("VELES_HEARTBEAT_FILE"):
+            from .parallel.supervisor import heartbeat
+            heartbeat()
         return self.read_loss()
 
     def read_loss(self):
