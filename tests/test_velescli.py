@@ -127,3 +127,34 @@ def test_range_arithmetic_keeps_a_tunable_interval():
     assert abs(float(Range(1.0, 0.0, 2.0) / 4) - 0.25) < 1e-12
     n = -Range(1.0, 0.5, 2.0)
     assert n.min_value == -2.0 and n.max_value == -0.5
+
+
+def test_data_parallel_cli_under_the_rank_supervisor(tmp_path):
+    """`python -m veles_b200 ...` started once per rank (WORLD_SIZE in the environment) trains replicas that exchange
+    gradients (host mode over gloo on the numpy backend) and walks the same global minibatches as one process:
+    same seed -> the same result as the single-process run, up to summation order."""
+    from veles_b200.parallel.supervisor import Supervisor
+    common = ["-r", "1234", os.path.join(SAMPLES, "mnist.py"), "-", "root.mnist.decision.max_epochs=2",
+              "root.mnist.loader.n_train=600", "root.mnist.loader.n_valid=200",
+              "root.common.disable.snapshotting=True"]
+    single = tmp_path / "single.json"
+    r = cli("--result-file", str(single), *common)
+    assert r.returncode == 0, r.stdout.decode()[-2000:]
+    multi = tmp_path / "multi.json"
+    cmd = [sys.executable, "-m", "veles_b200", "--no-logo", "-v", "warning", "-a", "numpy",
+           "--result-file", str(multi)] + common
+    logs = []
+    sup = Supervisor(cmd, 2, max_restarts=0, env={"PYTHONPATH": ROOT, "OMP_NUM_THREADS": "2"}, log=logs.append,
+                     log_dir=str(tmp_path / "logs"))
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    try:
+        rc = sup.run()
+    finally:
+        os.chdir(cwd)
+    rank_logs = "".join(open(os.path.join(str(tmp_path / "logs"), f), errors="replace").read()[-1500:]
+                        for f in sorted(os.listdir(str(tmp_path / "logs"))))
+    assert rc == 0, rank_logs
+    a, b = json.loads(single.read_text()), json.loads(multi.read_text())
+    assert a["Total epochs"] == b["Total epochs"]
+    assert abs(a["EvaluationFitness"] - b["EvaluationFitness"]) < 0.02, (a["EvaluationFitness"], b["EvaluationFitness"])

@@ -72,11 +72,33 @@ class Main(Logger, CommandLineBase):
         if self.args.debug_pickle:
             setup_pickle_debug()
 
+    def _rank_group_entropy(self, nbytes):
+        """One process per GPU (WORLD_SIZE > 1): replicas must start from identical weights, so random seed material
+        is drawn on rank 0 and broadcast (this also brings up the process group the data-parallel launcher uses)."""
+        import torch
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            if torch.cuda.is_available() and getattr(self.args, "backend", "auto") not in ("numpy",):
+                local = int(os.environ.get("LOCAL_RANK", "0"))
+                torch.cuda.set_device(local % torch.cuda.device_count())
+                dist.init_process_group("cpu:gloo,cuda:nccl")
+            else:
+                dist.init_process_group("gloo")
+        buf = torch.from_numpy(numpy.frombuffer(os.urandom(nbytes), dtype=numpy.uint8).copy())
+        dist.broadcast(buf, 0)
+        return buf.numpy().tobytes()
+
     def _seed_random(self, rndvals):
         """Seed PRNG key 1, 2, ... from comma separated specs (file:count[:dtype] | hex | '-')."""
+        world = int(os.environ.get("WORLD_SIZE", "1") or 1)
+        replicated = world > 1 and getattr(self.args, "data_parallel", "auto") != "off" and \
+            not self.args.master_address and not self.args.listen_address
         for i, rndval in enumerate(rndvals.split(",")):
             key = i + 1
             rg = prng.get(key)
+            if replicated and (rndval == "-" or rndval.split(":")[0] in ("/dev/urandom", "/dev/random")):
+                rg.seed(numpy.frombuffer(self._rank_group_entropy(64), dtype=numpy.uint32))
+                continue
             if rndval == "-":
                 rg.seed(numpy.frombuffer(os.urandom(64), dtype=numpy.uint32))
                 continue

@@ -72,6 +72,7 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
         self.workflow = None
         self.device = kwargs.get("device")
         self.agent = None
+        self.dp_ = None
         self._thread_pool = None
         self._initialized = False
         self._running = False
@@ -97,6 +98,9 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
         parser.add_argument("--max-nodes", type=int, default=0, help="Limit on the number of slaves.")
         parser.add_argument("--slave-launch-transform", type=str, default="",
                             help="printf-style wrapper (%%s = the command) applied to slave command lines.")
+        parser.add_argument("--data-parallel", type=str, default="auto", choices=["auto", "off", "fused", "nccl", "host"],
+                            help="With WORLD_SIZE > 1 (one process per GPU): synchronous data parallelism through "
+                                 "the fused all-reduce+update kernel (auto on GPUs), NCCL, or host all-reduce (numpy).")
         parser.add_argument("--yarn-nodes", type=str, default="", help="Accepted for compatibility; ignored.")
         parser.add_argument("-t", "--test", default=False, action="store_true",
                             help="Evaluation mode: run the workflow on the test data without training.")
@@ -208,10 +212,50 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
             except Exception as e:  # noqa: BLE001 - plotting is optional
                 self.debug("plotting is disabled: %s", e)
         self.event("work", "begin", mode=self.mode)
+        self.dp_ = self._setup_data_parallel()
         self.workflow.initialize(device=self.device, **kwargs)
+        if self.dp_ is not None:
+            self.dp_.finalize(self.workflow)
         self._initialized = True
         if self.is_master and self.args.nodes:
             self.launch_remote_progs()
+
+    def _setup_data_parallel(self):
+        """Synchronous data parallelism for a plain ``python -m veles_b200 ...`` run started once per GPU (torchrun or
+        ``veles_b200.parallel.supervisor``): ``WORLD_SIZE`` > 1 in the environment turns every rank's workflow into a
+        replica whose gradients are exchanged by ``parallel.DataParallel`` ("fused" kernel on GPUs, host all-reduce
+        over gloo on the numpy backend).  The configured minibatch is the GLOBAL one: each rank materialises its
+        1/world slice, so an N-rank run walks the same minibatch sequence as a single process.  Rank 0 keeps the
+        side effects (snapshots, plots, reports)."""
+        world = int(os.environ.get("WORLD_SIZE", "1") or 1)
+        mode = getattr(self.args, "data_parallel", "auto") or "auto"
+        wf = self.workflow
+        if world <= 1 or mode == "off" or self.is_master or self.is_slave or not hasattr(wf, "gds"):
+            return None
+        import torch
+        import torch.distributed as dist
+        on_gpu = self.device is not None and self.device.exists
+        if not dist.is_initialized():
+            if on_gpu:
+                dist.init_process_group("cpu:gloo,cuda:nccl", device_id=self.device.torch_device)
+            else:
+                dist.init_process_group("gloo")
+        if mode == "auto":
+            mode = "fused" if on_gpu else "host"
+        from .parallel.dp import DataParallel
+        dp = DataParallel(mode=mode)
+        dp.auto_finish = True
+        loader = getattr(wf, "loader", None)
+        if loader is not None:
+            loader.shard_rank, loader.shard_world = dp.rank, dp.world_size
+        if dp.rank != 0:
+            for key in ("snapshotting", "plotting", "publishing"):
+                setattr(root.common.disable, key, True)
+            if getattr(wf, "result_file", None):
+                wf.result_file = None           # every rank holds the same (reduced) results: rank 0 writes them
+        dp.attach(wf)
+        self.info("data parallel: rank %d of %d, mode %s", dp.rank, dp.world_size, mode)
+        return dp
 
     def run(self):
         """Run the workflow and block until it finishes."""

@@ -44,6 +44,8 @@ class DataParallel(object):
         # rank that four do and want more loads in flight (measured, AlexNet: 2 GPUs 3.60 / 3.46 ms with 64 / 96 CTAs;
         # 4 GPUs 3.94 / 4.12 ms with 64 / 128)
         self.n_ctas = int(n_ctas) if n_ctas else (96 if self.world_size <= 2 else 64)
+        self.auto_finish = False      # set by the launcher for graph-run workflows (FlatStep calls finish_step itself)
+        self.last_unit = None         # the exchanged GD unit that runs last in a backward pass
         self.timeout_s = timeout_s
         self.use_multimem = use_multimem
         # shard_master: each rank keeps only ITS slice of the fp32 master weights current (the slice it updates);
@@ -100,6 +102,7 @@ class DataParallel(object):
                 if hasattr(gd, "gradient_weights") and gd.weights is not None and gd.weights:
                     gd.dp_group_ = self
                     self.units.append(gd)
+            self.last_unit = self.units[0] if self.units else None      # wf.gds is in forward order
             if hasattr(wf, "decision") and wf.decision is not None:
                 wf.decision.dp_group = self
             return
@@ -109,6 +112,7 @@ class DataParallel(object):
             if hasattr(gd, "gradient_weights") and gd.weights is not None and gd.weights:
                 gd.dp_group_ = self
                 self.units.append(gd)
+        self.last_unit = self.units[0] if self.units else None          # wf.gds is in forward order
         if hasattr(wf, "decision") and wf.decision is not None:
             wf.decision.dp_group = self
         if self.mode != "fused":
@@ -220,7 +224,9 @@ class DataParallel(object):
     def update_unit(self, gd):
         import torch
         if self.mode == "fused":
-            return self._update_fused(gd)
+            res = self._update_fused(gd)
+            self._maybe_finish(gd)
+            return res
         # --- NCCL baseline: all-reduce, then the single-GPU fused GD kernel
         dist = self._dist
         op = dist.ReduceOp.AVG if self.grad_scale != 1.0 else dist.ReduceOp.SUM
@@ -232,6 +238,13 @@ class DataParallel(object):
             gd.device_update()
         finally:
             gd.dp_group_ = group
+        self._maybe_finish(gd)
+
+    def _maybe_finish(self, gd):
+        """Workflows driven by their own unit graph (``wf.run()``, the CLI) have no stepper that calls
+        ``finish_step``: the unit that runs last in the backward chain closes the step itself."""
+        if self.auto_finish and gd is self.last_unit:
+            self.finish_step()
 
     def _update_fused(self, gd):
         import torch
