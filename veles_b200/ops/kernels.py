@@ -47,24 +47,24 @@ def _p(t):
 
 
 _TLS = threading.local()
-_DEVICE_INDEX = [None]
+_BOUND = {"index": None, "generation": 0}    # the device this process computes on; bumped when it changes
 
 
 def bind_device(index):
     """The device this process computes on (set by B200Device); worker threads bind to it on their first launch."""
-    if _DEVICE_INDEX[0] != int(index):
-        _DEVICE_INDEX[0] = int(index)
-        _DEVICE_INDEX.append(None)       # new generation: every thread re-binds
+    if _BOUND["index"] != int(index):
+        _BOUND["index"] = int(index)
+        _BOUND["generation"] += 1          # every thread re-binds
 
 
 def _stream():
     # The C entry points use the calling thread's current CUDA device / context (driver-API tensor-map encoding
     # fails with CUDA_ERROR_INVALID_CONTEXT in a thread that never touched the runtime).  A workflow's thread
     # pool starts threads that may reach a launch before any torch op: bind them once.
-    if getattr(_TLS, "gen", -1) != len(_DEVICE_INDEX):
-        idx = _DEVICE_INDEX[0]
+    if getattr(_TLS, "generation", -1) != _BOUND["generation"]:
+        idx = _BOUND["index"]
         torch.cuda.set_device(torch.cuda.current_device() if idx is None else idx)
-        _TLS.gen = len(_DEVICE_INDEX)
+        _TLS.generation = _BOUND["generation"]
     return c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
