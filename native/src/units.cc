@@ -284,6 +284,124 @@ VELES_REGISTER_UNIT(MaxAbsPooling, "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0012", "MaxA
 VELES_REGISTER_UNIT(AvgPooling, "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0013", "AvgPooling");
 
 // ---------------------------------------------------------------------------------------------------------
+// Recurrent layers (veles_b200/znicz/recurrent.py): the concatenated operand [x_t | h_{t-1}] of every step lives
+// time-major in one bf16 scratch buffer; a step is one GEMM (bias in the epilogue) + one cell kernel that writes h_t
+// into the next step's slot and into the output rows.  GATES = 1: Elman RNN (tanh), 4: LSTM (i f g o).
+template <int GATES>
+class RecurrentUnit : public WeightedUnit {
+ public:
+  Shape OutputShape(const Shape& in) const override {
+    int64_t T, D;
+    Geometry(in, &T, &D);
+    if (return_sequences_) return Shape{T, hidden_};
+    return Shape{hidden_};
+  }
+  size_t ScratchBytes(int batch, const Shape& in) const override {
+    int64_t T, D;
+    Geometry(in, &T, &D);
+    const Layout l = MakeLayout(batch, T, D);
+    return l.total;
+  }
+  void Initialize(int, const Shape& in) override {
+    int64_t T, D;
+    Geometry(in, &T, &D);
+    Upload(GATES * hidden_, D + hidden_);
+  }
+  void Execute(const void* in, void* out, void* scratch, int batch, const Shape& ishape, cudaStream_t s) override {
+    int64_t T, D;
+    Geometry(ishape, &T, &D);
+    const int64_t H = hidden_;
+    const Layout l = MakeLayout(batch, T, D);
+    char* base = static_cast<char*>(scratch);
+    uint16_t* xh = reinterpret_cast<uint16_t*>(base + l.xh);
+    float* z = reinterpret_cast<float*>(base + l.z);
+    float* state = reinterpret_cast<float*>(base + l.state);      // LSTM: gates | c (ping) | c (pong); RNN: h
+    // h_{-1} = 0: the h slot of step 0 is the only one no cell kernel writes
+    VU_CUDA(cudaMemset2DAsync(xh + D, l.pitch * 2, 0, H * 2, batch, s));
+    const uint16_t* x = static_cast<const uint16_t*>(in);
+    for (int64_t t = 0; t < T; ++t) {
+      uint16_t* xh_t = xh + t * batch * l.pitch;
+      vb_check(vb_copy_2d(x + t * D, 1, T * D, xh_t, 1, l.pitch, batch, static_cast<int>(D), s), "vb_copy_2d");
+    }
+    uint16_t* o = static_cast<uint16_t*>(out);
+    const long long ld_out = return_sequences_ ? T * H : H;
+    for (int64_t t = 0; t < T; ++t) {
+      uint16_t* xh_t = xh + t * batch * l.pitch;
+      vb_check(vb_gemm_bf16(xh_t, l.pitch, 0, w_dev_, pitch_, 0, z, l.zpitch, batch, static_cast<int>(GATES * H),
+                            static_cast<int>(D + H), static_cast<const float*>(b_dev_), 0, 1, 0, nullptr, 0, 0, 1.0f,
+                            1, 0, s), "vb_gemm_bf16");
+      void* h_next = (t + 1 < T) ? static_cast<void*>(xh + (t + 1) * batch * l.pitch + D) : nullptr;
+      void* orow = return_sequences_ ? static_cast<void*>(o + t * H) : (t + 1 == T ? static_cast<void*>(o) : nullptr);
+      if (GATES == 4) {
+        float* gates = state;
+        float* c0 = state + static_cast<size_t>(batch) * 4 * H;
+        float* c1 = c0 + static_cast<size_t>(batch) * H;
+        float* c_prev = (t & 1) ? c0 : c1;
+        float* c_cur = (t & 1) ? c1 : c0;
+        vb_check(vb_lstm_cell_forward(z, l.zpitch, t ? c_prev : nullptr, c_cur, gates, 4 * H, h_next, l.pitch, orow, 1,
+                                      ld_out, batch, static_cast<int>(H), s), "vb_lstm_cell_forward");
+      } else {
+        vb_check(vb_rnn_cell_forward(z, l.zpitch, state, h_next, l.pitch, orow, 1, ld_out, batch,
+                                     static_cast<int>(H), s), "vb_rnn_cell_forward");
+      }
+    }
+  }
+
+ protected:
+  void SetExtra(const std::string& name, const Property& v) override {
+    if (name == "hidden_size") hidden_ = static_cast<int64_t>(v.num);
+    else if (name == "return_sequences") return_sequences_ = v.kind == Property::Bool ? v.b : v.num != 0;
+    else if (name == "sequence_length") seq_len_ = static_cast<int64_t>(v.num);
+  }
+
+ private:
+  struct Layout {
+    int64_t pitch, zpitch;
+    size_t xh, z, state, total;
+  };
+  static size_t Align(size_t v) { return (v + 255) / 256 * 256; }
+  Layout MakeLayout(int batch, int64_t T, int64_t D) const {
+    Layout l;
+    l.pitch = (D + hidden_ + 7) / 8 * 8;
+    l.zpitch = (GATES * hidden_ + 3) / 4 * 4;
+    l.xh = 0;
+    l.z = Align(static_cast<size_t>(T) * batch * l.pitch * 2);
+    l.state = l.z + Align(static_cast<size_t>(batch) * l.zpitch * 4);
+    const size_t state_floats = GATES == 4 ? static_cast<size_t>(batch) * hidden_ * 6 : static_cast<size_t>(batch) * hidden_;
+    l.total = l.state + Align(state_floats * 4);
+    return l;
+  }
+  void Geometry(const Shape& in, int64_t* T, int64_t* D) const {
+    if (hidden_ <= 0) throw std::runtime_error(std::string(Name()) + ": hidden_size was not set");
+    const int64_t n = shape_size(in);
+    if (in.size() == 2 && (seq_len_ <= 0 || seq_len_ == in[0])) {
+      *T = in[0];
+      *D = in[1];
+      return;
+    }
+    if (seq_len_ <= 0 || n % seq_len_) throw std::runtime_error(std::string(Name()) + ": input is not [T, D] and sequence_length does not divide it");
+    *T = seq_len_;
+    *D = n / seq_len_;
+  }
+  int64_t hidden_ = 0, seq_len_ = 0;
+  bool return_sequences_ = true;
+};
+
+class RNN : public RecurrentUnit<1> {
+ public:
+  const char* Uuid() const override { return "0d2a3e57-7b0f-4c63-9b55-5a4e3d6f2c11"; }
+  const char* Name() const override { return "RNN"; }
+};
+VELES_REGISTER_UNIT(RNN, "0d2a3e57-7b0f-4c63-9b55-5a4e3d6f2c11", "RNN");
+
+class LSTM : public RecurrentUnit<4> {
+ public:
+  const char* Uuid() const override { return "6c1e8f0a-2d47-4b39-8a6e-9f3b7c5d1e24"; }
+  const char* Name() const override { return "LSTM"; }
+};
+VELES_REGISTER_UNIT(LSTM, "6c1e8f0a-2d47-4b39-8a6e-9f3b7c5d1e24", "LSTM");
+
+// ---------------------------------------------------------------------------------------------------------
 class LRNormalizerForward : public Unit {
  public:
   const char* Uuid() const override { return "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0021"; }

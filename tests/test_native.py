@@ -42,6 +42,14 @@ def test_native_cpu_checks_and_package_loading(tmp_path):
     assert r.returncode == 0 and "0 failed" in out, out
     assert "All2All" not in out or "2 units" in out
     wf.launcher.stop()
+    # a recurrent model: the factory knows the LSTM unit and plans its shapes (784 = 28 steps x 28 pixels -> 10)
+    wf = _trained("mnist_lstm", NumpyDevice(), minibatch_size=50, n_train=100, n_valid=50)
+    z2 = str(tmp_path / "mnist_lstm.zip")
+    wf.package_export(z2, "zip")
+    r = subprocess.run([test_bin, z2], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=120)
+    out = r.stdout.decode()
+    assert r.returncode == 0 and "0 failed" in out and "2 units" in out, out
+    wf.launcher.stop()
 
 
 def _native(lib_path):
@@ -60,6 +68,7 @@ def _native(lib_path):
 @pytest.mark.parametrize("model,kw,shape", [
     ("mnist_mlp", dict(minibatch_size=50, n_train=200, n_valid=50), (784,)),
     ("cifar_convnet", dict(minibatch_size=32, n_train=64, n_valid=32, layers_kwargs={"caffe_init": False}), (32, 32, 3)),
+    ("mnist_lstm", dict(minibatch_size=50, n_train=200, n_valid=50), (784,)),
 ])
 def test_native_runtime_matches_python_forward(tmp_path, model, kw, shape):
     from veles_b200.backends import B200Device

@@ -79,7 +79,16 @@ def lstm_classifier_layers(hidden=128, n_classes=10, lr=0.02, stacked=False):
     return layers
 
 
+def mnist_lstm_layers(hidden=64, lr=0.02):
+    """MNIST-shape images read row by row: a 28-step LSTM over 28 pixels, last state -> softmax."""
+    return [{"type": "lstm", "->": {"hidden_size": hidden, "return_sequences": False, "sequence_length": 28},
+             "<-": _gd(lr, 0.0)},
+            {"type": "softmax", "->": {"output_sample_shape": 10}, "<-": _gd(lr, 0.0)}]
+
+
 MODEL_CONFIGS = {
+    "mnist_lstm": dict(layers=mnist_lstm_layers, loader_name="mnist_loader", loss_function="softmax",
+                       sample_shape=(784,), n_classes=10, minibatch=100),
     "lstm_classifier": dict(layers=lstm_classifier_layers, loader_name="synthetic_fullbatch", loss_function="softmax",
                             sample_shape=(16, 64), n_classes=10, minibatch=128),
     "mnist_mlp": dict(layers=mnist_mlp_layers, loader_name="mnist_loader", loss_function="softmax",

@@ -48,6 +48,7 @@ class RecurrentBase(Forward):
         self.hidden_size = int(hidden)
         self.return_sequences = bool(kwargs.get("return_sequences", True))
         self.sequence_length = kwargs.get("sequence_length")
+        self.exports = self.exports + ["hidden_size", "return_sequences", "sequence_length"]
 
     def init_unpickled(self):
         super(RecurrentBase, self).init_unpickled()
