@@ -311,3 +311,31 @@ def test_confluence_backend_against_a_local_xmlrpc_server(tmp_path):
     finally:
         srv.shutdown()
         srv.server_close()
+
+
+def test_update_forge_uploads_every_model_directory(tmp_path, capsys):
+    """scripts/update_forge: walk a tree, upload every directory with a manifest (reference: scripts/update_forge.py)."""
+    from veles_b200.forge.forge_client import ForgeClient
+    from veles_b200.forge.forge_server import ForgeServer
+    from veles_b200.scripts import update_forge
+    for name in ("alpha", "nested/beta"):
+        d = tmp_path / "models" / name
+        d.mkdir(parents=True)
+        (d / "wf.py").write_text("def run(load, main): pass\n")
+        (d / "cfg.py").write_text("# config\n")
+        (d / "manifest.json").write_text(json.dumps({
+            "name": os.path.basename(name), "workflow": "wf.py", "configuration": "cfg.py",
+            "short_description": name, "long_description": name, "author": "tester"}))
+    (tmp_path / "models" / "not_a_model").mkdir()
+    srv = ForgeServer(str(tmp_path / "store")).start()
+    try:
+        c = ForgeClient(srv.url)
+        token = c.register("me@example.com")
+        assert update_forge.main([]) == 1                       # usage
+        token = token if isinstance(token, str) else getattr(c, "token", None)
+        assert update_forge.main([str(tmp_path / "models"), srv.url, token]) == 0
+        assert sorted(row[0] for row in c.list()) == ["alpha", "beta"]
+        out = capsys.readouterr().out
+        assert "alpha" in out and "beta" in out and "not_a_model" not in out
+    finally:
+        srv.stop()

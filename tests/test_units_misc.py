@@ -126,3 +126,34 @@ def test_loader_validation_ratio_is_stratified():
     all_labels = np.array(l.original_labels)
     for c in range(4):
         assert abs((valid_labels == c).sum() - 0.25 * (all_labels == c).sum()) <= 1
+
+
+def test_device_benchmark_and_workflow_computing_power():
+    """DeviceBenchmark / AcceleratedWorkflow.computing_power on the numpy backend (reference:
+    accelerated_units.py:706-866: power = 1000 / time of the GEMM batch, cached between measurements)."""
+    from veles_b200.accelerated_units import DeviceBenchmark, AcceleratedWorkflow
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.dummy import DummyLauncher
+    launcher = DummyLauncher()
+    wf = AcceleratedWorkflow(launcher)
+    wf.initialize(device=NumpyDevice())
+    bench = DeviceBenchmark(wf, size=64, repeats=3)
+    bench.initialize(device=NumpyDevice())
+    bench.run()
+    assert bench.computing_power > 0
+    p1 = wf.computing_power
+    assert p1 > 0 and wf.computing_power == p1          # cached until the measurement interval passes
+    launcher.stop()
+
+
+def test_shell_unit_is_inert_without_a_terminal():
+    """Shell drops into a console only for interactive runs on a tty (reference: interaction.py:49-95)."""
+    from veles_b200.dummy import DummyWorkflow
+    from veles_b200.interaction import Shell
+    wf = DummyWorkflow()
+    sh = Shell(wf)
+    sh.initialize()
+    assert sh.run() is None                              # pytest has no tty: returns immediately
+    sh.enabled = False
+    assert sh.run() is None
+    assert "workflow" in Shell.BANNER
