@@ -10,8 +10,9 @@ filters are *derived*:
   unit circle (extremal phase), times the N-fold zero at z = -1.
 * Symlet(N): the same factorisation, but for every root group {z, 1/z} (real) or {z, z*, 1/z, 1/z*} (complex) the
   side that is kept is chosen by exhaustive search for the most linear phase (least asymmetric filter).
-* Coiflet(K), 6K taps: Newton / least-squares solution of the defining equations (orthonormality, 2K vanishing
-  wavelet moments, 2K-1 vanishing shifted scaling moments), the most symmetric solution wins.
+* Coiflet(K), 6K taps: least-squares solution of the defining equations (orthonormality, 2K vanishing wavelet
+  moments, 2K-1 vanishing shifted scaling moments); K = 1 from random starts, every further order by continuation
+  from the previous one.
 
 Every filter is normalised to sum sqrt(2) and checked for orthonormality before it is written.
 Usage: python scripts/gen_wavelet_tables.py [--max-daubechies 38] [--max-symlet 38]
@@ -161,8 +162,20 @@ def coiflet_equations(h, K):
 
 
 def coiflet(K, tries=12, seed=1):
+    """Coiflet with 6K taps.  K = 1 is found from random starts; every further order is grown from the previous one
+    (its taps shifted by two so that the centre taps line up, zeros at both ends): successive coiflets resemble
+    each other closely enough for the least-squares iteration to stay on the customary branch, where random starts
+    for 30 taps converge rarely and to several different solutions."""
     from scipy.optimize import least_squares
     L = 6 * K
+    if K > 1:
+        prev = np.asarray(coiflet(K - 1, tries, seed))
+        x0 = np.zeros(L)
+        x0[2:2 + len(prev)] = prev
+        sol = least_squares(coiflet_equations, x0, args=(K,), xtol=1e-15, ftol=1e-15, gtol=1e-15, max_nfev=8000)
+        if np.abs(sol.fun).max() > 1e-10:
+            raise RuntimeError("coiflet continuation failed for K=%d (residual %.2e)" % (K, np.abs(sol.fun).max()))
+        return coiflet_polish(sol.x, K)
     rng = np.random.RandomState(seed)
     best = None
     c = 2 * K
@@ -180,7 +193,46 @@ def coiflet(K, tries=12, seed=1):
             best = (score, h.copy())
     if best is None:
         raise RuntimeError("no coiflet solution for K=%d" % K)
-    return list(best[1])
+    return coiflet_polish(best[1], K)
+
+
+def coiflet_polish(h0, K, digits=60):
+    """Newton iteration on the coiflet equations in multi-precision arithmetic (analytic Jacobian, least-squares
+    step for the consistent but overdetermined system).  The 30-tap system is ill-conditioned in double precision:
+    two double solutions with residuals below 1e-13 differed by 5e-5; polished, they agree to every digit."""
+    mp = _mp()
+    mp.mp.dps = digits
+    L, c = 6 * K, 2 * K
+    quarter = mp.mpf(L) / 4
+    ug = [(mp.mpf(i - (L - 1 - c)) / quarter) for i in range(L)]
+    uh = [(mp.mpf(i - c) / quarter) for i in range(L)]
+    sign = [1 if i % 2 == 0 else -1 for i in range(L)]
+    x = [mp.mpf(float(v)) for v in h0]
+    for _ in range(20):
+        f, rows = [sum(x) - mp.sqrt(2)], [[mp.mpf(1)] * L]
+        for m in range(1, L // 2):
+            f.append(sum(x[i] * x[i + 2 * m] for i in range(L - 2 * m)))
+            r = [mp.mpf(0)] * L
+            for i in range(L - 2 * m):
+                r[i] += x[i + 2 * m]
+                r[i + 2 * m] += x[i]
+            rows.append(r)
+        f.append(sum(v * v for v in x) - 1)
+        rows.append([2 * v for v in x])
+        for p in range(2 * K):          # wavelet moments: g[i] = (-1)^i h[L-1-i]
+            f.append(sum(sign[i] * x[L - 1 - i] * ug[i] ** p for i in range(L)))
+            r = [mp.mpf(0)] * L
+            for i in range(L):
+                r[L - 1 - i] += sign[i] * ug[i] ** p
+            rows.append(r)
+        for p in range(1, 2 * K):       # scaling moments around the centre tap
+            f.append(sum(x[i] * uh[i] ** p for i in range(L)))
+            rows.append([uh[i] ** p for i in range(L)])
+        dx = mp.lu_solve(mp.matrix(rows), -mp.matrix(f))
+        x = [x[i] + dx[i] for i in range(L)]
+        if max(abs(v) for v in dx) < mp.mpf(10) ** (-(digits - 10)):
+            break
+    return [float(v) for v in x]
 
 
 def check_orthonormal(h, tol=1e-9):
@@ -195,11 +247,17 @@ def main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-daubechies", type=int, default=38)
     ap.add_argument("--max-symlet", type=int, default=38)
-    ap.add_argument("--max-coiflet", type=int, default=4)   # 30 taps: the solver does not settle on one solution
+    ap.add_argument("--max-coiflet", type=int, default=5)
+    ap.add_argument("--only-coiflets", action="store_true", help="keep the other families of the existing JSON")
     ap.add_argument("--out-json", default=os.path.join(ROOT, "veles_b200", "simd", "wavelet_tables.json"))
     ap.add_argument("--out-header", default=os.path.join(ROOT, "native", "include", "veles", "wavelet_tables.h"))
     args = ap.parse_args(argv)
     tables = {"daubechies": {}, "symlet": {}, "coiflet": {}}
+    if args.only_coiflets:
+        with open(args.out_json) as f:
+            old = json.load(f)
+        tables["daubechies"], tables["symlet"] = old["daubechies"], old["symlet"]
+        args.max_daubechies = args.max_symlet = 0
     for N in range(1, args.max_daubechies + 1):
         h = daubechies(N)
         check_orthonormal(h, 1e-9)
