@@ -158,3 +158,33 @@ def test_data_parallel_cli_under_the_rank_supervisor(tmp_path):
     a, b = json.loads(single.read_text()), json.loads(multi.read_text())
     assert a["Total epochs"] == b["Total epochs"]
     assert abs(a["EvaluationFitness"] - b["EvaluationFitness"]) < 0.02, (a["EvaluationFitness"], b["EvaluationFitness"])
+
+
+def test_supervised_cli_run_survives_a_rank_death(tmp_path):
+    """Two data-parallel CLI ranks (numpy backend); rank 1 is killed in the second epoch; the supervisor restarts the
+    group from the newest snapshot rank 0 wrote and the run completes all epochs."""
+    from veles_b200.parallel.supervisor import Supervisor
+    snaps = tmp_path / "snaps"
+    res = tmp_path / "res.json"
+    cmd = [sys.executable, "-m", "veles_b200", "--no-logo", "-v", "warning", "-a", "numpy", "--result-file", str(res),
+           "-r", "1234", "-w", "{snapshot}", os.path.join(SAMPLES, "mnist.py"), "-",
+           "root.mnist.decision.max_epochs=3", "root.mnist.loader.n_train=600", "root.mnist.loader.n_valid=200",
+           'root.common.dirs.snapshots="%s"' % snaps]
+    logs = []
+    # 600 train + 200 validation samples in minibatches of 100: 8 loop iterations per epoch -> call 13 is in epoch 2
+    sup = Supervisor(cmd, 2, max_restarts=2, snapshot_glob=str(snaps / "mnist_*.pickle.gz"), log=logs.append,
+                     log_dir=str(tmp_path / "logs"),
+                     env={"PYTHONPATH": ROOT, "OMP_NUM_THREADS": "2", "VELES_RANK_DEATH_STEP": "1:13"})
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    try:
+        rc = sup.run()
+    finally:
+        os.chdir(cwd)
+    rank_logs = "".join(open(os.path.join(str(tmp_path / "logs"), f), errors="replace").read()[-1200:]
+                        for f in sorted(os.listdir(str(tmp_path / "logs"))))
+    assert rc == 0, rank_logs + repr(sup.history)
+    assert [h["outcome"] for h in sup.history] == ["exit 42", "ok"], sup.history
+    assert sup.history[1]["snapshot"] and "mnist_" in sup.history[1]["snapshot"]
+    data = json.loads(res.read_text())
+    assert data["Total epochs"] >= 3 and data["EvaluationFitness"] > 0.8

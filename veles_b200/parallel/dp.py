@@ -74,6 +74,11 @@ class DataParallel(object):
         self._pending_events = []
 
     # -- setup -----------------------------------------------------------------------------------------------
+    def __reduce__(self):
+        # process groups, symmetric-memory handles and streams belong to this process: a snapshot of a workflow that
+        # references its group (Decision.dp_group) stores None there; the launcher attaches a new group on resume
+        return (type(None), ())
+
     def attach(self, wf):
         """Before ``wf.initialize``: route the exchanged arena kinds into symmetric memory."""
         self.wf = wf

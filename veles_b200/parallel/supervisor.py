@@ -55,13 +55,27 @@ heartbeat.min_interval = 0.5
 
 
 def maybe_die(step=None):
-    """Fault injection: with probability ``VELES_RANK_DEATH_PROBABILITY`` per call, exit abruptly (code 42)."""
+    """Fault injection: with probability ``VELES_RANK_DEATH_PROBABILITY`` per call, exit abruptly (code 42).
+    ``VELES_RANK_DEATH_STEP="<rank>:<n>"`` is the deterministic variant: that rank dies at its n-th call, in the first
+    attempt only (what the tests use)."""
+    spec = os.environ.get("VELES_RANK_DEATH_STEP")
+    if spec and restart_count() == 0:
+        rank, _, nth = spec.partition(":")
+        if os.environ.get("RANK", "0") == rank:
+            maybe_die.calls += 1
+            if maybe_die.calls == int(nth or 1):
+                sys.stderr.write("rank %s: injected death at call %d\n" % (rank, maybe_die.calls))
+                sys.stderr.flush()
+                os._exit(42)
     p = float(os.environ.get("VELES_RANK_DEATH_PROBABILITY", "0") or 0)
     if p > 0 and random.random() < p:
         sys.stderr.write("rank %s: injected death%s\n" % (os.environ.get("RANK", "?"),
                                                          "" if step is None else " at step %s" % step))
         sys.stderr.flush()
         os._exit(42)
+
+
+maybe_die.calls = 0
 
 
 def restart_count():

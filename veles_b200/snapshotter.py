@@ -134,16 +134,24 @@ class SnapshotterToFile(SnapshotterBase):
         os.makedirs(self.directory, exist_ok=True)
         self.destination = os.path.abspath(os.path.join(self.directory, rel))
         t0 = time.time()
-        if self.compression == "snappy":
-            sn = _snappy()
-            if sn is None:
-                raise RuntimeError("snappy compression requested but python-snappy is not installed")
-            payload = pickle.dumps(self.workflow, protocol=best_protocol)
-            with open(self.destination, "wb") as f:
-                f.write(sn.compress(payload))
-        else:
-            with self.WRITE_CODECS[self.compression](self.destination, self.compression_level) as fout:
-                pickle.dump(self.workflow, fout, protocol=best_protocol)
+        # written under a temporary name and renamed: a crash (or a failing pickle) in the middle of a snapshot must
+        # not leave a truncated file that a restart would then pick up as "the newest snapshot"
+        tmp = self.destination + ".part"
+        try:
+            if self.compression == "snappy":
+                sn = _snappy()
+                if sn is None:
+                    raise RuntimeError("snappy compression requested but python-snappy is not installed")
+                payload = pickle.dumps(self.workflow, protocol=best_protocol)
+                with open(tmp, "wb") as f:
+                    f.write(sn.compress(payload))
+            else:
+                with self.WRITE_CODECS[self.compression](tmp, self.compression_level) as fout:
+                    pickle.dump(self.workflow, fout, protocol=best_protocol)
+            os.replace(tmp, self.destination)
+        finally:
+            if os.path.exists(tmp):
+                os.remove(tmp)
         size = os.path.getsize(self.destination)
         self.check_snapshot_size(size)
         if self.verbose:
