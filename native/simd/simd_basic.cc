@@ -195,8 +195,13 @@ void vs_matrix_multiply_transposed(const float* m1, const float* m2, size_t w1, 
     const float* a = m1 + i * w1;
     for (size_t j = 0; j < h2; ++j) {
       const float* b = m2 + j * w1;
-      float s = 0.f;
-      for (size_t k = 0; k < w1; ++k) s += a[k] * b[k];
+      // eight independent partial sums: strict IEEE ordering would otherwise keep this dot product scalar
+      float p[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      size_t k = 0;
+      for (; k + 8 <= w1; k += 8)
+        for (int u = 0; u < 8; ++u) p[u] += a[k + u] * b[k + u];
+      float s = ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]));
+      for (; k < w1; ++k) s += a[k] * b[k];
       res[i * h2 + j] = s;
     }
   }

@@ -1,9 +1,11 @@
 // Self-checking test binary for libveles_simd (no test framework: each CHECK prints and counts failures).
 // Mirrors what the reference covers in libVeles/simd/tests/{convolve,correlate,wavelet,normalize,detect_peaks,
 // matrix,memory,arithmetic}.cc: every accelerated path against a plain restatement written here.
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <vector>
 
 #include "veles/simd.h"
@@ -226,7 +228,55 @@ static void test_basic() {
   CHECK(vs_fft_complex(z, 3, 1) == -1);
 }
 
-int main() {
+// Timing harness (the reference's simd/tests/benchmark.inc compares its SIMD and plain variants; here the three
+// convolution algorithms and the transforms are timed against each other): `test_simd --bench`.
+template <typename F>
+static double time_ms(F&& fn, int repeats) {
+  fn();
+  const auto t0 = std::chrono::steady_clock::now();
+  for (int i = 0; i < repeats; ++i) fn();
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() / repeats;
+}
+
+static void bench() {
+  const size_t sizes[][2] = {{512, 64}, {4096, 64}, {4096, 1024}, {65536, 512}};
+  for (auto& sz : sizes) {
+    auto x = noise(sz[0], 1), h = noise(sz[1], 2);
+    std::vector<float> out(sz[0] + sz[1] - 1);
+    printf("convolve %6zu x %4zu:", sz[0], sz[1]);
+    for (int alg = 0; alg < 3; ++alg) {
+      VsConvolution* c = vs_convolve_initialize_algorithm(sz[0], sz[1], alg);
+      const double ms = time_ms([&] { vs_convolve(c, x.data(), h.data(), out.data()); }, alg == 0 && sz[0] > 10000 ? 1 : 5);
+      printf("  %s %8.3f ms", alg == 0 ? "direct" : (alg == 1 ? "fft" : "overlap-save"), ms);
+      vs_convolve_finalize(c);
+    }
+    printf("   (heuristic picks %d)\n", vs_convolve_choose(sz[0], sz[1]));
+  }
+  auto x = noise(1 << 20, 3);
+  std::vector<float> hi(1 << 19), lo(1 << 19), shi(1 << 20), slo(1 << 20);
+  for (int order : {8, 20, 76})
+    printf("dwt daubechies %2d, 1M samples: %7.3f ms\n", order,
+           time_ms([&] { vs_wavelet_apply(VS_WAVELET_DAUBECHIES, order, VS_EXT_PERIODIC, x.data(), x.size(), hi.data(), lo.data()); }, 5));
+  printf("swt daubechies 8 level 3, 1M samples: %7.3f ms\n",
+         time_ms([&] { vs_stationary_wavelet_apply(VS_WAVELET_DAUBECHIES, 8, 3, VS_EXT_PERIODIC, x.data(), x.size(), shi.data(), slo.data()); }, 3));
+  auto a = noise(512 * 512, 4), b = noise(512 * 512, 5);
+  std::vector<float> c(512 * 512);
+  printf("matrix_multiply 512^3: %7.3f ms, transposed: %7.3f ms\n",
+         time_ms([&] { vs_matrix_multiply(a.data(), b.data(), 512, 512, 512, 512, c.data()); }, 3),
+         time_ms([&] { vs_matrix_multiply_transposed(a.data(), b.data(), 512, 512, 512, 512, c.data()); }, 3));
+  VsExtremumPoint* pts;
+  size_t n;
+  printf("detect_peaks 1M samples: %7.3f ms\n", time_ms([&] {
+           vs_detect_peaks(x.data(), x.size(), VS_EXTREMUM_BOTH, &pts, &n);
+           vs_free(pts);
+         }, 5));
+}
+
+int main(int argc, char** argv) {
+  if (argc > 1 && std::string(argv[1]) == "--bench") {
+    bench();
+    return 0;
+  }
   test_basic();
   test_convolution();
   test_wavelets();
