@@ -445,7 +445,25 @@ class GradientDescentBase(GDBase):
             vel[...] = rho * vel + (1 - rho) * d * d
             w += d
 
+    def warn_inert_options(self):
+        """Znicz hyper-parameters that are accepted (configurations written for the reference load unchanged) but have
+        no effect here - said once per unit instead of silently."""
+        if getattr(self, "_inert_warned_", False):
+            return
+        self._inert_warned_ = True
+        inert = []
+        if self.factor_ortho:
+            inert.append("factor_ortho=%r" % self.factor_ortho)
+        if self.fast_learning_rate is not None:
+            inert.append("fast_learning_rate=%r" % self.fast_learning_rate)
+        if not self.variant_gradient or not self.variant_moment_gradient:
+            inert.append("variant_gradient / variant_moment_gradient=False")
+        if inert:
+            self.warning("%s: %s accepted for compatibility, but this option has no effect in veles_b200",
+                         self.name, ", ".join(inert))
+
     def _ensure_state(self, like, vel, acc):
+        self.warn_inert_options()
         if not vel or vel.shape != like.shape:
             vel.reset(numpy.zeros(like.shape, dtype=numpy.float32))
         if self.solver_code != 0 and (not acc or acc.shape != like.shape):
