@@ -44,6 +44,9 @@ CASES = [
     ("lstm", (8, 5, 13), {"hidden_size": 20}),
     ("lstm", (32, 4, 64), {"hidden_size": 64, "return_sequences": False}),
     ("lstm", (4, 36), {"hidden_size": 8, "sequence_length": 6}),
+    ("all2all_tanh", (64, 96), {"output_sample_shape": 48, "weights_transposed": True}),
+    ("all2all_str", (33, 257), {"output_sample_shape": 130, "weights_transposed": True}),
+    ("softmax", (32, 100), {"output_sample_shape": 10, "weights_transposed": True}),
 ]
 
 

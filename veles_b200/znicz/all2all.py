@@ -21,6 +21,8 @@ class All2All(Forward):
     ACTIVATION = 0
     TWO_PHASE_SPLIT_K = False   # small-batch layers: split-K GEMM into an fp32 scratch + bias/activation pass
     PEER_WEIGHTS_OK = True   # data parallel "peer_tma" delivery: GEMMs may read weight tiles from the owner rank
+    # weights stored (n_in, n_out): the GEMMs read the same buffer with the other operand major, no transposed copy
+    TRANSPOSED_OK = True
     __id__ = "58a5eadf-ae1e-498f-bf35-7d93939c4c86"
 
     def __init__(self, workflow, **kwargs):
@@ -92,7 +94,7 @@ class All2All(Forward):
         self.output._pitched = True
         self.output.initialize(dev)
         self._x_stage_ = None
-        n_in = self.weights_bf16_.shape[1]
+        n_in = self.weights_bf16_.shape[0 if self.weights_transposed else 1]
         xin = self.input.devmem
         # "float" precision (root.common.engine.precision_type): fp32 activations and master weights go straight into
         # the tf32 tensor-core GEMM, no bf16 staging and no weight shadow on this layer's path
@@ -100,10 +102,10 @@ class All2All(Forward):
                       and not self.weights_transposed)
         # Small-batch layers stream the whole weight matrix through few M tiles: splitting K over more CTAs (fp32
         # reduce-add into a scratch, then one tiny bias+activation pass) cuts the re-reads of the activations.
-        n_out = self.weights_bf16_.shape[0]
+        n_out = self.weights_bf16_.shape[1 if self.weights_transposed else 0]
         self.acc_ = None
         # (measured on AlexNet's fc layers: GEMMs 15-30 % faster, but the extra pass eats the gain -> opt-in)
-        if (self.TWO_PHASE_SPLIT_K and not self.tf32_ and n_out % 4 == 0
+        if (self.TWO_PHASE_SPLIT_K and not self.tf32_ and n_out % 4 == 0 and not self.weights_transposed
                 and kernels.gemm_plan(self.input.shape[0], n_out, n_in)[1] >= 2):
             self.acc_ = torch.zeros(self.input.shape[0], n_out, dtype=torch.float32, device=dev.torch_device)
         need_stage = not self.tf32_ and ((xin.dtype != torch.bfloat16) or (n_in % 8 != 0))
@@ -136,7 +138,8 @@ class All2All(Forward):
             kernels.gemm(x, self.weights_bf16_, self.acc_, accumulate=True, split_k=0)
             kernels.bias_act(self.acc_, out2, bias=self.bias.devmem if self.include_bias else None, act=self.ACTIVATION)
         else:
-            kernels.gemm(x, self.weights_bf16_, out2, bias=self.bias.devmem if self.include_bias else None,
+            kernels.gemm(x, self.weights_bf16_, out2, b_mn=self.weights_transposed,
+                         bias=self.bias.devmem if self.include_bias else None,
                          act=self.ACTIVATION, b_peers=getattr(self, "peer_weights_", None))
         self.output.mark_device_written()
 
@@ -224,7 +227,8 @@ class All2AllSoftmax(All2All):
             kernels.gemm(x, self.weights_bf16_, self.logits_, bias=self.bias.devmem if self.include_bias else None,
                          accumulate=True, split_k=0)
         else:
-            kernels.gemm(x, self.weights_bf16_, self.logits_, bias=self.bias.devmem if self.include_bias else None,
+            kernels.gemm(x, self.weights_bf16_, self.logits_, b_mn=self.weights_transposed,
+                         bias=self.bias.devmem if self.include_bias else None,
                          b_peers=getattr(self, "peer_weights_", None))
         if not self.defer_softmax:
             out = self.output.devmem

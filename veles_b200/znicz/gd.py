@@ -110,14 +110,17 @@ class GradientDescent(GradientDescentBase):
                 and n_in % 4 == 0
                 and kernels.gemm_plan(self.err_output.shape[0], n_in, n_out, b_mn=True)[1] >= 2):
             self.ei_acc_ = torch.zeros(self.err_output.shape[0], n_in, dtype=torch.float32, device=dev.torch_device)
+        self.transposed_ = bool(getattr(self.forward, "weights_transposed", False))
+        dw_m, dw_n = (n_in, n_out) if self.transposed_ else (n_out, n_in)
         self.dw_store_ = (self.dp_group_ is None and self.apply_gradient and not self.tf32_mode() and
-                          kernels.gemm_plan(n_out, n_in, self.err_output.shape[0], b_mn=True)[1] == 1)
+                          kernels.gemm_plan(dw_m, dw_n, self.err_output.shape[0], b_mn=True)[1] == 1)
         # Optionally (root.common.engine.fuse_gd_update) the GD step runs in that GEMM's epilogue: the update reads w
         # and momentum at the tile's position and the gradient never reaches HBM (single GPU, momentum solver).
         # Measured on AlexNet's fc6/fc7 it only breaks even (+236 us in the GEMMs, -193 us of update kernels): the
         # separate update already finds the freshly written gradient in the 126 MB L2 -> off by default.
         from ..config import root, get
         self.fused_gd_ = bool(self.dw_store_ and self.solver_code == 0 and not self.accumulate_gradient and
+                              not self.transposed_ and
                               self.forward is not None and getattr(self.forward, "weights_bf16_", None) is not None and
                               get(root.common.engine.fuse_gd_update, False))
 
@@ -192,7 +195,10 @@ class GradientDescent(GradientDescentBase):
             ei = self.err_input.devmem
             ei2 = ei if ei.dim() == 2 else ei.reshape(ei.shape[0], -1)
             peers = getattr(self.forward, "peer_weights_", None)
-            if self.ei_acc_ is not None and peers is None:
+            if self.transposed_:
+                # weights are (n_in, n_out): dY . W^T reads them K-major, like a forward GEMM
+                kernels.gemm(eo, w_bf16, ei2, z=x if self.prev_activation else None, deriv=self.prev_activation)
+            elif self.ei_acc_ is not None and peers is None:
                 kernels.gemm(eo, w_bf16, self.ei_acc_, b_mn=True, accumulate=True, split_k=0)
                 kernels.bias_act(self.ei_acc_, ei2, z=x if self.prev_activation else None, deriv=self.prev_activation)
             else:
@@ -211,9 +217,11 @@ class GradientDescent(GradientDescentBase):
             self.weights.mark_device_written()
             self.gradient_weights_with_moment.mark_device_written()
         elif self.dw_store_:
-            kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=False, split_k=1)
+            ga, gb = (x, eo) if self.transposed_ else (eo, x)        # transposed weights: dW = X^T . dY
+            kernels.gemm(ga, gb, gw, a_mn=True, b_mn=True, accumulate=False, split_k=1)
         else:
-            kernels.gemm(eo, x, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
+            ga, gb = (x, eo) if self.transposed_ else (eo, x)
+            kernels.gemm(ga, gb, gw, a_mn=True, b_mn=True, accumulate=True, split_k=0)
         if self.bias is not None and self.bias:
             self.device_bias_sum(eo, gb_t)
         if not fused:

@@ -258,8 +258,9 @@ class Forward(ForwardBase):
         """Move weights/bias into the device parameter arena and create the bf16 shadow."""
         import torch
         from ..ops import kernels
-        if self.weights_transposed:
-            raise NotImplementedError("weights_transposed=True is supported on the numpy backend only")
+        if self.weights_transposed and not getattr(self, "TRANSPOSED_OK", False):
+            raise NotImplementedError("%s: weights_transposed=True is supported on the numpy backend only"
+                                      % type(self).__name__)
         arena = find_arena(self, self.device_)
         if self.weights.devmem is None:
             self.weights.initialize(self.device_, storage=arena.alloc("weights", self.name + ".weights",

@@ -9,6 +9,7 @@ from .gd import GradientDescent
 
 
 class ResizableAll2All(All2All):
+    TRANSPOSED_OK = False
     MAPPING = {"all2all_resizable"}
 
     def resize(self, n_out):

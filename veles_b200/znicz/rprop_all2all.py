@@ -10,6 +10,7 @@ from .gd import GradientDescent
 
 
 class RPropAll2All(All2All):
+    TRANSPOSED_OK = False
     MAPPING = {"rprop_all2all"}
 
 
