@@ -68,32 +68,67 @@ void vs_wavelet_recycle_source(int /*order*/, float* src, size_t length, float**
   *destlolo = src + 3 * lq;
 }
 
+// Both transforms run tap-outermost over an explicitly extended copy of the signal: every tap then is one
+// contiguous multiply-add sweep over the outputs (the compiler vectorises it), and the border needs no special case.
+// For the decimated transform the extended signal is first split into its even and odd samples, which turns the
+// stride-2 reads into unit-stride ones.
+static void extend_signal(const float* src, long n, long extra, int ext, std::vector<float>* out) {
+  out->resize(static_cast<size_t>(n + extra));
+  memcpy(out->data(), src, static_cast<size_t>(n) * sizeof(float));
+  for (long i = 0; i < extra; ++i) (*out)[n + i] = extended(src, n, n + i, ext);
+}
+
 void vs_wavelet_apply_ex(int type, int order, int ext, int reference_scale, const float* src, size_t length,
                          float* desthi, float* destlo) {
   std::vector<float> lo(order), hi(order);
   if (vs_wavelet_filters(type, order, reference_scale, lo.data(), hi.data()) != 0) return;
-  const long n = static_cast<long>(length);
-  const long interior = n - order >= 0 ? (n - order) / 2 + 1 : 0;   // outputs whose window stays inside src
-  long d = 0;
-  for (; d < interior && 2 * d + order <= n; ++d) {
-    const float* s = src + 2 * d;
-    float rh = 0.f, rl = 0.f;
-    for (int j = 0; j < order; ++j) {
-      rh += hi[j] * s[j];
-      rl += lo[j] * s[j];
+  const long n = static_cast<long>(length), half = n / 2;
+  if (order <= 16) {
+    // short filters: one pass over the signal with both dot products in registers beats the extra copies below
+    long d = 0;
+    for (; 2 * d + order <= n; ++d) {
+      const float* s = src + 2 * d;
+      float rh = 0.f, rl = 0.f;
+      for (int j = 0; j < order; ++j) {
+        rh += hi[j] * s[j];
+        rl += lo[j] * s[j];
+      }
+      desthi[d] = rh;
+      destlo[d] = rl;
     }
-    desthi[d] = rh;
-    destlo[d] = rl;
+    for (; d < half; ++d) {
+      float rh = 0.f, rl = 0.f;
+      for (int j = 0; j < order; ++j) {
+        const float v = extended(src, n, 2 * d + j, ext);
+        rh += hi[j] * v;
+        rl += lo[j] * v;
+      }
+      desthi[d] = rh;
+      destlo[d] = rl;
+    }
+    return;
   }
-  for (; 2 * d < n; ++d) {
-    float rh = 0.f, rl = 0.f;
+  std::vector<float> full;
+  extend_signal(src, n, order, ext, &full);
+  const long m = (n + order + 1) / 2;
+  std::vector<float> even(m + 1, 0.f), odd(m + 1, 0.f);
+  for (long k = 0; 2 * k < n + order; ++k) even[k] = full[2 * k];
+  for (long k = 0; 2 * k + 1 < n + order; ++k) odd[k] = full[2 * k + 1];
+  constexpr long kBlock = 2048;     // outputs per block: the two accumulator rows stay in L1 across the tap sweeps
+  for (long d0 = 0; d0 < half; d0 += kBlock) {
+    const long nb = (half - d0 < kBlock) ? half - d0 : kBlock;
+    float* ph = desthi + d0;
+    float* pl = destlo + d0;
+    for (long d = 0; d < nb; ++d) ph[d] = pl[d] = 0.f;
     for (int j = 0; j < order; ++j) {
-      const float v = extended(src, n, 2 * d + j, ext);
-      rh += hi[j] * v;
-      rl += lo[j] * v;
+      // ext[2 d + j] = even[d + j / 2] (j even) or odd[d + (j - 1) / 2] (j odd)
+      const float* s = ((j & 1) ? odd.data() + (j - 1) / 2 : even.data() + j / 2) + d0;
+      const float th = hi[j], tl = lo[j];
+      for (long d = 0; d < nb; ++d) {
+        ph[d] += th * s[d];
+        pl[d] += tl * s[d];
+      }
     }
-    desthi[d] = rh;
-    destlo[d] = rl;
   }
 }
 
@@ -107,15 +142,22 @@ void vs_stationary_wavelet_apply_ex(int type, int order, int level, int ext, int
   if (vs_wavelet_filters(type, order, reference_scale, lo.data(), hi.data()) != 0 || level < 1) return;
   const long stride = 1L << (level - 1);     // taps are spread `stride` samples apart ("a trous")
   const long n = static_cast<long>(length);
-  for (long i = 0; i < n; ++i) {
-    float rh = 0.f, rl = 0.f;
+  std::vector<float> full;
+  extend_signal(src, n, static_cast<long>(order) * stride, ext, &full);
+  constexpr long kBlock = 2048;
+  for (long i0 = 0; i0 < n; i0 += kBlock) {
+    const long nb = (n - i0 < kBlock) ? n - i0 : kBlock;
+    float* ph = desthi + i0;
+    float* pl = destlo + i0;
+    for (long i = 0; i < nb; ++i) ph[i] = pl[i] = 0.f;
     for (int j = 0; j < order; ++j) {
-      const float v = extended(src, n, i + j * stride, ext);
-      rh += hi[j] * v;
-      rl += lo[j] * v;
+      const float* s = full.data() + j * stride + i0;
+      const float th = hi[j], tl = lo[j];
+      for (long i = 0; i < nb; ++i) {
+        ph[i] += th * s[i];
+        pl[i] += tl * s[i];
+      }
     }
-    desthi[i] = rh;
-    destlo[i] = rl;
   }
 }
 
