@@ -257,3 +257,37 @@ def test_stacked_recurrent_layers_and_sequence_outputs():
     l1b.run()
     assert np.allclose(l1.output.mem[:, :3], l1b.output.mem[:, :3]) and \
         not np.allclose(l1.output.mem[:, 3:], l1b.output.mem[:, 3:])
+
+
+def test_recurrent_workflow_snapshot_roundtrip(tmp_path):
+    """A workflow with an LSTM layer pickles (cell-state caches are not part of the snapshot) and resumes training."""
+    import numpy as np
+    from veles_b200 import prng
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.config import root
+    from veles_b200.dummy import DummyLauncher
+    from veles_b200.models import build_workflow
+    from veles_b200.snapshotter import SnapshotterToFile
+    root.common.disable.snapshotting = True
+    prng.get().seed(5)
+    wf = build_workflow("lstm_classifier", minibatch_size=32, n_train=128, n_valid=32, max_epochs=1)
+    wf.initialize(device=NumpyDevice())
+    wf.run()
+    snap = SnapshotterToFile(wf, directory=str(tmp_path), prefix="seq", compression="gz", time_interval=0)
+    snap.suffix = "e1"
+    snap.export()
+    w_before = wf.forwards[0].weights.mem.copy()
+    wf.launcher.stop()
+    back = SnapshotterToFile.import_(snap.destination)
+    assert back.restored_from_snapshot and back.forwards[0].np_cache_ is None
+    assert np.array_equal(back.forwards[0].weights.mem, w_before)
+    assert back.forwards[0].hidden_size == 128 and not back.forwards[0].return_sequences
+    launcher = DummyLauncher()
+    back.workflow = launcher
+    back.decision.max_epochs = 2
+    back.decision.complete <<= False
+    back.initialize(device=NumpyDevice())
+    back.run()
+    assert back.decision.epoch_metrics_history[-1]["epoch"] == 2
+    assert np.abs(back.forwards[0].weights.mem - w_before).max() > 0
+    launcher.stop()
