@@ -28,6 +28,17 @@ WANT = [
     ("space_to_depth_bf16", r"space_to_depth_kernel<__nv_bfloat16>"),
     ("im2col_rowtile", r"im2col_rowtile_kernel"),
     ("xorshift1024star", r"xorshift1024star_kernel"),
+    ("pool_fwd_3x3s2_max", r"pool_fwd_3x3s2_kernel<0>"),
+    ("pool_bwd_3x3s2", r"pool_bwd_3x3s2_kernel"),
+    ("lrn_forward_shfl_n5", r"lrn_forward_shfl_kernel<2, true>"),
+    ("lrn_backward_shfl_n5", r"lrn_backward_shfl_kernel<2, true>"),
+    ("space_to_depth_rows", r"space_to_depth_rows_kernel"),
+    ("col_sum_final", r"col_sum_final_kernel"),
+    ("lstm_cell_forward", r"lstm_cell_forward_kernel"),
+    ("lstm_cell_backward", r"lstm_cell_backward_kernel"),
+    ("sig_conv", r"sig_conv_kernel"),
+    ("sig_dwt", r"sig_dwt_kernel"),
+    ("sig_peaks_write", r"sig_peaks_write_kernel"),
 ]
 
 
@@ -46,7 +57,7 @@ def main():
         body = blocks[1 + hit[0]]
         lines = ["// %s" % dem[hit[0]], "// cuobjdump -sass veles_b200/lib/libveles_b200.so (sm_100a), encodings stripped"]
         for ln in body.split("\n"):
-            m = re.match(r"\s*/\*([0-9a-f]{4})\*/\s+(.*?);\s*/\*", ln)
+            m = re.match(r"\s*/\*([0-9a-f]{4,6})\*/\s+(.*?);\s*/\*", ln)
             if m:
                 lines.append("/*%s*/ %s ;" % (m.group(1), re.sub(r"\s+", " ", m.group(2))))
         with open(os.path.join(OUT, stem + ".sass"), "w") as f:
