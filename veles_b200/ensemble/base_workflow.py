@@ -72,6 +72,11 @@ class EnsembleManagerBase(Unit):
         tmp = tempfile.mkdtemp(prefix="veles_b200_ens_")
         result_path = os.path.join(tmp, "result.json")
         env = dict(os.environ)
+        # an evaluation is an independent single-process training run: it must not join the rank group this process
+        # may itself belong to (the CLI turns data parallel when it sees the torch.distributed variables)
+        for key in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT",
+                    "VELES_HEARTBEAT_FILE", "VELES_RANK_DEATH_STEP", "VELES_RANK_DEATH_PROBABILITY"):
+            env.pop(key, None)
         env.update(self.extra_env)
         env["PYTHONPATH"] = os.pathsep.join(filter(None, [os.path.dirname(os.path.dirname(os.path.dirname(
             os.path.abspath(__file__)))), env.get("PYTHONPATH", "")]))
