@@ -14,6 +14,7 @@ Weak scaling: the per-GPU minibatch is fixed, the global batch grows with N.
 
 ``--impl reference`` would run the unmodified reference from baseline/_ref; it cannot be
 installed here (see DESIGN.md "Reference arm"), so it prints an "unavailable" line.
+``--impl torch|nccl|ps_emulation`` are stand-in comparison arms (baseline/standins.py).
 ``--model cifar_convnet|wide_mlp_ae|mnist_mlp`` benchmarks the other BASELINE configs.
 """
 from __future__ import annotations
@@ -33,7 +34,14 @@ def parse():
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=5)
-    p.add_argument("--impl", default="veles_b200", choices=["veles_b200", "reference", "nccl"])
+    p.add_argument("--impl", default="veles_b200", choices=["veles_b200", "reference", "nccl", "torch", "ps_emulation"],
+                   help="veles_b200 (the product); reference (unavailable here); stand-ins: nccl = this engine with an "
+                        "NCCL all-reduce + separate GD kernel, torch = stock torch.nn/cuDNN/DDP, ps_emulation = the "
+                        "reference's ZeroMQ master-slave schedule around torch compute (baseline/standins.py)")
+    p.add_argument("--min-seconds", type=float, default=0.0,
+                   help="repeat the timed region (in whole multiples of --steps) until it has run this long: sustained "
+                        "clocks instead of a burst")
+    p.add_argument("--ps-async", action="store_true", help="ps_emulation: two jobs in flight per slave (--async-slave)")
     p.add_argument("--model", default="alexnet")
     p.add_argument("--batch", type=int, default=0, help="per-GPU minibatch (default: model's)")
     p.add_argument("--no-graph", action="store_true")
@@ -88,6 +96,31 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if args.impl in ("torch", "ps_emulation"):
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import standins
+        args.batch = args.batch or MODEL_CONFIGS[args.model]["minibatch"]
+
+        def _sync():
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+                torch.cuda.synchronize()
+
+        def _max(ms):
+            if world == 1:
+                return ms
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        fn = standins.run_torch if args.impl == "torch" else standins.run_ps_emulation
+        fn(args, world, rank, local_rank, _sync, _max, ClockSampler)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+    if world > 1:
         from veles_b200.parallel.dp import DataParallel
         dp = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
                           shard_master=not args.replicate_master, n_ctas=args.comm_ctas,
@@ -135,15 +168,22 @@ def main():
     # L2 policy: AlexNet streams far more than the 126 MB L2 per step; the small models would otherwise re-hit
     # their previous step's lines, so L2 is flushed (a 256 MB write) between steps and every step is timed on its own.
     flush_buf = None if args.model == "alexnet" else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    steps_timed = args.steps
+    trainer.read_loss()     # the evaluator's loss sum restarts here: `loss` below is the mean over the timed steps
     if flush_buf is None:
-        e0 = torch.cuda.Event(enable_timing=True)
-        e1 = torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(args.steps):
-            trainer.step_resident()
-        e1.record()
-        sync_all()
-        ms_total = max_over_ranks(e0.elapsed_time(e1))
+        ms_total, steps_timed = 0.0, 0
+        while True:
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(args.steps):
+                trainer.step_resident()
+            e1.record()
+            sync_all()
+            ms_total += max_over_ranks(e0.elapsed_time(e1))
+            steps_timed += args.steps
+            if ms_total >= args.min_seconds * 1000.0:
+                break
     else:
         evs = []
         for _ in range(args.steps):
@@ -156,8 +196,8 @@ def main():
         sync_all()
         ms_total = max_over_ranks(sum(a.elapsed_time(b) for a, b in evs))
     clocks = sampler.stop() if sampler is not None else None
-    loss_after = trainer.read_loss()
-    ms_per_step = ms_total / args.steps
+    loss_after = trainer.read_loss() / steps_timed
+    ms_per_step = ms_total / steps_timed
     value = world * B * 1000.0 / ms_per_step
     trainer.close()
     del trainer
@@ -212,10 +252,25 @@ def main():
         tr.close()
 
     if rank == 0:
+        # BASELINE.md publishes no throughput; the denominators are the stand-in arms measured on this pool
+        # (baseline/standin_numbers.json, written from profiles/bench records): stock torch.nn/cuDNN/DDP first
+        vs_baseline, vs_source = None, None
+        try:
+            with open(os.path.join(ROOT, "baseline", "standin_numbers.json")) as f:
+                rec = json.load(f).get(args.model, {}).get(str(world), {})
+            for arm in ("torch", "nccl", "ps_emulation"):
+                if rec.get(arm):
+                    vs_baseline = value / float(rec[arm])
+                    vs_source = "stand-in '%s' at %d GPU(s): %.0f images/s (not the reference; BASELINE.md section 3)" % (
+                        arm, world, float(rec[arm]))
+                    break
+        except (OSError, ValueError):
+            pass
         out = {
             "metric": "AlexNet images/sec" if args.model == "alexnet" else "%s samples/sec" % args.model,
-            "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "value": value, "unit": "images/s", "n_gpus": world, "steps": steps_timed, "warmup": max(args.warmup, 3) + 4,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": vs_baseline,
+            "vs_baseline_source": vs_source,
             "dtype": "bf16", "data": "synthetic",
             "config": {"model": args.model, "global_batch": world * B, "per_gpu_batch": B,
                        "input_shape": list(cfg["sample_shape"]),
@@ -231,7 +286,7 @@ def main():
                                      "dataset and streams activations >> 126 MB" if args.model == "alexnet" else
                                      "L2 flushed (256 MB write) between steps; each step timed with its own CUDA events"),
                        "precision": "bf16 operands/activations, fp32 accumulate, fp32 master weights"},
-            "impl": args.impl, "gpu_launches": int(launches_per_step * args.steps),
+            "impl": args.impl, "gpu_launches": int(launches_per_step * steps_timed),
             "launches_per_step": int(launches_per_step), "clocks": clocks, "e2e": e2e, "loss": loss_after,
         }
         print(json.dumps(out))

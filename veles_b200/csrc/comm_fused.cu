@@ -23,16 +23,23 @@
 // not have entered this epoch otherwise).
 #include "common.cuh"
 
+#include <cstring>
+
 namespace vb {
 
 constexpr int MAX_WORLD = 8;
-constexpr int MAX_SEGS = 8;
+constexpr int MAX_SEGS = 16;
+constexpr int FUSED_THREADS = 512;   // x <= 128 registers = one SM's register file per CTA
+constexpr int SEG_ZERO_OTHER = 1;    // this segment's gradient GEMMs accumulate: clear the other parity's buffer
+constexpr int SEG_BCAST_MASTER = 2;  // the forward pass reads this segment's fp32 master (bias; tf32 layers): always
+                                     // publish the updated fp32 values to every rank, even with a sharded master
 
 struct FusedSeg {
   long long offset;         // element offset into the flat fp32 slabs
   long long numel;
   long long shadow_offset;  // element offset into the bf16 shadow slab, -1 = no shadow
   int row_len, row_pitch;   // shadow rows: element i -> shadow[(i / row_len) * row_pitch + i % row_len]
+  int flags;                // SEG_* bits
   float lr, wd, l12, moment;
 };
 
@@ -108,11 +115,16 @@ __device__ __forceinline__ bool wait_all(const FusedParams& p, int slot, uint32_
   return true;
 }
 
-// Footprint: 256 threads x <= 128 registers x 4 independent 16-byte chains, no shared memory.  (A 128-thread
-// variant sized to co-reside with a tcgen05 GEMM CTA was measured slower: 5.1 vs 4.2 ms/step on 4 GPUs - too few
-// loads in flight per CTA for the NVLink round trip.)
+// Footprint: FEW CTAs (4-8, launched as 2-CTA clusters so that each pair takes exactly one TPC) of 512 threads x <= 128
+// registers x 8 independent 16-byte chains, no shared memory.  While a launch of this kernel is pending the GEMMs of
+// the backward pass size their persistent grids to the remaining SMs (vb_set_sm_reserve), so the exchange runs
+// BESIDE the backward GEMMs instead of taking turns with them: a tcgen05 GEMM CTA owns its SM (227 KB of shared
+// memory, 54 K registers), and a full-width launch of either kernel simply waits for the other's CTAs to drain.
+// Bytes in flight per SM are bounded by the register file (64 KB of loads = 512 x 8 x 16 B), i.e. ~25 GB/s per CTA
+// at the ~2.5 us NVLink round trip of multimem.ld_reduce: enough to hide AlexNet's 244 MB / world behind the
+// convolution backward pass.  (Round 1 used 64-96 CTAs of 256 threads per LAYER: 0.4-0.5 ms per step exposed.)
 template <bool MULTIMEM>
-__global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedParams p) {
+__global__ void __launch_bounds__(FUSED_THREADS, 1) fused_allreduce_gd_kernel(const FusedParams p) {
   const int ready_slot = (p.channel * 2 + 0) * MAX_WORLD;
   const int done_slot = (p.channel * 2 + 1) * MAX_WORLD;
   // identical in every CTA: epochs[] is bumped by the LAST CTA to finish, i.e. after every CTA has read it here
@@ -140,8 +152,9 @@ __global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedPara
     const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
     for (int si = 0; si < p.nseg; ++si) {
       const FusedSeg s = p.seg[si];
-      // zero the other parity's local gradients of this segment (everybody is done reading them)
-      if (p.grads_other_local != nullptr) {
+      // zero the other parity's local gradients of this segment (everybody is done reading them); only segments
+      // whose gradient kernels accumulate (split-K reduce-add, column sums) need it - plainly stored ones do not
+      if (p.grads_other_local != nullptr && (s.flags & SEG_ZERO_OTHER)) {
         float* z = p.grads_other_local + s.offset;
         const long long n4 = s.numel >> 2;
         for (long long i = tid; i < n4; i += nthreads) reinterpret_cast<float4*>(z)[i] = make_float4(0, 0, 0, 0);
@@ -154,11 +167,12 @@ __global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedPara
       const long long hi = min(s.numel, lo + chunk);
       const long long n4 = (hi - lo) >> 2;  // lo is a multiple of 4 and offset is 64-element aligned
       const bool flat_shadow = s.shadow_offset >= 0 && s.row_len == s.row_pitch;
+      const bool bcast_master = p.bcast_master || (s.flags & SEG_BCAST_MASTER);
       // UNROLL independent 16-byte chains per thread: the NVLink round trip of multimem.ld_reduce is
       // several microseconds, so bandwidth needs many loads in flight per SM, not many SMs.
-      constexpr int UNROLL = 4;
+      constexpr int UNROLL = 8;
       for (long long b4 = tid; b4 < n4; b4 += nthreads * UNROLL) {
-        float4 g[UNROLL], w[UNROLL], v[UNROLL];
+        float4 g[UNROLL];
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
           const long long i4 = b4 + u * nthreads;
@@ -184,53 +198,59 @@ __global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedPara
             }
           }
         }
+        // weights / momentum are local (short latency): two half batches keep the live registers under 128
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) {
-          const long long i4 = b4 + u * nthreads;
-          if (i4 < n4) {
-            const long long gi = s.offset + lo + (i4 << 2);
-            w[u] = *reinterpret_cast<const float4*>(p.weights_local + gi);
-            v[u] = *reinterpret_cast<const float4*>(p.vel_local + gi);
-          }
-        }
+        for (int h = 0; h < UNROLL; h += UNROLL / 2) {
+          float4 w[UNROLL / 2], v[UNROLL / 2];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) {
-          const long long i4 = b4 + u * nthreads;
-          if (i4 >= n4) continue;
-          const long long i = lo + (i4 << 2);
-          const long long gi = s.offset + i;
-          float4 wv4 = w[u], vv = v[u];
-          wv4.x = gd_apply(wv4.x, g[u].x, vv.x, s, p.grad_scale);
-          wv4.y = gd_apply(wv4.y, g[u].y, vv.y, s, p.grad_scale);
-          wv4.z = gd_apply(wv4.z, g[u].z, vv.z, s, p.grad_scale);
-          wv4.w = gd_apply(wv4.w, g[u].w, vv.w, s, p.grad_scale);
-          *reinterpret_cast<float4*>(p.vel_local + gi) = vv;
-          if (!p.bcast_master) {
-            *reinterpret_cast<float4*>(p.weights_local + gi) = wv4;
-          } else if (MULTIMEM) {
-            mc_st_f32x4(p.weights_mc + gi, wv4);
-          } else {
-            for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = wv4;
+          for (int u = 0; u < UNROLL / 2; ++u) {
+            const long long i4 = b4 + (h + u) * nthreads;
+            if (i4 < n4) {
+              const long long gi = s.offset + lo + (i4 << 2);
+              w[u] = *reinterpret_cast<const float4*>(p.weights_local + gi);
+              v[u] = *reinterpret_cast<const float4*>(p.vel_local + gi);
+            }
           }
-          if (s.shadow_offset >= 0) {
-            const uint32_t b0 = pack_bf16x2(wv4.x, wv4.y), b1 = pack_bf16x2(wv4.z, wv4.w);
-            if (flat_shadow) {
-              const long long so = s.shadow_offset + i;
-              if (!p.bcast_shadow) {
-                *reinterpret_cast<uint2*>(p.shadow_local + so) = make_uint2(b0, b1);
-              } else if (MULTIMEM) {
-                mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
-              } else {
-                for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
-              }
+#pragma unroll
+          for (int u = 0; u < UNROLL / 2; ++u) {
+            const long long i4 = b4 + (h + u) * nthreads;
+            if (i4 >= n4) continue;
+            const long long i = lo + (i4 << 2);
+            const long long gi = s.offset + i;
+            float4 wv4 = w[u], vv = v[u];
+            const float4 gg = g[h + u];
+            wv4.x = gd_apply(wv4.x, gg.x, vv.x, s, p.grad_scale);
+            wv4.y = gd_apply(wv4.y, gg.y, vv.y, s, p.grad_scale);
+            wv4.z = gd_apply(wv4.z, gg.z, vv.z, s, p.grad_scale);
+            wv4.w = gd_apply(wv4.w, gg.w, vv.w, s, p.grad_scale);
+            *reinterpret_cast<float4*>(p.vel_local + gi) = vv;
+            if (!bcast_master) {
+              *reinterpret_cast<float4*>(p.weights_local + gi) = wv4;
+            } else if (MULTIMEM) {
+              mc_st_f32x4(p.weights_mc + gi, wv4);
             } else {
-              const float wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
+              for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = wv4;
+            }
+            if (s.shadow_offset >= 0) {
+              const uint32_t b0 = pack_bf16x2(wv4.x, wv4.y), b1 = pack_bf16x2(wv4.z, wv4.w);
+              if (flat_shadow) {
+                const long long so = s.shadow_offset + i;
+                if (!p.bcast_shadow) {
+                  *reinterpret_cast<uint2*>(p.shadow_local + so) = make_uint2(b0, b1);
+                } else if (MULTIMEM) {
+                  mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
+                } else {
+                  for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
+                }
+              } else {
+                const float wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
 #pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const long long e = i + q;
-                const long long so = s.shadow_offset + (e / s.row_len) * s.row_pitch + (e % s.row_len);
-                const __nv_bfloat16 bq = __float2bfloat16(wv[q]);
-                for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = bq;  // P2P scalar stores (tiny layers only)
+                for (int q = 0; q < 4; ++q) {
+                  const long long e = i + q;
+                  const long long so = s.shadow_offset + (e / s.row_len) * s.row_pitch + (e % s.row_len);
+                  const __nv_bfloat16 bq = __float2bfloat16(wv[q]);
+                  for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = bq;  // P2P scalar stores (tiny layers only)
+                }
               }
             }
           }
@@ -245,7 +265,7 @@ __global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedPara
         float v = p.vel_local[gi];
         const float w = gd_apply(p.weights_local[gi], g, v, s, p.grad_scale);
         p.vel_local[gi] = v;
-        if (!p.bcast_master) p.weights_local[gi] = w;
+        if (!bcast_master) p.weights_local[gi] = w;
         else
           for (int r = 0; r < p.world; ++r) p.weights_peer[r][gi] = w;
         if (s.shadow_offset >= 0) {
@@ -280,7 +300,8 @@ __global__ void __launch_bounds__(256) fused_allreduce_gd_kernel(const FusedPara
 using namespace vb;
 
 // Host ABI: all arrays are passed flat so that ctypes callers need no struct mirror.
-//   segs: nseg x {offset, numel, shadow_offset, row_len, row_pitch} as long long[5]
+//   segs: nseg x {offset, numel, shadow_offset, row_len, row_pitch, flags} as long long[6]
+//         flags bit 0: zero the other parity's gradients of the segment; bit 1: always broadcast the fp32 master
 //   hyper: nseg x {lr, wd, l1_vs_l2, moment} as float[4]
 //   *_peer: world device pointers each
 //   use_multimem: bit 0 = NVLS multimem path; bit 1 = keep the fp32 master slice local (no broadcast);
@@ -303,11 +324,12 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   FusedParams p;
   p.world = world; p.rank = rank; p.nseg = nseg; p.channel = channel;
   for (int i = 0; i < nseg; ++i) {
-    p.seg[i].offset = segs[i * 5 + 0];
-    p.seg[i].numel = segs[i * 5 + 1];
-    p.seg[i].shadow_offset = segs[i * 5 + 2];
-    p.seg[i].row_len = static_cast<int>(segs[i * 5 + 3]);
-    p.seg[i].row_pitch = static_cast<int>(segs[i * 5 + 4]);
+    p.seg[i].offset = segs[i * 6 + 0];
+    p.seg[i].numel = segs[i * 6 + 1];
+    p.seg[i].shadow_offset = segs[i * 6 + 2];
+    p.seg[i].row_len = static_cast<int>(segs[i * 6 + 3]);
+    p.seg[i].row_pitch = static_cast<int>(segs[i * 6 + 4]);
+    p.seg[i].flags = static_cast<int>(segs[i * 6 + 5]);
     p.seg[i].lr = hyper[i * 4 + 0];
     p.seg[i].wd = hyper[i * 4 + 1];
     p.seg[i].l12 = hyper[i * 4 + 2];
@@ -332,7 +354,8 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   p.bcast_master = !local_master;
   p.bcast_shadow = !local_shadow;
   p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
-  if (n_ctas <= 0) n_ctas = 32;
+  if (n_ctas <= 0) n_ctas = 4;
+  n_ctas = (n_ctas + 1) & ~1;   // whole 2-CTA clusters: a pair occupies one TPC, so GEMM CTA pairs lose no extra SMs
   if (split_handshake) {
     p.phase = 1;
     fused_allreduce_gd_kernel<false><<<1, 32, 0, stream>>>(p);
@@ -341,10 +364,20 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   } else {
     p.phase = 0;
   }
-  if (use_multimem)
-    fused_allreduce_gd_kernel<true><<<n_ctas, 256, 0, stream>>>(p);
-  else
-    fused_allreduce_gd_kernel<false><<<n_ctas, 256, 0, stream>>>(p);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(n_ctas);
+  cfg.blockDim = dim3(FUSED_THREADS);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (use_multimem) VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, fused_allreduce_gd_kernel<true>, p));
+  else VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, fused_allreduce_gd_kernel<false>, p));
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

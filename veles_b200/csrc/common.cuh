@@ -42,6 +42,7 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
 
 int device_sm_count();
+int gemm_sm_count();   // device_sm_count() minus the SMs reserved for a pending exchange kernel (vb_set_sm_reserve)
 
 // ----------------------------------------------------------------------------
 // Device-side primitives

@@ -27,14 +27,16 @@ constexpr int HALO_EPI_BYTES = 8 * 4096;
 
 struct HaloParams {
   int B, OH, OW;         // output grid (err_input mode: the layer INPUT grid)
-  int P, R;              // lanes per image row, image rows per 128-row tile (R = 128 / P)
+  int P, R;              // lanes per image row, image rows per 128-row sub-tile (R = 128 / P)
   int kx, ky;            // taps
   int low_w, low_h;      // first input coordinate of output 0 = -(padding)   (err_input: -(k-1-padding))
   int flip;              // 1: weight tap of window offset (r, s) is (ky-1-r, kx-1-s)    (err_input)
   int cblocks, cg;       // 64-channel blocks of the walked tensor; weight-matrix columns per tap
+  int ksteps_last;       // 16-channel MMA steps that hold data in the LAST channel block (1..4): padding is not multiplied
   int N, n_blocks;       // output channels, N tiles
-  int tiles_per_img;     // ceil(OH / R)
+  int tiles_per_img;     // ceil(OH / (R * MT))
   int a_rows;            // (R + ky - 1) * P rows of 128 B per activation tile
+  int resident;          // 1: the layer's taps*cblocks weight tiles are loaded ONCE and stay in shared memory
   const float* bias;
   int act;
   const __nv_bfloat16* Z;  // optional [pixels, N] (pixel pitch ldz): D *= f'(Z)
@@ -53,32 +55,39 @@ __device__ __forceinline__ void halo_apply_deriv(float (&f)[32], const float (&y
   for (int j = 0; j < 32; ++j) f[j] *= act_deriv_from_output(ACT, y[j]);
 }
 
-template <int BN>
+// MT = 128-row sub-tiles per CTA tile (consecutive groups of R image rows): every weight tile that streams in is
+// used by MT accumulators, so the weight bytes per output halve with MT = 2.
+template <int BN, int MT>
 struct HaloSmem {
   static constexpr int B_BYTES = BN * 128;
-  static constexpr int BUDGET = 227 * 1024 - 2 * HALO_A_SLOT - HALO_EPI_BYTES - 2048;
-  static constexpr int B_STAGES = (BUDGET / B_BYTES) > 12 ? 12 : (BUDGET / B_BYTES);
-  static constexpr int TOTAL = 2 * HALO_A_SLOT + B_STAGES * B_BYTES + HALO_EPI_BYTES + 2048;
+  static constexpr int A_SLOTS = 2 * MT;   // double-buffered over channel blocks / tiles
+  static constexpr int BUDGET = 227 * 1024 - A_SLOTS * HALO_A_SLOT - HALO_EPI_BYTES - 2048;
+  static constexpr int B_STAGES = (BUDGET / B_BYTES) > 16 ? 16 : (BUDGET / B_BYTES);
+  static constexpr int TOTAL = A_SLOTS * HALO_A_SLOT + B_STAGES * B_BYTES + HALO_EPI_BYTES + 2048;
 };
 
 // B_MN = false: weights K-major [N, taps*cg] (forward).  B_MN = true: weights [K = kernels, taps*cg] read as
 // MN-major [k, n = input channel] tiles (err_input).
-template <int BN, bool B_MN>
+template <int BN, bool B_MN, int MT>
 __global__ void __launch_bounds__(HALO_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w,
                  const __grid_constant__ CUtensorMap tma_d, const HaloParams p) {
-  using S = HaloSmem<BN>;
+  using S = HaloSmem<BN, MT>;
   constexpr int B_STAGES = S::B_STAGES;
-  constexpr int TMEM_COLS = (2 * BN <= 64) ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512));
+  constexpr int A_SLOTS = S::A_SLOTS;
+  constexpr int ACC_STRIDE = (BN <= 64) ? 64 : (BN <= 128 ? 128 : 256);   // TMEM columns per accumulator
+  constexpr int TMEM_NEED = 2 * MT * ACC_STRIDE;
+  constexpr int TMEM_COLS = TMEM_NEED <= 64 ? 64 : (TMEM_NEED <= 128 ? 128 : (TMEM_NEED <= 256 ? 256 : 512));
+  static_assert(TMEM_NEED <= 512, "accumulators exceed tensor memory");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* a_smem = smem;                                   // 2 activation slots
-  uint8_t* b_smem = smem + 2 * HALO_A_SLOT;                 // weight ring
+  uint8_t* a_smem = smem;                                   // activation slots
+  uint8_t* b_smem = smem + A_SLOTS * HALO_A_SLOT;           // weight ring (or the resident weights)
   uint8_t* epi_smem = b_smem + B_STAGES * S::B_BYTES;       // 8 x 4 KB staging slabs (1024-aligned)
   uint64_t* a_full = reinterpret_cast<uint64_t*>(epi_smem + HALO_EPI_BYTES);
-  uint64_t* a_empty = a_full + 2;
-  uint64_t* b_full = a_empty + 2;
+  uint64_t* a_empty = a_full + A_SLOTS;
+  uint64_t* b_full = a_empty + A_SLOTS;
   uint64_t* b_empty = b_full + B_STAGES;
   uint64_t* tmem_full = b_empty + B_STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -91,9 +100,11 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     tma_prefetch_desc(&tma_x);
     tma_prefetch_desc(&tma_w);
     tma_prefetch_desc(&tma_d);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < A_SLOTS; ++s) {
       mbar_init(&a_full[s], 1);
       mbar_init(&a_empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
       mbar_init(&tmem_empty[s], 8);
     }
@@ -116,28 +127,34 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
-      int a_slot = 0, b_stage = 0;
-      uint32_t a_phase = 0, b_phase = 0;
+      int b_stage = 0, a_par = 0;
+      uint32_t b_phase = 0, a_phase_bits = 0;   // one phase bit per activation slot (sub-tiles can be skipped)
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const bool first = (tile == static_cast<int>(blockIdx.x));
         const int nb = tile % p.n_blocks;
         const int sp = tile / p.n_blocks;
         const int img = sp / p.tiles_per_img;
-        const int oh0 = (sp - img * p.tiles_per_img) * p.R;
+        const int oh0 = (sp - img * p.tiles_per_img) * (p.R * MT);
         for (int cb = 0; cb < p.cblocks; ++cb) {
-          mbar_wait(&a_empty[a_slot], a_phase ^ 1);
-          mbar_expect_tx(&a_full[a_slot], static_cast<uint32_t>(p.a_rows) * 128u);
-          tma_load_4d(a_smem + a_slot * HALO_A_SLOT, &tma_x, &a_full[a_slot], cb * 64, p.low_w, oh0 + p.low_h, img);
-          if (++a_slot == 2) {
-            a_slot = 0;
-            a_phase ^= 1;
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) {
+            if (oh0 + mt * p.R >= p.OH) continue;   // this sub-tile lies below the image
+            const int slot = a_par * MT + mt;
+            mbar_wait(&a_empty[slot], ((a_phase_bits >> slot) & 1u) ^ 1u);
+            a_phase_bits ^= 1u << slot;
+            mbar_expect_tx(&a_full[slot], static_cast<uint32_t>(p.a_rows) * 128u);
+            tma_load_4d(a_smem + slot * HALO_A_SLOT, &tma_x, &a_full[slot], cb * 64, p.low_w,
+                        oh0 + mt * p.R + p.low_h, img);
           }
+          a_par ^= 1;
+          if (p.resident && !first) continue;   // the weights are already in shared memory
           for (int tap = 0; tap < taps; ++tap) {
             int wtap = tap;
             if (p.flip) {
               const int r = tap / p.kx, s = tap - r * p.kx;
               wtap = (p.ky - 1 - r) * p.kx + (p.kx - 1 - s);
             }
-            mbar_wait(&b_empty[b_stage], b_phase ^ 1);
+            if (!p.resident) mbar_wait(&b_empty[b_stage], b_phase ^ 1);
             uint8_t* sb = b_smem + b_stage * S::B_BYTES;
             mbar_expect_tx(&b_full[b_stage], S::B_BYTES);
             if (!B_MN) {
@@ -157,37 +174,58 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc(/*BF16*/ 1, false, B_MN, 128, BN);
-    int a_slot = 0, b_stage = 0, acc = 0;
-    uint32_t a_phase = 0, b_phase = 0, acc_phase = 0;
+    int b_stage = 0, acc = 0, a_par = 0;
+    uint32_t b_phase = 0, acc_phase = 0, a_phase_bits = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const bool first = (tile == static_cast<int>(blockIdx.x));
+      const int nb = tile % p.n_blocks;
+      const int sp = tile / p.n_blocks;
+      const int img = sp / p.tiles_per_img;
+      const int oh0 = (sp - img * p.tiles_per_img) * (p.R * MT);
+      // only the columns that exist are multiplied (N = 48 of a 64-wide tile: a quarter of the MMA time saved)
+      int n_mma = p.N - nb * BN;
+      n_mma = (B_MN || n_mma >= BN) ? BN : ((n_mma + 15) & ~15);
+      const uint32_t idesc = make_idesc(/*BF16*/ 1, false, B_MN, 128, n_mma);
       mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
-      const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+      if (p.resident) b_stage = 0;
       for (int cb = 0; cb < p.cblocks; ++cb) {
-        mbar_wait(&a_full[a_slot], a_phase);
-        const uint32_t sa0 = smem_u32(a_smem + a_slot * HALO_A_SLOT);
+        const int ksteps = (cb == p.cblocks - 1) ? p.ksteps_last : 4;
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          if (oh0 + mt * p.R >= p.OH) continue;
+          const int slot = a_par * MT + mt;
+          mbar_wait(&a_full[slot], (a_phase_bits >> slot) & 1u);
+          a_phase_bits ^= 1u << slot;
+        }
         for (int tap = 0; tap < taps; ++tap) {
-          mbar_wait(&b_full[b_stage], b_phase);
+          if (!p.resident || first) mbar_wait(&b_full[b_stage], b_phase);
           tc_fence_after();
           if (elect_one()) {
             const int r = tap / p.kx, s = tap - r * p.kx;
-            // the tap's 128-row window of the halo tile: (r*P + s) rows further down
-            const uint32_t sa = sa0 + static_cast<uint32_t>(r * p.P + s) * 128u;
             const uint32_t sb = smem_u32(b_smem + b_stage * S::B_BYTES);
             const uint64_t b_desc0 = B_MN ? make_smem_desc_sw128(sb, 8192, 1024) : make_smem_desc_sw128(sb, 16, 1024);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              // plain SWIZZLE_128B descriptor (base-offset field 0): the swizzle is a function of the absolute
-              // shared-memory address, so a window shifted by whole rows reads exactly what TMA wrote (measured:
-              // setting the base-offset field to the row phase gives wrong products)
-              const uint64_t a_desc = make_smem_desc_sw128(sa + k * 32, 16, 1024);
-              const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * 2048 : k * 32) >> 4);
-              umma_f16(d_tmem, a_desc, b_desc, idesc, (cb > 0 || tap > 0 || k > 0) ? 1u : 0u);
+            for (int mt = 0; mt < MT; ++mt) {
+              if (oh0 + mt * p.R >= p.OH) continue;
+              // the tap's 128-row window of the halo tile: (r*P + s) rows further down.  Plain SWIZZLE_128B descriptor
+              // (base-offset field 0): the swizzle is a function of the absolute shared-memory address, so a window
+              // shifted by whole rows reads exactly what TMA wrote (measured: setting the base-offset field to the
+              // row phase gives wrong products)
+              const uint32_t sa = smem_u32(a_smem + (a_par * MT + mt) * HALO_A_SLOT) +
+                                  static_cast<uint32_t>(r * p.P + s) * 128u;
+              const uint32_t d_tmem = tmem_base + static_cast<uint32_t>((acc * MT + mt) * ACC_STRIDE);
+              for (int k = 0; k < ksteps; ++k) {
+                const uint64_t a_desc = make_smem_desc_sw128(sa + k * 32, 16, 1024);
+                const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * 2048 : k * 32) >> 4);
+                umma_f16(d_tmem, a_desc, b_desc, idesc, (cb > 0 || tap > 0 || k > 0) ? 1u : 0u);
+              }
             }
-            umma_commit(&b_empty[b_stage]);
+            if (!p.resident) umma_commit(&b_empty[b_stage]);
             if (tap == taps - 1) {
-              umma_commit(&a_empty[a_slot]);
+#pragma unroll
+              for (int mt = 0; mt < MT; ++mt)
+                if (oh0 + mt * p.R < p.OH) umma_commit(&a_empty[a_par * MT + mt]);
               if (cb == p.cblocks - 1) umma_commit(&tmem_full[acc]);
             }
           }
@@ -197,10 +235,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             b_phase ^= 1;
           }
         }
-        if (++a_slot == 2) {
-          a_slot = 0;
-          a_phase ^= 1;
-        }
+        a_par ^= 1;
       }
       if (++acc == 2) {
         acc = 0;
@@ -219,78 +254,107 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
       const int nb = tile % p.n_blocks;
       const int sp = tile / p.n_blocks;
       const int img = sp / p.tiles_per_img;
-      const int oh0 = (sp - img * p.tiles_per_img) * p.R;
-      // this lane's output pixel
-      const int m = quarter * 32 + lane;
-      const int r_loc = m / p.P;
-      const int w = m - r_loc * p.P;
-      const int oh = oh0 + r_loc;
-      const bool px_ok = (oh < p.OH) && (w < p.OW);
-      const long long pixel = (static_cast<long long>(img) * p.OH + oh) * p.OW + w;
-      // the warp's store box: lanes 0..31 = rows (w fastest, then image rows) starting here
-      const int box_w0 = (quarter * 32) % p.P;
-      const int box_h0 = oh0 + (quarter * 32) / p.P;
+      const int oh0 = (sp - img * p.tiles_per_img) * (p.R * MT);
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
 #pragma unroll 1
-      for (int c0 = ehalf * 64; c0 < BN; c0 += 128) {
-        const int col0 = nb * BN + c0;
-        if (col0 >= p.N) break;
-        if (lane == 0) tma_store_wait_read<0>();
-        __syncwarp();
+      for (int mt = 0; mt < MT; ++mt) {
+        const int ohs = oh0 + mt * p.R;
+        if (ohs >= p.OH) break;
+        // this lane's output pixel
+        const int m = quarter * 32 + lane;
+        const int r_loc = m / p.P;
+        const int w = m - r_loc * p.P;
+        const int oh = ohs + r_loc;
+        const bool px_ok = (oh < p.OH) && (w < p.OW);
+        const long long pixel = (static_cast<long long>(img) * p.OH + oh) * p.OW + w;
+        // the warp's store box: lanes 0..31 = rows (w fastest, then image rows) starting here
+        const int box_w0 = (quarter * 32) % p.P;
+        const int box_h0 = ohs + (quarter * 32) / p.P;
+        if (box_h0 >= p.OH) continue;   // warp-uniform: all of this warp's rows lie below the image
 #pragma unroll 1
-        for (int half = 0; half < 2; ++half) {
-          const int colh = col0 + half * 32;
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                            static_cast<uint32_t>(acc * BN + c0 + half * 32),
-                        v);
-          tmem_ld_wait();
-          float f[32];
+        for (int c0 = ehalf * 64; c0 < BN; c0 += 128) {
+          const int col0 = nb * BN + c0;
+          if (col0 >= p.N) break;
+          if (lane == 0) tma_store_wait_read<0>();
+          __syncwarp();
+#pragma unroll 1
+          for (int half = 0; half < 2; ++half) {
+            const int colh = col0 + half * 32;
+            const int nvalid = p.N - colh;   // may be <= 0 for the second half of the last slab
+            if (nvalid <= 0) break;          // never stored: the box is clipped at N
+            uint32_t v[32];
+            tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                              static_cast<uint32_t>((acc * MT + mt) * ACC_STRIDE + c0 + half * 32),
+                          v);
+            tmem_ld_wait();
+            float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-          const int nvalid = p.N - colh;   // may be <= 0 for the second half of the last slab
-          if (p.bias != nullptr) {
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+            if (p.bias != nullptr) {
+              const float* bp = p.bias + colh;
+              if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j < nvalid) f[j] += __ldg(p.bias + colh + j);
-          }
-          switch (p.act) {
-            case ACT_TANH: halo_apply_act<ACT_TANH>(f); break;
-            case ACT_SIGMOID: halo_apply_act<ACT_SIGMOID>(f); break;
-            case ACT_RELU: halo_apply_act<ACT_RELU>(f); break;
-            case ACT_STRICT_RELU: halo_apply_act<ACT_STRICT_RELU>(f); break;
-            default: break;
-          }
-          if (p.Z != nullptr && px_ok) {
-            const __nv_bfloat16* zrow = p.Z + pixel * p.ldz + colh;
-            float d[32];
+                for (int j = 0; j < 32; j += 4) {
+                  const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp + j));
+                  f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+                }
+              } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) d[j] = (j < nvalid) ? __bfloat162float(zrow[j]) : 0.0f;
-            switch (p.deriv) {
-              case ACT_TANH: halo_apply_deriv<ACT_TANH>(f, d); break;
-              case ACT_SIGMOID: halo_apply_deriv<ACT_SIGMOID>(f, d); break;
-              case ACT_RELU: halo_apply_deriv<ACT_RELU>(f, d); break;
-              case ACT_STRICT_RELU: halo_apply_deriv<ACT_STRICT_RELU>(f, d); break;
+                for (int j = 0; j < 32; ++j)
+                  if (j < nvalid) f[j] += __ldg(bp + j);
+              }
+            }
+            switch (p.act) {
+              case ACT_TANH: halo_apply_act<ACT_TANH>(f); break;
+              case ACT_SIGMOID: halo_apply_act<ACT_SIGMOID>(f); break;
+              case ACT_RELU: halo_apply_act<ACT_RELU>(f); break;
+              case ACT_STRICT_RELU: halo_apply_act<ACT_STRICT_RELU>(f); break;
               default: break;
             }
-          }
+            if (p.Z != nullptr && px_ok) {
+              const __nv_bfloat16* zrow = p.Z + pixel * p.ldz + colh;
+              float d[32];
+              if (nvalid >= 32 && ((p.ldz & 7) == 0) && ((reinterpret_cast<uintptr_t>(zrow) & 15) == 0)) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint4 o;
-            o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
-            o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
-            o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
-            o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
-            *reinterpret_cast<uint4*>(srow + (((half * 4 + q) ^ (lane & 7)) << 4)) = o;
+                for (int j = 0; j < 32; j += 8) {
+                  const float4 z = *reinterpret_cast<const float4*>(zrow + j);
+                  const uint32_t* zu = reinterpret_cast<const uint32_t*>(&z);
+#pragma unroll
+                  for (int q = 0; q < 4; ++q) {
+                    d[j + 2 * q] = bf16_lo(zu[q]);
+                    d[j + 2 * q + 1] = bf16_hi(zu[q]);
+                  }
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) d[j] = (j < nvalid) ? __bfloat162float(zrow[j]) : 0.0f;
+              }
+              switch (p.deriv) {
+                case ACT_TANH: halo_apply_deriv<ACT_TANH>(f, d); break;
+                case ACT_SIGMOID: halo_apply_deriv<ACT_SIGMOID>(f, d); break;
+                case ACT_RELU: halo_apply_deriv<ACT_RELU>(f, d); break;
+                case ACT_STRICT_RELU: halo_apply_deriv<ACT_STRICT_RELU>(f, d); break;
+                default: break;
+              }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint4 o;
+              o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]);
+              o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+              o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+              o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+              *reinterpret_cast<uint4*>(srow + (((half * 4 + q) ^ (lane & 7)) << 4)) = o;
+            }
           }
-        }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          // {64 channels, min(P,32) pixels, 32/min(P,32) image rows, 1 image}: clipped to N, OW, OH by the map
-          tma_store_4d(&tma_d, buf, col0, box_w0, box_h0, img);
-          tma_store_commit();
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            // {64 channels, min(P,32) pixels, 32/min(P,32) image rows, 1 image}: clipped to N, OW, OH by the map
+            tma_store_4d(&tma_d, buf, col0, box_w0, box_h0, img);
+            tma_store_commit();
+          }
         }
       }
       tc_fence_before();
@@ -360,27 +424,50 @@ static int halo_tmap_4d(CUtensorMap* out, const void* base, int C, int W, int H,
 int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long long outer, long long pitch_elems,
                       int box_inner, int box_outer);   // gemm_tcgen05.cu
 
-template <int BN, bool B_MN>
+template <int BN, bool B_MN, int MT>
 static int launch_halo(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& td, const HaloParams& p,
                        cudaStream_t s) {
-  using S = HaloSmem<BN>;
-  auto kern = conv_halo_kernel<BN, B_MN>;
+  using S = HaloSmem<BN, MT>;
+  auto kern = conv_halo_kernel<BN, B_MN, MT>;
   static bool attr_set = false;
   if (!attr_set) {
     VB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
     attr_set = true;
   }
   const long long tiles = static_cast<long long>(p.B) * p.tiles_per_img * p.n_blocks;
-  const int sms = device_sm_count();
+  const int sms = gemm_sm_count();
   const int grid = static_cast<int>(tiles < sms ? tiles : sms);
   kern<<<grid, HALO_THREADS, S::TOTAL, s>>>(tx, tw, td, p);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
+template <int BN, bool B_MN>
+static int launch_halo_mt(int mt, const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& td,
+                          const HaloParams& p, cudaStream_t s) {
+  if (mt == 2) return launch_halo<BN, B_MN, 2>(tx, tw, td, p, s);
+  return launch_halo<BN, B_MN, 1>(tx, tw, td, p, s);
+}
+
 }  // namespace vb
 
 using namespace vb;
+
+// Tuning / test hook: sub-tiles per CTA tile (0 = choose, 1, 2) and whether small weight sets may stay resident in
+// shared memory (-1 = choose, 0 = never, 1 = whenever they fit).
+static int g_halo_mt = [] {
+  const char* e = getenv("VB_HALO_MT");
+  return e ? atoi(e) : 0;
+}();
+static int g_halo_resident = [] {
+  const char* e = getenv("VB_HALO_RESIDENT");
+  return e ? atoi(e) : -1;
+}();
+extern "C" int vb_conv_halo_set_options(int mt, int resident) {
+  g_halo_mt = (mt == 1 || mt == 2) ? mt : 0;
+  g_halo_resident = (resident == 0 || resident == 1) ? resident : -1;
+  return 0;
+}
 
 // mode 1 forward:   D[B,oH,oW,N]  = act(conv(T, W) + bias),  W = [N, ky*kx*cg] (row pitch ldw), T = [tB,tH,tW,t_ch]
 // mode 2 err_input: D[B,oH,oW,cg] = convT(T = dY, W) * f'(Z), W = [w_rows = t_ch kernels, ky*kx*cg]
@@ -404,11 +491,22 @@ extern "C" int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW
   p.B = tB; p.OH = oH; p.OW = oW; p.P = P; p.R = R; p.kx = kx; p.ky = ky; p.low_w = low_w; p.low_h = low_h;
   p.flip = (mode == 2) ? 1 : 0;
   p.cblocks = ceil_div(t_ch, 64); p.cg = cg; p.N = N;
-  p.tiles_per_img = ceil_div(oH, R);
+  p.ksteps_last = ceil_div(t_ch - (p.cblocks - 1) * 64, 16);
   p.a_rows = a_rows;
   p.bias = bias; p.act = act; p.Z = static_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv;
-  const int BN = (N <= 64) ? 64 : 128;
+  // tile width: the narrowest of 64 / 96 / 128 that holds N in one tile, else 128-wide tiles
+  const int BN = (N <= 64) ? 64 : ((N <= 96 && mode == 1) ? 96 : 128);
   p.n_blocks = ceil_div(N, BN);
+  // A layer whose whole weight set fits beside two activation slots keeps it in shared memory (AlexNet conv1 after
+  // space-to-depth: 9 taps x 96 kernels x 128 B = 108 KB): only activations stream.  Everything else streams weight
+  // tiles and shares each of them between two sub-tiles.
+  const int taps = kx * ky;
+  const int stages_mt1 = (227 * 1024 - 2 * HALO_A_SLOT - HALO_EPI_BYTES - 2048) / (BN * 128);
+  const bool fits = p.n_blocks == 1 && taps * p.cblocks <= (stages_mt1 > 16 ? 16 : stages_mt1);
+  p.resident = (g_halo_resident < 0 ? fits : (g_halo_resident && fits)) ? 1 : 0;
+  int mt = g_halo_mt ? g_halo_mt : (p.resident ? 1 : 2);
+  if (p.resident || oH <= R) mt = 1;
+  p.tiles_per_img = ceil_div(oH, R * mt);
   CUtensorMap tx, tw, td;
   int rc = halo_tmap_4d(&tx, T, t_ch, tW, tH, tB, t_pitch, 64, P, R + ky - 1);
   if (rc) return rc;
@@ -419,6 +517,11 @@ extern "C" int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW
   if (mode == 1) rc = make_tmap_bf16_2d(&tw, W, kk, w_rows, ldw, 64, BN);
   else rc = make_tmap_bf16_2d(&tw, W, kk, w_rows, ldw, 64, 64);
   if (rc) return rc;
-  if (mode == 1) return BN == 64 ? launch_halo<64, false>(tx, tw, td, p, stream) : launch_halo<128, false>(tx, tw, td, p, stream);
-  return BN == 64 ? launch_halo<64, true>(tx, tw, td, p, stream) : launch_halo<128, true>(tx, tw, td, p, stream);
+  if (mode == 1) {
+    if (BN == 64) return launch_halo_mt<64, false>(mt, tx, tw, td, p, stream);
+    if (BN == 96) return launch_halo<96, false, 1>(tx, tw, td, p, stream);   // resident / single sub-tile only
+    return launch_halo_mt<128, false>(mt, tx, tw, td, p, stream);
+  }
+  if (BN == 64) return launch_halo_mt<64, true>(mt, tx, tw, td, p, stream);
+  return launch_halo_mt<128, true>(mt, tx, tw, td, p, stream);
 }

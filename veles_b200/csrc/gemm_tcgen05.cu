@@ -79,6 +79,7 @@ struct GemmParams {
   float alpha;
   int split_k;
   int dyn_sched;      // 1: tiles are handed out by cluster launch control (grid = one CTA / pair per tile)
+  int ablate;         // profiling only (vb_gemm_set_ablation): 1 no A loads, 2 no B loads, 4 no MMAs, 8 no epilogue body
   int tma_store;      // 1: epilogue goes through smem + TMA store / reduce-add (tma_d valid)
   int m_blocks, n_blocks, k_blocks;
   // Fused gradient-descent epilogue (gd_w != null): the accumulator tile IS the weight gradient; instead of storing
@@ -277,12 +278,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           uint8_t* sb = sa + L::A_BYTES;
           // completion lands on the leader's barrier, armed for the bytes of both CTAs
           const uint32_t fb = PAIR ? mapa_u32(&full_bar[stage], 0) : smem_u32(&full_bar[stage]);
-          if (leader) mbar_expect_tx(&full_bar[stage], (PAIR ? 2 : 1) * L::STAGE_BYTES);
+          const bool no_a = (p.ablate & 1) != 0, no_b = (p.ablate & 2) != 0;
+          if (leader)
+            mbar_expect_tx(&full_bar[stage], (PAIR ? 2 : 1) * ((no_a ? 0 : L::A_BYTES) + (no_b ? 0 : L::B_BYTES)));
           auto ld2 = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
+            if (static_cast<uint8_t*>(dst) < sb ? no_a : no_b) return;
             if (PAIR) tma_load_2d_pair(dst, m, fb, c0, c1);
             else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
           };
           auto ldi = [&](void* dst, const CUtensorMap* m, int c, int w, int h, int n, int wo, int ho) {
+            if (static_cast<uint8_t*>(dst) < sb ? no_a : no_b) return;
             if (PAIR) tma_load_im2col_4d_pair(dst, m, fb, c, w, h, n, static_cast<uint16_t>(wo), static_cast<uint16_t>(ho));
             else tma_load_im2col_4d(dst, m, &full_bar[stage], c, w, h, n, static_cast<uint16_t>(wo), static_cast<uint16_t>(ho));
           };
@@ -393,6 +398,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((A_MN ? k * UK * 128 : k * 32) >> 4);
             const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * UK * 128 : k * 32) >> 4);
             const uint32_t accf = (kb > kb0 || k > 0) ? 1u : 0u;
+            if (p.ablate & 4) continue;
             if (TF32) {
               if (PAIR) umma_tf32_pair(d_tmem, a_desc, b_desc, idesc, accf);
               else umma_tf32(d_tmem, a_desc, b_desc, idesc, accf);
@@ -448,7 +454,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
         const int col0 = nb * BN + c0;
-        if (col0 >= p.N) break;  // warp-uniform
+        if (col0 >= p.N || (p.ablate & 8)) break;  // warp-uniform
         // slab ownership: 32-column fp32 slabs / 64-column bf16 slab pairs alternate between the two warps
         if ((((p.out_fp32 && p.tma_store) ? (c0 >> 5) : (c0 >> 6)) & 1) != ehalf) continue;
         int dcol0 = col0;          // first column of this slab in D
@@ -872,6 +878,12 @@ static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUt
 using namespace vb;
 
 static int g_disable_tma_store = 0;
+static int g_ablate = 0;
+// Profiling hook: switches parts of the kernel off (results are then garbage) to see which resource bounds a shape.
+extern "C" int vb_gemm_set_ablation(int mask) {
+  g_ablate = mask;
+  return 0;
+}
 // Test hook: 1 forces the per-thread store epilogue so both paths stay covered.
 extern "C" int vb_gemm_set_direct_epilogue(int on) {
   g_disable_tma_store = on ? 1 : 0;
@@ -891,7 +903,7 @@ static int g_pair_mode = 0;  // 0 = choose by cost, 1 = never pair, 2 = pair whe
 
 static void choose_config(int M, int N, int k_blocks, bool can_split, bool auto_split, bool b_mn, int* bn_io,
                           int* split_io, int* pair_out) {
-  const int sms = device_sm_count();
+  const int sms = gemm_sm_count();
   static const int cands[4] = {64, 128, 192, 256};
   double best = 1e300;
   int best_bn = 128, best_split = 1, best_pair = 0;
@@ -947,7 +959,7 @@ static thread_local const GdRequest* g_gd_request = nullptr;
 // Builds the output tensor map (when D qualifies) and launches the right instantiation.
 static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtensorMap& tb, bool a_mn, bool b_mn,
                              int BN, int pair, cudaStream_t stream, int d_cols = -1, bool tf32 = false) {
-  const int sms = device_sm_count();
+  const int sms = gemm_sm_count();
   // Output through TMA whenever D satisfies the tensor-map alignment rules; otherwise the
   // epilogue falls back to per-thread global stores / atomics.
   CUtensorMap td;
@@ -968,6 +980,7 @@ static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtenso
   const long long tiles = static_cast<long long>(p.m_blocks) * p.n_blocks * p.split_k;
   // dynamic (cluster-launch-control) scheduling: one unit per tile in the grid, running units steal the rest
   p.dyn_sched = (g_dyn_sched && tiles < (1LL << 30)) ? 1 : 0;
+  p.ablate = g_ablate;
   if (pair) {
     const int units = sms / 2;
     const int grid = 2 * static_cast<int>((p.dyn_sched || tiles < units) ? tiles : units);
@@ -1181,7 +1194,7 @@ static int conv_gemm_impl(int mode, const void* T, int tB, int tH, int tW, long 
   p.cv.low_w = low_w; p.cv.low_h = low_h; p.cv.cblocks = cblocks; p.cv.cg = cg;
   p.D = D; p.ldd = ldd; p.bias = bias; p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.alpha = alpha;
-  const int sms = device_sm_count();
+  const int sms = gemm_sm_count();
   int n_virtual = N;
   if (mode == 3) {
     VB_REQUIRE(out_fp32, "vb_conv_gemm_bf16: the weight gradient is fp32");

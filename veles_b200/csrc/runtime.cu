@@ -28,7 +28,23 @@ int device_sm_count() {
   return cached[dev];
 }
 
+// SMs the persistent tcgen05 kernels may fill: all of them, minus the ones a pending data-parallel exchange kernel
+// runs on (vb_set_sm_reserve).  Read at launch (= graph capture) time.
+static int g_sm_reserve = 0;
+int gemm_sm_count() {
+  int n = (device_sm_count() - g_sm_reserve) & ~1;   // whole TPCs: CTA pairs take two SMs
+  return n < 2 ? 2 : n;
+}
+
 }  // namespace vb
+
+// Keep `n` SMs free of persistent GEMM CTAs from now on (0 = none): the fused all-reduce + update kernel of the
+// data-parallel group runs on them beside the backward pass.  Returns the previous value.
+extern "C" int vb_set_sm_reserve(int n) {
+  const int prev = vb::g_sm_reserve;
+  vb::g_sm_reserve = n < 0 ? 0 : n;
+  return prev;
+}
 
 extern "C" const char* vb_last_error() { return vb::g_last_error; }
 

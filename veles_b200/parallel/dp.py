@@ -4,10 +4,13 @@ Every rank (one process per GPU) runs the identical workflow on its shard of eac
 minibatch.  What the reference did with a ZeroMQ parameter-server star — pickled weights down,
 pickled gradients up, merged by one Python master under a lock
 (``veles/server.py:141-169, 401-430``, ``veles/client.py:138-160``, ``veles/workflow.py:456-573``) —
-is ONE device kernel per layer here (``csrc/comm_fused.cu``): gradient all-reduce through NVLS
+is ONE device kernel per bucket of layers here (``csrc/comm_fused.cu``): gradient all-reduce through NVLS
 multicast (or P2P loads), the Znicz GD update in registers, and the updated fp32 weights + bf16
-shadow multicast-stored back to every rank, launched on a side stream as soon as the layer's
-backward GEMMs are enqueued so it overlaps the rest of the backward pass.
+shadow multicast-stored back to every rank.  Layers are bucketed in backward order (a bucket closes once it
+holds ``bucket_bytes`` of parameters: AlexNet = fc8 | fc7 | fc6 | conv5+conv4 | conv3+conv2 | conv1); a bucket's
+kernel is launched on a side stream as soon as its last layer's backward GEMMs are enqueued and runs on a few SMs
+that the backward GEMMs leave free for it (``vb_set_sm_reserve``), so the exchange overlaps the rest of the
+backward pass instead of taking turns with it.
 
 ``mode="nccl"`` is the conventional baseline (NCCL all-reduce, then the local GD kernel).
 ``mode="host"`` runs the same protocol for the numpy backend (gradients all-reduced as host arrays over whatever
@@ -24,13 +27,16 @@ from ctypes import c_double, c_float, c_int, c_longlong, c_void_p
 
 import numpy
 
-SYMMETRIC_KINDS = ("weights", "weights_bf16", "grads", "grads1", "dp_flags")
+SYMMETRIC_KINDS = ("weights", "weights_bf16", "grads", "grads1", "dp_flags", "velocity")
 MAX_WORLD = 8
+MAX_SEGS = 16          # csrc/comm_fused.cu
+SEG_ZERO_OTHER = 1     # the segment's gradient kernels accumulate: the update kernel clears the other parity's buffer
+SEG_BCAST_MASTER = 2   # forward passes read this segment's fp32 master: always publish it to every rank
 
 
 class DataParallel(object):
     def __init__(self, mode="fused", n_ctas=None, timeout_s=20.0, use_multimem=None, shard_master=True,
-                 weight_delivery="multicast", split_handshake=False):
+                 weight_delivery="multicast", split_handshake=False, bucket_bytes=4 << 20):
         import torch
         import torch.distributed as dist
         if not dist.is_initialized():
@@ -40,10 +46,15 @@ class DataParallel(object):
         self.world_size = dist.get_world_size()
         if self.world_size > MAX_WORLD:
             raise ValueError("the fused kernel supports at most %d ranks" % MAX_WORLD)
-        # CTAs of the update kernel: each rank reduces 1/world of every layer, so two ranks move twice the bytes per
-        # rank that four do and want more loads in flight (measured, AlexNet: 2 GPUs 3.60 / 3.46 ms with 64 / 96 CTAs;
-        # 4 GPUs 3.94 / 4.12 ms with 64 / 128)
-        self.n_ctas = int(n_ctas) if n_ctas else (96 if self.world_size <= 2 else 64)
+        # CTAs of the update kernel = SMs the backward GEMMs leave free while an exchange is pending.  Each rank
+        # reduces 1/world of every layer, so two ranks move twice the bytes per rank that four do: 8 SMs (~200 GB/s
+        # of multimem.ld_reduce at ~64 KB in flight per SM) for 2 ranks, 4 SMs beyond.
+        self.n_ctas = int(n_ctas) if n_ctas else (8 if self.world_size <= 2 else 4)
+        self.n_ctas = max(2, (self.n_ctas + 1) & ~1)
+        self.bucket_bytes = int(bucket_bytes)
+        self.buckets = []          # launch units: lists of GD units exchanged by one kernel, in backward order
+        self.bucket_of = {}
+        self._reserved = False
         self.auto_finish = False      # set by the launcher for graph-run workflows (FlatStep calls finish_step itself)
         self.last_unit = None         # the exchanged GD unit that runs last in a backward pass
         self.timeout_s = timeout_s
@@ -141,10 +152,38 @@ class DataParallel(object):
             self.handles[t.data_ptr()] = hdl
         if self.use_multimem is None:
             self.use_multimem = all(int(h.multicast_ptr) != 0 for h in self.handles.values())
-        for ch, gd in enumerate(self.units):
-            self.unit_info[id(gd)] = self._describe(ch, gd)
+        for gd in self.units:
+            self.unit_info[id(gd)] = self._describe(gd)
+        self._build_buckets()
         self._dist.barrier()
         torch.cuda.synchronize()
+
+    def _build_buckets(self):
+        """Group the exchanged units, in backward order, into launch buckets (one flag channel each)."""
+        self.buckets, self.bucket_of = [], {}
+        cur = None
+        for gd in reversed(self.units):          # wf.gds is in forward order: the backward pass meets them reversed
+            info = self.unit_info[id(gd)]
+            if (cur is None or cur["bytes"] >= self.bucket_bytes or cur["slab"] != info["slab"]
+                    or cur["shadow_slab"] != info["shadow_slab"] or len(cur["segs"]) + len(info["segs"]) > MAX_SEGS):
+                cur = {"channel": len(self.buckets), "units": [], "segs": [], "kinds": [], "bytes": 0,
+                       "slab": info["slab"], "shadow_slab": info["shadow_slab"], "pending": 0}
+                for key in ("grads", "weights", "shadow", "vel", "flags"):
+                    cur[key] = info[key]
+                self.buckets.append(cur)
+            cur["units"].append(gd)
+            cur["segs"] += info["segs"]
+            cur["kinds"] += [(gd, k) for k in info["kinds"]]
+            cur["bytes"] += 4 * sum(int(sg[1]) for sg in info["segs"])
+            cur["peer_shadow"] = cur.get("peer_shadow", False) or bool(info.get("peer_shadow"))
+            self.bucket_of[id(gd)] = cur
+        if len(self.buckets) > 64:
+            raise ValueError("at most 64 exchange buckets are supported by the flag layout")
+        for b in self.buckets:
+            # small buckets are latency-bound: two CTAs do; the reserve is sized for the largest launch
+            b["n_ctas"] = self.n_ctas if b["bytes"] >= (1 << 20) else 2
+            if b["peer_shadow"] and len(b["units"]) > 1:
+                raise ValueError("peer-TMA weight delivery needs one layer per bucket (bucket_bytes=0)")
 
     def _slab_ptrs(self, kind, idx):
         """(local base, multicast base or 0, [peer bases]) of slab ``idx`` of ``kind``."""
@@ -155,7 +194,7 @@ class DataParallel(object):
         mc = int(hdl.multicast_ptr)
         return t.data_ptr(), (mc + delta) if mc else 0, peers
 
-    def _describe(self, channel, gd):
+    def _describe(self, gd):
         import torch
         arena = self.arena
         fwd = gd.forward
@@ -178,7 +217,12 @@ class DataParallel(object):
                     pass
                 self._shadow_slab = sidx
                 shadow_off, row_len, row_pitch = soff // 2, sh.shape[1], sh.stride(0)
-            segs.append([off // 4, w.size, shadow_off, row_len, row_pitch])
+            flags = 0
+            if is_bias or not getattr(gd, "dw_store_", False):
+                flags |= SEG_ZERO_OTHER            # column sums / split-K weight gradients accumulate into the buffer
+            if shadow_off < 0 or (hasattr(gd, "tf32_mode") and gd.tf32_mode()):
+                flags |= SEG_BCAST_MASTER          # the forward pass reads the fp32 master of this segment
+            segs.append([off // 4, w.size, shadow_off, row_len, row_pitch, flags])
             hyper_keys.append("bias" if is_bias else "weights")
             if (not is_bias and shadow_off >= 0 and self.weight_delivery == "peer_tma" and row_len == row_pitch
                     and getattr(fwd, "PEER_WEIGHTS_OK", False) and not getattr(fwd, "weights_transposed", False)):
@@ -186,12 +230,8 @@ class DataParallel(object):
                 W = self.world_size
                 if n_rows % W == 0 and (n_rows // W) % 64 == 0 and (n_rows // W * row_len) % 4 == 0:
                     peer_shadow = (sidx, soff, n_rows // W)
-        info = {"channel": channel, "slab": slab_idx, "segs": segs, "kinds": hyper_keys,
+        info = {"slab": slab_idx, "segs": segs, "kinds": hyper_keys,
                 "shadow_slab": getattr(self, "_shadow_slab", 0)}
-        # CTAs of the update kernel scale with the layer: every CTA takes an SM's worth of registers away from the
-        # overlapped GEMMs for as long as it runs, and small layers are latency-, not bandwidth-bound
-        numel = sum(int(sg[1]) for sg in segs)
-        info["n_ctas"] = int(max(8, min(self.n_ctas, (numel + 131071) // 131072)))
         info["grads"] = [self._slab_ptrs("grads", slab_idx), self._slab_ptrs("grads1", slab_idx)]
         info["weights"] = self._slab_ptrs("weights", slab_idx)
         info["shadow"] = self._slab_ptrs("weights_bf16", info["shadow_slab"])
@@ -202,6 +242,7 @@ class DataParallel(object):
             fwd.peer_weights_ = ([p + soff for p in peers], shard_rows, self.rank)
             info["peer_shadow"] = True
         info["vel"] = arena.slabs["velocity"][slab_idx][0].data_ptr()
+        info["vel_symmetric"] = arena.slabs["velocity"][slab_idx][0].data_ptr() in self.handles
         fl_idx, fl_off = arena.locate(self.flags, "dp_flags")
         fl = self._slab_ptrs("dp_flags", fl_idx)
         info["flags"] = (fl[0] + fl_off, [p + fl_off for p in fl[2]])
@@ -252,27 +293,45 @@ class DataParallel(object):
             self.finish_step()
 
     def _update_fused(self, gd):
+        """The unit's gradients are enqueued on the current stream: note it, and launch its bucket's exchange kernel
+        once the bucket's last unit (in backward order) has reported."""
+        b = self.bucket_of[id(gd)]
+        b["pending"] += 1
+        self.master_stale = True      # at least the momentum now lives on its owners only
+        gd.weights.mark_device_written()
+        gd.gradient_weights_with_moment.mark_device_written()
+        if gd.bias is not None and gd.bias:
+            gd.bias.mark_device_written()
+            gd.gradient_bias_with_moment.mark_device_written()
+        if gd is b["units"][-1]:
+            self._launch_bucket(b)
+
+    def _launch_bucket(self, b):
         import torch
-        from ..ops import _lib
-        info = self.unit_info[id(gd)]
+        from ..ops import _lib, kernels
+        b["pending"] = 0
         main = torch.cuda.current_stream()
         ev = torch.cuda.Event()
         ev.record(main)
         self.comm_stream.wait_event(ev)
-        nseg = len(info["segs"])
-        segs = (c_longlong * (5 * nseg))(*[int(v) for s in info["segs"] for v in s])
+        if not self._reserved:
+            # GEMMs enqueued from here to finish_step leave n_ctas SMs to the exchange kernels
+            _lib.lib().vb_set_sm_reserve(c_int(self.n_ctas))
+            self._reserved = True
+        nseg = len(b["segs"])
+        segs = (c_longlong * (6 * nseg))(*[int(v) for s in b["segs"] for v in s])
         hyper = []
-        for kind in info["kinds"]:
+        for gd, kind in b["kinds"]:
             if kind == "weights":
                 hyper += [gd.learning_rate, gd.weights_decay, gd.l1_vs_l2, gd.gradient_moment]
             else:
                 hyper += [gd.learning_rate_bias, gd.weights_decay_bias, gd.l1_vs_l2_bias, gd.gradient_moment_bias]
         hyper = (c_float * (4 * nseg))(*hyper)
-        g_local, g_mc, g_peers = info["grads"][self.parity]
-        go_local = info["grads"][1 - self.parity][0]
-        w_local, w_mc, w_peers = info["weights"]
-        s_local, s_mc, s_peers = info["shadow"]
-        f_local, f_peers = info["flags"]
+        g_local, g_mc, g_peers = b["grads"][self.parity]
+        go_local = b["grads"][1 - self.parity][0]
+        w_local, w_mc, w_peers = b["weights"]
+        s_local, s_mc, s_peers = b["shadow"]
+        f_local, f_peers = b["flags"]
         W = self.world_size
 
         def arr(ptrs):
@@ -280,26 +339,21 @@ class DataParallel(object):
 
         with torch.cuda.stream(self.comm_stream):
             rc = _lib.lib().vb_fused_allreduce_gd(
-                c_int(W), c_int(self.rank), c_int(info["channel"]), c_int(nseg), segs, hyper,
+                c_int(W), c_int(self.rank), c_int(b["channel"]), c_int(nseg), segs, hyper,
                 c_void_p(g_local), c_void_p(g_mc), arr(g_peers), c_void_p(go_local),
-                c_void_p(w_local), c_void_p(w_mc), arr(w_peers), c_void_p(info["vel"]),
+                c_void_p(w_local), c_void_p(w_mc), arr(w_peers), c_void_p(b["vel"]),
                 c_void_p(s_local), c_void_p(s_mc), arr(s_peers), c_void_p(f_local), arr(f_peers),
                 c_void_p(self.epochs.data_ptr()), c_void_p(self.cta_counter.data_ptr()),
-                c_void_p(self.status.data_ptr()), c_float(self.grad_scale), c_int(info["n_ctas"]),
+                c_void_p(self.status.data_ptr()), c_float(self.grad_scale), c_int(b["n_ctas"]),
                 c_int((1 if self.use_multimem else 0) | (2 if self.shard_master else 0) |
-                      (4 if info.get("peer_shadow") else 0) | (8 if self.split_handshake else 0)),
+                      (4 if b.get("peer_shadow") else 0) | (8 if self.split_handshake else 0)),
                 c_double(self.timeout_s),
                 c_void_p(self.comm_stream.cuda_stream))
             _lib.check(rc, "vb_fused_allreduce_gd")
-            from ..ops import kernels
             kernels.LAUNCHES[0] += 2 if self.split_handshake else 1
             done = torch.cuda.Event()
             done.record(self.comm_stream)
         self._pending_events.append(done)
-        self.master_stale = self.shard_master
-        gd.weights.mark_device_written()
-        if gd.bias is not None and gd.bias:
-            gd.bias.mark_device_written()
 
     def allreduce_host(self, grad):
         """Host mode: sum a numpy gradient over the ranks (scaled like the device kernel scales it)."""
@@ -318,12 +372,20 @@ class DataParallel(object):
         if self.mode == "host":
             return
         import torch
+        if self.mode == "fused":
+            for b in self.buckets:        # a bucket whose closing unit did not run this step (gated off)
+                if b["pending"]:
+                    self._launch_bucket(b)
         main = torch.cuda.current_stream()
         for ev in self._pending_events:
             main.wait_event(ev)
         self._pending_events = []
         if self.mode == "fused":
             self.parity ^= 1
+            if self._reserved:
+                from ..ops import _lib
+                _lib.lib().vb_set_sm_reserve(c_int(0))
+                self._reserved = False
 
     def slice_bounds(self, numel, rank):
         """[lo, hi) of the flat segment that ``rank`` reduces and updates (same arithmetic as the kernel)."""
@@ -333,7 +395,7 @@ class DataParallel(object):
         return lo, min(numel, lo + chunk)
 
     def sync_master(self):
-        """Collective: reassemble the full fp32 master weights on every rank from the owners' slices
+        """Collective: reassemble the full fp32 master weights and momentum on every rank from the owners' slices
         (P2P copies out of the peers' symmetric slabs).  No-op unless ``shard_master`` left them stale."""
         import torch
         if self.mode != "fused" or not self.master_stale:
@@ -343,20 +405,26 @@ class DataParallel(object):
         self._dist.barrier()
         for gd in self.units:
             info = self.unit_info[id(gd)]
-            slab = self.arena.slabs["weights"][info["slab"]][0]
-            hdl = self.handles[slab.data_ptr()]
-            delta = slab.data_ptr() - int(hdl.buffer_ptrs[self.rank])
-            local = slab.view(torch.float32)
-            for seg in info["segs"]:
-                off, numel = int(seg[0]), int(seg[1])
-                for r in range(self.world_size):
-                    if r == self.rank:
-                        continue
-                    lo, hi = self.slice_bounds(numel, r)
-                    if hi <= lo:
-                        continue
-                    peer = hdl.get_buffer(r, (hi - lo,), torch.float32, delta // 4 + off + lo)
-                    local[off + lo:off + hi].copy_(peer)
+            # fp32 master weights, and the momentum each owner alone keeps (a snapshot written by rank 0 must carry
+            # all of it: a resumed or re-sharded run continues with the right velocity)
+            kinds = (["weights"] if self.shard_master else []) + (["velocity"] if info.get("vel_symmetric") else [])
+            for kind in kinds:
+                slab = self.arena.slabs[kind][info["slab"]][0]
+                hdl = self.handles[slab.data_ptr()]
+                delta = slab.data_ptr() - int(hdl.buffer_ptrs[self.rank])
+                local = slab.view(torch.float32)
+                for seg in info["segs"]:
+                    off, numel = int(seg[0]), int(seg[1])
+                    if kind == "weights" and (int(seg[5]) & SEG_BCAST_MASTER):
+                        continue               # already current on every rank
+                    for r in range(self.world_size):
+                        if r == self.rank:
+                            continue
+                        lo, hi = self.slice_bounds(numel, r)
+                        if hi <= lo:
+                            continue
+                        peer = hdl.get_buffer(r, (hi - lo,), torch.float32, delta // 4 + off + lo)
+                        local[off + lo:off + hi].copy_(peer)
         torch.cuda.synchronize()
         self._dist.barrier()
         self.master_stale = False
