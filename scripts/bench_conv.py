@@ -47,15 +47,19 @@ if __name__ == "__main__":
                 print(json.dumps(row), flush=True)
                 res.append(row)
         k.set_pair_mode(0)
-        row = dict(layer=name, kernel="halo")
-        for op, fn in (("fwd", lambda: k.conv_forward_halo(x, w, y, g, act=4)),
-                       ("dx", lambda: k.conv_err_input_halo(dy, w, dx, g))):
-            if fn():
-                t = timeit(fn, iters=5, warm=2)
-                row[op + "_us"] = round(t * 1e3, 1)
-                row[op + "_tflops"] = round(fl / t / 1e9, 1)
-        print(json.dumps(row), flush=True)
-        res.append(row)
+        for mt, resident in ((0, -1), (1, 0), (2, 0)):
+            k.conv_halo_set_options(mt, resident)
+            row = dict(layer=name, kernel="halo", mt=mt, resident=resident)
+            for op, fn in (("fwd", lambda: k.conv_forward_halo(x, w, y, g, act=4)),
+                           ("dx", lambda: k.conv_err_input_halo(dy, w, dx, g))):
+                if fn():
+                    t = timeit(fn, iters=5, warm=2)
+                    row[op + "_us"] = round(t * 1e3, 1)
+                    row[op + "_tflops"] = round(fl / t / 1e9, 1)
+            print(json.dumps(row), flush=True)
+            res.append(row)
+        k.conv_halo_set_options(0, -1)
     k.set_pair_mode(0)
-    os.makedirs("../gpurun_out", exist_ok=True)
-    json.dump(res, open("../gpurun_out/bench_conv.json", "w"), indent=1)
+    out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    os.makedirs(out_dir, exist_ok=True)
+    json.dump(res, open(os.path.join(out_dir, "bench_conv.json"), "w"), indent=1)

@@ -284,9 +284,18 @@ HALO_CASES = [
 ]
 
 
+@pytest.fixture(params=[(0, -1), (1, 0), (2, 0), (1, 1)], ids=["auto", "mt1_stream", "mt2_stream", "mt1_resident"])
+def halo_options(request):
+    k = K()
+    k.conv_halo_set_options(*request.param)
+    yield request.param
+    k.conv_halo_set_options(0, -1)
+
+
 @pytest.mark.parametrize("case", HALO_CASES)
-def test_halo_tile_conv_forward_and_err_input(case):
-    """Halo-tile kernel (all taps from one smem tile, shifted UMMA descriptors, 4-D TMA boxes) vs torch conv2d."""
+def test_halo_tile_conv_forward_and_err_input(case, halo_options):
+    """Halo-tile kernel (all taps from one smem tile, shifted UMMA descriptors, 4-D TMA boxes; one or two sub-tiles
+    per weight tile, streamed or resident weights) vs torch conv2d."""
     k = K()
     B, H, W, C, n, ky, kx, pt, pl, pb, pr, G = case
     torch.manual_seed(sum(case))

@@ -505,7 +505,7 @@ extern "C" int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW
   const bool fits = p.n_blocks == 1 && taps * p.cblocks <= (stages_mt1 > 16 ? 16 : stages_mt1);
   p.resident = (g_halo_resident < 0 ? fits : (g_halo_resident && fits)) ? 1 : 0;
   int mt = g_halo_mt ? g_halo_mt : (p.resident ? 1 : 2);
-  if (p.resident || oH <= R) mt = 1;
+  if (p.resident || oH <= R || BN == 96) mt = 1;   // 96-wide tiles exist for single sub-tiles only
   p.tiles_per_img = ceil_div(oH, R * mt);
   CUtensorMap tx, tw, td;
   int rc = halo_tmap_4d(&tx, T, t_ch, tW, tH, tB, t_pitch, 64, P, R + ky - 1);

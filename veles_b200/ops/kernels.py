@@ -293,6 +293,12 @@ def conv_err_input_grouped(dy4, w, dx2, g, groups, z=None, deriv=0, block_n=0):
                               deriv=deriv, block_n=block_n)
 
 
+def conv_halo_set_options(mt=0, resident=-1):
+    """Tuning / test hook of the halo-tile kernel: sub-tiles per CTA tile (0 = choose, 1, 2) and resident weights
+    (-1 = choose, 0 = never, 1 = whenever they fit)."""
+    _lib.check(_lib.lib().vb_conv_halo_set_options(c_int(mt), c_int(resident)), "vb_conv_halo_set_options")
+
+
 def _conv_halo(mode, t4, ky, kx, low_h, low_w, n_h, n_w, w, cg, out2, bias=None, act=ACT_LINEAR, z=None, deriv=0):
     """Halo-tile implicit GEMM (csrc/conv_halo.cu); returns False when the geometry is not supported."""
     B, H, W, C = t4.shape
