@@ -138,6 +138,29 @@ def test_blas_facade_column_major_sgemm():
 
 
 @pytest.mark.gpu
+def test_blas_facade_fp32_sgemm_is_tf32_and_dgemm_refuses():
+    import torch
+    from veles_b200.blas import BLAS, OP_N
+    torch.manual_seed(1)
+    m, n, k = 128, 192, 256
+    At = torch.randn(k, m, device="cuda")
+    Bt = torch.randn(n, k, device="cuda")
+    Ct = torch.zeros(n, m, device="cuda")
+    BLAS().sgemm(OP_N, OP_N, m, n, k, 1.0, At, Bt, 0.0, Ct)
+    ref = (At.t() @ Bt.t()).t()
+    err = ((Ct - ref).abs().max() / ref.abs().max()).item()
+    assert err < 2e-3            # tf32 products: ~1e-3; bf16 operands would sit near 1e-2 here
+    with pytest.raises(NotImplementedError):
+        BLAS().dgemm(OP_N, OP_N, m, n, k, 1.0, At.double(), Bt.double(), 0.0, Ct.double())
+
+
+def test_blas_dgemm_refuses_without_a_device():
+    from veles_b200.blas import BLAS
+    with pytest.raises(NotImplementedError):
+        BLAS().dgemm(0, 0, 1, 1, 1, 1.0, None, None, 0.0, None)
+
+
+@pytest.mark.gpu
 def test_sanitizer_smoke_program_runs():
     """The program compute-sanitizer is pointed at (scripts/sanitizer_smoke.py) must at least run clean on its own."""
     import runpy

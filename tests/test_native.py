@@ -52,6 +52,32 @@ def test_native_cpu_checks_and_package_loading(tmp_path):
     wf.launcher.stop()
 
 
+REF_FIXTURES = "/root/reference/libVeles/tests/workflow_files"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_FIXTURES), reason="the reference checkout is not on this machine")
+def test_native_loads_the_reference_fixtures():
+    """Format compatibility with the reference's own exported packages (libVeles/tests/workflow_files/mnist.zip and
+    mnist.tar.gz, read in place): the loader finds the MNIST workflow's two units and their four .npy members, the
+    planner sizes the arena, and the C API opens them."""
+    lib, test_bin = _build()
+    z, t = os.path.join(REF_FIXTURES, "mnist.zip"), os.path.join(REF_FIXTURES, "mnist.tar.gz")
+    r = subprocess.run([test_bin, z, t], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=120)
+    out = r.stdout.decode()
+    assert r.returncode == 0 and "0 failed" in out, out
+    assert out.count('workflow "MnistWorkflow", 2 units') == 2, out
+    assert "0001_100x784.npy" in out and "0003_10x100.npy" in out
+    L = _native(lib)
+    for path in (z, t):
+        h = L.veles_native_load(path.encode())
+        assert h, L.veles_native_last_error()
+        h = ctypes.c_void_p(h)
+        assert L.veles_native_unit_count(h) == 2
+        names = [L.veles_native_unit_name(h, i).decode() for i in range(2)]
+        assert "All2AllTanh" in names[0] and "All2AllSoftmax" in names[1], names
+        L.veles_native_free(h)
+
+
 def _native(lib_path):
     L = ctypes.CDLL(lib_path)
     L.veles_native_load.restype = ctypes.c_void_p

@@ -49,3 +49,12 @@ class VelesModule(_types.ModuleType):
 
 
 _sys.modules[__name__].__class__ = VelesModule
+
+
+# Workflows, configurations and snapshots written for the reference name its module paths (``veles.units``,
+# ``veles.znicz...``): alias them to this package unless a real ``veles`` distribution is importable.
+try:
+    from .compat import install_veles_alias as _install_veles_alias
+    _install_veles_alias()
+except Exception:   # pragma: no cover - the alias is a convenience, never a reason to fail the import
+    pass

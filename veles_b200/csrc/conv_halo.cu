@@ -124,11 +124,15 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
   const int taps = p.kx * p.ky;
   const int num_tiles = p.B * p.tiles_per_img * p.n_blocks;
 
+  // The two single-thread roles are bound by their own instruction streams (ncu source view): no divisions and no
+  // descriptor construction inside the tap loops - tap coordinates and descriptors advance by increments.
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       int b_stage = 0, a_par = 0;
       uint32_t b_phase = 0, a_phase_bits = 0;   // one phase bit per activation slot (sub-tiles can be skipped)
+      const int wtap_first = p.flip ? taps - 1 : 0;   // err_input walks the filter taps backwards
+      const int wtap_step = p.flip ? -1 : 1;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const bool first = (tile == static_cast<int>(blockIdx.x));
         const int nb = tile % p.n_blocks;
@@ -148,21 +152,19 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
           }
           a_par ^= 1;
           if (p.resident && !first) continue;   // the weights are already in shared memory
-          for (int tap = 0; tap < taps; ++tap) {
-            int wtap = tap;
-            if (p.flip) {
-              const int r = tap / p.kx, s = tap - r * p.kx;
-              wtap = (p.ky - 1 - r) * p.kx + (p.kx - 1 - s);
-            }
+          // weight column of window offset (r, s): tap (r, s), or the mirrored tap (ky-1-r, kx-1-s) = taps-1-tap
+          int wcol = wtap_first * p.cg + (B_MN ? nb * BN : cb * 64);
+          const int wcol_step = wtap_step * p.cg;
+          for (int tap = 0; tap < taps; ++tap, wcol += wcol_step) {
             if (!p.resident) mbar_wait(&b_empty[b_stage], b_phase ^ 1);
             uint8_t* sb = b_smem + b_stage * S::B_BYTES;
             mbar_expect_tx(&b_full[b_stage], S::B_BYTES);
             if (!B_MN) {
-              tma_load_2d(sb, &tma_w, &b_full[b_stage], wtap * p.cg + cb * 64, nb * BN);
+              tma_load_2d(sb, &tma_w, &b_full[b_stage], wcol, nb * BN);
             } else {
 #pragma unroll
               for (int c = 0; c < BN / 64; ++c)
-                tma_load_2d(sb + c * 8192, &tma_w, &b_full[b_stage], wtap * p.cg + nb * BN + c * 64, cb * 64);
+                tma_load_2d(sb + c * 8192, &tma_w, &b_full[b_stage], wcol + c * 64, cb * 64);
             }
             if (++b_stage == B_STAGES) {
               b_stage = 0;
@@ -173,75 +175,95 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    int b_stage = 0, acc = 0, a_par = 0;
-    uint32_t b_phase = 0, acc_phase = 0, a_phase_bits = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const bool first = (tile == static_cast<int>(blockIdx.x));
-      const int nb = tile % p.n_blocks;
-      const int sp = tile / p.n_blocks;
-      const int img = sp / p.tiles_per_img;
-      const int oh0 = (sp - img * p.tiles_per_img) * (p.R * MT);
-      // only the columns that exist are multiplied (N = 48 of a 64-wide tile: a quarter of the MMA time saved)
-      int n_mma = p.N - nb * BN;
-      n_mma = (B_MN || n_mma >= BN) ? BN : ((n_mma + 15) & ~15);
-      const uint32_t idesc = make_idesc(/*BF16*/ 1, false, B_MN, 128, n_mma);
-      mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
-      tc_fence_after();
-      if (p.resident) b_stage = 0;
-      for (int cb = 0; cb < p.cblocks; ++cb) {
-        const int ksteps = (cb == p.cblocks - 1) ? p.ksteps_last : 4;
+    // ===================== MMA issuer: ONE thread runs the whole loop =====================
+    if (elect_one()) {
+      int b_stage = 0, acc = 0, a_par = 0;
+      uint32_t b_phase = 0, acc_phase = 0, a_phase_bits = 0;
+      constexpr uint64_t B_STEP = static_cast<uint64_t>(S::B_BYTES >> 4);
+      constexpr uint64_t A_SLOT_STEP = static_cast<uint64_t>(HALO_A_SLOT >> 4);
+      constexpr uint64_t B_KSTEP = static_cast<uint64_t>((B_MN ? 2048 : 32) >> 4);
+      const uint64_t b_desc_s0 = B_MN ? make_smem_desc_sw128(smem_u32(b_smem), 8192, 1024)
+                                      : make_smem_desc_sw128(smem_u32(b_smem), 16, 1024);
+      // activation windows: plain SWIZZLE_128B descriptors (base-offset field 0) - the swizzle is a function of the
+      // absolute shared-memory address, so a window shifted by whole 128-byte rows reads exactly what TMA wrote
+      // (measured: setting the base-offset field to the row phase gives wrong products)
+      const uint64_t a_desc_s0 = make_smem_desc_sw128(smem_u32(a_smem), 16, 1024);
+      const uint64_t row_step = 128u >> 4;                                     // one lane (pixel) further
+      const uint64_t line_step = static_cast<uint64_t>((p.P - p.kx) * 8);      // from the last tap of a filter row to
+                                                                                // the first tap of the next one
+      uint64_t b_desc = b_desc_s0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const bool first = (tile == static_cast<int>(blockIdx.x));
+        const int nb = tile % p.n_blocks;
+        const int sp = tile / p.n_blocks;
+        const int img = sp / p.tiles_per_img;
+        const int oh0 = (sp - img * p.tiles_per_img) * (p.R * MT);
+        bool mt_ok[MT];
 #pragma unroll
-        for (int mt = 0; mt < MT; ++mt) {
-          if (oh0 + mt * p.R >= p.OH) continue;
-          const int slot = a_par * MT + mt;
-          mbar_wait(&a_full[slot], (a_phase_bits >> slot) & 1u);
-          a_phase_bits ^= 1u << slot;
+        for (int mt = 0; mt < MT; ++mt) mt_ok[mt] = oh0 + mt * p.R < p.OH;
+        // only the columns that exist are multiplied (N = 96 of a 128-wide tile: a quarter of the MMA time saved)
+        int n_mma = p.N - nb * BN;
+        n_mma = (B_MN || n_mma >= BN) ? BN : ((n_mma + 15) & ~15);
+        const uint32_t idesc = make_idesc(/*BF16*/ 1, false, B_MN, 128, n_mma);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        if (p.resident) {
+          b_stage = 0;
+          b_desc = b_desc_s0;
         }
-        for (int tap = 0; tap < taps; ++tap) {
-          if (!p.resident || first) mbar_wait(&b_full[b_stage], b_phase);
-          tc_fence_after();
-          if (elect_one()) {
-            const int r = tap / p.kx, s = tap - r * p.kx;
-            const uint32_t sb = smem_u32(b_smem + b_stage * S::B_BYTES);
-            const uint64_t b_desc0 = B_MN ? make_smem_desc_sw128(sb, 8192, 1024) : make_smem_desc_sw128(sb, 16, 1024);
+        uint32_t accf = 0u;
+        for (int cb = 0; cb < p.cblocks; ++cb) {
+          const int ksteps = (cb == p.cblocks - 1) ? p.ksteps_last : 4;
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) {
+            if (!mt_ok[mt]) continue;
+            const int slot = a_par * MT + mt;
+            mbar_wait(&a_full[slot], (a_phase_bits >> slot) & 1u);
+            a_phase_bits ^= 1u << slot;
+          }
+          uint64_t a_desc = a_desc_s0 + static_cast<uint64_t>(a_par * MT) * A_SLOT_STEP;   // window of tap (0, 0)
+          int s = 0;
+          for (int tap = 0; tap < taps; ++tap) {
+            if (!p.resident || first) mbar_wait(&b_full[b_stage], b_phase);
+            tc_fence_after();
 #pragma unroll
             for (int mt = 0; mt < MT; ++mt) {
-              if (oh0 + mt * p.R >= p.OH) continue;
-              // the tap's 128-row window of the halo tile: (r*P + s) rows further down.  Plain SWIZZLE_128B descriptor
-              // (base-offset field 0): the swizzle is a function of the absolute shared-memory address, so a window
-              // shifted by whole rows reads exactly what TMA wrote (measured: setting the base-offset field to the
-              // row phase gives wrong products)
-              const uint32_t sa = smem_u32(a_smem + (a_par * MT + mt) * HALO_A_SLOT) +
-                                  static_cast<uint32_t>(r * p.P + s) * 128u;
+              if (!mt_ok[mt]) continue;
               const uint32_t d_tmem = tmem_base + static_cast<uint32_t>((acc * MT + mt) * ACC_STRIDE);
-              for (int k = 0; k < ksteps; ++k) {
-                const uint64_t a_desc = make_smem_desc_sw128(sa + k * 32, 16, 1024);
-                const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * 2048 : k * 32) >> 4);
-                umma_f16(d_tmem, a_desc, b_desc, idesc, (cb > 0 || tap > 0 || k > 0) ? 1u : 0u);
-              }
+              const uint64_t ad = a_desc + mt * A_SLOT_STEP;
+              umma_f16(d_tmem, ad, b_desc, idesc, accf);
+              if (ksteps > 1) umma_f16(d_tmem, ad + 2, b_desc + B_KSTEP, idesc, 1u);
+              if (ksteps > 2) umma_f16(d_tmem, ad + 4, b_desc + 2 * B_KSTEP, idesc, 1u);
+              if (ksteps > 3) umma_f16(d_tmem, ad + 6, b_desc + 3 * B_KSTEP, idesc, 1u);
             }
+            accf = 1u;
             if (!p.resident) umma_commit(&b_empty[b_stage]);
-            if (tap == taps - 1) {
-#pragma unroll
-              for (int mt = 0; mt < MT; ++mt)
-                if (oh0 + mt * p.R < p.OH) umma_commit(&a_empty[a_par * MT + mt]);
-              if (cb == p.cblocks - 1) umma_commit(&tmem_full[acc]);
+            // next tap: one pixel to the right, or the start of the next filter row
+            a_desc += row_step;
+            if (++s == p.kx) {
+              s = 0;
+              a_desc += line_step;
+            }
+            b_desc += B_STEP;
+            if (++b_stage == B_STAGES) {
+              b_stage = 0;
+              b_phase ^= 1;
+              b_desc = b_desc_s0;
             }
           }
-          __syncwarp();
-          if (++b_stage == B_STAGES) {
-            b_stage = 0;
-            b_phase ^= 1;
-          }
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt)
+            if (mt_ok[mt]) umma_commit(&a_empty[a_par * MT + mt]);
+          a_par ^= 1;
         }
-        a_par ^= 1;
-      }
-      if (++acc == 2) {
-        acc = 0;
-        acc_phase ^= 1;
+        umma_commit(&tmem_full[acc]);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
       }
     }
+    __syncwarp();
   } else {
     // ===================== Epilogue (warps 2..9) =====================
     const int quarter = warp & 3;        // TMEM lanes [32*quarter, 32*quarter + 32)

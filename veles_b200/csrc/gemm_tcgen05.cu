@@ -49,6 +49,7 @@ struct ConvParams {
   int low_w, low_h;  // bounding-box lower corner (= -pad; -(k-1-pad) for mode 2)
   int cblocks;       // 64-channel blocks per tap along the im2col tensor's channel dimension
   int cg;            // weight-matrix columns per tap
+  int q64, r64;      // 64 / OW and 64 % OW: how the traversal position advances per 64-pixel k-block (mode 3)
   int nbpg;          // grouped convolution in one launch: N tiles per group (0 = not grouped); tile nb belongs to
                      // group nb / nbpg, whose im2col channels start at group * cblocks * 64
 };
@@ -79,7 +80,6 @@ struct GemmParams {
   float alpha;
   int split_k;
   int dyn_sched;      // 1: tiles are handed out by cluster launch control (grid = one CTA / pair per tile)
-  int ablate;         // profiling only (vb_gemm_set_ablation): 1 no A loads, 2 no B loads, 4 no MMAs, 8 no epilogue body
   int tma_store;      // 1: epilogue goes through smem + TMA store / reduce-add (tma_d valid)
   int m_blocks, n_blocks, k_blocks;
   // Fused gradient-descent epilogue (gd_w != null): the accumulator tile IS the weight gradient; instead of storing
@@ -246,12 +246,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     return ok ? static_cast<int>(PAIR ? (x >> 1) : x) : num_tiles;
   };
 
+  // Both single-thread roles below are bound by their own instruction stream, not by the units they feed (ncu
+  // source view, AlexNet conv2 forward: the producer thread spent its samples on the integer divisions that turned
+  // a k-block index into (tap, channel block, filter row) - ~115 dependent instructions per k-block = ~800 cycles
+  // for 256 cycles of tensor work).  So every per-k-block quantity is carried incrementally, and descriptors are
+  // built once and advanced by constants.
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      const int mode = p.cv.mode;
+      const int per_img = p.cv.OH * p.cv.OW;
       for (int tile = unit; tile < num_tiles; tile = sched_next(tile, it, true, false), ++it) {
         if (p.dyn_sched) sched_request(it);
         const int ks = tile / tiles_mn;
@@ -262,15 +269,48 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
         const int m_base = mb * TILE_M + static_cast<int>(cta_rank) * BLOCK_M;   // first A row staged here
         const int n_base = nb * BN + static_cast<int>(cta_rank) * BN_LOAD;       // first B row/column staged here
-        // im2col-mode A (modes 1, 2): first pixel of this CTA's rows in traversal coordinates
-        int a_w = 0, a_h = 0, a_n = 0;
-        if (p.cv.mode == 1 || p.cv.mode == 2) {
-          const int per_img = p.cv.OH * p.cv.OW;
+        // ---- per-tile set-up of the incremental walk (the only divisions of the producer) ----
+        int a_w = 0, a_h = 0, a_n = 0;       // modes 1, 2: first pixel of this CTA's rows in traversal coordinates
+        int cb = 0, tap_r = 0, tap_s = 0;    // modes 1, 2: channel block / filter row / filter column of k-block kb
+        int grp_c0 = 0, n_local = 0;
+        int p_img = 0, p_oh = 0, p_ow = 0;   // mode 3: image / row / column of the first pixel of k-block kb
+        int c_ch[4], c_wo[4], c_ho[4];       // mode 3: channel start and tap of each 64-column chunk staged here
+        if (mode == 1 || mode == 2) {
           a_n = m_base / per_img;
           const int rem = m_base - a_n * per_img;
           const int oh = rem / p.cv.OW;
           a_h = oh * p.cv.sy + p.cv.low_h;
           a_w = (rem - oh * p.cv.OW) * p.cv.sx + p.cv.low_w;
+          const int tap = kb0 / p.cv.cblocks;
+          cb = kb0 - tap * p.cv.cblocks;
+          tap_r = tap / p.cv.kx;
+          tap_s = tap - tap_r * p.cv.kx;
+          // grouped layers in one launch: this N tile's group selects the channel range of the walked tensor
+          const int grp = p.cv.nbpg > 0 ? nb / p.cv.nbpg : 0;
+          grp_c0 = grp * p.cv.cblocks * 64;
+          n_local = n_base - grp * p.cv.nbpg * BN;   // column inside the group's [kernels, taps*cg] slab
+        } else if (mode == 3) {
+          const int px0 = kb0 * BLOCK_K;
+          p_img = px0 / per_img;
+          const int rem = px0 - p_img * per_img;
+          p_oh = rem / p.cv.OW;
+          p_ow = rem - p_oh * p.cv.OW;
+          const int nblk = p.cv.kx * p.cv.ky * p.cv.cblocks;
+#pragma unroll
+          for (int c = 0; c < BN_LOAD / 64; ++c) {
+            const int blk = (n_base >> 6) + c;
+            if (blk < nblk) {
+              const int tap = blk / p.cv.cblocks;
+              const int r = tap / p.cv.kx;
+              c_ch[c] = (blk - tap * p.cv.cblocks) * 64;
+              c_wo[c] = tap - r * p.cv.kx;
+              c_ho[c] = r;
+            } else {  // past the last tap: channel coordinate out of range -> a box of zeros
+              c_ch[c] = p.cv.cblocks * 64;
+              c_wo[c] = 0;
+              c_ho[c] = 0;
+            }
+          }
         }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -278,20 +318,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           uint8_t* sb = sa + L::A_BYTES;
           // completion lands on the leader's barrier, armed for the bytes of both CTAs
           const uint32_t fb = PAIR ? mapa_u32(&full_bar[stage], 0) : smem_u32(&full_bar[stage]);
-          const bool no_a = (p.ablate & 1) != 0, no_b = (p.ablate & 2) != 0;
-          if (leader)
-            mbar_expect_tx(&full_bar[stage], (PAIR ? 2 : 1) * ((no_a ? 0 : L::A_BYTES) + (no_b ? 0 : L::B_BYTES)));
+          if (leader) mbar_expect_tx(&full_bar[stage], (PAIR ? 2 : 1) * L::STAGE_BYTES);
           auto ld2 = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
-            if (static_cast<uint8_t*>(dst) < sb ? no_a : no_b) return;
             if (PAIR) tma_load_2d_pair(dst, m, fb, c0, c1);
             else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
           };
           auto ldi = [&](void* dst, const CUtensorMap* m, int c, int w, int h, int n, int wo, int ho) {
-            if (static_cast<uint8_t*>(dst) < sb ? no_a : no_b) return;
             if (PAIR) tma_load_im2col_4d_pair(dst, m, fb, c, w, h, n, static_cast<uint16_t>(wo), static_cast<uint16_t>(ho));
             else tma_load_im2col_4d(dst, m, &full_bar[stage], c, w, h, n, static_cast<uint16_t>(wo), static_cast<uint16_t>(ho));
           };
-          if (p.cv.mode == 0) {
+          if (mode == 0) {
             if (!A_MN) {
               ld2(sa, &tma_a, kb * KE, m_base);
             } else {
@@ -309,49 +345,45 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               for (int c = 0; c < BN_LOAD / MNC; ++c)
                 ld2(sb + c * CHUNK_BYTES, mb_ptr, n_base + c * MNC, kb * KE);
             }
-          } else if (p.cv.mode == 3) {
+          } else if (mode == 3) {
             // A: dY, MN-major tiled.  B: one im2col box (64 pixels x 64 channels) per 64-column chunk.
 #pragma unroll
             for (int c = 0; c < BLOCK_M / 64; ++c)
               ld2(sa + c * (BLOCK_K * 128), &tma_a, m_base + c * 64, kb * BLOCK_K);
-            const int px0 = kb * BLOCK_K;
-            const int per_img = p.cv.OH * p.cv.OW;
-            const int img = px0 / per_img;
-            const int rem = px0 - img * per_img;
-            const int oh = rem / p.cv.OW;
-            const int bh = oh * p.cv.sy + p.cv.low_h;
-            const int bw = (rem - oh * p.cv.OW) * p.cv.sx + p.cv.low_w;
-            const int nblk = p.cv.kx * p.cv.ky * p.cv.cblocks;
+            const int bh = p_oh * p.cv.sy + p.cv.low_h;
+            const int bw = p_ow * p.cv.sx + p.cv.low_w;
 #pragma unroll
-            for (int c = 0; c < BN_LOAD / 64; ++c) {
-              const int blk = (n_base >> 6) + c;
-              if (blk < nblk) {
-                const int tap = blk / p.cv.cblocks;
-                const int cb = blk - tap * p.cv.cblocks;
-                const int r = tap / p.cv.kx;
-                ldi(sb + c * (BLOCK_K * 128), &tma_b, cb * 64, bw, bh, img, tap - r * p.cv.kx, r);
-              } else {  // past the last tap: channel coordinate out of range -> a box of zeros
-                ldi(sb + c * (BLOCK_K * 128), &tma_b, p.cv.cblocks * 64, bw, bh, img, 0, 0);
-              }
+            for (int c = 0; c < BN_LOAD / 64; ++c)
+              ldi(sb + c * (BLOCK_K * 128), &tma_b, c_ch[c], bw, bh, p_img, c_wo[c], c_ho[c]);
+            // the next k-block starts 64 pixels further along the traversal
+            p_ow += p.cv.r64;
+            p_oh += p.cv.q64;
+            if (p_ow >= p.cv.OW) {
+              p_ow -= p.cv.OW;
+              ++p_oh;
+            }
+            while (p_oh >= p.cv.OH) {
+              p_oh -= p.cv.OH;
+              ++p_img;
             }
           } else {
-            const int tap = kb / p.cv.cblocks;
-            const int cb = kb - tap * p.cv.cblocks;
-            const int r = tap / p.cv.kx;
-            const int sx_tap = tap - r * p.cv.kx;
-            // grouped layers in one launch: this N tile's group selects the channel range of the walked tensor
-            const int grp = p.cv.nbpg > 0 ? nb / p.cv.nbpg : 0;
-            const int ch0 = (grp * p.cv.cblocks + cb) * 64;
-            ldi(sa, &tma_a, ch0, a_w, a_h, a_n, sx_tap, r);
-            if (p.cv.mode == 1) {
-              ld2(sb, &tma_b, tap * p.cv.cg + cb * 64, n_base);
+            const int ch0 = grp_c0 + cb * 64;
+            ldi(sa, &tma_a, ch0, a_w, a_h, a_n, tap_s, tap_r);
+            if (mode == 1) {
+              ld2(sb, &tma_b, (tap_r * p.cv.kx + tap_s) * p.cv.cg + cb * 64, n_base);
             } else {
               // dX: the dY pixel reached through offset (s', r') pairs with filter tap (ky-1-r', kx-1-s')
-              const int wtap = (p.cv.ky - 1 - r) * p.cv.kx + (p.cv.kx - 1 - sx_tap);
-              const int n_local = n_base - grp * p.cv.nbpg * BN;   // column inside the group's [kernels, taps*cg] slab
+              const int wtap = (p.cv.ky - 1 - tap_r) * p.cv.kx + (p.cv.kx - 1 - tap_s);
 #pragma unroll
               for (int c = 0; c < BN_LOAD / 64; ++c)
                 ld2(sb + c * (BLOCK_K * 128), &tma_b, wtap * p.cv.cg + n_local + c * 64, ch0);
+            }
+            if (++cb == p.cv.cblocks) {
+              cb = 0;
+              if (++tap_s == p.cv.kx) {
+                tap_s = 0;
+                ++tap_r;
+              }
             }
           }
           if (++stage == STAGES) {
@@ -363,69 +395,76 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc(/*BF16 = 1, TF32 = 2*/ TF32 ? 2 : 1, A_MN, B_MN, TILE_M, BN);
-    int stage = 0;
-    uint32_t phase = 0;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    int it = 0;
-    for (int tile = unit; leader && tile < num_tiles; tile = sched_next(tile, it, lane == 0, true), ++it) {  // leader CTA only
-      const int ks = tile / tiles_mn;
-      const int kb0 = ks * kb_per_split;
-      const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
-      if (kb0 >= kb1) continue;  // empty split: the epilogue writes zeros without TMEM
-      mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
+    // ONE thread of the leader CTA runs the whole loop (waits included): no per-k-block election / reconvergence.
+    if (leader && elect_one()) {
+      constexpr uint32_t idesc = make_idesc(/*BF16 = 1, TF32 = 2*/ TF32 ? 2 : 1, A_MN, B_MN, TILE_M, BN);
+      // K-major : rows of 128 B, 8-row swizzle atoms 1024 B apart (SBO); k-step = +32 B.
+      // MN-major: 64-element column chunks BLOCK_K*128 B apart (LBO), 8 k-rows per
+      //           1024 B atom (SBO); k-step (16 rows) = +2048 B.
+      // MN-major tf32 operands use the 32-byte-atom flavour of the 128-byte swizzle: 4 k-rows per pattern
+      constexpr uint32_t MN_LAYOUT = TF32 ? 1u : 2u;
+      constexpr uint32_t MN_SBO = TF32 ? 512u : 1024u;
+      constexpr uint64_t STAGE_STEP = static_cast<uint64_t>(L::STAGE_BYTES >> 4);   // descriptor address units
+      constexpr uint64_t A_KSTEP = static_cast<uint64_t>((A_MN ? UK * 128 : 32) >> 4);
+      constexpr uint64_t B_KSTEP = static_cast<uint64_t>((B_MN ? UK * 128 : 32) >> 4);
+      const uint32_t sa0 = smem_u32(smem);
+      const uint64_t a_desc_s0 =
+          A_MN ? make_smem_desc(sa0, CHUNK_BYTES, MN_SBO, MN_LAYOUT) : make_smem_desc_sw128(sa0, 16, 1024);
+      const uint64_t b_desc_s0 = B_MN ? make_smem_desc(sa0 + L::A_BYTES, CHUNK_BYTES, MN_SBO, MN_LAYOUT)
+                                      : make_smem_desc_sw128(sa0 + L::A_BYTES, 16, 1024);
+      // (shared-memory addresses stay below 2^18, so adding stage offsets never carries out of the 14-bit field)
+      uint64_t a_desc = a_desc_s0, b_desc = b_desc_s0;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      int it = 0;
+      for (int tile = unit; tile < num_tiles; tile = sched_next(tile, it, true, false), ++it) {
+        const int ks = tile / tiles_mn;
+        const int kb0 = ks * kb_per_split;
+        const int kb1 = min(p.k_blocks, kb0 + kb_per_split);
+        if (kb0 >= kb1) continue;  // empty split: the epilogue writes zeros without TMEM
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        if (elect_one()) {
-          const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
-          const uint32_t sb = sa + L::A_BYTES;
-          // K-major : rows of 128 B, 8-row swizzle atoms 1024 B apart (SBO); k-step = +32 B.
-          // MN-major: 64-element column chunks BLOCK_K*128 B apart (LBO), 8 k-rows per
-          //           1024 B atom (SBO); k-step (16 rows) = +2048 B.
-          // MN-major tf32 operands use the 32-byte-atom flavour of the 128-byte swizzle: 4 k-rows per pattern
-          constexpr uint32_t MN_LAYOUT = TF32 ? 1u : 2u;
-          constexpr uint32_t MN_SBO = TF32 ? 512u : 1024u;
-          const uint64_t a_desc0 =
-              A_MN ? make_smem_desc(sa, CHUNK_BYTES, MN_SBO, MN_LAYOUT) : make_smem_desc_sw128(sa, 16, 1024);
-          const uint64_t b_desc0 =
-              B_MN ? make_smem_desc(sb, CHUNK_BYTES, MN_SBO, MN_LAYOUT) : make_smem_desc_sw128(sb, 16, 1024);
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        uint32_t accf = 0u;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
 #pragma unroll
           for (int k = 0; k < KE / UK; ++k) {   // 4 MMAs per k-block: +32 B along a K-major row, +UK rows MN-major
-            const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((A_MN ? k * UK * 128 : k * 32) >> 4);
-            const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((B_MN ? k * UK * 128 : k * 32) >> 4);
-            const uint32_t accf = (kb > kb0 || k > 0) ? 1u : 0u;
-            if (p.ablate & 4) continue;
+            const uint64_t ad = a_desc + k * A_KSTEP;
+            const uint64_t bd = b_desc + k * B_KSTEP;
             if (TF32) {
-              if (PAIR) umma_tf32_pair(d_tmem, a_desc, b_desc, idesc, accf);
-              else umma_tf32(d_tmem, a_desc, b_desc, idesc, accf);
+              if (PAIR) umma_tf32_pair(d_tmem, ad, bd, idesc, k == 0 ? accf : 1u);
+              else umma_tf32(d_tmem, ad, bd, idesc, k == 0 ? accf : 1u);
             } else {
-              if (PAIR) umma_f16_pair(d_tmem, a_desc, b_desc, idesc, accf);
-              else umma_f16(d_tmem, a_desc, b_desc, idesc, accf);
+              if (PAIR) umma_f16_pair(d_tmem, ad, bd, idesc, k == 0 ? accf : 1u);
+              else umma_f16(d_tmem, ad, bd, idesc, k == 0 ? accf : 1u);
             }
           }
+          accf = 1u;
           // frees the smem slot (in both CTAs of a pair) once these MMAs retire
           if (PAIR) umma_commit_pair(&empty_bar[stage]);
           else umma_commit(&empty_bar[stage]);
-          if (kb == kb1 - 1) {
-            if (PAIR) umma_commit_pair(&tmem_full[acc]);
-            else umma_commit(&tmem_full[acc]);
+          a_desc += STAGE_STEP;
+          b_desc += STAGE_STEP;
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+            a_desc = a_desc_s0;
+            b_desc = b_desc_s0;
           }
         }
-        __syncwarp();
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
+        if (PAIR) umma_commit_pair(&tmem_full[acc]);
+        else umma_commit(&tmem_full[acc]);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
         }
       }
-      if (++acc == 2) {
-        acc = 0;
-        acc_phase ^= 1;
-      }
     }
+    __syncwarp();
   } else {
     // ===================== Epilogue (warps 2..5) =====================
     // Two warps per TMEM lane quarter (a warp may only touch lanes 32*(warp%4)..+31): they take
@@ -454,7 +493,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
         const int col0 = nb * BN + c0;
-        if (col0 >= p.N || (p.ablate & 8)) break;  // warp-uniform
+        if (col0 >= p.N) break;  // warp-uniform
         // slab ownership: 32-column fp32 slabs / 64-column bf16 slab pairs alternate between the two warps
         if ((((p.out_fp32 && p.tma_store) ? (c0 >> 5) : (c0 >> 6)) & 1) != ehalf) continue;
         int dcol0 = col0;          // first column of this slab in D
@@ -878,12 +917,7 @@ static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUt
 using namespace vb;
 
 static int g_disable_tma_store = 0;
-static int g_ablate = 0;
-// Profiling hook: switches parts of the kernel off (results are then garbage) to see which resource bounds a shape.
-extern "C" int vb_gemm_set_ablation(int mask) {
-  g_ablate = mask;
-  return 0;
-}
+
 // Test hook: 1 forces the per-thread store epilogue so both paths stay covered.
 extern "C" int vb_gemm_set_direct_epilogue(int on) {
   g_disable_tma_store = on ? 1 : 0;
@@ -980,7 +1014,6 @@ static int finish_and_launch(GemmParams& p, const CUtensorMap& ta, const CUtenso
   const long long tiles = static_cast<long long>(p.m_blocks) * p.n_blocks * p.split_k;
   // dynamic (cluster-launch-control) scheduling: one unit per tile in the grid, running units steal the rest
   p.dyn_sched = (g_dyn_sched && tiles < (1LL << 30)) ? 1 : 0;
-  p.ablate = g_ablate;
   if (pair) {
     const int units = sms / 2;
     const int grid = 2 * static_cast<int>((p.dyn_sched || tiles < units) ? tiles : units);
@@ -1192,6 +1225,7 @@ static int conv_gemm_impl(int mode, const void* T, int tB, int tH, int tW, long 
   memset(&p, 0, sizeof(p));
   p.cv.mode = mode; p.cv.kx = kx; p.cv.ky = ky; p.cv.OW = oW; p.cv.OH = oH; p.cv.sx = sx; p.cv.sy = sy;
   p.cv.low_w = low_w; p.cv.low_h = low_h; p.cv.cblocks = cblocks; p.cv.cg = cg;
+  p.cv.q64 = BLOCK_K / oW; p.cv.r64 = BLOCK_K % oW;
   p.D = D; p.ldd = ldd; p.bias = bias; p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.Z = reinterpret_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv; p.alpha = alpha;
   const int sms = gemm_sm_count();

@@ -875,8 +875,8 @@ static int colsum_static_scratch(float** out) {
 extern "C" long long vb_col_sum_static_max_elems() { return VB_COLSUM_STATIC_MAX_ELEMS; }
 
 // out[j] (+)= alpha * sum_i a[i,j] without any caller-provided or allocated scratch.
-// Limit: ceil(rows / 64) * cols <= vb_col_sum_static_max_elems() (1 Mi), otherwise the call
-// is rejected with an error and nothing is launched.
+// Limits: ceil(rows / 64) * cols <= vb_col_sum_static_max_elems() (1 Mi) and rows <= 65535 * 64
+// (4 194 240), otherwise the call is rejected with an error and nothing is launched.
 // The first call on each device resolves the scratch address (a host-side runtime query, no
 // allocation); make that first call outside of any stream capture.
 extern "C" int vb_col_sum_static(const void* a, int dtype, long long lda, int rows, int cols, float* out,
@@ -889,6 +889,10 @@ extern "C" int vb_col_sum_static(const void* a, int dtype, long long lda, int ro
              "vb_col_sum_static: %d x %d needs %lld scratch floats, the built-in buffer holds %d; "
              "use vb_col_sum() with your own scratch for inputs this large",
              rows, cols, need, VB_COLSUM_STATIC_MAX_ELEMS);
+  VB_REQUIRE(slabs <= 65535,
+             "vb_col_sum_static: %d rows exceed the limit of %d rows (65535 slabs of %d rows); "
+             "use vb_col_sum() with your own scratch for inputs this tall",
+             rows, 65535 * COLSUM_ROWS_PER_SLAB, COLSUM_ROWS_PER_SLAB);
   VB_REQUIRE(dtype == D_F32 || dtype == D_BF16, "vb_col_sum_static: dtype must be f32 (0) or bf16 (1)");
   float* scratch = nullptr;
   if (int rc = colsum_static_scratch(&scratch)) return rc;

@@ -33,5 +33,15 @@ class GraphicsClient(object):
             self.poll_once()
 
 
+def main(argv=None):
+    """Console entry point (``veles_graphics_client`` in pyproject.toml): endpoint [output_dir]."""
+    argv = sys.argv[1:] if argv is None else list(argv)
+    if not argv or argv[0] in ("-h", "--help"):
+        print("usage: veles_graphics_client tcp://host:port [output_dir]")
+        return 0 if argv else 2
+    GraphicsClient(argv[0], argv[1] if len(argv) > 1 else None).run()
+    return 0
+
+
 if __name__ == "__main__":
-    GraphicsClient(sys.argv[1], sys.argv[2] if len(sys.argv) > 2 else None).run()
+    sys.exit(main())

@@ -80,8 +80,9 @@ class SnapshotterBase(Unit, TriviallyDistributable, metaclass=SnapshotterRegistr
     def run(self):
         if self.is_slave or get(root.common.disable.snapshotting, False) or self.skip:
             return
-        if int(os.environ.get("RANK", "0")) != 0:
-            return  # data-parallel: identical state everywhere, rank 0 writes
+        dp = getattr(self.workflow, "dp_group_", None)
+        if dp is not None and getattr(dp, "rank", 0) != 0:
+            return  # data-parallel group: identical state everywhere, rank 0 writes
         self._skipped_counter += 1
         if self._skipped_counter < self.interval:
             return

@@ -17,6 +17,8 @@ Topology (one iteration = one minibatch):
 """
 from __future__ import annotations
 
+import numpy
+
 import re
 
 from ..config import root, get, Config
@@ -210,6 +212,55 @@ class _DeferredLabelsCount(object):
         return int(self.loader.unique_labels_count)
 
     __index__ = __int__
+
+
+class _Indexed(object):
+    """``value`` = obj.<field>[i][j...] at the moment it is read (plotter inputs that live inside lists)."""
+
+    def __init__(self, obj, field, *index):
+        self.obj, self.field, self.index = obj, field, index
+
+    @property
+    def value(self):
+        v = getattr(self.obj, self.field)
+        for i in self.index:
+            v = v[i]
+        return v
+
+
+class _FirstRow(object):
+    """``value`` = the first sample of an Array, flattened."""
+
+    def __init__(self, arr):
+        self.arr = arr
+
+    @property
+    def value(self):
+        self.arr.map_read()
+        return numpy.asarray(self.arr.mem[0]).ravel()
+
+
+class _KernelShape(object):
+    """Sequence-like (ky, kx, channels) of a convolutional unit, resolved when the plotter draws."""
+
+    def __init__(self, unit):
+        self.unit = unit
+
+    def _shape(self):
+        u = self.unit
+        n = u.weights.shape[0] if not getattr(u, "weights_transposed", False) else u.weights.shape[-1]
+        per = u.weights.size // max(n, 1)
+        c = max(per // (u.ky * u.kx), 1)
+        return (u.ky, u.kx, c)
+
+    def __iter__(self):
+        return iter(self._shape())
+
+    def __len__(self):
+        return 3
+
+    def __getitem__(self, i):
+        return self._shape()[i]
 
 
 class StandardWorkflow(StandardWorkflowBase):
@@ -441,6 +492,168 @@ class StandardWorkflow(StandardWorkflowBase):
 
     def link_result_unit(self, *parents):
         return parents[0]
+
+    # -- service units documented in manualrst_veles_workflow_creation.rst:454-472, 550-644 ---------------------------
+    def _chain(self, units, parents, gate=None):
+        """Link ``units`` one after another behind ``parents``; returns the last one."""
+        prev = parents
+        for u in units:
+            u.link_from(*prev)
+            if gate is not None:
+                u.gate_skip = gate
+            self.plotters.append(u)
+            prev = (u,)
+        return prev[0]
+
+    def link_image_saver(self, *parents):
+        """ImageSaver: dumps (misclassified) samples of every minibatch, by class (``image_saver_config``)."""
+        from .image_saver import ImageSaver
+        self.image_saver = ImageSaver(self, **self.image_saver_config)
+        self.image_saver.link_from(*parents)
+        self.image_saver.link_attrs(self.forwards[0], "input")
+        self.image_saver.link_attrs(self.loader, ("indices", "minibatch_indices"), ("labels", "minibatch_labels"),
+                                    "minibatch_class", "minibatch_size")
+        self.image_saver.link_attrs(self.evaluator if self.evaluator is not None else self.forwards[-1], "max_idx")
+        if self.snapshotter is not None:
+            self.image_saver.gate_skip = ~self.decision.improved
+        return self.image_saver
+
+    def link_conf_matrix_plotter(self, *parents):
+        from ..plotting_units import MatrixPlotter
+        self.conf_matrix_plotters = []
+        for klass in (1, 2):
+            p = MatrixPlotter(self, name="Confusion matrix (%s)" % ("", "validation", "train")[klass],
+                              reversed_labels_mapping=getattr(self.loader, "reversed_labels_mapping", None))
+            p.input = _Indexed(self.decision, "confusion_matrixes", klass)
+            p.input_field = "value"
+            self.conf_matrix_plotters.append(p)
+        return self._chain(self.conf_matrix_plotters, parents, ~self.decision.epoch_ended)
+
+    def link_err_y_plotter(self, *parents):
+        from ..plotting_units import AccumulatingPlotter
+        self.err_y_plotters = []
+        for klass, style in ((1, "g-"), (2, "b-")):
+            p = AccumulatingPlotter(self, name="Last layer max gradient sum", plot_style=style,
+                                    label=("", "validation", "train")[klass], input_field="max_err_y_sums",
+                                    input_offset=klass)
+            p.input = self.decision
+            self.err_y_plotters.append(p)
+        return self._chain(self.err_y_plotters, parents, ~self.decision.epoch_ended)
+
+    def link_mse_plotter(self, *parents):
+        from ..plotting_units import AccumulatingPlotter
+        self.mse_plotters = []
+        for klass, style in ((1, "g-"), (2, "b-")):
+            p = AccumulatingPlotter(self, name="rmse", plot_style=style, label=("", "validation", "train")[klass],
+                                    input_field="epoch_rmse" if hasattr(self.decision, "epoch_rmse") else "epoch_loss",
+                                    input_offset=klass)
+            p.input = self.decision
+            self.mse_plotters.append(p)
+        return self._chain(self.mse_plotters, parents, ~self.decision.epoch_ended)
+
+    def link_min_max_plotter(self, is_min, *parents):
+        """Per-epoch minimum (``is_min``) or maximum of the per-sample MSE (``DecisionMSE.epoch_metrics``)."""
+        from ..plotting_units import AccumulatingPlotter
+        plotters = []
+        for klass, style in ((1, "g-"), (2, "b-")):
+            p = AccumulatingPlotter(self, name="mse %s" % ("min" if is_min else "max"), plot_style=style,
+                                    label=("", "validation", "train")[klass], input_field="value")
+            p.input = _Indexed(self.decision, "epoch_metrics", klass, 2 if is_min else 1)
+            plotters.append(p)
+        setattr(self, "min_plotters" if is_min else "max_plotters", plotters)
+        return self._chain(plotters, parents, ~self.decision.epoch_ended)
+
+    def link_multi_hist_plotter(self, layers=None, limit=None, *parents):
+        """One MultiHistogram (per-neuron weight histograms) per trainable layer."""
+        from ..plotting_units import MultiHistogram
+        self.multi_hist_plotters = []
+        for i, f in enumerate(self.forwards):
+            if not getattr(f, "HAS_WEIGHTS", False) or (layers is not None and i not in layers
+                                                        and self.layers[i].get("type") not in layers):
+                continue
+            p = MultiHistogram(self, name="Histogram %s %d" % (self.layers[i].get("type", "layer"), i + 1),
+                               hist_number=limit or 8)
+            p.input = f.weights
+            p.input_field = None
+            self.multi_hist_plotters.append(p)
+        return self._chain(self.multi_hist_plotters, parents, ~self.decision.epoch_ended)
+
+    def link_weights_plotter(self, layers=None, limit=64, weights_input="weights", *parents):
+        """One Weights2D per trainable layer (kernels / neurons as image tiles)."""
+        from .nn_plotting_units import Weights2D
+        self.weights_plotters = []
+        for i, f in enumerate(self.forwards):
+            if not getattr(f, "HAS_WEIGHTS", False) or (layers is not None and i not in layers
+                                                        and self.layers[i].get("type") not in layers):
+                continue
+            p = Weights2D(self, name="%s %d %s" % (self.layers[i].get("type", "layer"), i + 1, weights_input),
+                          limit=limit, transposed=bool(getattr(f, "weights_transposed", False)))
+            p.input = getattr(f, weights_input)
+            p.input_field = None
+            if hasattr(f, "kx") and hasattr(f, "ky"):
+                p.get_shape_from = _KernelShape(f)
+            self.weights_plotters.append(p)
+        return self._chain(self.weights_plotters, parents, ~self.decision.epoch_ended)
+
+    def link_similar_weights_plotter(self, layers=None, limit=64, magnitude_threshold=0.65, form_threshold=1.1,
+                                     peak_threshold=0.5, *parents):
+        from .nn_plotting_units import SimilarWeights2D
+        self.similar_weights_plotters = []
+        for i, f in enumerate(self.forwards):
+            if not getattr(f, "HAS_WEIGHTS", False) or (layers is not None and i not in layers
+                                                        and self.layers[i].get("type") not in layers):
+                continue
+            p = SimilarWeights2D(self, name="%s %d similar weights" % (self.layers[i].get("type", "layer"), i + 1),
+                                 limit=limit, magnitude_threshold=magnitude_threshold, form_threshold=form_threshold,
+                                 peak_threshold=peak_threshold,
+                                 transposed=bool(getattr(f, "weights_transposed", False)))
+            p.input = f.weights
+            p.input_field = None
+            if hasattr(f, "kx") and hasattr(f, "ky"):
+                p.get_shape_from = _KernelShape(f)
+            self.similar_weights_plotters.append(p)
+        return self._chain(self.similar_weights_plotters, parents, ~self.decision.epoch_ended)
+
+    def link_image_plotter(self, *parents):
+        """First samples of the current minibatch next to the last layer's outputs."""
+        from ..plotting_units import ImagePlotter
+        self.image_plotter = ImagePlotter(self, name="output sample")
+        self.image_plotter.inputs = [self.loader.minibatch_data, self.forwards[-1].output]
+        self.image_plotter.input_fields = [None, None]
+        return self._chain([self.image_plotter], parents, ~self.decision.epoch_ended)
+
+    def link_immediate_plotter(self, *parents):
+        """Target, output and input of the first sample of the minibatch as curves (MSE workflows)."""
+        from ..plotting_units import ImmediatePlotter
+        self.immediate_plotter = ImmediatePlotter(self, name="ImmediatePlotter")
+        p = self.immediate_plotter
+        for obj, style in ((getattr(self.loader, "minibatch_targets", None), "g-"),
+                           (self.forwards[-1].output, "r-"), (self.loader.minibatch_data, "b-")):
+            if obj is None:
+                continue
+            p.inputs.append(_FirstRow(obj))
+            p.input_fields.append("value")
+            p.input_styles.append(style)
+        return self._chain([p], parents, ~self.decision.epoch_ended)
+
+    def link_table_plotter(self, *parents):
+        """Max / min of every layer's weights, biases, outputs and gradients."""
+        from ..plotting_units import TableMaxMin
+        self.table_plotter = TableMaxMin(self, name="Max, Min")
+        t = self.table_plotter
+        for i, f in enumerate(self.forwards):
+            tag = "%s %d" % (self.layers[i].get("type", "layer"), i + 1)
+            if getattr(f, "HAS_WEIGHTS", False):
+                t.y += [f.weights, f.bias]
+                t.row_labels += [tag + " weights", tag + " bias"]
+            t.y.append(f.output)
+            t.row_labels.append(tag + " output")
+        for i, g in enumerate(self.gds or []):
+            if getattr(g, "gradient_weights", None) is not None and g.gradient_weights is not None:
+                t.y.append(g.gradient_weights)
+                t.row_labels.append("gd %d gradient" % (i + 1))
+        return self._chain([t], parents, ~self.decision.epoch_ended)
+
 
     # -- helpers --------------------------------------------------------------------------------------------------------
     def extract_forward_workflow(self, loader_name=None, loader_config=None, result_unit_factory=None, cyclic=False):
