@@ -339,3 +339,111 @@ def test_update_forge_uploads_every_model_directory(tmp_path, capsys):
         assert "alpha" in out and "beta" in out and "not_a_model" not in out
     finally:
         srv.stop()
+
+
+def test_standard_workflow_service_links(tmp_path):
+    """Every documented ``link_*`` of StandardWorkflow (manualrst_veles_workflow_creation.rst:454-472, 550-644): the
+    plotters hang behind Decision, run at epoch ends and write their SVG files; ImageSaver dumps samples."""
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.dummy import DummyLauncher
+    from veles_b200.models.configs import MODEL_CONFIGS
+    from veles_b200.loader import synthetic  # noqa: F401
+    from veles_b200.znicz.standard_workflow import StandardWorkflow
+    root.common.disable.snapshotting = True
+    root.common.disable.plotting = False
+    plots = str(tmp_path / "plots")
+
+    class Wf(StandardWorkflow):
+        def create_workflow(self):
+            self.link_repeater(self.start_point)
+            self.link_loader(self.repeater)
+            self.link_forwards(("input", "minibatch_data"), self.loader)
+            self.link_evaluator(self.forwards[-1])
+            self.link_decision(self.evaluator)
+            self.link_snapshotter(self.decision)
+            last = self.link_image_saver(self.snapshotter)
+            self.link_gds(last)
+            self.link_loop(self.gds[0])
+            last = self.link_error_plotter(last)      # a side branch behind ImageSaver: also runs on the last epoch
+            last = self.link_conf_matrix_plotter(last)
+            last = self.link_err_y_plotter(last)
+            last = self.link_multi_hist_plotter(None, 4, last)
+            last = self.link_weights_plotter(None, 16, "weights", last)
+            last = self.link_similar_weights_plotter(None, 16, 0.2, 1.1, 0.5, last)
+            last = self.link_image_plotter(last)
+            last = self.link_table_plotter(last)
+            self.link_end_point(last)
+
+    try:
+        cfg = MODEL_CONFIGS["mnist_mlp"]
+        wf = Wf(DummyLauncher(), layers=cfg["layers"](), loader_name=cfg["loader_name"],
+                loader_config={"minibatch_size": 50, "n_train": 200, "n_valid": 100, "sample_shape": (784,),
+                               "n_classes": 10},
+                loss_function="softmax", decision_config={"max_epochs": 2},
+                image_saver_config={"out_dirs": [str(tmp_path / "img" / n) for n in ("test", "validation", "train")],
+                                    "limit": 5, "only_errors": False})
+        wf.plotters_are_enabled = True
+        for p in wf.plotters:
+            p.output_dir = plots
+            p.redraw_threshold = 0
+        wf.initialize(device=NumpyDevice())
+        wf.run()
+        wf.thread_pool.wait_idle(10)
+        names = sorted(os.listdir(plots))
+        assert len(wf.plotters) >= 2 + 2 + 2 + 2 + 2 + 2 + 1 + 1
+        drawn = [p for p in wf.plotters if getattr(p, "last_file", None)]
+        assert len(drawn) == len(wf.plotters), [p.name for p in wf.plotters if not getattr(p, "last_file", None)]
+        for p in drawn:
+            assert open(p.last_file).read().startswith("<svg"), p.name
+        assert any("Confusion" in n for n in names) and any("weights" in n for n in names) and "Max__Min.svg" in names
+        assert wf.image_saver.saved == 5
+        assert sum(len(os.listdir(str(tmp_path / "img" / n))) for n in ("test", "validation", "train")) == 5
+        wf.launcher.stop()
+    finally:
+        root.common.disable.plotting = True
+
+
+def test_mse_workflow_plotter_links(tmp_path):
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.dummy import DummyLauncher
+    from veles_b200.loader import synthetic  # noqa: F401
+    from veles_b200.znicz.standard_workflow import StandardWorkflow
+    root.common.disable.snapshotting = True
+    root.common.disable.plotting = False
+
+    class Wf(StandardWorkflow):
+        def create_workflow(self):
+            self.link_repeater(self.start_point)
+            self.link_loader(self.repeater)
+            self.link_forwards(("input", "minibatch_data"), self.loader)
+            self.link_evaluator(self.forwards[-1])
+            self.link_decision(self.evaluator)
+            self.link_snapshotter(self.decision)
+            self.link_gds(self.snapshotter)
+            self.link_loop(self.gds[0])
+            last = self.link_mse_plotter(self.snapshotter)
+            last = self.link_min_max_plotter(True, last)
+            last = self.link_min_max_plotter(False, last)
+            last = self.link_immediate_plotter(last)
+            self.link_end_point(last)
+
+    try:
+        layers = [{"type": "all2all_tanh", "->": {"output_sample_shape": 16}, "<-": {"learning_rate": 0.01}},
+                  {"type": "all2all", "->": {"output_sample_shape": 32}, "<-": {"learning_rate": 0.01}}]
+        wf = Wf(DummyLauncher(), layers=layers, loader_name="synthetic_mse",
+                loader_config={"minibatch_size": 20, "n_train": 80, "n_valid": 40, "sample_shape": (32,)},
+                loss_function="mse", decision_config={"max_epochs": 2})
+        wf.plotters_are_enabled = True
+        for p in wf.plotters:
+            p.output_dir = str(tmp_path)
+            p.redraw_threshold = 0
+        wf.initialize(device=NumpyDevice())
+        wf.run()
+        wf.thread_pool.wait_idle(10)
+        assert len(wf.plotters) == 7
+        for p in wf.plotters:
+            assert p.last_file and open(p.last_file).read().startswith("<svg"), p.name
+        assert len(wf.mse_plotters[0].values) >= 2 and wf.mse_plotters[0].values[-1] < 1e29
+        wf.launcher.stop()
+    finally:
+        root.common.disable.plotting = True

@@ -293,6 +293,20 @@ def conv_err_input_grouped(dy4, w, dx2, g, groups, z=None, deriv=0, block_n=0):
                               deriv=deriv, block_n=block_n)
 
 
+def conv_halo_preferred(cg, g):
+    """Layer shapes on which the halo-tile kernel beats the im2col-mode kernel (measured, profiles/
+    conv_microbench_v3.json): few input channels per group with many taps on images of >= 24 rows - AlexNet conv1
+    after space-to-depth (+17 %) and conv2 (+15 % forward, +6 % err_input).  On 13x13 images its 128-row tiles waste a
+    third of the MMA rows.  ``root.common.engine.conv_halo``: "auto" (default), "on", "off"."""
+    from ..config import root, get
+    mode = get(root.common.engine.conv_halo, "auto")
+    if mode == "off" or g["sx"] != 1 or g["sy"] != 1 or g["OW"] + g["kx"] - 1 > 64:
+        return False
+    if mode == "on":
+        return True
+    return cg <= 64 and g["kx"] * g["ky"] >= 9 and min(g["OH"], g.get("H", g["OH"])) >= 24
+
+
 def conv_halo_set_options(mt=0, resident=-1):
     """Tuning / test hook of the halo-tile kernel: sub-tiles per CTA tile (0 = choose, 1, 2) and resident weights
     (-1 = choose, 0 = never, 1 = whenever they fit)."""

@@ -24,10 +24,11 @@ class Canvas(object):
 
     def axes(self, xmin, xmax, ymin, ymax, xlabel="", ylabel=""):
         l, t, r, b = self.plot
-        if xmax == xmin:
-            xmax = xmin + 1
-        if ymax == ymin:
-            ymax = ymin + 1
+        # degenerate or huge ranges (a curve of identical values, 1e30 "not measured yet" markers)
+        if not (xmax - xmin > 1e-12 * max(abs(xmin), abs(xmax), 1.0)):
+            xmax = xmin + max(1.0, abs(xmin) * 1e-6)
+        if not (ymax - ymin > 1e-12 * max(abs(ymin), abs(ymax), 1.0)):
+            ymax = ymin + max(1.0, abs(ymin) * 1e-6)
         self.range = (xmin, xmax, ymin, ymax)
         self.items.append('<rect x="%d" y="%d" width="%d" height="%d" fill="none" stroke="#444"/>'
                           % (l, t, r - l, b - t))

@@ -229,18 +229,21 @@ class Conv(Forward):
             sd = self.s2d_
             kernels.space_to_depth(x, sd["x"], g["sy"], g["sx"])
             kernels.gather_cols(self.weights_bf16_, sd["w"], sd["to_s2d"])   # refreshed bf16 weights, s2d order
-            kernels.conv_forward(sd["x"], sd["w"], out2, sd["geom"], bias=bias, act=self.ACTIVATION)
+            if not (kernels.conv_halo_preferred(sd["x"].shape[3], sd["geom"]) and
+                    kernels.conv_forward_halo(sd["x"], sd["w"], out2, sd["geom"], bias=bias, act=self.ACTIVATION)):
+                kernels.conv_forward(sd["x"], sd["w"], out2, sd["geom"], bias=bias, act=self.ACTIVATION)
         elif self.implicit_ and kernels.grouped_conv_ok(x.shape[3], self.n_kernels, G):
             # every group in ONE launch (tile -> group): fewer, fuller waves than one launch per group
             kernels.conv_forward_grouped(x, self.weights_bf16_, out2, g, G, bias=bias, act=self.ACTIVATION)
         elif self.implicit_:
             Cg = x.shape[3] // G
+            halo = kernels.conv_halo_preferred(Cg, g)
             for gi in range(G):
-                kernels.conv_forward(x[..., gi * Cg:(gi + 1) * Cg] if G > 1 else x,
-                                     self.weights_bf16_[gi * nkg:(gi + 1) * nkg],
-                                     out2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else out2, g,
-                                     bias=bias[gi * nkg:(gi + 1) * nkg] if bias is not None else None,
-                                     act=self.ACTIVATION)
+                args = (x[..., gi * Cg:(gi + 1) * Cg] if G > 1 else x, self.weights_bf16_[gi * nkg:(gi + 1) * nkg],
+                        out2[:, gi * nkg:(gi + 1) * nkg] if G > 1 else out2, g)
+                kw = dict(bias=bias[gi * nkg:(gi + 1) * nkg] if bias is not None else None, act=self.ACTIVATION)
+                if not (halo and kernels.conv_forward_halo(*args, **kw)):
+                    kernels.conv_forward(*args, **kw)
         else:
             kernels.im2col(x, self.cols_, g)
             for gi in range(G):

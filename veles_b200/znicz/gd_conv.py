@@ -163,12 +163,14 @@ class GradientDescentConv(GradientDescentBase):
                     self.err_input.mark_device_written()
                     self.device_update()
                     return
+                halo = kernels.conv_halo_preferred(Cg, g)
                 for gi in range(G):
-                    kernels.conv_err_input(eo4[..., gi * nkg:(gi + 1) * nkg] if G > 1 else eo4,
-                                           w_bf16[gi * nkg:(gi + 1) * nkg],
-                                           ei2[:, gi * Cg:(gi + 1) * Cg] if G > 1 else ei2, g,
-                                           z=(z2[:, gi * Cg:(gi + 1) * Cg] if G > 1 else z2) if z2 is not None else None,
-                                           deriv=self.prev_activation)
+                    args = (eo4[..., gi * nkg:(gi + 1) * nkg] if G > 1 else eo4, w_bf16[gi * nkg:(gi + 1) * nkg],
+                            ei2[:, gi * Cg:(gi + 1) * Cg] if G > 1 else ei2, g)
+                    kw = dict(z=(z2[:, gi * Cg:(gi + 1) * Cg] if G > 1 else z2) if z2 is not None else None,
+                              deriv=self.prev_activation)
+                    if not (halo and kernels.conv_err_input_halo(*args, **kw)):
+                        kernels.conv_err_input(*args, **kw)
             else:
                 cols = f.ensure_cols()   # (also the err_input scratch of strided / space-to-depth layers)
                 for gi in range(G):

@@ -527,7 +527,7 @@ class StandardWorkflow(StandardWorkflowBase):
             p.input = _Indexed(self.decision, "confusion_matrixes", klass)
             p.input_field = "value"
             self.conf_matrix_plotters.append(p)
-        return self._chain(self.conf_matrix_plotters, parents, ~self.decision.epoch_ended)
+        return self._chain(self.conf_matrix_plotters, parents, ~self.loader.epoch_ended)
 
     def link_err_y_plotter(self, *parents):
         from ..plotting_units import AccumulatingPlotter
@@ -538,7 +538,7 @@ class StandardWorkflow(StandardWorkflowBase):
                                     input_offset=klass)
             p.input = self.decision
             self.err_y_plotters.append(p)
-        return self._chain(self.err_y_plotters, parents, ~self.decision.epoch_ended)
+        return self._chain(self.err_y_plotters, parents, ~self.loader.epoch_ended)
 
     def link_mse_plotter(self, *parents):
         from ..plotting_units import AccumulatingPlotter
@@ -549,7 +549,7 @@ class StandardWorkflow(StandardWorkflowBase):
                                     input_offset=klass)
             p.input = self.decision
             self.mse_plotters.append(p)
-        return self._chain(self.mse_plotters, parents, ~self.decision.epoch_ended)
+        return self._chain(self.mse_plotters, parents, ~self.loader.epoch_ended)
 
     def link_min_max_plotter(self, is_min, *parents):
         """Per-epoch minimum (``is_min``) or maximum of the per-sample MSE (``DecisionMSE.epoch_metrics``)."""
@@ -561,7 +561,7 @@ class StandardWorkflow(StandardWorkflowBase):
             p.input = _Indexed(self.decision, "epoch_metrics", klass, 2 if is_min else 1)
             plotters.append(p)
         setattr(self, "min_plotters" if is_min else "max_plotters", plotters)
-        return self._chain(plotters, parents, ~self.decision.epoch_ended)
+        return self._chain(plotters, parents, ~self.loader.epoch_ended)
 
     def link_multi_hist_plotter(self, layers=None, limit=None, *parents):
         """One MultiHistogram (per-neuron weight histograms) per trainable layer."""
@@ -576,7 +576,7 @@ class StandardWorkflow(StandardWorkflowBase):
             p.input = f.weights
             p.input_field = None
             self.multi_hist_plotters.append(p)
-        return self._chain(self.multi_hist_plotters, parents, ~self.decision.epoch_ended)
+        return self._chain(self.multi_hist_plotters, parents, ~self.loader.epoch_ended)
 
     def link_weights_plotter(self, layers=None, limit=64, weights_input="weights", *parents):
         """One Weights2D per trainable layer (kernels / neurons as image tiles)."""
@@ -593,7 +593,7 @@ class StandardWorkflow(StandardWorkflowBase):
             if hasattr(f, "kx") and hasattr(f, "ky"):
                 p.get_shape_from = _KernelShape(f)
             self.weights_plotters.append(p)
-        return self._chain(self.weights_plotters, parents, ~self.decision.epoch_ended)
+        return self._chain(self.weights_plotters, parents, ~self.loader.epoch_ended)
 
     def link_similar_weights_plotter(self, layers=None, limit=64, magnitude_threshold=0.65, form_threshold=1.1,
                                      peak_threshold=0.5, *parents):
@@ -612,7 +612,7 @@ class StandardWorkflow(StandardWorkflowBase):
             if hasattr(f, "kx") and hasattr(f, "ky"):
                 p.get_shape_from = _KernelShape(f)
             self.similar_weights_plotters.append(p)
-        return self._chain(self.similar_weights_plotters, parents, ~self.decision.epoch_ended)
+        return self._chain(self.similar_weights_plotters, parents, ~self.loader.epoch_ended)
 
     def link_image_plotter(self, *parents):
         """First samples of the current minibatch next to the last layer's outputs."""
@@ -620,7 +620,7 @@ class StandardWorkflow(StandardWorkflowBase):
         self.image_plotter = ImagePlotter(self, name="output sample")
         self.image_plotter.inputs = [self.loader.minibatch_data, self.forwards[-1].output]
         self.image_plotter.input_fields = [None, None]
-        return self._chain([self.image_plotter], parents, ~self.decision.epoch_ended)
+        return self._chain([self.image_plotter], parents, ~self.loader.epoch_ended)
 
     def link_immediate_plotter(self, *parents):
         """Target, output and input of the first sample of the minibatch as curves (MSE workflows)."""
@@ -634,7 +634,7 @@ class StandardWorkflow(StandardWorkflowBase):
             p.inputs.append(_FirstRow(obj))
             p.input_fields.append("value")
             p.input_styles.append(style)
-        return self._chain([p], parents, ~self.decision.epoch_ended)
+        return self._chain([p], parents, ~self.loader.epoch_ended)
 
     def link_table_plotter(self, *parents):
         """Max / min of every layer's weights, biases, outputs and gradients."""
@@ -652,7 +652,7 @@ class StandardWorkflow(StandardWorkflowBase):
             if getattr(g, "gradient_weights", None) is not None and g.gradient_weights is not None:
                 t.y.append(g.gradient_weights)
                 t.row_labels.append("gd %d gradient" % (i + 1))
-        return self._chain([t], parents, ~self.decision.epoch_ended)
+        return self._chain([t], parents, ~self.loader.epoch_ended)
 
 
     # -- helpers --------------------------------------------------------------------------------------------------------
