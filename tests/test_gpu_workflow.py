@@ -187,3 +187,42 @@ def test_lstm_workflow_on_device_follows_numpy_oracle():
     assert np.abs(wf.forwards[0].weights.mem - ref.forwards[0].weights.mem).max() < 0.05
     l0.stop()
     l1.stop()
+
+
+def test_workflow_run_replays_cuda_graphs_and_matches_the_eager_walk():
+    """``wf.run()`` (the scheduler of the CLI path) executes the steady-state forward and backward unit sequences as
+    replayed CUDA graphs; the trajectory equals the one of the unit-by-unit walk."""
+    from veles_b200.backends import B200Device
+    from veles_b200.config import root
+    conv = [{"type": "conv_str", "->": {"n_kernels": 16, "kx": 3, "ky": 3, "padding": (1, 1, 1, 1)},
+             "<-": {"learning_rate": 0.02, "gradient_moment": 0.9}},
+            {"type": "max_pooling", "->": {"kx": 2, "ky": 2, "sliding": (2, 2)}},
+            {"type": "all2all_tanh", "->": {"output_sample_shape": 32}, "<-": {"learning_rate": 0.02}},
+            {"type": "softmax", "<-": {"learning_rate": 0.02}}]
+    cfg = {"minibatch_size": 64, "n_train": 640, "n_valid": 128, "sample_shape": (8, 8, 8), "noise": 1.0}
+    results = []
+    for replay in (True, False):
+        root.common.engine.graph_replay = replay
+        try:
+            l, wf = _build(B200Device(), conv, cfg, epochs=3)
+            chains = getattr(wf, "graph_chains_", [])
+            assert bool(chains) == replay
+            wf.run()
+            if replay:
+                assert [c.name for c in chains] == ["forward", "backward"]
+                assert all(c.enabled for c in chains)
+                assert chains[0].replays > 20 and chains[1].replays > 10, [(c.replays, c.captures) for c in chains]
+                assert chains[1].captures <= 2
+            wf.forwards[0].weights.map_read()
+            wf.forwards[-1].weights.map_read()
+            results.append((wf.decision.epoch_metrics_history, wf.forwards[0].weights.mem.copy(),
+                            wf.forwards[-1].weights.mem.copy()))
+            l.stop()
+        finally:
+            root.common.engine.graph_replay = True
+    (h1, a1, b1), (h0, a0, b0) = results
+    assert len(h1) == len(h0) == 3
+    for x, y in zip(h1, h0):
+        assert x["n_err"] == y["n_err"]
+    assert np.abs(a1 - a0).max() <= 1e-6 * max(1.0, np.abs(a0).max())
+    assert np.abs(b1 - b0).max() <= 1e-6 * max(1.0, np.abs(b0).max())

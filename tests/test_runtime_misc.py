@@ -142,3 +142,28 @@ def test_auto_label_image_loader_mse_serves_target_images(tmp_path):
         x, t = ld.minibatch_data.mem[i], ld.minibatch_targets.mem[i]
         # the target of every sample is the colour-inverted image of its label
         assert np.abs((255.0 - x) - t).max() < 1.0 or np.abs((1.0 - x) - t).max() < 1e-2
+
+
+def test_manhole_repl_over_unix_socket(tmp_path):
+    """``--manhole`` / SIGUSR2 (reference: veles/thread_pool.py:139-164, 527-533): a REPL on a UNIX socket whose
+    namespace holds the workflow and the launcher."""
+    import os
+    import stat
+    from veles_b200 import manhole
+
+    class FakeWorkflow(object):
+        name = "wf-under-inspection"
+
+    path = str(tmp_path / "manhole.sock")
+    assert manhole.install(workflow=FakeWorkflow(), launcher="the launcher", path=path) == path
+    try:
+        assert stat.S_IMODE(os.stat(path).st_mode) == 0o600
+        out = manhole.connect(path, ["print(workflow.name)", "x = 6 * 7", "x", "launcher", "1/0"])
+        assert "wf-under-inspection" in out and "42" in out and "the launcher" in out
+        assert "ZeroDivisionError" in out          # errors are reported to the client, the server survives
+        out2 = manhole.connect(path, ["dump_stacks is not None"])
+        assert "True" in out2
+        assert manhole.install(path=path, workflow=None) == path     # idempotent
+    finally:
+        manhole.uninstall(path)
+    assert not os.path.exists(path)

@@ -447,3 +447,52 @@ def test_mse_workflow_plotter_links(tmp_path):
         wf.launcher.stop()
     finally:
         root.common.disable.plotting = True
+
+
+def test_forge_confirmation_unregister_and_assist(tmp_path):
+    """E-mail confirmed registration, ``unregister`` and ``assist`` (reference: forge_server.py:462-520,
+    forge_client.py:514-621)."""
+    import urllib.error
+    from veles_b200.forge.forge_client import ForgeClient
+    from veles_b200.forge.forge_server import ForgeServer
+    sent = []
+    srv = ForgeServer(str(tmp_path / "store"), require_confirmation=True,
+                      mailer=lambda email, subject, body: sent.append((email, body))).start()
+    try:
+        wf_py = tmp_path / "my_model.py"
+        wf_py.write_text("from veles_b200.znicz.standard_workflow import StandardWorkflow\n\n\n"
+                         "class TinyWorkflow(StandardWorkflow):\n    pass\n\n\ndef run(load, main):\n    pass\n")
+        (tmp_path / "my_model_config.py").write_text("# configuration\n")
+        c = ForgeClient(srv.url)
+        asked = []
+        dest, meta = c.assist(str(wf_py), {"directory": str(tmp_path / "pkg"), "author": "tester"},
+                              ask=lambda prompt: asked.append(prompt) or "")
+        assert meta["name"] == "TinyWorkflow" and meta["configuration"] == "my_model_config.py"
+        assert len(asked) == 3                       # name, short and long description; the author was given
+        assert sorted(os.listdir(dest)) == ["manifest.json", "my_model.py", "my_model_config.py"]
+        c.register("me@example.com")
+        with pytest.raises(urllib.error.HTTPError):  # not confirmed yet
+            c.upload(dest)
+        assert sent and sent[0][0] == "me@example.com"
+        code = sent[0][1].split("Confirmation code: ")[1].split()[0]
+        with pytest.raises(urllib.error.HTTPError):
+            c.confirm("wrong")
+        assert c.confirm(code) is True
+        assert c.upload(dest)["version"] == "v1"
+        other = ForgeClient(srv.url)
+        other.register("other@example.com")
+        other.confirm(sent[1][1].split("Confirmation code: ")[1].split()[0])
+        with pytest.raises(urllib.error.HTTPError):  # a taken name belongs to its first author
+            other.upload(dest)
+        token = c.token
+        assert c.unregister() == "me@example.com" and c.token is None
+        c.token = token
+        with pytest.raises(urllib.error.HTTPError):  # the revoked token can no longer write
+            c.upload(dest)
+        assert [row[0] for row in c.list()] == ["TinyWorkflow"]      # what was published stays
+        # the default mailer drops the message into the store's outbox
+        srv2 = ForgeServer(str(tmp_path / "store2"), require_confirmation=True)
+        srv2.register("x@example.com")
+        assert "Confirmation code" in open(os.path.join(str(tmp_path / "store2"), "outbox", "x@example.com.txt")).read()
+    finally:
+        srv.stop()

@@ -291,3 +291,77 @@ def test_recurrent_workflow_snapshot_roundtrip(tmp_path):
     assert back.decision.epoch_metrics_history[-1]["epoch"] == 2
     assert np.abs(back.forwards[0].weights.mem - w_before).max() > 0
     launcher.stop()
+
+
+def _one_gd_step(gd_kwargs, device=None, steps=2):
+    """Train a 12-8-4 MLP for ``steps`` minibatches; returns the first layer's weights."""
+    from veles_b200 import prng
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.config import root
+    from veles_b200.dummy import DummyLauncher
+    from veles_b200.znicz.standard_workflow import StandardWorkflow
+    import veles_b200.loader.synthetic  # noqa: F401
+    root.common.disable.snapshotting = True
+    prng.get().seed(3)
+    layers = [{"type": "all2all_tanh", "->": {"output_sample_shape": 8}, "<-": dict(gd_kwargs)},
+              {"type": "softmax", "<-": {"learning_rate": 0.0}}]
+    wf = StandardWorkflow(DummyLauncher(), layers=layers, loader_name="synthetic_fullbatch",
+                          loader_config={"minibatch_size": 16, "n_train": 64, "n_valid": 0, "sample_shape": (12,),
+                                         "n_classes": 4},
+                          loss_function="softmax", decision_config={"max_epochs": 1})
+    wf.initialize(device=device or NumpyDevice())
+    w0 = None
+    for _ in range(steps):
+        wf.loader.run()
+        for f in wf.forwards:
+            f.run()
+        wf.evaluator.run()
+        if w0 is None:
+            wf.forwards[0].weights.map_read()
+            w0 = wf.forwards[0].weights.mem.copy()
+        for gd in reversed(wf.gds):
+            gd.run()
+    wf.forwards[0].weights.map_read()
+    w = wf.forwards[0].weights.mem.copy()
+    gd0 = wf.gds[0]
+    gd0.gradient_weights_with_moment.map_read()
+    vel = gd0.gradient_weights_with_moment.mem.copy()
+    wf.launcher.stop()
+    return w0, w, vel
+
+
+def test_gd_variant_switches_and_factor_ortho_have_semantics():
+    import numpy as np
+    import pytest
+    base = {"learning_rate": 0.1, "gradient_moment": 0.9, "weights_decay": 0.0}
+    w0, w_full, v_full = _one_gd_step(base)
+    # no momentum term: two plain SGD steps, the velocity holds the last step only
+    _, w_nomom, v_nomom = _one_gd_step(dict(base, variant_moment_gradient=False))
+    _, w_sgd, _ = _one_gd_step(dict(base, gradient_moment=0.0))
+    np.testing.assert_allclose(w_nomom, w_sgd, rtol=1e-6, atol=1e-7)
+    assert np.abs(w_nomom - w_full).max() > 1e-5
+    # no gradient step: with zero initial velocity the weights never move
+    _, w_coast, v_coast = _one_gd_step(dict(base, variant_gradient=False))
+    np.testing.assert_array_equal(w_coast, w0)
+    assert not v_coast.any()
+    # factor_ortho: the first step differs from the plain one by exactly -lr * f / n * (column sums - w)
+    f = 0.5
+    w0o, w_ortho, _ = _one_gd_step(dict(base, factor_ortho=f, gradient_moment=0.0), steps=1)
+    _, w_plain, _ = _one_gd_step(dict(base, gradient_moment=0.0), steps=1)
+    expect = w_plain - 0.1 * f / w0o.shape[0] * (w0o.sum(axis=0, keepdims=True) - w0o)
+    np.testing.assert_allclose(w_ortho, expect, rtol=1e-5, atol=1e-6)
+    # the undocumented option is refused, not ignored
+    with pytest.raises(ValueError, match="fast_learning_rate"):
+        _one_gd_step(dict(base, fast_learning_rate=0.5), steps=1)
+
+
+@pytest.mark.gpu
+def test_gd_options_on_device_match_the_numpy_oracle():
+    import numpy as np
+    from veles_b200.backends import B200Device
+    for kw in ({"learning_rate": 0.1, "gradient_moment": 0.9, "factor_ortho": 0.5},
+               {"learning_rate": 0.1, "gradient_moment": 0.9, "variant_moment_gradient": False},
+               {"learning_rate": 0.1, "gradient_moment": 0.9, "variant_gradient": False}):
+        _, w_ref, v_ref = _one_gd_step(kw, steps=3)
+        _, w_dev, v_dev = _one_gd_step(kw, device=B200Device(), steps=3)
+        assert np.abs(w_dev - w_ref).max() < 3e-2 * max(np.abs(w_ref).max(), 1e-3), kw

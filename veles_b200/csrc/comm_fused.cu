@@ -124,7 +124,7 @@ __device__ __forceinline__ bool wait_all(const FusedParams& p, int slot, uint32_
 // at the ~2.5 us NVLink round trip of multimem.ld_reduce: enough to hide AlexNet's 244 MB / world behind the
 // convolution backward pass.  (Round 1 used 64-96 CTAs of 256 threads per LAYER: 0.4-0.5 ms per step exposed.)
 template <bool MULTIMEM>
-__global__ void __launch_bounds__(FUSED_THREADS, 1) fused_allreduce_gd_kernel(const FusedParams p) {
+__device__ __forceinline__ void fused_allreduce_gd_body(const FusedParams& p) {
   const int ready_slot = (p.channel * 2 + 0) * MAX_WORLD;
   const int done_slot = (p.channel * 2 + 1) * MAX_WORLD;
   // identical in every CTA: epochs[] is bumped by the LAST CTA to finish, i.e. after every CTA has read it here
@@ -295,6 +295,19 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) fused_allreduce_gd_kernel(co
   }
 }
 
+template <bool MULTIMEM>
+__global__ void __launch_bounds__(FUSED_THREADS, 1) fused_allreduce_gd_kernel(const FusedParams p) {
+  fused_allreduce_gd_body<MULTIMEM>(p);
+}
+
+// All ranks of a group on ONE GPU, as one cooperative launch: blockIdx.y is the rank, every rank's CTAs run the very
+// same body against that rank's parameter block (P2P path; the "peers" are other buffers of this GPU).  The ranks
+// wait for each other's flags, so all CTAs must be resident at once - hence the cooperative launch.  This is how a
+// single-GPU box exercises the flag protocol, the slice arithmetic and the per-segment options.
+__global__ void __launch_bounds__(FUSED_THREADS, 1) fused_allreduce_gd_emulated_kernel(const FusedParams* ps) {
+  fused_allreduce_gd_body<false>(ps[blockIdx.y]);
+}
+
 }  // namespace vb
 
 using namespace vb;
@@ -379,5 +392,64 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   if (use_multimem) VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, fused_allreduce_gd_kernel<true>, p));
   else VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, fused_allreduce_gd_kernel<false>, p));
   VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Test / bring-up entry point: `world` ranks emulated on the current GPU (see fused_allreduce_gd_emulated_kernel).
+// Per-rank arrays hold `world` device pointers each (rank r's gradient slab of this step's parity, the other
+// parity's, weights, momentum, bf16 shadow, flag words [64][2][8], epoch words [64], CTA counters [64], status word).
+// `params_dev` is caller-provided device scratch of at least world * vb_fused_params_bytes() bytes.
+extern "C" long long vb_fused_params_bytes() { return static_cast<long long>(sizeof(FusedParams)); }
+
+extern "C" int vb_fused_allreduce_gd_emulated(int world, int channel, int nseg, const long long* segs,
+                                              const float* hyper, float** grads, float** grads_other, float** weights,
+                                              float** vel, void** shadow, unsigned int** flags, unsigned int** epochs,
+                                              unsigned int** cta_counter, int** status, float grad_scale, int n_ctas,
+                                              int options, double timeout_s, void* params_dev, cudaStream_t stream) {
+  VB_REQUIRE(world >= 2 && world <= MAX_WORLD, "vb_fused_allreduce_gd_emulated: world size %d not in [2,%d]", world, MAX_WORLD);
+  VB_REQUIRE(nseg >= 1 && nseg <= MAX_SEGS, "vb_fused_allreduce_gd_emulated: %d segments (max %d)", nseg, MAX_SEGS);
+  VB_REQUIRE(channel >= 0 && channel < 64, "vb_fused_allreduce_gd_emulated: channel %d out of range", channel);
+  VB_REQUIRE(params_dev != nullptr, "vb_fused_allreduce_gd_emulated: parameter scratch is required");
+  if (n_ctas <= 0) n_ctas = 2;
+  static FusedParams host[MAX_WORLD];
+  for (int r = 0; r < world; ++r) {
+    FusedParams& p = host[r];
+    memset(&p, 0, sizeof(p));
+    p.world = world; p.rank = r; p.nseg = nseg; p.channel = channel;
+    for (int i = 0; i < nseg; ++i) {
+      p.seg[i].offset = segs[i * 6 + 0];
+      p.seg[i].numel = segs[i * 6 + 1];
+      p.seg[i].shadow_offset = segs[i * 6 + 2];
+      p.seg[i].row_len = static_cast<int>(segs[i * 6 + 3]);
+      p.seg[i].row_pitch = static_cast<int>(segs[i * 6 + 4]);
+      p.seg[i].flags = static_cast<int>(segs[i * 6 + 5]);
+      p.seg[i].lr = hyper[i * 4 + 0];
+      p.seg[i].wd = hyper[i * 4 + 1];
+      p.seg[i].l12 = hyper[i * 4 + 2];
+      p.seg[i].moment = hyper[i * 4 + 3];
+      VB_REQUIRE((p.seg[i].offset & 3) == 0, "vb_fused_allreduce_gd_emulated: segment offset must be a multiple of 4");
+    }
+    p.grads_local = grads[r]; p.grads_other_local = grads_other ? grads_other[r] : nullptr;
+    p.weights_local = weights[r]; p.vel_local = vel[r];
+    p.shadow_local = static_cast<__nv_bfloat16*>(shadow ? shadow[r] : nullptr);
+    for (int q = 0; q < world; ++q) {
+      p.grads_peer[q] = grads[q];
+      p.weights_peer[q] = weights[q];
+      p.shadow_peer[q] = static_cast<__nv_bfloat16*>(shadow ? shadow[q] : nullptr);
+      p.flags_peer[q] = flags[q];
+    }
+    p.flags_local = flags[r]; p.epochs = epochs[r]; p.cta_counter = cta_counter[r]; p.status = status[r];
+    p.grad_scale = grad_scale;
+    p.bcast_master = !((options >> 1) & 1);
+    p.bcast_shadow = !((options >> 2) & 1);
+    p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
+    p.phase = 0;
+  }
+  VB_CHECK_CUDA(cudaMemcpyAsync(params_dev, host, sizeof(FusedParams) * world, cudaMemcpyHostToDevice, stream));
+  VB_CHECK_CUDA(cudaStreamSynchronize(stream));   // `host` is reused by the next call
+  const FusedParams* ps = static_cast<const FusedParams*>(params_dev);
+  void* args[1] = {&ps};
+  VB_CHECK_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(fused_allreduce_gd_emulated_kernel),
+                                            dim3(n_ctas, world), dim3(FUSED_THREADS), args, 0, stream));
   return 0;
 }

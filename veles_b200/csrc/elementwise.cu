@@ -525,3 +525,30 @@ extern "C" int vb_cast(const void* in, int in_dtype, void* out, int out_dtype, l
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// factor_ortho regulariser of the Znicz GD units: grad[i,j] += f * (sums[j] - w[i,j])  (transposed: sums[i]).
+// `sums` holds the column (row) sums of the fp32 weight matrix; f already carries factor_ortho / n_rows.
+namespace vb {
+__global__ void ortho_grad_kernel(const float* __restrict__ w, float* __restrict__ grad, const float* __restrict__ sums,
+                                  long long rows, long long cols, long long ldw, long long ldg, float f,
+                                  int by_row) {
+  const long long n = rows * cols;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / cols, c = i - r * cols;
+    grad[r * ldg + c] += f * (sums[by_row ? r : c] - w[r * ldw + c]);
+  }
+}
+}  // namespace vb
+
+extern "C" int vb_ortho_grad(const float* w, long long ldw, float* grad, long long ldg, const float* sums, long long rows,
+                             long long cols, float f, int by_row, cudaStream_t s) {
+  VB_REQUIRE(rows > 0 && cols > 0, "vb_ortho_grad: empty matrix");
+  const long long n = rows * cols;
+  const long long cap = static_cast<long long>(vb::device_sm_count()) * 16;
+  long long blocks = (n + 255) / 256;
+  if (blocks > cap) blocks = cap;
+  vb::ortho_grad_kernel<<<static_cast<int>(blocks), 256, 0, s>>>(w, grad, sums, rows, cols, ldw, ldg, f, by_row);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

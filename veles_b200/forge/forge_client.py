@@ -1,5 +1,5 @@
-"""Forge client: ``veles_b200 forge <action>`` with actions list | details | fetch | upload | delete | register
-(reference: ``veles/forge/forge_client.py:91-799``)."""
+"""Forge client: ``veles_b200 forge <action>`` with actions list | details | fetch | upload | delete | register |
+confirm | unregister | assist (reference: ``veles/forge/forge_client.py:91-799``)."""
 from __future__ import annotations
 
 import argparse
@@ -35,6 +35,60 @@ class ForgeClient(Logger):
         self.token = json.loads(self._get("service", query="register", email=email))["token"]
         return self.token
 
+    def confirm(self, code):
+        return json.loads(self._get("service", query="confirm", token=self.token, code=code))["ok"]
+
+    def unregister(self):
+        """Revoke this token's write access (the packages it uploaded stay published)."""
+        res = json.loads(self._get("service", query="unregister", token=self.token))
+        self.token = None
+        return res["email"]
+
+    def assist(self, workflow_path, answers=None, ask=input):
+        """Create ``<name>/manifest.json`` next to a copy of the workflow (and its ``*_config.py``) so that the
+        directory can be uploaded (reference: ``forge_client.py:514-599``).  ``answers`` pre-fills fields; whatever is
+        missing is asked interactively through ``ask``."""
+        import shutil
+        answers = dict(answers or {})
+        workflow_path = os.path.abspath(workflow_path)
+        if not os.path.isfile(workflow_path):
+            raise FileNotFoundError(workflow_path)
+        base, modname = os.path.dirname(workflow_path), os.path.splitext(os.path.basename(workflow_path))[0]
+        # the Workflow subclass defined in the file names the package by default
+        default_name = modname
+        try:
+            import ast
+            with open(workflow_path) as f:
+                tree = ast.parse(f.read())
+            classes = [n.name for n in tree.body if isinstance(n, ast.ClassDef)
+                       and any("Workflow" in ast.unparse(b) for b in n.bases)]
+            if classes:
+                default_name = classes[-1]
+        except SyntaxError:
+            pass
+        fields = (("name", default_name), ("short_description", ""), ("long_description", ""),
+                  ("author", os.environ.get("USER", "")))
+        meta = {}
+        for key, default in fields:
+            val = answers.get(key)
+            if val is None:
+                val = ask("%s [%s]: " % (key.replace("_", " "), default)).strip() or default
+            meta[key] = val
+        cfg_src = answers.get("configuration") or os.path.join(base, modname + "_config.py")
+        dest = os.path.join(answers.get("directory", "."), meta["name"])
+        os.makedirs(dest, exist_ok=True)
+        shutil.copy(workflow_path, os.path.join(dest, os.path.basename(workflow_path)))
+        cfg_name = os.path.basename(cfg_src)
+        if os.path.isfile(cfg_src):
+            shutil.copy(cfg_src, os.path.join(dest, cfg_name))
+        else:
+            open(os.path.join(dest, cfg_name), "w").close()      # an empty configuration, as the reference does
+        meta.update(workflow=os.path.basename(workflow_path), configuration=cfg_name,
+                    requires=answers.get("requires", ["veles_b200"]))
+        with open(os.path.join(dest, "manifest.json"), "w") as f:
+            json.dump(meta, f, sort_keys=True, indent=4)
+        return dest, meta
+
     def fetch(self, name, directory=".", version=None):
         blob = self._get("fetch", name=name, version=version)
         dest = os.path.join(directory, name)
@@ -57,7 +111,10 @@ class ForgeClient(Logger):
 
 def main(argv=None):
     p = argparse.ArgumentParser(prog="veles_b200 forge")
-    p.add_argument("action", choices=["list", "details", "fetch", "upload", "delete", "register"])
+    p.add_argument("action", choices=["list", "details", "fetch", "upload", "delete", "register", "confirm", "unregister",
+                                      "assist"])
+    p.add_argument("-c", "--code", default=None, help="confirmation code (confirm)")
+    p.add_argument("-w", "--workflow", default=None, help="path to the workflow file (assist)")
     p.add_argument("-s", "--server", default=None)
     p.add_argument("-n", "--name", default=None)
     p.add_argument("-d", "--directory", default=".")
@@ -79,6 +136,12 @@ def main(argv=None):
         print(json.dumps(c.delete(a.name)))
     elif a.action == "register":
         print(c.register(a.email))
+    elif a.action == "confirm":
+        print(c.confirm(a.code))
+    elif a.action == "unregister":
+        print(c.unregister())
+    elif a.action == "assist":
+        print(c.assist(a.workflow, {"name": a.name, "directory": a.directory})[0])
     return 0
 
 

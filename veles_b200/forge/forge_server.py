@@ -18,8 +18,13 @@ from .forge_common import unpack, validate_manifest
 
 
 class ForgeServer(Logger):
-    def __init__(self, root_dir, host="127.0.0.1", port=0):
+    def __init__(self, root_dir, host="127.0.0.1", port=0, require_confirmation=False, mailer=None):
+        """``require_confirmation``: a new token stays pending until ``confirm(token, code)`` presents the code that
+        was mailed to the address (reference: ``forge_server.py:462-520``).  ``mailer(email, subject, body)`` delivers
+        it; the default writes ``outbox/<email>.txt`` under the storage root (no SMTP relay is assumed)."""
         super(ForgeServer, self).__init__()
+        self.require_confirmation = bool(require_confirmation)
+        self.mailer = mailer or self._outbox_mailer
         self.root_dir = os.path.abspath(root_dir)
         os.makedirs(self.root_dir, exist_ok=True)
         self.host, self.port = host, port
@@ -61,22 +66,74 @@ class ForgeServer(Logger):
         return {"name": name, "description": m.get("long_description", ""), "versions": ["v" + v for v in vs],
                 "manifest": m}
 
+    def _outbox_mailer(self, email, subject, body):
+        box = os.path.join(self.root_dir, "outbox")
+        os.makedirs(box, exist_ok=True)
+        safe = "".join(c if c.isalnum() or c in "@._-" else "_" for c in email)
+        with open(os.path.join(box, safe + ".txt"), "a") as f:
+            f.write("Subject: %s\n\n%s\n" % (subject, body))
+
+    def _save_tokens(self):
+        with open(self.tokens_file, "w") as f:
+            json.dump(self.tokens, f)
+
     def register(self, email):
+        if not email or "@" not in email:
+            raise ValueError("a valid e-mail address is required")
         with self.lock:
+            if any(t["email"] == email and not t.get("pending") for t in self.tokens.values()):
+                raise PermissionError("%s is already registered; unregister first" % email)
             token = str(uuid.uuid4())
-            self.tokens[token] = {"email": email, "time": time.time()}
-            with open(self.tokens_file, "w") as f:
-                json.dump(self.tokens, f)
+            rec = {"email": email, "time": time.time()}
+            if self.require_confirmation:
+                rec["pending"] = uuid.uuid4().hex[:8]
+            self.tokens[token] = rec
+            self._save_tokens()
+        if self.require_confirmation:
+            self.mailer(email, "VelesForge registration",
+                        "Confirmation code: %s\n(forge confirm -t %s -c %s)" % (rec["pending"], token, rec["pending"]))
         return token
 
-    def upload(self, token, blob):
-        if token not in self.tokens:
+    def confirm(self, token, code):
+        with self.lock:
+            rec = self.tokens.get(token)
+            if rec is None:
+                raise PermissionError("unknown token")
+            if rec.get("pending") and rec["pending"] != code:
+                raise PermissionError("wrong confirmation code")
+            rec.pop("pending", None)
+            self._save_tokens()
+        return True
+
+    def unregister(self, token):
+        """Revoke write access: the token dies; packages it uploaded stay published but can no longer be deleted or
+        superseded by it (reference: ``forge_client.py:601-621``)."""
+        with self.lock:
+            if token not in self.tokens:
+                raise PermissionError("unknown token")
+            rec = self.tokens.pop(token)
+            self._save_tokens()
+        return rec["email"]
+
+    def _active(self, token):
+        rec = self.tokens.get(token)
+        if rec is None:
             raise PermissionError("unknown token")
+        if rec.get("pending"):
+            raise PermissionError("registration of %s is not confirmed yet" % rec["email"])
+        return rec
+
+    def upload(self, token, blob):
+        self._active(token)
         tmp = os.path.join(self.root_dir, "incoming-%s" % uuid.uuid4().hex)
         try:
             manifest = validate_manifest(unpack(blob, tmp))
             with self.lock:
                 vs = self.versions(manifest["name"])
+                if vs:
+                    with open(os.path.join(self.model_dir(manifest["name"]), vs[-1], "owner")) as f:
+                        if f.read() != self.tokens[token]["email"]:
+                            raise PermissionError("%s belongs to another author" % manifest["name"])
                 version = str(int(vs[-1]) + 1 if vs else 1)
                 dest = os.path.join(self.model_dir(manifest["name"]), version)
                 os.makedirs(os.path.dirname(dest), exist_ok=True)
@@ -104,7 +161,7 @@ class ForgeServer(Logger):
             raise KeyError(name)
         with open(os.path.join(d, vs[-1], "owner")) as f:
             owner = f.read()
-        if self.tokens.get(token, {}).get("email") != owner:
+        if self._active(token)["email"] != owner:
             raise PermissionError("only the uploader may delete a model")
         shutil.rmtree(d)
 
@@ -146,6 +203,10 @@ class ForgeServer(Logger):
                         return self._guard(lambda: self._send(200, srv.details(q.get("name"))))
                     if kind == "register":
                         return self._guard(lambda: self._send(200, {"token": srv.register(q.get("email", "?"))}))
+                    if kind == "confirm":
+                        return self._guard(lambda: self._send(200, {"ok": srv.confirm(q.get("token"), q.get("code"))}))
+                    if kind == "unregister":
+                        return self._guard(lambda: self._send(200, {"email": srv.unregister(q.get("token"))}))
                     if kind == "delete":
                         return self._guard(lambda: (srv.delete(q.get("token"), q.get("name")),
                                                     self._send(200, {"ok": True})))

@@ -121,7 +121,8 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
         parser.add_argument("-i", "--log-id", type=str, default="", help="Log session identifier.")
         parser.add_argument("--result-file", type=str, default="", help="Write the results JSON here.")
         parser.add_argument("--manhole", default=False, action="store_true",
-                            help="Open a local debugging REPL socket (SIGUSR2).")
+                            help="Run the embedded interactive shell on the UNIX socket /tmp/manhole-<pid> "
+                                 "(also opened on demand by SIGUSR2); attach with python -m veles_b200.manhole <pid>.")
         return parser
 
     # -- mode -------------------------------------------------------------------------------------------------
@@ -264,6 +265,12 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
         self._start_time = time.time()
         self._running = True
         self._finished.clear()
+        from .thread_pool import ThreadPool
+        ThreadPool.manhole_context = {"workflow": self.workflow, "launcher": self}
+        if getattr(self.args, "manhole", False):
+            from . import manhole
+            self.info("manhole listening on %s (python -m veles_b200.manhole %d)",
+                      manhole.install(workflow=self.workflow, launcher=self), os.getpid())
         if not self.args.stealth and get(root.common.web.host, None) and self.is_master:
             self._start_notifier()
         try:

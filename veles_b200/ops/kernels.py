@@ -450,6 +450,16 @@ def gd_update(w, grad, vel=None, acc=None, w_bf16=None, *, lr, wd=0.0, l1_vs_l2=
     LAUNCHES[0] += 1
 
 
+def ortho_grad(w2, grad2, sums, f, by_row=False):
+    """grad2[i,j] += f * (sums[j] - w2[i,j])  (``by_row``: sums[i]): the factor_ortho regulariser of the GD units."""
+    assert w2.dtype == torch.float32 and grad2.dtype == torch.float32 and w2.shape == grad2.shape
+    rc = _lib.lib().vb_ortho_grad(_p(w2), c_longlong(_ld(w2)), _p(grad2), c_longlong(_ld(grad2)), _p(sums),
+                                  c_longlong(w2.shape[0]), c_longlong(w2.shape[1]), c_float(f), c_int(int(by_row)),
+                                  _stream())
+    _lib.check(rc, "vb_ortho_grad")
+    LAUNCHES[0] += 1
+
+
 def cast(inp, out):
     rc = _lib.lib().vb_cast(_p(inp), c_int(_dt(inp)), _p(out), c_int(_dt(out)), c_longlong(inp.numel()), _stream())
     _lib.check(rc, "vb_cast")

@@ -51,7 +51,8 @@ class DataParallel(object):
         # of multimem.ld_reduce at ~64 KB in flight per SM) for 2 ranks, 4 SMs beyond.
         self.n_ctas = int(n_ctas) if n_ctas else (8 if self.world_size <= 2 else 4)
         self.n_ctas = max(2, (self.n_ctas + 1) & ~1)
-        self.bucket_bytes = int(bucket_bytes)
+        # peer-TMA delivery describes ONE layer's weight matrix per launch: no bucketing there
+        self.bucket_bytes = 0 if weight_delivery == "peer_tma" else int(bucket_bytes)
         self.buckets = []          # launch units: lists of GD units exchanged by one kernel, in backward order
         self.bucket_of = {}
         self._reserved = False
@@ -323,9 +324,13 @@ class DataParallel(object):
         hyper = []
         for gd, kind in b["kinds"]:
             if kind == "weights":
-                hyper += [gd.learning_rate, gd.weights_decay, gd.l1_vs_l2, gd.gradient_moment]
+                lr, mom = gd.eff(gd.learning_rate, gd.gradient_moment) if hasattr(gd, "eff") else (
+                    gd.learning_rate, gd.gradient_moment)
+                hyper += [lr, gd.weights_decay, gd.l1_vs_l2, mom]
             else:
-                hyper += [gd.learning_rate_bias, gd.weights_decay_bias, gd.l1_vs_l2_bias, gd.gradient_moment_bias]
+                lr, mom = gd.eff(gd.learning_rate_bias, gd.gradient_moment_bias) if hasattr(gd, "eff") else (
+                    gd.learning_rate_bias, gd.gradient_moment_bias)
+                hyper += [lr, gd.weights_decay_bias, gd.l1_vs_l2_bias, mom]
         hyper = (c_float * (4 * nseg))(*hyper)
         g_local, g_mc, g_peers = b["grads"][self.parity]
         go_local = b["grads"][1 - self.parity][0]

@@ -73,3 +73,134 @@ class FlatStep(object):
     def invalidate(self):
         self.graphs.clear()
         self.eager_steps.clear()
+
+
+class GraphedChain(object):
+    """A run of device units of a workflow that is walked by the ordinary unit scheduler (``Workflow.run()``, the
+    ``veles`` command line) but executes as ONE replayed CUDA graph.
+
+    The scheduler still visits every unit, evaluates its gates and notifies its successors; only the ``run()`` calls
+    change: the chain's first unit runs (or replays) the whole chain, the others find their work already done.  A
+    chain is valid for one signature - minibatch size, the GD hyper-parameters, the data-parallel gradient parity -
+    and falls back to running its units one by one whenever capture fails (a unit that synchronises or allocates).
+    This is what replaces the per-minibatch cost of the reference's scheduler on the public CLI path
+    (``/root/reference/veles/units.py:485-505, 782-803``): gates keep deciding WHAT runs at class / epoch boundaries,
+    the steady-state sequence inside a class is resolved once and replayed.
+    """
+
+    WARMUP = 2
+
+    def __init__(self, workflow, units, name="chain"):
+        self.wf = workflow
+        self.units = list(units)
+        self.name = name
+        self.graphs = {}
+        self.eager_runs = {}
+        self.enabled = True
+        self.replays = 0
+        self.captures = 0
+        self._done = set()
+        for u in self.units:
+            u.graph_chain_ = self
+
+    def _signature(self):
+        wf = self.wf
+        hyper = tuple((u.learning_rate, u.learning_rate_bias, u.weights_decay, u.gradient_moment,
+                       getattr(u, "weights_decay_bias", 0.0), getattr(u, "gradient_moment_bias", 0.0))
+                      for u in self.units if hasattr(u, "learning_rate"))
+        dp = getattr(wf, "dp_group_", None)
+        loader = getattr(wf, "loader", None)
+        return (int(loader.minibatch_size) if loader is not None else 0,
+                int(getattr(loader, "minibatch_class", 0) or 0) if loader is not None else 0,
+                hyper, getattr(dp, "parity", 0))
+
+    def _run_all(self):
+        for u in self.units:
+            u.run()
+
+    def run_member(self, unit):
+        """Called by the scheduler instead of ``unit.run()``."""
+        if unit is not self.units[0]:
+            if id(unit) in self._done:
+                self._done.discard(id(unit))      # executed with the head of the chain
+                return
+            unit.run()                            # the head was gated off this pass: plain behaviour
+            return
+        if not self.enabled:
+            unit.run()
+            return
+        import torch
+        self._done = set(id(u) for u in self.units[1:] if not u.gate_skip and not u.gate_block)
+        # every member must be due this pass; otherwise run unit by unit
+        if len(self._done) != len(self.units) - 1:
+            self._done = set()
+            unit.run()
+            return
+        key = self._signature()
+        g = self.graphs.get(key)
+        if g is not None:
+            g.replay()
+            self.replays += 1
+            return
+        n = self.eager_runs.get(key, 0)
+        if n < self.WARMUP:
+            self.eager_runs[key] = n + 1
+            self._run_all()
+            return
+        try:
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._run_all()
+        except Exception as e:   # a unit that cannot be captured: stay correct, stay eager
+            self.enabled = False
+            self.wf.warning("CUDA-graph replay of the %s chain is off (%s: %s)", self.name, type(e).__name__, e)
+            torch.cuda.synchronize()
+            self._run_all()
+            return
+        self.captures += 1
+        self.graphs[key] = g
+        if len(self.graphs) > 8:
+            self.graphs.pop(next(iter(self.graphs)))
+        g.replay()
+        self.replays += 1
+        if self.captures >= 16 and self.replays < 4 * self.captures:
+            # the signature changes nearly every minibatch (a per-iteration learning-rate schedule): capturing
+            # costs more than it saves
+            self.enabled = False
+            self.graphs.clear()
+
+    def invalidate(self):
+        self.graphs.clear()
+        self.eager_runs.clear()
+
+
+def install_graph_replay(wf):
+    """Chains of a StandardWorkflow on a CUDA device: [forwards..., evaluator] and [GD units in backward order].
+    Returns the chains (empty when the workflow does not qualify).  ``root.common.engine.graph_replay = False``
+    switches it off."""
+    from ..config import root, get
+    device = getattr(wf, "device", None)
+    if device is None or not getattr(device, "exists", False) or not get(root.common.engine.graph_replay, True):
+        return []
+    if getattr(wf, "is_slave", False) or getattr(wf, "is_master", False):
+        return []      # job-level master-slave runs exchange host arrays around every minibatch
+    forwards, gds = list(getattr(wf, "forwards", []) or []), list(getattr(wf, "gds", []) or [])
+    evaluator = getattr(wf, "evaluator", None)
+    chains = []
+
+    def consecutive(units):
+        """Each unit must be the only successor-in-chain of its predecessor: the scheduler then visits them in order."""
+        for a, b in zip(units, units[1:]):
+            if a not in b.links_from:
+                return False
+        return all(getattr(u, "on_device", True) is not False for u in units)
+
+    fwd_units = forwards + ([evaluator] if evaluator is not None else [])
+    if len(fwd_units) > 1 and consecutive(fwd_units):
+        chains.append(GraphedChain(wf, fwd_units, "forward"))
+    bwd_units = [g for g in reversed(gds) if g is not None]
+    if len(bwd_units) > 1 and consecutive(bwd_units):
+        chains.append(GraphedChain(wf, bwd_units, "backward"))
+    wf.graph_chains_ = chains
+    return chains

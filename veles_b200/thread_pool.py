@@ -190,6 +190,17 @@ class ThreadPool(Logger):
             ThreadPool._sigint_installed = True
         if hasattr(signal, "SIGUSR1"):
             signal.signal(signal.SIGUSR1, ThreadPool.sigusr1_handler)
+        if hasattr(signal, "SIGUSR2"):
+            signal.signal(signal.SIGUSR2, ThreadPool.sigusr2_handler)
+
+    manhole_context = {}    # what the manhole's namespace shows: set by the launcher (workflow=..., launcher=...)
+
+    @staticmethod
+    def sigusr2_handler(signum, frame):
+        """Open the manhole on demand (reference: veles/thread_pool.py:527-533)."""
+        from . import manhole
+        path = manhole.install(**ThreadPool.manhole_context)
+        print("SIGUSR2: manhole listening on %s" % path, file=sys.stderr)
 
     @staticmethod
     def sigusr1_handler(signum, frame):

@@ -534,7 +534,11 @@ class Unit(Distributable, Verified, metaclass=UnitRegistry):
                 if not self._is_initialized:
                     self.error("%s is not initialized", self.name)
                     raise NotInitializedError(self, "%s is not initialized" % self)
-                self.run()
+                chain = self.__dict__.get("graph_chain_")
+                if chain is not None:
+                    chain.run_member(self)     # CUDA-graph replay of a steady-state unit sequence (parallel/step.py)
+                else:
+                    self.run()
             finally:
                 self._run_lock_.release()
         self.run_dependent()

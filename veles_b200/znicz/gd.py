@@ -120,6 +120,7 @@ class GradientDescent(GradientDescentBase):
         # separate update already finds the freshly written gradient in the 126 MB L2 -> off by default.
         from ..config import root, get
         self.fused_gd_ = bool(self.dw_store_ and self.solver_code == 0 and not self.accumulate_gradient and
+                              not self.factor_ortho and
                               not self.transposed_ and
                               self.forward is not None and getattr(self.forward, "weights_bf16_", None) is not None and
                               get(root.common.engine.fuse_gd_update, False))
@@ -212,8 +213,8 @@ class GradientDescent(GradientDescentBase):
         if fused:
             w2d = self.weights.devmem.view(w_bf16.shape[0], -1)
             kernels.gemm_fused_gd(eo, x, w2d, self.gradient_weights_with_moment.devmem.view(w2d.shape), w_bf16,
-                                  lr=self.learning_rate, wd=self.weights_decay, l1_vs_l2=self.l1_vs_l2,
-                                  moment=self.gradient_moment)
+                                  lr=self.eff(self.learning_rate, 0)[0], wd=self.weights_decay, l1_vs_l2=self.l1_vs_l2,
+                                  moment=self.eff(0, self.gradient_moment)[1])
             self.weights.mark_device_written()
             self.gradient_weights_with_moment.mark_device_written()
         elif self.dw_store_:

@@ -430,8 +430,29 @@ class GradientDescentBase(GDBase):
         return int(bs)
 
     # -- numpy oracle of the update rule -----------------------------------------------------------------------
+    def eff(self, lr, moment):
+        """(learning rate, momentum) after the Znicz variant switches: ``variant_gradient = False`` drops the plain
+        gradient step (the weights then only coast on their momentum), ``variant_moment_gradient = False`` drops the
+        momentum term."""
+        return (lr if self.variant_gradient else 0.0), (moment if self.variant_moment_gradient else 0.0)
+
+    def ortho_term(self, w):
+        """``factor_ortho`` regulariser (decorrelates the rows of a weight matrix): every row is pulled towards the
+        sum of the OTHER rows' negatives, ``g_i += factor_ortho / n_rows * (sum_k w_k - w_i)``.  Weights only
+        (2-D); the transposed layout sums along the other axis."""
+        if not self.factor_ortho or w.ndim != 2:
+            return None
+        transposed = bool(getattr(self.forward, "weights_transposed", False)) if self.forward is not None else False
+        if transposed:
+            return (w.sum(axis=1, keepdims=True) - w) * (self.factor_ortho / w.shape[1])
+        return (w.sum(axis=0, keepdims=True) - w) * (self.factor_ortho / w.shape[0])
+
     def numpy_update(self, w, g, vel, acc, lr, wd, l12, moment):
+        lr, moment = self.eff(lr, moment)
         g = g + wd * ((1.0 - l12) * w + 0.5 * l12 * numpy.sign(w))
+        ortho = self.ortho_term(w)
+        if ortho is not None:
+            g = g + ortho
         solver = self.solver_code
         if solver == 0:
             vel[...] = moment * vel - lr * g
@@ -447,21 +468,13 @@ class GradientDescentBase(GDBase):
             w += d
 
     def warn_inert_options(self):
-        """Znicz hyper-parameters that are accepted (configurations written for the reference load unchanged) but have
-        no effect here - said once per unit instead of silently."""
-        if getattr(self, "_inert_warned_", False):
-            return
-        self._inert_warned_ = True
-        inert = []
-        if self.factor_ortho:
-            inert.append("factor_ortho=%r" % self.factor_ortho)
+        """``fast_learning_rate`` is the one Znicz hyper-parameter whose meaning the checkout does not document
+        (``manualrst_veles_workflow_parameters.rst:556-578`` only lists the name): a run that sets it is refused
+        rather than trained with a silently different rule."""
         if self.fast_learning_rate is not None:
-            inert.append("fast_learning_rate=%r" % self.fast_learning_rate)
-        if not self.variant_gradient or not self.variant_moment_gradient:
-            inert.append("variant_gradient / variant_moment_gradient=False")
-        if inert:
-            self.warning("%s: %s accepted for compatibility, but this option has no effect in veles_b200",
-                         self.name, ", ".join(inert))
+            raise ValueError("%s: fast_learning_rate=%r is not supported (its semantics are not documented in the "
+                             "reference checkout); remove it from the layer's '<-' parameters"
+                             % (self.name, self.fast_learning_rate))
 
     def _ensure_state(self, like, vel, acc):
         self.warn_inert_options()
@@ -519,9 +532,9 @@ class GradientDescentBase(GDBase):
                 and self.gradient_bias_with_moment.devmem is not None
                 and get(root.common.engine.fuse_bias_update, True))
         if fuse:
+            lr_b, mom_b = self.eff(self.learning_rate_bias, self.gradient_moment_bias)
             kernels.col_sum_gd(eo2, gb_t, self.col_scratch_, self.bias.devmem, self.gradient_bias_with_moment.devmem,
-                               lr=self.learning_rate_bias, wd=self.weights_decay_bias, l1_vs_l2=self.l1_vs_l2_bias,
-                               moment=self.gradient_moment_bias)
+                               lr=lr_b, wd=self.weights_decay_bias, l1_vs_l2=self.l1_vs_l2_bias, moment=mom_b)
             self.bias.mark_device_written()
             self.gradient_bias_with_moment.mark_device_written()
         else:
@@ -529,12 +542,42 @@ class GradientDescentBase(GDBase):
             self.gradient_bias.mark_device_written()
         self.bias_updated_ = fuse
 
+    def device_ortho(self):
+        """Device form of :meth:`ortho_term`: adds the regulariser to the weight gradient of this step (column sums of
+        the fp32 master, then one element-wise pass).  In a data-parallel group the exchanged gradients are summed,
+        so each rank contributes its share."""
+        if not self.factor_ortho or self.weights is None or not self.weights:
+            return
+        import torch
+        from ..ops import kernels
+        gw_t, _ = self.grad_tensors()
+        rows = self.weights.shape[0]
+        w2 = self.weights.devmem.view(rows, -1)
+        g2 = gw_t.view(rows, -1)
+        transposed = bool(getattr(self.forward, "weights_transposed", False)) if self.forward is not None else False
+        share = 1.0
+        dp = self.dp_group_
+        if dp is not None and getattr(dp, "mode", "") != "host" and getattr(dp, "grad_scale", 1.0) == 1.0:
+            share = 1.0 / dp.world_size
+        if getattr(self, "_ortho_sums_", None) is None:
+            self._ortho_sums_ = torch.zeros(w2.shape[0] if transposed else w2.shape[1], dtype=torch.float32,
+                                            device=w2.device)
+            self._ortho_scratch_ = torch.empty(kernels.col_sum_scratch_elems(w2.shape[0], w2.shape[1]),
+                                               dtype=torch.float32, device=w2.device)
+        if transposed:
+            kernels.row_sum(w2, self._ortho_sums_)
+        else:
+            kernels.col_sum(w2, self._ortho_sums_, self._ortho_scratch_)
+        kernels.ortho_grad(w2, g2, self._ortho_sums_, self.factor_ortho * share / (w2.shape[1] if transposed
+                                                                                   else w2.shape[0]), transposed)
+
     def device_update(self, forward=None, skip_weights=False):
         """U1: fused single-GPU GD step on weights and bias (or hand over to the DP group).  ``skip_weights``: the
         weight-gradient GEMM already applied the step in its epilogue (``kernels.gemm_fused_gd``)."""
         from ..ops import kernels
         if not self.apply_gradient:
             return
+        self.device_ortho()
         if self.dp_group_ is not None:
             self.dp_group_.update_unit(self)
             return
@@ -548,8 +591,9 @@ class GradientDescentBase(GDBase):
             kernels.gd_update(self.weights.devmem, self.gradient_weights.devmem,
                               self.gradient_weights_with_moment.devmem,
                               self.accumulated_gradient_weights.devmem if self.accumulated_gradient_weights else None,
-                              w_shadow, lr=self.learning_rate, wd=self.weights_decay, l1_vs_l2=self.l1_vs_l2,
-                              moment=self.gradient_moment, solver=solver, eps=eps, rho=rho,
+                              w_shadow, lr=self.eff(self.learning_rate, 0)[0], wd=self.weights_decay,
+                              l1_vs_l2=self.l1_vs_l2, moment=self.eff(0, self.gradient_moment)[1], solver=solver,
+                              eps=eps, rho=rho,
                               zero_grad=not getattr(self, "dw_store_", False))
             if shadow is not None and w_shadow is None:
                 kernels.copy_2d(self.weights.devmem.view(shadow.shape[0], -1), shadow)
@@ -559,8 +603,9 @@ class GradientDescentBase(GDBase):
         if self.bias is not None and self.bias and not bias_done:
             kernels.gd_update(self.bias.devmem, self.gradient_bias.devmem, self.gradient_bias_with_moment.devmem,
                               self.accumulated_gradient_bias.devmem if self.accumulated_gradient_bias else None,
-                              None, lr=self.learning_rate_bias, wd=self.weights_decay_bias,
-                              l1_vs_l2=self.l1_vs_l2_bias, moment=self.gradient_moment_bias, solver=solver, eps=eps,
+                              None, lr=self.eff(self.learning_rate_bias, 0)[0], wd=self.weights_decay_bias,
+                              l1_vs_l2=self.l1_vs_l2_bias, moment=self.eff(0, self.gradient_moment_bias)[1],
+                              solver=solver, eps=eps,
                               rho=rho, zero_grad=True)
             self.bias.mark_device_written()
             self.gradient_bias_with_moment.mark_device_written()

@@ -666,7 +666,12 @@ class StandardWorkflow(StandardWorkflowBase):
         return wf
 
     def initialize(self, device=None, **kwargs):
-        return super(StandardWorkflow, self).initialize(device=device, **kwargs)
+        res = super(StandardWorkflow, self).initialize(device=device, **kwargs)
+        if not res:
+            # steady-state unit sequences replay as CUDA graphs under the ordinary scheduler (wf.run(), the CLI)
+            from ..parallel.step import install_graph_replay
+            install_graph_replay(self)
+        return res
 
 
 class ForwardWorkflow(StandardWorkflowBase):
