@@ -41,6 +41,8 @@ def parse():
     p.add_argument("--min-seconds", type=float, default=0.0,
                    help="repeat the timed region (in whole multiples of --steps) until it has run this long: sustained "
                         "clocks instead of a burst")
+    p.add_argument("--fc-split-k", action="store_true",
+                   help="small-batch fully connected layers: split-K GEMM into an fp32 scratch + bias/activation pass")
     p.add_argument("--ps-async", action="store_true", help="ps_emulation: two jobs in flight per slave (--async-slave)")
     p.add_argument("--model", default="alexnet")
     p.add_argument("--batch", type=int, default=0, help="per-GPU minibatch (default: model's)")
@@ -131,6 +133,9 @@ def main():
     if args.gemm_schedule == "clc":
         from veles_b200.ops import kernels as _k
         _k.set_dynamic_schedule(True)
+    if args.fc_split_k:
+        from veles_b200.config import root as _root
+        _root.common.engine.two_phase_split_k = True
     cfg = MODEL_CONFIGS[args.model]
     B = args.batch or cfg["minibatch"]
     device = B200Device(index=local_rank)

@@ -223,6 +223,45 @@ int vb_rnn_cell_forward(const float* z, long long ldz, float* h_save, void* h_ne
 int vb_rnn_cell_backward(const void* dh_ext, int ext_dtype, long long ld_ext, const float* dh_rec, long long ld_rec,
                          const float* h_save, void* dz, long long ld_dz, int B, int H, cudaStream_t stream);
 
+/* ---- data-parallel exchange (csrc/comm_fused.cu): gradient all-reduce FUSED with the Znicz GD update and the
+ * updated-weight broadcast, one launch per bucket of layers; replaces the master-slave exchange of
+ * veles/server.py:141-169, 401-430 + veles/client.py:138-160, 333-342 + veles/workflow.py:513-529.
+ * All slabs are symmetric memory (same offsets on every rank); *_mc are NVLS multicast aliases (or null),
+ * *_peer arrays hold `world` device pointers.  segs: nseg x {offset, numel, shadow_offset, row_len, row_pitch,
+ * flags} (flags bit 0: zero the other parity's gradients; bit 1: always publish the fp32 master); hyper: nseg x
+ * {lr, wd, l1_vs_l2, moment}.  use_multimem bits: 0 multimem path, 1 sharded fp32 master, 2 shadow stays on its
+ * owner (peer-TMA delivery), 3 handshake in its own 1-CTA launch.  n_ctas is rounded up to whole 2-CTA clusters. */
+int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg, const long long* segs, const float* hyper,
+                          float* grads_local, float* grads_mc, float** grads_peer, float* grads_other_local,
+                          float* weights_local, float* weights_mc, float** weights_peer, float* vel_local,
+                          void* shadow_local, void* shadow_mc, void** shadow_peer, unsigned int* flags_local,
+                          unsigned int** flags_peer, unsigned int* epochs, unsigned int* cta_counter, int* status,
+                          float grad_scale, int n_ctas, int use_multimem, double timeout_s, cudaStream_t stream);
+/* The same kernel body with every rank emulated on the current GPU by one cooperative launch (blockIdx.y = rank,
+ * P2P path): how a single-GPU box tests the flag protocol and the slice arithmetic.  params_dev: device scratch of
+ * world * vb_fused_params_bytes() bytes.  No counterpart in the reference. */
+long long vb_fused_params_bytes(void);
+int vb_fused_allreduce_gd_emulated(int world, int channel, int nseg, const long long* segs, const float* hyper,
+                                   float** grads, float** grads_other, float** weights, float** vel, void** shadow,
+                                   unsigned int** flags, unsigned int** epochs, unsigned int** cta_counter,
+                                   int** status, float grad_scale, int n_ctas, int options, double timeout_s,
+                                   void* params_dev, cudaStream_t stream);
+/* SMs that the persistent tcgen05 kernels leave free from now on (0 = none): the exchange kernel runs there beside
+ * the backward pass.  Read at launch / graph-capture time; returns the previous value. */
+int vb_set_sm_reserve(int n);
+
+/* Max-pooling backward (3x3 / stride 2, byte argmax) fused into LRN backward (bf16 NHWC): the dense gradient of the
+ * LRN output is neither written nor read.  Returns 1 when the geometry is not covered (run the two kernels). */
+int vb_lrn_pool_backward(const void* x, const void* dpool, const unsigned char* offs8, void* dx, int B, int H, int W,
+                         int C, int OH, int OW, int ky, int kx, int sy, int sx, int n, float alpha, float beta, float k,
+                         int deriv, cudaStream_t stream);
+/* factor_ortho regulariser of the Znicz GD units: grad[i,j] += f * (sums[j] - w[i,j])  (by_row: sums[i]). */
+int vb_ortho_grad(const float* w, long long ldw, float* grad, long long ldg, const float* sums, long long rows,
+                  long long cols, float f, int by_row, cudaStream_t stream);
+/* Halo-tile convolution tuning / test hook: sub-tiles per CTA tile (0 = choose, 1, 2); resident weights (-1 = choose,
+ * 0 = never, 1 = whenever they fit). */
+int vb_conv_halo_set_options(int mt, int resident);
+
 #ifdef __cplusplus
 }
 #endif

@@ -766,6 +766,32 @@ def test_lrn_vector_paths(C, n):
     assert rel_err(dx, xr.grad * (x > 0).double()) < 2e-2
 
 
+@pytest.mark.parametrize("B,H,W,C,n", [(3, 13, 13, 96, 5), (2, 27, 27, 256, 5), (2, 8, 9, 40, 3), (1, 7, 7, 8, 9)])
+def test_pool_backward_fused_into_lrn_backward(B, H, W, C, n):
+    """One kernel = max-pooling backward (3x3 / 2, byte argmax) followed by LRN backward with the strict-ReLU
+    derivative, vs the two separate kernels (each of which is checked against autograd on its own)."""
+    k = K()
+    torch.manual_seed(B * H + C)
+    alpha, beta, kk = 0.3, 0.75, 1.5
+    x = torch.randn(B, H, W, C, device=dev()).bfloat16()
+    y = torch.empty_like(x)
+    k.lrn_forward(x, y, n, alpha, beta, kk)
+    OH, OW = (H - 3 + 1) // 2 + 1, (W - 3 + 1) // 2 + 1          # ceil mode, as the pooling units compute it
+    p = torch.empty(B, OH, OW, C, device=dev(), dtype=torch.bfloat16)
+    offs8 = torch.zeros(B, OH, OW, C, device=dev(), dtype=torch.uint8)
+    assert k.pool_forward_local(k.POOL_KINDS["max"], y, p, None, offs8, 3, 3, 2, 2)
+    dp = torch.randn_like(p)
+    # reference: the two kernels in sequence
+    dy = torch.zeros_like(x)
+    assert k.pool_backward_local(k.POOL_KINDS["max"], dp, offs8, dy, 3, 3, 2, 2)
+    dx_ref = torch.empty_like(x)
+    k.lrn_backward(x, dy, dx_ref, n, alpha, beta, kk, deriv=4)
+    dx = torch.full((B * H * W + 2, C), float("nan"), device=dev(), dtype=torch.bfloat16)
+    assert k.lrn_pool_backward(x, dp, offs8, dx[:B * H * W].view(B, H, W, C), 3, 3, 2, 2, n, alpha, beta, kk, deriv=4)
+    assert rel_err(dx[:B * H * W].view_as(x), dx_ref) < 2e-2
+    assert torch.isnan(dx[B * H * W:].float()).all()
+
+
 @pytest.mark.parametrize("N", [10, 1000])
 @pytest.mark.parametrize("in_dtype", [torch.float32, torch.bfloat16])
 def test_softmax_evaluator(N, in_dtype):

@@ -21,7 +21,10 @@
 
 namespace vb {
 
-constexpr int HALO_THREADS = 320;   // producer warp, MMA warp, 8 epilogue warps
+constexpr int HALO_THREADS = 320;   // 8 epilogue warps, producer warp, MMA warp (roles in the highest warps: see
+                                    // gemm_tcgen05.cu)
+constexpr int PRODUCER_WARP = 8;
+constexpr int MMA_WARP = 9;
 constexpr int HALO_A_SLOT = 32768;  // <= 256 rows x 128 B
 constexpr int HALO_EPI_BYTES = 8 * 4096;
 
@@ -42,7 +45,13 @@ struct HaloParams {
   const __nv_bfloat16* Z;  // optional [pixels, N] (pixel pitch ldz): D *= f'(Z)
   long long ldz;
   int deriv;
+  long long* trace;        // profiling (vb_conv_halo_set_trace): CTA 0 records clock64 stamps of its first tiles here
 };
+
+// Trace layout: TRACE_TILES tiles x 8 stamps: [0] MMA thread starts waiting for the accumulator, [1] has it,
+// [2] activation tile present, [3] all MMAs of the tile issued, [4] epilogue warp 0 starts waiting for the tile,
+// [5] tile complete in tensor memory, [6] epilogue warp 0 done, [7] producer issued the tile's activation load.
+constexpr int TRACE_TILES = 24;
 
 template <int ACT>
 __device__ __forceinline__ void halo_apply_act(float (&f)[32]) {
@@ -76,7 +85,11 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
   constexpr int B_STAGES = S::B_STAGES;
   constexpr int A_SLOTS = S::A_SLOTS;
   constexpr int ACC_STRIDE = (BN <= 64) ? 64 : (BN <= 128 ? 128 : 256);   // TMEM columns per accumulator
-  constexpr int TMEM_NEED = 2 * MT * ACC_STRIDE;
+  // Accumulation chains (see gemm_tcgen05.cu): a dependent tcgen05.mma waits ~170 cycles for its predecessor, so the
+  // MMAs of a sub-tile rotate over KS accumulators which the epilogue adds, and consecutive MMAs alternate between
+  // sub-tiles: MT * KS independent chains, MT * KS * ACC_STRIDE = 256 columns in flight.
+  constexpr int KS = 256 / (MT * ACC_STRIDE) < 1 ? 1 : 256 / (MT * ACC_STRIDE);
+  constexpr int TMEM_NEED = 2 * MT * KS * ACC_STRIDE;
   constexpr int TMEM_COLS = TMEM_NEED <= 64 ? 64 : (TMEM_NEED <= 128 ? 128 : (TMEM_NEED <= 256 ? 256 : 512));
   static_assert(TMEM_NEED <= 512, "accumulators exceed tensor memory");
 
@@ -96,7 +109,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  if (warp == 0 && elect_one()) {
+  if (warp == PRODUCER_WARP && elect_one()) {
     tma_prefetch_desc(&tma_x);
     tma_prefetch_desc(&tma_w);
     tma_prefetch_desc(&tma_d);
@@ -115,7 +128,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     fence_barrier_init();
     fence_proxy_async_smem();
   }
-  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_ptr);
+  if (warp == MMA_WARP) tmem_alloc<TMEM_COLS>(tmem_ptr);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -126,7 +139,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
 
   // The two single-thread roles are bound by their own instruction streams (ncu source view): no divisions and no
   // descriptor construction inside the tap loops - tap coordinates and descriptors advance by increments.
-  if (warp == 0) {
+  if (warp == PRODUCER_WARP) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       int b_stage = 0, a_par = 0;
@@ -151,6 +164,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
                         oh0 + mt * p.R + p.low_h, img);
           }
           a_par ^= 1;
+          if (p.trace != nullptr && blockIdx.x == 0 && cb == 0) {
+            const int ti = (tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x);
+            if (ti < TRACE_TILES) p.trace[ti * 8 + 7] = clock64();
+          }
           if (p.resident && !first) continue;   // the weights are already in shared memory
           // weight column of window offset (r, s): tap (r, s), or the mirrored tap (ky-1-r, kx-1-s) = taps-1-tap
           int wcol = wtap_first * p.cg + (B_MN ? nb * BN : cb * 64);
@@ -174,7 +191,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == MMA_WARP) {
     // ===================== MMA issuer: ONE thread runs the whole loop =====================
     if (elect_one()) {
       int b_stage = 0, acc = 0, a_par = 0;
@@ -205,13 +222,17 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         int n_mma = p.N - nb * BN;
         n_mma = (B_MN || n_mma >= BN) ? BN : ((n_mma + 15) & ~15);
         const uint32_t idesc = make_idesc(/*BF16*/ 1, false, B_MN, 128, n_mma);
+        const int ti = (tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x);
+        const bool tr = p.trace != nullptr && blockIdx.x == 0 && ti < TRACE_TILES;
+        if (tr) p.trace[ti * 8 + 0] = clock64();
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
+        if (tr) p.trace[ti * 8 + 1] = clock64();
         if (p.resident) {
           b_stage = 0;
           b_desc = b_desc_s0;
         }
-        uint32_t accf = 0u;
+        uint32_t issued = 0;   // MMAs issued per sub-tile in this tile
         for (int cb = 0; cb < p.cblocks; ++cb) {
           const int ksteps = (cb == p.cblocks - 1) ? p.ksteps_last : 4;
 #pragma unroll
@@ -221,22 +242,26 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             mbar_wait(&a_full[slot], (a_phase_bits >> slot) & 1u);
             a_phase_bits ^= 1u << slot;
           }
+          if (tr && cb == 0) p.trace[ti * 8 + 2] = clock64();
           uint64_t a_desc = a_desc_s0 + static_cast<uint64_t>(a_par * MT) * A_SLOT_STEP;   // window of tap (0, 0)
           int s = 0;
           for (int tap = 0; tap < taps; ++tap) {
             if (!p.resident || first) mbar_wait(&b_full[b_stage], b_phase);
             tc_fence_after();
 #pragma unroll
-            for (int mt = 0; mt < MT; ++mt) {
-              if (!mt_ok[mt]) continue;
-              const uint32_t d_tmem = tmem_base + static_cast<uint32_t>((acc * MT + mt) * ACC_STRIDE);
-              const uint64_t ad = a_desc + mt * A_SLOT_STEP;
-              umma_f16(d_tmem, ad, b_desc, idesc, accf);
-              if (ksteps > 1) umma_f16(d_tmem, ad + 2, b_desc + B_KSTEP, idesc, 1u);
-              if (ksteps > 2) umma_f16(d_tmem, ad + 4, b_desc + 2 * B_KSTEP, idesc, 1u);
-              if (ksteps > 3) umma_f16(d_tmem, ad + 6, b_desc + 3 * B_KSTEP, idesc, 1u);
+            for (int k = 0; k < 4; ++k) {
+              if (k >= ksteps) break;
+              const uint32_t chain = (issued + k) & (KS - 1);
+              const uint32_t af = (issued + k) >= KS ? 1u : 0u;   // a chain's first MMA of the tile overwrites
+#pragma unroll
+              for (int mt = 0; mt < MT; ++mt) {
+                if (!mt_ok[mt]) continue;
+                const uint32_t d_tmem =
+                    tmem_base + static_cast<uint32_t>(((acc * MT + mt) * KS + chain) * ACC_STRIDE);
+                umma_f16(d_tmem, a_desc + mt * A_SLOT_STEP + 2 * k, b_desc + k * B_KSTEP, idesc, af);
+              }
             }
-            accf = 1u;
+            issued += ksteps;
             if (!p.resident) umma_commit(&b_empty[b_stage]);
             // next tap: one pixel to the right, or the start of the next filter row
             a_desc += row_step;
@@ -257,6 +282,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
           a_par ^= 1;
         }
         umma_commit(&tmem_full[acc]);
+        if (tr) p.trace[ti * 8 + 3] = clock64();
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -265,10 +291,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     }
     __syncwarp();
   } else {
-    // ===================== Epilogue (warps 2..9) =====================
+    // ===================== Epilogue (warps 0..7) =====================
     const int quarter = warp & 3;        // TMEM lanes [32*quarter, 32*quarter + 32)
-    const int ehalf = (warp - 2) >> 2;   // which 64-column slabs this warp takes
-    uint8_t* buf = epi_smem + (warp - 2) * 4096;
+    const int ehalf = warp >> 2;   // which 64-column slabs this warp takes
+    uint8_t* buf = epi_smem + warp * 4096;
     uint8_t* srow = buf + lane * 128;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -277,8 +303,12 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
       const int sp = tile / p.n_blocks;
       const int img = sp / p.tiles_per_img;
       const int oh0 = (sp - img * p.tiles_per_img) * (p.R * MT);
-      mbar_wait(&tmem_full[acc], acc_phase);
+      const int ti = (tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x);
+      const bool tr = p.trace != nullptr && blockIdx.x == 0 && warp == 0 && lane == 0 && ti < TRACE_TILES;
+      if (tr) p.trace[ti * 8 + 4] = clock64();
+      mbar_wait_relaxed(&tmem_full[acc], acc_phase);
       tc_fence_after();
+      if (tr) p.trace[ti * 8 + 5] = clock64();
 #pragma unroll 1
       for (int mt = 0; mt < MT; ++mt) {
         const int ohs = oh0 + mt * p.R;
@@ -305,14 +335,29 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             const int colh = col0 + half * 32;
             const int nvalid = p.N - colh;   // may be <= 0 for the second half of the last slab
             if (nvalid <= 0) break;          // never stored: the box is clipped at N
+            const uint32_t t0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                                static_cast<uint32_t>((acc * MT + mt) * KS * ACC_STRIDE + c0 + half * 32);
             uint32_t v[32];
-            tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                              static_cast<uint32_t>((acc * MT + mt) * ACC_STRIDE + c0 + half * 32),
-                          v);
-            tmem_ld_wait();
             float f[32];
+            tmem_ld_32x32(t0, v);
+            if (KS == 1) {
+              tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+              for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+            } else {
+              uint32_t v2[32];   // the sub-tile is the sum of its KS chains
+              tmem_ld_32x32(t0 + ACC_STRIDE, v2);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __uint_as_float(v2[j]);
+              if (KS == 4) {
+                tmem_ld_32x32(t0 + 2 * ACC_STRIDE, v);
+                tmem_ld_32x32(t0 + 3 * ACC_STRIDE, v2);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) f[j] += __uint_as_float(v[j]) + __uint_as_float(v2[j]);
+              }
+            }
             if (p.bias != nullptr) {
               const float* bp = p.bias + colh;
               if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
@@ -382,6 +427,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (tr) p.trace[ti * 8 + 6] = clock64();
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -392,7 +438,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == MMA_WARP) {
     tc_fence_after();
     tmem_dealloc<TMEM_COLS>(tmem_base);
   }
@@ -485,6 +531,13 @@ static int g_halo_resident = [] {
   const char* e = getenv("VB_HALO_RESIDENT");
   return e ? atoi(e) : -1;
 }();
+// Profiling hook: a device buffer of 24 x 8 long longs that CTA 0 fills with clock64 stamps (see TRACE_TILES); null = off.
+static long long* g_halo_trace = nullptr;
+extern "C" int vb_conv_halo_set_trace(long long* buf) {
+  g_halo_trace = buf;
+  return 0;
+}
+
 extern "C" int vb_conv_halo_set_options(int mt, int resident) {
   g_halo_mt = (mt == 1 || mt == 2) ? mt : 0;
   g_halo_resident = (resident == 0 || resident == 1) ? resident : -1;
@@ -516,6 +569,7 @@ extern "C" int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW
   p.ksteps_last = ceil_div(t_ch - (p.cblocks - 1) * 64, 16);
   p.a_rows = a_rows;
   p.bias = bias; p.act = act; p.Z = static_cast<const __nv_bfloat16*>(Z); p.ldz = ldz; p.deriv = deriv;
+  p.trace = g_halo_trace;
   // tile width: the narrowest of 64 / 96 / 128 that holds N in one tile, else 128-wide tiles
   const int BN = (N <= 64) ? 64 : ((N <= 96 && mode == 1) ? 96 : 128);
   p.n_blocks = ceil_div(N, BN);
@@ -529,6 +583,13 @@ extern "C" int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW
   int mt = g_halo_mt ? g_halo_mt : (p.resident ? 1 : 2);
   if (p.resident || oH <= R || BN == 96) mt = 1;   // 96-wide tiles exist for single sub-tiles only
   p.tiles_per_img = ceil_div(oH, R * mt);
+  {
+    // every accumulation chain of a sub-tile must receive at least one MMA (see KS in the kernel)
+    const int stride = BN <= 64 ? 64 : 128;
+    const int ks = 256 / (mt * stride) < 1 ? 1 : 256 / (mt * stride);
+    const int mmas = taps * ((p.cblocks - 1) * 4 + p.ksteps_last);
+    if (mmas < ks) return 1;
+  }
   CUtensorMap tx, tw, td;
   int rc = halo_tmap_4d(&tx, T, t_ch, tW, tH, tB, t_pitch, 64, P, R + ky - 1);
   if (rc) return rc;

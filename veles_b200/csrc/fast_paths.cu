@@ -806,6 +806,133 @@ lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
 }
 
 // ---------------------------------------------------------------------------------------------
+// Max-pooling backward (3x3 / stride 2, byte argmax) FUSED into LRN backward: the thread that owns 8 channels of an
+// LRN pixel gathers its dL/dy from the (up to four) pooling windows that cover the pixel - a window contributes where
+// its argmax byte names this pixel - and goes straight on with the LRN backward math.  The dense dL/dy tensor of the
+// LRN output (as large as the convolution output: 148 MB for AlexNet norm1) is neither written nor read.
+// Same lane layout as lrn_backward_shfl_kernel (C <= 256).
+// ---------------------------------------------------------------------------------------------
+template <int HALF, bool B34>
+__global__ void __launch_bounds__(256)
+lrn_pool_backward_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dpool,
+                         const uint8_t* __restrict__ offs8, __nv_bfloat16* __restrict__ dx, const FastPoolGeom g,
+                         float alpha, float beta, float k, int deriv) {
+  const int C = g.C;
+  const int T = C >> 3;
+  const int ppw = 32 / T;
+  const int lane = threadIdx.x & 31;
+  const int pl = lane / T, gq = lane - pl * T;
+  const bool active_lane = pl < ppw;
+  constexpr bool beta34 = B34;
+  const float coef = 2.0f * alpha * beta;
+  const unsigned pixels = static_cast<unsigned>(g.B) * g.H * g.W;
+  const long long warps_total = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  const long long groups = (static_cast<long long>(pixels) + ppw - 1) / ppw;
+  for (long long wv = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5; wv < groups;
+       wv += warps_total) {
+    const unsigned px = static_cast<unsigned>(wv) * ppw + pl;
+    const bool active = active_lane && px < pixels;
+    float xv[8], dv[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) xv[q] = dv[q] = 0.0f;
+    if (active) {
+      const uint4 xr = ldg16(x + static_cast<long long>(px) * C + gq * 8);
+      const unsigned w = px % g.W;
+      const unsigned r = px / g.W;
+      const unsigned h = r % g.H;
+      const unsigned b = r / g.H;
+      // windows (oh, ow) with 2 oh <= h <= 2 oh + 2: even h lies in two window rows, odd h in one
+      const int oh_hi = static_cast<int>(h >> 1), ow_hi = static_cast<int>(w >> 1);
+      const int oh_lo = (h & 1u) ? oh_hi : oh_hi - 1, ow_lo = (w & 1u) ? ow_hi : ow_hi - 1;
+      uint4 dr[4];
+      uint2 lr[4];
+      unsigned want[4];
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int oh = a ? oh_hi : oh_lo, ow = e ? ow_hi : ow_lo;
+          // (the "lo" window equals the "hi" one for odd coordinates: count it once)
+          const bool ok = oh >= 0 && oh < g.OH && ow >= 0 && ow < g.OW && (a == 1 || oh_lo != oh_hi) &&
+                          (e == 1 || ow_lo != ow_hi);
+          const long long o = ((static_cast<long long>(b) * g.OH + (ok ? oh : 0)) * g.OW + (ok ? ow : 0)) * C + gq * 8;
+          dr[a * 2 + e] = ok ? ldg16(dpool + o) : make_uint4(0, 0, 0, 0);
+          lr[a * 2 + e] = ok ? __ldg(reinterpret_cast<const uint2*>(offs8 + o)) : make_uint2(0xffffffffu, 0xffffffffu);
+          want[a * 2 + e] = (h - 2u * static_cast<unsigned>(ok ? oh : 0)) * 3u + (w - 2u * static_cast<unsigned>(ok ? ow : 0));
+        }
+      unpack8(xr, xv);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float f[8];
+        unpack8(dr[i], f);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const unsigned l = ((q < 4 ? lr[i].x : lr[i].y) >> (8 * (q & 3))) & 0xffu;
+          dv[q] += (l == want[i]) ? f[q] : 0.0f;
+        }
+      }
+    }
+    float sq[8], ext[8 + 2 * HALF];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) sq[q] = xv[q] * xv[q];
+    lrn_exchange<HALF>(sq, ext, gq == 0, gq == T - 1);
+    float t[8], dp[8], ws[8];
+    lrn_window_sums<HALF>(ext, ws);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const float s = k + alpha * ws[q];
+      float inv_s;
+      const float pw = lrn_pow_neg_inv(s, beta, beta34, inv_s);
+      dp[q] = dv[q] * pw;
+      t[q] = dp[q] * xv[q] * inv_s;
+    }
+    lrn_exchange<HALF>(t, ext, gq == 0, gq == T - 1);
+    float out[8];
+    lrn_window_sums<HALF>(ext, ws);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) out[q] = dp[q] - coef * xv[q] * ws[q];
+    if (deriv == ACT_STRICT_RELU) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) out[q] = xv[q] > 0.0f ? out[q] : 0.0f;
+    } else if (deriv) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) out[q] *= act_deriv_from_output(deriv, xv[q]);
+    }
+    if (active) *reinterpret_cast<uint4*>(dx + static_cast<long long>(px) * C + gq * 8) = pack8(out);
+  }
+}
+
+// 1 = launched; 0 = geometry outside the fused kernel (3x3 / stride 2 max pooling, C % 8 == 0, C <= 256, window size
+// n = 3..9, 16-byte aligned tensors)
+int fast_lrn_pool_backward(const void* x, const void* dpool, const uint8_t* offs8, void* dx, const FastPoolGeom& g, int n,
+                           float alpha, float beta, float k, int deriv, cudaStream_t s) {
+  const int half = n / 2;
+  if (g.ky != 3 || g.kx != 3 || g.sy != 2 || g.sx != 2 || g.C % 8 || g.C > 256 || half < 1 || half > 4) return 0;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dpool) | reinterpret_cast<uintptr_t>(dx)) & 15) return 0;
+  if (reinterpret_cast<uintptr_t>(offs8) & 7) return 0;
+  const long long pixels = static_cast<long long>(g.B) * g.H * g.W;
+  if (pixels == 0) return 1;
+  if (pixels >= (1LL << 31)) return 0;
+  const int ppw = 32 / (g.C >> 3);
+  const int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
+  const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* dp = static_cast<const __nv_bfloat16*>(dpool);
+  __nv_bfloat16* op = static_cast<__nv_bfloat16*>(dx);
+#define VB_LRN_PB(H_)                                                                                                   \
+  if (beta == 0.75f) lrn_pool_backward_kernel<H_, true><<<g2, 256, 0, s>>>(xp, dp, offs8, op, g, alpha, beta, k, deriv);   \
+  else lrn_pool_backward_kernel<H_, false><<<g2, 256, 0, s>>>(xp, dp, offs8, op, g, alpha, beta, k, deriv)
+  switch (half) {
+    case 1: VB_LRN_PB(1); break;
+    case 2: VB_LRN_PB(2); break;
+    case 3: VB_LRN_PB(3); break;
+    default: VB_LRN_PB(4); break;
+  }
+#undef VB_LRN_PB
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 1;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Launchers (return 1 when the fast path was taken, 0 when the caller must use the generic one,
 // negative on error)
 // ---------------------------------------------------------------------------------------------

@@ -27,4 +27,9 @@ int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, flo
 int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels, int C, int n, float alpha, float beta,
                       float k, int deriv, cudaStream_t s);
 
+// max pooling backward (3x3 / stride 2, byte argmax) fused into LRN backward: dpool / offs8 are the pooling layer's
+// err_output and argmax bytes, x the LRN input, dx the LRN err_input
+int fast_lrn_pool_backward(const void* x, const void* dpool, const uint8_t* offs8, void* dx, const FastPoolGeom& g, int n,
+                           float alpha, float beta, float k, int deriv, cudaStream_t s);
+
 }  // namespace vb

@@ -13,10 +13,10 @@
 // OpenCL tiled GEMM with its STORE_OUTPUT epilogue include
 // (ocl/matrix_multiplication_precise.cl:43-45).
 //
-// Kernel anatomy (one persistent CTA per SM, 192 threads):
-//   warp 0   : TMA producer   (cp.async.bulk.tensor -> 128B-swizzled smem ring)
-//   warp 1   : TMEM allocator + single-thread tcgen05.mma issuer
-//   warps 2-5: epilogue       (tcgen05.ld -> bias/activation/derivative -> global)
+// Kernel anatomy (one persistent CTA per SM, 320 threads):
+//   warps 0-7: epilogue       (tcgen05.ld -> bias/activation/derivative -> smem -> TMA store)
+//   warp 8   : TMA producer   (cp.async.bulk.tensor -> 128B-swizzled smem ring), one elected thread
+//   warp 9   : TMEM allocator + single-thread tcgen05.mma issuer
 // The fp32 accumulator lives in TMEM, double-buffered (2 x BN columns) so the
 // epilogue of tile i overlaps the mainloop of tile i+1.
 #include "common.cuh"
@@ -32,8 +32,13 @@ namespace vb {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 320;  // producer warp, MMA warp, 8 epilogue warps
+constexpr int GEMM_THREADS = 320;  // 8 epilogue warps, producer warp, MMA warp
 constexpr int EPI_WARPS = 8;
+// The two single-thread roles sit in the HIGHEST warps: the warp scheduler prefers the highest eligible warp id of a
+// sub-partition, and the epilogue warps that share it spend most of their time polling mbarriers - with the roles in
+// warps 0 and 1 their (pacing) instruction streams kept losing the issue slot to those polls.
+constexpr int PRODUCER_WARP = 8;
+constexpr int MMA_WARP = 9;
 
 // Implicit-GEMM convolution: one operand is fetched by TMA in im2col mode straight from the NHWC
 // activation tensor (no column matrix is ever materialised).  mode:
@@ -168,7 +173,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   constexpr int BN_LOAD = L::B_ROWS;  // B rows / columns this CTA stages per k-block
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
   const bool leader = (cta_rank == 0);
-  constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+  // Accumulation chains.  A tcgen05.mma that accumulates into the columns the previous one wrote waits for it: measured
+  // ~170 cycles from one dependent MMA to the next whatever N is (8192^3 at N = 256: 190; conv2 at N = 128: 153;
+  // conv1 halo at N = 96: 190), so a single chain keeps the tensor pipe busy for (N / 2) / 170 of the time - 75 % at
+  // N = 256, 38 % at N = 128, 19 % at N = 64.  Narrow tiles therefore split the k-steps of a k-block over KS
+  // independent accumulators (k-step k -> chain k % KS), which the epilogue adds: KS * BN = 256 columns in flight.
+  constexpr int KS = BN <= 64 ? 4 : (BN <= 128 ? 2 : 1);
+  constexpr int TMEM_NEED = 2 * KS * BN;
+  constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : (TMEM_NEED <= 64 ? 64 : (TMEM_NEED <= 128 ? 128 : (TMEM_NEED <= 256 ? 256 : 512)));
+  static_assert(TMEM_NEED <= 512, "accumulators exceed tensor memory");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -187,7 +200,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  if (warp == 0 && elect_one()) {
+  if (warp == PRODUCER_WARP && elect_one()) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
     if (p.tma_store) tma_prefetch_desc(&tma_d);
@@ -205,7 +218,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     fence_barrier_init();
     fence_proxy_async_smem();
   }
-  if (warp == 1) {
+  if (warp == MMA_WARP) {
     if (PAIR) tmem_alloc_pair<TMEM_COLS>(tmem_ptr);
     else tmem_alloc<TMEM_COLS>(tmem_ptr);
   }
@@ -251,7 +264,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   // a k-block index into (tap, channel block, filter row) - ~115 dependent instructions per k-block = ~800 cycles
   // for 256 cycles of tensor work).  So every per-k-block quantity is carried incrementally, and descriptors are
   // built once and advanced by constants.
-  if (warp == 0) {
+  if (warp == PRODUCER_WARP) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       int stage = 0;
@@ -393,7 +406,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == MMA_WARP) {
     // ===================== MMA issuer =====================
     // ONE thread of the leader CTA runs the whole loop (waits included): no per-k-block election / reconvergence.
     if (leader && elect_one()) {
@@ -426,7 +439,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         if (kb0 >= kb1) continue;  // empty split: the epilogue writes zeros without TMEM
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        const uint32_t d_tmem0 = tmem_base + static_cast<uint32_t>(acc * KS * BN);
         uint32_t accf = 0u;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
@@ -435,12 +448,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           for (int k = 0; k < KE / UK; ++k) {   // 4 MMAs per k-block: +32 B along a K-major row, +UK rows MN-major
             const uint64_t ad = a_desc + k * A_KSTEP;
             const uint64_t bd = b_desc + k * B_KSTEP;
+            const uint32_t d_tmem = d_tmem0 + static_cast<uint32_t>((k % KS) * BN);   // consecutive MMAs: other chains
+            const uint32_t af = k < KS ? accf : 1u;   // a chain's first MMA of the tile overwrites
             if (TF32) {
-              if (PAIR) umma_tf32_pair(d_tmem, ad, bd, idesc, k == 0 ? accf : 1u);
-              else umma_tf32(d_tmem, ad, bd, idesc, k == 0 ? accf : 1u);
+              if (PAIR) umma_tf32_pair(d_tmem, ad, bd, idesc, af);
+              else umma_tf32(d_tmem, ad, bd, idesc, af);
             } else {
-              if (PAIR) umma_f16_pair(d_tmem, ad, bd, idesc, k == 0 ? accf : 1u);
-              else umma_f16(d_tmem, ad, bd, idesc, k == 0 ? accf : 1u);
+              if (PAIR) umma_f16_pair(d_tmem, ad, bd, idesc, af);
+              else umma_f16(d_tmem, ad, bd, idesc, af);
             }
           }
           accf = 1u;
@@ -466,12 +481,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     __syncwarp();
   } else {
-    // ===================== Epilogue (warps 2..5) =====================
+    // ===================== Epilogue (warps 0..7) =====================
     // Two warps per TMEM lane quarter (a warp may only touch lanes 32*(warp%4)..+31): they take
     // alternate column slabs, so every SM sub-partition has two epilogue warps to interleave and
     // the dependent tcgen05.ld -> math -> st.shared chain of one hides behind the other.
     const int quarter = warp & 3;
-    const int ehalf = (warp - 2) >> 2;
+    const int ehalf = warp >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
     int it = 0;
@@ -484,7 +499,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       const bool has_k = kb0 < p.k_blocks;
       const bool add_bias = (p.bias != nullptr) && (ks == 0);
       if (has_k) {
-        mbar_wait(&tmem_full[acc], acc_phase);
+        mbar_wait_relaxed(&tmem_full[acc], acc_phase);
         tc_fence_after();
       }
       const int row0 = mb * TILE_M + static_cast<int>(cta_rank) * BLOCK_M + quarter * 32;
@@ -506,19 +521,35 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           dcol0 = tap * p.cv.cg + cpos;
           nvalid = p.cv.cg - cpos;
         }
-        uint32_t v[32];
+        float f[32];
         if (has_k) {
-          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                            static_cast<uint32_t>(acc * BN + c0),
-                        v);
-          tmem_ld_wait();
+          const uint32_t t0 = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                              static_cast<uint32_t>(acc * KS * BN + c0);
+          uint32_t v[32];
+          tmem_ld_32x32(t0, v);
+          if (KS == 1) {
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          } else {
+            // the tile is the sum of its KS accumulation chains (two loads in flight at a time)
+            uint32_t v2[32];
+            tmem_ld_32x32(t0 + BN, v2);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __uint_as_float(v2[j]);
+            if (KS == 4) {
+              tmem_ld_32x32(t0 + 2 * BN, v);
+              tmem_ld_32x32(t0 + 3 * BN, v2);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] += __uint_as_float(v[j]) + __uint_as_float(v2[j]);
+            }
+          }
         } else {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = 0u;
+          for (int j = 0; j < 32; ++j) f[j] = 0.0f;
         }
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
         if (p.alpha != 1.0f) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] *= p.alpha;
@@ -529,7 +560,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           // load and store instruction hit 32 different cache lines.  So the slab is transposed through this warp's
           // (swizzled) staging buffer, and the update runs with 8 lanes x 16 bytes along each row: four full
           // 128-byte row segments per instruction, for w, momentum and the bf16 shadow alike.
-          uint8_t* buf = epi_smem + (warp - 2) * EPI_BUF_BYTES;
+          uint8_t* buf = epi_smem + warp * EPI_BUF_BYTES;
           uint8_t* srow = buf + lane * 128;
           __syncwarp();
 #pragma unroll
@@ -655,7 +686,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           // Stage the 32-row slab in 128B-swizzled smem (conflict-free 16-byte writes: the eight
           // lanes of a quarter-warp phase hit eight different chunks), then one TMA store /
           // L2 reduce-add per slab: full-line writes, M/N tails clipped by the tensor map.
-          uint8_t* buf = epi_smem + (warp - 2) * EPI_BUF_BYTES;
+          uint8_t* buf = epi_smem + warp * EPI_BUF_BYTES;
           uint8_t* srow = buf + lane * 128;
           if (p.out_fp32) {
             if (lane == 0) tma_store_wait_read<0>();  // the previous slab has left this warp's buffer
@@ -751,7 +782,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   tc_fence_before();
   if (PAIR) cluster_sync_all();  // nobody may still signal barriers or read operands of a CTA that exits
   else __syncthreads();
-  if (warp == 1) {
+  if (warp == MMA_WARP) {
     tc_fence_after();
     if (PAIR) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
     else tmem_dealloc<TMEM_COLS>(tmem_base);

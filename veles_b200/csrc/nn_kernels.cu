@@ -753,6 +753,19 @@ extern "C" int vb_lrn_backward_fused(const void* x, const void* dy, void* dx, in
   return 0;
 }
 
+// Max-pooling backward fused into LRN backward (bf16 NHWC; 3x3 / stride 2 max pooling over the LRN output):
+//   dx = LRN'(x) applied to the pooling gradient scattered by the argmax bytes, optionally times f'(x).
+// x, dx: [B, H, W, C]; dpool, offs8: [B, OH, OW, C].  Returns 1 when the geometry is not supported (run the two
+// kernels separately), 0 on success, negative on error.
+extern "C" int vb_lrn_pool_backward(const void* x, const void* dpool, const unsigned char* offs8, void* dx, int B, int H,
+                                    int W, int C, int OH, int OW, int ky, int kx, int sy, int sx, int n, float alpha,
+                                    float beta, float k, int deriv, cudaStream_t s) {
+  FastPoolGeom g{B, H, W, C, OH, OW, ky, kx, sy, sx};
+  const int fr = fast_lrn_pool_backward(x, dpool, offs8, dx, g, n, alpha, beta, k, deriv, s);
+  if (fr < 0) return fr;
+  return fr == 1 ? 0 : 1;
+}
+
 // in_dtype: dtype of the pre-softmax activations s; out_dtype: dtype of y / err_output.
 extern "C" int vb_softmax_eval(const void* sm_in, int in_dtype, long long lds, void* y, long long ldy, void* err,
                                long long lde, int out_dtype, const int* labels, int* max_idx, int batch, int N,

@@ -22,6 +22,12 @@ import numpy
 from .distributable import Pickleable
 
 
+
+# Per-thread log of the host<->device bookkeeping a traced unit sequence performs (parallel/step.py GraphedChain): a
+# CUDA-graph replay repeats the kernels but not this Python-side state, so the chain re-applies it around each replay.
+import threading as _threading
+SYNC_TRACE = _threading.local()
+
 class Watcher(object):
     """Device memory accounting."""
     _lock = threading.Lock()
@@ -252,6 +258,9 @@ class Array(Pickleable):
     def unmap(self):
         if self.devmem_ is None or not self.host_dirty_:
             return
+        log = getattr(SYNC_TRACE, "log", None)
+        if log is not None:
+            log["unmaps"].append(self)       # a real host -> device copy happened inside a traced unit sequence
         with self.lock_:
             import torch
             hm = numpy.ascontiguousarray(self._mem)
@@ -268,6 +277,9 @@ class Array(Pickleable):
         if self.devmem_ is not None:
             self.dev_dirty_ = True
             self.host_dirty_ = False
+            log = getattr(SYNC_TRACE, "log", None)
+            if log is not None:
+                log["marks"].append(self)
 
     # -- pickling -------------------------------------------------------------------------------------------
     def __getstate__(self):

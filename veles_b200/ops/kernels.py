@@ -571,6 +571,22 @@ def lrn_backward(x, dy, dx, n, alpha, beta, k, deriv=0):
     return dx
 
 
+def lrn_pool_backward(x4, dpool4, offs8, dx4, ky, kx, sy, sx, n, alpha, beta, k, deriv=0):
+    """Max-pooling backward fused into LRN backward (csrc/fast_paths.cu); False when the geometry is not covered."""
+    B, H, W, C = x4.shape
+    OH, OW = dpool4.shape[1], dpool4.shape[2]
+    if x4.dtype != torch.bfloat16 or dpool4.dtype != torch.bfloat16 or not (x4.is_contiguous() and dpool4.is_contiguous()):
+        return False
+    rc = _lib.lib().vb_lrn_pool_backward(_p(x4), _p(dpool4), _p(offs8), _p(dx4), c_int(B), c_int(H), c_int(W), c_int(C),
+                                         c_int(OH), c_int(OW), c_int(ky), c_int(kx), c_int(sy), c_int(sx), c_int(n),
+                                         c_float(alpha), c_float(beta), c_float(k), c_int(deriv), _stream())
+    if rc == 1:
+        return False
+    _lib.check(rc, "vb_lrn_pool_backward")
+    LAUNCHES[0] += 1
+    return True
+
+
 def softmax_eval(s, y, err, labels, max_idx, *, err_scale=1.0, n_err=None, confusion=None, max_err_sum=None,
                  loss_sum=None):
     batch, N = s.shape

@@ -100,6 +100,7 @@ class GraphedChain(object):
         self.replays = 0
         self.captures = 0
         self._done = set()
+        self.sync = {}         # key -> {"unmaps": [Array], "marks": [Array]} learnt during the eager / capture runs
         for u in self.units:
             u.graph_chain_ = self
 
@@ -114,9 +115,40 @@ class GraphedChain(object):
                 int(getattr(loader, "minibatch_class", 0) or 0) if loader is not None else 0,
                 hyper, getattr(dp, "parity", 0))
 
-    def _run_all(self):
-        for u in self.units:
-            u.run()
+    def _run_all(self, key=None):
+        """Run the members one by one, logging the Arrays they upload (``unmap`` of host-written data) and the ones
+        their kernels write (``mark_device_written``): a replay repeats the kernels only, so the chain uploads the
+        former before and flags the latter after every replay."""
+        from .. import memory
+        if key is None:
+            for u in self.units:
+                u.run()
+            return
+        log = {"unmaps": [], "marks": []}
+        memory.SYNC_TRACE.log = log
+        try:
+            for u in self.units:
+                u.run()
+        finally:
+            memory.SYNC_TRACE.log = None
+        rec = self.sync.setdefault(key, {"unmaps": [], "marks": []})
+        for kind in ("unmaps", "marks"):
+            seen = set(id(a) for a in rec[kind])
+            for a in log[kind]:
+                if id(a) not in seen:
+                    seen.add(id(a))
+                    rec[kind].append(a)
+
+    def _replay(self, key, g):
+        rec = self.sync.get(key)
+        if rec is not None:
+            for a in rec["unmaps"]:
+                a.unmap()
+        g.replay()
+        if rec is not None:
+            for a in rec["marks"]:
+                a.mark_device_written()
+        self.replays += 1
 
     def run_member(self, unit):
         """Called by the scheduler instead of ``unit.run()``."""
@@ -139,19 +171,20 @@ class GraphedChain(object):
         key = self._signature()
         g = self.graphs.get(key)
         if g is not None:
-            g.replay()
-            self.replays += 1
+            self._replay(key, g)
             return
         n = self.eager_runs.get(key, 0)
         if n < self.WARMUP:
             self.eager_runs[key] = n + 1
-            self._run_all()
+            self._run_all(key)
             return
         try:
+            for a in self.sync.get(key, {}).get("unmaps", ()):
+                a.unmap()          # uploads happen OUTSIDE the captured region
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self._run_all()
+                self._run_all(key)
         except Exception as e:   # a unit that cannot be captured: stay correct, stay eager
             self.enabled = False
             self.wf.warning("CUDA-graph replay of the %s chain is off (%s: %s)", self.name, type(e).__name__, e)
@@ -162,8 +195,7 @@ class GraphedChain(object):
         self.graphs[key] = g
         if len(self.graphs) > 8:
             self.graphs.pop(next(iter(self.graphs)))
-        g.replay()
-        self.replays += 1
+        self._replay(key, g)
         if self.captures >= 16 and self.replays < 4 * self.captures:
             # the signature changes nearly every minibatch (a per-iteration learning-rate schedule): capturing
             # costs more than it saves

@@ -105,6 +105,9 @@ class All2All(Forward):
         n_out = self.weights_bf16_.shape[1 if self.weights_transposed else 0]
         self.acc_ = None
         # (measured on AlexNet's fc layers: GEMMs 15-30 % faster, but the extra pass eats the gain -> opt-in)
+        from ..config import root, get
+        if get(root.common.engine.two_phase_split_k, False):
+            self.TWO_PHASE_SPLIT_K = True
         if (self.TWO_PHASE_SPLIT_K and not self.tf32_ and n_out % 4 == 0 and not self.weights_transposed
                 and kernels.gemm_plan(self.input.shape[0], n_out, n_in)[1] >= 2):
             self.acc_ = torch.zeros(self.input.shape[0], n_out, dtype=torch.float32, device=dev.torch_device)

@@ -20,6 +20,29 @@ class GDPooling(GDBase):
     def __init__(self, workflow, **kwargs):
         super(GDPooling, self).__init__(workflow, **kwargs)
         self.demand("input")
+        self.lrn_consumer = None     # LRN backward unit that consumes err_input (StandardWorkflow fusion plan)
+
+    def init_unpickled(self):
+        super(GDPooling, self).init_unpickled()
+        self.handed_over_ = False
+
+    def hands_over_to_lrn(self):
+        """True when this run's work is done by the LRN backward unit's fused kernel: 3x3 / stride 2 max pooling with
+        byte argmax on a bf16 device tensor of at most 256 channels."""
+        from ..config import root, get
+        f = self.forward
+        c = self.lrn_consumer
+        if c is None or not self.on_device or not get(root.common.engine.fuse_lrn_pool, True):
+            return False
+        if getattr(f, "offs8_", None) is None or self.prev_activation:
+            return False
+        import torch
+        eo = self.err_output.devmem
+        C = f.in_shape4[3]
+        return (f.ky == 3 and f.kx == 3 and tuple(f.sliding) == (2, 2) and C % 8 == 0 and C <= 256
+                and 3 <= getattr(c.forward, "n", 0) <= 9 and eo is not None and eo.dtype == torch.bfloat16
+                and eo.is_contiguous() and c.input.devmem is not None and c.input.devmem.dtype == torch.bfloat16
+                and c.input.devmem.is_contiguous())
 
     def initialize(self, device=None, **kwargs):
         if self.err_output is None or not self.err_output or self.input is None or not self.input:
@@ -58,6 +81,9 @@ class GDPooling(GDBase):
         from ..ops import kernels
         f = self.forward
         self.err_output.unmap()
+        self.handed_over_ = self.hands_over_to_lrn()
+        if self.handed_over_:
+            return       # the LRN backward unit gathers straight from err_output + argmax bytes
         eo = self.err_output.devmem
         if eo.dtype != self.err_input.devmem.dtype or not eo.is_contiguous():
             if getattr(self, "_eo_stage_", None) is None:

@@ -68,6 +68,7 @@ class LRNormalizerBackward(GDBase):
     def __init__(self, workflow, **kwargs):
         super(LRNormalizerBackward, self).__init__(workflow, **kwargs)
         self.demand("input")
+        self.pool_gd = None      # backward unit of the max pooling layer that follows (StandardWorkflow fusion plan)
 
     def initialize(self, device=None, **kwargs):
         if self.err_output is None or not self.err_output or self.input is None or not self.input:
@@ -98,8 +99,20 @@ class LRNormalizerBackward(GDBase):
         from ..ops import kernels
         f = self.forward
         x = self.input.devmem
-        eo = self.err_output.devmem
         ei = self.err_input.devmem
+        pg = self.pool_gd
+        if pg is not None and getattr(pg, "handed_over_", False):
+            # the pooling backward unit skipped its pass: scatter its err_output by the argmax bytes and apply the
+            # LRN derivative in one kernel
+            pf = pg.forward
+            x4 = x.reshape(pf.in_shape4)
+            if not kernels.lrn_pool_backward(x4, pg.err_output.devmem.reshape(pf.out_shape4), pf.offs8_,
+                                             ei.reshape(pf.in_shape4), pf.ky, pf.kx, pf.sliding[1], pf.sliding[0],
+                                             f.n, f.alpha, f.beta, f.k, deriv=self.prev_activation):
+                raise RuntimeError("%s: fused pooling + LRN backward refused a geometry its planner accepted" % self.name)
+            self.err_input.mark_device_written()
+            return
+        eo = self.err_output.devmem
         if eo.dtype != x.dtype or not eo.is_contiguous():
             eo = eo.contiguous().to(x.dtype)
         kernels.lrn_backward(x, eo.view(x.shape), ei, f.n, f.alpha, f.beta, f.k, deriv=self.prev_activation)

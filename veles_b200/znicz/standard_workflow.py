@@ -402,7 +402,24 @@ class StandardWorkflow(StandardWorkflowBase):
             prev_gd = gd
         if self.fuse_derivatives:
             self._plan_derivative_fusion()
+        self._plan_lrn_pool_fusion()
         return self.gds[0]
+
+    def _plan_lrn_pool_fusion(self):
+        """norm -> max pooling pairs: the pooling layer's backward unit hands its work to the LRN backward unit, whose
+        device kernel scatters the pooling gradient by the argmax bytes and applies the LRN derivative in one pass
+        (the dense gradient of the LRN output never touches memory).  Decided per run on the device; the numpy
+        backend and unsupported geometries keep the two units separate."""
+        from .normalization import LRNormalizerForward, LRNormalizerBackward
+        from .gd_pooling import GDPooling
+        for i in range(len(self.forwards) - 1):
+            f, nxt = self.forwards[i], self.forwards[i + 1]
+            gd, gd_pool = self.gds[i], self.gds[i + 1]
+            if (isinstance(f, LRNormalizerForward) and isinstance(gd, LRNormalizerBackward)
+                    and isinstance(gd_pool, GDPooling) and getattr(nxt, "KIND", "") in ("max", "maxabs")
+                    and gd.need_err_input):
+                gd.pool_gd = gd_pool
+                gd_pool.lrn_consumer = gd
 
     def _plan_derivative_fusion(self):
         """gd[i] multiplies its err_input by f'_{i-1}(input) when forward[i-1] has an activation that
