@@ -41,6 +41,9 @@ def parse():
     p.add_argument("--min-seconds", type=float, default=0.0,
                    help="repeat the timed region (in whole multiples of --steps) until it has run this long: sustained "
                         "clocks instead of a burst")
+    p.add_argument("--dp-profile", action="store_true",
+                   help="N>1, with --no-graph: print the duration of every exchange kernel of one step to stderr")
+    p.add_argument("--bucket-mb", type=float, default=4.0, help="N>1: parameter bytes that close an exchange bucket")
     p.add_argument("--fc-split-k", action="store_true",
                    help="small-batch fully connected layers: split-K GEMM into an fp32 scratch + bias/activation pass")
     p.add_argument("--ps-async", action="store_true", help="ps_emulation: two jobs in flight per slave (--async-slave)")
@@ -51,7 +54,8 @@ def parse():
     p.add_argument("--weight-delivery", default="multicast", choices=["multicast", "peer_tma"],
                    help="N>1: multimem.st broadcast of updated bf16 weights, or GEMMs TMA-loading weight tiles from owners")
     p.add_argument("--comm-ctas", type=int, default=0,
-                   help="N>1: CTAs of the fused all-reduce+GD kernel (0 = by world size: 96 for 2 ranks, else 64)")
+                   help="N>1: CTAs of the fused all-reduce+GD kernel = SMs the backward GEMMs leave free for it "
+                        "(0 = by world size: 8 for 2 ranks, else 4)")
     p.add_argument("--gemm-schedule", default="static", choices=["static", "clc"],
                    help="GEMM tile scheduling: static persistent round-robin, or cluster-launch-control work stealing")
     p.add_argument("--split-handshake", action="store_true",
@@ -126,7 +130,7 @@ def main():
         from veles_b200.parallel.dp import DataParallel
         dp = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
                           shard_master=not args.replicate_master, n_ctas=args.comm_ctas,
-                          split_handshake=args.split_handshake)
+                          split_handshake=args.split_handshake, bucket_bytes=int(args.bucket_mb * (1 << 20)))
 
     from veles_b200.backends import B200Device
     from veles_b200.trainer import Trainer
@@ -169,6 +173,19 @@ def main():
     for _ in range(3):
         trainer.step_resident()
     sync_all()
+    if args.dp_profile and dp is not None and not use_graph and args.impl != "nccl":
+        dp.profile = True
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        trainer.step_resident()
+        e1.record()
+        times = dp.bucket_times()
+        dp.profile = False
+        if rank == 0:
+            sys.stderr.write("exchange kernels of one eager step (%.3f ms): %s\n" % (
+                e0.elapsed_time(e1), ", ".join("bucket %d %.1f MB %.3f ms" % (c, b / 1e6, t) for c, b, t in times)))
+        sync_all()
     sampler = ClockSampler(local_rank).start() if rank == 0 else None
     # L2 policy: AlexNet streams far more than the 126 MB L2 per step; the small models would otherwise re-hit
     # their previous step's lines, so L2 is flushed (a 256 MB write) between steps and every step is timed on its own.
@@ -217,7 +234,7 @@ def main():
             from veles_b200.parallel.dp import DataParallel
             dp2 = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
                                shard_master=not args.replicate_master, n_ctas=args.comm_ctas,
-                               split_handshake=args.split_handshake)
+                               split_handshake=args.split_handshake, bucket_bytes=int(args.bucket_mb * (1 << 20)))
         tr = Trainer(args.model, minibatch_size=B, device=device, use_graph=use_graph, streaming=True,
                      data_parallel=dp2)
         shape = cfg["sample_shape"]

@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <type_traits>
 
 namespace vb {
 
@@ -196,19 +197,23 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     if (elect_one()) {
       int b_stage = 0, acc = 0, a_par = 0;
       uint32_t b_phase = 0, acc_phase = 0, a_phase_bits = 0;
-      constexpr uint64_t B_STEP = static_cast<uint64_t>(S::B_BYTES >> 4);
-      constexpr uint64_t A_SLOT_STEP = static_cast<uint64_t>(HALO_A_SLOT >> 4);
-      constexpr uint64_t B_KSTEP = static_cast<uint64_t>((B_MN ? 2048 : 32) >> 4);
+      // Descriptors are carried as low words (the 14-bit shared-memory address field never carries out: addresses
+      // stay below 2^18); the high words are constants.
+      constexpr uint32_t B_STEP = static_cast<uint32_t>(S::B_BYTES >> 4);
+      constexpr uint32_t A_SLOT_STEP = static_cast<uint32_t>(HALO_A_SLOT >> 4);
+      constexpr uint32_t B_KSTEP = static_cast<uint32_t>((B_MN ? 2048 : 32) >> 4);
       const uint64_t b_desc_s0 = B_MN ? make_smem_desc_sw128(smem_u32(b_smem), 8192, 1024)
                                       : make_smem_desc_sw128(smem_u32(b_smem), 16, 1024);
       // activation windows: plain SWIZZLE_128B descriptors (base-offset field 0) - the swizzle is a function of the
       // absolute shared-memory address, so a window shifted by whole 128-byte rows reads exactly what TMA wrote
       // (measured: setting the base-offset field to the row phase gives wrong products)
       const uint64_t a_desc_s0 = make_smem_desc_sw128(smem_u32(a_smem), 16, 1024);
-      const uint64_t row_step = 128u >> 4;                                     // one lane (pixel) further
-      const uint64_t line_step = static_cast<uint64_t>((p.P - p.kx) * 8);      // from the last tap of a filter row to
-                                                                                // the first tap of the next one
-      uint64_t b_desc = b_desc_s0;
+      const uint32_t a_hi = static_cast<uint32_t>(a_desc_s0 >> 32), b_hi = static_cast<uint32_t>(b_desc_s0 >> 32);
+      const uint32_t a_lo_s0 = static_cast<uint32_t>(a_desc_s0), b_lo_s0 = static_cast<uint32_t>(b_desc_s0);
+      const uint32_t line_step = static_cast<uint32_t>((p.P - p.kx) * 8);   // from the last tap of a filter row to the
+                                                                            // first tap of the next one (16-byte units)
+      const int ky = p.ky, kx = p.kx;
+      uint32_t b_lo = b_lo_s0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const bool first = (tile == static_cast<int>(blockIdx.x));
         const int nb = tile % p.n_blocks;
@@ -228,13 +233,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         if (tr) p.trace[ti * 8 + 1] = clock64();
+        const bool stream = !(p.resident && !first);   // weight tiles arrive through the ring (else: already resident)
         if (p.resident) {
           b_stage = 0;
-          b_desc = b_desc_s0;
+          b_lo = b_lo_s0;
         }
-        uint32_t issued = 0;   // MMAs issued per sub-tile in this tile
+        const uint32_t d_tile = tmem_base + static_cast<uint32_t>(acc * MT * KS * ACC_STRIDE);
         for (int cb = 0; cb < p.cblocks; ++cb) {
-          const int ksteps = (cb == p.cblocks - 1) ? p.ksteps_last : 4;
 #pragma unroll
           for (int mt = 0; mt < MT; ++mt) {
             if (!mt_ok[mt]) continue;
@@ -242,38 +247,73 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             mbar_wait(&a_full[slot], (a_phase_bits >> slot) & 1u);
             a_phase_bits ^= 1u << slot;
           }
+          tc_fence_after();
           if (tr && cb == 0) p.trace[ti * 8 + 2] = clock64();
-          uint64_t a_desc = a_desc_s0 + static_cast<uint64_t>(a_par * MT) * A_SLOT_STEP;   // window of tap (0, 0)
-          int s = 0;
-          for (int tap = 0; tap < taps; ++tap) {
-            if (!p.resident || first) mbar_wait(&b_full[b_stage], b_phase);
-            tc_fence_after();
+          // All taps of one channel block.  KSTEPS (16-channel MMA steps per tap) and STREAM are compile-time in the
+          // body: the loop is the pacing instruction stream of the kernel (one thread, ~30 cycles per MMA plus
+          // ~350 per iteration measured with the generic form), so it carries no run-time branches.
+          auto run_cb = [&](auto ksteps_c, auto stream_c) {
+            constexpr int KSTEPS = decltype(ksteps_c)::value;
+            constexpr bool STREAM = decltype(stream_c)::value;
+            uint32_t a_lo = a_lo_s0 + static_cast<uint32_t>(a_par * MT) * A_SLOT_STEP;   // window of tap (0, 0)
+            uint32_t fresh = (cb == 0) ? 0u : 1u;     // 0: the chains' first MMAs of the tile overwrite
+            uint32_t rot = (cb == 0) ? 0u : static_cast<uint32_t>(KS);   // KSTEPS < KS: MMAs issued so far (capped)
+            for (int r = 0; r < ky; ++r) {
+              for (int sx = 0; sx < kx; ++sx) {
+                if (STREAM) {
+                  mbar_wait(&b_full[b_stage], b_phase);
+                  tc_fence_after();
+                }
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              if (k >= ksteps) break;
-              const uint32_t chain = (issued + k) & (KS - 1);
-              const uint32_t af = (issued + k) >= KS ? 1u : 0u;   // a chain's first MMA of the tile overwrites
+                for (int k = 0; k < KSTEPS; ++k) {
 #pragma unroll
-              for (int mt = 0; mt < MT; ++mt) {
-                if (!mt_ok[mt]) continue;
-                const uint32_t d_tmem =
-                    tmem_base + static_cast<uint32_t>(((acc * MT + mt) * KS + chain) * ACC_STRIDE);
-                umma_f16(d_tmem, a_desc + mt * A_SLOT_STEP + 2 * k, b_desc + k * B_KSTEP, idesc, af);
+                  for (int mt = 0; mt < MT; ++mt) {
+                    if (!mt_ok[mt]) continue;
+                    if (KSTEPS >= KS) {
+                      // k-step k feeds chain k % KS: the same assignment at every tap, all compile-time
+                      umma_f16_lohi(d_tile + static_cast<uint32_t>((mt * KS + (k % KS)) * ACC_STRIDE),
+                                    a_lo + mt * A_SLOT_STEP + 2 * k, a_hi, b_lo + k * B_KSTEP, b_hi, idesc,
+                                    k < KS ? fresh : 1u);
+                    } else {
+                      // fewer k-steps than chains (16-channel layers): rotate over the chains from tap to tap
+                      const uint32_t n = rot + k;
+                      umma_f16_lohi(d_tile + static_cast<uint32_t>(mt * KS * ACC_STRIDE) + (n & (KS - 1)) * ACC_STRIDE,
+                                    a_lo + mt * A_SLOT_STEP + 2 * k, a_hi, b_lo + k * B_KSTEP, b_hi, idesc,
+                                    n >= KS ? 1u : 0u);
+                    }
+                  }
+                }
+                fresh = 1u;
+                if (KSTEPS < KS) rot = rot + KSTEPS >= 2 * KS ? rot + KSTEPS - KS : rot + KSTEPS;   // keeps n >= KS true
+                if (STREAM) {
+                  if (!p.resident) umma_commit(&b_empty[b_stage]);
+                }
+                a_lo += 8;                // next tap: one pixel (128 B) to the right
+                b_lo += B_STEP;
+                if (++b_stage == B_STAGES) {
+                  b_stage = 0;
+                  b_phase ^= 1;
+                  b_lo = b_lo_s0;
+                }
               }
+              a_lo += line_step;          // start of the next filter row
             }
-            issued += ksteps;
-            if (!p.resident) umma_commit(&b_empty[b_stage]);
-            // next tap: one pixel to the right, or the start of the next filter row
-            a_desc += row_step;
-            if (++s == p.kx) {
-              s = 0;
-              a_desc += line_step;
+          };
+          const int ksteps = (cb == p.cblocks - 1) ? p.ksteps_last : 4;
+          using std::integral_constant;
+          if (stream) {
+            switch (ksteps) {
+              case 1: run_cb(integral_constant<int, 1>{}, integral_constant<bool, true>{}); break;
+              case 2: run_cb(integral_constant<int, 2>{}, integral_constant<bool, true>{}); break;
+              case 3: run_cb(integral_constant<int, 3>{}, integral_constant<bool, true>{}); break;
+              default: run_cb(integral_constant<int, 4>{}, integral_constant<bool, true>{}); break;
             }
-            b_desc += B_STEP;
-            if (++b_stage == B_STAGES) {
-              b_stage = 0;
-              b_phase ^= 1;
-              b_desc = b_desc_s0;
+          } else {
+            switch (ksteps) {
+              case 1: run_cb(integral_constant<int, 1>{}, integral_constant<bool, false>{}); break;
+              case 2: run_cb(integral_constant<int, 2>{}, integral_constant<bool, false>{}); break;
+              case 3: run_cb(integral_constant<int, 3>{}, integral_constant<bool, false>{}); break;
+              default: run_cb(integral_constant<int, 4>{}, integral_constant<bool, false>{}); break;
             }
           }
 #pragma unroll
@@ -587,8 +627,9 @@ extern "C" int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW
     // every accumulation chain of a sub-tile must receive at least one MMA (see KS in the kernel)
     const int stride = BN <= 64 ? 64 : 128;
     const int ks = 256 / (mt * stride) < 1 ? 1 : 256 / (mt * stride);
-    const int mmas = taps * ((p.cblocks - 1) * 4 + p.ksteps_last);
-    if (mmas < ks) return 1;
+    // every accumulation chain of a sub-tile must receive an MMA: a single channel block with fewer k-steps than
+    // chains rotates over them tap by tap
+    if (p.cblocks == 1 && p.ksteps_last < ks && taps * p.ksteps_last < ks) return 1;
   }
   CUtensorMap tx, tw, td;
   int rc = halo_tmap_4d(&tx, T, t_ch, tW, tH, tB, t_pitch, 64, P, R + ky - 1);

@@ -53,6 +53,8 @@ class DataParallel(object):
         self.n_ctas = max(2, (self.n_ctas + 1) & ~1)
         # peer-TMA delivery describes ONE layer's weight matrix per launch: no bucketing there
         self.bucket_bytes = 0 if weight_delivery == "peer_tma" else int(bucket_bytes)
+        self.profile = False       # eager runs: time every exchange kernel with CUDA events (bucket_times())
+        self._prof_events = []
         self.buckets = []          # launch units: lists of GD units exchanged by one kernel, in backward order
         self.bucket_of = {}
         self._reserved = False
@@ -342,7 +344,11 @@ class DataParallel(object):
         def arr(ptrs):
             return (c_void_p * W)(*[c_void_p(p) for p in ptrs])
 
+        prof = self.profile and not torch.cuda.is_current_stream_capturing()
         with torch.cuda.stream(self.comm_stream):
+            if prof:
+                t0 = torch.cuda.Event(enable_timing=True)
+                t0.record(self.comm_stream)
             rc = _lib.lib().vb_fused_allreduce_gd(
                 c_int(W), c_int(self.rank), c_int(b["channel"]), c_int(nseg), segs, hyper,
                 c_void_p(g_local), c_void_p(g_mc), arr(g_peers), c_void_p(go_local),
@@ -356,9 +362,20 @@ class DataParallel(object):
                 c_void_p(self.comm_stream.cuda_stream))
             _lib.check(rc, "vb_fused_allreduce_gd")
             kernels.LAUNCHES[0] += 2 if self.split_handshake else 1
-            done = torch.cuda.Event()
+            done = torch.cuda.Event(enable_timing=prof)
             done.record(self.comm_stream)
+            if prof:
+                self._prof_events.append((b["channel"], b["bytes"], None, t0, done))
         self._pending_events.append(done)
+
+    def bucket_times(self):
+        """[(bucket, parameter bytes, kernel ms)] of the profiled exchange launches since the last call (eager runs
+        with ``profile = True``; includes the time the kernel waited for its peers)."""
+        import torch
+        torch.cuda.synchronize()
+        out = [(ch, nbytes, t0.elapsed_time(t1)) for ch, nbytes, _, t0, t1 in self._prof_events]
+        self._prof_events = []
+        return out
 
     def allreduce_host(self, grad):
         """Host mode: sum a numpy gradient over the ranks (scaled like the device kernel scales it)."""

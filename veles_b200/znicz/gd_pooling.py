@@ -32,7 +32,9 @@ class GDPooling(GDBase):
         from ..config import root, get
         f = self.forward
         c = self.lrn_consumer
-        if c is None or not self.on_device or not get(root.common.engine.fuse_lrn_pool, True):
+        # opt-in: measured on AlexNet the per-pixel gather makes the (instruction-bound) LRN backward kernel slower
+        # than the two separate kernels (step 2.46 vs 2.33 ms) - see DESIGN.md section 8
+        if c is None or not self.on_device or not get(root.common.engine.fuse_lrn_pool, False):
             return False
         if getattr(f, "offs8_", None) is None or self.prev_activation:
             return False
