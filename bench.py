@@ -41,6 +41,9 @@ def parse():
     p.add_argument("--min-seconds", type=float, default=0.0,
                    help="repeat the timed region (in whole multiples of --steps) until it has run this long: sustained "
                         "clocks instead of a burst")
+    p.add_argument("--exchange", default="pull", choices=["push", "pull"],
+                   help="N>1: gradients reach their owner by remote stores (push) or by multimem.ld_reduce / peer loads (pull)")
+    p.add_argument("--no-multimem", action="store_true", help="N>1: peer loads / stores instead of NVLS multimem")
     p.add_argument("--dp-profile", action="store_true",
                    help="N>1, with --no-graph: print the duration of every exchange kernel of one step to stderr")
     p.add_argument("--bucket-mb", type=float, default=4.0, help="N>1: parameter bytes that close an exchange bucket")
@@ -55,7 +58,7 @@ def parse():
                    help="N>1: multimem.st broadcast of updated bf16 weights, or GEMMs TMA-loading weight tiles from owners")
     p.add_argument("--comm-ctas", type=int, default=0,
                    help="N>1: CTAs of the fused all-reduce+GD kernel = SMs the backward GEMMs leave free for it "
-                        "(0 = by world size: 8 for 2 ranks, else 4)")
+                        "(0 = by world size: 16 up to 4 ranks, else 8)")
     p.add_argument("--gemm-schedule", default="static", choices=["static", "clc"],
                    help="GEMM tile scheduling: static persistent round-robin, or cluster-launch-control work stealing")
     p.add_argument("--split-handshake", action="store_true",
@@ -130,7 +133,8 @@ def main():
         from veles_b200.parallel.dp import DataParallel
         dp = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
                           shard_master=not args.replicate_master, n_ctas=args.comm_ctas,
-                          split_handshake=args.split_handshake, bucket_bytes=int(args.bucket_mb * (1 << 20)))
+                          split_handshake=args.split_handshake, bucket_bytes=int(args.bucket_mb * (1 << 20)),
+                          exchange=args.exchange, use_multimem=False if args.no_multimem else None)
 
     from veles_b200.backends import B200Device
     from veles_b200.trainer import Trainer
@@ -234,7 +238,8 @@ def main():
             from veles_b200.parallel.dp import DataParallel
             dp2 = DataParallel(mode="nccl" if args.impl == "nccl" else "fused", weight_delivery=args.weight_delivery,
                                shard_master=not args.replicate_master, n_ctas=args.comm_ctas,
-                               split_handshake=args.split_handshake, bucket_bytes=int(args.bucket_mb * (1 << 20)))
+                               split_handshake=args.split_handshake, bucket_bytes=int(args.bucket_mb * (1 << 20)),
+                          exchange=args.exchange, use_multimem=False if args.no_multimem else None)
         tr = Trainer(args.model, minibatch_size=B, device=device, use_graph=use_graph, streaming=True,
                      data_parallel=dp2)
         shape = cfg["sample_shape"]
@@ -298,7 +303,9 @@ def main():
                        "input_shape": list(cfg["sample_shape"]),
                        "parallelism": "dp%d" % world if world > 1 else "single",
                        "grad_exchange": ("none" if world == 1 else
-                                         ("nccl_allreduce+gd" if args.impl == "nccl" else "fused_multimem_allreduce_gd")),
+                                         ("nccl_allreduce+gd" if args.impl == "nccl" else
+                                          ("fused_push_reduce_gd_multimem_bcast" if args.exchange == "push"
+                                           else "fused_multimem_allreduce_gd"))),
                        "weight_delivery": (None if world == 1 or args.impl == "nccl" else args.weight_delivery),
                        "master_weights": (None if world == 1 or args.impl == "nccl" else
                                           ("replicated" if args.replicate_master else "sharded, gathered at epoch ends")),

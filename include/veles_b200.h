@@ -230,13 +230,17 @@ int vb_rnn_cell_backward(const void* dh_ext, int ext_dtype, long long ld_ext, co
  * *_peer arrays hold `world` device pointers.  segs: nseg x {offset, numel, shadow_offset, row_len, row_pitch,
  * flags} (flags bit 0: zero the other parity's gradients; bit 1: always publish the fp32 master); hyper: nseg x
  * {lr, wd, l1_vs_l2, moment}.  use_multimem bits: 0 multimem path, 1 sharded fp32 master, 2 shadow stays on its
- * owner (peer-TMA delivery), 3 handshake in its own 1-CTA launch.  n_ctas is rounded up to whole 2-CTA clusters. */
+ * owner (peer-TMA delivery), 3 handshake in its own 1-CTA launch, 4 PUSH form (the default of parallel/dp.py): every
+ * rank stores the gradient parts its peers own into their staging slabs (stage_local / stage_peer, laid out like the
+ * gradient slab), the owner reduces locally - no load crosses NVLink; cta_counter then has 128 words.
+ * n_ctas is rounded up to whole 2-CTA clusters. */
 int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg, const long long* segs, const float* hyper,
                           float* grads_local, float* grads_mc, float** grads_peer, float* grads_other_local,
                           float* weights_local, float* weights_mc, float** weights_peer, float* vel_local,
                           void* shadow_local, void* shadow_mc, void** shadow_peer, unsigned int* flags_local,
                           unsigned int** flags_peer, unsigned int* epochs, unsigned int* cta_counter, int* status,
-                          float grad_scale, int n_ctas, int use_multimem, double timeout_s, cudaStream_t stream);
+                          float grad_scale, int n_ctas, int use_multimem, double timeout_s, float* stage_local,
+                          float** stage_peer, cudaStream_t stream);
 /* The same kernel body with every rank emulated on the current GPU by one cooperative launch (blockIdx.y = rank,
  * P2P path): how a single-GPU box tests the flag protocol and the slice arithmetic.  params_dev: device scratch of
  * world * vb_fused_params_bytes() bytes.  No counterpart in the reference. */
@@ -245,7 +249,7 @@ int vb_fused_allreduce_gd_emulated(int world, int channel, int nseg, const long 
                                    float** grads, float** grads_other, float** weights, float** vel, void** shadow,
                                    unsigned int** flags, unsigned int** epochs, unsigned int** cta_counter,
                                    int** status, float grad_scale, int n_ctas, int options, double timeout_s,
-                                   void* params_dev, cudaStream_t stream);
+                                   void* params_dev, float** stage, cudaStream_t stream);
 /* SMs that the persistent tcgen05 kernels leave free from now on (0 = none): the exchange kernel runs there beside
  * the backward pass.  Read at launch / graph-capture time; returns the previous value. */
 int vb_set_sm_reserve(int n);

@@ -29,7 +29,8 @@ def _slice(numel, world, rank):
 
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("sharded", [False, True])
-def test_fused_allreduce_gd_emulated_ranks(world, sharded):
+@pytest.mark.parametrize("push", [True, False], ids=["push", "pull"])
+def test_fused_allreduce_gd_emulated_ranks(world, sharded, push):
     import torch
     from veles_b200.ops import _lib
     L = _lib.lib()
@@ -56,7 +57,8 @@ def test_fused_allreduce_gd_emulated_ranks(world, sharded):
             shadow=torch.full((shadow_elems,), 7.0, device=dev, dtype=torch.bfloat16),
             flags=torch.zeros(64 * 2 * 8, dtype=torch.int32, device=dev),
             epochs=torch.zeros(64, dtype=torch.int32, device=dev),
-            counter=torch.zeros(64, dtype=torch.int32, device=dev),
+            counter=torch.zeros(128, dtype=torch.int32, device=dev),
+            stage=torch.full((slab,), float("nan"), device=dev),
             status=torch.zeros(1, dtype=torch.int32, device=dev)))
     params = torch.zeros(int(L.vb_fused_params_bytes()) * world + 256, dtype=torch.uint8, device=dev)
     seg_arr = (c_longlong * (6 * len(segs)))(*[v for s in segs for v in s])
@@ -71,14 +73,16 @@ def test_fused_allreduce_gd_emulated_ranks(world, sharded):
     v_ref = np.zeros(slab)
     channel = 3
     for step in range(2):
-        parity = step & 1
+        parity = 0 if push else (step & 1)      # push: one gradient buffer, cleared in place where flagged
         g_sum = sum(rk["grads"][parity].double().cpu().numpy() for rk in ranks)
+        g_before = [rk["grads"][parity].clone() for rk in ranks]
         other_before = [rk["grads"][1 - parity].clone() for rk in ranks]
         rc = L.vb_fused_allreduce_gd_emulated(
             c_int(world), c_int(channel), c_int(len(segs)), seg_arr, hyp_arr, ptrs("grads", parity),
             ptrs("grads", 1 - parity), ptrs("weights"), ptrs("vel"), ptrs("shadow"), ptrs("flags"), ptrs("epochs"),
-            ptrs("counter"), ptrs("status"), c_float(scale), c_int(2), c_int(2 if sharded else 0), c_double(5.0),
-            c_void_p(params.data_ptr()), c_void_p(torch.cuda.current_stream().cuda_stream))
+            ptrs("counter"), ptrs("status"), c_float(scale), c_int(2),
+            c_int((2 if sharded else 0) | (16 if push else 0)), c_double(5.0),
+            c_void_p(params.data_ptr()), ptrs("stage"), c_void_p(torch.cuda.current_stream().cuda_stream))
         _lib.check(rc, "vb_fused_allreduce_gd_emulated")
         torch.cuda.synchronize()
         for (off, numel, sh_off, row_len, pitch, flags), (lr, wd, l12, mom) in zip(segs, hyper):
@@ -111,11 +115,19 @@ def test_fused_allreduce_gd_emulated_ranks(world, sharded):
                     np.testing.assert_allclose(got, ref, rtol=1e-2, atol=1e-6)
                     if pitch > row_len:   # the pitch padding is not written
                         assert sh[sh_off + row_len] == 7.0
-                other = rk["grads"][1 - parity][off:off + numel]
-                if flags & SEG_ZERO_OTHER:
-                    assert float(other.abs().max()) == 0.0
+                if push:    # accumulating segments restart from zero in place, stored ones are left alone
+                    mine = rk["grads"][0][off:off + numel]
+                    if flags & SEG_ZERO_OTHER:
+                        assert float(mine.abs().max()) == 0.0
+                    else:
+                        assert torch.equal(mine, g_before[r][off:off + numel])
+                    assert torch.equal(rk["grads"][1][off:off + numel], other_before[r][off:off + numel])
                 else:
-                    assert torch.equal(other, other_before[r][off:off + numel])
+                    other = rk["grads"][1 - parity][off:off + numel]
+                    if flags & SEG_ZERO_OTHER:
+                        assert float(other.abs().max()) == 0.0
+                    else:
+                        assert torch.equal(other, other_before[r][off:off + numel])
             # the oracle follows rank-local truth: owners hold the new values
             w_ref[off:off + numel] = w_new
             v_ref[off:off + numel] = v_new
@@ -128,7 +140,4 @@ def test_fused_allreduce_gd_emulated_ranks(world, sharded):
                         rk["weights"][off + lo:off + hi] = rq["weights"][off + lo:off + hi]
         # fresh gradients for the next step in the buffer that was just cleared / left alone
         for rk in ranks:
-            rk["grads"][1 - parity].normal_()
-            for (off, numel, _s, _l, _p, flags) in segs:
-                if flags & SEG_ZERO_OTHER:
-                    pass   # accumulate semantics would add into zeros; the oracle just sums what is there
+            rk["grads"][0 if push else 1 - parity].normal_()

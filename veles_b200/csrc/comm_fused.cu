@@ -49,7 +49,10 @@ struct FusedParams {
   float* grads_local;        // this step's parity
   float* grads_mc;           // multicast alias of the same slab or null
   float* grads_peer[MAX_WORLD];
-  float* grads_other_local;  // other parity: zeroed here
+  float* grads_other_local;  // other parity: zeroed here (pull); null in push mode
+  float* stage_local;        // push mode: region r of a segment holds rank r's contribution to MY slice
+  float* stage_peer[MAX_WORLD];
+  int push;                  // 1: gradients travel by remote STORES into the owners' staging slabs
   float* weights_local;
   float* weights_mc;
   float* weights_peer[MAX_WORLD];
@@ -168,21 +171,19 @@ __device__ __forceinline__ void fused_allreduce_gd_body(const FusedParams& p) {
       const long long n4 = (hi - lo) >> 2;  // lo is a multiple of 4 and offset is 64-element aligned
       const bool flat_shadow = s.shadow_offset >= 0 && s.row_len == s.row_pitch;
       const bool bcast_master = p.bcast_master || (s.flags & SEG_BCAST_MASTER);
-      // UNROLL independent 16-byte chains per thread: the NVLink round trip of multimem.ld_reduce is
-      // several microseconds, so bandwidth needs many loads in flight per SM, not many SMs.
-      constexpr int UNROLL = 8;
-      for (long long b4 = tid; b4 < n4; b4 += nthreads * UNROLL) {
-        float4 g[UNROLL];
+      // UNROLL independent 16-byte chains per thread, and the NEXT batch of reduced gradients is requested before
+      // the current one is consumed: the NVLink round trip of multimem.ld_reduce is several microseconds, so an SM
+      // earns bandwidth only while its loads are in flight (without the prefetch they were in flight a third of
+      // the time: 61 GB/s from 8 SMs at 2 ranks).
+      constexpr int UNROLL = 4;
+      auto load_g = [&](long long b4, float4 (&g)[UNROLL]) {
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
           const long long i4 = b4 + u * nthreads;
           if (i4 < n4) {
             const long long gi = s.offset + lo + (i4 << 2);
-            if (MULTIMEM) {
-              g[u] = mc_ld_reduce_f32x4(p.grads_mc + gi);
-            } else {
-              g[u] = *reinterpret_cast<const float4*>(p.grads_local + gi);
-            }
+            if (MULTIMEM) g[u] = mc_ld_reduce_f32x4(p.grads_mc + gi);
+            else g[u] = *reinterpret_cast<const float4*>(p.grads_local + gi);
           }
         }
         if (!MULTIMEM) {
@@ -198,63 +199,70 @@ __device__ __forceinline__ void fused_allreduce_gd_body(const FusedParams& p) {
             }
           }
         }
-        // weights / momentum are local (short latency): two half batches keep the live registers under 128
+      };
+      float4 g[UNROLL];
+      long long b4 = tid;
+      if (b4 < n4) load_g(b4, g);
+      while (b4 < n4) {
+        const long long b4_next = b4 + nthreads * UNROLL;
+        float4 gn[UNROLL];
+        if (b4_next < n4) load_g(b4_next, gn);
+        float4 w[UNROLL], v[UNROLL];
 #pragma unroll
-        for (int h = 0; h < UNROLL; h += UNROLL / 2) {
-          float4 w[UNROLL / 2], v[UNROLL / 2];
-#pragma unroll
-          for (int u = 0; u < UNROLL / 2; ++u) {
-            const long long i4 = b4 + (h + u) * nthreads;
-            if (i4 < n4) {
-              const long long gi = s.offset + lo + (i4 << 2);
-              w[u] = *reinterpret_cast<const float4*>(p.weights_local + gi);
-              v[u] = *reinterpret_cast<const float4*>(p.vel_local + gi);
-            }
+        for (int u = 0; u < UNROLL; ++u) {
+          const long long i4 = b4 + u * nthreads;
+          if (i4 < n4) {
+            const long long gi = s.offset + lo + (i4 << 2);
+            w[u] = *reinterpret_cast<const float4*>(p.weights_local + gi);
+            v[u] = *reinterpret_cast<const float4*>(p.vel_local + gi);
           }
+        }
 #pragma unroll
-          for (int u = 0; u < UNROLL / 2; ++u) {
-            const long long i4 = b4 + (h + u) * nthreads;
-            if (i4 >= n4) continue;
-            const long long i = lo + (i4 << 2);
-            const long long gi = s.offset + i;
-            float4 wv4 = w[u], vv = v[u];
-            const float4 gg = g[h + u];
-            wv4.x = gd_apply(wv4.x, gg.x, vv.x, s, p.grad_scale);
-            wv4.y = gd_apply(wv4.y, gg.y, vv.y, s, p.grad_scale);
-            wv4.z = gd_apply(wv4.z, gg.z, vv.z, s, p.grad_scale);
-            wv4.w = gd_apply(wv4.w, gg.w, vv.w, s, p.grad_scale);
-            *reinterpret_cast<float4*>(p.vel_local + gi) = vv;
-            if (!bcast_master) {
-              *reinterpret_cast<float4*>(p.weights_local + gi) = wv4;
-            } else if (MULTIMEM) {
-              mc_st_f32x4(p.weights_mc + gi, wv4);
-            } else {
-              for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = wv4;
-            }
-            if (s.shadow_offset >= 0) {
-              const uint32_t b0 = pack_bf16x2(wv4.x, wv4.y), b1 = pack_bf16x2(wv4.z, wv4.w);
-              if (flat_shadow) {
-                const long long so = s.shadow_offset + i;
-                if (!p.bcast_shadow) {
-                  *reinterpret_cast<uint2*>(p.shadow_local + so) = make_uint2(b0, b1);
-                } else if (MULTIMEM) {
-                  mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
-                } else {
-                  for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
-                }
+        for (int u = 0; u < UNROLL; ++u) {
+          const long long i4 = b4 + u * nthreads;
+          if (i4 >= n4) continue;
+          const long long i = lo + (i4 << 2);
+          const long long gi = s.offset + i;
+          float4 wv4 = w[u], vv = v[u];
+          const float4 gg = g[u];
+          wv4.x = gd_apply(wv4.x, gg.x, vv.x, s, p.grad_scale);
+          wv4.y = gd_apply(wv4.y, gg.y, vv.y, s, p.grad_scale);
+          wv4.z = gd_apply(wv4.z, gg.z, vv.z, s, p.grad_scale);
+          wv4.w = gd_apply(wv4.w, gg.w, vv.w, s, p.grad_scale);
+          *reinterpret_cast<float4*>(p.vel_local + gi) = vv;
+          if (!bcast_master) {
+            *reinterpret_cast<float4*>(p.weights_local + gi) = wv4;
+          } else if (MULTIMEM) {
+            mc_st_f32x4(p.weights_mc + gi, wv4);
+          } else {
+            for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = wv4;
+          }
+          if (s.shadow_offset >= 0) {
+            const uint32_t b0 = pack_bf16x2(wv4.x, wv4.y), b1 = pack_bf16x2(wv4.z, wv4.w);
+            if (flat_shadow) {
+              const long long so = s.shadow_offset + i;
+              if (!p.bcast_shadow) {
+                *reinterpret_cast<uint2*>(p.shadow_local + so) = make_uint2(b0, b1);
+              } else if (MULTIMEM) {
+                mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
               } else {
-                const float wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
+                for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
+              }
+            } else {
+              const float wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  const long long e = i + q;
-                  const long long so = s.shadow_offset + (e / s.row_len) * s.row_pitch + (e % s.row_len);
-                  const __nv_bfloat16 bq = __float2bfloat16(wv[q]);
-                  for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = bq;  // P2P scalar stores (tiny layers only)
-                }
+              for (int q = 0; q < 4; ++q) {
+                const long long e = i + q;
+                const long long so = s.shadow_offset + (e / s.row_len) * s.row_pitch + (e % s.row_len);
+                const __nv_bfloat16 bq = __float2bfloat16(wv[q]);
+                for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = bq;  // P2P scalar stores (tiny layers only)
               }
             }
           }
         }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) g[u] = gn[u];
+        b4 = b4_next;
       }
       // scalar tail of my slice (numel not a multiple of 4)
       for (long long i = lo + (n4 << 2) + tid; i < hi; i += nthreads) {
@@ -295,9 +303,203 @@ __device__ __forceinline__ void fused_allreduce_gd_body(const FusedParams& p) {
   }
 }
 
+// ----------------------------------------------------------------------------------------------------------------
+// PUSH form of the exchange (the default): no load ever crosses NVLink.
+//   phase 1  every rank STORES, for each peer q, the part of its gradient that q owns into q's staging slab
+//            (region `rank` of the segment there); stores are posted, so a few SMs keep the link busy, where the
+//            pull form (multimem.ld_reduce / peer loads) stalls ~3 us per 64 KB of loads an SM can hold in registers
+//            (measured at 2 ranks, 8 CTAs: 61 GB/s, 1.24 ms for AlexNet fc6 - longer than the backward pass it
+//            was meant to hide behind);
+//   handshake: the last CTA to finish phase 1 publishes "my pushes are out" to everybody (and to itself);
+//   phase 2  once all contributions have arrived, the owner sums its own slice (local gradient + W - 1 staging
+//            regions, all local HBM reads), applies the Znicz update to the fp32 master and momentum, and publishes
+//            the bf16 operand copy (and flagged fp32 segments) with multimem.st / peer stores;
+//   phase 3  clears the local gradient of segments whose producers accumulate, completion handshake.
+// Gradients need no second parity buffer here: nobody reads another rank's gradient slab.
+// Staging layout: a segment of numel n occupies the same [offset, offset + n) range in the staging slab; its W
+// chunks of `chunk` = roundup4(ceil(n / W)) elements hold, on rank q, the contributions of ranks 0..W-1 to q's slice
+// (W * chunk never exceeds n rounded up to the 64-element slab alignment).
+// ----------------------------------------------------------------------------------------------------------------
+template <bool MULTIMEM>
+__device__ __forceinline__ void fused_push_gd_body(const FusedParams& p) {
+  const int ready_slot = (p.channel * 2 + 0) * MAX_WORLD;
+  const int done_slot = (p.channel * 2 + 1) * MAX_WORLD;
+  const uint32_t epoch = p.epochs[p.channel] + 1;
+  const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  constexpr int UNROLL = 8;
+
+  // ---- phase 1: push my contributions to the owners ----
+  for (int si = 0; si < p.nseg; ++si) {
+    const FusedSeg s = p.seg[si];
+    long long chunk = (s.numel + p.world - 1) / p.world;
+    chunk = (chunk + 3) & ~3LL;
+    for (int q = 0; q < p.world; ++q) {
+      if (q == p.rank) continue;
+      const long long lo = min(s.numel, chunk * q), hi = min(s.numel, lo + chunk);
+      const long long n4 = (hi - lo + 3) >> 2;      // whole 16-byte vectors (the slab is padded to 64 elements)
+      const float4* src = reinterpret_cast<const float4*>(p.grads_local + s.offset + lo);
+      float4* dst = reinterpret_cast<float4*>(p.stage_peer[q] + s.offset + chunk * p.rank);
+      for (long long b4 = tid; b4 < n4; b4 += nthreads * UNROLL) {
+        float4 g[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const long long i4 = b4 + u * nthreads;
+          if (i4 < n4) g[u] = src[i4];
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const long long i4 = b4 + u * nthreads;
+          if (i4 < n4) dst[i4] = g[u];
+        }
+      }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(p.cta_counter + p.channel, 1u);
+    if (prev == gridDim.x - 1) {
+      __threadfence_system();
+      for (int r = 0; r < p.world; ++r) st_release_sys(p.flags_peer[r] + ready_slot + p.rank, epoch);   // me included
+      p.cta_counter[p.channel] = 0;
+    }
+  }
+  // ---- wait for every rank's pushes (and for all CTAs of this rank: its own flag) ----
+  int my_ok = 1;
+  if (threadIdx.x == 0) {
+    const long long t0 = clock64();
+    for (int r = 0; r < p.world && my_ok; ++r) {
+      const uint32_t* f = p.flags_local + ready_slot + r;
+      while (static_cast<int32_t>(ld_acquire_sys(f) - epoch) < 0) {
+        if (clock64() - t0 > p.timeout_cycles) {
+          my_ok = 0;
+          break;
+        }
+        __nanosleep(64);
+      }
+    }
+  }
+  const bool ok = __syncthreads_and(my_ok) != 0;
+
+  // ---- phase 2: reduce my slice from local memory, update, publish ----
+  if (ok) {
+    for (int si = 0; si < p.nseg; ++si) {
+      const FusedSeg s = p.seg[si];
+      long long chunk = (s.numel + p.world - 1) / p.world;
+      chunk = (chunk + 3) & ~3LL;
+      const long long lo = min(s.numel, chunk * p.rank);
+      const long long hi = min(s.numel, lo + chunk);
+      const long long n4 = (hi - lo) >> 2;
+      const bool flat_shadow = s.shadow_offset >= 0 && s.row_len == s.row_pitch;
+      const bool bcast_master = p.bcast_master || (s.flags & SEG_BCAST_MASTER);
+      const float* stage = p.stage_local + s.offset;
+      for (long long i4 = tid; i4 < n4; i4 += nthreads) {
+        const long long i = lo + (i4 << 2);
+        const long long gi = s.offset + i;
+        float4 g = *reinterpret_cast<const float4*>(p.grads_local + gi);
+        // (an accumulating segment restarts from zero: the thread that read an element clears it)
+        if (s.flags & SEG_ZERO_OTHER) *reinterpret_cast<float4*>(p.grads_local + gi) = make_float4(0, 0, 0, 0);
+        for (int r = 0; r < p.world; ++r) {
+          if (r == p.rank) continue;
+          const float4 o = *reinterpret_cast<const float4*>(stage + chunk * r + (i4 << 2));
+          g.x += o.x; g.y += o.y; g.z += o.z; g.w += o.w;
+        }
+        float4 wv4 = *reinterpret_cast<const float4*>(p.weights_local + gi);
+        float4 vv = *reinterpret_cast<const float4*>(p.vel_local + gi);
+        wv4.x = gd_apply(wv4.x, g.x, vv.x, s, p.grad_scale);
+        wv4.y = gd_apply(wv4.y, g.y, vv.y, s, p.grad_scale);
+        wv4.z = gd_apply(wv4.z, g.z, vv.z, s, p.grad_scale);
+        wv4.w = gd_apply(wv4.w, g.w, vv.w, s, p.grad_scale);
+        *reinterpret_cast<float4*>(p.vel_local + gi) = vv;
+        if (!bcast_master) {
+          *reinterpret_cast<float4*>(p.weights_local + gi) = wv4;
+        } else if (MULTIMEM) {
+          mc_st_f32x4(p.weights_mc + gi, wv4);
+        } else {
+          for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.weights_peer[r] + gi) = wv4;
+        }
+        if (s.shadow_offset >= 0) {
+          const uint32_t b0 = pack_bf16x2(wv4.x, wv4.y), b1 = pack_bf16x2(wv4.z, wv4.w);
+          if (flat_shadow) {
+            const long long so = s.shadow_offset + i;
+            if (!p.bcast_shadow) {
+              *reinterpret_cast<uint2*>(p.shadow_local + so) = make_uint2(b0, b1);
+            } else if (MULTIMEM) {
+              mc_st_f32x2(reinterpret_cast<float*>(p.shadow_mc + so), __uint_as_float(b0), __uint_as_float(b1));
+            } else {
+              for (int r = 0; r < p.world; ++r) *reinterpret_cast<uint2*>(p.shadow_peer[r] + so) = make_uint2(b0, b1);
+            }
+          } else {
+            const float wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const long long e = i + q;
+              const long long so = s.shadow_offset + (e / s.row_len) * s.row_pitch + (e % s.row_len);
+              const __nv_bfloat16 bq = __float2bfloat16(wv[q]);
+              for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = bq;
+            }
+          }
+        }
+      }
+      // scalar tail of my slice (numel not a multiple of 4)
+      for (long long i = lo + (n4 << 2) + tid; i < hi; i += nthreads) {
+        const long long gi = s.offset + i;
+        float g = p.grads_local[gi];
+        if (s.flags & SEG_ZERO_OTHER) p.grads_local[gi] = 0.0f;
+        for (int r = 0; r < p.world; ++r)
+          if (r != p.rank) g += stage[chunk * r + (i - lo)];
+        float v = p.vel_local[gi];
+        const float w = gd_apply(p.weights_local[gi], g, v, s, p.grad_scale);
+        p.vel_local[gi] = v;
+        if (!bcast_master) p.weights_local[gi] = w;
+        else
+          for (int r = 0; r < p.world; ++r) p.weights_peer[r][gi] = w;
+        if (s.shadow_offset >= 0) {
+          const long long so = s.shadow_offset + (i / s.row_len) * s.row_pitch + (i % s.row_len);
+          for (int r = 0; r < p.world; ++r) p.shadow_peer[r][so] = __float2bfloat16(w);
+        }
+      }
+    }
+    // ---- phase 3: the parts of accumulating segments that OTHER ranks own restart from zero too ----
+    // (their last readers were this rank's phase-1 pushes, complete on every CTA: the rank's own "ready" flag was
+    // awaited above; the own slice was cleared element by element in phase 2)
+    for (int si = 0; si < p.nseg; ++si) {
+      const FusedSeg s = p.seg[si];
+      if (!(s.flags & SEG_ZERO_OTHER)) continue;
+      long long chunk = (s.numel + p.world - 1) / p.world;
+      chunk = (chunk + 3) & ~3LL;
+      const long long lo = min(s.numel, chunk * p.rank);
+      const long long hi = min(s.numel, lo + chunk);
+      float* z = p.grads_local + s.offset;
+      for (long long i = tid; i < s.numel; i += nthreads)
+        if (i < lo || i >= hi) z[i] = 0.0f;
+    }
+  }
+
+  // ---- completion: the last CTA tells the peers that all my stores are out and waits for theirs ----
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(p.cta_counter + 64 + p.channel, 1u);
+    if (prev == gridDim.x - 1) {
+      bool fine = ok;
+      __threadfence_system();
+      for (int r = 0; r < p.world; ++r)
+        if (r != p.rank) st_release_sys(p.flags_peer[r] + done_slot + p.rank, epoch);
+      if (fine) fine = wait_all(p, done_slot, epoch);
+      if (!fine) atomicExch(p.status, 1 + p.channel);
+      p.cta_counter[64 + p.channel] = 0;
+      p.epochs[p.channel] = epoch;
+      __threadfence();
+    }
+  }
+}
+
 template <bool MULTIMEM>
 __global__ void __launch_bounds__(FUSED_THREADS, 1) fused_allreduce_gd_kernel(const FusedParams p) {
-  fused_allreduce_gd_body<MULTIMEM>(p);
+  if (p.push) fused_push_gd_body<MULTIMEM>(p);
+  else fused_allreduce_gd_body<MULTIMEM>(p);
 }
 
 // All ranks of a group on ONE GPU, as one cooperative launch: blockIdx.y is the rank, every rank's CTAs run the very
@@ -305,7 +507,8 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) fused_allreduce_gd_kernel(co
 // wait for each other's flags, so all CTAs must be resident at once - hence the cooperative launch.  This is how a
 // single-GPU box exercises the flag protocol, the slice arithmetic and the per-segment options.
 __global__ void __launch_bounds__(FUSED_THREADS, 1) fused_allreduce_gd_emulated_kernel(const FusedParams* ps) {
-  fused_allreduce_gd_body<false>(ps[blockIdx.y]);
+  if (ps[blockIdx.y].push) fused_push_gd_body<false>(ps[blockIdx.y]);
+  else fused_allreduce_gd_body<false>(ps[blockIdx.y]);
 }
 
 }  // namespace vb
@@ -320,16 +523,22 @@ using namespace vb;
 //   use_multimem: bit 0 = NVLS multimem path; bit 1 = keep the fp32 master slice local (no broadcast);
 //                 bit 2 = keep the bf16 shadow slice local (flat-shadow segments only; peer-TMA weight delivery)
 //                 bit 3 = wait for the peers' gradients in a separate 1-CTA launch ahead of the worker CTAs
+//                 bit 4 = PUSH form: gradients are stored into the owners' staging slabs (stage_local / stage_peer:
+//                         slabs laid out like the gradient slab); cta_counter then needs 128 words
 extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg, const long long* segs,
                                      const float* hyper, float* grads_local, float* grads_mc, float** grads_peer,
                                      float* grads_other_local, float* weights_local, float* weights_mc,
                                      float** weights_peer, float* vel_local, void* shadow_local, void* shadow_mc,
                                      void** shadow_peer, unsigned int* flags_local, unsigned int** flags_peer,
                                      unsigned int* epochs, unsigned int* cta_counter, int* status, float grad_scale,
-                                     int n_ctas, int use_multimem, double timeout_s, cudaStream_t stream) {
+                                     int n_ctas, int use_multimem, double timeout_s, float* stage_local,
+                                     float** stage_peer, cudaStream_t stream) {
   const int local_master = (use_multimem >> 1) & 1, local_shadow = (use_multimem >> 2) & 1;
   const int split_handshake = (use_multimem >> 3) & 1;
+  const int push = (use_multimem >> 4) & 1;
   use_multimem &= 1;
+  VB_REQUIRE(!push || (stage_local != nullptr && stage_peer != nullptr), "vb_fused_allreduce_gd: push mode needs the staging slabs");
+  VB_REQUIRE(!push || !split_handshake, "vb_fused_allreduce_gd: push mode has no separate handshake launch");
   VB_REQUIRE(world >= 2 && world <= MAX_WORLD, "vb_fused_allreduce_gd: world size %d not in [2,%d]", world, MAX_WORLD);
   VB_REQUIRE(nseg >= 1 && nseg <= MAX_SEGS, "vb_fused_allreduce_gd: %d segments (max %d per launch)", nseg, MAX_SEGS);
   VB_REQUIRE(channel >= 0 && channel < 64, "vb_fused_allreduce_gd: channel %d out of range", channel);
@@ -364,6 +573,9 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
   }
   p.flags_local = flags_local; p.epochs = epochs; p.cta_counter = cta_counter; p.status = status;
   p.grad_scale = grad_scale;
+  p.push = push;
+  p.stage_local = stage_local;
+  for (int r = 0; r < MAX_WORLD; ++r) p.stage_peer[r] = (push && r < world) ? stage_peer[r] : nullptr;
   p.bcast_master = !local_master;
   p.bcast_shadow = !local_shadow;
   p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
@@ -398,14 +610,16 @@ extern "C" int vb_fused_allreduce_gd(int world, int rank, int channel, int nseg,
 // Test / bring-up entry point: `world` ranks emulated on the current GPU (see fused_allreduce_gd_emulated_kernel).
 // Per-rank arrays hold `world` device pointers each (rank r's gradient slab of this step's parity, the other
 // parity's, weights, momentum, bf16 shadow, flag words [64][2][8], epoch words [64], CTA counters [64], status word).
-// `params_dev` is caller-provided device scratch of at least world * vb_fused_params_bytes() bytes.
+// `params_dev` is caller-provided device scratch of at least world * vb_fused_params_bytes() bytes.  options bit 4 with
+// `stage` (one staging slab per rank) selects the push form; cta_counter then needs 128 words per rank.
 extern "C" long long vb_fused_params_bytes() { return static_cast<long long>(sizeof(FusedParams)); }
 
 extern "C" int vb_fused_allreduce_gd_emulated(int world, int channel, int nseg, const long long* segs,
                                               const float* hyper, float** grads, float** grads_other, float** weights,
                                               float** vel, void** shadow, unsigned int** flags, unsigned int** epochs,
                                               unsigned int** cta_counter, int** status, float grad_scale, int n_ctas,
-                                              int options, double timeout_s, void* params_dev, cudaStream_t stream) {
+                                              int options, double timeout_s, void* params_dev, float** stage,
+                                              cudaStream_t stream) {
   VB_REQUIRE(world >= 2 && world <= MAX_WORLD, "vb_fused_allreduce_gd_emulated: world size %d not in [2,%d]", world, MAX_WORLD);
   VB_REQUIRE(nseg >= 1 && nseg <= MAX_SEGS, "vb_fused_allreduce_gd_emulated: %d segments (max %d)", nseg, MAX_SEGS);
   VB_REQUIRE(channel >= 0 && channel < 64, "vb_fused_allreduce_gd_emulated: channel %d out of range", channel);
@@ -442,6 +656,11 @@ extern "C" int vb_fused_allreduce_gd_emulated(int world, int channel, int nseg, 
     p.grad_scale = grad_scale;
     p.bcast_master = !((options >> 1) & 1);
     p.bcast_shadow = !((options >> 2) & 1);
+    p.push = ((options >> 4) & 1) && stage != nullptr;
+    if (p.push) {
+      p.stage_local = stage[r];
+      for (int q = 0; q < world; ++q) p.stage_peer[q] = stage[q];
+    }
     p.timeout_cycles = static_cast<long long>(timeout_s * 1.9e9);
     p.phase = 0;
   }

@@ -27,7 +27,7 @@ from ctypes import c_double, c_float, c_int, c_longlong, c_void_p
 
 import numpy
 
-SYMMETRIC_KINDS = ("weights", "weights_bf16", "grads", "grads1", "dp_flags", "velocity")
+SYMMETRIC_KINDS = ("weights", "weights_bf16", "grads", "grads1", "grads_in", "dp_flags", "velocity")
 MAX_WORLD = 8
 MAX_SEGS = 16          # csrc/comm_fused.cu
 SEG_ZERO_OTHER = 1     # the segment's gradient kernels accumulate: the update kernel clears the other parity's buffer
@@ -36,7 +36,7 @@ SEG_BCAST_MASTER = 2   # forward passes read this segment's fp32 master: always 
 
 class DataParallel(object):
     def __init__(self, mode="fused", n_ctas=None, timeout_s=20.0, use_multimem=None, shard_master=True,
-                 weight_delivery="multicast", split_handshake=False, bucket_bytes=4 << 20):
+                 weight_delivery="multicast", split_handshake=False, bucket_bytes=4 << 20, exchange="pull"):
         import torch
         import torch.distributed as dist
         if not dist.is_initialized():
@@ -46,13 +46,23 @@ class DataParallel(object):
         self.world_size = dist.get_world_size()
         if self.world_size > MAX_WORLD:
             raise ValueError("the fused kernel supports at most %d ranks" % MAX_WORLD)
-        # CTAs of the update kernel = SMs the backward GEMMs leave free while an exchange is pending.  Each rank
-        # reduces 1/world of every layer, so two ranks move twice the bytes per rank that four do: 8 SMs (~200 GB/s
-        # of multimem.ld_reduce at ~64 KB in flight per SM) for 2 ranks, 4 SMs beyond.
-        self.n_ctas = int(n_ctas) if n_ctas else (8 if self.world_size <= 2 else 4)
+        # CTAs of the update kernel = SMs the backward GEMMs leave free while an exchange is pending.  One SM pulls
+        # ~8 GB/s through multimem.ld_reduce (or peer loads: the same), whatever it keeps in flight, and each rank
+        # reduces 244 MB / world for AlexNet.  Measured at 2 ranks (ms per step, 1 GPU = 2.32): 8 SMs 3.45, 16 SMs
+        # 2.49, 24 SMs 2.57, 32 SMs 2.56 -> 16 SMs up to 4 ranks, 8 beyond.
+        self.n_ctas = int(n_ctas) if n_ctas else (16 if self.world_size <= 4 else 8)
         self.n_ctas = max(2, (self.n_ctas + 1) & ~1)
         # peer-TMA delivery describes ONE layer's weight matrix per launch: no bucketing there
         self.bucket_bytes = 0 if weight_delivery == "peer_tma" else int(bucket_bytes)
+        # exchange: how gradients reach the rank that owns (updates) a slice:
+        #   "pull": the owner reads them: multimem.ld_reduce through the switch (or peer loads), the next batch
+        #           requested while the current one is consumed (default);
+        #   "push": every rank STORES its contributions into the owner's staging slab, the owner reduces from local
+        #           memory.  Measured at 2 ranks with 8 SMs: slower than the pull form (fc6: 1.9 vs 1.2 ms) - remote
+        #           stores from a few SMs do not reach link bandwidth either; kept as an option.
+        if exchange not in ("push", "pull"):
+            raise ValueError("exchange must be 'push' or 'pull'")
+        self.exchange = exchange
         self.profile = False       # eager runs: time every exchange kernel with CUDA events (bucket_times())
         self._prof_events = []
         self.buckets = []          # launch units: lists of GD units exchanged by one kernel, in backward order
@@ -125,7 +135,9 @@ class DataParallel(object):
             if hasattr(wf, "decision") and wf.decision is not None:
                 wf.decision.dp_group = self
             return
-        self.comm_stream = torch.cuda.Stream(device=dev.torch_device)
+        # high priority: when SMs free up, the exchange kernel's CTAs are placed before the (many) pending CTAs of the
+        # backward kernels - otherwise it can starve behind them until the backward pass ends
+        self.comm_stream = torch.cuda.Stream(device=dev.torch_device, priority=-1)
         self.arena = wf.get_arena(dev)
         for gd in wf.gds:
             if hasattr(gd, "gradient_weights") and gd.weights is not None and gd.weights:
@@ -143,10 +155,12 @@ class DataParallel(object):
         for gd in self.units:
             for w in (gd.weights, gd.bias):
                 if w is not None and w:
-                    arena.mirror("grads1", w.devmem.view(-1))
+                    # pull: second gradient parity (peers read my slab while I start the next step);
+                    # push: staging slab the peers store their contributions into
+                    arena.mirror("grads1" if self.exchange == "pull" else "grads_in", w.devmem.view(-1))
         self.flags = arena.alloc("dp_flags", "flags", 64 * 2 * MAX_WORLD, torch.int32)
         self.epochs = torch.zeros(64, dtype=torch.int32, device=dev.torch_device)
-        self.cta_counter = torch.zeros(64, dtype=torch.int32, device=dev.torch_device)
+        self.cta_counter = torch.zeros(128, dtype=torch.int32, device=dev.torch_device)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev.torch_device)
         torch.cuda.synchronize()
         group = self._dist.group.WORLD
@@ -171,7 +185,7 @@ class DataParallel(object):
                     or cur["shadow_slab"] != info["shadow_slab"] or len(cur["segs"]) + len(info["segs"]) > MAX_SEGS):
                 cur = {"channel": len(self.buckets), "units": [], "segs": [], "kinds": [], "bytes": 0,
                        "slab": info["slab"], "shadow_slab": info["shadow_slab"], "pending": 0}
-                for key in ("grads", "weights", "shadow", "vel", "flags"):
+                for key in ("grads", "weights", "shadow", "vel", "flags", "stage"):
                     cur[key] = info[key]
                 self.buckets.append(cur)
             cur["units"].append(gd)
@@ -235,7 +249,12 @@ class DataParallel(object):
                     peer_shadow = (sidx, soff, n_rows // W)
         info = {"slab": slab_idx, "segs": segs, "kinds": hyper_keys,
                 "shadow_slab": getattr(self, "_shadow_slab", 0)}
-        info["grads"] = [self._slab_ptrs("grads", slab_idx), self._slab_ptrs("grads1", slab_idx)]
+        if self.exchange == "push":
+            info["grads"] = [self._slab_ptrs("grads", slab_idx)] * 2
+            info["stage"] = self._slab_ptrs("grads_in", slab_idx)
+        else:
+            info["grads"] = [self._slab_ptrs("grads", slab_idx), self._slab_ptrs("grads1", slab_idx)]
+            info["stage"] = (0, 0, [0] * self.world_size)
         info["weights"] = self._slab_ptrs("weights", slab_idx)
         info["shadow"] = self._slab_ptrs("weights_bf16", info["shadow_slab"])
         if peer_shadow is not None:
@@ -251,7 +270,7 @@ class DataParallel(object):
         info["flags"] = (fl[0] + fl_off, [p + fl_off for p in fl[2]])
         # per-parity views for the backward GEMMs
         views = []
-        for kind in ("grads", "grads1"):
+        for kind in (("grads", "grads") if self.exchange == "push" else ("grads", "grads1")):
             slab = arena.slabs[kind][slab_idx][0]
             pair = []
             for w in (gd.weights, gd.bias):
@@ -334,8 +353,10 @@ class DataParallel(object):
                     gd.learning_rate_bias, gd.gradient_moment_bias)
                 hyper += [lr, gd.weights_decay_bias, gd.l1_vs_l2_bias, mom]
         hyper = (c_float * (4 * nseg))(*hyper)
+        push = self.exchange == "push"
         g_local, g_mc, g_peers = b["grads"][self.parity]
-        go_local = b["grads"][1 - self.parity][0]
+        go_local = 0 if push else b["grads"][1 - self.parity][0]
+        st_local, _, st_peers = b["stage"]
         w_local, w_mc, w_peers = b["weights"]
         s_local, s_mc, s_peers = b["shadow"]
         f_local, f_peers = b["flags"]
@@ -357,8 +378,9 @@ class DataParallel(object):
                 c_void_p(self.epochs.data_ptr()), c_void_p(self.cta_counter.data_ptr()),
                 c_void_p(self.status.data_ptr()), c_float(self.grad_scale), c_int(b["n_ctas"]),
                 c_int((1 if self.use_multimem else 0) | (2 if self.shard_master else 0) |
-                      (4 if b.get("peer_shadow") else 0) | (8 if self.split_handshake else 0)),
-                c_double(self.timeout_s),
+                      (4 if b.get("peer_shadow") else 0) | (8 if (self.split_handshake and not push) else 0) |
+                      (16 if push else 0)),
+                c_double(self.timeout_s), c_void_p(st_local), arr(st_peers),
                 c_void_p(self.comm_stream.cuda_stream))
             _lib.check(rc, "vb_fused_allreduce_gd")
             kernels.LAUNCHES[0] += 2 if self.split_handshake else 1
@@ -403,7 +425,8 @@ class DataParallel(object):
             main.wait_event(ev)
         self._pending_events = []
         if self.mode == "fused":
-            self.parity ^= 1
+            if self.exchange == "pull":
+                self.parity ^= 1      # (push: nobody reads another rank's gradients, one buffer does)
             if self._reserved:
                 from ..ops import _lib
                 _lib.lib().vb_set_sm_reserve(c_int(0))
