@@ -27,12 +27,81 @@ def test_web_status_update_and_service():
         wfs = _post(base + "/service", {"request": "workflows"})
         assert wfs["m1"]["name"] == "wf" and wfs["m1"]["slaves"]["s1"]["state"] == "WORK"
         assert _post(base + "/service", {"request": "graph", "id": "m1"})["graph"] == "digraph {}"
-        assert b"wf" in urllib.request.urlopen(base + "/", timeout=10).read()
+        assert b"<td>wf</td>" in urllib.request.urlopen(base + "/plain", timeout=10).read()
+        page = urllib.request.urlopen(base + "/", timeout=10).read()
+        assert b"<script>" in page and b"request:'logs'" in page      # the polling UI
         srv.drop_time = -1
         _post(base + "/update", {"id": "m2", "name": "x"})
         assert "m1" not in _post(base + "/service", {"request": "workflows"})
     finally:
         srv.stop()
+
+
+def test_web_status_queries_logs_and_events_of_other_processes(tmp_path):
+    """Log / event queries by session, node, level, text (reference: MongoDB queries of veles/web_status.py:113-186)
+    over this process' sinks and the JSON-lines files other processes wrote."""
+    import logging
+    from veles_b200.logger import Logger, events, install_log_sink, logs
+    from veles_b200.web_status import WebServer
+    other = tmp_path / "9.9-1.logs.jsonl"
+    other.write_text("\n".join(json.dumps(r) for r in [
+        {"session": "9.9", "node": "far:1", "time": 10.0, "level": "INFO", "levelno": 20, "name": "Loader",
+         "message": "epoch 1 done"},
+        {"session": "9.9", "node": "far:1", "time": 11.0, "level": "ERROR", "levelno": 40, "name": "Decision",
+         "message": "diverged"}]) + "\n")
+    (tmp_path / "9.9-1.events.jsonl").write_text(json.dumps(
+        {"session": "9.9", "time": 10.5, "domain": "Workflow", "name": "run", "type": "begin"}) + "\n")
+    install_log_sink(str(tmp_path / "own.logs.jsonl"))
+    try:
+        lg = logging.getLogger("QueryTest")
+        lg.setLevel(logging.INFO)
+        lg.warning("needle in %s", "haystack")
+        Logger().event("probe", "single", height=3)
+        srv = WebServer(port=0, log_dir=str(tmp_path)).start()
+        try:
+            url = "http://127.0.0.1:%d/service" % srv.port
+            far = _post(url, {"request": "logs", "session": "9.9"})["logs"]
+            assert [r["message"] for r in far] == ["epoch 1 done", "diverged"]
+            assert [r["message"] for r in _post(url, {"request": "logs", "session": "9.9", "level": "warning"})["logs"]] \
+                == ["diverged"]
+            mine = _post(url, {"request": "logs", "text": "NEEDLE"})["logs"]
+            assert len(mine) == 1 and mine[0]["session"] == events.session and mine[0]["level"] == "WARNING"
+            assert _post(url, {"request": "logs", "node": "far:1", "since": 10.5, "limit": 5})["logs"][0]["time"] == 11.0
+            ev = _post(url, {"request": "events", "session": "9.9"})["events"]
+            assert len(ev) == 1 and ev[0]["name"] == "run"
+            own = _post(url, {"request": "events", "name": "probe"})["events"]
+            assert own and own[-1]["height"] == 3
+            sessions = _post(url, {"request": "sessions"})["sessions"]
+            assert "9.9" in sessions and events.session in sessions
+        finally:
+            srv.stop()
+    finally:
+        logging.getLogger().removeHandler(logs)
+
+
+def test_frontend_composer_serves_the_form_and_returns_the_posted_command_line():
+    """``--frontend`` (reference: veles/__main__.py:258-327): the form lists the parser's options; the argv the page
+    posts comes back from serve()."""
+    import threading
+    from veles_b200.scripts.generate_frontend import generate, serve
+    page = generate(["wf.py", "cfg.py", "root.a.b=1"])
+    assert "data-opt='--snapshot'" in page or "data-opt='-w'" in page
+    assert "value='wf.py'" in page and "function compose()" in page and "--frontend" not in page.split("<table>")[1]
+    got = {}
+
+    def drive(port):
+        def client():
+            base = "http://127.0.0.1:%d" % port
+            got["page"] = urllib.request.urlopen(base + "/", timeout=10).read()
+            req = urllib.request.Request(base + "/cmdline", data=json.dumps(
+                {"cmdline": "-v debug 'my wf.py' - root.x.y=3"}).encode())
+            urllib.request.urlopen(req, timeout=10).read()
+        threading.Thread(target=client, daemon=True).start()
+
+    argv = serve(["wf.py"], open_browser=False, ready=drive, timeout=20)
+    assert argv == ["-v", "debug", "my wf.py", "-", "root.x.y=3"]
+    assert b"Run</button>" in got["page"]
+    assert serve([], open_browser=False, timeout=0.2) is None       # nobody posted: cancelled
 
 
 def test_launcher_status_heartbeat_payload():

@@ -101,6 +101,15 @@ def test_ensemble_train_then_test(tmp_path):
     assert r.returncode == 0, r.stdout.decode()[-3000:]
     d2 = json.loads(res2.read_text())
     assert len(d2["models"]) == 2 and all("EvaluationFitness" in m for m in d2["models"])
+    # the members trained under this command line's overrides (one epoch => the snapshot is of a FINISHED run, which
+    # the evaluation above still replays) and wrote distinct files
+    names = sorted(os.path.basename(m["Snapshot"]) for m in data["models"])
+    assert names[0].startswith("0000_") and names[1].startswith("0001_")
+    assert all(m["Best epoch"] <= 1 for m in data["models"])
+    # resuming a finished run without new limits returns at once instead of waiting on a shut gate
+    r = cli("-w", data["models"][0]["Snapshot"], os.path.join(SAMPLES, "mnist.py"), "-",
+            "root.mnist.loader.n_train=400", "root.mnist.loader.n_valid=200", timeout=120)
+    assert r.returncode == 0 and b"already complete" in r.stdout, r.stdout.decode()[-2000:]
 
 
 import pytest as _pytest

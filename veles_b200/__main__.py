@@ -24,7 +24,7 @@ import numpy
 
 from . import __version__, prng
 from .cmdline import CommandLineBase
-from .config import root
+from .config import root, get
 from .import_file import import_file_as_module, import_file_as_package
 from .launcher import Launcher
 from .logger import Logger
@@ -67,6 +67,13 @@ class Main(Logger, CommandLineBase):
     def _setup_logging(self):
         level = CommandLineBase.LOG_LEVEL_MAP[self.args.verbosity]
         Logger.setup_logging(level)
+        log_dir = get(root.common.dirs.logs, None) if get(root.common.engine.log_sinks, False) else None
+        if log_dir:
+            # JSON-lines sinks the web status searches (the reference's MongoDB logging: veles/logger.py:226-262)
+            from .logger import events, install_log_sink
+            stem = os.path.join(log_dir, "%s-%d" % (events.session, os.getpid()))
+            install_log_sink(stem + ".logs.jsonl")
+            events.open(stem + ".events.jsonl")
         for name in filter(None, self.args.debug.split(",")):
             logging.getLogger(name).setLevel(logging.DEBUG)
         if self.args.debug_pickle:
@@ -306,8 +313,20 @@ class Main(Logger, CommandLineBase):
         if args.version:
             print("veles_b200", __version__)
             return Main.EXIT_SUCCESS
-        if args.html_help or args.frontend:
-            print("The HTML help / web frontend are served by veles_b200.web_status; see docs/.")
+        if args.frontend:
+            # interactive composer (reference: veles/__main__.py:258-327): serve the option form locally, then run
+            # with the command line the user posted
+            from .scripts.generate_frontend import serve
+            composed = serve([a for a in self.argv if a != "--frontend"])
+            if not composed:
+                print("Cancelled.")
+                return Main.EXIT_SUCCESS
+            print("Running with the following command line: %s" % " ".join(composed))
+            self.argv = [a for a in composed if a != "--frontend"]
+            args = self._parse()
+        if args.html_help:
+            from .scripts.generate_frontend import generate
+            print(generate(self.argv))
             return Main.EXIT_SUCCESS
         if not args.workflow:
             Main.init_parser(ignore_conflicts=True).print_help()

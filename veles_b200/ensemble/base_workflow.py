@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import json
 import os
+import re
 import subprocess
 import sys
 import tempfile
@@ -64,6 +65,10 @@ class EnsembleManagerBase(Unit):
             elif a.startswith("-") and a != "-":
                 keep.append(a)
         return keep
+
+    def _overrides(self):
+        """The ``root.x.y=value`` positionals of this run's command line: every member trains under them too."""
+        return [a for a in self.argv if re.match(r"^root\.[\w.]+=", a)]
 
     def command(self, index, result_path):
         raise NotImplementedError
@@ -152,7 +157,9 @@ class EnsembleWorkflowBase(Workflow):
     MANAGER = None
 
     def __init__(self, workflow, **kwargs):
-        super(EnsembleWorkflowBase, self).__init__(workflow, **kwargs)
+        manager_keys = ("model", "config_file", "argv", "size", "train_ratio", "input_file", "parallel", "env")
+        super(EnsembleWorkflowBase, self).__init__(
+            workflow, **{k: v for k, v in kwargs.items() if k not in manager_keys})
         self.repeater = Repeater(self)
         self.repeater.link_from(self.start_point)
         self.ensemble = type(self).MANAGER(self, **kwargs)

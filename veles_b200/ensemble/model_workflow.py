@@ -23,7 +23,7 @@ class EnsembleModelManager(EnsembleManagerBase):
     def command(self, index, result_path):
         cmd = [sys.executable, "-m", "veles_b200"] + self._base_argv() + [
             "-s", "--no-logo", "--result-file", result_path, "--train-ratio", str(self.train_ratio),
-            "-r", "%08x" % (0x5eed0000 + index), self.model_path, self.config_file or "",
+            "-r", "%08x" % (0x5eed0000 + index), self.model_path, self.config_file or ""] + self._overrides() + [
             "root.common.ensemble.model_index=%d" % index, "root.common.ensemble.size=%d" % self.size]
         return cmd
 

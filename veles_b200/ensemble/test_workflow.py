@@ -26,7 +26,7 @@ class EnsembleTestManager(EnsembleManagerBase):
     def command(self, index, result_path):
         return [sys.executable, "-m", "veles_b200"] + self._base_argv() + [
             "-s", "--no-logo", "--test", "--result-file", result_path, "-w", self.models[index]["Snapshot"],
-            self.model_path, self.config_file or ""]
+            self.model_path, self.config_file or ""] + self._overrides()
 
 
 class EnsembleTestWorkflow(EnsembleWorkflowBase):

@@ -376,7 +376,9 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
 
     def status(self):
         wf = self.workflow
-        return {"id": self.id, "log_id": self.log_id, "name": wf.name if wf else None, "master": socket.gethostname(),
+        from .logger import events
+        return {"id": self.id, "log_id": self.log_id, "session": events.session, "name": wf.name if wf else None,
+                "master": socket.gethostname(),
                 "time": time.time() - (self._start_time or time.time()), "user": os.environ.get("USER", "?"),
                 "mode": self.mode, "graph": wf.generate_graph(write_on_disk=False) if wf else "",
                 "slaves": self.agent.slaves_status() if self.is_master and self.agent is not None else {},

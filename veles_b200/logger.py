@@ -68,6 +68,102 @@ class EventSink(object):
 events = EventSink()
 
 
+class LogSink(logging.Handler):
+    """Log records as JSON lines (ring buffer + optional file): what the reference kept in MongoDB
+    (``veles/logger.py:226-262``) and the web status queries by session / node / level / text."""
+
+    def __init__(self, capacity=65536):
+        logging.Handler.__init__(self)
+        self.records = []
+        self.capacity = capacity
+        self._file = None
+        self.node = "%s:%d" % (os.uname().nodename, os.getpid())
+
+    def open(self, path):
+        self.acquire()
+        try:
+            if self._file is not None:
+                self._file.close()
+            os.makedirs(os.path.dirname(os.path.abspath(path)) or ".", exist_ok=True)
+            self._file = open(path, "a")
+        finally:
+            self.release()
+
+    def emit(self, record):
+        try:
+            rec = {"session": events.session, "node": self.node, "time": record.created, "level": record.levelname,
+                   "levelno": record.levelno, "name": record.name, "message": record.getMessage(),
+                   "pathname": record.pathname, "lineno": record.lineno}
+            self.records.append(rec)
+            if len(self.records) > self.capacity:
+                del self.records[:len(self.records) - self.capacity]
+            if self._file is not None:
+                self._file.write(json.dumps(rec, default=str) + "\n")
+                self._file.flush()
+        except Exception:  # noqa: BLE001 - logging must never raise
+            pass
+
+
+logs = LogSink()
+
+
+def install_log_sink(path=None):
+    """Route every log record into ``logs`` (idempotent); ``path`` additionally appends JSON lines to a file."""
+    rootlog = logging.getLogger()
+    if logs not in rootlog.handlers:
+        rootlog.addHandler(logs)
+    if path:
+        logs.open(path)
+    return logs
+
+
+def query_records(records, session=None, node=None, level=None, name=None, domain=None, text=None, since=None,
+                  limit=200):
+    """Filter log / event records (dicts): the query language of the web status (``veles/web_status.py:113-186``)."""
+    levelno = logging.getLevelName(level.upper()) if isinstance(level, str) and level else level
+    if not isinstance(levelno, int):
+        levelno = None
+    out = []
+    for r in records:
+        if session is not None and r.get("session") != session:
+            continue
+        if node is not None and r.get("node") != node:
+            continue
+        if levelno is not None and int(r.get("levelno", 0)) < levelno:
+            continue
+        if name is not None and r.get("name") != name:
+            continue
+        if domain is not None and r.get("domain") != domain:
+            continue
+        if since is not None and float(r.get("time", 0)) < float(since):
+            continue
+        if text and text.lower() not in (str(r.get("message", "")) + " " + str(r.get("name", ""))).lower():
+            continue
+        out.append(r)
+    return out[-int(limit):] if limit else out
+
+
+def read_jsonl_dir(directory, suffix):
+    """Records of every ``*<suffix>`` file of a directory (other processes' sinks), oldest first."""
+    out = []
+    if directory and os.path.isdir(directory):
+        for fn in sorted(os.listdir(directory)):
+            if fn.endswith(suffix):
+                try:
+                    with open(os.path.join(directory, fn)) as f:
+                        for line in f:
+                            line = line.strip()
+                            if line:
+                                try:
+                                    out.append(json.loads(line))
+                                except ValueError:
+                                    pass
+                except OSError:
+                    pass
+    out.sort(key=lambda r: r.get("time", 0))
+    return out
+
+
 class Logger(object):
     """Mixin providing ``self.logger`` and shortcuts, plus ``event()``."""
 

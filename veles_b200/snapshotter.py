@@ -55,8 +55,11 @@ class SnapshotterBase(Unit, TriviallyDistributable, metaclass=SnapshotterRegistr
         super(SnapshotterBase, self).__init__(workflow, **kwargs)
         self.verbose = kwargs.get("verbose", True)
         self.prefix = kwargs.get("prefix", "")
-        if "model_index" in kwargs:
-            self.prefix = ("%04d_" % kwargs["model_index"]) + self.prefix
+        # members of an ensemble train side by side (one per GPU) and can reach the same metric in the same epoch:
+        # their files are told apart by the model index the manager passes (root.common.ensemble.model_index)
+        model_index = kwargs.get("model_index", get(root.common.ensemble.model_index, None))
+        if model_index is not None:
+            self.prefix = ("%04d_" % int(model_index)) + self.prefix
         self.compression = kwargs.get("compression", "gz")
         self.compression_level = kwargs.get("compression_level", 6)
         self.interval = kwargs.get("interval", 1)
@@ -137,7 +140,7 @@ class SnapshotterToFile(SnapshotterBase):
         t0 = time.time()
         # written under a temporary name and renamed: a crash (or a failing pickle) in the middle of a snapshot must
         # not leave a truncated file that a restart would then pick up as "the newest snapshot"
-        tmp = self.destination + ".part"
+        tmp = "%s.%d.part" % (self.destination, os.getpid())
         try:
             if self.compression == "snappy":
                 sn = _snappy()

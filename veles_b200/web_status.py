@@ -11,12 +11,59 @@ import time
 from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 
 from .config import root, get
-from .logger import Logger, events
+from .logger import Logger, events, logs, query_records, read_jsonl_dir
+
+PAGE = """<!doctype html><html><head><meta charset="utf-8"><title>veles_b200 status</title>
+<style>body{font-family:sans-serif;margin:1.2em}table{border-collapse:collapse}td,th{border:1px solid #999;padding:3px 8px}
+tr.sel{background:#def}pre{background:#f4f4f4;padding:6px;max-height:18em;overflow:auto}.ERROR,.CRITICAL{color:#b00}
+.WARNING{color:#a60}input,select{margin-right:8px}</style></head><body>
+<h2>Running workflows</h2><table id="wf"><thead><tr><th>workflow</th><th>host</th><th>mode</th><th>uptime</th>
+<th>slaves</th><th>user</th></tr></thead><tbody></tbody></table>
+<h3 id="title"></h3><div id="slaves"></div><pre id="graph"></pre>
+<h3>Logs</h3>level <select id="level"><option>DEBUG</option><option selected>INFO</option><option>WARNING</option>
+<option>ERROR</option></select>text <input id="text" size="24"><label><input type="checkbox" id="all"> all sessions</label>
+<table id="logs"><thead><tr><th>time</th><th>node</th><th>level</th><th>logger</th><th>message</th></tr></thead><tbody></tbody></table>
+<h3>Events</h3><table id="events"><thead><tr><th>time</th><th>domain</th><th>name</th><th>type</th></tr></thead><tbody></tbody></table>
+<script>
+let selected = null;
+async function ask(req){const r = await fetch('/service',{method:'POST',body:JSON.stringify(req)});return r.json();}
+function esc(s){return String(s==null?'':s).replace(/[&<>]/g,c=>({'&':'&amp;','<':'&lt;','>':'&gt;'}[c]));}
+function ts(t){return new Date(1000*t).toISOString().substr(11,12);}
+async function refresh(){
+  const w = await ask({request:'workflows'});
+  const tb = document.querySelector('#wf tbody'); tb.innerHTML='';
+  for (const [id,d] of Object.entries(w)){
+    const tr=document.createElement('tr'); if(id===selected) tr.className='sel';
+    tr.innerHTML=`<td>${esc(d.name)}</td><td>${esc(d.master)}</td><td>${esc(d.mode)}</td><td>${Math.round(d.time||0)} s</td>`+
+      `<td>${Object.keys(d.slaves||{}).length}</td><td>${esc(d.user)}</td>`;
+    tr.onclick=()=>{selected=id;refresh();}; tb.appendChild(tr);
+    if(selected===null) selected=id;
+  }
+  if(selected && w[selected]){
+    document.getElementById('title').textContent=w[selected].name+' ('+selected+')';
+    const sl=w[selected].slaves||{};
+    document.getElementById('slaves').innerHTML=Object.entries(sl).map(([k,v])=>esc(k)+': '+esc(JSON.stringify(v))).join('<br>');
+    const g=await ask({request:'graph',id:selected}); document.getElementById('graph').textContent=g.graph||'';
+  }
+  const sess = document.getElementById('all').checked ? null : (selected && w[selected] ? w[selected].session : null);
+  const lg = await ask({request:'logs',session:sess,level:document.getElementById('level').value,
+                        text:document.getElementById('text').value,limit:100});
+  document.querySelector('#logs tbody').innerHTML=(lg.logs||[]).reverse().map(r=>`<tr class="${esc(r.level)}"><td>${ts(r.time)}</td>`+
+    `<td>${esc(r.node)}</td><td>${esc(r.level)}</td><td>${esc(r.name)}</td><td>${esc(r.message)}</td></tr>`).join('');
+  const ev = await ask({request:'events',session:sess,limit:60});
+  document.querySelector('#events tbody').innerHTML=(ev.events||[]).reverse().map(r=>`<tr><td>${ts(r.time)}</td>`+
+    `<td>${esc(r.domain)}</td><td>${esc(r.name)}</td><td>${esc(r.type)}</td></tr>`).join('');
+}
+refresh(); setInterval(refresh, 2000);
+</script></body></html>"""
 
 
 class WebServer(Logger):
-    def __init__(self, host=None, port=None, drop_time=None):
+    def __init__(self, host=None, port=None, drop_time=None, log_dir=None):
+        """``log_dir``: directory with the ``*.logs.jsonl`` / ``*.events.jsonl`` sinks of the monitored processes
+        (``root.common.dirs.logs``); the server's own in-process sinks are always searched too."""
         super(WebServer, self).__init__()
+        self.log_dir = log_dir if log_dir is not None else get(root.common.dirs.logs, None)
         self.host = host or get(root.common.web.host, "127.0.0.1")
         self.port = port if port is not None else get(root.common.web.port, 8090)
         self.drop_time = drop_time or get(root.common.web.drop_time, 30 * 24 * 3600)
@@ -46,13 +93,29 @@ class WebServer(Logger):
             if kind == "graph":
                 d = self.masters.get(request.get("id"))
                 return {"graph": d.get("graph") if d else None}
-        if kind == "events":
-            session = request.get("session")
-            recs = [r for r in events.records if session in (None, r.get("session"))]
-            return {"events": recs[-int(request.get("limit", 200)):]}
+        if kind in ("events", "logs"):
+            # the reference queried MongoDB collections here (veles/web_status.py:113-186): session / node / level /
+            # logger or event name / text / since filters over the JSON-lines sinks
+            own = events.records if kind == "events" else logs.records
+            recs = read_jsonl_dir(self.log_dir, ".%s.jsonl" % kind) + list(own)
+            seen, uniq = set(), []
+            for r in recs:
+                key = (r.get("session"), r.get("time"), r.get("name"), r.get("message"), r.get("type"))
+                if key not in seen:
+                    seen.add(key)
+                    uniq.append(r)
+            flt = {k: request.get(k) for k in ("session", "node", "level", "name", "domain", "text", "since")}
+            return {kind: query_records(uniq, limit=request.get("limit", 200), **flt)}
+        if kind == "sessions":
+            recs = read_jsonl_dir(self.log_dir, ".logs.jsonl") + list(logs.records)
+            return {"sessions": sorted({r.get("session") for r in recs if r.get("session")})}
         return {"error": "unknown request %r" % kind}
 
     def page(self):
+        return PAGE
+
+    def static_page(self):
+        """Script-free table of the running workflows (``GET /plain``)."""
         rows = []
         with self.lock:
             for mid, d in sorted(self.masters.items(), key=lambda kv: -kv[1]["last_update"]):
@@ -93,7 +156,7 @@ class WebServer(Logger):
                 self._json({"error": "not found"}, 404)
 
             def do_GET(self):
-                body = server.page().encode()
+                body = (server.static_page() if self.path.startswith("/plain") else server.page()).encode()
                 self.send_response(200)
                 self.send_header("Content-Type", "text/html")
                 self.send_header("Content-Length", str(len(body)))

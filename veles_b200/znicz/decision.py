@@ -59,7 +59,17 @@ class DecisionBase(Unit):
         if self.epoch_timestamp is None:
             self.epoch_timestamp = time.time()
         if self.testing:
+            # evaluation of a snapshot: one pass over the test set, whatever state training stopped in (a snapshot
+            # written in the last epoch carries complete = True, which would keep the loader's gate shut)
             self.max_epochs = None
+            self.complete <<= False
+            self.improved <<= False
+        elif bool(self.complete) and self.class_lengths is not None and self.epoch_number is not None:
+            # resumed from the snapshot of a finished run: go on if this run's limits allow more epochs
+            done = int(self.epoch_number) + (0 if self.has_validation else 1)
+            if ((self.max_epochs is None or done < self.max_epochs)
+                    and self._epochs_without_improvement < self.fail_iterations):
+                self.complete <<= False
         return None
 
     @property

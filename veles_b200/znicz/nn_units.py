@@ -20,6 +20,8 @@ Pinned conventions (numpy oracle == device kernels):
 """
 from __future__ import annotations
 
+import time
+
 import numpy
 
 from .. import prng
@@ -137,6 +139,21 @@ class NNWorkflow(AcceleratedWorkflow):
         if self.arena_ is None or self.arena_.device is not device:
             self.arena_ = ParameterArena(device, allocator=self.__dict__.get("arena_allocator_"))
         return self.arena_
+
+    def run(self):
+        decision = getattr(self, "decision", None)
+        if (decision is not None and bool(getattr(decision, "complete", False)) and not self.is_slave
+                and not self.testing):
+            # resumed from the snapshot of a finished training and the limits allow nothing more: the loader's gate
+            # stays shut, so nothing would ever reach the end point
+            self.warning("training is already complete (epoch %s): nothing to run; raise decision.max_epochs / "
+                         "fail_iterations to continue from this snapshot", getattr(decision, "epoch_number", "?"))
+            self._run_time_started_ = time.time()
+            self._finished_ = False
+            self._is_running = True
+            self.on_workflow_finished()
+            return
+        super(NNWorkflow, self).run()
 
 
 def find_arena(unit, device):
