@@ -49,6 +49,8 @@ def parse():
     p.add_argument("--bucket-mb", type=float, default=4.0, help="N>1: parameter bytes that close an exchange bucket")
     p.add_argument("--fc-split-k", action="store_true",
                    help="small-batch fully connected layers: split-K GEMM into an fp32 scratch + bias/activation pass")
+    p.add_argument("--pdl", type=int, default=-1, choices=[-1, 0, 1],
+                   help="programmatic dependent launch of this library's kernels (-1: the engine default)")
     p.add_argument("--ps-async", action="store_true", help="ps_emulation: two jobs in flight per slave (--async-slave)")
     p.add_argument("--model", default="alexnet")
     p.add_argument("--batch", type=int, default=0, help="per-GPU minibatch (default: model's)")
@@ -77,6 +79,13 @@ def reference_unavailable():
         if first:
             why = first
     print(json.dumps({"impl": "reference", "unavailable": why}))
+
+
+def _pdl_state():
+    from veles_b200.ops import kernels as _k
+    on = _k.set_pdl(False)
+    _k.set_pdl(on)
+    return bool(on)
 
 
 def main():
@@ -144,6 +153,9 @@ def main():
     if args.fc_split_k:
         from veles_b200.config import root as _root
         _root.common.engine.two_phase_split_k = True
+    if args.pdl >= 0:
+        from veles_b200.ops import kernels as _k
+        _k.set_pdl(bool(args.pdl))
     cfg = MODEL_CONFIGS[args.model]
     B = args.batch or cfg["minibatch"]
     device = B200Device(index=local_rank)
@@ -310,6 +322,7 @@ def main():
                        "master_weights": (None if world == 1 or args.impl == "nccl" else
                                           ("replicated" if args.replicate_master else "sharded, gathered at epoch ends")),
                        "gemm_schedule": args.gemm_schedule,
+                       "programmatic_dependent_launch": _pdl_state(),
                        "cuda_graph": use_graph,
                        "l2_policy": ("inputs larger than L2: every step gathers a new minibatch from the resident "
                                      "dataset and streams activations >> 126 MB" if args.model == "alexnet" else

@@ -250,6 +250,25 @@ int vb_fused_allreduce_gd_emulated(int world, int channel, int nseg, const long 
                                    unsigned int** flags, unsigned int** epochs, unsigned int** cta_counter,
                                    int** status, float grad_scale, int n_ctas, int options, double timeout_s,
                                    void* params_dev, float** stage, cudaStream_t stream);
+/* Class / epoch ends of a data-parallel group, device-side (csrc/comm_counters.cu): all-reduce n doubles (op 0 sum,
+ * 1 max; n = 0: barrier) through a region of symmetric memory of vb_counter_region_bytes(slot_elems) bytes per rank
+ * (zeroed once; base_peer[r] = rank r's mapping), flags by st.release.sys / ld.acquire.sys; a missing peer sets
+ * *status = 1001 after timeout_s and leaves *epoch alone.  The reference's master summed these out of its slaves'
+ * pickled updates (veles/server.py:401-430). */
+long long vb_counter_region_bytes(long long slot_elems);
+int vb_counter_allreduce(int world, int rank, int n, int op, long long slot_elems, const double* in, double* out,
+                         void* base_local, void** base_peer, unsigned int* epoch, int* status, double timeout_s,
+                         cudaStream_t stream);
+/* All ranks of that exchange on the current GPU in one cooperative launch (single-GPU tests). */
+long long vb_counter_params_bytes(void);
+int vb_counter_allreduce_emulated(int world, int n, int op, long long slot_elems, const double** ins, double** outs,
+                                  void** bases, unsigned int** epochs, int** status, double timeout_s,
+                                  void* params_dev, cudaStream_t stream);
+/* Reassemble sharded fp32 state: for each (offset, numel) pair of segs copy every peer's slice (the update kernel's
+ * slice arithmetic) out of peers[r] into local; order it after a vb_counter_allreduce barrier. */
+int vb_gather_slices(int world, int rank, int nseg, const long long* segs, float* local, void** peers, int n_ctas,
+                     cudaStream_t stream);
+
 /* SMs that the persistent tcgen05 kernels leave free from now on (0 = none): the exchange kernel runs there beside
  * the backward pass.  Read at launch / graph-capture time; returns the previous value. */
 int vb_set_sm_reserve(int n);

@@ -37,6 +37,8 @@ def run(model, B, steps, dp, rank, world, device, layers_kwargs=None, use_graph=
                         print("rank %d: %s of %s differs from rank 0 before sync_master" % (
                             rank, "bias" if t.dtype == torch.float32 else "shadow", f.name), flush=True)
         dp.sync_master()
+        if not counters_ok(dp, rank, world):
+            bias_same = False
         if dp.mode == "fused" and dp.weight_delivery == "peer_tma":
             for f in tr.wf.forwards:   # non-owned shadow rows are stale by design: rebuild them for the comparison
                 if getattr(f, "peer_weights_", None) is not None:
@@ -58,6 +60,26 @@ def run(model, B, steps, dp, rank, world, device, layers_kwargs=None, use_graph=
     if not bias_same:
         out.append("MISMATCH")
     return out
+
+
+def counters_ok(dp, rank, world):
+    """The class-end reductions of the group (device-side exchange in fused mode, the process group otherwise):
+    counters + loss, max / min, a confusion matrix - several rounds, so both slot parities are reused."""
+    ok = True
+    ranks = np.arange(1, world + 1)
+    for it in range(5):
+        vals, loss = dp.sum_counters([3 * (rank + 1) + it, 100 + rank], 0.125 * (rank + 1))
+        ok &= list(vals) == [int(3 * ranks.sum() + it * world), int(100 * world + ranks.sum() - world)]
+        ok &= abs(loss - 0.125 * ranks.sum()) < 1e-12
+        mx, mn = dp.max_min(float(rank) + it, -2.0 * rank)
+        ok &= (mx, mn) == (float(world - 1 + it), -2.0 * (world - 1))
+        cm = dp.sum_array((np.arange(100, dtype=np.int32).reshape(10, 10) + it) * (rank + 1))
+        ok &= cm.dtype == np.int32 and np.array_equal(cm, (np.arange(100).reshape(10, 10) + it) * ranks.sum())
+        top = dp.sum_array(np.array([0.5 * rank], dtype=np.float32), op="max")
+        ok &= float(top[0]) == 0.5 * (world - 1)
+    if not ok:
+        print("rank %d: class-end reductions differ from the expected sums (mode %s)" % (rank, dp.mode), flush=True)
+    return bool(ok)
 
 
 model = "cifar_convnet"

@@ -141,3 +141,106 @@ def test_fused_allreduce_gd_emulated_ranks(world, sharded, push):
         # fresh gradients for the next step in the buffer that was just cleared / left alone
         for rk in ranks:
             rk["grads"][0 if push else 1 - parity].normal_()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_counter_allreduce_emulated_ranks(world):
+    """The class-end counter exchange (``csrc/comm_counters.cu``) with all ranks on one GPU: sums, maxima, the n = 0
+    barrier form and slot reuse over several consecutive epochs against numpy."""
+    import torch
+    from veles_b200.ops import _lib
+    L = _lib.lib()
+    L.vb_counter_region_bytes.restype = ctypes.c_longlong
+    L.vb_counter_params_bytes.restype = ctypes.c_longlong
+    dev = torch.device("cuda:0")
+    slot = 512
+    region = int(L.vb_counter_region_bytes(c_longlong(slot)))
+    bases = [torch.zeros(region, dtype=torch.uint8, device=dev) for _ in range(world)]
+    epochs = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(world)]
+    status = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(world)]
+    ins = [torch.zeros(slot, dtype=torch.float64, device=dev) for _ in range(world)]
+    outs = [torch.full((slot,), -1.0, dtype=torch.float64, device=dev) for _ in range(world)]
+    params = torch.zeros(int(L.vb_counter_params_bytes()) * world + 256, dtype=torch.uint8, device=dev)
+
+    def arr(ts):
+        return (c_void_p * world)(*[c_void_p(t.data_ptr()) for t in ts])
+
+    rng = np.random.default_rng(world)
+    for step, (n, op) in enumerate([(3, 0), (slot, 0), (0, 0), (100, 1), (7, 0)]):
+        vals = rng.integers(-1000, 1000, size=(world, max(n, 1))).astype(np.float64) + 0.25
+        for r in range(world):
+            ins[r][:max(n, 1)] = torch.from_numpy(vals[r]).to(dev)
+        rc = L.vb_counter_allreduce_emulated(c_int(world), c_int(n), c_int(op), c_longlong(slot), arr(ins), arr(outs),
+                                             arr(bases), arr(epochs), arr(status), c_double(5.0),
+                                             c_void_p(params.data_ptr()),
+                                             c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.check(rc, "vb_counter_allreduce_emulated")
+        torch.cuda.synchronize()
+        ref = vals[:, :n].max(axis=0) if op == 1 else vals[:, :n].sum(axis=0)
+        for r in range(world):
+            assert int(status[r].item()) == 0 and int(epochs[r].item()) == step + 1
+            got = outs[r][:n].cpu().numpy()
+            np.testing.assert_array_equal(got, ref)          # same order of additions on every rank: same bits
+    # more values than the slot holds are refused before any launch
+    rc = L.vb_counter_allreduce_emulated(c_int(world), c_int(slot + 1), c_int(0), c_longlong(slot), arr(ins), arr(outs),
+                                         arr(bases), arr(epochs), arr(status), c_double(5.0),
+                                         c_void_p(params.data_ptr()), c_void_p(0))
+    assert rc != 0
+
+
+def test_counter_allreduce_times_out_when_a_rank_is_missing():
+    """A rank whose peers never arrive sets ``status`` and leaves its epoch untouched (the host raises)."""
+    import torch
+    from veles_b200.ops import _lib
+    L = _lib.lib()
+    L.vb_counter_region_bytes.restype = ctypes.c_longlong
+    dev = torch.device("cuda:0")
+    slot = 64
+    bases = [torch.zeros(int(L.vb_counter_region_bytes(c_longlong(slot))), dtype=torch.uint8, device=dev)
+             for _ in range(2)]
+    epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    vin = torch.ones(slot, dtype=torch.float64, device=dev)
+    vout = torch.zeros(slot, dtype=torch.float64, device=dev)
+    peers = (c_void_p * 8)(*([c_void_p(b.data_ptr()) for b in bases] + [c_void_p(0)] * 6))
+    rc = L.vb_counter_allreduce(c_int(2), c_int(0), c_int(4), c_int(0), c_longlong(slot), c_void_p(vin.data_ptr()),
+                                c_void_p(vout.data_ptr()), c_void_p(bases[0].data_ptr()), peers,
+                                c_void_p(epoch.data_ptr()), c_void_p(status.data_ptr()), c_double(0.05),
+                                c_void_p(torch.cuda.current_stream().cuda_stream))
+    _lib.check(rc, "vb_counter_allreduce")
+    torch.cuda.synchronize()
+    assert int(status.item()) == 1001 and int(epoch.item()) == 0
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_gather_slices_reassembles_sharded_state(world):
+    """``vb_gather_slices``: every rank copies each peer's slice of every segment (the slice arithmetic of the update
+    kernel) - odd sizes, unaligned segment offsets, segments shorter than the world."""
+    import torch
+    from veles_b200.ops import _lib
+    L = _lib.lib()
+    dev = torch.device("cuda:0")
+    segs = [(0, 40000), (40064, 203), (40321, 1850), (42200, 3)]
+    slab = 42240
+    truth = torch.randn(slab, device=dev)
+    slabs = []
+    for r in range(world):
+        t = torch.full((slab,), float(-1 - r), device=dev)
+        for off, numel in segs:
+            lo, hi = _slice(numel, world, r)
+            t[off + lo:off + hi] = truth[off + lo:off + hi]       # each rank is current on its own slices only
+        slabs.append(t)
+    seg_arr = (c_longlong * (2 * len(segs)))(*[v for sg in segs for v in sg])
+    peers = (c_void_p * 8)(*([c_void_p(t.data_ptr()) for t in slabs] + [c_void_p(0)] * (8 - world)))
+    before = [t.clone() for t in slabs]
+    for r in range(world):
+        rc = L.vb_gather_slices(c_int(world), c_int(r), c_int(len(segs)), seg_arr, c_void_p(slabs[r].data_ptr()),
+                                peers, c_int(4), c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.check(rc, "vb_gather_slices")
+    torch.cuda.synchronize()
+    for r in range(world):
+        covered = torch.zeros(slab, dtype=torch.bool, device=dev)
+        for off, numel in segs:
+            assert torch.equal(slabs[r][off:off + numel], truth[off:off + numel])
+            covered[off:off + numel] = True
+        assert torch.equal(slabs[r][~covered], before[r][~covered])     # nothing outside the segments is touched

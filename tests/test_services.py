@@ -284,6 +284,24 @@ def test_pdf_backend_writes_a_wellformed_document(tmp_path):
     assert write_text_pdf(str(tmp_path / "one.pdf"), "a (b) \\ c") == 1
 
 
+def test_ipynb_and_latex_backends(tmp_path):
+    """Notebook and LaTeX reports (the reference's jinja2 templates ipynb_template.ipynb / latex_template.tex)."""
+    from veles_b200.publishing.backend import BackendRegistry
+    info = _report_info(tmp_path)
+    info["results"]["odd_key & 100%"] = "a_b{c}"
+    nb = json.load(open(BackendRegistry.backends["ipynb"](directory=str(tmp_path)).render(info)))
+    assert nb["nbformat"] == 4 and nb["cells"][0]["cell_type"] == "markdown"
+    assert any("".join(c["source"]).startswith("## Results") for c in nb["cells"])
+    code = [c for c in nb["cells"] if c["cell_type"] == "code"]
+    scope = {}
+    exec("".join(code[0]["source"]).rsplit("\n", 2)[0], scope)      # the data cell runs and reloads the numbers
+    assert scope["results"]["odd_key & 100%"] == "a_b{c}" and scope["unit_times"][1] == ["fc_tanh1", 0.25]
+    tex = open(BackendRegistry.backends["latex"](directory=str(tmp_path)).render(info)).read()
+    assert tex.startswith("\\documentclass") and tex.rstrip().endswith("\\end{document}")
+    assert "odd\\_key \\& 100\\%" in tex and "a\\_b\\{c\\}" in tex and "fc\\_tanh1 & 0.2500" in tex
+    assert tex.count("\\begin{") == tex.count("\\end{")
+
+
 def test_confluence_backend_against_a_local_xmlrpc_server(tmp_path):
     """The XML-RPC client and the backend against an in-process server speaking the confluence2 API."""
     import threading

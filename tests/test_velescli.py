@@ -86,6 +86,25 @@ def test_genetic_optimization_of_ranges(tmp_path):
     os.remove(best)
 
 
+def test_genetic_example_sample(tmp_path):
+    """``veles_b200/samples/GeneticExample`` (reference: veles/samples/GeneticExample): a one-unit workflow whose
+    fitness the optimizer raises by evolving two configuration values inside their ranges."""
+    sample = os.path.join(ROOT, "veles_b200", "samples", "GeneticExample")
+    manifest = json.load(open(os.path.join(sample, "manifest.json")))
+    res = tmp_path / "gen.json"
+    r = cli("--optimize", "6:3", "--result-file", str(res), os.path.join(sample, manifest["workflow"]), "-", timeout=600)
+    assert r.returncode == 0, r.stdout.decode()[-3000:]
+    data = json.loads(res.read_text())
+    assert data["Generations"] == 3 and set(data["BestGenes"]) == {"root.test.x", "root.test.y"}
+    x, y = data["BestGenes"]["root.test.x"], data["BestGenes"]["root.test.y"]
+    assert -5.0 <= x <= 5.0 and -5.0 <= y <= 5.0
+    assert abs(data["EvaluationFitness"] + ((x * x + y - 11.0) ** 2 + (x + y * y - 7.0) ** 2)) < 1e-6
+    assert data["EvaluationFitness"] > -170.0          # better than the default genes (0, 0)
+    best = os.path.join(sample, "genetics_best_config.py")
+    assert os.path.exists(best)
+    os.remove(best)
+
+
 def test_ensemble_train_then_test(tmp_path):
     res = tmp_path / "ens.json"
     snaps = tmp_path / "snaps"

@@ -12,6 +12,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <utility>
+
 namespace vb {
 
 // ----------------------------------------------------------------------------
@@ -41,12 +43,42 @@ void set_last_error(const char* fmt, ...);
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
 
+// Programmatic dependent launch.  Every kernel starts with pdl_sync(): griddepcontrol.wait returns once the grids this
+// launch depends on have completed and their writes are visible (at once for an ordinary launch), and
+// griddepcontrol.launch_dependents then lets the NEXT kernel of the stream be scheduled while this one runs - its CTAs
+// become resident as SMs drain and run their prologue up to their own wait.  Waiting first keeps at most two
+// consecutive kernels in flight and makes the ordering transitive.  launch_k() launches with the programmatic
+// stream serialisation attribute when vb_set_pdl(1) is in force (captured into CUDA graphs as programmatic edges).
+extern int g_pdl_enabled;
+template <typename... ExpTypes, typename... ActTypes>
+inline cudaError_t launch_k(void (*kernel)(ExpTypes...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                            ActTypes&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_pdl_enabled ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<ActTypes>(args)...);
+}
+
 int device_sm_count();
 int gemm_sm_count();   // device_sm_count() minus the SMs reserved for a pending exchange kernel (vb_set_sm_reserve)
 
 // ----------------------------------------------------------------------------
 // Device-side primitives
 // ----------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() {
+  pdl_wait();
+  pdl_launch_dependents();
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

@@ -134,6 +134,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_sync();   // the set-up above overlaps the previous kernel's tail; global memory is touched from here on
 
   const int taps = p.kx * p.ky;
   const int num_tiles = p.B * p.tiles_per_img * p.n_blocks;
@@ -545,7 +546,7 @@ static int launch_halo(const CUtensorMap& tx, const CUtensorMap& tw, const CUten
   const long long tiles = static_cast<long long>(p.B) * p.tiles_per_img * p.n_blocks;
   const int sms = gemm_sm_count();
   const int grid = static_cast<int>(tiles < sms ? tiles : sms);
-  kern<<<grid, HALO_THREADS, S::TOTAL, s>>>(tx, tw, td, p);
+  VB_CHECK_CUDA(launch_k(kern, dim3(grid), dim3(HALO_THREADS), S::TOTAL, s, tx, tw, td, p));
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

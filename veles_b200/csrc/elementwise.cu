@@ -39,6 +39,7 @@ __global__ void __launch_bounds__(256)
 gather_rows_kernel(const SRC* __restrict__ src, long long src_ld, const int* __restrict__ indices, int start, int count,
                    int max_rows, int row_size, DST* __restrict__ dst, long long dst_ld,
                    const float* __restrict__ mean, const float* __restrict__ rdisp) {
+  vb::pdl_sync();
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (c >= row_size) return;
   const int nc = min(4, row_size - c);
@@ -72,6 +73,7 @@ gather_rows_kernel(const SRC* __restrict__ src, long long src_ld, const int* __r
 __global__ void gather_labels_kernel(const int* __restrict__ labels, const int* __restrict__ indices,
                                      int start, int count, int max_rows, int* __restrict__ mb_labels,
                                      int* __restrict__ mb_indices) {
+  vb::pdl_sync();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= max_rows) return;
   if (i < count) {
@@ -91,10 +93,10 @@ static int launch_gather(int dst_dtype, const void* src, long long src_ld, const
   dim3 block(256);
   dim3 grid(ceil_div(row_size, 256 * 4), ceil_div(max_rows, GATHER_ROWS_PER_BLOCK));
   if (dst_dtype == DT_F32)
-    gather_rows_kernel<SRC, float><<<grid, block, 0, s>>>(static_cast<const SRC*>(src), src_ld, indices, start, count,
+    vb::launch_k(gather_rows_kernel<SRC, float>, dim3(grid), dim3(block), 0, s, static_cast<const SRC*>(src), src_ld, indices, start, count,
                                                           max_rows, row_size, static_cast<float*>(dst), dst_ld, mean, rdisp);
   else
-    gather_rows_kernel<SRC, __nv_bfloat16><<<grid, block, 0, s>>>(static_cast<const SRC*>(src), src_ld, indices, start,
+    vb::launch_k(gather_rows_kernel<SRC, __nv_bfloat16>, dim3(grid), dim3(block), 0, s, static_cast<const SRC*>(src), src_ld, indices, start,
                                                                   count, max_rows, row_size,
                                                                   static_cast<__nv_bfloat16*>(dst), dst_ld, mean, rdisp);
   VB_CHECK_CUDA(cudaGetLastError());
@@ -107,6 +109,7 @@ static int launch_gather(int dst_dtype, const void* src, long long src_ld, const
 template <typename SRC, typename DST>
 __global__ void copy2d_kernel(const SRC* __restrict__ src, long long src_ld, DST* __restrict__ dst,
                               long long dst_ld, int rows, int cols) {
+  vb::pdl_sync();
   const long long total = static_cast<long long>(rows) * cols;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -160,6 +163,7 @@ __device__ __forceinline__ float act_backward_full(int act, float x, float y, fl
 
 template <typename T>
 __global__ void act_forward_kernel(int act, const T* __restrict__ x, T* __restrict__ y, long long n, float factor) {
+  vb::pdl_sync();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
     y[i] = from_f<T>(act_forward_full(act, to_f<T>(x[i]), factor, static_cast<int>(i & 1)));
@@ -167,6 +171,7 @@ __global__ void act_forward_kernel(int act, const T* __restrict__ x, T* __restri
 template <typename T>
 __global__ void act_backward_kernel(int act, const T* __restrict__ err_out, const T* __restrict__ x,
                                     const T* __restrict__ y, T* __restrict__ err_in, long long n, float factor) {
+  vb::pdl_sync();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const float xv = x ? to_f<T>(x[i]) : 0.0f;
@@ -194,6 +199,7 @@ template <typename T>
 __global__ void dropout_kernel(const T* __restrict__ in, T* __restrict__ out, long long n,
                                const ulonglong2* __restrict__ states_in, ulonglong2* __restrict__ states_out,
                                int n_states, uint32_t threshold, float scale) {
+  vb::pdl_sync();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_states) return;
   ulonglong2 st = states_in[t];
@@ -266,6 +272,7 @@ __device__ __forceinline__ float gd_step(const GDParams& p, float w, float g, fl
 __global__ void gd_update_kernel(float* __restrict__ w, float* __restrict__ grad, float* __restrict__ vel,
                                  float* __restrict__ acc, __nv_bfloat16* __restrict__ w_bf16, long long n,
                                  const GDParams p) {
+  vb::pdl_sync();
   const long long n4 = n >> 2;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -304,11 +311,13 @@ __global__ void gd_update_kernel(float* __restrict__ w, float* __restrict__ grad
 
 // fp32 -> bf16 (weight shadow initialisation) and bf16 -> fp32
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n) {
+  vb::pdl_sync();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
     out[i] = __float2bfloat16(in[i]);
 }
 __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ in, float* __restrict__ out, long long n) {
+  vb::pdl_sync();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
     out[i] = __bfloat162float(in[i]);
@@ -342,7 +351,7 @@ extern "C" int vb_gather_minibatch(const void* src, int src_dtype, long long src
   }
   if (rc) return rc;
   if (mb_labels || mb_indices) {
-    gather_labels_kernel<<<ceil_div(max_rows, 256), 256, 0, s>>>(labels, indices, start, count, max_rows, mb_labels, mb_indices);
+    vb::launch_k(gather_labels_kernel, dim3(ceil_div(max_rows, 256)), dim3(256), 0, s, labels, indices, start, count, max_rows, mb_labels, mb_indices);
     VB_CHECK_CUDA(cudaGetLastError());
   }
   return 0;
@@ -352,6 +361,7 @@ namespace vb {
 template <typename SRC, typename DST>
 __global__ void mean_disp_kernel(const SRC* __restrict__ in, const float* __restrict__ mean,
                                  const float* __restrict__ rdisp, DST* __restrict__ out, int batch, int size) {
+  vb::pdl_sync();
   const long long total = static_cast<long long>(batch) * size;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -367,7 +377,7 @@ extern "C" int vb_mean_disp_normalize(const void* in, int in_dtype, const float*
   const long long total = static_cast<long long>(batch) * size;
   if (total == 0) return 0;
   const int g = grid_for(total, 256, 4);
-#define VB_MD(SRC, DST) mean_disp_kernel<SRC, DST><<<g, 256, 0, s>>>(static_cast<const SRC*>(in), mean, rdisp, static_cast<DST*>(out), batch, size)
+#define VB_MD(SRC, DST) vb::launch_k(mean_disp_kernel<SRC, DST>, dim3(g), dim3(256), 0, s, static_cast<const SRC*>(in), mean, rdisp, static_cast<DST*>(out), batch, size)
   if (in_dtype == DT_U8 && out_dtype == DT_F32) VB_MD(uint8_t, float);
   else if (in_dtype == DT_U8 && out_dtype == DT_BF16) VB_MD(uint8_t, __nv_bfloat16);
   else if (in_dtype == DT_F32 && out_dtype == DT_F32) VB_MD(float, float);
@@ -385,7 +395,7 @@ extern "C" int vb_copy_2d(const void* src, int src_dtype, long long src_ld, void
   const long long total = static_cast<long long>(rows) * cols;
   if (total == 0) return 0;
   const int g = grid_for(total, 256, 4);
-#define VB_CP(SRC, DST) copy2d_kernel<SRC, DST><<<g, 256, 0, s>>>(static_cast<const SRC*>(src), src_ld, static_cast<DST*>(dst), dst_ld, rows, cols)
+#define VB_CP(SRC, DST) vb::launch_k(copy2d_kernel<SRC, DST>, dim3(g), dim3(256), 0, s, static_cast<const SRC*>(src), src_ld, static_cast<DST*>(dst), dst_ld, rows, cols)
   if (src_dtype == DT_F32 && dst_dtype == DT_F32) VB_CP(float, float);
   else if (src_dtype == DT_F32 && dst_dtype == DT_BF16) VB_CP(float, __nv_bfloat16);
   else if (src_dtype == DT_BF16 && dst_dtype == DT_BF16) VB_CP(__nv_bfloat16, __nv_bfloat16);
@@ -402,8 +412,8 @@ extern "C" int vb_activation_forward(int act, const void* x, void* y, long long 
                                      cudaStream_t s) {
   if (n == 0) return 0;
   const int g = grid_for(n, 256, 4);
-  if (dtype == DT_F32) act_forward_kernel<float><<<g, 256, 0, s>>>(act, static_cast<const float*>(x), static_cast<float*>(y), n, factor);
-  else if (dtype == DT_BF16) act_forward_kernel<__nv_bfloat16><<<g, 256, 0, s>>>(act, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), n, factor);
+  if (dtype == DT_F32) vb::launch_k(act_forward_kernel<float>, dim3(g), dim3(256), 0, s, act, static_cast<const float*>(x), static_cast<float*>(y), n, factor);
+  else if (dtype == DT_BF16) vb::launch_k(act_forward_kernel<__nv_bfloat16>, dim3(g), dim3(256), 0, s, act, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), n, factor);
   else VB_REQUIRE(false, "vb_activation_forward: dtype must be f32/bf16");
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -414,10 +424,10 @@ extern "C" int vb_activation_backward(int act, const void* err_out, const void* 
   if (n == 0) return 0;
   const int g = grid_for(n, 256, 4);
   if (dtype == DT_F32)
-    act_backward_kernel<float><<<g, 256, 0, s>>>(act, static_cast<const float*>(err_out), static_cast<const float*>(x),
+    vb::launch_k(act_backward_kernel<float>, dim3(g), dim3(256), 0, s, act, static_cast<const float*>(err_out), static_cast<const float*>(x),
                                                  static_cast<const float*>(y), static_cast<float*>(err_in), n, factor);
   else if (dtype == DT_BF16)
-    act_backward_kernel<__nv_bfloat16><<<g, 256, 0, s>>>(act, static_cast<const __nv_bfloat16*>(err_out),
+    vb::launch_k(act_backward_kernel<__nv_bfloat16>, dim3(g), dim3(256), 0, s, act, static_cast<const __nv_bfloat16*>(err_out),
                                                          static_cast<const __nv_bfloat16*>(x),
                                                          static_cast<const __nv_bfloat16*>(y),
                                                          static_cast<__nv_bfloat16*>(err_in), n, factor);
@@ -436,11 +446,11 @@ extern "C" int vb_dropout(const void* in, void* out, long long n, int dtype, con
   const float scale = 1.0f / (1.0f - ratio);
   const int g = ceil_div(n_states, 128);
   if (dtype == DT_F32)
-    dropout_kernel<float><<<g, 128, 0, s>>>(static_cast<const float*>(in), static_cast<float*>(out), n,
+    vb::launch_k(dropout_kernel<float>, dim3(g), dim3(128), 0, s, static_cast<const float*>(in), static_cast<float*>(out), n,
                                             static_cast<const ulonglong2*>(states_in), static_cast<ulonglong2*>(states_out),
                                             n_states, threshold, scale);
   else if (dtype == DT_BF16)
-    dropout_kernel<__nv_bfloat16><<<g, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(in), static_cast<__nv_bfloat16*>(out), n,
+    vb::launch_k(dropout_kernel<__nv_bfloat16>, dim3(g), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(in), static_cast<__nv_bfloat16*>(out), n,
                                                     static_cast<const ulonglong2*>(states_in),
                                                     static_cast<ulonglong2*>(states_out), n_states, threshold, scale);
   else VB_REQUIRE(false, "vb_dropout: dtype must be f32/bf16");
@@ -456,7 +466,7 @@ extern "C" int vb_gd_update(float* w, float* grad, float* vel, float* acc, void*
              "vb_gd_update: weights/grad must be 16-byte aligned");
   GDParams p{lr, wd, l1_vs_l2, moment, grad_scale, eps, rho, solver, zero_grad};
   const int g = grid_for(n, 256, 4);
-  gd_update_kernel<<<g, 256, 0, s>>>(w, grad, vel, acc, static_cast<__nv_bfloat16*>(w_bf16), n, p);
+  vb::launch_k(gd_update_kernel, dim3(g), dim3(256), 0, s, w, grad, vel, acc, static_cast<__nv_bfloat16*>(w_bf16), n, p);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -469,6 +479,7 @@ template <typename DST>
 __global__ void bias_act_kernel(float* __restrict__ acc, long long ld_acc, const float* __restrict__ bias, int act,
                                 const __nv_bfloat16* __restrict__ z, long long ldz, int deriv, DST* __restrict__ out,
                                 long long ld_out, int M, int N, int zero_acc) {
+  vb::pdl_sync();
   const int n4 = N >> 2;   // N % 4 == 0 (checked by the launcher)
   const long long total = static_cast<long long>(M) * n4;
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
@@ -503,10 +514,10 @@ extern "C" int vb_bias_act_2d(float* acc, long long ld_acc, const float* bias, i
              "vb_bias_act_2d: N and the accumulator pitch must be multiples of 4, pointers 16-byte aligned");
   const int g = grid_for(static_cast<long long>(M) * (N >> 2), 256, 2);
   if (out_dtype == DT_F32)
-    bias_act_kernel<float><<<g, 256, 0, s>>>(acc, ld_acc, bias, act, static_cast<const __nv_bfloat16*>(z), ldz, deriv,
+    vb::launch_k(bias_act_kernel<float>, dim3(g), dim3(256), 0, s, acc, ld_acc, bias, act, static_cast<const __nv_bfloat16*>(z), ldz, deriv,
                                              static_cast<float*>(out), ld_out, M, N, zero_acc);
   else if (out_dtype == DT_BF16)
-    bias_act_kernel<__nv_bfloat16><<<g, 256, 0, s>>>(acc, ld_acc, bias, act, static_cast<const __nv_bfloat16*>(z), ldz,
+    vb::launch_k(bias_act_kernel<__nv_bfloat16>, dim3(g), dim3(256), 0, s, acc, ld_acc, bias, act, static_cast<const __nv_bfloat16*>(z), ldz,
                                                      deriv, static_cast<__nv_bfloat16*>(out), ld_out, M, N, zero_acc);
   else
     VB_REQUIRE(false, "vb_bias_act_2d: output dtype must be f32/bf16");
@@ -518,9 +529,9 @@ extern "C" int vb_cast(const void* in, int in_dtype, void* out, int out_dtype, l
   if (n == 0) return 0;
   const int g = grid_for(n, 256, 4);
   if (in_dtype == DT_F32 && out_dtype == DT_BF16)
-    cast_f32_bf16_kernel<<<g, 256, 0, s>>>(static_cast<const float*>(in), static_cast<__nv_bfloat16*>(out), n);
+    vb::launch_k(cast_f32_bf16_kernel, dim3(g), dim3(256), 0, s, static_cast<const float*>(in), static_cast<__nv_bfloat16*>(out), n);
   else if (in_dtype == DT_BF16 && out_dtype == DT_F32)
-    cast_bf16_f32_kernel<<<g, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(in), static_cast<float*>(out), n);
+    vb::launch_k(cast_bf16_f32_kernel, dim3(g), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(in), static_cast<float*>(out), n);
   else VB_REQUIRE(false, "vb_cast: unsupported dtype pair %d -> %d", in_dtype, out_dtype);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -532,6 +543,7 @@ namespace vb {
 __global__ void ortho_grad_kernel(const float* __restrict__ w, float* __restrict__ grad, const float* __restrict__ sums,
                                   long long rows, long long cols, long long ldw, long long ldg, float f,
                                   int by_row) {
+  vb::pdl_sync();
   const long long n = rows * cols;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -548,7 +560,7 @@ extern "C" int vb_ortho_grad(const float* w, long long ldw, float* grad, long lo
   const long long cap = static_cast<long long>(vb::device_sm_count()) * 16;
   long long blocks = (n + 255) / 256;
   if (blocks > cap) blocks = cap;
-  vb::ortho_grad_kernel<<<static_cast<int>(blocks), 256, 0, s>>>(w, grad, sums, rows, cols, ldw, ldg, f, by_row);
+  vb::launch_k(vb::ortho_grad_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, s, w, grad, sums, rows, cols, ldw, ldg, f, by_row);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

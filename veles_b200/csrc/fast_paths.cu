@@ -38,6 +38,7 @@ static inline int grid_cap2(long long n, int block) {
 // ---------------------------------------------------------------------------------------------
 __global__ void im2col_any8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols,
                                    const FastConvGeom g) {
+  vb::pdl_sync();
   const int Cg = g.C / g.groups;
   const int kk = g.ky * g.kx;
   const int vec_per_row = static_cast<int>(g.ld >> 3);
@@ -100,6 +101,7 @@ __global__ void im2col_any8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
 __global__ void __launch_bounds__(256)
 im2col_rowtile_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, const FastConvGeom g,
                       int rw) {
+  vb::pdl_sync();
   extern __shared__ unsigned short srows[];  // [ky][rw], rw = ((OW-1)*sx + kx) * C
   const int b = blockIdx.x / g.OH;
   const int oh = blockIdx.x - b * g.OH;
@@ -147,6 +149,7 @@ im2col_rowtile_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __rest
 // ---------------------------------------------------------------------------------------------
 __global__ void col2im_vec8_kernel(const __nv_bfloat16* __restrict__ dcols, __nv_bfloat16* __restrict__ dx,
                                    const FastConvGeom g, const __nv_bfloat16* __restrict__ z, int deriv) {
+  vb::pdl_sync();
   const int Cg = g.C / g.groups;
   const int kk = g.ky * g.kx;
   const int C8 = g.C >> 3;
@@ -198,6 +201,7 @@ __global__ void col2im_vec8_kernel(const __nv_bfloat16* __restrict__ dcols, __nv
 __global__ void __launch_bounds__(128, 8)   // <= 64 registers: latency-bound gather, occupancy matters
 pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                          int* __restrict__ offs, uint8_t* __restrict__ offs8, const FastPoolGeom g) {
+  vb::pdl_sync();
   const unsigned C8 = g.C >> 3;
   const long long total = static_cast<long long>(g.B) * g.OH * g.OW * C8;   // < 2^31 (checked by the launcher)
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
@@ -263,6 +267,7 @@ pool_forward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ x, __nv_bfl
 // int32 global offsets (the Znicz-visible ``input_offset``) from the 1-byte window-local argmax.
 __global__ void pool_expand_offsets_kernel(const uint8_t* __restrict__ offs8, int* __restrict__ offs,
                                            const FastPoolGeom g) {
+  vb::pdl_sync();
   const long long total = static_cast<long long>(g.B) * g.OH * g.OW * g.C;
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
        t += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -282,6 +287,7 @@ __global__ void pool_expand_offsets_kernel(const uint8_t* __restrict__ offs8, in
 __global__ void pool_backward_vec8_kernel(int kind, const __nv_bfloat16* __restrict__ dy, const int* __restrict__ offs,
                                           const uint8_t* __restrict__ offs8, __nv_bfloat16* __restrict__ dx,
                                           const FastPoolGeom g, const __nv_bfloat16* __restrict__ z, int deriv) {
+  vb::pdl_sync();
   const unsigned C8 = g.C >> 3;
   const long long total = static_cast<long long>(g.B) * g.H * g.W * C8;   // < 2^31 (checked by the launcher)
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
@@ -357,6 +363,7 @@ template <int KIND>
 __global__ void __launch_bounds__(128)
 pool_fwd_3x3s2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ offs8,
                       const FastPoolGeom g) {
+  vb::pdl_sync();
   const unsigned C8 = g.C >> 3;
   const unsigned total = static_cast<unsigned>(g.B) * g.OH * g.OW * C8;
   const unsigned NEG_INF2 = 0xff80ff80u;     // (-inf, -inf): never wins, stands for taps outside the image
@@ -414,6 +421,7 @@ __global__ void __launch_bounds__(128)
 pool_bwd_3x3s2_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ offs8,
                       __nv_bfloat16* __restrict__ dx, const FastPoolGeom g, const __nv_bfloat16* __restrict__ z,
                       int deriv) {
+  vb::pdl_sync();
   const unsigned C8 = g.C >> 3;
   const int BH = (g.H + 1) >> 1, BW = (g.W + 1) >> 1;
   const unsigned total = static_cast<unsigned>(g.B) * BH * BW * C8;
@@ -489,6 +497,7 @@ pool_bwd_3x3s2_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __res
 // ---------------------------------------------------------------------------------------------
 __global__ void lrn_forward_row_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                        long long pixels, int C, int n, float alpha, float beta, float k) {
+  vb::pdl_sync();
   extern __shared__ float sm[];
   const int warps = blockDim.x >> 5;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -513,6 +522,7 @@ __global__ void lrn_forward_row_kernel(const __nv_bfloat16* __restrict__ x, __nv
 __global__ void lrn_backward_row_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                         __nv_bfloat16* __restrict__ dx, long long pixels, int C, int n, float alpha,
                                         float beta, float k, int deriv) {
+  vb::pdl_sync();
   extern __shared__ float sm[];
   const int warps = blockDim.x >> 5;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -605,6 +615,7 @@ template <int HALF>
 __global__ void __launch_bounds__(256)
 lrn_forward_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels, int C,
                         float alpha, float beta, float k) {
+  vb::pdl_sync();
   const int T = C >> 3;
   const long long total = pixels * T;
   const bool beta34 = (beta == 0.75f);
@@ -636,6 +647,7 @@ __global__ void __launch_bounds__(256)
 lrn_backward_vec8_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                          __nv_bfloat16* __restrict__ dx, long long pixels, int C, float alpha, float beta, float k,
                          int deriv) {
+  vb::pdl_sync();
   const int T = C >> 3;
   const long long total = pixels * T;
   const float coef = 2.0f * alpha * beta;
@@ -719,6 +731,7 @@ template <int HALF, bool B34>
 __global__ void __launch_bounds__(256)
 lrn_forward_shfl_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels, int C,
                         float alpha, float beta, float k) {
+  vb::pdl_sync();
   const int T = C >> 3;
   const int ppw = 32 / T;                       // pixels per warp
   const int lane = threadIdx.x & 31;
@@ -753,6 +766,7 @@ __global__ void __launch_bounds__(256)
 lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                          __nv_bfloat16* __restrict__ dx, long long pixels, int C, float alpha, float beta, float k,
                          int deriv) {
+  vb::pdl_sync();
   const int T = C >> 3;
   const int ppw = 32 / T;
   const int lane = threadIdx.x & 31;
@@ -817,6 +831,7 @@ __global__ void __launch_bounds__(256)
 lrn_pool_backward_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dpool,
                          const uint8_t* __restrict__ offs8, __nv_bfloat16* __restrict__ dx, const FastPoolGeom g,
                          float alpha, float beta, float k, int deriv) {
+  vb::pdl_sync();
   const int C = g.C;
   const int T = C >> 3;
   const int ppw = 32 / T;
@@ -919,8 +934,8 @@ int fast_lrn_pool_backward(const void* x, const void* dpool, const uint8_t* offs
   const __nv_bfloat16* dp = static_cast<const __nv_bfloat16*>(dpool);
   __nv_bfloat16* op = static_cast<__nv_bfloat16*>(dx);
 #define VB_LRN_PB(H_)                                                                                                   \
-  if (beta == 0.75f) lrn_pool_backward_kernel<H_, true><<<g2, 256, 0, s>>>(xp, dp, offs8, op, g, alpha, beta, k, deriv);   \
-  else lrn_pool_backward_kernel<H_, false><<<g2, 256, 0, s>>>(xp, dp, offs8, op, g, alpha, beta, k, deriv)
+  if (beta == 0.75f) vb::launch_k(lrn_pool_backward_kernel<H_, true>, dim3(g2), dim3(256), 0, s, xp, dp, offs8, op, g, alpha, beta, k, deriv);   \
+  else vb::launch_k(lrn_pool_backward_kernel<H_, false>, dim3(g2), dim3(256), 0, s, xp, dp, offs8, op, g, alpha, beta, k, deriv)
   switch (half) {
     case 1: VB_LRN_PB(1); break;
     case 2: VB_LRN_PB(2); break;
@@ -949,13 +964,13 @@ int fast_im2col(const void* x, void* cols, const FastConvGeom& g, cudaStream_t s
         VB_CHECK_CUDA(cudaFuncSetAttribute(im2col_rowtile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
         attr_set = true;
       }
-      im2col_rowtile_kernel<<<g.B * g.OH, 256, smem, s>>>(static_cast<const __nv_bfloat16*>(x),
+      vb::launch_k(im2col_rowtile_kernel, dim3(g.B * g.OH), dim3(256), smem, s, static_cast<const __nv_bfloat16*>(x),
                                                           static_cast<__nv_bfloat16*>(cols), g, rw);
       VB_CHECK_CUDA(cudaGetLastError());
       return 1;
     }
   }
-  im2col_any8_kernel<<<grid_cap2(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x),
+  vb::launch_k(im2col_any8_kernel, dim3(grid_cap2(total, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x),
                                                            static_cast<__nv_bfloat16*>(cols), g);
   VB_CHECK_CUDA(cudaGetLastError());
   return 1;
@@ -968,7 +983,7 @@ int fast_col2im(const void* dcols, void* dx, const FastConvGeom& g, const void* 
     return 0;
   const long long total = static_cast<long long>(g.B) * g.H * g.W * (g.C >> 3);
   if (total == 0) return 1;
-  col2im_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(static_cast<const __nv_bfloat16*>(dcols),
+  vb::launch_k(col2im_vec8_kernel, dim3(grid_cap2(total, 128)), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(dcols),
                                                            static_cast<__nv_bfloat16*>(dx), g,
                                                            static_cast<const __nv_bfloat16*>(z), deriv);
   VB_CHECK_CUDA(cudaGetLastError());
@@ -986,15 +1001,15 @@ int fast_pool_forward(int kind, const void* x, void* y, int* offs, uint8_t* offs
   if (total == 0) return 1;
   if (offs == nullptr && offs8 != nullptr && kind != 2 && g.kx == 3 && g.ky == 3 && g.sx == 2 && g.sy == 2) {
     if (kind == 1)
-      pool_fwd_3x3s2_kernel<1><<<grid_cap2(total, 128), 128, 0, s>>>(static_cast<const __nv_bfloat16*>(x),
+      vb::launch_k(pool_fwd_3x3s2_kernel<1>, dim3(grid_cap2(total, 128)), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(x),
                                                                     static_cast<__nv_bfloat16*>(y), offs8, g);
     else
-      pool_fwd_3x3s2_kernel<0><<<grid_cap2(total, 128), 128, 0, s>>>(static_cast<const __nv_bfloat16*>(x),
+      vb::launch_k(pool_fwd_3x3s2_kernel<0>, dim3(grid_cap2(total, 128)), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(x),
                                                                     static_cast<__nv_bfloat16*>(y), offs8, g);
     VB_CHECK_CUDA(cudaGetLastError());
     return 1;
   }
-  pool_forward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(x),
+  vb::launch_k(pool_forward_vec8_kernel, dim3(grid_cap2(total, 128)), dim3(128), 0, s, kind, static_cast<const __nv_bfloat16*>(x),
                                                                  static_cast<__nv_bfloat16*>(y), offs, offs8, g);
   VB_CHECK_CUDA(cudaGetLastError());
   return 1;
@@ -1011,13 +1026,13 @@ int fast_pool_backward(int kind, const void* dy, const int* offs, const uint8_t*
   if (total == 0) return 1;
   if (offs8 != nullptr && kind != 2 && g.kx == 3 && g.ky == 3 && g.sx == 2 && g.sy == 2) {
     const long long blocks4 = static_cast<long long>(g.B) * ((g.H + 1) / 2) * ((g.W + 1) / 2) * (g.C >> 3);
-    pool_bwd_3x3s2_kernel<<<grid_cap2(blocks4, 128), 128, 0, s>>>(static_cast<const __nv_bfloat16*>(dy), offs8,
+    vb::launch_k(pool_bwd_3x3s2_kernel, dim3(grid_cap2(blocks4, 128)), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(dy), offs8,
                                                                  static_cast<__nv_bfloat16*>(dx), g,
                                                                  static_cast<const __nv_bfloat16*>(z), deriv);
     VB_CHECK_CUDA(cudaGetLastError());
     return 1;
   }
-  pool_backward_vec8_kernel<<<grid_cap2(total, 128), 128, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(dy), offs, offs8,
+  vb::launch_k(pool_backward_vec8_kernel, dim3(grid_cap2(total, 128)), dim3(128), 0, s, kind, static_cast<const __nv_bfloat16*>(dy), offs, offs8,
                                                                   static_cast<__nv_bfloat16*>(dx), g,
                                                                   static_cast<const __nv_bfloat16*>(z), deriv);
   VB_CHECK_CUDA(cudaGetLastError());
@@ -1028,7 +1043,7 @@ int fast_pool_expand_offsets(const uint8_t* offs8, int* offs, const FastPoolGeom
   const long long total = static_cast<long long>(g.B) * g.OH * g.OW * g.C;
   if (total == 0) return 1;
   if (static_cast<long long>(g.B) * g.H * g.W * g.C >= 2147483647LL) return 0;
-  pool_expand_offsets_kernel<<<grid_cap2(total, 256), 256, 0, s>>>(offs8, offs, g);
+  vb::launch_k(pool_expand_offsets_kernel, dim3(grid_cap2(total, 256)), dim3(256), 0, s, offs8, offs, g);
   VB_CHECK_CUDA(cudaGetLastError());
   return 1;
 }
@@ -1047,8 +1062,8 @@ int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, flo
       const int ppw = 32 / (C >> 3);
       const int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
 #define VB_LRN_F(H_)                                                                                              \
-  if (beta == 0.75f) lrn_forward_shfl_kernel<H_, true><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k);        \
-  else lrn_forward_shfl_kernel<H_, false><<<g2, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k)
+  if (beta == 0.75f) vb::launch_k(lrn_forward_shfl_kernel<H_, true>, dim3(g2), dim3(256), 0, s, xp, yp, pixels, C, alpha, beta, k);        \
+  else vb::launch_k(lrn_forward_shfl_kernel<H_, false>, dim3(g2), dim3(256), 0, s, xp, yp, pixels, C, alpha, beta, k)
       switch (half) {
         case 1: VB_LRN_F(1); break;
         case 2: VB_LRN_F(2); break;
@@ -1060,10 +1075,10 @@ int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, flo
       return 1;
     }
     switch (half) {
-      case 1: lrn_forward_vec8_kernel<1><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
-      case 2: lrn_forward_vec8_kernel<2><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
-      case 3: lrn_forward_vec8_kernel<3><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
-      default: lrn_forward_vec8_kernel<4><<<grid, 256, 0, s>>>(xp, yp, pixels, C, alpha, beta, k); break;
+      case 1: vb::launch_k(lrn_forward_vec8_kernel<1>, dim3(grid), dim3(256), 0, s, xp, yp, pixels, C, alpha, beta, k); break;
+      case 2: vb::launch_k(lrn_forward_vec8_kernel<2>, dim3(grid), dim3(256), 0, s, xp, yp, pixels, C, alpha, beta, k); break;
+      case 3: vb::launch_k(lrn_forward_vec8_kernel<3>, dim3(grid), dim3(256), 0, s, xp, yp, pixels, C, alpha, beta, k); break;
+      default: vb::launch_k(lrn_forward_vec8_kernel<4>, dim3(grid), dim3(256), 0, s, xp, yp, pixels, C, alpha, beta, k); break;
     }
     VB_CHECK_CUDA(cudaGetLastError());
     return 1;
@@ -1074,8 +1089,7 @@ int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, flo
   long long blocks = (pixels + warps - 1) / warps;
   const long long cap = static_cast<long long>(device_sm_count()) * 8;
   if (blocks > cap) blocks = cap;
-  lrn_forward_row_kernel<<<static_cast<int>(blocks), warps * 32, smem, s>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, n, alpha, beta, k);
+  vb::launch_k(lrn_forward_row_kernel, dim3(static_cast<int>(blocks)), dim3(warps * 32), smem, s, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, n, alpha, beta, k);
   VB_CHECK_CUDA(cudaGetLastError());
   return 1;
 }
@@ -1095,8 +1109,8 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
       const int ppw = 32 / (C >> 3);
       const int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
 #define VB_LRN_B(H_)                                                                                                     \
-  if (beta == 0.75f) lrn_backward_shfl_kernel<H_, true><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv);   \
-  else lrn_backward_shfl_kernel<H_, false><<<g2, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv)
+  if (beta == 0.75f) vb::launch_k(lrn_backward_shfl_kernel<H_, true>, dim3(g2), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv);   \
+  else vb::launch_k(lrn_backward_shfl_kernel<H_, false>, dim3(g2), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv)
       switch (half) {
         case 1: VB_LRN_B(1); break;
         case 2: VB_LRN_B(2); break;
@@ -1108,10 +1122,10 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
       return 1;
     }
     switch (half) {
-      case 1: lrn_backward_vec8_kernel<1><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
-      case 2: lrn_backward_vec8_kernel<2><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
-      case 3: lrn_backward_vec8_kernel<3><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
-      default: lrn_backward_vec8_kernel<4><<<grid, 256, 0, s>>>(xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+      case 1: vb::launch_k(lrn_backward_vec8_kernel<1>, dim3(grid), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+      case 2: vb::launch_k(lrn_backward_vec8_kernel<2>, dim3(grid), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+      case 3: vb::launch_k(lrn_backward_vec8_kernel<3>, dim3(grid), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
+      default: vb::launch_k(lrn_backward_vec8_kernel<4>, dim3(grid), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv); break;
     }
     VB_CHECK_CUDA(cudaGetLastError());
     return 1;
@@ -1122,8 +1136,7 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
   long long blocks = (pixels + warps - 1) / warps;
   const long long cap = static_cast<long long>(device_sm_count()) * 12;
   if (blocks > cap) blocks = cap;
-  lrn_backward_row_kernel<<<static_cast<int>(blocks), warps * 32, smem, s>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
+  vb::launch_k(lrn_backward_row_kernel, dim3(static_cast<int>(blocks)), dim3(warps * 32), smem, s, static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx),
       pixels, C, n, alpha, beta, k, deriv);
   VB_CHECK_CUDA(cudaGetLastError());
   return 1;
@@ -1139,6 +1152,7 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
 template <typename T>
 __global__ void space_to_depth_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ xs, int B, int H, int W,
                                       int C, int sy, int sx, int H2, int W2) {
+  vb::pdl_sync();
   const int C2 = sy * sx * C;
   const int V = C2 >> 3;
   const long long total = static_cast<long long>(B) * H2 * W2 * V;
@@ -1180,6 +1194,7 @@ __global__ void space_to_depth_kernel(const T* __restrict__ x, __nv_bfloat16* __
 __global__ void __launch_bounds__(256)
 space_to_depth_rows_kernel(const unsigned short* __restrict__ x, unsigned short* __restrict__ xs, int B, int H, int W,
                            int C, int sy, int sx, int H2, int W2) {
+  vb::pdl_sync();
   const int n = sx * C;                 // segment length (elements), multiple of 4
   const int C2 = sy * n;
   const long long total = static_cast<long long>(B) * H2 * W2 * sy;
@@ -1214,6 +1229,7 @@ space_to_depth_rows_kernel(const unsigned short* __restrict__ x, unsigned short*
 template <typename TS, typename TD>
 __global__ void gather_cols_kernel(const TS* __restrict__ src, long long ld_src, TD* __restrict__ dst,
                                    long long ld_dst, const int* __restrict__ map, int rows, int cols, int accumulate) {
+  vb::pdl_sync();
   const long long total = static_cast<long long>(rows) * cols;
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
        t += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -1240,7 +1256,7 @@ extern "C" int vb_space_to_depth(const void* x, int dtype, void* xs, int B, int 
   if (total == 0) return 0;
   const long long segs = static_cast<long long>(B) * H2 * W2 * sy;
   if (dtype == 1 && (sx * C) % 4 == 0 && segs < 0xffffffffLL) {
-    space_to_depth_rows_kernel<<<grid_cap2(segs, 256), 256, 0, s>>>(static_cast<const unsigned short*>(x),
+    vb::launch_k(space_to_depth_rows_kernel, dim3(grid_cap2(segs, 256)), dim3(256), 0, s, static_cast<const unsigned short*>(x),
                                                                    static_cast<unsigned short*>(xs), B, H, W, C, sy, sx,
                                                                    H2, W2);
     VB_CHECK_CUDA(cudaGetLastError());
@@ -1248,9 +1264,9 @@ extern "C" int vb_space_to_depth(const void* x, int dtype, void* xs, int B, int 
   }
   const int grid = grid_cap2(total, 256);
   if (dtype == 0)
-    space_to_depth_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(x), static_cast<__nv_bfloat16*>(xs), B, H, W, C, sy, sx, H2, W2);
+    vb::launch_k(space_to_depth_kernel<float>, dim3(grid), dim3(256), 0, s, static_cast<const float*>(x), static_cast<__nv_bfloat16*>(xs), B, H, W, C, sy, sx, H2, W2);
   else if (dtype == 1)
-    space_to_depth_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(xs), B, H, W, C, sy, sx, H2, W2);
+    vb::launch_k(space_to_depth_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(xs), B, H, W, C, sy, sx, H2, W2);
   else
     VB_REQUIRE(false, "vb_space_to_depth: dtype must be f32 (0) or bf16 (1)");
   VB_CHECK_CUDA(cudaGetLastError());
@@ -1263,7 +1279,7 @@ extern "C" int vb_gather_cols(const void* src, int src_dtype, long long ld_src, 
   const long long total = static_cast<long long>(rows) * cols;
   if (total == 0) return 0;
   const int grid = grid_cap2(total, 256);
-#define VB_GC(TS, TD) gather_cols_kernel<TS, TD><<<grid, 256, 0, s>>>(static_cast<const TS*>(src), ld_src, static_cast<TD*>(dst), ld_dst, map, rows, cols, accumulate)
+#define VB_GC(TS, TD) vb::launch_k(gather_cols_kernel<TS, TD>, dim3(grid), dim3(256), 0, s, static_cast<const TS*>(src), ld_src, static_cast<TD*>(dst), ld_dst, map, rows, cols, accumulate)
   if (src_dtype == 0 && dst_dtype == 0) VB_GC(float, float);
   else if (src_dtype == 0 && dst_dtype == 1) VB_GC(float, __nv_bfloat16);
   else if (src_dtype == 1 && dst_dtype == 1) VB_GC(__nv_bfloat16, __nv_bfloat16);

@@ -227,6 +227,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  // barriers, tensor memory and descriptor prefetches above overlap the previous kernel's tail; global memory is
+  // touched only from here on
+  pdl_sync();
 
   const int tiles_mn = p.m_blocks * p.n_blocks;
   const int num_tiles = tiles_mn * p.split_k;
@@ -919,16 +922,18 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     cfg.blockDim = dim3(GEMM_THREADS);
     cfg.dynamicSmemBytes = L::TOTAL;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = g_pdl_enabled ? 2 : 1;
     VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, tp, p));
   } else {
-    kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ta, tb, td, tp, p);
+    VB_CHECK_CUDA(launch_k(kern, dim3(grid), dim3(GEMM_THREADS), L::TOTAL, stream, ta, tb, td, tp, p));
   }
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;

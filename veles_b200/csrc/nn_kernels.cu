@@ -42,6 +42,7 @@ struct ConvGeom {
 
 __global__ void im2col_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols,
                                    const ConvGeom g) {
+  vb::pdl_sync();
   const int Cg = g.C / g.groups;
   const int kk = g.ky * g.kx;
   const int vec_per_row = static_cast<int>(g.ld >> 3);
@@ -73,6 +74,7 @@ __global__ void im2col_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
 
 __global__ void im2col_scalar_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols,
                                      const ConvGeom g) {
+  vb::pdl_sync();
   const int Cg = g.C / g.groups;
   const int kk = g.ky * g.kx;
   const int used = g.groups * kk * Cg;
@@ -107,6 +109,7 @@ __global__ void im2col_scalar_kernel(const __nv_bfloat16* __restrict__ x, __nv_b
 // PREVIOUS layer (dx *= f'(z)), which is what Znicz GD units apply to err_output.
 __global__ void col2im_kernel(const __nv_bfloat16* __restrict__ dcols, __nv_bfloat16* __restrict__ dx,
                               const ConvGeom g, const __nv_bfloat16* __restrict__ z, int deriv) {
+  vb::pdl_sync();
   const int Cg = g.C / g.groups;
   const int kk = g.ky * g.kx;
   const long long total = static_cast<long long>(g.B) * g.H * g.W * g.C;
@@ -152,6 +155,7 @@ struct PoolGeom {
 template <typename T>
 __global__ void pool_forward_kernel(int kind, const T* __restrict__ x, T* __restrict__ y, int* __restrict__ offs,
                                     const PoolGeom g, const uint16_t* __restrict__ rnd) {
+  vb::pdl_sync();
   const long long total = static_cast<long long>(g.B) * g.OH * g.OW * g.C;
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
        t += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -219,6 +223,7 @@ __global__ void pool_forward_kernel(int kind, const T* __restrict__ x, T* __rest
 template <typename T>
 __global__ void pool_backward_kernel(int kind, const T* __restrict__ dy, const int* __restrict__ offs,
                                      T* __restrict__ dx, const PoolGeom g) {
+  vb::pdl_sync();
   const long long total = static_cast<long long>(g.B) * g.H * g.W * g.C;
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
        t += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -254,6 +259,7 @@ __global__ void pool_backward_kernel(int kind, const T* __restrict__ dy, const i
 template <typename T>
 __global__ void lrn_forward_kernel(const T* __restrict__ x, T* __restrict__ y, long long pixels, int C, int n,
                                    float alpha, float beta, float k) {
+  vb::pdl_sync();
   const long long total = pixels * C;
   const int half = n / 2;
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
@@ -274,6 +280,7 @@ __global__ void lrn_forward_kernel(const T* __restrict__ x, T* __restrict__ y, l
 template <typename T>
 __global__ void lrn_backward_kernel(const T* __restrict__ x, const T* __restrict__ dy, T* __restrict__ dx,
                                     long long pixels, int C, int n, float alpha, float beta, float k) {
+  vb::pdl_sync();
   const long long total = pixels * C;
   const int half = n / 2;
   for (long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; t < total;
@@ -313,6 +320,7 @@ __global__ void softmax_eval_kernel(const TIN* __restrict__ s, long long lds, TO
                                     int* __restrict__ max_idx, int batch, int N, float err_scale,
                                     int* __restrict__ n_err, int* __restrict__ confusion,
                                     float* __restrict__ max_err_sum, float* __restrict__ loss_sum) {
+  vb::pdl_sync();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= batch) return;
@@ -374,6 +382,7 @@ template <typename T>
 __global__ void mse_eval_kernel(const T* __restrict__ y, long long ldy, const T* __restrict__ target, long long ldt,
                                 T* __restrict__ err, long long lde, int batch, int batch_valid, int N,
                                 float err_scale, float* __restrict__ metrics, float* __restrict__ mse_per_sample) {
+  vb::pdl_sync();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= batch) return;
@@ -428,6 +437,7 @@ __global__ void mse_eval_kernel(const T* __restrict__ y, long long ldy, const T*
 // ---------------------------------------------------------------------------
 template <typename T>
 __global__ void row_sum_kernel(const T* __restrict__ a, long long lda, int rows, int cols, float* __restrict__ out) {
+  vb::pdl_sync();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= rows) return;
@@ -451,6 +461,7 @@ static inline int colsum_rows_per_slab(int rows) {
 template <typename T>
 __global__ void col_sum_partial_kernel(const T* __restrict__ a, long long lda, int rows, int cols,
                                        float* __restrict__ scratch, int rows_per_slab) {
+  vb::pdl_sync();
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
   const int slab = blockIdx.y;
   if (col >= cols) return;
@@ -466,6 +477,7 @@ __global__ void col_sum_partial_kernel(const T* __restrict__ a, long long lda, i
 __global__ void __launch_bounds__(256)
 col_sum_partial_vec8_kernel(const __nv_bfloat16* __restrict__ a, long long lda, int rows, int cols,
                             float* __restrict__ scratch, int rows_per_slab, int vcb, int rl) {
+  vb::pdl_sync();
   __shared__ float red[256 * 8];
   const int vc_local = threadIdx.x % vcb;
   const int lane_r = threadIdx.x / vcb;
@@ -520,6 +532,7 @@ struct ColSumGD {
 __global__ void __launch_bounds__(256)
 col_sum_final_kernel(const float* __restrict__ scratch, int slabs, int cols, float* __restrict__ out, float alpha,
                      int accumulate, const ColSumGD gd) {
+  vb::pdl_sync();
   __shared__ float red[32][9];
   const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
   const int col = blockIdx.x * 8 + tx;
@@ -560,18 +573,18 @@ static int launch_col_sum(const void* a, int dtype, long long lda, int rows, int
       const int vcb = vcols < 32 ? vcols : 32;
       const int rl = 256 / vcb;
       dim3 grid(ceil_div(vcols, vcb), slabs);
-      col_sum_partial_vec8_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch,
+      vb::launch_k(col_sum_partial_vec8_kernel, dim3(grid), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch,
                                                        rps, vcb, rl);
     } else {
       dim3 grid(ceil_div(cols, 128), slabs);
       if (dtype == D_F32)
-        col_sum_partial_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, scratch, rps);
+        vb::launch_k(col_sum_partial_kernel<float>, dim3(grid), dim3(128), 0, s, static_cast<const float*>(a), lda, rows, cols, scratch, rps);
       else
-        col_sum_partial_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch, rps);
+        vb::launch_k(col_sum_partial_kernel<__nv_bfloat16>, dim3(grid), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(a), lda, rows, cols, scratch, rps);
     }
     VB_CHECK_CUDA(cudaGetLastError());
   }
-  col_sum_final_kernel<<<ceil_div(cols, 8), 256, 0, s>>>(scratch, slabs, cols, out, alpha, accumulate, gd);
+  vb::launch_k(col_sum_final_kernel, dim3(ceil_div(cols, 8)), dim3(256), 0, s, scratch, slabs, cols, out, alpha, accumulate, gd);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -595,13 +608,13 @@ extern "C" int vb_im2col(const void* x, void* cols, int B, int H, int W, int C, 
   const int Cg = C / groups;
   if (Cg % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(cols) & 15) == 0) {
     const long long total = rows * (ld >> 3);
-    im2col_vec8_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), g);
+    vb::launch_k(im2col_vec8_kernel, dim3(grid_cap(total, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), g);
   } else {
     FastConvGeom fg{B, H, W, C, OH, OW, ky, kx, sy, sx, pad_top, pad_left, groups, ld};
     const int fr = fast_im2col(x, cols, fg, s);
     if (fr != 0) return fr < 0 ? fr : 0;
     const long long total = rows * ld;
-    im2col_scalar_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), g);
+    vb::launch_k(im2col_scalar_kernel, dim3(grid_cap(total, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(cols), g);
   }
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -619,7 +632,7 @@ extern "C" int vb_col2im(const void* dcols, void* dx, int B, int H, int W, int C
     const int fr = fast_col2im(dcols, dx, fg, z, deriv, s);
     if (fr != 0) return fr < 0 ? fr : 0;
   }
-  col2im_kernel<<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dcols), static_cast<__nv_bfloat16*>(dx), g,
+  vb::launch_k(col2im_kernel, dim3(grid_cap(total, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(dcols), static_cast<__nv_bfloat16*>(dx), g,
                                                       static_cast<const __nv_bfloat16*>(z), deriv);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -639,9 +652,9 @@ extern "C" int vb_pool_forward(int kind, const void* x, void* y, int* offs, int 
     if (fr != 0) return fr < 0 ? fr : 0;
   }
   if (dtype == D_F32)
-    pool_forward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const float*>(x), static_cast<float*>(y), offs, g, static_cast<const uint16_t*>(rnd_u16));
+    vb::launch_k(pool_forward_kernel<float>, dim3(grid_cap(total, 256)), dim3(256), 0, s, kind, static_cast<const float*>(x), static_cast<float*>(y), offs, g, static_cast<const uint16_t*>(rnd_u16));
   else
-    pool_forward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), offs, g, static_cast<const uint16_t*>(rnd_u16));
+    vb::launch_k(pool_forward_kernel<__nv_bfloat16>, dim3(grid_cap(total, 256)), dim3(256), 0, s, kind, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), offs, g, static_cast<const uint16_t*>(rnd_u16));
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -673,9 +686,9 @@ extern "C" int vb_pool_backward_fused(int kind, const void* dy, const int* offs,
     if (fr != 0) return fr < 0 ? fr : 0;
   }
   if (dtype == D_F32)
-    pool_backward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const float*>(dy), offs, static_cast<float*>(dx), g);
+    vb::launch_k(pool_backward_kernel<float>, dim3(grid_cap(total, 256)), dim3(256), 0, s, kind, static_cast<const float*>(dy), offs, static_cast<float*>(dx), g);
   else
-    pool_backward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(kind, static_cast<const __nv_bfloat16*>(dy), offs, static_cast<__nv_bfloat16*>(dx), g);
+    vb::launch_k(pool_backward_kernel<__nv_bfloat16>, dim3(grid_cap(total, 256)), dim3(256), 0, s, kind, static_cast<const __nv_bfloat16*>(dy), offs, static_cast<__nv_bfloat16*>(dx), g);
   VB_CHECK_CUDA(cudaGetLastError());
   if (z && deriv) return vb_activation_backward(deriv, dx, nullptr, z, dx, total, dtype, 1.0f, s);
   return 0;
@@ -720,9 +733,9 @@ extern "C" int vb_lrn_forward(const void* x, void* y, int dtype, long long pixel
     if (fr != 0) return fr < 0 ? fr : 0;
   }
   if (dtype == D_F32)
-    lrn_forward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const float*>(x), static_cast<float*>(y), pixels, C, n, alpha, beta, k);
+    vb::launch_k(lrn_forward_kernel<float>, dim3(grid_cap(total, 256)), dim3(256), 0, s, static_cast<const float*>(x), static_cast<float*>(y), pixels, C, n, alpha, beta, k);
   else
-    lrn_forward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, n, alpha, beta, k);
+    vb::launch_k(lrn_forward_kernel<__nv_bfloat16>, dim3(grid_cap(total, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), pixels, C, n, alpha, beta, k);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -745,9 +758,9 @@ extern "C" int vb_lrn_backward_fused(const void* x, const void* dy, void* dx, in
     if (fr != 0) return fr < 0 ? fr : 0;
   }
   if (dtype == D_F32)
-    lrn_backward_kernel<float><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const float*>(x), static_cast<const float*>(dy), static_cast<float*>(dx), pixels, C, n, alpha, beta, k);
+    vb::launch_k(lrn_backward_kernel<float>, dim3(grid_cap(total, 256)), dim3(256), 0, s, static_cast<const float*>(x), static_cast<const float*>(dy), static_cast<float*>(dx), pixels, C, n, alpha, beta, k);
   else
-    lrn_backward_kernel<__nv_bfloat16><<<grid_cap(total, 256), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), pixels, C, n, alpha, beta, k);
+    vb::launch_k(lrn_backward_kernel<__nv_bfloat16>, dim3(grid_cap(total, 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), pixels, C, n, alpha, beta, k);
   VB_CHECK_CUDA(cudaGetLastError());
   if (deriv) return vb_activation_backward(deriv, dx, nullptr, x, dx, total, dtype, 1.0f, s);
   return 0;
@@ -775,7 +788,7 @@ extern "C" int vb_softmax_eval(const void* sm_in, int in_dtype, long long lds, v
   const int threads = 128;
   const int grid = ceil_div(batch * 32, threads);
 #define VB_SM(TIN, TOUT)                                                                                      \
-  softmax_eval_kernel<TIN, TOUT><<<grid, threads, 0, s>>>(static_cast<const TIN*>(sm_in), lds,                \
+  vb::launch_k(softmax_eval_kernel<TIN, TOUT>, dim3(grid), dim3(threads), 0, s, static_cast<const TIN*>(sm_in), lds,                \
                                                           static_cast<TOUT*>(y), ldy, static_cast<TOUT*>(err), \
                                                           lde, labels, max_idx, batch, N, err_scale, n_err,   \
                                                           confusion, max_err_sum, loss_sum)
@@ -796,10 +809,10 @@ extern "C" int vb_mse_eval(const void* y, long long ldy, const void* target, lon
   const int threads = 128;
   const int grid = ceil_div(batch * 32, threads);
   if (dtype == D_F32)
-    mse_eval_kernel<float><<<grid, threads, 0, s>>>(static_cast<const float*>(y), ldy, static_cast<const float*>(target), ldt,
+    vb::launch_k(mse_eval_kernel<float>, dim3(grid), dim3(threads), 0, s, static_cast<const float*>(y), ldy, static_cast<const float*>(target), ldt,
                                                     static_cast<float*>(err), lde, batch, batch_valid, N, err_scale, metrics, mse_per_sample);
   else
-    mse_eval_kernel<__nv_bfloat16><<<grid, threads, 0, s>>>(static_cast<const __nv_bfloat16*>(y), ldy,
+    vb::launch_k(mse_eval_kernel<__nv_bfloat16>, dim3(grid), dim3(threads), 0, s, static_cast<const __nv_bfloat16*>(y), ldy,
                                                             static_cast<const __nv_bfloat16*>(target), ldt,
                                                             static_cast<__nv_bfloat16*>(err), lde, batch, batch_valid, N,
                                                             err_scale, metrics, mse_per_sample);
@@ -810,8 +823,8 @@ extern "C" int vb_mse_eval(const void* y, long long ldy, const void* target, lon
 extern "C" int vb_row_sum(const void* a, int dtype, long long lda, int rows, int cols, float* out, cudaStream_t s) {
   if (rows == 0) return 0;
   const int grid = ceil_div(rows * 32, 128);
-  if (dtype == D_F32) row_sum_kernel<float><<<grid, 128, 0, s>>>(static_cast<const float*>(a), lda, rows, cols, out);
-  else row_sum_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(static_cast<const __nv_bfloat16*>(a), lda, rows, cols, out);
+  if (dtype == D_F32) vb::launch_k(row_sum_kernel<float>, dim3(grid), dim3(128), 0, s, static_cast<const float*>(a), lda, rows, cols, out);
+  else vb::launch_k(row_sum_kernel<__nv_bfloat16>, dim3(grid), dim3(128), 0, s, static_cast<const __nv_bfloat16*>(a), lda, rows, cols, out);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -14,6 +14,7 @@ namespace vb {
 
 __global__ void xorshift1024star_kernel(uint64_t* __restrict__ states, int n_states, int rounds,
                                         uint64_t* __restrict__ out) {
+  vb::pdl_sync();
   const int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= n_states) return;
   uint64_t s[16];
@@ -40,6 +41,7 @@ __global__ void xorshift1024star_kernel(uint64_t* __restrict__ states, int n_sta
 }
 
 __global__ void xorshift128plus_kernel(ulonglong2* __restrict__ states, long long n, uint64_t* __restrict__ out) {
+  vb::pdl_sync();
   const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   if (i >= n) return;
   ulonglong2 st = states[i];
@@ -57,6 +59,7 @@ __global__ void xorshift128plus_kernel(ulonglong2* __restrict__ states, long lon
 // (the reference clips host-side normal fills the same way: veles/prng/random_generator.py:185-198).
 __global__ void fill_random_kernel(ulonglong2* __restrict__ states, int n_states, float* __restrict__ out,
                                    long long n, int kind, float amp) {
+  vb::pdl_sync();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_states) return;
   ulonglong2 st = states[t];
@@ -94,7 +97,7 @@ using namespace vb;
 extern "C" int vb_xorshift1024star(void* states, int n_states, int rounds, void* out, cudaStream_t s) {
   if (n_states == 0 || rounds == 0) return 0;
   // block <= 32 threads like the reference launch (64 live u64 registers per thread)
-  xorshift1024star_kernel<<<ceil_div(n_states, 32), 32, 0, s>>>(static_cast<uint64_t*>(states), n_states, rounds,
+  vb::launch_k(xorshift1024star_kernel, dim3(ceil_div(n_states, 32)), dim3(32), 0, s, static_cast<uint64_t*>(states), n_states, rounds,
                                                                static_cast<uint64_t*>(out));
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -102,7 +105,7 @@ extern "C" int vb_xorshift1024star(void* states, int n_states, int rounds, void*
 
 extern "C" int vb_xorshift128plus(void* states, long long n, void* out, cudaStream_t s) {
   if (n == 0) return 0;
-  xorshift128plus_kernel<<<static_cast<int>(ceil_div_ll(n, 256)), 256, 0, s>>>(static_cast<ulonglong2*>(states), n,
+  vb::launch_k(xorshift128plus_kernel, dim3(static_cast<int>(ceil_div_ll(n, 256))), dim3(256), 0, s, static_cast<ulonglong2*>(states), n,
                                                                               static_cast<uint64_t*>(out));
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -112,7 +115,7 @@ extern "C" int vb_fill_random(void* states, int n_states, float* out, long long 
                               cudaStream_t s) {
   if (n == 0) return 0;
   VB_REQUIRE(n_states > 0, "vb_fill_random: need at least one generator state");
-  fill_random_kernel<<<ceil_div(n_states, 128), 128, 0, s>>>(static_cast<ulonglong2*>(states), n_states, out, n, kind, amp);
+  vb::launch_k(fill_random_kernel, dim3(ceil_div(n_states, 128)), dim3(128), 0, s, static_cast<ulonglong2*>(states), n_states, out, n, kind, amp);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

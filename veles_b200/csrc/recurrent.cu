@@ -26,6 +26,7 @@ lstm_cell_forward_kernel(const float* __restrict__ z, long long ldz, const float
                          float* __restrict__ c, float* __restrict__ gates, long long ldg,
                          __nv_bfloat16* __restrict__ h_next, long long ld_next, void* __restrict__ out, int out_dt,
                          long long ld_out, int B, int H) {
+  vb::pdl_sync();
   const long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   if (idx >= static_cast<long long>(B) * H) return;
   const int b = static_cast<int>(idx / H), j = static_cast<int>(idx - static_cast<long long>(b) * H);
@@ -53,6 +54,7 @@ lstm_cell_backward_kernel(const void* __restrict__ dh_ext, int ext_dt, long long
                           const float* __restrict__ dh_rec, long long ld_rec, float* __restrict__ dc, int first,
                           const float* __restrict__ gates, long long ldg, const float* __restrict__ c_prev,
                           const float* __restrict__ c, __nv_bfloat16* __restrict__ dz, long long ld_dz, int B, int H) {
+  vb::pdl_sync();
   const long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   if (idx >= static_cast<long long>(B) * H) return;
   const int b = static_cast<int>(idx / H), j = static_cast<int>(idx - static_cast<long long>(b) * H);
@@ -76,6 +78,7 @@ __global__ void __launch_bounds__(256)
 rnn_cell_forward_kernel(const float* __restrict__ z, long long ldz, float* __restrict__ h_save,
                         __nv_bfloat16* __restrict__ h_next, long long ld_next, void* __restrict__ out, int out_dt,
                         long long ld_out, int B, int H) {
+  vb::pdl_sync();
   const long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   if (idx >= static_cast<long long>(B) * H) return;
   const int b = static_cast<int>(idx / H), j = static_cast<int>(idx - static_cast<long long>(b) * H);
@@ -89,6 +92,7 @@ __global__ void __launch_bounds__(256)
 rnn_cell_backward_kernel(const void* __restrict__ dh_ext, int ext_dt, long long ld_ext,
                          const float* __restrict__ dh_rec, long long ld_rec, const float* __restrict__ h_save,
                          __nv_bfloat16* __restrict__ dz, long long ld_dz, int B, int H) {
+  vb::pdl_sync();
   const long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   if (idx >= static_cast<long long>(B) * H) return;
   const int b = static_cast<int>(idx / H), j = static_cast<int>(idx - static_cast<long long>(b) * H);
@@ -110,7 +114,7 @@ extern "C" int vb_lstm_cell_forward(const float* z, long long ldz, const float* 
                                     long long ld_out, int B, int H, cudaStream_t s) {
   VB_REQUIRE(B > 0 && H > 0, "vb_lstm_cell_forward: empty cell");
   VB_REQUIRE(out_dtype == 0 || out_dtype == 1, "vb_lstm_cell_forward: output must be fp32 or bf16");
-  lstm_cell_forward_kernel<<<rec_blocks(B, H), 256, 0, s>>>(z, ldz, c_prev, c, gates, ldg,
+  vb::launch_k(lstm_cell_forward_kernel, dim3(rec_blocks(B, H)), dim3(256), 0, s, z, ldz, c_prev, c, gates, ldg,
                                                            static_cast<__nv_bfloat16*>(h_next), ld_next, out, out_dtype,
                                                            ld_out, B, H);
   VB_CHECK_CUDA(cudaGetLastError());
@@ -123,7 +127,7 @@ extern "C" int vb_lstm_cell_backward(const void* dh_ext, int ext_dtype, long lon
                                      cudaStream_t s) {
   VB_REQUIRE(B > 0 && H > 0, "vb_lstm_cell_backward: empty cell");
   VB_REQUIRE(ext_dtype == 0 || ext_dtype == 1, "vb_lstm_cell_backward: err_output must be fp32 or bf16");
-  lstm_cell_backward_kernel<<<rec_blocks(B, H), 256, 0, s>>>(dh_ext, ext_dtype, ld_ext, dh_rec, ld_rec, dc, first, gates,
+  vb::launch_k(lstm_cell_backward_kernel, dim3(rec_blocks(B, H)), dim3(256), 0, s, dh_ext, ext_dtype, ld_ext, dh_rec, ld_rec, dc, first, gates,
                                                             ldg, c_prev, c, static_cast<__nv_bfloat16*>(dz), ld_dz, B,
                                                             H);
   VB_CHECK_CUDA(cudaGetLastError());
@@ -134,7 +138,7 @@ extern "C" int vb_rnn_cell_forward(const float* z, long long ldz, float* h_save,
                                    void* out, int out_dtype, long long ld_out, int B, int H, cudaStream_t s) {
   VB_REQUIRE(B > 0 && H > 0, "vb_rnn_cell_forward: empty cell");
   VB_REQUIRE(out_dtype == 0 || out_dtype == 1, "vb_rnn_cell_forward: output must be fp32 or bf16");
-  rnn_cell_forward_kernel<<<rec_blocks(B, H), 256, 0, s>>>(z, ldz, h_save, static_cast<__nv_bfloat16*>(h_next), ld_next,
+  vb::launch_k(rnn_cell_forward_kernel, dim3(rec_blocks(B, H)), dim3(256), 0, s, z, ldz, h_save, static_cast<__nv_bfloat16*>(h_next), ld_next,
                                                           out, out_dtype, ld_out, B, H);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -145,7 +149,7 @@ extern "C" int vb_rnn_cell_backward(const void* dh_ext, int ext_dtype, long long
                                     cudaStream_t s) {
   VB_REQUIRE(B > 0 && H > 0, "vb_rnn_cell_backward: empty cell");
   VB_REQUIRE(ext_dtype == 0 || ext_dtype == 1, "vb_rnn_cell_backward: err_output must be fp32 or bf16");
-  rnn_cell_backward_kernel<<<rec_blocks(B, H), 256, 0, s>>>(dh_ext, ext_dtype, ld_ext, dh_rec, ld_rec, h_save,
+  vb::launch_k(rnn_cell_backward_kernel, dim3(rec_blocks(B, H)), dim3(256), 0, s, dh_ext, ext_dtype, ld_ext, dh_rec, ld_rec, h_save,
                                                            static_cast<__nv_bfloat16*>(dz), ld_dz, B, H);
   VB_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -30,6 +30,7 @@ int device_sm_count() {
 
 // SMs the persistent tcgen05 kernels may fill: all of them, minus the ones a pending data-parallel exchange kernel
 // runs on (vb_set_sm_reserve).  Read at launch (= graph capture) time.
+int g_pdl_enabled = 0;
 static int g_sm_reserve = 0;
 int gemm_sm_count() {
   int n = (device_sm_count() - g_sm_reserve) & ~1;   // whole TPCs: CTA pairs take two SMs
@@ -43,6 +44,14 @@ int gemm_sm_count() {
 extern "C" int vb_set_sm_reserve(int n) {
   const int prev = vb::g_sm_reserve;
   vb::g_sm_reserve = n < 0 ? 0 : n;
+  return prev;
+}
+
+// 1: kernels of this library are launched with programmatic stream serialisation from now on (each waits for its
+// predecessor with griddepcontrol.wait, so results are unchanged); 0: ordinary launches.  Returns the previous value.
+extern "C" int vb_set_pdl(int on) {
+  const int prev = vb::g_pdl_enabled;
+  vb::g_pdl_enabled = on ? 1 : 0;
   return prev;
 }
 

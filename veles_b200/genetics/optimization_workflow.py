@@ -252,7 +252,9 @@ class OptimizationWorkflow(Workflow):
     hide_from_registry = True
 
     def __init__(self, workflow, **kwargs):
-        super(OptimizationWorkflow, self).__init__(workflow, **kwargs)
+        optimizer_keys = ("model", "config_file", "argv", "size", "generations", "parallel", "env")
+        super(OptimizationWorkflow, self).__init__(
+            workflow, **{k: v for k, v in kwargs.items() if k not in optimizer_keys})
         self.repeater = Repeater(self)
         self.repeater.link_from(self.start_point)
         self.optimizer = GeneticsOptimizer(self, **kwargs)

@@ -28,6 +28,9 @@ _lock = threading.Lock()
 _lib = None
 
 
+PDL_DEFAULT = False
+
+
 def kernel_sources():
     return sorted(os.path.join(CSRC_DIR, f) for f in os.listdir(CSRC_DIR) if f.endswith(".cu"))
 
@@ -103,6 +106,10 @@ def lib():
     handle = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
     handle.vb_last_error.restype = ctypes.c_char_p
     handle.vb_col_sum_scratch_elems.restype = ctypes.c_longlong
+    # programmatic dependent launch between consecutive kernels (root.common.engine.pdl / VELES_B200_PDL)
+    from ..config import root, get
+    pdl = os.environ.get("VELES_B200_PDL")
+    handle.vb_set_pdl(ctypes.c_int(int(pdl) if pdl is not None else int(bool(get(root.common.engine.pdl, PDL_DEFAULT)))))
     _lib = handle
     return _lib
 

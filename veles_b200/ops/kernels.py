@@ -91,6 +91,12 @@ def set_dynamic_schedule(on):
     _lib.check(_lib.lib().vb_gemm_set_dynamic_schedule(c_int(int(bool(on)))), "vb_gemm_set_dynamic_schedule")
 
 
+def set_pdl(on):
+    """Programmatic dependent launch for every kernel of the library (csrc/common.cuh ``launch_k``): the next kernel of
+    a stream is scheduled while the current one drains and waits at its first global access.  Returns the old value."""
+    return bool(_lib.lib().vb_set_pdl(c_int(int(bool(on)))))
+
+
 def set_pair_mode(mode):
     """Test hook: 0 = the cost model picks, 1 = single-CTA tiles only, 2 = CTA-pair (cta_group::2) tiles whenever
     the shape allows."""

@@ -27,7 +27,8 @@ from ctypes import c_double, c_float, c_int, c_longlong, c_void_p
 
 import numpy
 
-SYMMETRIC_KINDS = ("weights", "weights_bf16", "grads", "grads1", "grads_in", "dp_flags", "velocity")
+SYMMETRIC_KINDS = ("weights", "weights_bf16", "grads", "grads1", "grads_in", "dp_flags", "dp_counters", "velocity")
+COUNTER_SLOT = 16384   # doubles per parity of the device-side counter exchange (csrc/comm_counters.cu)
 MAX_WORLD = 8
 MAX_SEGS = 16          # csrc/comm_fused.cu
 SEG_ZERO_OTHER = 1     # the segment's gradient kernels accumulate: the update kernel clears the other parity's buffer
@@ -159,6 +160,16 @@ class DataParallel(object):
                     # push: staging slab the peers store their contributions into
                     arena.mirror("grads1" if self.exchange == "pull" else "grads_in", w.devmem.view(-1))
         self.flags = arena.alloc("dp_flags", "flags", 64 * 2 * MAX_WORLD, torch.int32)
+        # class / epoch ends: counters are summed and the sharded state gathered by kernels over peer memory
+        from ..ops import _lib
+        L = _lib.lib()
+        L.vb_counter_region_bytes.restype = ctypes.c_longlong
+        self.counter_region = arena.alloc("dp_counters", "counters",
+                                          int(L.vb_counter_region_bytes(ctypes.c_longlong(COUNTER_SLOT))), torch.uint8)
+        self.counter_epoch = torch.zeros(1, dtype=torch.int32, device=dev.torch_device)
+        self.counter_in = torch.zeros(COUNTER_SLOT, dtype=torch.float64, device=dev.torch_device)
+        self.counter_out = torch.zeros(COUNTER_SLOT, dtype=torch.float64, device=dev.torch_device)
+        self.counter_host = torch.zeros(COUNTER_SLOT, dtype=torch.float64).pin_memory()
         self.epochs = torch.zeros(64, dtype=torch.int32, device=dev.torch_device)
         self.cta_counter = torch.zeros(128, dtype=torch.int32, device=dev.torch_device)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev.torch_device)
@@ -172,6 +183,9 @@ class DataParallel(object):
         for gd in self.units:
             self.unit_info[id(gd)] = self._describe(gd)
         self._build_buckets()
+        cidx, coff = arena.locate(self.counter_region, "dp_counters")
+        cl = self._slab_ptrs("dp_counters", cidx)
+        self.counter_ptrs = (cl[0] + coff, [p + coff for p in cl[2]])
         self._dist.barrier()
         torch.cuda.synchronize()
 
@@ -440,39 +454,69 @@ class DataParallel(object):
         return lo, min(numel, lo + chunk)
 
     def sync_master(self):
-        """Collective: reassemble the full fp32 master weights and momentum on every rank from the owners' slices
-        (P2P copies out of the peers' symmetric slabs).  No-op unless ``shard_master`` left them stale."""
+        """Collective: reassemble the full fp32 master weights and momentum on every rank from the owners' slices.
+        Device-side only: a flag barrier over peer memory, one gather kernel per slab that reads the peers' slices,
+        a closing barrier - no NCCL collective and no host synchronisation (the caller's next host read waits on
+        the stream as usual).  No-op unless ``shard_master`` left them stale."""
         import torch
         if self.mode != "fused" or not self.master_stale:
             return
+        from ..ops import _lib
+        L = _lib.lib()
         self.finish_step_events()
-        torch.cuda.synchronize()
-        self._dist.barrier()
+        stream = c_void_p(torch.cuda.current_stream().cuda_stream)
+        self.device_allreduce(None)            # every rank's last update has completed
+        launched = False
+        by_slab = {}
         for gd in self.units:
             info = self.unit_info[id(gd)]
             # fp32 master weights, and the momentum each owner alone keeps (a snapshot written by rank 0 must carry
             # all of it: a resumed or re-sharded run continues with the right velocity)
             kinds = (["weights"] if self.shard_master else []) + (["velocity"] if info.get("vel_symmetric") else [])
             for kind in kinds:
-                slab = self.arena.slabs[kind][info["slab"]][0]
-                hdl = self.handles[slab.data_ptr()]
-                delta = slab.data_ptr() - int(hdl.buffer_ptrs[self.rank])
-                local = slab.view(torch.float32)
+                segs = by_slab.setdefault((kind, info["slab"]), [])
                 for seg in info["segs"]:
-                    off, numel = int(seg[0]), int(seg[1])
                     if kind == "weights" and (int(seg[5]) & SEG_BCAST_MASTER):
                         continue               # already current on every rank
-                    for r in range(self.world_size):
-                        if r == self.rank:
-                            continue
-                        lo, hi = self.slice_bounds(numel, r)
-                        if hi <= lo:
-                            continue
-                        peer = hdl.get_buffer(r, (hi - lo,), torch.float32, delta // 4 + off + lo)
-                        local[off + lo:off + hi].copy_(peer)
-        torch.cuda.synchronize()
-        self._dist.barrier()
+                    segs.append((int(seg[0]), int(seg[1])))
+        for (kind, slab_idx), segs in by_slab.items():
+            local, _, peers = self._slab_ptrs(kind, slab_idx)
+            peer_arr = (c_void_p * MAX_WORLD)(*[c_void_p(p) for p in peers])
+            for k in range(0, len(segs), MAX_SEGS):
+                part = segs[k:k + MAX_SEGS]
+                seg_arr = (c_longlong * (2 * len(part)))(*[v for sg in part for v in sg])
+                rc = L.vb_gather_slices(c_int(self.world_size), c_int(self.rank), c_int(len(part)), seg_arr,
+                                        c_void_p(local), peer_arr, c_int(32), stream)
+                _lib.check(rc, "vb_gather_slices")
+                launched = True
+        if launched:
+            self.device_allreduce(None)        # nobody updates a slice a peer may still be reading
         self.master_stale = False
+
+    def device_allreduce(self, values, op="sum"):
+        """All-reduce a few doubles over the group with ``vb_counter_allreduce`` (flags and slots in symmetric memory);
+        ``values`` None = barrier only.  Returns a numpy array (one D2H read: the caller is host logic)."""
+        import torch
+        from ..ops import _lib
+        n = 0 if values is None else len(values)
+        if n > COUNTER_SLOT:
+            raise ValueError("device_allreduce: %d values exceed the %d-element slot" % (n, COUNTER_SLOT))
+        if n:
+            self.counter_host[:n] = torch.as_tensor(numpy.asarray(values, dtype=numpy.float64))
+            self.counter_in[:n].copy_(self.counter_host[:n], non_blocking=True)
+        peer_arr = (c_void_p * MAX_WORLD)(*[c_void_p(p) for p in self.counter_ptrs[1]])
+        rc = _lib.lib().vb_counter_allreduce(
+            c_int(self.world_size), c_int(self.rank), c_int(n), c_int(1 if op == "max" else 0),
+            c_longlong(COUNTER_SLOT), c_void_p(self.counter_in.data_ptr()), c_void_p(self.counter_out.data_ptr()),
+            c_void_p(self.counter_ptrs[0]), peer_arr, c_void_p(self.counter_epoch.data_ptr()),
+            c_void_p(self.status.data_ptr()), c_double(self.timeout_s),
+            c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.check(rc, "vb_counter_allreduce")
+        if not n:
+            return None
+        out = self.counter_out[:n].cpu().numpy()
+        self.check()
+        return out
 
     def finish_step_events(self):
         import torch
@@ -485,6 +529,8 @@ class DataParallel(object):
         """Raise if any fused kernel hit its synchronisation timeout (reads one int from the device)."""
         if self.mode == "fused":
             st = int(self.status.item())
+            if st > 1000:
+                raise RuntimeError("counter exchange timed out waiting for peers (a rank is missing or hung)")
             if st:
                 raise RuntimeError("fused all-reduce+GD kernel timed out waiting for peers (channel %d)" % (st - 1))
 
@@ -492,17 +538,37 @@ class DataParallel(object):
     def sum_counters(self, vals, loss):
         import torch
         self.sync_master()   # class boundary: the host (Decision, Snapshotter, plotters) may read the weights now
-        t = torch.tensor(list(map(float, vals)) + [float(loss)], dtype=torch.float64, device=self._reduce_device())
-        self._dist.all_reduce(t)
-        out = t.cpu().numpy()
+        if self.mode == "fused":
+            out = self.device_allreduce(list(map(float, vals)) + [float(loss)])
+        else:
+            t = torch.tensor(list(map(float, vals)) + [float(loss)], dtype=torch.float64, device=self._reduce_device())
+            self._dist.all_reduce(t)
+            out = t.cpu().numpy()
         return numpy.round(out[:-1]).astype(numpy.int64), float(out[-1])
 
     def max_min(self, mx, mn):
         import torch
-        t = torch.tensor([mx, -mn], dtype=torch.float64, device=self._reduce_device())
-        self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX)
-        out = t.cpu().numpy()
+        if self.mode == "fused":
+            out = self.device_allreduce([mx, -mn], op="max")
+        else:
+            t = torch.tensor([mx, -mn], dtype=torch.float64, device=self._reduce_device())
+            self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX)
+            out = t.cpu().numpy()
         return float(out[0]), float(-out[1])
+
+    def sum_array(self, arr, op="sum"):
+        """Sum (or max) a small host array over the ranks (confusion matrices, max_err_y_sum); arrays larger than the
+        device slot go through the process group."""
+        import torch
+        a = numpy.asarray(arr)
+        if self.mode == "fused" and a.size <= COUNTER_SLOT:
+            out = self.device_allreduce(a.reshape(-1).astype(numpy.float64), op=op)
+        else:
+            t = torch.tensor(a.reshape(-1).astype(numpy.float64), device=self._reduce_device())
+            self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX if op == "max" else self._dist.ReduceOp.SUM)
+            out = t.cpu().numpy()
+        out = out.reshape(a.shape)
+        return numpy.round(out).astype(a.dtype) if numpy.issubdtype(a.dtype, numpy.integer) else out.astype(a.dtype)
 
     def _reduce_device(self):
         return "cpu" if self.mode == "host" else "cuda"

@@ -1,6 +1,7 @@
 """Publishing backends selected by name (reference: ``veles/publishing/*_backend.py``: markdown, pdf via weasyprint,
-confluence).  Here: ``markdown``, ``html`` (self-contained, plots inlined as SVG), ``json``, ``pdf`` (weasyprint
-when installed, else a built-in text PDF writer) and ``confluence`` (XML-RPC client in ``confluence.py``)."""
+confluence).  Here: ``markdown``, ``html`` (self-contained, plots inlined as SVG), ``json``, ``ipynb``, ``latex``, ``pdf``
+(weasyprint when installed, else a built-in text PDF writer) and ``confluence`` (XML-RPC client in
+``confluence.py``)."""
 from __future__ import annotations
 
 import json
@@ -82,6 +83,83 @@ class JSONBackend(Backend):
         path = self.target(info["name"], "json")
         with open(path, "w") as f:
             json.dump(info, f, indent=1, default=str)
+        return path
+
+
+class IPythonNotebookBackend(MarkdownBackend):
+    """Report as a Jupyter notebook (nbformat 4): the sections of the Markdown report as text cells, the results and
+    unit timings as data a code cell loads into ``results`` / ``unit_times`` for further analysis (the reference ships
+    an ``ipynb_template.ipynb`` for its jinja2 backend: ``veles/publishing/jinja2_template_backend.py``)."""
+    MAPPING = "ipynb"
+
+    def render(self, info):
+        def md(text):
+            return {"cell_type": "markdown", "metadata": {}, "source": text.splitlines(True)}
+
+        def code(text):
+            return {"cell_type": "code", "metadata": {}, "execution_count": None, "outputs": [],
+                    "source": text.splitlines(True)}
+
+        sections = self.text(dict(info, plots=[])).split("\n## ")
+        cells = [md(sections[0])] + [md("## " + sec) for sec in sections[1:]]
+        plain = {k: v for k, v in info.get("results", {}).items() if k not in ("Confusion", "Labels", "models")}
+        cells.append(code("import json\nresults = json.loads(%r)\nunit_times = json.loads(%r)\nresults\n"
+                          % (json.dumps(plain, default=str), json.dumps(info.get("unit_times", []), default=str))))
+        for p in info.get("plots", []):
+            if p:
+                cells.append(md("![%s](%s)" % (os.path.basename(p), p)))
+        nb = {"cells": cells, "metadata": {"kernelspec": {"display_name": "Python 3", "language": "python",
+                                                          "name": "python3"},
+                                           "language_info": {"name": "python"}, "title": str(info["name"])},
+              "nbformat": 4, "nbformat_minor": 5}
+        path = self.target(info["name"], "ipynb")
+        with open(path, "w") as f:
+            json.dump(nb, f, indent=1)
+        return path
+
+
+class LatexBackend(Backend):
+    """Report as a LaTeX article (``latex_template.tex`` of the reference's jinja2 backend): description, result and
+    unit-time tables, the configuration verbatim, plots as figures when they are PDF / PNG files."""
+    MAPPING = "latex"
+    SPECIAL = {"\\": r"\textbackslash{}", "&": r"\&", "%": r"\%", "$": r"\$", "#": r"\#", "_": r"\_", "{": r"\{",
+               "}": r"\}", "~": r"\textasciitilde{}", "^": r"\textasciicircum{}"}
+
+    @classmethod
+    def esc(cls, text):
+        return "".join(cls.SPECIAL.get(c, c) for c in str(text))
+
+    def text(self, info):
+        e = self.esc
+        out = [r"\documentclass[a4paper,10pt]{article}", r"\usepackage[utf8]{inputenc}", r"\usepackage{graphicx}",
+               r"\usepackage{longtable}", r"\usepackage[margin=2cm]{geometry}",
+               r"\title{%s}" % e(info["name"]), r"\date{}", r"\begin{document}", r"\maketitle",
+               e(info.get("description") or ""), "",
+               r"\begin{itemize}", r"\item id: \texttt{%s}" % e(info.get("id")),
+               r"\item mode: %s, device: %s" % (e(info.get("mode")), e(info.get("device"))),
+               r"\item run time: %.1f s, epochs: %s" % (info.get("run_time", 0), e(info.get("epochs"))),
+               r"\item random seeds: %s" % e(info.get("seeds")), r"\end{itemize}",
+               r"\section{Results}", r"\begin{longtable}{ll}"]
+        for k, v in sorted(info.get("results", {}).items()):
+            if k not in ("Confusion", "Labels", "models"):
+                out.append(r"%s & %s \\" % (e(k), e(v)))
+        out += [r"\end{longtable}", r"\section{Unit run times}", r"\begin{longtable}{lr}", r"unit & seconds \\ \hline"]
+        out += [r"%s & %.4f \\" % (e(n), t) for n, t in info.get("unit_times", [])]
+        out += [r"\end{longtable}", r"\section{Configuration}", r"\begin{verbatim}",
+                json.dumps(info.get("config", {}), indent=1, default=str), r"\end{verbatim}"]
+        figs = [p for p in info.get("plots", []) if p and p.lower().endswith((".pdf", ".png", ".jpg"))]
+        if figs:
+            out.append(r"\section{Plots}")
+            for p in figs:
+                out += [r"\begin{figure}[h]\centering", r"\includegraphics[width=0.8\textwidth]{%s}" % p,
+                        r"\caption{%s}" % e(os.path.basename(p)), r"\end{figure}"]
+        out += [r"\end{document}", ""]
+        return "\n".join(out)
+
+    def render(self, info):
+        path = self.target(info["name"], "tex")
+        with open(path, "w") as f:
+            f.write(self.text(info))
         return path
 
 

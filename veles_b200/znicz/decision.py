@@ -208,14 +208,16 @@ class DecisionGD(DecisionBase):
             cm.map_read()
             if self.confusion_matrixes[klass] is None:
                 self.confusion_matrixes[klass] = numpy.zeros_like(cm.mem)
-            self.confusion_matrixes[klass] += cm.mem
+            # every rank evaluated its shard of the class: the matrix of the whole class is the sum over ranks
+            self.confusion_matrixes[klass] += (cm.mem if self.dp_group is None else self.dp_group.sum_array(cm.mem))
             cm.map_write()
             cm.mem[...] = 0
             cm.unmap()
         ms = self.minibatch_max_err_y_sum
         if ms is not None and ms:
             ms.map_read()
-            self.max_err_y_sums[klass] = max(self.max_err_y_sums[klass], float(ms.mem[0]))
+            top = float(ms.mem[0]) if self.dp_group is None else float(self.dp_group.sum_array(ms.mem[:1], op="max")[0])
+            self.max_err_y_sums[klass] = max(self.max_err_y_sums[klass], top)
             ms.map_write()
             ms.mem[0] = 0
             ms.unmap()

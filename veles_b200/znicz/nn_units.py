@@ -69,7 +69,7 @@ class ParameterArena(object):
     multicast-mapped): ``allocator(kind, nbytes)`` decides."""
 
     ALIGN = 256  # bytes
-    SMALL_KINDS = {"dp_flags": 1 << 16}
+    SMALL_KINDS = {"dp_flags": 1 << 16, "dp_counters": (1 << 18) + 4096}
 
     def __init__(self, device, slab_bytes=None, allocator=None):
         self.device = device
