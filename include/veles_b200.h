@@ -76,6 +76,12 @@ int vb_conv_halo_bf16(int mode, const void* T, int tB, int tH, int tW, long long
  * become unit-stride ones the implicit GEMM can walk. */
 int vb_space_to_depth(const void* x, int dtype, void* xs, int B, int H, int W, int C, int sy, int sx,
                       cudaStream_t stream);
+/* Minibatch gather (rows by shuffled index, cast, (x - mean) * rdisp, zero rows past `count`) fused with that
+ * transform: xs [max_rows, ceil(H/sy), ceil(W/sx), sy*sx*C] bf16 is written directly and the NHWC minibatch never
+ * exists.  src_dtype: 0 f32, 1 bf16, 2 u8.  Returns 1 (nothing launched) when the geometry is not covered. */
+int vb_gather_s2d(const void* src, int src_dtype, long long src_ld, const int* indices, int start, int count,
+                  int max_rows, int H, int W, int C, int sy, int sx, void* xs, const float* mean, const float* rdisp,
+                  const int* labels, int* mb_labels, int* mb_indices, cudaStream_t stream);
 /* dst[r, j] (+)= src[r, map[j]] (0 where map[j] < 0); dtypes 0 f32 / 1 bf16. */
 int vb_gather_cols(const void* src, int src_dtype, long long ld_src, void* dst, int dst_dtype, long long ld_dst,
                    const int* map, int rows, int cols, int accumulate, cudaStream_t stream);

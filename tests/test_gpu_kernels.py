@@ -517,6 +517,61 @@ def test_gather_u8_to_bf16_is_exact_for_odd_row_sizes():
         assert torch.isnan(dst[mb:].float()).all(), "kernel wrote past the minibatch"
 
 
+@pytest.mark.parametrize("src_dtype", [torch.uint8, torch.float32])
+@pytest.mark.parametrize("H,W,C,sy,sx", [(227, 227, 3, 4, 4), (32, 30, 2, 2, 2), (17, 9, 1, 4, 2), (12, 12, 4, 1, 2)])
+def test_gather_fused_with_space_to_depth(src_dtype, H, W, C, sy, sx):
+    """``vb_gather_s2d`` against a plain fp32 restatement: gather by index, normalise, then x[b, h2*sy+dy, w2*sx+dx, c]
+    -> xs[b, h2, w2, (dy*sx+dx)*C + c] with zeros past the image edge and for rows past ``count``."""
+    k = K()
+    g = torch.Generator(device="cpu").manual_seed(H + W + C)
+    n, mb, count, start = 40, 19, 13, 5
+    size = H * W * C
+    if src_dtype == torch.uint8:
+        src = torch.randint(0, 256, (n, size), generator=g, dtype=torch.uint8).to(dev())
+    else:
+        src = torch.randn(n, size, generator=g).to(dev())
+    labels = torch.randint(0, 10, (n,), generator=g, dtype=torch.int32).to(dev())
+    idx = torch.randperm(n, generator=g).int().to(dev())
+    mean = torch.randn(size, generator=g).to(dev())
+    rdisp = (torch.rand(size, generator=g) + 0.5).to(dev())
+    H2, W2, C2 = -(-H // sy), -(-W // sx), sy * sx * C
+    xs = torch.full((mb + 2, H2, W2, C2), float("nan"), device=dev(), dtype=torch.bfloat16)
+    mbl = torch.full((mb,), 77, device=dev(), dtype=torch.int32)
+    mbi = torch.full((mb,), 77, device=dev(), dtype=torch.int32)
+    for m_, r_ in ((mean, rdisp), (None, None)):
+        assert k.gather_s2d(src, idx, start, count, xs[:mb], H, W, C, sy, sx, m_, r_, labels, mbl, mbi)
+        sel = idx[start:start + count].long()
+        x = src[sel].float()
+        if m_ is not None:
+            x = (x - mean) * rdisp
+        x = x.reshape(count, H, W, C)
+        pad = torch.zeros(mb, H2 * sy, W2 * sx, C, device=dev())
+        pad[:count, :H, :W] = x
+        ref = pad.reshape(mb, H2, sy, W2, sx, C).permute(0, 1, 3, 2, 4, 5).reshape(mb, H2, W2, C2)
+        got = xs[:mb].float()
+        assert (got - ref).abs().max().item() <= 1e-2 * max(1.0, ref.abs().max().item())
+        assert (got[count:] == 0).all() and torch.equal(got == 0, got == 0)
+        assert (got[ref == 0] == 0).all()                       # padding positions are exact zeros
+        assert torch.isnan(xs[mb:].float()).all(), "kernel wrote past the minibatch"
+        assert (mbl[:count] == labels[sel]).all() and (mbl[count:] == -1).all()
+        assert (mbi[:count] == idx[start:start + count]).all() and (mbi[count:] == -1).all()
+    # the two-kernel path it replaces gives the same bits for bf16-exact inputs
+    if src_dtype == torch.uint8:
+        nhwc = torch.zeros(mb, size, device=dev(), dtype=torch.bfloat16)
+        k.gather_minibatch(src, idx, start, count, nhwc, None, None, None, None, None)
+        xs2 = torch.zeros(mb, H2, W2, C2, device=dev(), dtype=torch.bfloat16)
+        k.space_to_depth(nhwc.view(mb, H, W, C), xs2, sy, sx)
+        assert torch.equal(xs2, xs[:mb])
+
+
+def test_gather_s2d_refuses_uncovered_geometry():
+    k = K()
+    src = torch.zeros(4, 40 * 400 * 3, dtype=torch.uint8, device=dev())
+    idx = torch.arange(4, dtype=torch.int32, device=dev())
+    xs = torch.zeros(4, 10, 100, 48, device=dev(), dtype=torch.bfloat16)
+    assert k.gather_s2d(src, idx, 0, 4, xs, 40, 400, 3, 4, 4) is False      # strip of 4 x 400 x 3 > 3072 elements
+
+
 def test_mean_disp_normalizer():
     k = K()
     g = torch.Generator(device="cpu").manual_seed(4)

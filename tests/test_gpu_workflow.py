@@ -227,3 +227,44 @@ def test_workflow_run_replays_cuda_graphs_and_matches_the_eager_walk():
         assert all(abs(a - b) <= 2 for a, b in zip(x["n_err"], y["n_err"]))
     assert np.abs(a1 - a0).max() <= 1e-3 * max(1.0, np.abs(a0).max())
     assert np.abs(b1 - b0).max() <= 1e-3 * max(1.0, np.abs(b0).max())
+
+
+@pytest.mark.parametrize("streaming", [False, True])
+def test_input_gather_fused_with_space_to_depth_matches_the_two_kernel_path(streaming):
+    """AlexNet's first layer reads its input through a space-to-depth transform; when it is the only reader of the
+    loader's minibatch the loader gathers straight into that layout (``vb_gather_s2d``).  Same losses and weights as
+    with the NHWC minibatch + separate transform, for the resident data set and for minibatches fed from the host."""
+    import torch
+    from veles_b200.backends import B200Device
+    from veles_b200.config import root
+    from veles_b200.trainer import Trainer
+    rng = np.random.default_rng(5)
+    fed = [(rng.integers(0, 256, size=(8, 227, 227, 3), dtype=np.uint8), rng.integers(0, 1000, size=8).astype(np.int32))
+           for _ in range(3)]
+    out = []
+    for fuse in (True, False):
+        root.common.engine.fuse_input_gather = fuse
+        try:
+            tr = Trainer("alexnet", minibatch_size=8, device=B200Device(), use_graph=False, streaming=streaming,
+                         n_train=32, layers_kwargs={"dropout": 0.0})
+            conv1 = tr.wf.forwards[0]
+            sink = tr.wf.loader.__dict__.get("minibatch_sink_")
+            assert (sink is not None) == fuse and (conv1.s2d_.get("sink") is not None) == fuse
+            losses = []
+            for data, labels in fed:
+                if streaming:
+                    losses.append(tr.step(torch.from_numpy(data).pin_memory(), torch.from_numpy(labels).pin_memory()))
+                else:
+                    tr.step_resident()
+                    losses.append(tr.read_loss())
+            assert sink is None or sink["fed"]
+            conv1.weights.map_read()
+            tr.wf.forwards[-1].weights.map_read()
+            out.append((losses, conv1.weights.mem.copy(), tr.wf.forwards[-1].weights.mem.copy()))
+            tr.close()
+        finally:
+            root.common.engine.fuse_input_gather = True
+    (l1, a1, b1), (l0, a0, b0) = out
+    assert np.allclose(l1, l0, rtol=2e-3, atol=1e-4), (l1, l0)
+    assert np.abs(a1 - a0).max() <= 2e-3 * max(1e-3, np.abs(a0).max())
+    assert np.abs(b1 - b0).max() <= 2e-3 * max(1e-3, np.abs(b0).max())

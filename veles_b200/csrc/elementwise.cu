@@ -70,6 +70,93 @@ gather_rows_kernel(const SRC* __restrict__ src, long long src_ld, const int* __r
   }
 }
 
+// ---------------------------------------------------------------------------
+// Minibatch gather FUSED with the first layer's space-to-depth transform: rows picked by shuffled index, cast,
+// (x - mean) * rdisp, and written straight in the [B, ceil(H/sy), ceil(W/sx), sy*sx*C] bf16 layout the strided
+// few-channel convolution reads (AlexNet conv1: 227x227x3 -> 57x57x48).  The plain NHWC minibatch (79 MB per 256
+// images) is then neither written nor read again.
+// One block = one output row h2 of GS2D_ROWS consecutive minibatch rows.  The sy input rows that feed it are contiguous
+// strips of W*C elements: threads read them element by element (coalesced whatever the row alignment - image rows of
+// 3-channel uint8 pixels are 1-byte aligned), GS2D_GROUP minibatch rows at a time so that each thread has 4 x 11
+// loads in flight (one row at a time was latency-bound: 2x slower than the two kernels it replaces).  Each strip
+// element's mean / 1/dispersion and its position in the output strip are tabulated in shared memory once per block;
+// converted values are scattered into shared-memory images of the output strips, which leave as aligned 16-byte
+// vectors.  Positions past the image edge stay zero.
+// ---------------------------------------------------------------------------
+constexpr int GS2D_ROWS = 32;     // minibatch rows per block
+constexpr int GS2D_GROUP = 4;     // rows whose loads are in flight together
+constexpr int GS2D_EPT = 12;      // strip elements per thread: sy * W * C <= 256 * 12
+
+template <typename SRC>
+__global__ void __launch_bounds__(256, 3)
+gather_s2d_kernel(const SRC* __restrict__ src, long long src_ld, const int* __restrict__ indices, int start, int count,
+                  int max_rows, int H, int W, int C, int sy, int sx, int H2, int W2, __nv_bfloat16* __restrict__ xs,
+                  const float* __restrict__ mean, const float* __restrict__ rdisp) {
+  vb::pdl_sync();
+  extern __shared__ __align__(16) unsigned char gs2d_smem[];
+  const int C2 = sy * sx * C;
+  const int out_elems = W2 * C2;                 // one output strip (multiple of 8)
+  const int row_elems = W * C;
+  const int strip_cap = sy * row_elems;
+  // [GROUP output strips][(mean, 1/disp) per strip element][output position per strip element]
+  __nv_bfloat16* obuf = reinterpret_cast<__nv_bfloat16*>(gs2d_smem);
+  float2* md = reinterpret_cast<float2*>(gs2d_smem + static_cast<size_t>(GS2D_GROUP) * out_elems * 2);
+  unsigned short* pos = reinterpret_cast<unsigned short*>(md + strip_cap);
+  const int h2 = blockIdx.x;
+  const int rows_in = min(sy, H - h2 * sy);      // input rows that exist for this strip
+  const int strip = rows_in * row_elems;
+  const long long col0 = static_cast<long long>(h2) * sy * row_elems;   // first feature of the strip
+  for (int e = threadIdx.x; e < strip; e += 256) {
+    const int dy = e / row_elems, rem = e - dy * row_elems;
+    const int w = rem / C, c = rem - w * C;
+    const int w2 = w / sx, dx = w - w2 * sx;
+    pos[e] = static_cast<unsigned short>(w2 * C2 + (dy * sx + dx) * C + c);
+    md[e] = mean != nullptr ? make_float2(__ldg(mean + col0 + e), __ldg(rdisp + col0 + e)) : make_float2(0.0f, 1.0f);
+  }
+  for (int i = threadIdx.x; i < GS2D_GROUP * out_elems; i += 256)      // padding positions are never written again
+    obuf[i] = __float2bfloat16(0.0f);
+  __syncthreads();
+  const int r0 = blockIdx.y * GS2D_ROWS;
+  const int r1 = min(max_rows, r0 + GS2D_ROWS);
+  const int vecs = out_elems >> 3;
+  for (int g0 = r0; g0 < r1; g0 += GS2D_GROUP) {
+    const SRC* srow[GS2D_GROUP];
+#pragma unroll
+    for (int r = 0; r < GS2D_GROUP; ++r) {
+      const int row = g0 + r;
+      srow[r] = (row < r1 && row < count)
+                    ? src + static_cast<long long>(__ldg(indices + start + row)) * src_ld + col0 : nullptr;
+    }
+    SRC v[GS2D_GROUP][GS2D_EPT];
+#pragma unroll
+    for (int r = 0; r < GS2D_GROUP; ++r)
+#pragma unroll
+      for (int i = 0; i < GS2D_EPT; ++i) {
+        const int e = threadIdx.x + 256 * i;
+        if (e < strip && srow[r] != nullptr) v[r][i] = srow[r][e];
+      }
+#pragma unroll
+    for (int i = 0; i < GS2D_EPT; ++i) {
+      const int e = threadIdx.x + 256 * i;
+      if (e < strip) {
+        const float2 t = md[e];
+        const int p = pos[e];
+#pragma unroll
+        for (int r = 0; r < GS2D_GROUP; ++r)
+          obuf[r * out_elems + p] = __float2bfloat16(srow[r] != nullptr ? (to_f<SRC>(v[r][i]) - t.x) * t.y : 0.0f);
+      }
+    }
+    __syncthreads();
+    const int live = min(GS2D_GROUP, r1 - g0);
+    for (int i = threadIdx.x; i < live * vecs; i += 256) {
+      const int r = i / vecs, k = i - r * vecs;
+      reinterpret_cast<uint4*>(xs + (static_cast<long long>(g0 + r) * H2 + h2) * out_elems)[k] =
+          reinterpret_cast<const uint4*>(obuf + r * out_elems)[k];
+    }
+    __syncthreads();
+  }
+}
+
 __global__ void gather_labels_kernel(const int* __restrict__ labels, const int* __restrict__ indices,
                                      int start, int count, int max_rows, int* __restrict__ mb_labels,
                                      int* __restrict__ mb_indices) {
@@ -352,6 +439,56 @@ extern "C" int vb_gather_minibatch(const void* src, int src_dtype, long long src
   if (rc) return rc;
   if (mb_labels || mb_indices) {
     vb::launch_k(gather_labels_kernel, dim3(ceil_div(max_rows, 256)), dim3(256), 0, s, labels, indices, start, count, max_rows, mb_labels, mb_indices);
+    VB_CHECK_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+// Fused gather + space-to-depth (see gather_s2d_kernel).  Returns 1 when the geometry is not covered (run
+// vb_gather_minibatch and vb_space_to_depth instead).  xs: bf16 [max_rows, ceil(H/sy), ceil(W/sx), sy*sx*C], 16-byte
+// aligned; labels / indices are gathered like vb_gather_minibatch does.
+extern "C" int vb_gather_s2d(const void* src, int src_dtype, long long src_ld, const int* indices, int start,
+                             int count, int max_rows, int H, int W, int C, int sy, int sx, void* xs, const float* mean,
+                             const float* rdisp, const int* labels, int* mb_labels, int* mb_indices, cudaStream_t s) {
+  VB_REQUIRE(count >= 0 && count <= max_rows, "vb_gather_s2d: count %d out of [0,%d]", count, max_rows);
+  if (max_rows == 0) return 0;
+  const int C2 = sy * sx * C;
+  const int H2 = (H + sy - 1) / sy, W2 = (W + sx - 1) / sx;
+  // GROUP output strips + (mean, 1/disp) and output position per strip element
+  const long long smem = static_cast<long long>(GS2D_GROUP) * W2 * C2 * 2 + static_cast<long long>(sy) * W * C * 10;
+  if (C2 % 8 != 0 || sy * W * C > 256 * GS2D_EPT || W2 * C2 > 65535 || smem > 96 * 1024 ||
+      (reinterpret_cast<uintptr_t>(xs) & 15) != 0)
+    return 1;
+  if (smem > 48 * 1024) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      VB_CHECK_CUDA(cudaFuncSetAttribute(gather_s2d_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      VB_CHECK_CUDA(cudaFuncSetAttribute(gather_s2d_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      VB_CHECK_CUDA(cudaFuncSetAttribute(gather_s2d_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      attr_set = true;
+    }
+  }
+  dim3 grid(H2, ceil_div(max_rows, GS2D_ROWS));
+  __nv_bfloat16* out = static_cast<__nv_bfloat16*>(xs);
+  switch (src_dtype) {
+    case DT_U8:
+      vb::launch_k(gather_s2d_kernel<uint8_t>, grid, dim3(256), smem, s, static_cast<const uint8_t*>(src), src_ld,
+                   indices, start, count, max_rows, H, W, C, sy, sx, H2, W2, out, mean, rdisp);
+      break;
+    case DT_F32:
+      vb::launch_k(gather_s2d_kernel<float>, grid, dim3(256), smem, s, static_cast<const float*>(src), src_ld, indices,
+                   start, count, max_rows, H, W, C, sy, sx, H2, W2, out, mean, rdisp);
+      break;
+    case DT_BF16:
+      vb::launch_k(gather_s2d_kernel<__nv_bfloat16>, grid, dim3(256), smem, s, static_cast<const __nv_bfloat16*>(src),
+                   src_ld, indices, start, count, max_rows, H, W, C, sy, sx, H2, W2, out, mean, rdisp);
+      break;
+    default: VB_REQUIRE(false, "vb_gather_s2d: unsupported source dtype %d", src_dtype);
+  }
+  VB_CHECK_CUDA(cudaGetLastError());
+  if (mb_labels || mb_indices) {
+    vb::launch_k(gather_labels_kernel, dim3(ceil_div(max_rows, 256)), dim3(256), 0, s, labels, indices, start, count,
+                 max_rows, mb_labels, mb_indices);
     VB_CHECK_CUDA(cudaGetLastError());
   }
   return 0;

@@ -249,11 +249,18 @@ class FullBatchLoader(Loader):
         self.local_count = count
         idx = self._device_indices()
         data2d = self.minibatch_data.devmem
-        kernels.gather_minibatch(
-            self.original_data.devmem, idx, start_offset, count, data2d,
-            self._mean_dev_, self._rdisp_dev_,
-            self._mapped_original_labels_.devmem if self._has_labels else None,
-            self.minibatch_labels.devmem if self._has_labels else None, self.minibatch_indices.devmem)
+        lab = (self._mapped_original_labels_.devmem if self._has_labels else None,
+               self.minibatch_labels.devmem if self._has_labels else None, self.minibatch_indices.devmem)
+        sink = self.__dict__.get("minibatch_sink_")
+        if sink is not None and kernels.gather_s2d(self.original_data.devmem, idx, start_offset, count, sink["xs"],
+                                                   sink["H"], sink["W"], sink["C"], sink["sy"], sink["sx"],
+                                                   self._mean_dev_, self._rdisp_dev_, *lab):
+            sink["fed"] = True     # the consumer finds its rearranged input ready (minibatch_data is not written)
+        else:
+            if sink is not None:
+                sink["fed"] = False
+            kernels.gather_minibatch(self.original_data.devmem, idx, start_offset, count, data2d,
+                                     self._mean_dev_, self._rdisp_dev_, *lab)
         self.minibatch_data.mark_device_written()
         self.minibatch_labels.mark_device_written()
         self.minibatch_indices.mark_device_written()

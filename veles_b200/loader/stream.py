@@ -150,9 +150,18 @@ class StreamLoader(Loader):
         self._minibatch_size_ = count
         self.minibatch_class = self.feed_class
         md = self.minibatch_data.devmem
-        kernels.gather_minibatch(self.staging_[slot], self.identity_, 0, count, md.view(md.shape[0], -1),
-                                 self.mean_dev_, self.rdisp_dev_, self.staging_labels_[slot],
-                                 self.minibatch_labels.devmem, self.minibatch_indices.devmem)
+        sink = self.__dict__.get("minibatch_sink_") if self.targets is None else None
+        if sink is not None and kernels.gather_s2d(self.staging_[slot], self.identity_, 0, count, sink["xs"], sink["H"],
+                                                   sink["W"], sink["C"], sink["sy"], sink["sx"], self.mean_dev_,
+                                                   self.rdisp_dev_, self.staging_labels_[slot],
+                                                   self.minibatch_labels.devmem, self.minibatch_indices.devmem):
+            sink["fed"] = True     # the first convolution finds its rearranged input ready
+        else:
+            if sink is not None:
+                sink["fed"] = False
+            kernels.gather_minibatch(self.staging_[slot], self.identity_, 0, count, md.view(md.shape[0], -1),
+                                     self.mean_dev_, self.rdisp_dev_, self.staging_labels_[slot],
+                                     self.minibatch_labels.devmem, self.minibatch_indices.devmem)
         if self.targets is not None:
             mt = self._minibatch_targets.devmem
             mt2 = mt.view(mt.shape[0], -1)

@@ -403,6 +403,23 @@ def gather_minibatch(src, indices, start, count, dst, mean=None, rdisp=None, lab
     return dst
 
 
+def gather_s2d(src, indices, start, count, xs, H, W, C, sy, sx, mean=None, rdisp=None, labels=None, mb_labels=None,
+               mb_indices=None):
+    """Minibatch gather fused with the first convolution's space-to-depth transform: ``xs`` [rows, ceil(H/sy),
+    ceil(W/sx), sy*sx*C] bf16 receives normalise(cast(src[indices[start+s]])) rearranged; False when the geometry is
+    not covered (nothing was launched)."""
+    src2 = src.reshape(src.shape[0], -1)
+    assert xs.dtype == torch.bfloat16 and xs.is_contiguous() and src2.shape[1] == H * W * C
+    rc = _lib.lib().vb_gather_s2d(_p(src2), c_int(_dt(src2)), c_longlong(src2.stride(0)), _p(indices), c_int(start),
+                                  c_int(count), c_int(xs.shape[0]), c_int(H), c_int(W), c_int(C), c_int(sy), c_int(sx),
+                                  _p(xs), _p(mean), _p(rdisp), _p(labels), _p(mb_labels), _p(mb_indices), _stream())
+    if rc == 1:
+        return False
+    _lib.check(rc, "vb_gather_s2d")
+    LAUNCHES[0] += 2 if (mb_labels is not None or mb_indices is not None) else 1
+    return True
+
+
 def mean_disp_normalize(inp, mean, rdisp, out):
     inp2 = inp.reshape(inp.shape[0], -1)
     rc = _lib.lib().vb_mean_disp_normalize(_p(inp2), c_int(_dt(inp2)), _p(mean), _p(rdisp), _p(out), c_int(_dt(out)),

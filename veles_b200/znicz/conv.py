@@ -18,6 +18,7 @@ from __future__ import annotations
 
 import numpy
 
+from ..config import root, get
 from ..memory import Array
 from .nn_units import Forward, act_forward_numpy
 
@@ -196,6 +197,28 @@ class Conv(Forward):
             w=torch.zeros(self.n_kernels, ky2 * kx2 * C2, dtype=torch.bfloat16, device=dev),
             gw=torch.zeros(self.n_kernels, ky2 * kx2 * C2, dtype=torch.float32, device=dev),
             to_s2d=torch.from_numpy(to_s2d).to(dev), from_s2d=torch.from_numpy(from_s2d).to(dev))
+        self._offer_input_sink(B, H, W, C)
+
+    def _offer_input_sink(self, B, H, W, C):
+        """When this layer is the ONLY reader of the loader's minibatch, the loader gathers straight into the
+        space-to-depth layout (``vb_gather_s2d``): the NHWC minibatch is neither written nor re-read.  Any other unit
+        that holds the same Array (a plotter, an image saver, an MSE evaluator...) keeps the two-kernel path."""
+        if not get(root.common.engine.fuse_input_gather, True):
+            return
+        wf = self.workflow
+        loader = getattr(wf, "loader", None)
+        if loader is None or getattr(loader, "minibatch_data", None) is not self.input:
+            return
+        if self.input.devmem is None or tuple(self.input.shape[1:]) != (H, W, C):
+            return
+        for u in list(getattr(wf, "_units", [])):
+            if u is loader or u is self or getattr(u, "forward", None) is self:
+                continue       # (this layer's GD unit takes its weight gradient from the rearranged input too)
+            if any(v is self.input for v in u.__dict__.values()):
+                return
+        sx, sy = self.sliding
+        loader.minibatch_sink_ = dict(xs=self.s2d_["x"], H=H, W=W, C=C, sy=sy, sx=sx, fed=False, owner=self.name)
+        self.s2d_["sink"] = loader.minibatch_sink_
 
     def ensure_cols(self):
         """The [B*OH*OW, G*ky*kx*Cg] bf16 column matrix (explicit path and strided err_input scratch)."""
@@ -227,7 +250,8 @@ class Conv(Forward):
         bias = self.bias.devmem if self.include_bias else None
         if self.s2d_ is not None:
             sd = self.s2d_
-            kernels.space_to_depth(x, sd["x"], g["sy"], g["sx"])
+            if not (sd.get("sink") is not None and sd["sink"]["fed"]):
+                kernels.space_to_depth(x, sd["x"], g["sy"], g["sx"])
             kernels.gather_cols(self.weights_bf16_, sd["w"], sd["to_s2d"])   # refreshed bf16 weights, s2d order
             if not (kernels.conv_halo_preferred(sd["x"].shape[3], sd["geom"]) and
                     kernels.conv_forward_halo(sd["x"], sd["w"], out2, sd["geom"], bias=bias, act=self.ACTIVATION)):
