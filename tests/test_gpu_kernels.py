@@ -518,7 +518,8 @@ def test_gather_u8_to_bf16_is_exact_for_odd_row_sizes():
 
 
 @pytest.mark.parametrize("src_dtype", [torch.uint8, torch.float32])
-@pytest.mark.parametrize("H,W,C,sy,sx", [(227, 227, 3, 4, 4), (32, 30, 2, 2, 2), (17, 9, 1, 4, 2), (12, 12, 4, 1, 2)])
+@pytest.mark.parametrize("H,W,C,sy,sx", [(227, 227, 3, 4, 4), (32, 30, 2, 2, 2), (17, 9, 1, 4, 2), (12, 12, 4, 1, 2),
+                                         (10, 7, 3, 2, 4), (9, 11, 6, 4, 2), (33, 250, 3, 4, 4)])
 def test_gather_fused_with_space_to_depth(src_dtype, H, W, C, sy, sx):
     """``vb_gather_s2d`` against a plain fp32 restatement: gather by index, normalise, then x[b, h2*sy+dy, w2*sx+dx, c]
     -> xs[b, h2, w2, (dy*sx+dx)*C + c] with zeros past the image edge and for rows past ``count``."""

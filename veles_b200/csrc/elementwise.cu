@@ -78,7 +78,8 @@ gather_rows_kernel(const SRC* __restrict__ src, long long src_ld, const int* __r
 // One block = one output row h2 of GS2D_ROWS consecutive minibatch rows.  The sy input rows that feed it are contiguous
 // strips of W*C elements: threads read them element by element (coalesced whatever the row alignment - image rows of
 // 3-channel uint8 pixels are 1-byte aligned), GS2D_GROUP minibatch rows at a time so that each thread has 4 x 11
-// loads in flight (one row at a time was latency-bound: 2x slower than the two kernels it replaces).  Each strip
+// loads in flight (one row at a time was latency-bound: 2x slower than the two kernels it replaces); uint8 sources are
+// fetched as aligned words, 8 rows at a time.  Each strip
 // element's mean / 1/dispersion and its position in the output strip are tabulated in shared memory once per block;
 // converted values are scattered into shared-memory images of the output strips, which leave as aligned 16-byte
 // vectors.  Positions past the image edge stay zero.
@@ -93,6 +94,7 @@ gather_s2d_kernel(const SRC* __restrict__ src, long long src_ld, const int* __re
                   int max_rows, int H, int W, int C, int sy, int sx, int H2, int W2, __nv_bfloat16* __restrict__ xs,
                   const float* __restrict__ mean, const float* __restrict__ rdisp) {
   vb::pdl_sync();
+  constexpr int GROUP = GS2D_GROUP;
   extern __shared__ __align__(16) unsigned char gs2d_smem[];
   const int C2 = sy * sx * C;
   const int out_elems = W2 * C2;                 // one output strip (multiple of 8)
@@ -100,7 +102,7 @@ gather_s2d_kernel(const SRC* __restrict__ src, long long src_ld, const int* __re
   const int strip_cap = sy * row_elems;
   // [GROUP output strips][(mean, 1/disp) per strip element][output position per strip element]
   __nv_bfloat16* obuf = reinterpret_cast<__nv_bfloat16*>(gs2d_smem);
-  float2* md = reinterpret_cast<float2*>(gs2d_smem + static_cast<size_t>(GS2D_GROUP) * out_elems * 2);
+  float2* md = reinterpret_cast<float2*>(gs2d_smem + static_cast<size_t>(GROUP) * out_elems * 2);
   unsigned short* pos = reinterpret_cast<unsigned short*>(md + strip_cap);
   const int h2 = blockIdx.x;
   const int rows_in = min(sy, H - h2 * sy);      // input rows that exist for this strip
@@ -113,23 +115,23 @@ gather_s2d_kernel(const SRC* __restrict__ src, long long src_ld, const int* __re
     pos[e] = static_cast<unsigned short>(w2 * C2 + (dy * sx + dx) * C + c);
     md[e] = mean != nullptr ? make_float2(__ldg(mean + col0 + e), __ldg(rdisp + col0 + e)) : make_float2(0.0f, 1.0f);
   }
-  for (int i = threadIdx.x; i < GS2D_GROUP * out_elems; i += 256)      // padding positions are never written again
+  for (int i = threadIdx.x; i < GROUP * out_elems; i += 256)      // padding positions are never written again
     obuf[i] = __float2bfloat16(0.0f);
   __syncthreads();
   const int r0 = blockIdx.y * GS2D_ROWS;
   const int r1 = min(max_rows, r0 + GS2D_ROWS);
   const int vecs = out_elems >> 3;
-  for (int g0 = r0; g0 < r1; g0 += GS2D_GROUP) {
-    const SRC* srow[GS2D_GROUP];
+  for (int g0 = r0; g0 < r1; g0 += GROUP) {
+    const SRC* srow[GROUP];
 #pragma unroll
-    for (int r = 0; r < GS2D_GROUP; ++r) {
+    for (int r = 0; r < GROUP; ++r) {
       const int row = g0 + r;
       srow[r] = (row < r1 && row < count)
                     ? src + static_cast<long long>(__ldg(indices + start + row)) * src_ld + col0 : nullptr;
     }
-    SRC v[GS2D_GROUP][GS2D_EPT];
+    SRC v[GROUP][GS2D_EPT];
 #pragma unroll
-    for (int r = 0; r < GS2D_GROUP; ++r)
+    for (int r = 0; r < GROUP; ++r)
 #pragma unroll
       for (int i = 0; i < GS2D_EPT; ++i) {
         const int e = threadIdx.x + 256 * i;
@@ -142,13 +144,110 @@ gather_s2d_kernel(const SRC* __restrict__ src, long long src_ld, const int* __re
         const float2 t = md[e];
         const int p = pos[e];
 #pragma unroll
-        for (int r = 0; r < GS2D_GROUP; ++r)
+        for (int r = 0; r < GROUP; ++r)
           obuf[r * out_elems + p] = __float2bfloat16(srow[r] != nullptr ? (to_f<SRC>(v[r][i]) - t.x) * t.y : 0.0f);
       }
     }
     __syncthreads();
-    const int live = min(GS2D_GROUP, r1 - g0);
+    const int live = min(GROUP, r1 - g0);
     for (int i = threadIdx.x; i < live * vecs; i += 256) {
+      const int r = i / vecs, k = i - r * vecs;
+      reinterpret_cast<uint4*>(xs + (static_cast<long long>(g0 + r) * H2 + h2) * out_elems)[k] =
+          reinterpret_cast<const uint4*>(obuf + r * out_elems)[k];
+    }
+    __syncthreads();
+  }
+}
+
+// The same for uint8 sources whose segments are 12 elements long (sx * C = 12: RGB at stride 4, AlexNet's first
+// layer).  A thread owns one (dy, w2) segment: 12 CONSECUTIVE source bytes that become 12 CONSECUTIVE output
+// elements.  It fetches the (at most four) aligned 32-bit words covering them, shifts the row's misalignment out,
+// and writes the 24 output bytes to the shared strip image with three 8-byte stores (element-wise 2-byte stores at
+// this lane stride of 96 bytes are 8-way bank conflicts: they made the first form of this kernel conversion-bound);
+// mean / 1/dispersion of its 12 features stay in registers for all rows of the block.  A row's last word may reach
+// up to 3 bytes past the strip: inside the source tensor except for its very last word, which the allocator's
+// granularity covers.
+__global__ void __launch_bounds__(256, 3)
+gather_s2d_seg12_kernel(const unsigned char* __restrict__ src, long long src_ld, const int* __restrict__ indices,
+                        int start, int count, int max_rows, int H, int W, int C, int sy, int H2, int W2,
+                        __nv_bfloat16* __restrict__ xs, const float* __restrict__ mean,
+                        const float* __restrict__ rdisp) {
+  vb::pdl_sync();
+  constexpr int GROUP = GS2D_GROUP;
+  constexpr int SEG = 12;
+  extern __shared__ __align__(16) unsigned char gs2d_smem[];
+  const int C2 = sy * SEG;
+  const int out_elems = W2 * C2;
+  const int row_elems = W * C;
+  __nv_bfloat16* obuf = reinterpret_cast<__nv_bfloat16*>(gs2d_smem);
+  const int h2 = blockIdx.x;
+  const int rows_in = min(sy, H - h2 * sy);
+  const long long col0 = static_cast<long long>(h2) * sy * row_elems;
+  const int dy = threadIdx.x / W2, w2 = threadIdx.x - dy * W2;
+  const int e0 = dy * row_elems + w2 * SEG;                        // first strip element of this thread's segment
+  const int n = (dy < rows_in) ? min(SEG, row_elems - w2 * SEG) : 0;   // 0: no segment (or the image ended above)
+  float m[SEG], d[SEG];
+#pragma unroll
+  for (int k = 0; k < SEG; ++k) {
+    m[k] = 0.0f;
+    d[k] = (k < n) ? 1.0f : 0.0f;                                 // past the image edge: (x - 0) * 0 = 0
+    if (k < n && mean != nullptr) {
+      m[k] = __ldg(mean + col0 + e0 + k);
+      d[k] = __ldg(rdisp + col0 + e0 + k);
+    }
+  }
+  for (int i = threadIdx.x; i < GROUP * out_elems; i += 256) obuf[i] = __float2bfloat16(0.0f);
+  __syncthreads();
+  const int r0 = blockIdx.y * GS2D_ROWS;
+  const int r1 = min(max_rows, r0 + GS2D_ROWS);
+  const int vecs = out_elems >> 3;
+  const bool owner = dy < sy;                                      // threads past sy * W2 only help with the stores
+  for (int g0 = r0; g0 < r1; g0 += GROUP) {
+    uint32_t wd[GROUP][4];
+    unsigned sh[GROUP];
+#pragma unroll
+    for (int r = 0; r < GROUP; ++r) {
+      const int row = g0 + r;
+      sh[r] = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) wd[r][j] = 0;
+      if (n > 0 && row < r1 && row < count) {
+        const unsigned char* pb = src + static_cast<long long>(__ldg(indices + start + row)) * src_ld + col0 + e0;
+        const unsigned a = static_cast<unsigned>(reinterpret_cast<uintptr_t>(pb) & 3);
+        const uint32_t* pw = reinterpret_cast<const uint32_t*>(pb - a);
+        const int nw = (static_cast<int>(a) + n + 3) >> 2;
+        sh[r] = a * 8;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (j < nw) wd[r][j] = __ldg(pw + j);
+      }
+    }
+    if (owner) {
+#pragma unroll
+      for (int r = 0; r < GROUP; ++r) {
+        const bool live = (g0 + r < count);
+        uint32_t o[SEG / 2];
+#pragma unroll
+        for (int j = 0; j < SEG / 4; ++j) {
+          const uint32_t word = __funnelshift_r(wd[r][j], wd[r][j + 1], sh[r]);
+          float f[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int k = 4 * j + q;
+            f[q] = live ? (static_cast<float>((word >> (8 * q)) & 0xffu) - m[k]) * d[k] : 0.0f;
+          }
+          o[2 * j] = pack_bf16x2(f[0], f[1]);
+          o[2 * j + 1] = pack_bf16x2(f[2], f[3]);
+        }
+        uint2* dst = reinterpret_cast<uint2*>(obuf + r * out_elems + w2 * C2 + dy * SEG);
+        dst[0] = make_uint2(o[0], o[1]);
+        dst[1] = make_uint2(o[2], o[3]);
+        dst[2] = make_uint2(o[4], o[5]);
+      }
+    }
+    __syncthreads();
+    const int live_rows = min(GROUP, r1 - g0);
+    for (int i = threadIdx.x; i < live_rows * vecs; i += 256) {
       const int r = i / vecs, k = i - r * vecs;
       reinterpret_cast<uint4*>(xs + (static_cast<long long>(g0 + r) * H2 + h2) * out_elems)[k] =
           reinterpret_cast<const uint4*>(obuf + r * out_elems)[k];
@@ -455,7 +554,7 @@ extern "C" int vb_gather_s2d(const void* src, int src_dtype, long long src_ld, c
   const int C2 = sy * sx * C;
   const int H2 = (H + sy - 1) / sy, W2 = (W + sx - 1) / sx;
   // GROUP output strips + (mean, 1/disp) and output position per strip element
-  const long long smem = static_cast<long long>(GS2D_GROUP) * W2 * C2 * 2 + static_cast<long long>(sy) * W * C * 10;
+  long long smem = static_cast<long long>(GS2D_GROUP) * W2 * C2 * 2 + static_cast<long long>(sy) * W * C * 10;
   if (C2 % 8 != 0 || sy * W * C > 256 * GS2D_EPT || W2 * C2 > 65535 || smem > 96 * 1024 ||
       (reinterpret_cast<uintptr_t>(xs) & 15) != 0)
     return 1;
@@ -470,20 +569,27 @@ extern "C" int vb_gather_s2d(const void* src, int src_dtype, long long src_ld, c
   }
   dim3 grid(H2, ceil_div(max_rows, GS2D_ROWS));
   __nv_bfloat16* out = static_cast<__nv_bfloat16*>(xs);
-  switch (src_dtype) {
-    case DT_U8:
-      vb::launch_k(gather_s2d_kernel<uint8_t>, grid, dim3(256), smem, s, static_cast<const uint8_t*>(src), src_ld,
-                   indices, start, count, max_rows, H, W, C, sy, sx, H2, W2, out, mean, rdisp);
-      break;
-    case DT_F32:
-      vb::launch_k(gather_s2d_kernel<float>, grid, dim3(256), smem, s, static_cast<const float*>(src), src_ld, indices,
-                   start, count, max_rows, H, W, C, sy, sx, H2, W2, out, mean, rdisp);
-      break;
-    case DT_BF16:
-      vb::launch_k(gather_s2d_kernel<__nv_bfloat16>, grid, dim3(256), smem, s, static_cast<const __nv_bfloat16*>(src),
-                   src_ld, indices, start, count, max_rows, H, W, C, sy, sx, H2, W2, out, mean, rdisp);
-      break;
-    default: VB_REQUIRE(false, "vb_gather_s2d: unsupported source dtype %d", src_dtype);
+  if (src_dtype == DT_U8 && sx * C == 12 && sy * W2 <= 256) {
+    smem = static_cast<long long>(GS2D_GROUP) * W2 * C2 * 2;
+    vb::launch_k(gather_s2d_seg12_kernel, grid, dim3(256), smem, s, static_cast<const unsigned char*>(src), src_ld,
+                 indices, start, count, max_rows, H, W, C, sy, H2, W2, out, mean, rdisp);
+  } else {
+    switch (src_dtype) {
+      case DT_U8:
+        vb::launch_k(gather_s2d_kernel<uint8_t>, grid, dim3(256), smem, s, static_cast<const uint8_t*>(src), src_ld,
+                     indices, start, count, max_rows, H, W, C, sy, sx, H2, W2, out, mean, rdisp);
+        break;
+      case DT_F32:
+        vb::launch_k(gather_s2d_kernel<float>, grid, dim3(256), smem, s, static_cast<const float*>(src), src_ld,
+                     indices, start, count, max_rows, H, W, C, sy, sx, H2, W2, out, mean, rdisp);
+        break;
+      case DT_BF16:
+        vb::launch_k(gather_s2d_kernel<__nv_bfloat16>, grid, dim3(256), smem, s,
+                     static_cast<const __nv_bfloat16*>(src), src_ld, indices, start, count, max_rows, H, W, C, sy, sx,
+                     H2, W2, out, mean, rdisp);
+        break;
+      default: VB_REQUIRE(false, "vb_gather_s2d: unsupported source dtype %d", src_dtype);
+    }
   }
   VB_CHECK_CUDA(cudaGetLastError());
   if (mb_labels || mb_indices) {

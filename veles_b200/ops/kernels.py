@@ -26,6 +26,7 @@ ACT_CODES = {
 POOL_KINDS = {"max": 0, "maxabs": 1, "avg": 2, "stochastic": 3, "stochastic_abs": 4}
 
 LAUNCHES = [0]
+_BYTES = [None]   # traffic override of the call being traced (gathers touch a slice of their source)
 TRACE = None      # set to a list to record (name, start event, end event, tensor bytes, flops, shapes) per call
 _FLOPS = [0.0]
 
@@ -400,6 +401,8 @@ def gather_minibatch(src, indices, start, count, dst, mean=None, rdisp=None, lab
                                _p(mb_indices), _stream())
     _lib.check(rc, "vb_gather_minibatch")
     LAUNCHES[0] += 2 if (mb_labels is not None or mb_indices is not None) else 1
+    _BYTES[0] = count * src2.shape[1] * src2.element_size() + dst2.numel() * dst2.element_size() + (
+        2 * 4 * src2.shape[1] if mean is not None else 0)
     return dst
 
 
@@ -417,6 +420,8 @@ def gather_s2d(src, indices, start, count, xs, H, W, C, sy, sx, mean=None, rdisp
         return False
     _lib.check(rc, "vb_gather_s2d")
     LAUNCHES[0] += 2 if (mb_labels is not None or mb_indices is not None) else 1
+    _BYTES[0] = count * src2.shape[1] * src2.element_size() + xs.numel() * 2 + (
+        2 * 4 * src2.shape[1] if mean is not None else 0)
     return True
 
 
@@ -705,16 +710,19 @@ def _traced(fn):
         nbytes = sum(t.numel() * t.element_size() for t in tensors)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         _FLOPS[0] = 0.0
+        _BYTES[0] = None
         e0.record()
         r = fn(*a, **kw)
         e1.record()
+        if _BYTES[0] is not None:      # the call knows its traffic better than the sizes of its arguments
+            nbytes = _BYTES[0]
         TRACE.append([fn.__name__, e0, e1, nbytes, _FLOPS[0], [tuple(t.shape) for t in tensors[:3]]])
         return r
     return wrap
 
 
 for _name in ("gemm", "gemm_fused_gd", "bias_act", "gemm_tf32", "conv_forward", "conv_forward_grouped", "conv_err_input_grouped", "conv_forward_halo", "conv_err_input_halo", "conv_err_input", "conv_weight_grad", "space_to_depth", "gather_cols",
-              "gather_minibatch", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
+              "gather_minibatch", "gather_s2d", "lrn_pool_backward", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
               "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",
               "row_sum", "col_sum", "col_sum_gd", "xorshift1024star", "xorshift128plus", "fill_random"):
