@@ -279,6 +279,16 @@ int vb_gather_slices(int world, int rank, int nseg, const long long* segs, float
  * the backward pass.  Read at launch / graph-capture time; returns the previous value. */
 int vb_set_sm_reserve(int n);
 
+/* LRN backward (bf16) that also leaves per-block partial column sums of dx in partials[*blocks_out][C] (fp32, at most
+ * max_blocks rows): the bias gradient of the convolution in front of the LRN, so that layer does not read dx again.
+ * Returns 1 (nothing launched) when the shape has no summing kernel (C % 8, C <= 256, window <= 9). */
+int vb_lrn_backward_colsum(const void* x, const void* dy, void* dx, long long pixels, int C, int n, float alpha,
+                           float beta, float k, int deriv, float* partials, int max_blocks, int* blocks_out,
+                           cudaStream_t stream);
+/* Second phase of the column-sum kernels alone: grad[c] (+)= sum of `slabs` partial rows; with w / vel the momentum
+ * GD step of that bias is applied instead and grad is left zeroed. */
+int vb_col_sum_finish(const float* scratch, int slabs, int cols, float* grad, int accumulate, float* w, float* vel,
+                      float lr, float wd, float l1_vs_l2, float moment, cudaStream_t stream);
 /* Max-pooling backward (3x3 / stride 2, byte argmax) fused into LRN backward (bf16 NHWC): the dense gradient of the
  * LRN output is neither written nor read.  Returns 1 when the geometry is not covered (run the two kernels). */
 int vb_lrn_pool_backward(const void* x, const void* dpool, const unsigned char* offs8, void* dx, int B, int H, int W,

@@ -822,6 +822,48 @@ def test_lrn_vector_paths(C, n):
     assert rel_err(dx, xr.grad * (x > 0).double()) < 2e-2
 
 
+@pytest.mark.parametrize("B,H,W,C,n,deriv", [(3, 13, 13, 96, 5, 4), (8, 27, 27, 256, 5, 4), (2, 8, 9, 40, 3, 0),
+                                              (1, 7, 7, 8, 9, 4), (64, 20, 20, 96, 5, 4)])
+def test_lrn_backward_accumulates_bias_column_sums(B, H, W, C, n, deriv):
+    """LRN backward with ``partials``: same dx as without, plus per-block partial column sums of dx that
+    ``col_sum_finish`` folds into the bias gradient of the convolution in front (plain accumulate, and with the fused
+    momentum step), against an fp32 sum of the stored dx."""
+    k = K()
+    torch.manual_seed(B + H + C)
+    alpha, beta, kk = 0.3, 0.75, 1.5
+    x = torch.randn(B, H, W, C, device=dev()).bfloat16()
+    dy = torch.randn_like(x)
+    dx_ref = torch.empty_like(x)
+    k.lrn_backward(x, dy, dx_ref, n, alpha, beta, kk, deriv=deriv)
+    dx = torch.full((B * H * W + 2, C), float("nan"), device=dev(), dtype=torch.bfloat16)
+    for rows in (1184, 3):                         # few rows: the grid shrinks to what the scratch holds
+        partials = torch.full((rows + 1, C), float("nan"), device=dev())
+        slabs = k.lrn_backward(x, dy, dx[:B * H * W].view_as(x), n, alpha, beta, kk, deriv=deriv,
+                               partials=partials[:rows])
+        assert slabs is not None and 1 <= slabs <= rows
+        assert torch.equal(dx[:B * H * W].view_as(x), dx_ref)
+        assert torch.isnan(dx[B * H * W:].float()).all() and torch.isnan(partials[slabs:]).all()
+        colsum = dx_ref.float().reshape(-1, C).sum(0)
+        # the kernel sums the fp32 values before they are rounded to bf16: allow the rounding of B*H*W terms
+        tol = 2e-3 * dx_ref.float().abs().reshape(-1, C).sum(0).max().item() + 1e-3
+        grad = torch.ones(C, device=dev())
+        k.col_sum_finish(partials, slabs, grad)
+        assert (grad - (1.0 + colsum)).abs().max().item() < tol
+        w = torch.randn(C, device=dev())
+        vel = torch.randn(C, device=dev()) * 0.1
+        w0, v0 = w.clone(), vel.clone()
+        grad = torch.full((C,), 0.5, device=dev())
+        k.col_sum_finish(partials, slabs, grad, w, vel, lr=0.01, wd=0.1, l1_vs_l2=0.0, moment=0.9)
+        g = 0.5 + colsum + 0.1 * w0
+        v1 = 0.9 * v0 - 0.01 * g
+        assert (vel - v1).abs().max().item() < 0.01 * tol + 1e-6 and (w - (w0 + v1)).abs().max().item() < 0.01 * tol + 1e-6
+        assert (grad == 0).all()
+    # shapes without a summing kernel report it and launch nothing
+    xw = torch.randn(2, 3, 3, 264, device=dev()).bfloat16()
+    assert k.lrn_backward(xw, torch.randn_like(xw), torch.empty_like(xw), 5, alpha, beta, kk,
+                          partials=torch.zeros(8, 264, device=dev())) is None
+
+
 @pytest.mark.parametrize("B,H,W,C,n", [(3, 13, 13, 96, 5), (2, 27, 27, 256, 5), (2, 8, 9, 40, 3), (1, 7, 7, 8, 9)])
 def test_pool_backward_fused_into_lrn_backward(B, H, W, C, n):
     """One kernel = max-pooling backward (3x3 / 2, byte argmax) followed by LRN backward with the strict-ReLU

@@ -268,3 +268,41 @@ def test_input_gather_fused_with_space_to_depth_matches_the_two_kernel_path(stre
     assert np.allclose(l1, l0, rtol=2e-3, atol=1e-4), (l1, l0)
     assert np.abs(a1 - a0).max() <= 2e-3 * max(1e-3, np.abs(a0).max())
     assert np.abs(b1 - b0).max() <= 2e-3 * max(1e-3, np.abs(b0).max())
+
+
+def test_bias_gradient_summed_by_lrn_backward_matches_the_column_sum_pass():
+    """conv -> LRN: the LRN backward kernel accumulates the convolution's bias gradient while it writes that layer's
+    err_output (StandardWorkflow._plan_bias_sum_fusion).  Same biases, momenta and losses as with the separate
+    column-sum pass."""
+    from veles_b200.backends import B200Device
+    from veles_b200.config import root
+    from veles_b200.trainer import Trainer
+    out = []
+    for fuse in (True, False):
+        root.common.engine.fuse_bias_sum = fuse
+        try:
+            tr = Trainer("alexnet", minibatch_size=8, device=B200Device(), use_graph=False, n_train=32,
+                         layers_kwargs={"dropout": 0.0})
+            planned = [g.name for g in tr.wf.gds if getattr(g, "bias_sum_for", None) is not None]
+            assert (len(planned) == 2) == fuse, planned          # norm1 and norm2
+            losses = []
+            for _ in range(4):
+                tr.step_resident()
+                losses.append(tr.read_loss())
+            state = []
+            for f, g in zip(tr.wf.forwards[:4], tr.wf.gds[:4]):
+                if getattr(f, "HAS_WEIGHTS", False):
+                    f.bias.map_read()
+                    g.gradient_bias_with_moment.map_read()
+                    state.append((f.bias.mem.copy(), g.gradient_bias_with_moment.mem.copy()))
+            out.append((losses, state))
+            tr.close()
+        finally:
+            root.common.engine.fuse_bias_sum = True
+    (l1, s1), (l0, s0) = out
+    assert np.allclose(l1, l0, rtol=2e-3, atol=1e-4), (l1, l0)
+    assert len(s1) == len(s0) >= 2
+    for (b1, v1), (b0, v0) in zip(s1, s0):
+        assert np.abs(v0).max() > 0
+        assert np.abs(b1 - b0).max() <= 1e-2 * np.abs(b0 - b0.mean()).max() + 1e-2 * np.abs(v0).max()
+        assert np.abs(v1 - v0).max() <= 2e-2 * np.abs(v0).max()

@@ -761,12 +761,29 @@ lrn_forward_shfl_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __re
   }
 }
 
-template <int HALF, bool B34>
-__global__ void __launch_bounds__(256)
+template <int HALF, bool B34, bool COLSUM>
+__global__ void __launch_bounds__(256, 4)      // 4 blocks per SM with or without the 8 column accumulators
 lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                          __nv_bfloat16* __restrict__ dx, long long pixels, int C, float alpha, float beta, float k,
-                         int deriv) {
+                         int deriv, float* __restrict__ colsum) {
   vb::pdl_sync();
+  // colsum (optional, [gridDim.x][C] fp32 partial rows, one per block): per-channel sums of dx - the bias gradient of
+  // the convolution whose output this LRN normalises (dx IS that layer's err_output), so that layer does not read dx
+  // again for it.  A lane keeps the same 8 channels for every pixel it visits: 8 adds per pixel in registers, one
+  // shared-memory reduction per block, one plain row store per block; the second phase of the column-sum kernels
+  // (vb_col_sum_finish) folds the rows.  (Global atomics from every block on the same C addresses cost more than the
+  // column-sum pass they replaced: +36 us on AlexNet norm1.)
+  // the running sums live in shared memory, 8 floats per thread touched with 16-byte accesses: as registers they pushed
+  // the kernel from 4 to 3 resident blocks per SM (or into spills), +10-30 % on its run time
+  __shared__ float bsum[256];
+  __shared__ __align__(16) float bacc_s[COLSUM ? 256 * 8 : 8];
+  float4* bacc = reinterpret_cast<float4*>(bacc_s + (COLSUM ? threadIdx.x * 8 : 0));
+  if (COLSUM) {
+    bacc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    bacc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = threadIdx.x; i < C; i += blockDim.x) bsum[i] = 0.0f;
+    __syncthreads();
+  }
   const int T = C >> 3;
   const int ppw = 32 / T;
   const int lane = threadIdx.x & 31;
@@ -815,7 +832,27 @@ lrn_backward_shfl_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
 #pragma unroll
       for (int q = 0; q < 8; ++q) out[q] *= act_deriv_from_output(deriv, xv[q]);
     }
-    if (active) *reinterpret_cast<uint4*>(dx + px * C + g * 8) = pack8(out);
+    if (active) {
+      *reinterpret_cast<uint4*>(dx + px * C + g * 8) = pack8(out);
+      if (COLSUM) {
+        float4 a0 = bacc[0], a1 = bacc[1];
+        a0.x += out[0]; a0.y += out[1]; a0.z += out[2]; a0.w += out[3];
+        a1.x += out[4]; a1.y += out[5]; a1.z += out[6]; a1.w += out[7];
+        bacc[0] = a0;
+        bacc[1] = a1;
+      }
+    }
+  }
+  if (COLSUM) {
+    if (active_lane) {
+      const float4 a0 = bacc[0], a1 = bacc[1];
+      atomicAdd(&bsum[g * 8 + 0], a0.x); atomicAdd(&bsum[g * 8 + 1], a0.y);
+      atomicAdd(&bsum[g * 8 + 2], a0.z); atomicAdd(&bsum[g * 8 + 3], a0.w);
+      atomicAdd(&bsum[g * 8 + 4], a1.x); atomicAdd(&bsum[g * 8 + 5], a1.y);
+      atomicAdd(&bsum[g * 8 + 6], a1.z); atomicAdd(&bsum[g * 8 + 7], a1.w);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < C; i += blockDim.x) colsum[static_cast<long long>(blockIdx.x) * C + i] = bsum[i];
   }
 }
 
@@ -1095,8 +1132,9 @@ int fast_lrn_forward(const void* x, void* y, long long pixels, int C, int n, flo
 }
 
 int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels, int C, int n, float alpha, float beta,
-                      float k, int deriv, cudaStream_t s) {
+                      float k, int deriv, cudaStream_t s, float* colsum, int max_blocks, int* blocks_out) {
   const int half = n / 2;
+  if (colsum != nullptr && !(C % 8 == 0 && C <= 256 && half >= 1 && half <= 4)) return 0;   // only the lane-per-8-channels form sums
   if (C % 8 == 0 && half >= 1 && half <= 4 && !(reinterpret_cast<uintptr_t>(x) & 15) &&
       !(reinterpret_cast<uintptr_t>(dy) & 15) && !(reinterpret_cast<uintptr_t>(dx) & 15)) {
     const long long total = pixels * (C >> 3);
@@ -1107,10 +1145,18 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
     __nv_bfloat16* op = static_cast<__nv_bfloat16*>(dx);
     if (C <= 256) {
       const int ppw = 32 / (C >> 3);
-      const int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
+      int g2 = grid_cap2(((pixels + ppw - 1) / ppw) * 32, 256);
+      if (colsum != nullptr) {                       // one partial row per block
+        if (g2 > device_sm_count() * 4) g2 = device_sm_count() * 4;        // the four resident blocks per SM: one wave
+        if (g2 > max_blocks) g2 = max_blocks;
+        if (g2 < 1) return 0;
+        if (blocks_out) *blocks_out = g2;
+      }
+#define VB_LRN_B2(H_, B_)                                                                                                \
+  if (colsum != nullptr) vb::launch_k(lrn_backward_shfl_kernel<H_, B_, true>, dim3(g2), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv, colsum);   \
+  else vb::launch_k(lrn_backward_shfl_kernel<H_, B_, false>, dim3(g2), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv, colsum)
 #define VB_LRN_B(H_)                                                                                                     \
-  if (beta == 0.75f) vb::launch_k(lrn_backward_shfl_kernel<H_, true>, dim3(g2), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv);   \
-  else vb::launch_k(lrn_backward_shfl_kernel<H_, false>, dim3(g2), dim3(256), 0, s, xp, dp, op, pixels, C, alpha, beta, k, deriv)
+  if (beta == 0.75f) { VB_LRN_B2(H_, true); } else { VB_LRN_B2(H_, false); }
       switch (half) {
         case 1: VB_LRN_B(1); break;
         case 2: VB_LRN_B(2); break;
@@ -1118,6 +1164,7 @@ int fast_lrn_backward(const void* x, const void* dy, void* dx, long long pixels,
         default: VB_LRN_B(4); break;
       }
 #undef VB_LRN_B
+#undef VB_LRN_B2
       VB_CHECK_CUDA(cudaGetLastError());
       return 1;
     }

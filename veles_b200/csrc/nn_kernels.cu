@@ -766,6 +766,32 @@ extern "C" int vb_lrn_backward_fused(const void* x, const void* dy, void* dx, in
   return 0;
 }
 
+// LRN backward that also leaves the per-channel sums of dx as partial rows partials[blocks][C] (fp32; *blocks_out rows,
+// at most max_blocks): the bias gradient of the convolution in front of the LRN, to be folded by vb_col_sum_finish.
+// bf16 only; returns 1 when the shape is not covered (run vb_lrn_backward_fused and a column sum instead), 0 on
+// success.
+extern "C" int vb_lrn_backward_colsum(const void* x, const void* dy, void* dx, long long pixels, int C, int n,
+                                      float alpha, float beta, float k, int deriv, float* partials, int max_blocks,
+                                      int* blocks_out, cudaStream_t s) {
+  VB_REQUIRE(partials != nullptr && blocks_out != nullptr && max_blocks >= 1, "vb_lrn_backward_colsum: no room for partial sums");
+  *blocks_out = 0;
+  if (pixels * C == 0) return 0;
+  const int fr = fast_lrn_backward(x, dy, dx, pixels, C, n, alpha, beta, k, deriv, s, partials, max_blocks, blocks_out);
+  return fr < 0 ? fr : (fr == 0 ? 1 : 0);
+}
+
+// Second phase of the column-sum kernels on its own: grad[c] (+)= sum over `slabs` partial rows of scratch[slab][c];
+// with w / vel given, the momentum GD step of the bias is applied instead and grad is left zeroed (vb_col_sum_gd).
+extern "C" int vb_col_sum_finish(const float* scratch, int slabs, int cols, float* grad, int accumulate, float* w,
+                                 float* vel, float lr, float wd, float l1_vs_l2, float moment, cudaStream_t s) {
+  VB_REQUIRE(scratch != nullptr && grad != nullptr && slabs >= 0 && cols >= 1, "vb_col_sum_finish: bad arguments");
+  VB_REQUIRE((w == nullptr) == (vel == nullptr), "vb_col_sum_finish: w and vel go together");
+  ColSumGD gd{w, vel, lr, wd, l1_vs_l2, moment};
+  vb::launch_k(col_sum_final_kernel, dim3(ceil_div(cols, 8)), dim3(256), 0, s, scratch, slabs, cols, grad, 1.0f, accumulate, gd);
+  VB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // Max-pooling backward fused into LRN backward (bf16 NHWC; 3x3 / stride 2 max pooling over the LRN output):
 //   dx = LRN'(x) applied to the pooling gradient scattered by the argmax bytes, optionally times f'(x).
 // x, dx: [B, H, W, C]; dpool, offs8: [B, OH, OW, C].  Returns 1 when the geometry is not supported (run the two

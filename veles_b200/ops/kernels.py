@@ -588,9 +588,25 @@ def lrn_forward(x, y, n, alpha, beta, k):
     return y
 
 
-def lrn_backward(x, dy, dx, n, alpha, beta, k, deriv=0):
-    """LRN backward; ``deriv`` folds in f'(x) of the activation that produced x."""
+def lrn_backward(x, dy, dx, n, alpha, beta, k, deriv=0, partials=None):
+    """LRN backward; ``deriv`` folds in f'(x) of the activation that produced x.  ``partials`` ([rows, C] fp32 scratch):
+    the kernel also leaves per-block partial sums of dx's columns there (the bias gradient of the convolution that
+    produced x; fold them with :func:`col_sum_finish`) and the number of rows written is returned - or None when the
+    shape's kernel cannot produce them (nothing launched).  Without ``partials`` returns dx."""
     C = x.shape[-1]
+    if partials is not None:
+        if x.dtype != torch.bfloat16:
+            return None
+        assert partials.dtype == torch.float32 and partials.dim() == 2 and partials.shape[1] == C
+        blocks = c_int(0)
+        rc = _lib.lib().vb_lrn_backward_colsum(_p(x), _p(dy), _p(dx), c_longlong(x.numel() // C), c_int(C), c_int(n),
+                                               c_float(alpha), c_float(beta), c_float(k), c_int(deriv), _p(partials),
+                                               c_int(partials.shape[0]), ctypes.byref(blocks), _stream())
+        if rc == 1:
+            return None
+        _lib.check(rc, "vb_lrn_backward_colsum")
+        LAUNCHES[0] += 1
+        return blocks.value
     rc = _lib.lib().vb_lrn_backward_fused(_p(x), _p(dy), _p(dx), c_int(_dt(x)), c_longlong(x.numel() // C), c_int(C),
                                           c_int(n), c_float(alpha), c_float(beta), c_float(k), c_int(deriv),
                                           _stream())
@@ -673,6 +689,19 @@ def col_sum_gd(a, grad, scratch, w, vel, *, lr, wd=0.0, l1_vs_l2=0.0, moment=0.0
     return w
 
 
+def col_sum_finish(partials, slabs, grad, w=None, vel=None, *, lr=0.0, wd=0.0, l1_vs_l2=0.0, moment=0.0,
+                   accumulate=True):
+    """grad (+)= column sums of ``partials[:slabs]``; with ``w`` / ``vel`` the momentum GD step of that bias is applied
+    instead and ``grad`` is left zeroed (the second phase of :func:`col_sum_gd` on its own)."""
+    assert partials.dtype == torch.float32 and grad.dtype == torch.float32 and partials.shape[1] == grad.numel()
+    rc = _lib.lib().vb_col_sum_finish(_p(partials), c_int(slabs), c_int(grad.numel()), _p(grad), c_int(int(accumulate)),
+                                      _p(w), _p(vel), c_float(lr), c_float(wd), c_float(l1_vs_l2), c_float(moment),
+                                      _stream())
+    _lib.check(rc, "vb_col_sum_finish")
+    LAUNCHES[0] += 1
+    return grad
+
+
 def xorshift1024star(states, rounds, out):
     n_states = states.numel() // 16
     rc = _lib.lib().vb_xorshift1024star(_p(states), c_int(n_states), c_int(rounds), _p(out), _stream())
@@ -725,7 +754,7 @@ for _name in ("gemm", "gemm_fused_gd", "bias_act", "gemm_tf32", "conv_forward", 
               "gather_minibatch", "gather_s2d", "lrn_pool_backward", "mean_disp_normalize", "copy_2d", "activation_forward", "activation_backward",
               "dropout", "gd_update", "cast", "im2col", "col2im", "pool_forward", "pool_backward", "pool_forward_local",
               "pool_backward_local", "pool_expand_offsets", "lrn_forward", "lrn_backward", "softmax_eval", "mse_eval",
-              "row_sum", "col_sum", "col_sum_gd", "xorshift1024star", "xorshift128plus", "fill_random"):
+              "row_sum", "col_sum", "col_sum_gd", "col_sum_finish", "xorshift1024star", "xorshift128plus", "fill_random"):
     globals()[_name] = _traced(globals()[_name])
 
 

@@ -148,7 +148,12 @@ class GradientDescentConv(GradientDescentBase):
                              accumulate=True, split_k=0)
         self.gradient_weights.mark_device_written()
         if self.bias is not None and self.bias:
-            self.device_bias_sum(eo2, gb_t)
+            if self.__dict__.get("bias_partials_") is not None:
+                # the unit that produced err_output left per-block column sums of it
+                self.device_bias_from_partials(gb_t, *self.bias_partials_)
+                self.bias_partials_ = None
+            else:
+                self.device_bias_sum(eo2, gb_t)
         if self.need_err_input:
             ei = self.err_input.devmem
             ei4 = ei.reshape(f.in_shape4) if tuple(ei.shape) != tuple(f.in_shape4) else ei

@@ -559,6 +559,27 @@ class GradientDescentBase(GDBase):
             self.gradient_bias.mark_device_written()
         self.bias_updated_ = fuse
 
+    def device_bias_from_partials(self, gb_t, partials, slabs):
+        """The bias gradient arrives as ``slabs`` partial rows (written by the kernel that produced err_output): the
+        second phase of the column-sum kernels folds them, and applies the bias step where :meth:`device_bias_sum`
+        would have fused it (leaving the gradient buffer zeroed like it does)."""
+        from ..ops import kernels
+        fuse = (self.apply_gradient and self.dp_group_ is None and self.solver_code == 0
+                and not self.accumulate_gradient and self.gradient_bias_with_moment
+                and self.gradient_bias_with_moment.devmem is not None
+                and get(root.common.engine.fuse_bias_update, True))
+        if fuse:
+            lr_b, mom_b = self.eff(self.learning_rate_bias, self.gradient_moment_bias)
+            kernels.col_sum_finish(partials, slabs, gb_t.view(-1), self.bias.devmem.view(-1),
+                                   self.gradient_bias_with_moment.devmem.view(-1), lr=lr_b, wd=self.weights_decay_bias,
+                                   l1_vs_l2=self.l1_vs_l2_bias, moment=mom_b)
+            self.bias.mark_device_written()
+            self.gradient_bias_with_moment.mark_device_written()
+        else:
+            kernels.col_sum_finish(partials, slabs, gb_t.view(-1))
+            self.gradient_bias.mark_device_written()
+        self.bias_updated_ = fuse
+
     def device_ortho(self):
         """Device form of :meth:`ortho_term`: adds the regulariser to the weight gradient of this step (column sums of
         the fp32 master, then one element-wise pass).  In a data-parallel group the exchanged gradients are summed,

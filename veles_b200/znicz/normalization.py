@@ -69,6 +69,9 @@ class LRNormalizerBackward(GDBase):
         super(LRNormalizerBackward, self).__init__(workflow, **kwargs)
         self.demand("input")
         self.pool_gd = None      # backward unit of the max pooling layer that follows (StandardWorkflow fusion plan)
+        # GD unit of the convolution in front of this LRN whose bias gradient (= column sums of this unit's err_input)
+        # is accumulated by the LRN backward kernel itself (StandardWorkflow._plan_bias_sum_fusion)
+        self.bias_sum_for = None
 
     def initialize(self, device=None, **kwargs):
         if self.err_output is None or not self.err_output or self.input is None or not self.input:
@@ -111,9 +114,23 @@ class LRNormalizerBackward(GDBase):
                                              f.n, f.alpha, f.beta, f.k, deriv=self.prev_activation):
                 raise RuntimeError("%s: fused pooling + LRN backward refused a geometry its planner accepted" % self.name)
             self.err_input.mark_device_written()
+            if self.bias_sum_for is not None:
+                self.bias_sum_for.bias_partials_ = None
             return
         eo = self.err_output.devmem
         if eo.dtype != x.dtype or not eo.is_contiguous():
             eo = eo.contiguous().to(x.dtype)
-        kernels.lrn_backward(x, eo.view(x.shape), ei, f.n, f.alpha, f.beta, f.k, deriv=self.prev_activation)
+        tgt = self.bias_sum_for
+        done = None
+        if tgt is not None:
+            import torch
+            C = x.shape[-1]
+            if getattr(self, "bias_partials_", None) is None:
+                self.bias_partials_ = torch.zeros(max(1, self.device_.device_info.sm_count) * 4, C, dtype=torch.float32, device=x.device)
+            done = kernels.lrn_backward(x, eo.view(x.shape), ei, f.n, f.alpha, f.beta, f.k,
+                                        deriv=self.prev_activation, partials=self.bias_partials_)
+            # the convolution's GD unit folds the rows (and applies its bias step) instead of summing err_output
+            tgt.bias_partials_ = (self.bias_partials_, done) if done is not None else None
+        if done is None:
+            kernels.lrn_backward(x, eo.view(x.shape), ei, f.n, f.alpha, f.beta, f.k, deriv=self.prev_activation)
         self.err_input.mark_device_written()

@@ -403,6 +403,7 @@ class StandardWorkflow(StandardWorkflowBase):
         if self.fuse_derivatives:
             self._plan_derivative_fusion()
         self._plan_lrn_pool_fusion()
+        self._plan_bias_sum_fusion()
         return self.gds[0]
 
     def _plan_lrn_pool_fusion(self):
@@ -420,6 +421,25 @@ class StandardWorkflow(StandardWorkflowBase):
                     and gd.need_err_input):
                 gd.pool_gd = gd_pool
                 gd_pool.lrn_consumer = gd
+
+    def _plan_bias_sum_fusion(self):
+        """conv -> LRN: the LRN backward kernel writes the convolution's err_output; it also accumulates its column
+        sums (= the convolution's bias gradient), so the convolution's GD unit does not read that tensor again.
+        Needs the derivative of the convolution's activation to be applied by the LRN unit (or to be absent)."""
+        from .gd_conv import GradientDescentConv
+        from .normalization import LRNormalizerBackward
+        if not get(root.common.engine.fuse_bias_sum, True):
+            return
+        for i in range(1, len(self.forwards)):
+            prev_f, gd, prev_gd = self.forwards[i - 1], self.gds[i], self.gds[i - 1]
+            if not (isinstance(gd, LRNormalizerBackward) and isinstance(prev_gd, GradientDescentConv)):
+                continue
+            if not gd.need_err_input or not getattr(prev_f, "include_bias", True):
+                continue
+            act = getattr(prev_f, "ACTIVATION", 0)
+            if act and not (gd.prev_activation == act and getattr(prev_gd, "derivative_applied", False)):
+                continue
+            gd.bias_sum_for = prev_gd
 
     def _plan_derivative_fusion(self):
         """gd[i] multiplies its err_input by f'_{i-1}(input) when forward[i-1] has an activation that
