@@ -98,6 +98,15 @@ class Trainer(object):
             heartbeat()
         return self.read_loss()
 
+    def _loss_denominator(self):
+        """Samples behind the evaluator's loss sum on THIS rank (the resident loader serves global minibatches and
+        materialises this rank's share)."""
+        loader = self.wf.loader
+        n = max(1, loader.minibatch_size)
+        if not self.streaming and self.world > 1:
+            n = max(1, int(getattr(loader, "local_minibatch_size", 0)) or n // self.world)
+        return n
+
     def read_loss(self):
         import torch
         ev = self.wf.evaluator
@@ -105,12 +114,12 @@ class Trainer(object):
             src = ev.loss_sum if hasattr(ev, "loss_sum") else ev.metrics
             val = float(src.mem[0])
             src.mem[0] = 0
-            return val / max(1, self.wf.loader.minibatch_size)
+            return val / self._loss_denominator()
         src = ev.loss_sum.devmem if hasattr(ev, "loss_sum") else ev.metrics.devmem[:1]
         self._loss_host.copy_(src, non_blocking=True)
         src.zero_()
         torch.cuda.current_stream().synchronize()
-        return float(self._loss_host[0]) / max(1, self.wf.loader.minibatch_size)
+        return float(self._loss_host[0]) / self._loss_denominator()
 
     def close(self):
         self.wf.launcher.stop()
