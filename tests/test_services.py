@@ -178,8 +178,20 @@ def test_graphics_server_publishes_to_client(tmp_path):
             if path:
                 break
         assert path and os.path.dirname(path) == str(tmp_path)
+        # the browser view: index.html names the newest file of the plotter and reloads itself
+        index = (tmp_path / "index.html").read_text()
+        assert "http-equiv='refresh'" in index and os.path.basename(path) in index and "remote" in index
+        report = client.write_report(str(tmp_path / "all.html"))
+        assert "<svg" in open(report).read() and "<h3>remote</h3>" in open(report).read()
+        assert not client.finished
     finally:
         srv.shutdown()
+    # the server's goodbye ends the client's loop
+    for _ in range(10):
+        client.poll_once(200)
+        if client.finished:
+            break
+    assert client.finished
 
 
 def test_forge_roundtrip(tmp_path):

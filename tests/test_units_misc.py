@@ -157,3 +157,23 @@ def test_shell_unit_is_inert_without_a_terminal():
     sh.enabled = False
     assert sh.run() is None
     assert "workflow" in Shell.BANNER
+
+
+def test_shell_key_poll_and_scripted_console():
+    """An ``i`` typed while the workflow runs opens the console (reference: interaction.py:84-95); the console sees the
+    workflow and can change it."""
+    import os
+    from veles_b200.dummy import DummyWorkflow
+    from veles_b200.interaction import Shell
+    wf = DummyWorkflow()
+    sh = Shell(wf)
+    r, w = os.pipe()
+    with os.fdopen(r, "r") as rf:
+        assert Shell.poll_key(rf) == ""                  # nothing typed: returns at once
+        os.write(w, b"i\n")
+        assert Shell.poll_key(rf) == "i"
+        os.write(w, b"x\n")
+        assert Shell.poll_key(rf) == "x"
+        os.close(w)
+    ns = sh.interact({"extra": 5}, stdin=["workflow.visited_by_shell = extra + len(units)\n", "y = root.common.engine\n"])
+    assert wf.visited_by_shell == 5 + len(wf.units) and sh.entered == 1 and "y" in ns

@@ -83,5 +83,9 @@ class GraphicsServer(Logger):
     def shutdown(self):
         self._stop.set()
         if self._sock is not None:
+            try:     # tell remote clients that the stream is over (the reference pickles None for that too)
+                self._sock.send_multipart([b"graphics", zlib.compress(pickle.dumps(None), 1)])
+            except Exception:  # noqa: BLE001
+                pass
             self._sock.close()
         GraphicsServer._instance = None
