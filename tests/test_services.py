@@ -115,6 +115,43 @@ def test_launcher_status_heartbeat_payload():
     assert st["mode"] == "standalone" and st["graph"].startswith("digraph") and st["name"] == wf.name
 
 
+def test_forge_keeps_a_git_history_of_every_model(tmp_path):
+    """Every upload is a tagged commit in the model's git repository on the server (reference:
+    forge_server.py:462-560): history and version-to-version diffs come from it."""
+    import shutil
+    if shutil.which("git") is None:
+        pytest.skip("no git executable")
+    from veles_b200.forge.forge_client import ForgeClient
+    from veles_b200.forge.forge_server import ForgeServer
+    model = tmp_path / "model"
+    model.mkdir()
+    (model / "wf.py").write_text("def run(load, main): pass\n")
+    (model / "cfg.py").write_text("# config\n")
+    manifest = {"name": "hist", "workflow": "wf.py", "configuration": "cfg.py", "short_description": "first cut",
+                "long_description": "x", "author": "tester"}
+    (model / "manifest.json").write_text(json.dumps(manifest))
+    srv = ForgeServer(str(tmp_path / "store")).start()
+    try:
+        c = ForgeClient(srv.url)
+        c.register("me@example.com")
+        c.upload(str(model))
+        (model / "cfg.py").write_text("# config\nroot.x = 1\n")
+        (model / "extra.txt").write_text("notes\n")
+        (model / "manifest.json").write_text(json.dumps(dict(manifest, short_description="second cut",
+                                                             files=["extra.txt"])))
+        c.upload(str(model))
+        h = c.history("hist")
+        assert [e["version"] for e in h] == ["v2", "v1"]
+        assert h[0]["subject"] == "v2: second cut" and h[1]["author"] == "tester <me@example.com>"
+        assert c.details("hist")["history"][0]["commit"] == h[0]["commit"]
+        d = c.diff("hist", "v1", "v2")
+        assert "cfg.py" in d and "extra.txt" in d and "wf.py" not in d
+        with pytest.raises(urllib.error.HTTPError):
+            c.diff("hist", "v1", "v9")
+    finally:
+        srv.stop()
+
+
 def test_plotters_and_publisher(tmp_path):
     from veles_b200.backends import NumpyDevice
     from veles_b200.models import build_workflow

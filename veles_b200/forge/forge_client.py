@@ -1,4 +1,4 @@
-"""Forge client: ``veles_b200 forge <action>`` with actions list | details | fetch | upload | delete | register |
+"""Forge client: ``veles_b200 forge <action>`` with actions list | details | history | diff | fetch | upload | delete | register |
 confirm | unregister | assist (reference: ``veles/forge/forge_client.py:91-799``)."""
 from __future__ import annotations
 
@@ -30,6 +30,14 @@ class ForgeClient(Logger):
 
     def details(self, name):
         return json.loads(self._get("service", query="details", name=name))
+
+    def history(self, name):
+        """Upload history of a model from the server's git repository: [{version, commit, date, author, subject}]."""
+        return json.loads(self._get("service", query="history", name=name))
+
+    def diff(self, name, a, b):
+        """File-level summary of what changed between two versions (``git diff --stat``)."""
+        return json.loads(self._get("service", query="diff", name=name, a=a, b=b))["diff"]
 
     def register(self, email):
         self.token = json.loads(self._get("service", query="register", email=email))["token"]
@@ -112,7 +120,8 @@ class ForgeClient(Logger):
 def main(argv=None):
     p = argparse.ArgumentParser(prog="veles_b200 forge")
     p.add_argument("action", choices=["list", "details", "fetch", "upload", "delete", "register", "confirm", "unregister",
-                                      "assist"])
+                                      "assist", "history", "diff"])
+    p.add_argument("--against", default=None, help="the other version of a diff (diff -n NAME -v v2 --against v1)")
     p.add_argument("-c", "--code", default=None, help="confirmation code (confirm)")
     p.add_argument("-w", "--workflow", default=None, help="path to the workflow file (assist)")
     p.add_argument("-s", "--server", default=None)
@@ -128,6 +137,11 @@ def main(argv=None):
             print("%-24s %-40s %-16s %s" % tuple(row))
     elif a.action == "details":
         print(json.dumps(c.details(a.name), indent=1))
+    elif a.action == "history":
+        for h in c.history(a.name):
+            print("%-6s %s  %-32s %s" % (h["version"] or "", h["date"], h["author"], h["subject"]))
+    elif a.action == "diff":
+        print(c.diff(a.name, a.against, a.version))
     elif a.action == "fetch":
         print(c.fetch(a.name, a.directory, a.version)[0])
     elif a.action == "upload":

@@ -46,6 +46,68 @@ class ForgeServer(Logger):
         d = self.model_dir(name)
         return sorted((v for v in os.listdir(d) if v.isdigit()), key=int) if os.path.isdir(d) else []
 
+    # -- git history of a model (the reference keeps every model as a git repository: forge_server.py:462-560) -----
+    def _git(self, name, *args, check=True):
+        import subprocess
+        repo = os.path.join(self.model_dir(name), "history")
+        env = dict(os.environ, GIT_CONFIG_GLOBAL=os.devnull, GIT_CONFIG_SYSTEM=os.devnull)
+        r = subprocess.run(["git", "-C", repo] + list(args), stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env)
+        if check and r.returncode != 0:
+            raise RuntimeError("git %s failed: %s" % (" ".join(args), r.stderr.decode(errors="replace")[-300:]))
+        return r.stdout.decode(errors="replace")
+
+    def _record_in_git(self, name, version, src_dir, email, manifest):
+        """Mirror version ``version`` (already stored as a numbered directory) into the model's git repository:
+        one commit per upload, tagged ``v<N>``.  Without a ``git`` executable the numbered directories are the store."""
+        if shutil.which("git") is None:
+            return False
+        repo = os.path.join(self.model_dir(name), "history")
+        try:
+            if not os.path.isdir(os.path.join(repo, ".git")):
+                os.makedirs(repo, exist_ok=True)
+                self._git(name, "init", "-q")
+            for entry in os.listdir(repo):                      # the tree of a version replaces the previous one
+                if entry != ".git":
+                    path = os.path.join(repo, entry)
+                    shutil.rmtree(path) if os.path.isdir(path) else os.remove(path)
+            for entry in os.listdir(src_dir):
+                if entry in ("package.tar.gz", "owner"):
+                    continue
+                path = os.path.join(src_dir, entry)
+                dst = os.path.join(repo, entry)
+                shutil.copytree(path, dst) if os.path.isdir(path) else shutil.copy2(path, dst)
+            self._git(name, "add", "-A")
+            who = "%s <%s>" % (manifest.get("author") or email.split("@")[0], email)
+            self._git(name, "-c", "user.name=forge", "-c", "user.email=forge@localhost", "commit", "-q", "--allow-empty",
+                      "--author", who, "-m", "v%s: %s" % (version, manifest.get("short_description", "")))
+            self._git(name, "tag", "-f", "v%s" % version)
+            return True
+        except Exception as e:  # noqa: BLE001 - the history is a mirror: the upload itself has succeeded
+            self.warning("git history of %s was not updated: %s", name, e)
+            return False
+
+    def history(self, name):
+        """[{version, commit, date, author, subject}] newest first (empty without git)."""
+        if not self.versions(name):
+            raise KeyError(name)
+        if shutil.which("git") is None or not os.path.isdir(os.path.join(self.model_dir(name), "history", ".git")):
+            return []
+        out = []
+        log = self._git(name, "log", "--format=%H%x1f%aI%x1f%an <%ae>%x1f%s%x1f%D", check=False)
+        for line in log.splitlines():
+            h, date, author, subject, refs = (line.split("\x1f") + [""] * 5)[:5]
+            tags = [r.strip()[5:] for r in refs.split(",") if r.strip().startswith("tag: ")]
+            out.append({"version": tags[0] if tags else None, "commit": h, "date": date, "author": author,
+                        "subject": subject})
+        return out
+
+    def diff(self, name, a, b):
+        """``git diff --stat`` between two versions of a model."""
+        vs = ["v" + v for v in self.versions(name)]
+        if a not in vs or b not in vs:
+            raise KeyError("%s %s..%s" % (name, a, b))
+        return self._git(name, "diff", "--stat", a, b)
+
     def list(self):
         base = os.path.join(self.root_dir, "models")
         out = []
@@ -64,7 +126,7 @@ class ForgeServer(Logger):
         with open(os.path.join(self.model_dir(name), vs[-1], "manifest.json")) as f:
             m = json.load(f)
         return {"name": name, "description": m.get("long_description", ""), "versions": ["v" + v for v in vs],
-                "manifest": m}
+                "manifest": m, "history": self.history(name)}
 
     def _outbox_mailer(self, email, subject, body):
         box = os.path.join(self.root_dir, "outbox")
@@ -142,6 +204,7 @@ class ForgeServer(Logger):
                     f.write(blob)
                 with open(os.path.join(dest, "owner"), "w") as f:
                     f.write(self.tokens[token]["email"])
+                self._record_in_git(manifest["name"], version, dest, self.tokens[token]["email"], manifest)
             return {"name": manifest["name"], "version": "v" + version}
         finally:
             shutil.rmtree(tmp, ignore_errors=True)
@@ -201,6 +264,11 @@ class ForgeServer(Logger):
                         return self._guard(lambda: self._send(200, srv.list()))
                     if kind == "details":
                         return self._guard(lambda: self._send(200, srv.details(q.get("name"))))
+                    if kind == "history":
+                        return self._guard(lambda: self._send(200, srv.history(q.get("name"))))
+                    if kind == "diff":
+                        return self._guard(lambda: self._send(200, {"diff": srv.diff(q.get("name"), q.get("a"),
+                                                                                      q.get("b"))}))
                     if kind == "register":
                         return self._guard(lambda: self._send(200, {"token": srv.register(q.get("email", "?"))}))
                     if kind == "confirm":
