@@ -306,3 +306,111 @@ def test_bias_gradient_summed_by_lrn_backward_matches_the_column_sum_pass():
         assert np.abs(v0).max() > 0
         assert np.abs(b1 - b0).max() <= 1e-2 * np.abs(b0 - b0.mean()).max() + 1e-2 * np.abs(v0).max()
         assert np.abs(v1 - v0).max() <= 2e-2 * np.abs(v0).max()
+
+
+def test_full_alexnet_pass_matches_numpy_oracle():
+    """The whole flagship network once, every kernel of the benchmark at its real shape (227x227x3 input, grouped
+    convolutions, LRN, overlapping pooling, 4096-wide fully connected layers; batch 4) against the numpy backend:
+    * forward: the output of every layer;
+    * backward, layer by layer: each device unit is handed the ORACLE's err_output and must reproduce the oracle's
+      err_input and weight / bias gradients (no accumulation of differences from layer to layer).  Max-pooling units
+      are compared by gradient mass only: this random-init network has bias-dominated activations, so bf16 rounding
+      makes many window maxima tie and a quarter of the gradient is routed to a different (equally valid) position."""
+    from veles_b200.backends import NumpyDevice, B200Device
+    from veles_b200.trainer import Trainer
+    from veles_b200.znicz.gd_pooling import GDPooling
+
+    def build(dev):
+        tr = Trainer("alexnet", minibatch_size=4, device=dev, use_graph=False, n_train=8, seed=11,
+                     layers_kwargs={"dropout": 0.0})
+        for gd in tr.wf.gds:
+            gd.apply_gradient = False
+        tr.wf.loader.run()
+        for f in tr.wf.forwards:
+            f.run()
+        tr.wf.evaluator.run()
+        return tr
+
+    def grab(arr):
+        arr.map_read()
+        return np.array(arr.mem, dtype=np.float32).copy()
+
+    # oracle pass
+    tr = build(NumpyDevice())
+    wf = tr.wf
+    ref = {"y": [grab(f.output).reshape(4, -1) for f in wf.forwards], "eo": {}, "ei": {}, "gw": {}, "gb": {}}
+    for i in range(len(wf.gds) - 1, -1, -1):
+        gd = wf.gds[i]
+        ref["eo"][i] = grab(gd.err_output)
+        gd.run()
+        if i > 0 and gd.err_input is not None and gd.err_input:
+            ref["ei"][i] = grab(gd.err_input)
+        if getattr(wf.forwards[i], "HAS_WEIGHTS", False):
+            ref["gw"][i] = grab(gd.gradient_weights)
+            ref["gb"][i] = grab(gd.gradient_bias)
+    tr.close()
+
+    def fro(a, b):
+        return float(np.linalg.norm((a - b).ravel()) / (np.linalg.norm(a.ravel()) + 1e-20))
+
+    tr = build(B200Device())
+    wf = tr.wf
+    errors = {}
+    for i, f in enumerate(wf.forwards):
+        y = grab(f.output).reshape(4, -1)
+        assert np.isfinite(y).all()
+        errors["y%02d_%s" % (i, type(f).__name__)] = float(np.abs(y - ref["y"][i]).max() / (np.abs(ref["y"][i]).max() + 1e-12))
+    top = len(wf.gds) - 1
+    for i in range(top, -1, -1):
+        gd = wf.gds[i]
+        if i < top:                                   # the top unit keeps the evaluator's err_output
+            gd.err_output.map_invalidate()
+            gd.err_output.mem[...] = ref["eo"][i].reshape(gd.err_output.mem.shape)
+        gd.run()
+        name = "%02d_%s" % (i, type(gd).__name__)
+        if i in ref["ei"]:
+            ei = grab(gd.err_input)
+            assert np.isfinite(ei).all(), name
+            if isinstance(gd, GDPooling):
+                errors["ei" + name + "_mass"] = abs(float(np.linalg.norm(ei)) / float(np.linalg.norm(ref["ei"][i])) - 1.0)
+            else:
+                errors["ei" + name] = fro(ref["ei"][i].ravel(), ei.ravel())
+        if i in ref["gw"]:
+            errors["gw" + name] = fro(ref["gw"][i].ravel(), grab(gd.gradient_weights).ravel())
+            errors["gb" + name] = fro(ref["gb"][i].ravel(), grab(gd.gradient_bias).ravel())
+    tr.close()
+    import json, os
+    if os.path.isdir("gpurun_out"):
+        with open("gpurun_out/alexnet_oracle_errors.json", "w") as fdbg:
+            json.dump(errors, fdbg, indent=1)
+    assert sum(k.startswith("gw") for k in errors) == 8
+    fwd = {k: v for k, v in errors.items() if k.startswith("y")}
+    assert max(fwd.values()) < 0.02, fwd            # bf16 through eight layers: half a per cent of each tensor's maximum
+    # relative Frobenius error per tensor.  Most land at 0.2-0.4 % (bf16 operands); units that multiply by a strict-ReLU
+    # derivative reach 2-4 %: an activation that is a rounding error away from zero passes its gradient on one side
+    # and blocks it on the other, and a fraction p of such elements costs sqrt(p)
+    bad = {k: v for k, v in errors.items() if not k.startswith("y") and v > 0.06}
+    assert not bad, bad
+    tight = [v for k, v in errors.items() if k.startswith("gw")]
+    assert sorted(tight)[len(tight) // 2] < 0.005, tight
+
+
+def test_device_tensor_reflects_pending_host_writes():
+    """``Array.devmem`` flushes a pending host write: a device unit that reads its input without an explicit unmap()
+    (LRN, dropout, activations...) still sees what a host-side producer wrote."""
+    from veles_b200.backends import B200Device
+    from veles_b200.memory import Array
+    dev = B200Device()
+    a = Array(np.arange(12, dtype=np.float32).reshape(3, 4))
+    a.initialize(dev)
+    assert float(a.devmem.sum()) == 66.0
+    a.map_write()
+    a.mem[...] = 1.0
+    assert float(a.devmem.sum()) == 12.0            # no unmap() in between
+    a.devmem.mul_(2.0)
+    a.mark_device_written()
+    a.map_read()
+    assert float(a.mem.sum()) == 24.0
+    a.map_invalidate()
+    a.mem[...] = 3.0
+    assert float(a.devmem[0, 0]) == 3.0

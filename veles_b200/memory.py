@@ -123,6 +123,10 @@ class Array(Pickleable):
                 hook()
             finally:
                 self.lazy_device_ = hook
+        # pending host writes reach the device before a kernel reads the tensor, whether or not the reading unit
+        # remembered its unmap() (the usual producers are device units, so this is one flag test on the hot path)
+        if self.host_dirty_ and self.devmem_ is not None:
+            self.unmap()
         return self.devmem_
 
     @property
