@@ -171,8 +171,9 @@ int vb_col_sum_gd(const void* a, int dtype, long long lda, int rows, int cols, f
  * capture, latency-critical loops where cudaMalloc is forbidden).  Same result as vb_col_sum, but the
  * inter-block scratch is a fixed 4 MiB array inside the library, so only inputs and outputs are passed.
  * This entry point has no counterpart in the reference.
- * Limit: ceil(rows/64) * cols <= vb_col_sum_static_max_elems() (1 Mi floats); larger inputs are rejected
- * with an error before anything is launched.  The first call on each device looks up the array's device
+ * Limits: ceil(rows/64) * cols <= vb_col_sum_static_max_elems() (1 Mi floats) and ceil(rows/64) <= 65535
+ * (rows <= 4 194 240: the slabs are the grid's y dimension); larger inputs are rejected with an error before
+ * anything is launched.  The first call on each device looks up the array's device
  * address (no allocation) — make it before any stream capture.  All calls on a device share the array:
  * calls whose kernels can overlap on the GPU race with each other; nothing needs zeroing between calls. */
 long long vb_col_sum_static_max_elems(void);
