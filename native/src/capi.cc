@@ -2,6 +2,7 @@
 #include <cstring>
 #include <string>
 
+#include "veles/logger.h"
 #include "veles/unit_factory.h"
 #include "veles/workflow_loader.h"
 
@@ -67,5 +68,26 @@ int veles_native_run(void* wf, const float* input, float* output, int batch) {
 }
 
 void veles_native_free(void* wf) { delete static_cast<Workflow*>(wf); }
+
+// -- logging (veles/logger.h) -------------------------------------------------------------------------------------
+// level: 0 critical .. 4 debug; returns the previous global threshold, -1 for a bad argument
+int veles_native_set_log_level(int level) {
+  if (level < 0 || level > 4) return -1;
+  const int prev = static_cast<int>(Logger::Level());
+  Logger::SetLevel(static_cast<LogLevel>(level));
+  return prev;
+}
+int veles_native_set_domain_log_level(const char* domain, int level) {
+  if (domain == nullptr || level < 0 || level > 4) return -1;
+  Logger::SetDomainLevel(domain, static_cast<LogLevel>(level));
+  return 0;
+}
+// records go to sink(level, domain, message, user) instead of stderr; nullptr restores stderr
+void veles_native_set_log_sink(LogSink sink, void* user) { Logger::SetSink(sink, user); }
+// emit a record through the runtime's logger (embedding applications share its sink and thresholds)
+void veles_native_log(int level, const char* domain, const char* message) {
+  if (level < 0 || level > 4 || domain == nullptr || message == nullptr) return;
+  Logger(domain).log(static_cast<LogLevel>(level), "%s", message);
+}
 
 }  // extern "C"

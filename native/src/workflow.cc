@@ -1,5 +1,7 @@
 #include "veles/workflow.h"
 
+#include "veles/logger.h"
+
 #include <algorithm>
 #include <map>
 #include <stdexcept>
@@ -89,8 +91,13 @@ void Workflow::Plan(int batch, const Shape& input_shape) {
 }
 
 void Workflow::Initialize(int batch, const Shape& input_shape, int device) {
+  static const Logger log("Workflow", kLogColorGreen);
   VN_CUDA(cudaSetDevice(device));
   Plan(batch, input_shape);
+  size_t naive = 0;
+  for (const auto& node : nodes_) naive += node.size;
+  VELES_INF(log, "\"%s\": batch %d on device %d, activation arena %zu bytes (%zu without buffer reuse)", name_.c_str(),
+            batch, device, arena_bytes_, naive);
   VN_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   VN_CUDA(cudaMalloc(reinterpret_cast<void**>(&arena_), arena_bytes_));
   VN_CUDA(cudaMemset(arena_, 0, arena_bytes_));

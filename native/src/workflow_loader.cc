@@ -2,9 +2,15 @@
 
 #include <stdexcept>
 
+#include "veles/logger.h"
 #include "veles/unit_factory.h"
 
 namespace veles {
+
+static const Logger& loader_log() {
+  static const Logger log("WorkflowLoader", kLogColorCyan);
+  return log;
+}
 
 Property WorkflowLoader::ToProperty(const JsonValue& v, const WorkflowArchive& archive) {
   Property p;
@@ -39,6 +45,7 @@ std::unique_ptr<Workflow> WorkflowLoader::FromArchive(const WorkflowArchive& arc
   for (const JsonValue& u : units.arr) {
     const JsonValue& cls = u.at("class");
     std::unique_ptr<Unit> unit = UnitFactory::Instance().Create(cls.at("uuid").str, cls.at("name").str);
+    VELES_DBG(loader_log(), "unit %zu: %s (%s)", wf->Size(), cls.at("name").str.c_str(), cls.at("uuid").str.c_str());
     // arrays last: scalar properties (include_bias, geometry, ...) must be known when weights arrive
     const JsonValue& data = u.at("data");
     for (int pass = 0; pass < 2; ++pass)
@@ -57,10 +64,13 @@ std::unique_ptr<Workflow> WorkflowLoader::FromArchive(const WorkflowArchive& arc
       wf->Get(j)->LinkFrom(wf->Get(i));
     }
   }
+  VELES_INF(loader_log(), "loaded workflow \"%s\" (%zu units, checksum %s)", wf->name().c_str(), wf->Size(),
+            wf->checksum().empty() ? "-" : wf->checksum().c_str());
   return wf;
 }
 
 std::unique_ptr<Workflow> WorkflowLoader::Load(const std::string& package_path) {
+  VELES_DBG(loader_log(), "opening %s", package_path.c_str());
   return FromArchive(WorkflowArchive::Load(package_path));
 }
 

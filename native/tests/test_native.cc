@@ -12,6 +12,9 @@
 #include "veles/memory_optimizer.h"
 #include "veles/numpy_array_loader.h"
 #include "veles/unit_factory.h"
+#include <typeinfo>
+
+#include "veles/logger.h"
 #include "veles/workflow_loader.h"
 
 using namespace veles;
@@ -134,7 +137,51 @@ static void test_package(const char* path) {
   std::printf("arena %zu bytes (sum of buffers %zu)\n", wf->arena_bytes(), naive);
 }
 
+// logger: thresholds (global and per domain), sink callback, level parsing, long records, class-name domains
+struct SinkRecord {
+  int level;
+  std::string domain, message;
+};
+static std::vector<SinkRecord> g_sink;
+static void test_sink(int level, const char* domain, const char* message, void* user) {
+  (void)user;
+  g_sink.push_back({level, domain, message});
+}
+
+static void test_logger() {
+  using veles::Logger;
+  using veles::LogLevel;
+  LogLevel l;
+  CHECK(Logger::ParseLevel("DEBUG", &l) && l == LogLevel::kDebug);
+  CHECK(Logger::ParseLevel("warn", &l) && l == LogLevel::kWarning);
+  CHECK(Logger::ParseLevel("1", &l) && l == LogLevel::kError);
+  CHECK(!Logger::ParseLevel("loud", &l));
+  CHECK(std::string(Logger::LevelName(LogLevel::kCritical)) == "CRITICAL");
+  CHECK(Logger::Demangle(typeid(veles::WorkflowLoader).name()) == "WorkflowLoader");
+  const LogLevel before = Logger::Level();
+  Logger::SetSink(test_sink, nullptr);
+  Logger::SetLevel(LogLevel::kWarning);
+  Logger a("Alpha", veles::kLogColorCyan), b("Beta");
+  VELES_INF(a, "hidden %d", 1);
+  VELES_WRN(a, "shown %d", 2);
+  CHECK(g_sink.size() == 1 && g_sink[0].level == 2 && g_sink[0].domain == "Alpha" && g_sink[0].message == "shown 2");
+  Logger::SetDomainLevel("Beta", LogLevel::kDebug);
+  VELES_DBG(b, "beta debug");
+  VELES_DBG(a, "alpha debug");
+  CHECK(g_sink.size() == 2 && g_sink[1].domain == "Beta" && g_sink[1].level == 4);
+  CHECK(b.enabled(LogLevel::kDebug) && !a.enabled(LogLevel::kInfo) && a.enabled(LogLevel::kError));
+  const std::string big(2000, 'x');
+  VELES_ERR(a, "%s!", big.c_str());
+  CHECK(g_sink.size() == 3 && g_sink[2].message.size() == 2001 && g_sink[2].message.back() == '!');
+  Logger::ClearDomainLevels();
+  VELES_DBG(b, "gone");
+  CHECK(g_sink.size() == 3);
+  Logger::SetSink(nullptr, nullptr);
+  Logger::SetLevel(before);
+}
+
 int main(int argc, char** argv) {
+  test_logger();
   test_json();
   test_npy();
   test_memory_optimizer();

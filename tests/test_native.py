@@ -78,6 +78,36 @@ def test_native_loads_the_reference_fixtures():
         L.veles_native_free(h)
 
 
+@pytest.mark.skipif(not os.path.isdir(REF_FIXTURES), reason="the reference checkout is not on this machine")
+def test_native_logger_through_the_c_api():
+    """The runtime's logger (reference: libVeles/src/logger.cc): an embedding application installs a sink, sets the
+    thresholds and sees the loader's records; its own records go through the same path."""
+    lib, _ = _build()
+    L = _native(lib)
+    records = []
+    SINK = ctypes.CFUNCTYPE(None, ctypes.c_int, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p)
+    sink = SINK(lambda level, domain, message, user: records.append((level, domain.decode(), message.decode())))
+    L.veles_native_set_log_sink(sink, None)
+    try:
+        prev = L.veles_native_set_log_level(3)                      # info
+        assert 0 <= prev <= 4 and L.veles_native_set_log_level(9) == -1
+        h = L.veles_native_load(os.path.join(REF_FIXTURES, "mnist.zip").encode())
+        assert h
+        L.veles_native_free(ctypes.c_void_p(h))
+        assert any(d == "WorkflowLoader" and lv == 3 and "MnistWorkflow" in m and "2 units" in m for lv, d, m in records)
+        assert not any(lv == 4 for lv, _, _ in records)             # debug records stay below the threshold
+        n = len(records)
+        assert L.veles_native_set_domain_log_level(b"WorkflowLoader", 4) == 0
+        h = L.veles_native_load(os.path.join(REF_FIXTURES, "mnist.tar.gz").encode())
+        L.veles_native_free(ctypes.c_void_p(h))
+        assert sum(1 for lv, d, _ in records[n:] if lv == 4 and d == "WorkflowLoader") >= 3   # opening + one per unit
+        L.veles_native_log(1, b"App", b"from the host application")
+        assert records[-1] == (1, "App", "from the host application")
+        L.veles_native_set_log_level(prev)
+    finally:
+        L.veles_native_set_log_sink(None, None)
+
+
 def _native(lib_path):
     L = ctypes.CDLL(lib_path)
     L.veles_native_load.restype = ctypes.c_void_p

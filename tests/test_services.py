@@ -104,6 +104,40 @@ def test_frontend_composer_serves_the_form_and_returns_the_posted_command_line()
     assert serve([], open_browser=False, timeout=0.2) is None       # nobody posted: cancelled
 
 
+def test_yarn_node_discovery_against_a_local_resource_manager():
+    """``--yarn-nodes`` (reference: launcher.py:887-906): RUNNING nodes of /ws/v1/cluster/nodes become node specs; an
+    unreachable manager only warns."""
+    import threading
+    from http.server import BaseHTTPRequestHandler, HTTPServer
+    from veles_b200.launcher import Launcher
+    seen = []
+
+    class RM(BaseHTTPRequestHandler):
+        def log_message(self, *a):
+            pass
+
+        def do_GET(self):
+            seen.append(self.path)
+            body = json.dumps({"nodes": {"node": [
+                {"nodeHostName": "gpu-a", "state": "RUNNING"}, {"nodeHostName": "gpu-b", "state": "LOST"},
+                {"nodeHostName": "gpu-c", "state": "RUNNING"}, {"nodeHostName": "gpu-a", "state": "RUNNING"}]}}).encode()
+            self.send_response(200)
+            self.send_header("Content-Length", str(len(body)))
+            self.end_headers()
+            self.wfile.write(body)
+
+    srv = HTTPServer(("127.0.0.1", 0), RM)
+    threading.Thread(target=srv.serve_forever, kwargs={"poll_interval": 0.05}, daemon=True).start()
+    try:
+        l = Launcher(True)
+        nodes = l.discover_nodes_from_yarn("127.0.0.1:%d" % srv.server_address[1])
+        assert nodes == ["gpu-a/auto:0", "gpu-c/auto:0"] and seen == ["/ws/v1/cluster/nodes"]
+    finally:
+        srv.shutdown()
+        srv.server_close()
+    assert Launcher(True).discover_nodes_from_yarn("127.0.0.1:9", timeout=0.5) == []
+
+
 def test_launcher_status_heartbeat_payload():
     from veles_b200.dummy import DummyWorkflow
     from veles_b200.launcher import Launcher, filter_argv

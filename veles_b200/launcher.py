@@ -101,7 +101,9 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
         parser.add_argument("--data-parallel", type=str, default="auto", choices=["auto", "off", "fused", "nccl", "host"],
                             help="With WORLD_SIZE > 1 (one process per GPU): synchronous data parallelism through "
                                  "the fused all-reduce+update kernel (auto on GPUs), NCCL, or host all-reduce (numpy).")
-        parser.add_argument("--yarn-nodes", type=str, default="", help="Accepted for compatibility; ignored.")
+        parser.add_argument("--yarn-nodes", type=str, default="",
+                            help="Discover the slave nodes from this YARN ResourceManager (host[:8088]): every "
+                                 "RUNNING node of /ws/v1/cluster/nodes is launched as host/auto:0.")
         parser.add_argument("-t", "--test", default=False, action="store_true",
                             help="Evaluation mode: run the workflow on the test data without training.")
         parser.add_argument("-p", "--matplotlib-backend", type=str, nargs="?", const="", default="Agg",
@@ -218,6 +220,10 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
         if self.dp_ is not None:
             self.dp_.finalize(self.workflow)
         self._initialized = True
+        if self.is_master and getattr(self.args, "yarn_nodes", ""):
+            found = self.discover_nodes_from_yarn(self.args.yarn_nodes)
+            if found:
+                self.args.nodes = ",".join(filter(None, [self.args.nodes] + found))
         if self.is_master and self.args.nodes:
             self.launch_remote_progs()
 
@@ -326,6 +332,34 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
         self.thread_pool.resume()
 
     # -- slaves ----------------------------------------------------------------------------------------------------------
+    def discover_nodes_from_yarn(self, address, timeout=5.0):
+        """Node specs ``host/auto:0`` of the RUNNING nodes a YARN ResourceManager lists
+        (reference: ``veles/launcher.py:887-906``: GET /ws/v1/cluster/nodes, one slave per ``nodeHostName``).  An
+        unreachable manager or an unexpected answer is a warning, not an error: the run goes on with ``--nodes``."""
+        import urllib.request
+        if ":" not in address.split("//")[-1]:
+            address += ":8088"
+        if not address.startswith(("http://", "https://")):
+            address = "http://" + address
+        url = address.rstrip("/") + "/ws/v1/cluster/nodes"
+        self.debug("Requesting GET %s", url)
+        try:
+            with urllib.request.urlopen(url, timeout=timeout) as resp:
+                tree = json.loads(resp.read().decode())
+            nodes = (tree.get("nodes") or {}).get("node") or []
+            hosts = []
+            for node in nodes:
+                if node.get("state", "RUNNING") != "RUNNING":
+                    continue
+                host = node.get("nodeHostName")
+                if host and host not in hosts:
+                    hosts.append(host)
+        except Exception as e:  # noqa: BLE001
+            self.warning("Failed to get the nodes list from YARN ResourceManager %s: %s", url, e)
+            return []
+        self.info("YARN ResourceManager lists %d running node(s): %s", len(hosts), ", ".join(hosts))
+        return ["%s/auto:0" % h for h in hosts]
+
     def launch_remote_progs(self):
         """Start slaves described by ``--nodes host/backend:devs[xN],...`` (local ones via subprocess,
         one per device ordinal with CUDA_VISIBLE_DEVICES; remote ones via ssh)."""
