@@ -30,8 +30,18 @@ def main():
     model = sys.argv[1] if len(sys.argv) > 1 else "mnist_mlp"
     kw = {"caffe_init": False, "lr": 0.01} if model == "cifar_convnet" else None
     B, steps = 16, 4
-    res = run(model, B, steps, DataParallel(mode="host"), kw)
+    dp = DataParallel(mode="host")
+    res = run(model, B, steps, dp, kw)
     ok = True
+    # the class-end reductions of the group (what Decision calls): counters + loss, max / min, small arrays
+    ranks = np.arange(1, world + 1)
+    vals, loss = dp.sum_counters([3 * (rank + 1), 100 + rank], 0.125 * (rank + 1))
+    ok = ok and list(vals) == [int(3 * ranks.sum()), int(100 * world + ranks.sum() - world)]
+    ok = ok and abs(loss - 0.125 * ranks.sum()) < 1e-12
+    ok = ok and dp.max_min(float(rank), -2.0 * rank) == (float(world - 1), -2.0 * (world - 1))
+    cm = dp.sum_array(np.arange(12, dtype=np.int32).reshape(3, 4) * (rank + 1))
+    ok = ok and cm.dtype == np.int32 and np.array_equal(cm, np.arange(12).reshape(3, 4) * ranks.sum())
+    ok = ok and float(dp.sum_array(np.array([0.5 * rank], dtype=np.float32), op="max")[0]) == 0.5 * (world - 1)
     if rank == 0:
         ref = run(model, B * world, steps, None, kw)
         for li, ((w, b), (rw, rb)) in enumerate(zip(res, ref)):

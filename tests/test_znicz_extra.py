@@ -365,3 +365,29 @@ def test_gd_options_on_device_match_the_numpy_oracle():
         _, w_ref, v_ref = _one_gd_step(kw, steps=3)
         _, w_dev, v_dev = _one_gd_step(kw, device=B200Device(), steps=3)
         assert np.abs(w_dev - w_ref).max() < 3e-2 * max(np.abs(w_ref).max(), 1e-3), kw
+
+
+def test_bias_sum_fusion_plan_pairs_lrn_units_with_their_convolutions():
+    """StandardWorkflow plans conv -> LRN pairs whose LRN backward unit also produces the convolution's bias-gradient
+    sums (device path); the plan is inert on the numpy backend and can be switched off."""
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.config import root
+    from veles_b200.trainer import Trainer
+    from veles_b200.znicz.gd_conv import GradientDescentConv
+    from veles_b200.znicz.normalization import LRNormalizerBackward
+    for fuse in (True, False):
+        root.common.engine.fuse_bias_sum = fuse
+        try:
+            tr = Trainer("alexnet", minibatch_size=2, device=NumpyDevice(), use_graph=False, n_train=4,
+                         layers_kwargs={"dropout": 0.0})
+            gds = tr.wf.gds
+            pairs = [(i, gds.index(g.bias_sum_for)) for i, g in enumerate(gds) if getattr(g, "bias_sum_for", None) is not None]
+            assert pairs == ([(1, 0), (4, 3)] if fuse else [])
+            for i, j in pairs:
+                assert isinstance(gds[i], LRNormalizerBackward) and isinstance(gds[j], GradientDescentConv)
+                assert gds[i].prev_activation and gds[j].derivative_applied      # the sums are of the masked gradient
+            tr.step_resident()                                                    # the oracle path ignores the plan
+            assert tr.wf.loader.__dict__.get("minibatch_sink_") is None           # (and gathers into minibatch_data)
+            tr.close()
+        finally:
+            root.common.engine.fuse_bias_sum = True
