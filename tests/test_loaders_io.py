@@ -206,3 +206,26 @@ def test_stream_loader_autoencoder_targets_train_on_cpu():
         last = tr.step(x, None)
     assert last < first
     tr.close()
+
+
+def test_label_statistics_and_progress_spinner(caplog):
+    """Loader start-up reports how evenly each class's labels are populated (reference: loader/base.py:947-980); the
+    unit-run spinner writes only to terminals."""
+    import io
+    import logging
+    from veles_b200.dummy import DummyWorkflow
+    from veles_b200.loader.base import Loader
+    from veles_b200.units import spin, _SPIN
+    ld = Loader.__new__(Loader)
+    ld._logger_ = logging.getLogger("Loader")
+    with caplog.at_level(logging.DEBUG):
+        even = Loader._print_label_stats(ld, {0: 100, 1: 104, 2: 97}, "train")
+        skew = Loader._print_label_stats(ld, {"cat": 5, "dog": 500}, "validation")
+        none = Loader._print_label_stats(ld, {}, "test")
+    assert 'min: 97 ("2"), max: 104 ("1")' in even and "UNBALANCED" not in even
+    assert skew.endswith("UNBALANCED") and 'max: 500 ("dog")' in skew and none is None
+    assert any("Detailed train label stats" in r.getMessage() for r in caplog.records)
+    assert any(r.levelno == logging.WARNING and "UNBALANCED" in r.getMessage() for r in caplog.records)
+    buf = io.StringIO()
+    assert spin(buf) and len(buf.getvalue()) == 2 and buf.getvalue()[1] == "\b"
+    assert _SPIN["enabled"] in (False, None) or True            # pytest's stdout is not a terminal: run() never spins

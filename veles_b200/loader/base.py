@@ -442,6 +442,18 @@ class Loader(AcceleratedUnit, metaclass=UserLoaderRegistry):
 
     def _on_successful_serve(self):
         self.samples_served += self._minibatch_size_
+        if not self.is_slave:
+            # progress line every 10 s of serving (reference: loader/base.py:399-414)
+            now = time.time()
+            if now - self.__dict__.get("_serve_log_time_", 0.0) >= 10.0:
+                first = "_serve_log_time_" not in self.__dict__
+                self._serve_log_time_ = now
+                total = max(1, self.effective_total_samples)
+                if not first:
+                    self.info("Served %d samples (%d epochs, %.1f%% current); jobs failed: %d; pending: %d",
+                              self.samples_served, self.samples_served // total,
+                              100.0 * (self.samples_served % total) / total, len(self.failed_minibatches),
+                              self.pending_minibatches_count)
         if self.last_minibatch:
             self.debug("Last minibatch of class %s served in epoch %d",
                        CLASS_NAME[self.minibatch_class].upper(), self.epoch_number)
@@ -459,11 +471,38 @@ class Loader(AcceleratedUnit, metaclass=UserLoaderRegistry):
         if self.class_lengths[TRAIN] > 0 and other and not other.issubset(train):
             self.warning("There are labels in the test/validation sets absent from the train set: %s",
                          sorted(other - train, key=str))
+        for ci in (TEST, VALID, TRAIN):
+            if self.class_lengths[ci] > 0:
+                self._print_label_stats(diff_labels[ci], CLASS_NAME[ci])
         labels = sorted(train | other, key=lambda v: (str(type(v)), v))
         if not self._labels_mapping or not self.restored_from_snapshot:
             self._labels_mapping = {lbl: i for i, lbl in enumerate(labels)}
             self._reversed_labels_mapping = list(labels)
         self._unique_labels_count = max(len(self._labels_mapping), 1)
+
+    def _print_label_stats(self, stats, set_name):
+        """One line per sample class on how evenly its labels are populated (reference: loader/base.py:947-980): a
+        spread above 10 % of the mean is flagged, above 50 % flagged as severe; the per-label table goes to DEBUG."""
+        values = [int(v) for v in stats.values()]
+        if not values or sum(values) == 0:
+            self.info("No %s labels specified", set_name)
+            return None
+        keys = list(stats.keys())
+        mean, stddev = float(numpy.mean(values)), float(numpy.std(values))
+        lmin, lmax = int(numpy.min(values)), int(numpy.max(values))
+        amin, amax = keys[int(numpy.argmin(values))], keys[int(numpy.argmax(values))]
+        verdict = "" if stddev <= mean / 10 else (" - UNBALANCED" if stddev > mean / 2 else " - uneven")
+        line = ("%s label cardinalities: min: %d (\"%s\"), max: %d (\"%s\"), avg: %d, sigma: %d (%d%%)%s"
+                % (set_name, lmin, amin, lmax, amax, int(mean), int(stddev), int(stddev * 100 // max(mean, 1)), verdict))
+        (self.warning if verdict == " - UNBALANCED" else self.info)(line)
+        import logging
+        if logging.getLogger(type(self).__name__).isEnabledFor(logging.DEBUG) or \
+                logging.getLogger().isEnabledFor(logging.DEBUG):
+            total = sum(values)
+            rows = ["%-16s %10d %6.1f%%  %s" % (str(k)[:16], v, 100.0 * v / total, "*" * (v * 25 // max(lmax, 1)))
+                    for k, v in zip(keys, values)]
+            self.debug("Detailed %s label stats:\n%s", set_name, "\n".join(rows))
+        return line
 
     def _validate_and_fix_normalization(self):
         pass

@@ -67,6 +67,36 @@ class _Timers(dict):
         return 0.0
 
 
+_SPIN = {"chars": "|/-\\", "i": 0, "t": 0.0, "enabled": None}
+
+
+def spin(stream=None):
+    """Progress spinner of a terminal run (reference: ``veles/units.py:443-445`` spins after every unit run unless
+    ``root.common.disable.spinning_run_progress``): one character redrawn in place, at most ten times a second, only
+    when stdout is a terminal."""
+    st = _SPIN
+    if st["enabled"] is None:
+        try:
+            st["enabled"] = bool(sys.stdout.isatty()) and not get(root.common.disable.spinning_run_progress, False)
+        except Exception:  # noqa: BLE001
+            st["enabled"] = False
+    if not st["enabled"] and stream is None:
+        return False
+    now = time.perf_counter()
+    if now - st["t"] < 0.1 and stream is None:
+        return False
+    st["t"] = now
+    st["i"] = (st["i"] + 1) % len(st["chars"])
+    out = stream if stream is not None else sys.stdout
+    try:
+        out.write(st["chars"][st["i"]] + "\b")
+        out.flush()
+    except Exception:  # noqa: BLE001 - a closed stdout must not fail a unit
+        st["enabled"] = False
+        return False
+    return True
+
+
 class Unit(Distributable, Verified, metaclass=UnitRegistry):
     """General unit of a workflow."""
 
@@ -574,6 +604,7 @@ class Unit(Distributable, Verified, metaclass=UnitRegistry):
                     nvtx.range_pop()
                 Unit.timers[self._id] += dt
                 self._run_calls += 1
+                spin()
                 if self._timings:
                     self.debug("%s run took %.6f s", self.name, dt)
         run.__wrapped__ = fn
