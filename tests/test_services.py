@@ -180,6 +180,13 @@ def test_forge_keeps_a_git_history_of_every_model(tmp_path):
         assert c.details("hist")["history"][0]["commit"] == h[0]["commit"]
         d = c.diff("hist", "v1", "v2")
         assert "cfg.py" in d and "extra.txt" in d and "wf.py" not in d
+        # the browser pages: index with a link per model, details with history and downloads
+        index = urllib.request.urlopen(srv.url, timeout=10).read().decode()
+        assert "VelesForge: 1 model(s)" in index and "<a href='?name=hist'>hist</a>" in index and "second cut" in index
+        page = urllib.request.urlopen(srv.url + "?name=hist", timeout=10).read().decode()
+        assert "fetch?name=hist&version=v2" in page and "v1: first cut" in page and "&quot;workflow&quot;" in page
+        with pytest.raises(urllib.error.HTTPError):
+            urllib.request.urlopen(srv.url + "?name=nope", timeout=10)
         with pytest.raises(urllib.error.HTTPError):
             c.diff("hist", "v1", "v9")
     finally:

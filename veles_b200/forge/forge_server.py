@@ -228,6 +228,38 @@ class ForgeServer(Logger):
             raise PermissionError("only the uploader may delete a model")
         shutil.rmtree(d)
 
+    # -- html ---------------------------------------------------------------------------------------------------
+    _PAGE = ("<!doctype html><html><head><meta charset='utf-8'><title>%s</title><style>body{font-family:sans-serif;"
+             "margin:1.5em}table{border-collapse:collapse}td,th{border:1px solid #999;padding:4px 10px;text-align:left}"
+             "pre{background:#f4f4f4;padding:8px}</style></head><body>%s</body></html>")
+
+    def index_page(self):
+        import html
+        rows = ["<tr><td><a href='?name=%s'>%s</a></td><td>%s</td><td>%s</td><td>%s</td></tr>"
+                % (html.escape(n, quote=True), html.escape(n), html.escape(d), html.escape(a), html.escape(v))
+                for n, d, a, v in self.list()]
+        body = ("<h2>VelesForge: %d model(s)</h2><table><tr><th>name</th><th>description</th><th>author</th>"
+                "<th>latest</th></tr>%s</table><p><code>veles forge fetch -n NAME -s %s</code></p>"
+                % (len(rows), "".join(rows), html.escape(self.url)))
+        return self._PAGE % ("VelesForge", body)
+
+    def details_page(self, name):
+        import html
+        d = self.details(name)
+        m = d["manifest"]
+        hist = "".join("<tr><td>%s</td><td>%s</td><td>%s</td><td>%s</td></tr>"
+                       % (html.escape(str(h["version"] or "")), html.escape(h["date"]), html.escape(h["author"]),
+                          html.escape(h["subject"])) for h in d["history"])
+        links = " ".join("<a href='fetch?name=%s&version=%s'>%s</a>" % (html.escape(name, quote=True), v, v)
+                         for v in reversed(d["versions"]))
+        body = ("<p><a href='?'>all models</a></p><h2>%s</h2><p>%s</p><p>author: %s; workflow: <code>%s</code>; "
+                "configuration: <code>%s</code></p><p>download: %s</p>%s<h3>manifest</h3><pre>%s</pre>"
+                % (html.escape(name), html.escape(d["description"]), html.escape(str(m.get("author", ""))),
+                   html.escape(str(m.get("workflow", ""))), html.escape(str(m.get("configuration", ""))), links,
+                   ("<h3>history</h3><table><tr><th>version</th><th>date</th><th>author</th><th>subject</th></tr>%s"
+                    "</table>" % hist) if hist else "", html.escape(json.dumps(m, indent=1))))
+        return self._PAGE % (html.escape(name), body)
+
     # -- http -----------------------------------------------------------------------------------------------------
     def start(self):
         srv = self
@@ -282,6 +314,12 @@ class ForgeServer(Logger):
                 if url.path.endswith("/fetch"):
                     return self._guard(lambda: self._send(200, srv.fetch(q.get("name"), q.get("version")),
                                                           "application/x-gzip"))
+                if url.path.rstrip("/").endswith("/forge") or url.path in ("", "/"):
+                    # the browser face of the zoo (reference: forge_server.py serves forge.html / details pages)
+                    name = q.get("name")
+                    return self._guard(lambda: self._send(
+                        200, (srv.details_page(name) if name else srv.index_page()).encode(),
+                        "text/html; charset=utf-8"))
                 self._send(404, {"error": "not found"})
 
             def do_POST(self):
