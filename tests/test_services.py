@@ -304,20 +304,47 @@ def test_forge_roundtrip(tmp_path):
         srv.stop()
 
 
-def test_compare_snapshots(tmp_path):
+def test_compare_snapshots(tmp_path, capsys):
+    """Average relative / average / maximum difference per Array, sorting, the workflow identity check and the command
+    line (reference: scripts/compare_snapshots.py:82-146)."""
     from veles_b200.backends import NumpyDevice
     from veles_b200.models import build_workflow
-    from veles_b200.scripts.compare_snapshots import compare
+    from veles_b200.scripts.compare_snapshots import compare, format_table, main
+    from veles_b200.snapshotter import SnapshotterToFile
     root.common.disable.snapshotting = True
     wf = build_workflow("mnist_mlp", minibatch_size=50, n_train=100, n_valid=0, max_epochs=1)
     wf.initialize(device=NumpyDevice())
     a = pickle.loads(pickle.dumps(wf))
     wf.run()
     b = pickle.loads(pickle.dumps(wf))
-    rows = dict((k, d) for k, _, d in compare(a, b))
-    assert rows["fc_tanh1.weights"] > 0 and rows["fc_softmax2.bias"] > 0
-    assert dict((k, d) for k, _, d in compare(a, a))["fc_tanh1.weights"] == 0
+    rows = {(u, k): (rel, avg, mx) for _, u, k, rel, avg, mx in compare(a, b)}
+    rel, avg, mx = rows[("fc_tanh1", "weights")]
+    assert 0 < avg <= mx and 0 < rel < 2.0 and rows[("fc_softmax2", "bias")][2] > 0
+    assert all(v == (0.0, 0.0, 0.0) for v in {(u, k): r[0:3] for (u, k), r in rows.items()}.values()) is False
+    same = compare(a, a)
+    assert same and all(r[3] == 0 and r[5] == 0 for r in same)
+    deps = [r[0] for r in compare(a, b, ("dep", "avgreldiff"))]
+    assert deps == sorted(deps)
+    by_max = [r[5] for r in compare(a, b, ("maxdiff",))]
+    assert by_max == sorted(by_max)
+    table = format_table(compare(a, b))
+    assert "Average Relative Diff" in table and "fc_tanh1" in table and table.count("+--") >= 3
+    other = build_workflow("wide_mlp_ae", minibatch_size=8, n_train=16, n_valid=0, max_epochs=1)
+    other.initialize(device=NumpyDevice())
+    other_copy = pickle.loads(pickle.dumps(other))
+    other_copy.__class__ = type("SomeOtherWorkflow", (type(other_copy),), {})
+    with pytest.raises(ValueError):
+        compare(a, other_copy)
+    # command line on snapshot files
+    pa, pb = str(tmp_path / "a.pickle"), str(tmp_path / "b.pickle")
+    for path, obj in ((pa, a), (pb, b)):
+        with open(path, "wb") as f:
+            pickle.dump(obj, f)
+    assert main(["-q", pa, pb, "-s", "maxdiff", "unit"]) == 0
+    assert "fc_softmax2" in capsys.readouterr().out
+    assert main([pa]) == 1
     wf.launcher.stop()
+    other.launcher.stop()
 
 
 def test_downloader_unpacks_local_archive(tmp_path):
