@@ -147,6 +147,31 @@ def test_launcher_status_heartbeat_payload():
     wf = DummyWorkflow(launcher=l)
     st = l.status()
     assert st["mode"] == "standalone" and st["graph"].startswith("digraph") and st["name"] == wf.name
+    assert st["graph_svg"].startswith("<svg") and st["session"]
+
+
+def test_workflow_graph_picture_layers_units_and_marks_the_loop():
+    """generate_graph_svg: one box per unit, forward edges between consecutive layers, the Repeater loop as a dashed
+    back edge, gate-blocked edges in red; well-formed XML."""
+    import xml.etree.ElementTree as ET
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.models import build_workflow
+    root.common.disable.snapshotting = True
+    wf = build_workflow("mnist_mlp", minibatch_size=50, n_train=100, n_valid=50, max_epochs=1)
+    wf.initialize(device=NumpyDevice())
+    svg = wf.generate_graph_svg()
+    tree = ET.fromstring(svg)
+    ns = "{http://www.w3.org/2000/svg}"
+    boxes = tree.findall(".//%srect" % ns)
+    titles = [t.text for t in tree.findall(".//%stitle" % ns)]
+    assert len(boxes) == len(titles) >= 8 and any("Repeater" in t for t in titles) and any("Decision" in t for t in titles)
+    paths = tree.findall("%spath" % ns)
+    dashed = [p for p in paths if p.get("stroke-dasharray")]
+    assert dashed and len(dashed) < len(paths)                     # the training loop closes through back edges
+    assert any(p.get("stroke") == "#c00" for p in paths)           # end point / gds are gate-blocked
+    ys = sorted({float(b.get("y")) for b in boxes})
+    assert len(ys) >= 5                                            # start -> repeater -> loader -> forwards -> ... layers
+    wf.launcher.stop()
 
 
 def test_forge_keeps_a_git_history_of_every_model(tmp_path):

@@ -44,6 +44,9 @@ def test_dry_run_and_graph_and_config_dump(tmp_path):
     assert r.returncode == 0, r.stdout.decode()[-2000:]
     text = graph.read_text()
     assert "digraph" in text and "All2AllTanh" in text and "GDSoftmax" in text
+    pic = tmp_path / "wf.svg"
+    r = cli("--dry-run", "init", "--workflow-graph", str(pic), os.path.join(SAMPLES, "mnist.py"), "-")
+    assert r.returncode == 0 and pic.read_text().startswith("<svg") and "All2AllTanh" in pic.read_text()
     r = cli("--dump-config", os.path.join(SAMPLES, "mnist.py"), "-")
     assert r.returncode == 0 and b"loader_name" in r.stdout
     r = cli("--version")

@@ -249,7 +249,12 @@ class Main(Logger, CommandLineBase):
         self.launcher.args.backend = getattr(self.args, "backend", "auto")
         self.launcher.initialize(**kw)
         if self.args.workflow_graph:
-            self.workflow.generate_graph(filename=self.args.workflow_graph, with_data_links=True)
+            if self.args.workflow_graph.lower().endswith(".svg"):       # a picture instead of the DOT text
+                with open(self.args.workflow_graph, "w") as f:
+                    f.write(self.workflow.generate_graph_svg())
+                self.info("Saved the workflow graph picture to %s", self.args.workflow_graph)
+            else:
+                self.workflow.generate_graph(filename=self.args.workflow_graph, with_data_links=True)
         if self.args.dump_unit_attributes != "no":
             self._dump_unit_attributes(self.args.dump_unit_attributes == "all")
         if self.args.dry_run == "init" or self.args.visualize:

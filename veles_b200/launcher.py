@@ -408,6 +408,15 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
         self._notify_thread = threading.Thread(target=loop, name="status-notifier", daemon=True)
         self._notify_thread.start()
 
+    def _graph_svg(self, wf):
+        if wf is None or not hasattr(wf, "generate_graph_svg"):
+            return ""
+        try:
+            return wf.generate_graph_svg()
+        except Exception as e:  # noqa: BLE001 - a picture must not break the heartbeat
+            self.debug("workflow graph picture failed: %s", e)
+            return ""
+
     def status(self):
         wf = self.workflow
         from .logger import events
@@ -415,5 +424,6 @@ class Launcher(Logger, metaclass=CommandLineArgumentsRegistry):
                 "master": socket.gethostname(),
                 "time": time.time() - (self._start_time or time.time()), "user": os.environ.get("USER", "?"),
                 "mode": self.mode, "graph": wf.generate_graph(write_on_disk=False) if wf else "",
+                "graph_svg": self._graph_svg(wf),
                 "slaves": self.agent.slaves_status() if self.is_master and self.agent is not None else {},
                 "plots": self.plots_endpoints, "description": (wf.__doc__ or "") if wf else ""}

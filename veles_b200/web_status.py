@@ -19,7 +19,8 @@ tr.sel{background:#def}pre{background:#f4f4f4;padding:6px;max-height:18em;overfl
 .WARNING{color:#a60}input,select{margin-right:8px}</style></head><body>
 <h2>Running workflows</h2><table id="wf"><thead><tr><th>workflow</th><th>host</th><th>mode</th><th>uptime</th>
 <th>slaves</th><th>user</th></tr></thead><tbody></tbody></table>
-<h3 id="title"></h3><div id="slaves"></div><pre id="graph"></pre>
+<h3 id="title"></h3><div id="slaves"></div><div id="graphsvg" style="overflow:auto;max-height:32em"></div>
+<details><summary>graph (DOT)</summary><pre id="graph"></pre></details>
 <h3>Logs</h3>level <select id="level"><option>DEBUG</option><option selected>INFO</option><option>WARNING</option>
 <option>ERROR</option></select>text <input id="text" size="24"><label><input type="checkbox" id="all"> all sessions</label>
 <table id="logs"><thead><tr><th>time</th><th>node</th><th>level</th><th>logger</th><th>message</th></tr></thead><tbody></tbody></table>
@@ -44,6 +45,8 @@ async function refresh(){
     const sl=w[selected].slaves||{};
     document.getElementById('slaves').innerHTML=Object.entries(sl).map(([k,v])=>esc(k)+': '+esc(JSON.stringify(v))).join('<br>');
     const g=await ask({request:'graph',id:selected}); document.getElementById('graph').textContent=g.graph||'';
+    if(g.svg!==document.getElementById('graphsvg').dataset.src){document.getElementById('graphsvg').innerHTML=g.svg||'';
+      document.getElementById('graphsvg').dataset.src=g.svg||'';}
   }
   const sess = document.getElementById('all').checked ? null : (selected && w[selected] ? w[selected].session : null);
   const lg = await ask({request:'logs',session:sess,level:document.getElementById('level').value,
@@ -92,7 +95,7 @@ class WebServer(Logger):
                 return {mid: {k: d.get(k) for k in fields} for mid, d in self.masters.items()}
             if kind == "graph":
                 d = self.masters.get(request.get("id"))
-                return {"graph": d.get("graph") if d else None}
+                return {"graph": d.get("graph") if d else None, "svg": d.get("graph_svg") if d else None}
         if kind in ("events", "logs"):
             # the reference queried MongoDB collections here (veles/web_status.py:113-186): session / node / level /
             # logger or event name / text / since filters over the JSON-lines sinks

@@ -542,6 +542,102 @@ class Workflow(Container):
             self.info("Saved the workflow graph to %s", filename)
         return text
 
+    def generate_graph_svg(self, box=(150, 34), gap=(26, 30)):
+        """The control-flow graph as a self-contained SVG picture (the reference's web status lays the DOT text out in
+        the browser with viz.js; here the layout is done once, on this side).  Layers = longest path from the start
+        point along forward edges (an edge into an already placed ancestor - the Repeater loop - is a back edge, drawn
+        dashed); inside a layer units are ordered by the mean position of their parents.  Gate-blocked edges are red."""
+        import html
+        order, seen = [], set()
+        for u in list(self.start_point.dependent_units()) + self._units:
+            if id(u) not in seen and u is not self:
+                seen.add(id(u))
+                order.append(u)
+        index = {id(u): i for i, u in enumerate(order)}
+        edges = [(index[id(u)], index[id(d)], d) for u in order for d in u.links_to_sorted if id(d) in index]
+        # depth-first classification of back edges, then longest-path layering over the remaining DAG
+        state, back = {}, set()
+        children = {}
+        for a, b, _ in edges:
+            children.setdefault(a, []).append(b)
+        for root_i in range(len(order)):
+            if root_i in state:
+                continue
+            stack = [(root_i, iter(children.get(root_i, ())))]
+            state[root_i] = 1
+            while stack:
+                node, it = stack[-1]
+                nxt = next(it, None)
+                if nxt is None:
+                    state[node] = 2
+                    stack.pop()
+                elif state.get(nxt) == 1:
+                    back.add((node, nxt))
+                elif nxt not in state:
+                    state[nxt] = 1
+                    stack.append((nxt, iter(children.get(nxt, ()))))
+        layer = [0] * len(order)
+        for _ in range(len(order)):
+            changed = False
+            for a, b, _d in edges:
+                if (a, b) not in back and layer[b] < layer[a] + 1:
+                    layer[b] = layer[a] + 1
+                    changed = True
+            if not changed:
+                break
+        rows = {}
+        for i, l in enumerate(layer):
+            rows.setdefault(l, []).append(i)
+        pos = {}
+        for l in sorted(rows):
+            members = rows[l]
+            if l > 0:
+                def bary(i):
+                    ps = [pos[a][0] for a, b, _d in edges if b == i and a in pos and (a, b) not in back]
+                    return sum(ps) / len(ps) if ps else 0.0
+                members.sort(key=bary)
+            for k, i in enumerate(members):
+                pos[i] = (k, l)
+        width = max(len(m) for m in rows.values())
+        bw, bh = box
+        gx, gy = gap
+        W = width * (bw + gx) + gx
+        H = (max(rows) + 1) * (bh + gy) + gy
+
+        def xy(i):
+            k, l = pos[i]
+            pad = (width - len(rows[l])) * (bw + gx) / 2.0
+            return gx + pad + k * (bw + gx), gy + l * (bh + gy)
+
+        out = ['<svg xmlns="http://www.w3.org/2000/svg" width="%d" height="%d" viewBox="0 0 %d %d" '
+               'font-family="sans-serif" font-size="10">' % (W, H, W, H),
+               '<defs><marker id="arr" markerWidth="8" markerHeight="8" refX="7" refY="3" orient="auto">'
+               '<path d="M0,0 L7,3 L0,6 z" fill="context-stroke"/></marker></defs>']
+        for a, b, dst in edges:
+            xa, ya = xy(a)
+            xb, yb = xy(b)
+            blocked = dst.gate_block._op is not None or bool(dst.gate_block)
+            color = "#c00" if blocked else "#555"
+            if (a, b) in back:      # around the right-hand side, dashed
+                x0, y0, x1, y1 = xa + bw, ya + bh / 2.0, xb + bw, yb + bh / 2.0
+                bend = max(x0, x1) + gx * 0.8
+                out.append('<path d="M%.1f,%.1f C%.1f,%.1f %.1f,%.1f %.1f,%.1f" fill="none" stroke="%s" '
+                           'stroke-dasharray="4,3" marker-end="url(#arr)"/>' % (x0, y0, bend, y0, bend, y1, x1, y1, color))
+            else:
+                x0, y0, x1, y1 = xa + bw / 2.0, ya + bh, xb + bw / 2.0, yb
+                out.append('<path d="M%.1f,%.1f C%.1f,%.1f %.1f,%.1f %.1f,%.1f" fill="none" stroke="%s" '
+                           'marker-end="url(#arr)"/>' % (x0, y0, x0, y0 + gy / 2.0, x1, y1 - gy / 2.0, x1, y1, color))
+        for i, u in enumerate(order):
+            x, y = xy(i)
+            fill = self.VIEW_GROUP_COLORS.get(u.view_group, "white")
+            out.append('<g><title>%s</title><rect x="%.1f" y="%.1f" width="%d" height="%d" rx="4" fill="%s" '
+                       'stroke="#333"/><text x="%.1f" y="%.1f" text-anchor="middle">%s</text>'
+                       '<text x="%.1f" y="%.1f" text-anchor="middle" fill="#444" font-size="8">%s</text></g>'
+                       % (html.escape("%s (%s)" % (u.name, type(u).__name__)), x, y, bw, bh, fill, x + bw / 2.0, y + 14,
+                          html.escape(str(u.name)[:26]), x + bw / 2.0, y + 26, html.escape(type(u).__name__[:30])))
+        out.append("</svg>")
+        return "\n".join(out)
+
     def gather_results(self):
         results = {"id": getattr(self.launcher, "id", None), "log_id": getattr(self.launcher, "log_id", None)}
         methods = interface_methods(IResultProvider)
