@@ -89,6 +89,8 @@ def _pdl_state():
 
 
 def main():
+    from veles_b200.config import root as _cfg
+    _cfg.common.disable.spinning_run_progress = True      # stdout carries exactly one JSON line
     args = parse()
     if args.impl == "reference":
         reference_unavailable()

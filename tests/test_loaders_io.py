@@ -228,4 +228,5 @@ def test_label_statistics_and_progress_spinner(caplog):
     assert any(r.levelno == logging.WARNING and "UNBALANCED" in r.getMessage() for r in caplog.records)
     buf = io.StringIO()
     assert spin(buf) and len(buf.getvalue()) == 2 and buf.getvalue()[1] == "\b"
-    assert _SPIN["enabled"] in (False, None) or True            # pytest's stdout is not a terminal: run() never spins
+    _SPIN["enabled"] = None
+    assert spin() is False and _SPIN["enabled"] is False        # pytest's stdout is not a terminal: run() never spins

@@ -73,11 +73,12 @@ _SPIN = {"chars": "|/-\\", "i": 0, "t": 0.0, "enabled": None}
 def spin(stream=None):
     """Progress spinner of a terminal run (reference: ``veles/units.py:443-445`` spins after every unit run unless
     ``root.common.disable.spinning_run_progress``): one character redrawn in place, at most ten times a second, only
-    when stdout is a terminal."""
+    when stderr is a terminal (stderr, so that programs whose stdout is data - ``bench.py``'s JSON line, ``--dump-config``
+    - stay clean even when run by hand)."""
     st = _SPIN
     if st["enabled"] is None:
         try:
-            st["enabled"] = bool(sys.stdout.isatty()) and not get(root.common.disable.spinning_run_progress, False)
+            st["enabled"] = bool(sys.stderr.isatty()) and not get(root.common.disable.spinning_run_progress, False)
         except Exception:  # noqa: BLE001
             st["enabled"] = False
     if not st["enabled"] and stream is None:
@@ -87,7 +88,7 @@ def spin(stream=None):
         return False
     st["t"] = now
     st["i"] = (st["i"] + 1) % len(st["chars"])
-    out = stream if stream is not None else sys.stdout
+    out = stream if stream is not None else sys.stderr
     try:
         out.write(st["chars"][st["i"]] + "\b")
         out.flush()
