@@ -414,3 +414,27 @@ def test_device_tensor_reflects_pending_host_writes():
     a.map_invalidate()
     a.mem[...] = 3.0
     assert float(a.devmem[0, 0]) == 3.0
+
+
+def test_pipelined_step_on_device_returns_each_loss_one_call_late():
+    """Trainer.step_pipelined on the device: the loss of step i is copied to pinned memory asynchronously and returned by
+    call i + 1 (flush_loss for the last); same values as the synchronous step()."""
+    import torch
+    from veles_b200.backends import B200Device
+    from veles_b200.trainer import Trainer
+    xs = [torch.from_numpy(np.random.RandomState(k).rand(8, 4096).astype(np.float32)).pin_memory() for k in range(6)]
+    seqs = []
+    for pipelined in (False, True):
+        tr = Trainer("wide_mlp_ae", minibatch_size=8, device=B200Device(), streaming=True, seed=3, use_graph=False,
+                     layers_kwargs={"width": 64, "depth": 2, "in_features": 4096})
+        if pipelined:
+            got = [tr.step_pipelined(x, None) for x in xs]
+            assert got[0] is None
+            got = got[1:] + [tr.flush_loss()]
+            assert tr.flush_loss() is None
+        else:
+            got = [tr.step(x, None) for x in xs]
+        assert all(np.isfinite(v) and v > 0 for v in got)
+        seqs.append(got)
+        tr.close()
+    assert np.allclose(seqs[0], seqs[1], rtol=1e-3), seqs

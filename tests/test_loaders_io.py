@@ -208,6 +208,29 @@ def test_stream_loader_autoencoder_targets_train_on_cpu():
     tr.close()
 
 
+def test_pipelined_step_returns_each_loss_one_call_late():
+    """Trainer.step_pipelined: the loss of step i comes back from call i + 1 (flush_loss for the last one); the
+    sequence equals what step() returns for the same minibatches."""
+    import numpy as np
+    from veles_b200.backends import NumpyDevice
+    from veles_b200.trainer import Trainer
+    xs = [np.random.RandomState(k).rand(8, 4096).astype(np.float32) for k in range(5)]
+    seqs = []
+    for pipelined in (False, True):
+        tr = Trainer("wide_mlp_ae", minibatch_size=8, device=NumpyDevice(), streaming=True, seed=3,
+                     layers_kwargs={"width": 32, "depth": 2, "in_features": 4096})
+        if pipelined:
+            got = [tr.step_pipelined(x, None) for x in xs]
+            assert got[0] is None and tr._pending_loss is not None
+            got = got[1:] + [tr.flush_loss()]
+            assert tr.flush_loss() is None                     # nothing left
+        else:
+            got = [tr.step(x, None) for x in xs]
+        seqs.append(got)
+        tr.close()
+    assert np.allclose(seqs[0], seqs[1], rtol=1e-6) and len(seqs[1]) == 5
+
+
 def test_label_statistics_and_progress_spinner(caplog):
     """Loader start-up reports how evenly each class's labels are populated (reference: loader/base.py:947-980); the
     unit-run spinner writes only to terminals."""
