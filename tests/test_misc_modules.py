@@ -167,3 +167,22 @@ def test_sanitizer_smoke_program_runs():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     mod = runpy.run_path(os.path.join(root, "scripts", "sanitizer_smoke.py"), run_name="smoke")
     mod["main"]()
+
+
+def test_package_introspection(tmp_path):
+    """veles_b200.__units__ / __modules__ / __loc__ / __plugins__ / allow_root (reference: veles/__init__.py:190-310)."""
+    import os
+    import veles_b200
+    assert os.path.isdir(os.path.join(veles_b200.__root__, "veles_b200"))
+    mods = veles_b200.__modules__
+    names = {m.__name__ for m in mods}
+    assert {"veles_b200.units", "veles_b200.znicz.conv", "veles_b200.loader.fullbatch", "veles_b200.forge.forge_server"} <= names
+    units = [c.__name__ for c in veles_b200.__units__]
+    assert {"Conv", "All2AllSoftmax", "LRNormalizerForward", "Shell", "Repeater"} <= set(units) and len(units) > 100
+    loc = veles_b200.__loc__
+    assert loc["core"] > 10000 and loc["cuda"] > 5000 and loc["c/c++"] > 1000 and loc["all"] == sum(
+        v for k, v in loc.items() if k != "all")
+    assert isinstance(veles_b200.__plugins__, set)
+    veles_b200.allow_root = True
+    assert veles_b200.allow_root is True
+    veles_b200.allow_root = False

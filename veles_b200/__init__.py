@@ -42,10 +42,98 @@ class VelesModule(_types.ModuleType):
         from .trainer import Trainer
         return Trainer
 
+    # -- introspection of the installed tree (reference: veles/__init__.py:190-300) ---------------------------------
+    @property
+    def __root__(self):
+        return _os.path.dirname(_os.path.dirname(_os.path.abspath(self.__file__)))
+
+    def _scan(self):
+        """Import every module of the package tree (tests and build products aside); yields the modules, reports the
+        ones that do not import on stderr."""
+        import importlib
+        skip = {"tests", "csrc", "lib", "__pycache__"}
+        base = _os.path.dirname(_os.path.abspath(self.__file__))
+        for root_dir, dirs, files in _os.walk(base):
+            dirs[:] = sorted(d for d in dirs if d not in skip)
+            rel = _os.path.relpath(root_dir, _os.path.dirname(base)).replace(_os.sep, ".")
+            if not all(part.isidentifier() for part in rel.split(".")):
+                continue
+            for fn in sorted(files):
+                name, ext = _os.path.splitext(fn)
+                if ext != ".py" or name == "__main__":
+                    continue
+                modname = rel if name == "__init__" else "%s.%s" % (rel, name)
+                try:
+                    yield importlib.import_module(modname)
+                except Exception as e:  # noqa: BLE001 - optional dependencies (h5py, pyodbc, ...) may be absent
+                    _sys.stderr.write("%s: %s\n" % (modname, e))
+
+    @property
+    def __modules__(self):
+        cache = self.__dict__.get("_modules_cache")
+        if cache is None:
+            cache = self.__dict__["_modules_cache"] = list(self._scan())
+        return cache
+
     @property
     def __units__(self):
+        """Every Unit class of the package tree (all modules are imported first, so the registry is complete)."""
+        self.__modules__
         from .unit_registry import UnitRegistry
         return sorted(UnitRegistry.units, key=lambda c: c.__name__)
+
+    @property
+    def __loc__(self):
+        """Non-blank lines of the source tree by kind (the reference shells out to ``cloc``; counted here directly)."""
+        cache = self.__dict__.get("_loc_cache")
+        if cache is not None:
+            return cache
+        kinds = {"core": ((".py",), ("veles_b200",)), "tests": ((".py",), ("tests",)),
+                 "cuda": ((".cu", ".cuh"), ("veles_b200/csrc",)),
+                 "c/c++": ((".cc", ".h", ".c"), ("native", "include")), "scripts": ((".py", ".sh"), ("scripts",))}
+        result = {}
+        for kind, (exts, roots) in kinds.items():
+            n = 0
+            for r in roots:
+                for root_dir, dirs, files in _os.walk(_os.path.join(self.__root__, r)):
+                    dirs[:] = [d for d in dirs if d not in ("__pycache__", "lib", "obj")]
+                    for fn in files:
+                        if fn.endswith(exts):
+                            try:
+                                with open(_os.path.join(root_dir, fn), errors="replace") as f:
+                                    n += sum(1 for line in f if line.strip())
+                            except OSError:
+                                pass
+            result[kind] = n
+        result["all"] = sum(result.values())
+        self.__dict__["_loc_cache"] = result
+        return result
+
+    @property
+    def __plugins__(self):
+        """Packages under the installation root that carry a ``.veles`` marker file, imported (reference :154-167)."""
+        cache = self.__dict__.get("_plugins_cache")
+        if cache is None:
+            import importlib
+            cache = set()
+            for root_dir, dirs, files in _os.walk(self.__root__):
+                dirs[:] = [d for d in dirs if not d.startswith(".") and d not in ("__pycache__", "gpurun_out")]
+                if ".veles" in files:
+                    package = _os.path.relpath(root_dir, self.__root__).replace(_os.sep, ".")
+                    try:
+                        cache.add(importlib.import_module(package))
+                    except ImportError:
+                        continue
+            self.__dict__["_plugins_cache"] = cache
+        return cache
+
+    @property
+    def allow_root(self):
+        return bool(self.__dict__.get("_allow_root", False))
+
+    @allow_root.setter
+    def allow_root(self, value):
+        self.__dict__["_allow_root"] = bool(value)
 
 
 _sys.modules[__name__].__class__ = VelesModule
