@@ -137,7 +137,7 @@ def test_ensemble_train_then_test(tmp_path):
 import pytest as _pytest
 
 
-@_pytest.mark.parametrize("sample", ["mnist", "cifar", "mnist_ae"])
+@_pytest.mark.parametrize("sample", ["mnist", "cifar", "mnist_ae", "alexnet", "sequences"])
 def test_every_sample_loads_its_config_and_initialises(sample):
     """`python -m veles_b200 --dry-run init samples/<x>.py -` for every bundled sample (configs with Range genes too)."""
     import os

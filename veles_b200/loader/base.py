@@ -494,7 +494,8 @@ class Loader(AcceleratedUnit, metaclass=UserLoaderRegistry):
         verdict = "" if stddev <= mean / 10 else (" - UNBALANCED" if stddev > mean / 2 else " - uneven")
         line = ("%s label cardinalities: min: %d (\"%s\"), max: %d (\"%s\"), avg: %d, sigma: %d (%d%%)%s"
                 % (set_name, lmin, amin, lmax, amax, int(mean), int(stddev), int(stddev * 100 // max(mean, 1)), verdict))
-        (self.warning if verdict == " - UNBALANCED" else self.info)(line)
+        # with a handful of samples per label the spread says nothing: a warning only when the counts are meaningful
+        (self.warning if verdict == " - UNBALANCED" and mean >= 10 else self.info)(line)
         import logging
         if logging.getLogger(type(self).__name__).isEnabledFor(logging.DEBUG) or \
                 logging.getLogger().isEnabledFor(logging.DEBUG):
