@@ -83,9 +83,13 @@ def test_frontend_composer_serves_the_form_and_returns_the_posted_command_line()
     """``--frontend`` (reference: veles/__main__.py:258-327): the form lists the parser's options; the argv the page
     posts comes back from serve()."""
     import threading
-    from veles_b200.scripts.generate_frontend import generate, serve
+    from veles_b200.scripts.generate_frontend import generate, scan_workflows, serve
     page = generate(["wf.py", "cfg.py", "root.a.b=1"])
     assert "data-opt='--snapshot'" in page or "data-opt='-w'" in page
+    offered = dict(scan_workflows())
+    assert offered["veles_b200/znicz/samples/mnist.py"].endswith("mnist_config.py") and len(offered) >= 6
+    assert not any("optimization_workflow" in w for w in offered)
+    assert "<option value='veles_b200/znicz/samples/alexnet.py'>" in page
     assert "value='wf.py'" in page and "function compose()" in page and "--frontend" not in page.split("<table>")[1]
     got = {}
 

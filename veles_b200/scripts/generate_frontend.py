@@ -36,6 +36,31 @@ document.addEventListener('input',compose);document.addEventListener('DOMContent
 """
 
 
+def scan_workflows():
+    """Workflow files that ship with the package (modules defining ``run(load, main)``) with their ``*_config.py``
+    when there is one: the composer offers them in the workflow field (reference: ``scan_workflows``)."""
+    import os
+    import re
+    base = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    found = []
+    for root_dir, dirs, files in os.walk(base):
+        dirs[:] = sorted(d for d in dirs if d not in ("__pycache__", "csrc", "lib", "tests"))
+        for fn in sorted(files):
+            if not fn.endswith(".py") or fn.endswith("_config.py") or fn.startswith("__"):
+                continue
+            path = os.path.join(root_dir, fn)
+            try:
+                with open(path, errors="replace") as f:
+                    text = f.read()
+            except OSError:
+                continue
+            if re.search(r"^def run\(load, main\):", text, re.M):
+                cfg = path[:-3] + "_config.py"
+                found.append((os.path.relpath(path, os.path.dirname(base)),
+                              os.path.relpath(cfg, os.path.dirname(base)) if os.path.exists(cfg) else "-"))
+    return found
+
+
 def _control(act):
     opt = act.option_strings[-1]
     q = html.escape(opt, quote=True)
@@ -69,12 +94,14 @@ def generate(cmdline=""):
             "td,th{border:1px solid #999;padding:3px 8px}#cmdline{width:100%%;font-family:monospace}</style>"
             "<script>%s</script></head><body>"
             "<h2>veles_b200 [options] workflow.py [config.py] [root.x.y=value ...]</h2>"
-            "<p>workflow <input id='workflow' size='48' value='%s'> config <input id='config' size='32' value='%s'>"
+            "<p>workflow <input id='workflow' size='48' value='%s' list='workflows'> config "
+            "<input id='config' size='32' value='%s'><datalist id='workflows'>%s</datalist>"
             "<br>overrides <input id='overrides' size='90' value='%s' placeholder='root.loader.minibatch_size=128'></p>"
             "<table><tr><th>option</th><th>value</th><th>meaning</th></tr>%s</table>"
             "<p><input id='cmdline' readonly></p>"
             "<p><button onclick='send(true)'>Run</button> <button onclick='send(false)'>Cancel</button></p>"
-            "</body></html>" % (SCRIPT, wf, cfg, ov, "\n".join(rows)))
+            "</body></html>" % (SCRIPT, wf, cfg, "".join(
+                "<option value='%s'>" % html.escape(w, quote=True) for w, _c in scan_workflows()), ov, "\n".join(rows)))
 
 
 def serve(argv=(), host="127.0.0.1", port=0, open_browser=True, ready=None, timeout=None):
