@@ -68,55 +68,7 @@ def loads(frames):
     return pickle.loads(decomp(b"".join(frames[1:-1])))
 
 
-class SharedIO(object):
-    """A named shared-memory segment carrying one pickled payload between processes on one host."""
 
-    def __init__(self, name=None, size=0, create=False):
-        self.name = name
-        self.size = size
-        self._shm = shared_memory.SharedMemory(name=name, create=create, size=size if create else 0)
-        if not create:
-            self.size = self._shm.size
-
-    @staticmethod
-    def put(name, payload):
-        try:
-            old = shared_memory.SharedMemory(name=name)
-            if old.size >= len(payload) + 8:
-                shm = old
-            else:
-                old.close()
-                old.unlink()
-                shm = shared_memory.SharedMemory(name=name, create=True, size=int(len(payload) * 1.05) + 8)
-        except FileNotFoundError:
-            shm = shared_memory.SharedMemory(name=name, create=True, size=int(len(payload) * 1.05) + 8)
-        shm.buf[:8] = len(payload).to_bytes(8, "little")
-        shm.buf[8:8 + len(payload)] = payload
-        shm.close()
-        return name
-
-    @staticmethod
-    def get(name, unlink=False):
-        shm = shared_memory.SharedMemory(name=name)
-        try:
-            n = int.from_bytes(bytes(shm.buf[:8]), "little")
-            return bytes(shm.buf[8:8 + n])
-        finally:
-            shm.close()
-            if unlink:
-                try:
-                    shm.unlink()
-                except FileNotFoundError:
-                    pass
-
-    @staticmethod
-    def remove(name):
-        try:
-            shm = shared_memory.SharedMemory(name=name)
-            shm.close()
-            shm.unlink()
-        except FileNotFoundError:
-            pass
 
 
 def parse_address(address, default_host="127.0.0.1"):
@@ -128,3 +80,7 @@ def parse_address(address, default_host="127.0.0.1"):
 
 def default_codec():
     return get(root.common.engine.network_compression, "gzip")
+
+
+# SharedIO lives with the ZeroMQ transport (txzmq/sharedio.py); imported last: txzmq.connection needs the codecs above
+from .txzmq.sharedio import SharedIO  # noqa: E402,F401 - the class lives with the ZeroMQ transport
