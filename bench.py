@@ -310,6 +310,8 @@ def main():
                 raise
             sys.stderr.write("pipelined loss read-back failed (%s): timing the synchronous form\n" % exc)
             e2e_sync = True
+            while len(getattr(tr.wf.loader, "pending_", ())) >= 2:     # leave room for the region's first upload
+                tr.step(prefetched=True)
             last_loss, h2d, dev_ms, wall_ms = timed_region(True)
         e2e_ms = max(dev_ms, max_over_ranks(wall_ms)) / args.steps
         e2e = {"value": world * B * 1000.0 / e2e_ms, "unit": "images/s", "ms_per_step": e2e_ms,

@@ -121,6 +121,9 @@ class StreamLoader(Loader):
         if not self.on_device:
             self.host_pending_.append((data, labels, count, targets))
             return 0
+        if len(self.pending_) >= 2:
+            raise RuntimeError("feed(): both staging slots hold minibatches that were not consumed yet; run a step "
+                               "before feeding a third one")
         slot = self.slot_
         self.slot_ ^= 1
         nbytes = data.numel() * data.element_size()
