@@ -53,6 +53,26 @@ def test_dry_run_and_graph_and_config_dump(tmp_path):
     assert r.returncode == 0 and b"veles_b200" in r.stdout
 
 
+def test_cli_run_leaves_logs_and_events_the_web_status_can_query(tmp_path):
+    """``root.common.engine.log_sinks=True``: the run appends its log records and timeline events as JSON lines under
+    ``dirs.logs``; a status server pointed at that directory answers queries about the session."""
+    from veles_b200.web_status import WebServer
+    logs = tmp_path / "logs"
+    r = cli("-v", "info", os.path.join(SAMPLES, "mnist.py"), "-", "root.mnist.decision.max_epochs=1",
+            "root.mnist.loader.n_train=200", "root.mnist.loader.n_valid=100", "root.common.disable.snapshotting=True",
+            "root.common.engine.log_sinks=True", 'root.common.dirs.logs="%s"' % logs)
+    assert r.returncode == 0, r.stdout.decode()[-2000:]
+    files = sorted(os.listdir(logs))
+    assert len(files) == 2 and files[0].endswith(".events.jsonl") and files[1].endswith(".logs.jsonl")
+    srv = WebServer(port=0, log_dir=str(logs))
+    sessions = srv.service({"request": "sessions"})["sessions"]
+    assert len(sessions) == 1
+    found = srv.service({"request": "logs", "session": sessions[0], "text": "samples:", "level": "info"})["logs"]
+    assert found and found[0]["name"].endswith("Loader")
+    ev = srv.service({"request": "events", "session": sessions[0], "name": "run"})["events"]
+    assert {e["type"] for e in ev} >= {"begin", "end"}
+
+
 def test_same_seed_same_result(tmp_path):
     outs = []
     for i in range(2):

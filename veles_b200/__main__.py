@@ -67,17 +67,26 @@ class Main(Logger, CommandLineBase):
     def _setup_logging(self):
         level = CommandLineBase.LOG_LEVEL_MAP[self.args.verbosity]
         Logger.setup_logging(level)
-        log_dir = get(root.common.dirs.logs, None) if get(root.common.engine.log_sinks, False) else None
-        if log_dir:
-            # JSON-lines sinks the web status searches (the reference's MongoDB logging: veles/logger.py:226-262)
-            from .logger import events, install_log_sink
-            stem = os.path.join(log_dir, "%s-%d" % (events.session, os.getpid()))
-            install_log_sink(stem + ".logs.jsonl")
-            events.open(stem + ".events.jsonl")
+        self._install_sinks()
         for name in filter(None, self.args.debug.split(",")):
             logging.getLogger(name).setLevel(logging.DEBUG)
         if self.args.debug_pickle:
             setup_pickle_debug()
+
+    def _install_sinks(self):
+        """JSON-lines log / event files the web status searches (the reference's MongoDB logging:
+        ``veles/logger.py:226-262``), when ``root.common.engine.log_sinks`` is set - by a site configuration, the
+        configuration file or a ``root.common.engine.log_sinks=True`` override (hence called again after those)."""
+        if getattr(self, "_sinks_installed", False) or not get(root.common.engine.log_sinks, False):
+            return
+        log_dir = get(root.common.dirs.logs, None)
+        if not log_dir:
+            return
+        from .logger import events, install_log_sink
+        stem = os.path.join(log_dir, "%s-%d" % (events.session, os.getpid()))
+        install_log_sink(stem + ".logs.jsonl")
+        events.open(stem + ".events.jsonl")
+        self._sinks_installed = True
 
     def _rank_group_entropy(self, nbytes):
         """One process per GPU (WORLD_SIZE > 1): replicas must start from identical weights, so random seed material
@@ -353,6 +362,7 @@ class Main(Logger, CommandLineBase):
         if self.config_file:
             self._apply_config(self.config_file)
         self._override_config(args.config_list)
+        self._install_sinks()
         if args.dump_config:
             root.print_()
             return Main.EXIT_SUCCESS
