@@ -178,6 +178,40 @@ def test_workflow_graph_picture_layers_units_and_marks_the_loop():
     wf.launcher.stop()
 
 
+def test_status_and_forge_servers_run_as_processes(tmp_path):
+    """Both servers have command-line entry points (the reference runs them as daemons): start, answer, stop on SIGINT."""
+    import signal
+    import socket
+    import subprocess
+    import sys
+    import time
+
+    def free_port():
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            return s.getsockname()[1]
+
+    env = dict(os.environ, PYTHONPATH=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    p_status, p_forge = free_port(), free_port()
+    procs = [subprocess.Popen([sys.executable, "-m", "veles_b200.web_status", "--port", str(p_status), "--log-dir",
+                               str(tmp_path)], env=env, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL),
+             subprocess.Popen([sys.executable, "-m", "veles_b200.forge.forge_server", "--root", str(tmp_path / "zoo"),
+                               "--port", str(p_forge), "--confirm"], env=env, stdout=subprocess.PIPE,
+                              stderr=subprocess.DEVNULL)]
+    try:
+        assert b"status server on" in procs[0].stdout.readline()
+        assert b"forge server on" in procs[1].stdout.readline()
+        assert _post("http://127.0.0.1:%d/service" % p_status, {"request": "workflows"}) == {}
+        base = "http://127.0.0.1:%d/forge" % p_forge
+        assert json.loads(urllib.request.urlopen(base + "/service?query=list", timeout=10).read()) == []
+        tok = json.loads(urllib.request.urlopen(base + "/service?query=register&email=a@b.c", timeout=10).read())["token"]
+        assert tok and os.path.exists(tmp_path / "zoo" / "outbox" / "a@b.c.txt")     # --confirm: the code was "mailed"
+    finally:
+        for p in procs:
+            p.send_signal(signal.SIGINT)
+        assert [p.wait(timeout=30) for p in procs] == [0, 0]
+
+
 def test_forge_keeps_a_git_history_of_every_model(tmp_path):
     """Every upload is a tagged commit in the model's git repository on the server (reference:
     forge_server.py:462-560): history and version-to-version diffs come from it."""

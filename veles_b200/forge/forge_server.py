@@ -343,3 +343,55 @@ class ForgeServer(Logger):
         if self.httpd is not None:
             self.httpd.shutdown()
             self.httpd.server_close()
+
+
+def smtp_mailer(host, port=25, sender="forge@localhost", user=None, password=None, tls=False):
+    """A ``mailer(email, subject, body)`` that hands confirmation mails to an SMTP relay (the default mailer only
+    writes them into the outbox directory)."""
+    def send(email, subject, body):
+        import smtplib
+        from email.message import EmailMessage
+        msg = EmailMessage()
+        msg["From"], msg["To"], msg["Subject"] = sender, email, subject
+        msg.set_content(body)
+        with smtplib.SMTP(host, port, timeout=30) as s:
+            if tls:
+                s.starttls()
+            if user:
+                s.login(user, password or "")
+            s.send_message(msg)
+    return send
+
+
+def main(argv=None):
+    """``python -m veles_b200.forge.forge_server --root DIR [--host H] [--port P] [--confirm] [--smtp host[:port]]``:
+    the model zoo server as a process of its own (reference: ``veles/forge/forge_server.py`` daemon)."""
+    import argparse
+    import time as _time
+    ap = argparse.ArgumentParser(prog="veles_b200.forge.forge_server", description=main.__doc__)
+    ap.add_argument("--root", required=True, help="storage directory (models, tokens, outbox)")
+    ap.add_argument("--host", default="127.0.0.1")
+    ap.add_argument("--port", type=int, default=8180)
+    ap.add_argument("--confirm", action="store_true", help="new tokens stay pending until the mailed code is presented")
+    ap.add_argument("--smtp", default=None, help="SMTP relay host[:port] for the confirmation mails (default: outbox files)")
+    ap.add_argument("--sender", default="forge@localhost")
+    a = ap.parse_args(argv)
+    mailer = None
+    if a.smtp:
+        h, _, p = a.smtp.partition(":")
+        mailer = smtp_mailer(h, int(p or 25), sender=a.sender)
+    srv = ForgeServer(a.root, host=a.host, port=a.port, require_confirmation=a.confirm, mailer=mailer).start()
+    print("forge server on %s (storage %s)" % (srv.url, srv.root_dir), flush=True)
+    try:
+        while True:
+            _time.sleep(1)
+    except KeyboardInterrupt:
+        pass
+    finally:
+        srv.stop()
+    return 0
+
+
+if __name__ == "__main__":
+    import sys
+    sys.exit(main())

@@ -180,14 +180,28 @@ class WebServer(Logger):
             self.httpd = None
 
 
-def main():
-    srv = WebServer().start()
+def main(argv=None):
+    """``python -m veles_b200.web_status [--host H] [--port P] [--log-dir DIR] [--drop-time S]``: the status server
+    as a process of its own (reference: ``veles/web_status.py`` runs as a daemon the launchers POST to)."""
+    import argparse
+    ap = argparse.ArgumentParser(prog="veles_b200.web_status", description=main.__doc__)
+    ap.add_argument("--host", default=None, help="interface to listen on (default: root.common.web.host)")
+    ap.add_argument("--port", type=int, default=None, help="port (default: root.common.web.port)")
+    ap.add_argument("--log-dir", default=None, help="directory with the *.logs.jsonl / *.events.jsonl sinks of the runs")
+    ap.add_argument("--drop-time", type=float, default=None, help="forget a workflow this long after its last heartbeat, s")
+    a = ap.parse_args(argv)
+    srv = WebServer(host=a.host, port=a.port, drop_time=a.drop_time, log_dir=a.log_dir).start()
+    print("status server on http://%s:%d/ (POST /update, POST /service)" % (srv.host, srv.port), flush=True)
     try:
         while True:
             time.sleep(1)
     except KeyboardInterrupt:
+        pass
+    finally:
         srv.stop()
+    return 0
 
 
 if __name__ == "__main__":
-    main()
+    import sys
+    sys.exit(main())
