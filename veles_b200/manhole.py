@@ -171,7 +171,15 @@ def connect(pid_or_path, commands=None, timeout=5.0):
     return None
 
 
+def main(argv=None):
+    """``veles_manhole <pid | socket path>``: attach a terminal to the REPL of a running workflow."""
+    argv = sys.argv[1:] if argv is None else list(argv)
+    if len(argv) != 1 or argv[0] in ("-h", "--help"):
+        print("usage: python -m veles_b200.manhole <pid | socket path>")
+        return 0 if argv else 2
+    connect(argv[0])
+    return 0
+
+
 if __name__ == "__main__":
-    if len(sys.argv) < 2:
-        sys.exit("usage: python -m veles_b200.manhole <pid | socket path>")
-    connect(sys.argv[1])
+    sys.exit(main())
