@@ -24,12 +24,33 @@ tr.sel{background:#def}pre{background:#f4f4f4;padding:6px;max-height:18em;overfl
 <h3>Logs</h3>level <select id="level"><option>DEBUG</option><option selected>INFO</option><option>WARNING</option>
 <option>ERROR</option></select>text <input id="text" size="24"><label><input type="checkbox" id="all"> all sessions</label>
 <table id="logs"><thead><tr><th>time</th><th>node</th><th>level</th><th>logger</th><th>message</th></tr></thead><tbody></tbody></table>
+<h3>Timeline</h3><div id="timeline" style="overflow:auto"></div>
 <h3>Events</h3><table id="events"><thead><tr><th>time</th><th>domain</th><th>name</th><th>type</th></tr></thead><tbody></tbody></table>
 <script>
 let selected = null;
 async function ask(req){const r = await fetch('/service',{method:'POST',body:JSON.stringify(req)});return r.json();}
 function esc(s){return String(s==null?'':s).replace(/[&<>]/g,c=>({'&':'&amp;','<':'&lt;','>':'&gt;'}[c]));}
 function ts(t){return new Date(1000*t).toISOString().substr(11,12);}
+function timeline(evs){
+  // begin / end pairs of (domain, name, instance) become bars on one row per (domain, name); singles become ticks
+  const open={}, rows={}, bars=[], ticks=[];
+  let t0=Infinity, t1=-Infinity;
+  for(const e of evs){ t0=Math.min(t0,e.time); t1=Math.max(t1,e.time);
+    const key=e.domain+'.'+e.name; if(!(key in rows)) rows[key]=Object.keys(rows).length;
+    const k=key+'#'+e.instance;
+    if(e.type==='begin') open[k]=e.time;
+    else if(e.type==='end' && k in open){ bars.push([rows[key],open[k],e.time,key]); delete open[k]; }
+    else if(e.type==='single') ticks.push([rows[key],e.time,key]); }
+  for(const k in open){ const key=k.split('#')[0]; bars.push([rows[key],open[k],t1,key+' (running)']); }
+  const n=Object.keys(rows).length; if(!n||!(t1>t0)) return '';
+  const W=900,L=170,H=16, sx=t=>L+(W-L-10)*(t-t0)/(t1-t0);
+  let out=`<svg xmlns="http://www.w3.org/2000/svg" width="${W}" height="${n*H+18}" font-size="10" font-family="sans-serif">`;
+  for(const [key,r] of Object.entries(rows)) out+=`<text x="2" y="${r*H+12}">${esc(key)}</text>`;
+  for(const [r,a,b,label] of bars) out+=`<rect x="${sx(a).toFixed(1)}" y="${r*H+3}" width="${Math.max(1,sx(b)-sx(a)).toFixed(1)}" height="${H-5}" fill="#69c"><title>${esc(label)} ${(b-a).toFixed(3)} s</title></rect>`;
+  for(const [r,t,label] of ticks) out+=`<line x1="${sx(t).toFixed(1)}" x2="${sx(t).toFixed(1)}" y1="${r*H+2}" y2="${r*H+H-2}" stroke="#c33"><title>${esc(label)}</title></line>`;
+  out+=`<text x="${L}" y="${n*H+14}">0 s</text><text x="${W-60}" y="${n*H+14}">${(t1-t0).toFixed(1)} s</text></svg>`;
+  return out;
+}
 async function refresh(){
   const w = await ask({request:'workflows'});
   const tb = document.querySelector('#wf tbody'); tb.innerHTML='';
@@ -53,6 +74,8 @@ async function refresh(){
                         text:document.getElementById('text').value,limit:100});
   document.querySelector('#logs tbody').innerHTML=(lg.logs||[]).reverse().map(r=>`<tr class="${esc(r.level)}"><td>${ts(r.time)}</td>`+
     `<td>${esc(r.node)}</td><td>${esc(r.level)}</td><td>${esc(r.name)}</td><td>${esc(r.message)}</td></tr>`).join('');
+  const tl = await ask({request:'events',session:sess,limit:2000});
+  document.getElementById('timeline').innerHTML = timeline(tl.events||[]);
   const ev = await ask({request:'events',session:sess,limit:60});
   document.querySelector('#events tbody').innerHTML=(ev.events||[]).reverse().map(r=>`<tr><td>${ts(r.time)}</td>`+
     `<td>${esc(r.domain)}</td><td>${esc(r.name)}</td><td>${esc(r.type)}</td></tr>`).join('');
