@@ -418,23 +418,26 @@ def test_device_tensor_reflects_pending_host_writes():
 
 def test_pipelined_step_on_device_returns_each_loss_one_call_late():
     """Trainer.step_pipelined on the device: the loss of step i is copied to pinned memory asynchronously and returned by
-    call i + 1 (flush_loss for the last); same values as the synchronous step()."""
+    call i + 1 (flush_loss for the last); same values as the synchronous step().  (Same model / feeding as the
+    streaming case of the input-gather test above.)"""
     import torch
     from veles_b200.backends import B200Device
     from veles_b200.trainer import Trainer
-    xs = [torch.from_numpy(np.random.RandomState(k).rand(8, 4096).astype(np.float32)).pin_memory() for k in range(6)]
+    rng = np.random.default_rng(6)
+    fed = [(torch.from_numpy(rng.integers(0, 256, size=(8, 227, 227, 3), dtype=np.uint8)).pin_memory(),
+            torch.from_numpy(rng.integers(0, 1000, size=8).astype(np.int32)).pin_memory()) for _ in range(4)]
     seqs = []
     for pipelined in (False, True):
-        tr = Trainer("wide_mlp_ae", minibatch_size=8, device=B200Device(), streaming=True, seed=3, use_graph=False,
-                     layers_kwargs={"width": 64, "depth": 2, "in_features": 4096})
+        tr = Trainer("alexnet", minibatch_size=8, device=B200Device(), use_graph=False, streaming=True, n_train=32,
+                     layers_kwargs={"dropout": 0.0})
         if pipelined:
-            got = [tr.step_pipelined(x, None) for x in xs]
+            got = [tr.step_pipelined(d, l) for d, l in fed]
             assert got[0] is None
             got = got[1:] + [tr.flush_loss()]
             assert tr.flush_loss() is None
         else:
-            got = [tr.step(x, None) for x in xs]
+            got = [tr.step(d, l) for d, l in fed]
         assert all(np.isfinite(v) and v > 0 for v in got)
         seqs.append(got)
         tr.close()
-    assert np.allclose(seqs[0], seqs[1], rtol=1e-3), seqs
+    assert np.allclose(seqs[0], seqs[1], rtol=2e-3), seqs
