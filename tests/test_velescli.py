@@ -65,11 +65,11 @@ def test_cli_run_leaves_logs_and_events_the_web_status_can_query(tmp_path):
     files = sorted(os.listdir(logs))
     assert len(files) == 2 and files[0].endswith(".events.jsonl") and files[1].endswith(".logs.jsonl")
     srv = WebServer(port=0, log_dir=str(logs))
-    sessions = srv.service({"request": "sessions"})["sessions"]
-    assert len(sessions) == 1
-    found = srv.service({"request": "logs", "session": sessions[0], "text": "samples:", "level": "info"})["logs"]
+    session = files[1].rsplit("-", 1)[0]                 # <session>-<pid>.logs.jsonl
+    assert session in srv.service({"request": "sessions"})["sessions"]     # (this process' own records may be there too)
+    found = srv.service({"request": "logs", "session": session, "text": "samples:", "level": "info"})["logs"]
     assert found and found[0]["name"].endswith("Loader")
-    ev = srv.service({"request": "events", "session": sessions[0], "name": "run"})["events"]
+    ev = srv.service({"request": "events", "session": session, "name": "run"})["events"]
     assert {e["type"] for e in ev} >= {"begin", "end"}
 
 

@@ -14,6 +14,8 @@ from .mutable import Bool
 
 
 class Avatar(AcceleratedUnit, TriviallyDistributable):
+    """Mirror of another unit's attributes: clones the listed Arrays / values on every run, so that a reader (a
+    plotter, a saver) sees a consistent copy while the original keeps changing (reference: veles/avatar.py)."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -14,6 +14,8 @@ from .units import Unit
 
 
 class Downloader(Unit, TriviallyDistributable):
+    """Fetches and unpacks a dataset archive (URL or local path) into a directory unless the listed files are
+    already there."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

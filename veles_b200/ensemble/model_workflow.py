@@ -9,6 +9,8 @@ from .base_workflow import EnsembleManagerBase, EnsembleWorkflowBase
 
 
 class EnsembleModelManager(EnsembleManagerBase):
+    """Trains the N members of an ensemble as separate `veles` runs (one per GPU at a time), each on a random
+    subset of the train set, and collects their result files."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):
@@ -29,6 +31,7 @@ class EnsembleModelManager(EnsembleManagerBase):
 
 
 class EnsembleModelWorkflow(EnsembleWorkflowBase):
+    """start -> Repeater -> EnsembleModelManager -> end: the workflow behind `--ensemble-train`."""
     MANAGER = EnsembleModelManager
 
 

@@ -10,6 +10,7 @@ from .base_workflow import EnsembleManagerBase, EnsembleWorkflowBase
 
 
 class EnsembleTestManager(EnsembleManagerBase):
+    """Replays the snapshot of every ensemble member in evaluation mode and collects the outputs."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):
@@ -30,6 +31,7 @@ class EnsembleTestManager(EnsembleManagerBase):
 
 
 class EnsembleTestWorkflow(EnsembleWorkflowBase):
+    """start -> Repeater -> EnsembleTestManager -> end: the workflow behind `--ensemble-test`."""
     MANAGER = EnsembleTestManager
 
 

@@ -11,6 +11,8 @@ from .memory import Array
 
 
 class InputJoiner(AcceleratedUnit, TriviallyDistributable):
+    """Concatenates the samples of several input Arrays along the feature axis into one output (column blocks
+    copied by `vb_copy_2d` on the device)."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -12,6 +12,8 @@ from .fullbatch import FullBatchLoader, FullBatchLoaderMSEMixin
 
 
 class EnsembleLoader(FullBatchLoader):
+    """Serves the stacked outputs of ensemble members (read from their result files) as features for a
+    second-level model."""
     MAPPING = "ensemble"
     hide_from_registry = False
 
@@ -42,6 +44,7 @@ class EnsembleLoader(FullBatchLoader):
 
 
 class EnsembleLoaderMSE(FullBatchLoaderMSEMixin, EnsembleLoader):
+    """EnsembleLoader with regression targets."""
     MAPPING = "ensemble_mse"
     hide_from_registry = False
 

@@ -70,6 +70,7 @@ class ImageLoader(Loader):
 
 
 class FileListImageLoader(FileListLoaderBase, ImageLoader):
+    """Image files named by list files (`path label` per line)."""
     MAPPING = "file_list_image"
     hide_from_registry = False
 
@@ -79,6 +80,7 @@ class FileListImageLoader(FileListLoaderBase, ImageLoader):
 
 
 class AutoLabelFileImageLoader(AutoLabelFileLoader, ImageLoader):
+    """Image files found under directories; the label is derived from the path by `label_regexp`."""
     MAPPING = "auto_label_file_image"
     hide_from_registry = False
 

@@ -45,6 +45,7 @@ class FullBatchImageLoader(FullBatchLoader):
 
 
 class FullBatchFileListImageLoader(FileListLoaderBase, FullBatchImageLoader):
+    """FileListImageLoader that decodes the whole set once and keeps it resident."""
     MAPPING = "full_batch_file_list_image"
     hide_from_registry = False
 
@@ -54,6 +55,8 @@ class FullBatchFileListImageLoader(FileListLoaderBase, FullBatchImageLoader):
 
 
 class FullBatchAutoLabelFileImageLoader(AutoLabelFileLoader, FullBatchImageLoader):
+    """AutoLabelFileImageLoader that decodes the whole set once and keeps it resident (device gather per
+    minibatch)."""
     MAPPING = "full_batch_auto_label_file_image"
     hide_from_registry = False
 

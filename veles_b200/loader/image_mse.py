@@ -56,10 +56,12 @@ class ImageLoaderMSEMixin(LoaderMSEMixin):
 
 
 class FileListImageLoaderMSE(ImageLoaderMSEMixin, FileListImageLoader):
+    """FileListImageLoader with target images."""
     MAPPING = "file_list_image_mse"
     hide_from_registry = False
 
 
 class AutoLabelFileImageLoaderMSE(ImageLoaderMSEMixin, AutoLabelFileImageLoader):
+    """AutoLabelFileImageLoader with per-class target images."""
     MAPPING = "auto_label_file_image_mse"
     hide_from_registry = False

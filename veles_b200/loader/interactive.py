@@ -12,6 +12,7 @@ from .base import Loader, TEST, VALID, TRAIN
 
 
 class InteractiveLoader(Loader):
+    """Minibatches are whatever the user feeds from a Python prompt: `feed(array or path)`."""
     MAPPING = "interactive"
     hide_from_registry = False
 

@@ -9,6 +9,7 @@ from .fullbatch import FullBatchLoader
 
 
 class HDF5Loader(FullBatchLoader):
+    """Samples and labels from HDF5 files (needs h5py)."""
     MAPPING = "full_batch_hdf5"
     hide_from_registry = False
 

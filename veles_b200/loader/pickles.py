@@ -11,6 +11,7 @@ from .fullbatch import FullBatchLoader
 
 
 class PicklesImageFullBatchLoader(FullBatchLoader):
+    """Whole data set from pickle files of (images, labels), kept resident."""
     MAPPING = "full_batch_pickles_image"
     hide_from_registry = False
 

@@ -12,6 +12,8 @@ from .interactive import InteractiveLoader
 
 
 class RestfulLoader(InteractiveLoader):
+    """Collects samples posted to the RESTful API into minibatches (until full or `max_response_time`) and
+    hands results back to the requests."""
     MAPPING = "restful"
     hide_from_registry = False
 

@@ -24,6 +24,8 @@ MAGIC = b"VB2MB1"
 
 
 class MinibatchesSaver(Unit, TriviallyDistributable):
+    """Writes every served minibatch to a chunked compressed stream with an offset table (read back by
+    MinibatchesLoader)."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -16,6 +16,8 @@ from .base import Loader, TRAIN, VALID, TEST
 
 
 class StreamLoader(Loader):
+    """Minibatches fed by the host program: two pinned staging slots, uploads on their own stream, gather /
+    normalise on the device (`Trainer.feed`)."""
     MAPPING = "stream"
     hide_from_registry = False
 

@@ -12,6 +12,7 @@ from .memory import Array
 
 
 class MeanDispNormalizer(AcceleratedUnit, TriviallyDistributable):
+    """output = (input - mean) * rdisp per feature, as a unit (device kernel `vb_mean_disp_normalize`)."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -12,6 +12,8 @@ from .backend import BackendRegistry
 
 
 class Publisher(Unit, TriviallyDistributable):
+    """Collects the facts of a finished run (metrics, timings, configuration, plots, graph) and renders them
+    through the configured report back-ends."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -25,6 +25,8 @@ class _Pending(object):
 
 
 class RESTfulAPI(Unit, TriviallyDistributable):
+    """HTTP endpoint that turns a posted sample into a request for the RestfulLoader and answers with the
+    model's output."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -16,6 +16,7 @@ from .network_common import machine_id
 
 
 class ZeroMQLoader(InteractiveLoader):
+    """Samples arrive as pickled messages on a ZeroMQ socket; one job per message."""
     MAPPING = "zeromq"
     hide_from_registry = False
     negotiates_on_connect = True

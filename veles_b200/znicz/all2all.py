@@ -148,24 +148,28 @@ class All2All(Forward):
 
 
 class All2AllTanh(All2All):
+    """Fully connected layer with y = 1.7159 tanh(0.6666 (x W^T + b))."""
     MAPPING = {"all2all_tanh"}
     ACTIVATION = 1
     __id__ = "b3a2bd5c-3c01-46ef-978a-fef22e008f31"
 
 
 class All2AllRELU(All2All):
+    """Fully connected layer with softplus activation y = log(1 + exp(x W^T + b))."""
     MAPPING = {"all2all_relu"}
     ACTIVATION = 3
     __id__ = "5b7f36d8-f8c8-4eb7-8af3-75eb3cfca3fe"
 
 
 class All2AllStrictRELU(All2All):
+    """Fully connected layer with y = max(0, x W^T + b)."""
     MAPPING = {"all2all_str"}
     ACTIVATION = 4
     __id__ = "fe63baf0-4fe4-4cf3-bafb-ef1215bf27a8"
 
 
 class All2AllSigmoid(All2All):
+    """Fully connected layer with logistic activation."""
     MAPPING = {"all2all_sigmoid"}
     ACTIVATION = 2
     __id__ = "a27974ec-1764-4944-925d-4862de237881"

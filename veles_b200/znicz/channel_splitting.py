@@ -36,12 +36,14 @@ class _Permute(ForwardBase):
 
 
 class ChannelSplitter(_Permute):
+    """Splits the channel axis of an NHWC tensor into groups (one output per group)."""
     hide_from_registry = False
     MAPPING = {"channel_splitter"}
     PERM = (0, 3, 1, 2)
 
 
 class ChannelMerger(_Permute):
+    """Concatenates tensors along the channel axis."""
     hide_from_registry = False
     MAPPING = {"channel_merger"}
     PERM = (0, 2, 3, 1)
@@ -74,12 +76,14 @@ class _GDPermute(GDBase):
 
 
 class GDChannelSplitter(_GDPermute):
+    """Backward pass of ChannelSplitter."""
     hide_from_registry = False
     MAPPING = {"channel_splitter"}
     PERM = (0, 2, 3, 1)
 
 
 class GDChannelMerger(_GDPermute):
+    """Backward pass of ChannelMerger."""
     hide_from_registry = False
     MAPPING = {"channel_merger"}
     PERM = (0, 3, 1, 2)

@@ -56,6 +56,8 @@ def numpy_col2im(dcols, shape, ky, kx, sy, sx, pl, pt, pr, pb, groups=1):
 
 
 class Conv(Forward):
+    """Convolutional layer, linear output: NHWC input, `n_kernels` filters of `ky` x `kx`, `sliding`,
+    `padding`, `grouping`; implicit-GEMM tcgen05 kernels on the device."""
     hide_from_registry = False
     MAPPING = {"conv"}
     ACTIVATION = 0
@@ -278,24 +280,28 @@ class Conv(Forward):
 
 
 class ConvTanh(Conv):
+    """Convolutional layer with scaled tanh activation."""
     MAPPING = {"conv_tanh"}
     ACTIVATION = 1
     __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0002"
 
 
 class ConvRELU(Conv):
+    """Convolutional layer with softplus activation."""
     MAPPING = {"conv_relu"}
     ACTIVATION = 3
     __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0004"
 
 
 class ConvStrictRELU(Conv):
+    """Convolutional layer with y = max(0, .)."""
     MAPPING = {"conv_str"}
     ACTIVATION = 4
     __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0005"
 
 
 class ConvSigmoid(Conv):
+    """Convolutional layer with logistic activation."""
     MAPPING = {"conv_sigmoid"}
     ACTIVATION = 2
     __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0003"

@@ -8,6 +8,7 @@ from .nn_units import ForwardBase, GDBase
 
 
 class Cutter(ForwardBase):
+    """Crops a window (`padding` = left, top, right, bottom) out of an NHWC tensor."""
     hide_from_registry = False
     MAPPING = {"cutter"}
 
@@ -55,6 +56,7 @@ class Cutter(ForwardBase):
 
 
 class GDCutter(GDBase):
+    """Backward pass of Cutter (zero-pads the gradient)."""
     hide_from_registry = False
     MAPPING = {"cutter"}
 
@@ -127,6 +129,7 @@ class Cutter1D(ForwardBase):
 
 
 class GDCutter1D(GDBase):
+    """Backward pass of Cutter1D."""
     hide_from_registry = False
     MAPPING = {"cutter_1d"}
 

@@ -14,6 +14,7 @@ from .nn_units import Forward, GradientDescentBase
 
 
 class Deconv(Forward):
+    """Transposed convolution sharing (or owning) the weights of a Conv layer: convolutional auto-encoders."""
     hide_from_registry = False
     MAPPING = {"deconv"}
     ACTIVATION = 0
@@ -106,6 +107,7 @@ class Deconv(Forward):
 
 
 class GDDeconv(GradientDescentBase):
+    """Backward pass of Deconv."""
     hide_from_registry = False
     MAPPING = {"deconv"}
 

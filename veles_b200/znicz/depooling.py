@@ -8,6 +8,7 @@ from .nn_units import ForwardBase, GDBase
 
 
 class Depooling(ForwardBase):
+    """Puts pooled values back at the positions a max pooling layer took them from."""
     hide_from_registry = False
     MAPPING = {"depooling"}
 
@@ -43,6 +44,7 @@ class Depooling(ForwardBase):
 
 
 class GDDepooling(GDBase):
+    """Backward pass of Depooling."""
     hide_from_registry = False
     MAPPING = {"depooling"}
 

@@ -16,6 +16,8 @@ from .nn_units import ForwardBase, GDBase
 
 
 class DropoutForward(ForwardBase):
+    """Zeroes a `dropout_ratio` share of the inputs (mask from in-kernel xorshift128+ states) and rescales the
+    rest; identity in evaluation."""
     hide_from_registry = False
     MAPPING = {"dropout"}
     LOADER_ATTRS = ("minibatch_class",)
@@ -100,6 +102,7 @@ class DropoutForward(ForwardBase):
 
 
 class DropoutBackward(GDBase):
+    """Applies the forward mask (regenerated from the saved generator states) to the gradient."""
     hide_from_registry = False
     MAPPING = {"dropout"}
 

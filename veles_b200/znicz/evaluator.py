@@ -42,6 +42,8 @@ class EvaluatorBase(AcceleratedUnit, TriviallyDistributable):
 
 
 class EvaluatorSoftmax(EvaluatorBase):
+    """Cross-entropy gradient, error count, loss sum, confusion matrix and max error from softmax outputs and
+    labels; counters accumulate on the device."""
     hide_from_registry = False
     MAPPING = "evaluator_softmax"
     LOSS = "softmax"
@@ -140,6 +142,7 @@ class EvaluatorSoftmax(EvaluatorBase):
 
 
 class EvaluatorMSE(EvaluatorBase):
+    """Squared-error gradient and metrics (sum, max, min of per-sample MSE) from outputs and targets."""
     hide_from_registry = False
     MAPPING = "evaluator_mse"
     LOSS = "mse"

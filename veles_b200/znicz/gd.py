@@ -19,6 +19,8 @@ from .nn_units import GradientDescentBase, act_deriv_numpy
 
 
 class GradientDescent(GradientDescentBase):
+    """Backward pass and update of a fully connected linear layer: err_input GEMM, weight-gradient GEMM, bias
+    sums, Znicz momentum / decay update (fused on the device)."""
     hide_from_registry = False
     MAPPING = {"all2all"}
     ACTIVATION = 0
@@ -253,21 +255,25 @@ class GradientDescent(GradientDescentBase):
 
 
 class GDTanh(GradientDescent):
+    """GradientDescent for All2AllTanh."""
     MAPPING = {"all2all_tanh"}
     ACTIVATION = 1
 
 
 class GDRELU(GradientDescent):
+    """GradientDescent for All2AllRELU."""
     MAPPING = {"all2all_relu"}
     ACTIVATION = 3
 
 
 class GDStrictRELU(GradientDescent):
+    """GradientDescent for All2AllStrictRELU."""
     MAPPING = {"all2all_str"}
     ACTIVATION = 4
 
 
 class GDSigmoid(GradientDescent):
+    """GradientDescent for All2AllSigmoid."""
     MAPPING = {"all2all_sigmoid"}
     ACTIVATION = 2
 

@@ -17,6 +17,8 @@ from .nn_units import GradientDescentBase, act_deriv_numpy
 
 
 class GradientDescentConv(GradientDescentBase):
+    """Backward pass and update of a convolutional layer: err_input and weight-gradient as implicit GEMMs, bias
+    sums, Znicz update."""
     hide_from_registry = False
     MAPPING = {"conv"}
     ACTIVATION = 0
@@ -187,20 +189,24 @@ class GradientDescentConv(GradientDescentBase):
 
 
 class GDTanhConv(GradientDescentConv):
+    """GradientDescentConv for ConvTanh."""
     MAPPING = {"conv_tanh"}
     ACTIVATION = 1
 
 
 class GDRELUConv(GradientDescentConv):
+    """GradientDescentConv for ConvRELU."""
     MAPPING = {"conv_relu"}
     ACTIVATION = 3
 
 
 class GDStrictRELUConv(GradientDescentConv):
+    """GradientDescentConv for ConvStrictRELU."""
     MAPPING = {"conv_str"}
     ACTIVATION = 4
 
 
 class GDSigmoidConv(GradientDescentConv):
+    """GradientDescentConv for ConvSigmoid."""
     MAPPING = {"conv_sigmoid"}
     ACTIVATION = 2

@@ -110,16 +110,19 @@ class GDPooling(GDBase):
 
 
 class GDMaxPooling(GDPooling):
+    """Backward pass of max (and stochastic) pooling: routes each gradient to its window's recorded position."""
     hide_from_registry = False
     MAPPING = {"max_pooling", "stochastic_pooling", "stochastic_abs_pooling"}
 
 
 class GDMaxAbsPooling(GDPooling):
+    """Backward pass of max-abs pooling."""
     hide_from_registry = False
     MAPPING = {"maxabs_pooling"}
 
 
 class GDAvgPooling(GDPooling):
+    """Backward pass of average pooling."""
     hide_from_registry = False
     MAPPING = {"avg_pooling"}
 

@@ -13,6 +13,7 @@ from ..units import Unit
 
 
 class ImageSaver(Unit, TriviallyDistributable):
+    """Writes misclassified (or all) samples of a minibatch as image files grouped by class / outcome."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -22,6 +22,7 @@ class KohonenBase(AcceleratedUnit, TriviallyDistributable):
 
 
 class KohonenForward(KohonenBase):
+    """Winner lookup of a Kohonen self-organising map."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):
@@ -50,6 +51,7 @@ class KohonenForward(KohonenBase):
 
 
 class KohonenTrainer(KohonenBase):
+    """Kohonen map training: neighbourhood-weighted pull of the weights toward each sample."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -70,6 +70,8 @@ POLICIES = {"exp": ExpPolicy, "fixed": FixedAdjustPolicy, "step_exp": StepExpPol
 
 
 class LearningRateAdjust(Unit, TriviallyDistributable):
+    """Applies learning-rate schedules (exp, inv, step, arbitrary-step policies) to GD units as training
+    proceeds."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -19,6 +19,7 @@ def _window_sums(sq, n):
 
 
 class LRNormalizerForward(ForwardBase):
+    """Local response normalisation across channels: y = x (k + alpha sum_{window} x^2)^-beta."""
     hide_from_registry = False
     MAPPING = {"norm"}
     __id__ = "0e4d2e9a-6a0b-4c1b-9a5f-1c4b9c7e0021"
@@ -61,6 +62,8 @@ class LRNormalizerForward(ForwardBase):
 
 
 class LRNormalizerBackward(GDBase):
+    """Backward pass of local response normalisation (can also apply the previous layer's activation derivative
+    and leave that layer's bias-gradient sums)."""
     hide_from_registry = False
     MAPPING = {"norm"}
     CAN_FUSE_PREV_DERIVATIVE = True

@@ -160,6 +160,7 @@ class Pooling(ForwardBase):
 
 
 class MaxPooling(Pooling):
+    """Max pooling; records the chosen position of every window for the backward pass."""
     hide_from_registry = False
     MAPPING = {"max_pooling"}
     KIND = "max"
@@ -167,6 +168,7 @@ class MaxPooling(Pooling):
 
 
 class MaxAbsPooling(Pooling):
+    """Pooling that keeps the element of largest magnitude (with its sign)."""
     hide_from_registry = False
     MAPPING = {"maxabs_pooling"}
     KIND = "maxabs"
@@ -174,6 +176,7 @@ class MaxAbsPooling(Pooling):
 
 
 class AvgPooling(Pooling):
+    """Average pooling over `ky` x `kx` windows with `sliding`."""
     hide_from_registry = False
     MAPPING = {"avg_pooling"}
     KIND = "avg"
@@ -189,12 +192,14 @@ class StochasticPoolingBase(Pooling):
 
 
 class StochasticPooling(StochasticPoolingBase):
+    """Pooling that samples an element of the window with probability proportional to its value."""
     hide_from_registry = False
     MAPPING = {"stochastic_pooling"}
     KIND = "stochastic"
 
 
 class StochasticAbsPooling(StochasticPoolingBase):
+    """Stochastic pooling on magnitudes."""
     hide_from_registry = False
     MAPPING = {"stochastic_abs_pooling"}
     KIND = "stochastic_abs"
@@ -246,5 +251,6 @@ class StochasticPoolingDepooling(StochasticPoolingBase):
 
 
 class StochasticAbsPoolingDepooling(StochasticPoolingDepooling):
+    """Stochastic-abs pooling immediately undone in place (a sparsifying regulariser)."""
     MAPPING = {"stochastic_abs_pool_depool"}
     KIND = "stochastic_abs"

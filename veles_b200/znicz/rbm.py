@@ -12,6 +12,7 @@ from .. import prng
 
 
 class RBM(AcceleratedUnit, TriviallyDistributable):
+    """Restricted Boltzmann machine layer trained by contrastive divergence."""
     hide_from_registry = False
 
     def __init__(self, workflow, **kwargs):

@@ -364,6 +364,7 @@ class GDRecurrentBase(GradientDescentBase):
 
 
 class GDRNN(GDRecurrentBase):
+    """Back-propagation through time for the simple recurrent layer."""
     hide_from_registry = False
     MAPPING = {"rnn"}
 
@@ -376,6 +377,7 @@ class GDRNN(GDRecurrentBase):
 
 
 class GDLSTM(GDRecurrentBase):
+    """Back-propagation through time for the LSTM layer."""
     hide_from_registry = False
     MAPPING = {"lstm"}
 

@@ -9,6 +9,8 @@ from .gd import GradientDescent
 
 
 class ResizableAll2All(All2All):
+    """Fully connected layer whose number of outputs can be changed between runs (weights are extended or
+    cropped)."""
     TRANSPOSED_OK = False
     MAPPING = {"all2all_resizable"}
 
@@ -39,4 +41,5 @@ class ResizableAll2All(All2All):
 
 
 class GDResizableAll2All(GradientDescent):
+    """GradientDescent for ResizableAll2All."""
     MAPPING = {"all2all_resizable"}

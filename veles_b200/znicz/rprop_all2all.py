@@ -10,11 +10,13 @@ from .gd import GradientDescent
 
 
 class RPropAll2All(All2All):
+    """Fully connected layer trained by resilient propagation."""
     TRANSPOSED_OK = False
     MAPPING = {"rprop_all2all"}
 
 
 class GDRProp(GradientDescent):
+    """RProp update: per-weight step sizes grown / shrunk by the sign history of the gradient."""
     MAPPING = {"rprop_all2all"}
 
     def __init__(self, workflow, **kwargs):

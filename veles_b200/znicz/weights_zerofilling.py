@@ -9,6 +9,7 @@ from .nn_units import ForwardBase, GDBase
 
 
 class ZeroFiller(ForwardBase):
+    """Keeps the cross-group weights of a grouped layer at zero after every update."""
     hide_from_registry = False
     MAPPING = {"zero_filter"}
 
