@@ -14,6 +14,7 @@ from .units import Unit
 
 
 class Shell(Unit, TriviallyDistributable):
+    """Console with the workflow in scope, opened by typing ``i`` + Enter while the workflow runs."""
     hide_from_registry = False
     KEY = "i"
     BANNER = ("veles_b200 interactive console: `workflow`, `units`, `root` are in scope; "
