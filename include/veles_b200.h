@@ -301,6 +301,18 @@ int vb_ortho_grad(const float* w, long long ldw, float* grad, long long ldg, con
 /* Halo-tile convolution tuning / test hook: sub-tiles per CTA tile (0 = choose, 1, 2); resident weights (-1 = choose,
  * 0 = never, 1 = whenever they fit). */
 int vb_conv_halo_set_options(int mt, int resident);
+/* Profiling hook of the halo-tile kernel: a device buffer of 24 x 8 long longs that CTA 0 fills with clock64 stamps at
+ * the hand-over points of its first 24 tiles (scripts/trace_halo.py); null switches it off. */
+int vb_conv_halo_set_trace(long long* buf);
+/* Weight-gradient GEMM dW = A^T B whose epilogue applies the Znicz momentum step to w / vel (and refreshes the bf16
+ * shadow) instead of storing the gradient; opt-in (measured slower than GEMM + vb_gd_update on this machine). */
+int vb_gemm_bf16_fused_gd(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major,
+                          int M, int N, int K, float* w, long long ldw, float* vel, void* shadow, long long ld_shadow,
+                          float lr, float wd, float l1_vs_l2, float moment, float alpha, int block_n,
+                          cudaStream_t stream);
+/* 1: every kernel of the library is launched with programmatic stream serialisation from now on (each kernel starts
+ * with griddepcontrol.wait, so results are unchanged); 0: ordinary launches.  Returns the previous value. */
+int vb_set_pdl(int on);
 
 #ifdef __cplusplus
 }
