@@ -108,6 +108,23 @@ def test_native_logger_through_the_c_api():
         L.veles_native_set_log_sink(None, None)
 
 
+def test_header_declares_every_exported_kernel_entry_point():
+    """include/veles_b200.h is the C ABI of libveles_b200.so: every exported ``vb_*`` symbol is declared there and
+    every declared one is exported."""
+    import re
+    import shutil
+    lib = os.path.join(ROOT, "veles_b200", "lib", "libveles_b200.so")
+    if not os.path.exists(lib) or shutil.which("nm") is None:
+        pytest.skip("kernel library or nm not available")
+    out = subprocess.run(["nm", "-D", "--defined-only", lib], stdout=subprocess.PIPE, check=True).stdout.decode()
+    exported = {ln.split()[-1] for ln in out.splitlines() if ln.split() and ln.split()[-1].startswith("vb_")}
+    header = open(os.path.join(ROOT, "include", "veles_b200.h")).read()
+    declared = set(re.findall(r"\b(vb_[a-z0-9_]+)\s*\(", header))
+    assert exported - declared == set(), sorted(exported - declared)
+    assert declared - exported == set(), sorted(declared - exported)
+    assert len(exported) >= 70
+
+
 def _native(lib_path):
     L = ctypes.CDLL(lib_path)
     L.veles_native_load.restype = ctypes.c_void_p
